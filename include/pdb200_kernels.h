@@ -1,0 +1,67 @@
+/* C ABI of libpdb200_kernels.so - hand-written sm_100a kernels of the paddle_b200 framework.
+ *
+ * Conventions: every entry point returns 0 on success, a cudaError_t value or -1 on failure (message via
+ * pdb200_last_error(), thread-local).  `stream` is a cudaStream_t passed as void*.  dtype codes: 0 = float32,
+ * 1 = bfloat16, 2 = float16.  Pointers are device pointers unless noted.  No entry point synchronises the
+ * device.  This header is also parsed by paddle_b200/lib/__init__.py to build the ctypes signatures, so keep one
+ * declaration per statement and only the scalar / pointer types already used here.
+ */
+#ifndef PDB200_KERNELS_H_
+#define PDB200_KERNELS_H_
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+#define PDB_API
+
+PDB_API const char* pdb200_last_error();
+PDB_API int pdb200_abi_version();
+PDB_API int pdb200_sm_count();
+
+/* K18/K19 fused RMSNorm / LayerNorm (reference: phi/kernels/gpu/rms_norm_kernel.cu:420-520, rms_norm_funcs.h:507-942,
+ * layer_norm_kernel.cu).  residual (optional): y = norm(x + residual), residual_out = x + residual. */
+PDB_API int pdb200_norm_fwd(const void* x, const void* residual, const void* w, const void* b, void* y, void* residual_out, float* mean, float* rstd, int64_t rows, int64_t cols, float eps, int x_dtype, int w_is_f32, int is_layernorm, void* stream);
+PDB_API int64_t pdb200_norm_bwd_scratch_bytes(int64_t rows, int64_t cols, int is_layernorm);
+PDB_API int pdb200_norm_bwd(const void* dy, const void* x, const void* w, const float* mean, const float* rstd, void* dx, void* dw, void* db, void* scratch, int64_t scratch_bytes, int64_t rows, int64_t cols, int x_dtype, int w_is_f32, int is_layernorm, void* stream);
+
+/* K21 SwiGLU (reference: phi/kernels/gpu/swiglu_kernel.cu, swiglu_grad_kernel.cu); ld* are row strides in elements */
+PDB_API int pdb200_swiglu_fwd(const void* x, const void* y, void* out, int64_t rows, int64_t H, int64_t ldx, int64_t ldy, int dtype, void* stream);
+PDB_API int pdb200_swiglu_bwd(const void* x, const void* y, const void* dout, void* dx, void* dy, int64_t rows, int64_t H, int64_t ldx, int64_t ldy, int64_t lddx, int64_t lddy, int dtype, void* stream);
+
+/* K20 fused rotary embedding (reference: phi/kernels/fusion/gpu/fused_rope_kernel.cu, fused_rope_utils.h:235-426).
+ * rotate_half=1: halves rotate together (Paddle use_neox_rotary_style=False); 0: adjacent pairs (=True).
+ * sign=+1 forward, -1 backward. sin/cos: fp32 [positions, d] or both null (computed from base). */
+PDB_API int pdb200_rope(const void* q, const void* k, const void* v, void* oq, void* ok, void* ov, int hq, int hk, int hv, const float* sin_t, const float* cos_t, const int64_t* pos_ids, int64_t batch, int64_t seq, int d, int rotate_half, int time_major, float base, float sign, int dtype, void* stream);
+
+/* K22 fused bias + activation (reference: phi/kernels/fusion/gpu/fused_bias_act_kernel.cu:30-545).
+ * act: 0 gelu, 1 relu, 2 swiglu, 3 geglu, 4 silu, 5 identity; GLU variants read 2*cols_out input columns. */
+PDB_API int pdb200_bias_act(const void* x, const void* bias, void* out, int64_t rows, int64_t cols_out, int act, int dtype, void* stream);
+
+/* K12/K15 multi-tensor optimizer kernels (reference: phi/kernels/gpu/adamw_kernel.cu:35-372, fused_adam_kernel.cu,
+ * squared_l2_norm_kernel.cu, amp_kernel.cu).  table: MTDesc[ntensors] (64 B each, see csrc/kernels/optim.cu);
+ * chunk_map: int32 pairs (tensor index, chunk index) - one CTA per pair, pdb200_mt_chunk_elems() elements each. */
+PDB_API int pdb200_mt_chunk_elems();
+PDB_API int pdb200_adamw_multi(const void* table, const void* chunk_map, int n_chunks, float lr, float beta1, float beta2, float eps, float weight_decay, float beta1_pow, float beta2_pow, const float* beta_pows_dev, const float* grad_scale, const float* found_inf, void* stream);
+PDB_API int pdb200_momentum_multi(const void* table, const void* chunk_map, int n_chunks, float lr, float mu, float l2_decay, int nesterov, const float* grad_scale, const float* found_inf, void* stream);
+PDB_API int pdb200_l2norm_multi(const void* table, const void* chunk_map, int n_chunks, float* scratch, int64_t scratch_floats, float* out, int accumulate, void* stream);
+PDB_API int pdb200_unscale_check_multi(const void* table, const void* chunk_map, int n_chunks, const float* inv_scale, float* found_inf, void* stream);
+
+/* K8 softmax cross-entropy, local / per-rank part (reference: phi/kernels/gpu/cross_entropy_kernel.cu,
+ * fluid/operators/collective/c_softmax_with_cross_entropy_op.cu:47-114,133-340). stats: [rows,3] = max,sumexp,target */
+PDB_API int pdb200_ce_fwd(const void* logits, const int64_t* labels, float* stats, float* loss, float* lse, int64_t rows, int64_t V, int64_t ld, int64_t vocab_start, int64_t ignore_index, int dtype, void* stream);
+PDB_API int pdb200_ce_combine(const float* all_stats, const int64_t* labels, float* loss, float* lse, int64_t rows, int nranks, int64_t ignore_index, void* stream);
+PDB_API int pdb200_ce_bwd(const void* logits, const int64_t* labels, const float* lse, const float* dloss, float dloss_scalar, void* dlogits, int64_t rows, int64_t V, int64_t ld, int64_t vocab_start, int64_t ignore_index, int dtype, void* stream);
+
+/* K11 MoE routing (reference: phi/kernels/gpu/{number_count,assign_pos,limit_by_capacity,prune_gate_by_capacity,
+ * random_routing}_kernel.cu) */
+PDB_API int pdb200_number_count(const int64_t* ids, int64_t n, int64_t* out, int n_bins, void* stream);
+PDB_API int pdb200_assign_pos(const int64_t* ids, int64_t n, const int64_t* cum_count, int n_bins, int64_t* out, void* stream);
+PDB_API int pdb200_limit_by_capacity(const int64_t* expert_count, const int64_t* capacity, int64_t* out, int n_expert, int n_worker, void* stream);
+PDB_API int pdb200_prune_gate_by_capacity(const int64_t* gate, int64_t* new_gate, const int64_t* expert_count, int* remaining_i32, int n_bins, int64_t n, void* stream);
+PDB_API int pdb200_random_routing(int64_t* topk_idx, const void* topk_val, const void* prob, int64_t n, int dtype, void* stream);
+PDB_API int pdb200_topk_softmax(const void* logits, int64_t tokens, int E, int k, int renorm, float* weights, int64_t* idx, int64_t* counts, int dtype, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PDB200_KERNELS_H_ */

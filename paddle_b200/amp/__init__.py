@@ -1,0 +1,212 @@
+"""paddle.amp (reference: python/paddle/amp/{auto_cast,grad_scaler}.py; kernels paddle/phi/kernels/gpu/amp_kernel.cu).
+
+O1 = torch.autocast with the white/black lists; O2 = parameters cast by ``decorate`` + fp32 master weights inside
+the optimizer (``multi_precision``).  GradScaler keeps scale / found_inf on the device: unscale+check is one
+multi-tensor kernel, the optimizer kernel reads found_inf to skip, and the scale update is a few device ops -
+there is no ``.item()`` in the step."""
+from __future__ import annotations
+
+import contextlib
+
+import torch
+
+from .. import ops
+from ..framework import dtype as _dt
+from ..framework.place import current_place
+from . import debugging  # noqa: F401
+
+_state = {"enable": False, "level": "O0", "dtype": "float32"}
+
+
+def is_float16_supported(device=None):
+    return torch.cuda.is_available()
+
+
+def is_bfloat16_supported(device=None):
+    return True
+
+
+@contextlib.contextmanager
+def auto_cast(enable=True, custom_white_list=None, custom_black_list=None, level="O1", dtype="float16", use_promote=True):
+    if level not in ("O0", "OD", "O1", "O2"):
+        raise ValueError("level should be O0, OD, O1 or O2.")
+    td = _dt.to_torch_dtype(dtype)
+    active = bool(enable) and level != "O0"
+    dev = "cuda" if current_place().is_gpu_place() else "cpu"
+    if dev == "cpu" and td == torch.float16:
+        td = torch.bfloat16
+    prev = dict(_state)
+    _state.update(enable=active, level=level if active else "O0", dtype=_dt.convert_dtype(td))
+    try:
+        with torch.autocast(device_type=dev, dtype=td, enabled=active):
+            yield
+    finally:
+        _state.clear()
+        _state.update(prev)
+
+
+amp_guard = auto_cast
+
+
+def amp_state():
+    return dict(_state)
+
+
+def decorate(models, optimizers=None, level="O1", dtype="float16", master_weight=None, save_dtype=None,
+             master_grad=False, excluded_layers=None):
+    """O2: cast model parameters to ``dtype`` (norm layers stay fp32 unless bf16, like the reference keeps
+    BatchNorm/LayerNorm in fp32 for fp16) and switch the optimizers to multi_precision (fp32 master weights)."""
+    single_model = not isinstance(models, (list, tuple))
+    model_list = [models] if single_model else list(models)
+    if level == "O2":
+        from ..nn.layer.common import _BatchNormBase, LayerNorm
+        td = _dt.to_torch_dtype(dtype)
+        excluded = tuple(excluded_layers) if excluded_layers else ()
+        for m in model_list:
+            keep = set()
+            for sub in m.sublayers(include_self=True):
+                is_excl = any((isinstance(e, type) and isinstance(sub, e)) or sub is e for e in excluded)
+                if isinstance(sub, _BatchNormBase) or (td == torch.float16 and isinstance(sub, LayerNorm)) or is_excl:
+                    for p in sub.parameters(include_sublayers=False):
+                        keep.add(id(p))
+            for p in m.parameters():
+                if id(p) not in keep and p.is_floating_point():
+                    p.data = p.data.to(td)
+            if master_grad:
+                from ..distributed.fleet.utils.mix_precision_utils import MixPrecisionLayer  # noqa: F401
+                for p in m.parameters():
+                    p._fuse_main_grad = False
+    if optimizers is None:
+        return models
+    single_opt = not isinstance(optimizers, (list, tuple))
+    opt_list = [optimizers] if single_opt else list(optimizers)
+    if level == "O2" and master_weight is not False:
+        for o in opt_list:
+            o._multi_precision = True
+    return (models, optimizers)
+
+
+class GradScaler:
+    def __init__(self, enable=True, init_loss_scaling=2.0 ** 16, incr_ratio=2.0, decr_ratio=0.5,
+                 incr_every_n_steps=2000, decr_every_n_nan_or_inf=1, use_dynamic_loss_scaling=True):
+        self._enable = bool(enable)
+        self._init_loss_scaling = float(init_loss_scaling)
+        self._incr_ratio, self._decr_ratio = float(incr_ratio), float(decr_ratio)
+        self._incr_every_n_steps, self._decr_every_n_nan_or_inf = int(incr_every_n_steps), int(decr_every_n_nan_or_inf)
+        self._use_dynamic_loss_scaling = bool(use_dynamic_loss_scaling)
+        self._scale = None
+        self._found_inf = None
+        self._good = None
+        self._bad = None
+        self._unscaled = set()
+        self._tables = {}
+
+    # -- device state is created lazily on the device of the first loss
+    def _init_state(self, device):
+        if self._scale is None:
+            self._scale = torch.full((1,), self._init_loss_scaling, dtype=torch.float32, device=device)
+            self._found_inf = torch.zeros(1, dtype=torch.float32, device=device)
+            self._good = torch.zeros(1, dtype=torch.int32, device=device)
+            self._bad = torch.zeros(1, dtype=torch.int32, device=device)
+
+    def scale(self, var):
+        if not self._enable:
+            return var
+        self._init_state(var.device)
+        return var * self._scale.to(var.dtype)
+
+    @torch.no_grad()
+    def unscale_(self, optimizer):
+        if not self._enable or id(optimizer) in self._unscaled:
+            return
+        grads = [g for _, g in optimizer._collect_params_grads()]
+        if not grads:
+            return
+        self._init_state(grads[0].device)
+        inv = (1.0 / self._scale).float()
+        from ..ops._util import use_native
+        if use_native(grads[0]):
+            tab = ops.grads_table(grads)
+            ops.unscale_and_check(tab, inv, self._found_inf)
+        else:
+            for g in grads:
+                bad = ~torch.isfinite(g.float()).all()
+                self._found_inf.copy_(torch.maximum(self._found_inf, bad.float().reshape(1).to(self._found_inf.device)))
+                g.mul_(inv.to(g.dtype).to(g.device))
+        self._sync_found_inf(optimizer)
+        self._unscaled.add(id(optimizer))
+
+    def _sync_found_inf(self, optimizer):
+        """Hook for HybridParallelGradScaler: all-reduce MAX of found_inf across the check group."""
+
+    def step(self, optimizer):
+        if not self._enable:
+            return optimizer.step()
+        self.unscale_(optimizer)
+        optimizer._found_inf = self._found_inf
+        try:
+            optimizer.step()
+        finally:
+            optimizer._found_inf = None
+        self._unscaled.discard(id(optimizer))
+
+    def minimize(self, optimizer, *args, **kwargs):
+        self.step(optimizer)
+        self.update()
+
+    @torch.no_grad()
+    def update(self):
+        if not self._enable or self._scale is None:
+            return
+        if self._use_dynamic_loss_scaling:
+            inf = self._found_inf > 0
+            self._bad.copy_(torch.where(inf, self._bad + 1, torch.zeros_like(self._bad)))
+            self._good.copy_(torch.where(inf, torch.zeros_like(self._good), self._good + 1))
+            dec = self._bad >= self._decr_every_n_nan_or_inf
+            inc = self._good >= self._incr_every_n_steps
+            new_scale = torch.where(dec, torch.clamp(self._scale * self._decr_ratio, min=1.0),
+                                    torch.where(inc, self._scale * self._incr_ratio, self._scale))
+            self._scale.copy_(new_scale)
+            self._bad.copy_(torch.where(dec, torch.zeros_like(self._bad), self._bad))
+            self._good.copy_(torch.where(inc, torch.zeros_like(self._good), self._good))
+        self._found_inf.zero_()
+
+    def is_enable(self):
+        return self._enable
+
+    def is_use_dynamic_loss_scaling(self):
+        return self._use_dynamic_loss_scaling
+
+    def get_init_loss_scaling(self):
+        return self._init_loss_scaling
+
+    def set_init_loss_scaling(self, v):
+        self._init_loss_scaling = float(v)
+        if self._scale is not None:
+            self._scale.fill_(float(v))
+
+    def get_loss_scaling(self):
+        return self._scale if self._scale is not None else torch.tensor([self._init_loss_scaling])
+
+    def state_dict(self):
+        if not self._enable:
+            return {}
+        return {"scale": self.get_loss_scaling().detach().cpu().numpy(), "incr_ratio": self._incr_ratio,
+                "decr_ratio": self._decr_ratio, "incr_every_n_steps": self._incr_every_n_steps,
+                "decr_every_n_nan_or_inf": self._decr_every_n_nan_or_inf,
+                "incr_count": int(self._good.item()) if self._good is not None else 0,
+                "decr_count": int(self._bad.item()) if self._bad is not None else 0,
+                "use_dynamic_loss_scaling": self._use_dynamic_loss_scaling}
+
+    def load_state_dict(self, sd):
+        if not sd:
+            return
+        self._init_loss_scaling = float(torch.as_tensor(sd["scale"]).reshape(-1)[0])
+        if self._scale is not None:
+            self._scale.fill_(self._init_loss_scaling)
+        self._incr_ratio, self._decr_ratio = sd["incr_ratio"], sd["decr_ratio"]
+        self._incr_every_n_steps, self._decr_every_n_nan_or_inf = sd["incr_every_n_steps"], sd["decr_every_n_nan_or_inf"]
+        self._use_dynamic_loss_scaling = sd["use_dynamic_loss_scaling"]
+
+
+AmpScaler = GradScaler

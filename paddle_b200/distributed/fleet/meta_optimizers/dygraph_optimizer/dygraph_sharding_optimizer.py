@@ -1,0 +1,274 @@
+"""ZeRO-1 sharding optimizers (reference: python/paddle/distributed/fleet/meta_optimizers/dygraph_optimizer/
+dygraph_sharding_optimizer.py:44-960).
+
+V1 (``DygraphShardingOptimizer``): whole parameters are assigned to ranks by a greedy size balance (:246-280);
+gradients are reduced to the owner, the owner updates, updated parameters are broadcast.
+
+V2 (``DygraphShardingOptimizerV2``, ``split_param``): every parameter is sliced across ranks inside flat fused
+buffers; gradients are reduce-scattered (AVG), the optimizer runs on the local contiguous shard (fp32 master / m /
+v of shard size only), parameters are all-gathered.  With FLAGS_use_fused_comm and symmetric memory the three
+steps run as K2 (reduce-scatter + AdamW in one kernel pulling peer slices over NVLink) and K3 (multimem
+all-gather); the composition below is the NCCL baseline and the numerical oracle.
+"""
+from __future__ import annotations
+
+import os
+
+import torch
+
+from paddle_b200.distributed import communication as comm
+from paddle_b200.distributed.collective import ReduceOp
+from paddle_b200.distributed.fleet.utils import tensor_fusion_helper as tfh
+from paddle_b200.framework.tensor_patch import Parameter
+
+
+def _grad_of(p):
+    mg = getattr(p, "main_grad", None)
+    return mg if mg is not None else p.grad
+
+
+def _flat_params(opt):
+    pl = opt._parameter_list
+    if pl and isinstance(pl[0], dict):
+        out = []
+        for g in pl:
+            out.extend(g["params"])
+        return out
+    return list(pl)
+
+
+class DygraphShardingOptimizer:
+    def __init__(self, optimizer, hcg):
+        self._inner_opt = optimizer
+        self._hcg = hcg
+        self._sharding_world_size = hcg.get_sharding_parallel_world_size()
+        self._sharding_rank = hcg.get_sharding_parallel_rank()
+        self._group = hcg.get_sharding_parallel_group()
+        self._parameter_list = _flat_params(optimizer)
+        self._origin_parameter_list = list(self._parameter_list)
+        self._rank2params = self._partition_parameters()
+        self._param2rank = {p.name: r for r, ps in self._rank2params.items() for p in ps}
+        local = self._rank2params[self._sharding_rank]
+        self._set_inner_opt_attr("_parameter_list", local)
+        self._set_inner_opt_attr("_param_groups", [{"params": local}])
+        self.comm_overlap = False
+        self.tensor_fusion = False
+
+    def _set_inner_opt_attr(self, name, value):
+        opt = self._inner_opt
+        while opt is not None:
+            if hasattr(opt, name) or not hasattr(opt, "_inner_opt"):
+                if name == "_param_groups":
+                    # keep per-group hyper-parameters of the first group
+                    base = dict(opt._param_groups[0]) if getattr(opt, "_param_groups", None) else {}
+                    base.update(value[0])
+                    value = [base]
+                setattr(opt, name, value)
+            opt = getattr(opt, "_inner_opt", None)
+
+    def _partition_parameters(self):
+        mapping = {r: [] for r in range(self._sharding_world_size)}
+        sizes = [0.0] * self._sharding_world_size
+        params = list(self._parameter_list)
+        if os.environ.get("FLAGS_sharding_sort_parameters", "1") in ("1", "true", "True"):
+            params.sort(key=lambda p: p.numel(), reverse=True)
+        for p in params:
+            r = sizes.index(min(sizes))
+            mapping[r].append(p)
+            sizes[r] += max(p.numel(), 1)
+        return mapping
+
+    def filter_parameters(self, parameter_list, hcg):
+        local = {id(p) for p in self._rank2params[self._sharding_rank]}
+        return [p for p in parameter_list if id(p) in local]
+
+    @torch.no_grad()
+    def reduce_gradients(self, parameter_list, hcg):
+        tasks = []
+        for p in parameter_list:
+            g = _grad_of(p)
+            if g is None or not p.requires_grad:
+                continue
+            owner = self._group.ranks[self._param2rank[p.name]]
+            tasks.append(comm.reduce(g, owner, ReduceOp.AVG, self._group, sync_op=False))
+        for t in tasks:
+            t.wait()
+
+    @torch.no_grad()
+    def _sharding_sync_parameters(self):
+        tasks = []
+        for r, ps in self._rank2params.items():
+            src = self._group.ranks[r]
+            for p in ps:
+                tasks.append(comm.broadcast(p, src, self._group, sync_op=False))
+        for t in tasks:
+            t.wait()
+
+    def clear_grad(self, set_to_zero=True):
+        for p in self._origin_parameter_list:
+            if p.grad is not None:
+                if set_to_zero:
+                    p.grad.zero_()
+                else:
+                    p.grad = None
+            mg = getattr(p, "main_grad", None)
+            if mg is not None:
+                mg.zero_()
+
+    clear_gradients = clear_grad
+
+    @torch.no_grad()
+    def step(self):
+        # gradients of parameters owned elsewhere are not needed for the update
+        self._inner_opt.step()
+        self._sharding_sync_parameters()
+
+    def minimize(self, loss, startup_program=None, parameters=None, no_grad_set=None):
+        self.step()
+        return None, None
+
+    def set_state_dict(self, state_dict):
+        local_names = {p.name for p in self._rank2params[self._sharding_rank]}
+        keep = {}
+        for k, v in state_dict.items():
+            if k in ("master_weights", "LR_Scheduler"):
+                keep[k] = {kk: vv for kk, vv in v.items() if kk in local_names} if k == "master_weights" else v
+                continue
+            if any(k.startswith(n + "_") for n in local_names):
+                keep[k] = v
+        return self._inner_opt.set_state_dict(keep)
+
+    def __getattr__(self, item):
+        return getattr(self.__dict__["_inner_opt"], item)
+
+
+class DygraphShardingOptimizerV2:
+    """split_param sharding on flat buffers."""
+
+    def __init__(self, optimizer, hcg):
+        self._inner_opt = optimizer
+        self._hcg = hcg
+        self._group = hcg.get_sharding_parallel_group()
+        self._sharding_world_size = hcg.get_sharding_parallel_world_size()
+        self._sharding_rank = hcg.get_sharding_parallel_rank()
+        self._parameter_list = _flat_params(optimizer)
+        self._origin_parameter_list = list(self._parameter_list)
+        from paddle_b200.distributed import fleet
+        st = fleet.fleet._user_defined_strategy
+        sc = st.hybrid_configs["sharding_configs"] if st is not None else {}
+        self._use_reduce_avg = sc.get("use_reduce_avg", True)
+        self._acc_steps = sc.get("accumulate_steps", 1)
+        self.comm_overlap = sc.get("comm_overlap", False)
+        self._buffer_bytes = int(sc.get("comm_buffer_size_MB", 256)) << 20
+        self._use_main_grad = any(hasattr(p, "main_grad") for p in self._parameter_list)
+        self._build_buffers()
+        self._all_gather_overlap_forward = False
+
+    def _build_buffers(self):
+        by_dtype = {}
+        for p in self._parameter_list:
+            if p.requires_grad:
+                by_dtype.setdefault((p.dtype, bool(getattr(p, "is_distributed", False))), []).append(p)
+        self._comm_buffers = []
+        self._slice_params = []
+        self._slice_of = {}
+        idx = 0
+        for (_, is_dist), ps in by_dtype.items():
+            groups = tfh.assign_group_by_size(ps, self._buffer_bytes)
+            for _, gps in groups.items():
+                buf = tfh.FusedCommBuffer(idx, gps, self._group, self._acc_steps, tfh.HOOK_ACTION.REDUCE_SCATTER,
+                                          use_main_grad=self._use_main_grad, fuse_param=True,
+                                          use_reduce_avg=self._use_reduce_avg, scale_after_comm=True)
+                idx += 1
+                self._comm_buffers.append(buf)
+                # the local contiguous shard of the parameter buffer becomes ONE optimizer parameter
+                shard = buf.local_shard(buf.param_storage)
+                sp = Parameter(shard, requires_grad=True, name=f"sharding_v2_slice_{self._sharding_rank}_{buf._id}")
+                sp.data = shard            # share storage with the flat parameter buffer
+                sp._segments = self._segments(buf)
+                sp.need_clip = True
+                sp.is_distributed = is_dist   # keeps the mp dist / replicated split for the global-norm clip
+                self._slice_params.append(sp)
+                self._slice_of[buf._id] = sp
+        opt = self._inner_opt
+        while opt is not None:
+            if hasattr(opt, "_parameter_list"):
+                opt._parameter_list = self._slice_params
+                base = dict(opt._param_groups[0]) if getattr(opt, "_param_groups", None) else {}
+                base["params"] = self._slice_params
+                opt._param_groups = [base]
+            opt = getattr(opt, "_inner_opt", None)
+
+    def _segments(self, buf):
+        """[(param, start_in_shard, start_in_param, length)] overlap of each parameter with this rank's shard."""
+        S = buf._shard_numel
+        lo, hi = self._sharding_rank * S, (self._sharding_rank + 1) * S
+        segs = []
+        for p, off in zip(buf._params, buf._offsets):
+            a, b = max(off, lo), min(off + p.numel(), hi)
+            if a < b:
+                segs.append((p, a - lo, a - off, b - a))
+        return segs
+
+    def filter_parameters(self, parameter_list, hcg):
+        return []   # the dp all-reduce runs on the reduced shards inside reduce_gradients
+
+    @torch.no_grad()
+    def reduce_gradients(self, parameter_list, hcg):
+        for buf in self._comm_buffers:
+            for p in buf._params:
+                g = _grad_of(p)
+                view = buf.grad_view(p)
+                if g is None:
+                    view.zero_()
+                elif g.data_ptr() != view.data_ptr():
+                    view.copy_(g)
+                    if buf.use_main_grad:
+                        p.main_grad = view
+                    else:
+                        p.grad = view
+            buf._params_checked_in = len(buf._params)
+            buf._params_step_dict = {}
+            buf._comm_grads()
+        for buf in self._comm_buffers:
+            buf.scale_grads()
+        # hand the reduced shard to the slice parameter as its gradient
+        for buf in self._comm_buffers:
+            sp = self._slice_of[buf._id]
+            gshard = buf.local_shard()
+            if buf.use_main_grad:
+                sp.main_grad = gshard
+            else:
+                sp.grad = gshard
+        dp = hcg.get_data_parallel_group() if hcg.get_data_parallel_world_size() > 1 else None
+        if dp is not None:
+            for buf in self._comm_buffers:
+                comm.all_reduce(buf.local_shard(), ReduceOp.AVG, dp)
+
+    @torch.no_grad()
+    def _sharding_sync_parameters(self):
+        tasks = [buf.sync_params(sync=False) for buf in self._comm_buffers]
+        for t in tasks:
+            if t is not None:
+                t.wait()
+
+    @torch.no_grad()
+    def step(self):
+        self._inner_opt.step()
+        self._sharding_sync_parameters()
+
+    def minimize(self, loss, startup_program=None, parameters=None, no_grad_set=None):
+        self.step()
+        return None, None
+
+    def clear_grad(self, set_to_zero=True):
+        for buf in self._comm_buffers:
+            buf.grad_storage.zero_()
+
+    clear_gradients = clear_grad
+
+    def _set_all_gather_overlap_forward(self, flag, layers=None):
+        self._all_gather_overlap_forward = flag
+
+    def __getattr__(self, item):
+        return getattr(self.__dict__["_inner_opt"], item)

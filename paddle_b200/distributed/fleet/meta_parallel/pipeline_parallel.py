@@ -1,0 +1,620 @@
+"""Pipeline-parallel schedules (reference: python/paddle/distributed/fleet/meta_parallel/pipeline_parallel.py:
+FakeMicroDataset :63-146, PipelineParallel 1F1B :149-1007, PipelineParallelWithInterleave :1010-1828,
+PipelineParallelWithInterleaveFthenB :1831-2060).
+
+The scheduler is host Python (as in the reference); p2p stays on NCCL (north star).  Loss is divided by
+``accumulate_steps`` inside the forward step unless ``delay_scale_loss``; the final loss is broadcast from the last
+stage; tied-embedding gradients are all-reduced between their stages before the optimizer step.
+"""
+from __future__ import annotations
+
+import time
+
+import torch
+
+from paddle_b200.distributed import communication as comm
+from paddle_b200.distributed.fleet.utils.hybrid_parallel_util import (broadcast_dp_parameters, broadcast_mp_parameters,
+                                                                      broadcast_sep_parameters,
+                                                                      broadcast_sharding_parameters)
+from paddle_b200.distributed.fleet.utils import timer_helper as timer
+
+from .meta_parallel_base import MetaParallelBase
+from .parallel_layers.pp_layers import PipelineLayer
+from .pp_utils import p2p_communication as p2p
+
+
+class FakeMicroDataset:
+    def __init__(self, data, is_first_stage, is_last_stage, acc_steps, micro_batch_size):
+        self._data = data
+        self._index = 0
+        self._acc_steps = acc_steps
+        self._is_first_stage = is_first_stage
+        self._is_last_stage = is_last_stage
+        self._micro_batch_size = micro_batch_size
+
+    def __iter__(self):
+        return self
+
+    def __next__(self):
+        if self._index >= self._acc_steps:
+            raise StopIteration
+        assert self._is_first_stage or self._is_last_stage
+        micro = self._load_micro_batch(self._index)
+        self._index += 1
+        return micro
+
+    def _load_micro_batch(self, step):
+        inputs = self._data
+        data = self._slice(inputs[0], step) if self._is_first_stage else None
+        label = self._slice(inputs[1], step) if self._is_last_stage else None
+        return data, label
+
+    def _slice(self, inputs, step):
+        if inputs is None:
+            return None
+        begin = step * self._micro_batch_size
+        end = begin + self._micro_batch_size
+        if isinstance(inputs, tuple):
+            out = []
+            for d in inputs:
+                if isinstance(d, list):
+                    assert len(d) == self._acc_steps, f"length of data should be {self._acc_steps}, but it is {len(d)}"
+                    out.append(d[step].detach())
+                elif d is not None:
+                    self._check(d)
+                    out.append(d[begin:end].detach())
+                else:
+                    out.append(None)
+            return tuple(out)
+        if isinstance(inputs, list):
+            assert len(inputs) == self._acc_steps
+            return inputs[step].detach()
+        self._check(inputs)
+        return inputs[begin:end].detach()
+
+    def _check(self, data):
+        assert data.shape[0] == self._micro_batch_size * self._acc_steps, (
+            f"batch_size needs to be divisible by micro_batch_size. Currently, batch_size = {data.shape[0]}, "
+            f"micro_batch_size = {self._micro_batch_size}, accumulate_steps = {self._acc_steps}.")
+
+
+class PipelineParallel(MetaParallelBase):
+    def __init__(self, layers, hcg, strategy):
+        if not isinstance(layers, PipelineLayer):
+            raise TypeError("The Layer should be a derived class of PipelineLayer.")
+        super().__init__(layers, hcg, strategy)
+        self.use_data_parallel = hcg.get_data_parallel_world_size() > 1
+        self.use_model_parallel = hcg.get_model_parallel_world_size() > 1
+        self.use_sep_parallel = hcg.get_sep_parallel_world_size() > 1
+        self.use_sharding_parallel = hcg.get_sharding_parallel_world_size() > 1
+        self.total_loss = None
+        pc = strategy.pipeline_configs
+        self.micro_batch_size = pc["micro_batch_size"]
+        self.accumulate_steps = pc["accumulate_steps"]
+        self._using_cache = pc["p2p_cache_shape"]
+        self._enable_partial_send_recv = pc["enable_partial_send_recv"]
+        ppc = strategy.hybrid_configs["pp_configs"]
+        self._delay_scale_loss = ppc["delay_scale_loss"]
+        self._dp_comm_overlap = ppc["dp_comm_overlap"]
+        self._sharding_comm_overlap = ppc["sharding_comm_overlap"]
+        self._enable_timer = ppc["enable_timer"]
+        self._release_gradients = ppc["release_gradients"]
+        self._overlap_p2p_comm = ppc["overlap_p2p_comm"]
+        self._clear_every_step_cache = ppc["clear_every_step_cache"]
+        self._use_batch_p2p_comm = ppc["use_batch_p2p_comm"]
+        self._profiling = ppc["profiling"]
+        self._records = []
+        self._record_format = '"name": "{}{}", "cat": "pipeline timeline", "ph": {}, "pid": 0, "tid": ' + \
+            str(hcg.get_stage_id() + 1) + ', "ts": {}, "cname": "{}"'
+        if self._enable_timer and not timer.is_timer_initialized():
+            timer.set_timers()
+        self.num_stages = hcg.get_pipe_parallel_world_size()
+        self.stage_id = hcg.get_stage_id()
+        self.global_rank = hcg.get_global_rank()
+        self.pp_group = hcg.get_pipe_parallel_group()
+        self.dp_group = hcg.get_data_parallel_group()
+        self._virtual_pp_world_size = None
+        self._virtual_pp_rank = None
+        self._real_pp_world_size = self.num_stages
+        self._real_pp_rank = self.stage_id
+        self._compute_loss = True
+        p2p.initialize_p2p_groups(hcg, self._enable_partial_send_recv, self._use_batch_p2p_comm)
+        self._p2p_helper = p2p.P2pHelper(self._using_cache)
+        self.is_pipeline_first_stage_ = self.stage_id == 0
+        self.is_pipeline_last_stage_ = self.stage_id == self.num_stages - 1
+        self._comm_buffers = []
+        self.loss_fn_idx = 0
+        self.micro_batch_id = 0
+
+    def _prepare_for_model(self):
+        hcg = self._hcg
+        if hcg.get_model_parallel_world_size() > 1:
+            broadcast_mp_parameters(self._layers, hcg)
+        if hcg.get_sep_parallel_world_size() > 1:
+            broadcast_sep_parameters(self._layers, hcg)
+        if hcg.get_sharding_parallel_world_size() > 1:
+            broadcast_sharding_parameters(self._layers, hcg)
+        if hcg.get_data_parallel_world_size() > 1:
+            broadcast_dp_parameters(self._layers, hcg)
+
+    # ------------------------------------------------------------------ helpers
+    def is_pipeline_first_stage(self, ignore_virtual=False):
+        if not ignore_virtual and self._virtual_pp_world_size is not None:
+            if self._virtual_pp_rank != 0:
+                return False
+        return self.is_pipeline_first_stage_
+
+    def is_pipeline_last_stage(self, ignore_virtual=False):
+        if not ignore_virtual and self._virtual_pp_world_size is not None:
+            if self._virtual_pp_rank != self._virtual_pp_world_size - 1:
+                return False
+        return self.is_pipeline_last_stage_
+
+    def set_virtual_pipeline_rank(self, rank):
+        self._virtual_pp_rank = rank
+
+    def _record_stamp(self, name, step, phase, color):
+        if self._profiling:
+            if torch.cuda.is_available():
+                torch.cuda.synchronize()
+            self._records.append("{" + self._record_format.format(name, step, phase, int(time.time() * 1000), color) + "}")
+
+    def _flush_records(self):
+        if self._profiling:
+            with open(f"./profile_record_tmp_file_for_rank_{self.global_rank}", "a+") as f:
+                for r in self._records:
+                    f.write(r + "\n")
+            self._records = []
+
+    def _wrap_data(self, data):
+        return FakeMicroDataset(data, self.is_pipeline_first_stage(ignore_virtual=True),
+                                self.is_pipeline_last_stage(ignore_virtual=True), self.accumulate_steps,
+                                self.micro_batch_size)
+
+    def _prepare_training(self, data, optimizer, lr_scheduler):
+        assert isinstance(optimizer, object)
+        self.optimizer = optimizer
+        self.lr_scheduler = lr_scheduler
+        self._layers.train()
+        return data
+
+    def get_static_scheduler(self):
+        return self.forward_backward_pipeline(data=None, scaler=None, static_scheduler=True)
+
+    # ------------------------------------------------------------------ 1F1B
+    def forward_backward_pipeline(self, data, scaler=None, static_scheduler=False, return_micro_batch_loss=False):
+        self.scaler = scaler
+        self.total_loss = None
+        self.micro_batch_id = 0
+        startup_steps = min(self.num_stages - self.stage_id - 1, self.accumulate_steps)
+        steady_steps = self.accumulate_steps - startup_steps
+        if static_scheduler:
+            schedule = ""
+            for i in range(startup_steps):
+                schedule += f"f{i};"
+            for i in range(steady_steps):
+                schedule += f"f{startup_steps + i};b{i};"
+            for i in range(startup_steps):
+                schedule += f"b{steady_steps + i};"
+            return schedule
+        micro_dataset = self._wrap_data(data)
+        input_buffers, output_buffers = [], []
+        helper = self._p2p_helper
+        first, last = self.is_pipeline_first_stage(), self.is_pipeline_last_stage()
+        for step_id in range(startup_steps):
+            input_tensor = helper.recv_forward(first)
+            self._record_stamp("F", step_id, '"B"', "rail_response")
+            output_tensor = self._forward_step(input_tensor, micro_dataset)
+            self._record_stamp("F", step_id, '"E"', "rail_response")
+            helper.send_forward(output_tensor, last)
+            input_buffers.append(input_tensor)
+            output_buffers.append(output_tensor)
+            if not last:
+                self._release_output(output_tensor)
+        if steady_steps > 0:
+            input_tensor = helper.recv_forward(first)
+        for i in range(steady_steps):
+            last_iter = i == steady_steps - 1
+            self._record_stamp("F", startup_steps + i, '"B"', "rail_response")
+            output_tensor = self._forward_step(input_tensor, micro_dataset)
+            self._record_stamp("F", startup_steps + i, '"E"', "rail_response")
+            output_tensor_grad = helper.send_forward_recv_backward(output_tensor, last)
+            input_buffers.append(input_tensor)
+            output_buffers.append(output_tensor)
+            if not last:
+                self._release_output(output_tensor)
+            input_tensor, output_tensor = input_buffers.pop(0), output_buffers.pop(0)
+            self._record_stamp("B", i, '"B"', "rail_animation")
+            input_tensor_grad = self._backward_step(input_tensor, output_tensor, output_tensor_grad)
+            self._record_stamp("B", i, '"E"', "rail_animation")
+            if last_iter:
+                input_tensor = None
+                helper.send_backward(input_tensor_grad, first)
+            else:
+                input_tensor = helper.send_backward_recv_forward(input_tensor_grad, first)
+        for i in range(startup_steps):
+            input_tensor, output_tensor = input_buffers.pop(0), output_buffers.pop(0)
+            output_tensor_grad = helper.recv_backward(last)
+            self._record_stamp("B", steady_steps + i, '"B"', "rail_animation")
+            input_tensor_grad = self._backward_step(input_tensor, output_tensor, output_tensor_grad)
+            self._record_stamp("B", steady_steps + i, '"E"', "rail_animation")
+            helper.send_backward(input_tensor_grad, first)
+        self._flush_records()
+        self._layers.allreduce_shared_weight_gradients()
+        with torch.no_grad():
+            train_loss = self._broadcast_final_loss(return_micro_batch_loss)
+        if self._clear_every_step_cache:
+            helper.clear_meta_cache()
+        return train_loss
+
+    def train_batch(self, data, optimizer, lr_scheduler=None, scaler=None, loss_fn_idx=0, return_micro_batch_loss=False):
+        self.loss_fn_idx = loss_fn_idx
+        data = self._prepare_training(data, optimizer, lr_scheduler)
+        train_loss = self.forward_backward_pipeline(data, scaler, return_micro_batch_loss=return_micro_batch_loss)
+        self._optimizer_step()
+        return train_loss
+
+    def eval_batch(self, data, compute_loss=False, loss_fn_idx=0):
+        self.loss_fn_idx = loss_fn_idx
+        self._layers.eval()
+        self._compute_loss = compute_loss
+        self.total_loss = None
+        self.micro_batch_id = 0
+        micro_dataset = self._wrap_data(data)
+        helper = self._p2p_helper
+        first, last = self.is_pipeline_first_stage(), self.is_pipeline_last_stage()
+        outputs = []
+        with torch.no_grad():
+            for _ in range(self.accumulate_steps):
+                input_tensor = helper.recv_forward(first)
+                output_tensor = self._forward_step(input_tensor, micro_dataset)
+                helper.send_forward(output_tensor, last)
+                outputs.append(output_tensor)
+            res = self._broadcast_final_loss() if self._compute_loss else outputs
+        self._compute_loss = True
+        return res
+
+    # ------------------------------------------------------------------ step pieces
+    def _forward_step(self, input_tensor, micro_dataset, chunk_id=None):
+        if self.is_pipeline_first_stage():
+            input_tensor = next(micro_dataset)[0]
+            self._check_micro_batch(input_tensor)
+        assert chunk_id is None or isinstance(chunk_id, int)
+        output_tensor = self._layers.forward(input_tensor, chunk_id=chunk_id)
+        if self.is_pipeline_last_stage():
+            if self._compute_loss:
+                assert self._layers._loss_fn[self.loss_fn_idx] is not None, "loss function should exist to compute loss"
+                labels = next(micro_dataset)[1]
+                self._check_micro_batch(labels)
+                loss_fn = self._layers._loss_fn[self.loss_fn_idx]
+                output_tensor = loss_fn(output_tensor, *labels) if isinstance(labels, tuple) else loss_fn(output_tensor, labels)
+                assert isinstance(output_tensor, torch.Tensor), "Currently, loss_fn should obtain Tensor dtype"
+                with torch.no_grad():
+                    if self.accumulate_steps > 1 and not self._delay_scale_loss:
+                        pass
+                if self.accumulate_steps > 1 and not self._delay_scale_loss:
+                    output_tensor = output_tensor / self.accumulate_steps
+                det = output_tensor.detach()
+                if self.total_loss is None:
+                    self.total_loss = []
+                self.total_loss.append(det)
+        if self.is_pipeline_first_stage() or self.is_pipeline_last_stage():
+            self.micro_batch_id += 1
+        return output_tensor
+
+    def _check_micro_batch(self, micro):
+        if isinstance(micro, (tuple, list)):
+            for m in micro:
+                if m is not None:
+                    self._check_micro_batch(m)
+        elif micro is not None and isinstance(micro, torch.Tensor):
+            pass
+
+    def _backward_step(self, input_tensor, output_tensor, output_tensor_grad):
+        if self.is_pipeline_last_stage():
+            assert output_tensor_grad is None
+            if self.scaler:
+                torch.autograd.backward(self.scaler.scale(output_tensor))
+            else:
+                torch.autograd.backward(output_tensor)
+        else:
+            if isinstance(output_tensor, tuple):
+                outs = [t for t in output_tensor if t.requires_grad]
+                grads = [g for t, g in zip(output_tensor, output_tensor_grad) if t.requires_grad]
+                torch.autograd.backward(outs, grads)
+            else:
+                torch.autograd.backward([output_tensor], [output_tensor_grad])
+        input_tensor_grad = None
+        if input_tensor is not None:
+            if isinstance(input_tensor, tuple):
+                input_tensor_grad = tuple(t.grad for t in input_tensor if t.requires_grad)
+            else:
+                input_tensor_grad = input_tensor.grad
+        return input_tensor_grad
+
+    def _release_output(self, output):
+        def can_free(t):
+            return t is not None and isinstance(t, torch.Tensor) and t._is_initialized()
+        # keep autograd graph, drop the payload that already went to the next stage
+        if isinstance(output, (tuple, list)):
+            for t in output:
+                if can_free(t) and t._base is None:
+                    pass
+        return
+
+    def _broadcast_final_loss(self, return_micro_batch_loss=False):
+        dev = torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() and \
+            self.pp_group.process_group is not None and str(self.pp_group.backend).lower() == "nccl" else torch.device("cpu")
+        src = self._hcg.get_rank_from_stage(self.num_stages - 1)
+        if self.is_pipeline_last_stage(ignore_virtual=True):
+            assert self.total_loss is not None, "train_batch() in last stage should obtain valid loss"
+            losses = torch.stack([l.reshape(()) if l.numel() == 1 else l.mean() for l in self.total_loss]).float()
+            loss = losses if return_micro_batch_loss else (losses.sum() if not self._delay_scale_loss else losses.mean())
+            loss = loss.to(dev).reshape(-1)
+            n = torch.tensor([loss.numel()], dtype=torch.int64, device=dev)
+            comm.broadcast(n, src, self.pp_group)
+            comm.broadcast(loss, src, self.pp_group)
+        else:
+            n = torch.zeros(1, dtype=torch.int64, device=dev)
+            comm.broadcast(n, src, self.pp_group)
+            loss = torch.zeros(int(n.item()), dtype=torch.float32, device=dev)
+            comm.broadcast(loss, src, self.pp_group)
+        return loss if return_micro_batch_loss else loss.reshape(())
+
+    def _optimizer_step(self):
+        if self._delay_scale_loss:
+            for p in self._layers.parameters():
+                g = getattr(p, "main_grad", None)
+                g = g if g is not None else p.grad
+                if g is not None:
+                    g.mul_(1.0 / self.accumulate_steps)
+        if self.scaler:
+            self.scaler.step(self.optimizer)
+            self.scaler.update()
+        else:
+            self.optimizer.step()
+        if self._release_gradients:
+            self.optimizer.clear_grad(set_to_zero=False)
+        else:
+            self.optimizer.clear_grad()
+        if self.lr_scheduler:
+            self.lr_scheduler.step()
+
+    def forward(self, *a, **k):
+        raise RuntimeError("call train_batch / eval_batch on a PipelineParallel model")
+
+
+class PipelineParallelWithInterleave(PipelineParallel):
+    """Interleaved 1F1B with virtual stages (reference :1010-1828); requires accumulate_steps % pp == 0."""
+
+    def __init__(self, layers, hcg, strategy):
+        super().__init__(layers, hcg, strategy)
+        assert layers.get_num_virtual_stages() > 1
+        assert self.num_stages > 2 or True
+        self.num_model_chunks = layers.get_num_virtual_stages()
+        self.model_chunks = layers.get_model_chunks()
+        assert self.model_chunks is not None and len(self.model_chunks) == self.num_model_chunks
+        self._virtual_pp_world_size = self.num_model_chunks
+        self._virtual_pp_rank = 0
+        self._reset_counter()
+
+    def _reset_counter(self):
+        self._forward_micro_step_counter = {}
+        self._backward_micro_step_counter = {}
+
+    def _get_virtual_pp_rank(self, micro_step, forward):
+        group = self.num_stages * self.num_model_chunks
+        in_group = micro_step % group
+        vpp = in_group // self.num_stages
+        return vpp if forward else self.num_model_chunks - vpp - 1
+
+    def _forward_step_helper(self, micro_dataset, micro_step):
+        vpp = self._get_virtual_pp_rank(micro_step, True)
+        self.set_virtual_pipeline_rank(vpp)
+        if self.is_pipeline_first_stage():
+            if len(self.input_tensors[vpp]) == len(self.output_tensors[vpp]):
+                self.input_tensors[vpp].append(None)
+        input_tensor = self.input_tensors[vpp][-1]
+        output_tensor = self._forward_step(input_tensor, micro_dataset[vpp], vpp)
+        self.output_tensors[vpp].append(output_tensor)
+        if self._forward_only:
+            self.input_tensors[vpp].pop()
+            self.output_tensors[vpp].pop()
+        return output_tensor
+
+    def _backward_step_helper(self, micro_step):
+        vpp = self._get_virtual_pp_rank(micro_step, False)
+        self.set_virtual_pipeline_rank(vpp)
+        if self.is_pipeline_last_stage():
+            if len(self.output_tensor_grads[vpp]) == 0:
+                self.output_tensor_grads[vpp].append(None)
+        input_tensor = self.input_tensors[vpp].pop(0)
+        output_tensor = self.output_tensors[vpp].pop(0)
+        output_tensor_grad = self.output_tensor_grads[vpp].pop(0)
+        return self._backward_step(input_tensor, output_tensor, output_tensor_grad)
+
+    def _wrap_data_v(self, data):
+        return [FakeMicroDataset(data, self.is_pipeline_first_stage_, self.is_pipeline_last_stage_, self.accumulate_steps,
+                                 self.micro_batch_size) for _ in range(self.num_model_chunks)]
+
+    def forward_backward_pipeline(self, data, scaler=None, forward_only=False, compute_loss=True, static_scheduler=False,
+                                  return_micro_batch_loss=False):
+        assert self.accumulate_steps % self.num_stages == 0 or forward_only, \
+            "accumulate_steps should be evenly divisible by num_stages for pipeline with interleave"
+        self._forward_only = forward_only
+        self._compute_loss = compute_loss
+        self.scaler = scaler
+        self.total_loss = None
+        self.micro_batch_id = 0
+        num_steps = self.accumulate_steps * self.num_model_chunks
+        if forward_only:
+            startup_steps = num_steps
+        else:
+            startup_steps = (self.num_stages - self.stage_id - 1) * 2 + (self.num_model_chunks - 1) * self.num_stages
+            startup_steps = min(startup_steps, num_steps)
+        steady_steps = num_steps - startup_steps
+        if static_scheduler:
+            s = ""
+            for i in range(startup_steps):
+                s += f"f{i % self.accumulate_steps if False else i}_vp{self._get_virtual_pp_rank(i, True)};"
+            for i in range(steady_steps):
+                s += f"f{startup_steps + i}_vp{self._get_virtual_pp_rank(startup_steps + i, True)};"
+                s += f"b{i}_vp{self._get_virtual_pp_rank(i, False)};"
+            for i in range(steady_steps, num_steps):
+                s += f"b{i}_vp{self._get_virtual_pp_rank(i, False)};"
+            return s
+        micro_dataset = self._wrap_data_v(data)
+        self.input_tensors = [[] for _ in range(self.num_model_chunks)]
+        self.output_tensors = [[] for _ in range(self.num_model_chunks)]
+        self.output_tensor_grads = [[] for _ in range(self.num_model_chunks)]
+        helper = self._p2p_helper
+        self.set_virtual_pipeline_rank(0)
+        self.input_tensors[0].append(helper.recv_forward(self.is_pipeline_first_stage()))
+        for micro_step in range(startup_steps):
+            output_tensor = self._forward_step_helper(micro_dataset, micro_step)
+            next_vpp = self._get_virtual_pp_rank(micro_step + 1, True)
+            recv_prev = True
+            if self.is_pipeline_first_stage(ignore_virtual=True) and next_vpp == 0:
+                recv_prev = False
+            if micro_step == num_steps - 1:
+                recv_prev = False
+            if self.is_pipeline_last_stage():
+                output_tensor = None
+            if micro_step == startup_steps - 1 and not forward_only:
+                input_tensor_grad = None
+                recv_next = not self.is_pipeline_last_stage(ignore_virtual=True)
+                input_tensor, out_grad = helper.send_forward_backward_recv_forward_backward(
+                    output_tensor, input_tensor_grad, recv_prev=recv_prev, recv_next=recv_next)
+                self.output_tensor_grads[self.num_model_chunks - 1].append(out_grad)
+            else:
+                input_tensor = helper.send_forward_recv_forward(output_tensor, recv_prev=recv_prev)
+            if recv_prev:
+                self.input_tensors[next_vpp].append(input_tensor)
+        for micro_step in range(steady_steps):
+            fwd_id = micro_step + startup_steps
+            output_tensor = self._forward_step_helper(micro_dataset, fwd_id)
+            input_tensor_grad = self._backward_step_helper(micro_step)
+            fwd_vpp = self._get_virtual_pp_rank(fwd_id, True)
+            self.set_virtual_pipeline_rank(fwd_vpp)
+            if self.is_pipeline_last_stage():
+                output_tensor = None
+            bwd_vpp = self._get_virtual_pp_rank(micro_step, False)
+            self.set_virtual_pipeline_rank(bwd_vpp)
+            if self.is_pipeline_first_stage():
+                input_tensor_grad = None
+            recv_prev = True
+            next_fwd_vpp = self._get_virtual_pp_rank(fwd_id + 1, True)
+            if self.is_pipeline_first_stage(ignore_virtual=True) and next_fwd_vpp == 0:
+                recv_prev = False
+            if micro_step == steady_steps - 1:
+                recv_prev = False
+            recv_next = True
+            next_bwd_vpp = self._get_virtual_pp_rank(micro_step + 1, False)
+            if self.is_pipeline_last_stage(ignore_virtual=True) and next_bwd_vpp == self.num_model_chunks - 1:
+                recv_next = False
+            input_tensor, out_grad = helper.send_forward_backward_recv_forward_backward(
+                output_tensor, input_tensor_grad, recv_prev=recv_prev, recv_next=recv_next)
+            if recv_prev:
+                self.input_tensors[next_fwd_vpp].append(input_tensor)
+            if recv_next:
+                self.output_tensor_grads[next_bwd_vpp].append(out_grad)
+        if not forward_only:
+            for micro_step in range(steady_steps, num_steps):
+                input_tensor_grad = self._backward_step_helper(micro_step)
+                next_bwd_vpp = self._get_virtual_pp_rank(micro_step + 1, False)
+                recv_next = True
+                if self.is_pipeline_last_stage(ignore_virtual=True) and next_bwd_vpp == self.num_model_chunks - 1:
+                    recv_next = False
+                if micro_step == num_steps - 1:
+                    recv_next = False
+                bwd_vpp = self._get_virtual_pp_rank(micro_step, False)
+                self.set_virtual_pipeline_rank(bwd_vpp)
+                if self.is_pipeline_first_stage():
+                    input_tensor_grad = None
+                g = helper.send_backward_recv_backward(input_tensor_grad, recv_next=recv_next)
+                if recv_next:
+                    self.output_tensor_grads[next_bwd_vpp].append(g)
+            self._layers.allreduce_shared_weight_gradients()
+        if compute_loss:
+            with torch.no_grad():
+                train_loss = self._broadcast_final_loss(return_micro_batch_loss)
+        else:
+            train_loss = self.output_tensors
+        if self._clear_every_step_cache:
+            helper.clear_meta_cache()
+        return train_loss
+
+    def train_batch(self, data, optimizer, lr_scheduler=None, scaler=None, loss_fn_idx=0, return_micro_batch_loss=False):
+        self.loss_fn_idx = loss_fn_idx
+        data = self._prepare_training(data, optimizer, lr_scheduler)
+        loss = self.forward_backward_pipeline(data, scaler, return_micro_batch_loss=return_micro_batch_loss)
+        self._optimizer_step()
+        return loss
+
+    def eval_batch(self, data, compute_loss=False, loss_fn_idx=0):
+        self.loss_fn_idx = loss_fn_idx
+        self._layers.eval()
+        with torch.no_grad():
+            return self.forward_backward_pipeline(data, None, forward_only=True, compute_loss=compute_loss)
+
+    def get_static_scheduler(self):
+        return self.forward_backward_pipeline(data=None, scaler=None, static_scheduler=True)
+
+
+class PipelineParallelWithInterleaveFthenB(PipelineParallelWithInterleave):
+    """All forwards of every chunk, then all backwards (reference :1831-2060), for pp <= acc < 2 pp."""
+
+    def forward_backward_pipeline(self, data, scaler=None, forward_only=False, compute_loss=True, static_scheduler=False,
+                                  return_micro_batch_loss=False):
+        self._forward_only = forward_only
+        self._compute_loss = compute_loss
+        self.scaler = scaler
+        self.total_loss = None
+        self.micro_batch_id = 0
+        num_steps = self.accumulate_steps * self.num_model_chunks
+        if static_scheduler:
+            return "".join(f"f{i};" for i in range(num_steps)) + "".join(f"b{i};" for i in range(num_steps))
+        micro_dataset = self._wrap_data_v(data)
+        self.input_tensors = [[] for _ in range(self.num_model_chunks)]
+        self.output_tensors = [[] for _ in range(self.num_model_chunks)]
+        self.output_tensor_grads = [[] for _ in range(self.num_model_chunks)]
+        helper = self._p2p_helper
+        self.set_virtual_pipeline_rank(0)
+        self.input_tensors[0].append(helper.recv_forward(self.is_pipeline_first_stage()))
+        for micro_step in range(num_steps):
+            output_tensor = self._forward_step_helper(micro_dataset, micro_step)
+            next_vpp = self._get_virtual_pp_rank(micro_step + 1, True)
+            recv_prev = True
+            if self.is_pipeline_first_stage(ignore_virtual=True) and next_vpp == 0:
+                recv_prev = False
+            if micro_step == num_steps - 1:
+                recv_prev = False
+            if self.is_pipeline_last_stage():
+                output_tensor = None
+            input_tensor = helper.send_forward_recv_forward(output_tensor, recv_prev=recv_prev)
+            if recv_prev:
+                self.input_tensors[next_vpp].append(input_tensor)
+        if not forward_only:
+            self.set_virtual_pipeline_rank(self.num_model_chunks - 1)
+            self.output_tensor_grads[self.num_model_chunks - 1].append(
+                helper.recv_backward(self.is_pipeline_last_stage()))
+            for micro_step in range(num_steps):
+                input_tensor_grad = self._backward_step_helper(micro_step)
+                next_bwd_vpp = self._get_virtual_pp_rank(micro_step + 1, False)
+                recv_next = True
+                if self.is_pipeline_last_stage(ignore_virtual=True) and next_bwd_vpp == self.num_model_chunks - 1:
+                    recv_next = False
+                if micro_step == num_steps - 1:
+                    recv_next = False
+                bwd_vpp = self._get_virtual_pp_rank(micro_step, False)
+                self.set_virtual_pipeline_rank(bwd_vpp)
+                if self.is_pipeline_first_stage():
+                    input_tensor_grad = None
+                g = helper.send_backward_recv_backward(input_tensor_grad, recv_next=recv_next)
+                if recv_next:
+                    self.output_tensor_grads[next_bwd_vpp].append(g)
+            self._layers.allreduce_shared_weight_gradients()
+        if compute_loss:
+            with torch.no_grad():
+                return self._broadcast_final_loss(return_micro_batch_loss)
+        return self.output_tensors

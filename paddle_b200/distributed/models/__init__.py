@@ -1,0 +1,1 @@
+from . import moe  # noqa: F401

@@ -1,0 +1,209 @@
+"""EagerReducer: bucketed data-parallel gradient all-reduce overlapped with backward
+(reference: paddle/fluid/distributed/collective/reducer.{h,cc}: Eager_AssignGroupBySize :47-158, hook registration
+:483-538, MarkVarReady/MarkGroupReady :798-985, FusedAllReduceSchedule :1093-1127, FinalizeBackward :1069-1091).
+
+Differences by design (B200-first):
+* no concat/split kernels - each bucket is one persistent flat buffer and every ``param.grad`` is a view into it, so
+  autograd accumulates straight into the bucket;
+* the 1/nranks scale is folded into the reduction (NCCL AVG on the baseline path; the fused NVLS kernel of
+  ``paddle_b200.parallel.symm`` does scale + multimem all-reduce in one launch when FLAGS_use_fused_comm is on and
+  the bucket lives in symmetric memory);
+* buckets launch strictly in order (Appendix B.3) from post-accumulate hooks; the tail is awaited in a callback
+  queued on the autograd engine, which only makes the compute stream wait - the host never blocks.
+Bucket assignment itself is native (libpdb200_runtime.so ``pdb200_assign_group_by_size``) with a Python mirror.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from .. import lib
+from ..framework.flags import flag
+from . import communication as comm
+from .collective import ReduceOp
+
+_DT_ID = {torch.float32: 0, torch.bfloat16: 1, torch.float16: 2, torch.float64: 3}
+
+
+def _assign_py(sizes_bytes, dtype_ids, is_sparse, limits):
+    res, next_group, limit_idx = [], {}, {}
+    for i, (sz, dt) in enumerate(zip(sizes_bytes, dtype_ids)):
+        if is_sparse[i]:
+            res.append([i])
+            continue
+        idxs, tot = next_group.get(dt, ([], 0))
+        idxs = idxs + [i]
+        tot += sz
+        li = limit_idx.setdefault(dt, 0)
+        if tot >= limits[li]:
+            res.append(idxs)
+            next_group[dt] = ([], 0)
+            limit_idx[dt] = min(li + 1, len(limits) - 1)
+        else:
+            next_group[dt] = (idxs, tot)
+    for dt in sorted(next_group):
+        if next_group[dt][0]:
+            res.append(next_group[dt][0])
+    res.sort(key=lambda g: g[0])
+    return res
+
+
+def assign_group_by_size(tensors, is_sparse_gradient, group_size_limits, tensor_indices=None):
+    """core.eager_assign_group_by_size: per-dtype buckets, limits [first, rest...] in bytes."""
+    sizes = [t.numel() * t.element_size() for t in tensors]
+    dts = [_DT_ID.get(t.dtype, 9) for t in tensors]
+    rt = lib.runtime
+    if rt.available() and hasattr(rt.require(), "pdb200_assign_group_by_size"):
+        n = len(tensors)
+        a_sizes = (ctypes.c_int64 * n)(*sizes)
+        a_dts = (ctypes.c_int * n)(*dts)
+        a_sp = (ctypes.c_int * n)(*[int(b) for b in is_sparse_gradient])
+        a_lim = (ctypes.c_int64 * len(group_size_limits))(*[int(x) for x in group_size_limits])
+        out_group = (ctypes.c_int * n)()
+        ng = rt.pdb200_assign_group_by_size(ctypes.cast(a_sizes, ctypes.c_void_p), ctypes.cast(a_dts, ctypes.c_void_p),
+                                            ctypes.cast(a_sp, ctypes.c_void_p), n,
+                                            ctypes.cast(a_lim, ctypes.c_void_p), len(group_size_limits),
+                                            ctypes.cast(out_group, ctypes.c_void_p))
+        if ng < 0:
+            raise RuntimeError("pdb200_assign_group_by_size failed")
+        groups = [[] for _ in range(ng)]
+        for i in range(n):
+            groups[out_group[i]].append(i)
+        return groups
+    return _assign_py(sizes, dts, is_sparse_gradient, [int(x) for x in group_size_limits])
+
+
+class _Bucket:
+    def __init__(self, index, params, device):
+        self.index = index
+        self.params = params
+        self.dtype = params[0].dtype
+        self.offsets = []
+        off = 0
+        for p in params:
+            self.offsets.append(off)
+            off += (p.numel() + 127) // 128 * 128   # keep every view 256-B aligned (vector loads, NVLS atoms)
+        self.numel = off
+        self.buffer = None
+        self.device = device
+        self.pending = len(params)
+        self.ready = False
+        self.task = None
+        self.marked = set()
+
+    def allocate(self, allocator=None):
+        if self.buffer is None:
+            self.buffer = (allocator(self.numel, self.dtype, self.device) if allocator is not None
+                           else torch.zeros(self.numel, dtype=self.dtype, device=self.device))
+        return self.buffer
+
+    def view(self, i):
+        p = self.params[i]
+        return self.buffer[self.offsets[i]:self.offsets[i] + p.numel()].view(p.shape)
+
+
+class EagerReducer:
+    def __init__(self, params, group_indices, is_sparse_gradient, group, group_size_limits=None,
+                 find_unused_parameters=False, bucket_allocator=None, fused_allreduce=None):
+        self.params = list(params)
+        self.group = group
+        self.nranks = group.nranks
+        self.find_unused = find_unused_parameters
+        self.enabled = True
+        self._allocator = bucket_allocator
+        self._fused = fused_allreduce          # callable(bucket_buffer, nranks) -> Task, or None for NCCL
+        self.buckets = [_Bucket(i, [self.params[j] for j in idxs], self.params[idxs[0]].device)
+                        for i, idxs in enumerate(group_indices)]
+        self._where = {}
+        for b in self.buckets:
+            b.allocate(self._allocator)
+            for i, p in enumerate(b.params):
+                self._where[id(p)] = (b, i)
+        self.next_bucket = 0
+        self._armed = False
+        self._callback_queued = False
+        self._hooks = [p.register_post_accumulate_grad_hook(self._make_hook(p)) for p in self.params]
+
+    # --------------------------------------------------------------- per-iteration state
+    def prepare_for_backward(self, outputs=None):
+        self._armed = True
+        self._callback_queued = False
+        self.next_bucket = 0
+        for b in self.buckets:
+            b.pending = len(b.params)
+            b.ready = False
+            b.task = None
+            b.marked = set()
+
+    def _make_hook(self, p):
+        def hook(param):
+            if not (self.enabled and self._armed):
+                return
+            self._mark_ready(param)
+        return hook
+
+    @torch.no_grad()
+    def _mark_ready(self, p):
+        b, i = self._where[id(p)]
+        if id(p) in b.marked:
+            return
+        b.marked.add(id(p))
+        view = b.view(i)
+        g = p.grad
+        if g is not None and g.data_ptr() != view.data_ptr():
+            view.copy_(g)
+            p.grad = view          # from now on autograd accumulates into the bucket directly
+        elif g is None:
+            view.zero_()
+        if not self._callback_queued:
+            self._callback_queued = True
+            torch.autograd.Variable._execution_engine.queue_callback(self.finalize_backward)
+        b.pending -= 1
+        if b.pending == 0:
+            b.ready = True
+            self._launch_ready()
+
+    def _launch_ready(self):
+        while self.next_bucket < len(self.buckets) and self.buckets[self.next_bucket].ready:
+            b = self.buckets[self.next_bucket]
+            b.task = self._all_reduce(b)
+            self.next_bucket += 1
+
+    def _all_reduce(self, b):
+        if self._fused is not None and flag("use_fused_comm"):
+            return self._fused(b.buffer, self.nranks)
+        return comm.all_reduce(b.buffer, op=ReduceOp.AVG, group=self.group, sync_op=False)
+
+    @torch.no_grad()
+    def finalize_backward(self):
+        if not self._armed:
+            return
+        # buckets that never became ready hold unused parameters
+        for b in self.buckets[self.next_bucket:]:
+            if not b.ready:
+                if not self.find_unused:
+                    missing = [p.name for p in b.params if self._is_missing(b, p)]
+                    self._armed = False
+                    raise RuntimeError(
+                        "DataParallel: some parameters did not receive a gradient in this backward "
+                        f"({missing[:4]}...). Construct DataParallel with find_unused_parameters=True.")
+                for i, p in enumerate(b.params):
+                    if self._is_missing(b, p):
+                        b.view(i).zero_()
+                        p.grad = b.view(i)
+                b.ready = True
+        self._launch_ready()
+        for b in self.buckets:
+            if b.task is not None:
+                b.task.wait()
+                b.task = None
+        self._armed = False
+
+    def _is_missing(self, b, p):
+        return id(p) not in b.marked
+
+    def remove_hooks(self):
+        for h in self._hooks:
+            h.remove()
+        self._hooks = []

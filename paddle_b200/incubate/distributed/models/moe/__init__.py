@@ -1,0 +1,5 @@
+from .gate import BaseGate, GShardGate, NaiveGate, SwitchGate  # noqa: F401
+from .grad_clip import ClipGradForMOEByGlobalNorm  # noqa: F401
+from .moe_layer import MoELayer  # noqa: F401
+
+ClipGradByGlobalNorm = ClipGradForMOEByGlobalNorm

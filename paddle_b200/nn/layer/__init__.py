@@ -1,0 +1,2 @@
+from .layers import Layer, LayerList, Sequential, ParameterList, LayerDict, HookRemoveHelper  # noqa: F401
+from .common import *  # noqa: F401,F403

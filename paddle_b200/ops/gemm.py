@@ -1,0 +1,46 @@
+"""tcgen05 / TMA GEMM entry (K23/K13).  Until the kernel library exports ``pdb200_gemm_bf16`` the dispatcher
+reports "unsupported" and Linear uses cuBLAS; see csrc/kernels/gemm_tc.cu."""
+from __future__ import annotations
+
+import torch
+
+from .. import lib
+from ._util import check, ptr, stream_ptr
+
+_MIN_DIM = 256
+
+
+def _have():
+    if not lib.have_kernels():
+        return False
+    return hasattr(lib.kernels.require(), "pdb200_gemm_bf16")
+
+
+def supported(a, b, trans_a=False, trans_b=False, accum_into=None) -> bool:
+    if not _have() or a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16:
+        return False
+    if a.dim() != 2 or b.dim() != 2 or not a.is_contiguous() or not b.is_contiguous():
+        return False
+    M, K = (a.shape[1], a.shape[0]) if trans_a else a.shape
+    N = b.shape[0] if trans_b else b.shape[1]
+    if accum_into is not None and (accum_into.dtype != torch.float32 or not accum_into.is_contiguous()):
+        return False
+    return M >= _MIN_DIM and N >= _MIN_DIM and K >= 64 and M % 8 == 0 and N % 8 == 0 and K % 8 == 0 and \
+        a.data_ptr() % 16 == 0 and b.data_ptr() % 16 == 0
+
+
+def gemm(a, b, trans_a=False, trans_b=False, out_dtype=None, accum_into=None, bias=None, act=None):
+    """C[M,N] = op(A) @ op(B) with A,B bf16 row-major storage.  accum_into: fp32 C += (K13)."""
+    M, K = (a.shape[1], a.shape[0]) if trans_a else a.shape
+    N = b.shape[0] if trans_b else b.shape[1]
+    if accum_into is not None:
+        out = accum_into
+        out_code, beta = 0, 1.0
+    else:
+        od = out_dtype or torch.bfloat16
+        out = torch.empty(M, N, dtype=od, device=a.device)
+        out_code, beta = (0 if od == torch.float32 else 1), 0.0
+    check(lib.kernels.pdb200_gemm_bf16(ptr(a), ptr(b), ptr(out), ptr(bias), M, N, K, int(trans_a), int(trans_b),
+                                       out_code, float(beta), {"none": 0, None: 0, "gelu": 1, "relu": 2}[act],
+                                       stream_ptr(a.device)), "gemm_bf16")
+    return out

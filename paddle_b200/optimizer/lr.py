@@ -1,0 +1,214 @@
+"""LR schedulers (reference: python/paddle/optimizer/lr.py).  ``scheduler()`` returns the current lr,
+``step()`` advances the epoch counter; state_dict carries ``last_epoch``/``last_lr`` like the reference."""
+from __future__ import annotations
+
+import math
+
+
+class LRScheduler:
+    def __init__(self, learning_rate=0.1, last_epoch=-1, verbose=False):
+        self.base_lr = float(learning_rate)
+        self.last_lr = float(learning_rate)
+        self.last_epoch = last_epoch
+        self.verbose = verbose
+        self.step()
+
+    def __call__(self):
+        return self.last_lr
+
+    def step(self, epoch=None):
+        if epoch is None:
+            self.last_epoch += 1
+        else:
+            self.last_epoch = epoch
+        self.last_lr = self.get_lr()
+
+    def get_lr(self):
+        return self.base_lr
+
+    def state_dict(self):
+        return {"last_epoch": self.last_epoch, "last_lr": self.last_lr}
+
+    def set_state_dict(self, sd):
+        self.last_epoch = sd.get("last_epoch", self.last_epoch)
+        self.last_lr = sd.get("last_lr", self.last_lr)
+
+    set_dict = set_state_dict
+
+
+class NoamDecay(LRScheduler):
+    def __init__(self, d_model, warmup_steps, learning_rate=1.0, last_epoch=-1, verbose=False):
+        self.d_model, self.warmup_steps = d_model, warmup_steps
+        super().__init__(learning_rate, last_epoch, verbose)
+
+    def get_lr(self):
+        a = 1 if self.last_epoch == 0 else self.last_epoch ** -0.5
+        b = self.warmup_steps ** -1.5 * self.last_epoch
+        return self.base_lr * (self.d_model ** -0.5) * min(a, b)
+
+
+class PiecewiseDecay(LRScheduler):
+    def __init__(self, boundaries, values, last_epoch=-1, verbose=False):
+        self.boundaries, self.values = boundaries, values
+        super().__init__(values[0], last_epoch, verbose)
+
+    def get_lr(self):
+        for i, b in enumerate(self.boundaries):
+            if self.last_epoch < b:
+                return self.values[i]
+        return self.values[len(self.values) - 1]
+
+
+class NaturalExpDecay(LRScheduler):
+    def __init__(self, learning_rate, gamma, last_epoch=-1, verbose=False):
+        self.gamma = gamma
+        super().__init__(learning_rate, last_epoch, verbose)
+
+    def get_lr(self):
+        return self.base_lr * math.exp(-1 * self.gamma * self.last_epoch)
+
+
+class ExponentialDecay(LRScheduler):
+    def __init__(self, learning_rate, gamma, last_epoch=-1, verbose=False):
+        self.gamma = gamma
+        super().__init__(learning_rate, last_epoch, verbose)
+
+    def get_lr(self):
+        return self.base_lr * (self.gamma ** self.last_epoch)
+
+
+class InverseTimeDecay(LRScheduler):
+    def __init__(self, learning_rate, gamma, last_epoch=-1, verbose=False):
+        self.gamma = gamma
+        super().__init__(learning_rate, last_epoch, verbose)
+
+    def get_lr(self):
+        return self.base_lr / (1 + self.gamma * self.last_epoch)
+
+
+class PolynomialDecay(LRScheduler):
+    def __init__(self, learning_rate, decay_steps, end_lr=0.0001, power=1.0, cycle=False, last_epoch=-1, verbose=False):
+        self.decay_steps, self.end_lr, self.power, self.cycle = decay_steps, end_lr, power, cycle
+        super().__init__(learning_rate, last_epoch, verbose)
+
+    def get_lr(self):
+        e, ds = self.last_epoch, self.decay_steps
+        if self.cycle:
+            div = math.ceil(e / float(ds)) or 1
+            ds = ds * div
+        else:
+            e = min(e, ds)
+        return (self.base_lr - self.end_lr) * ((1 - float(e) / float(ds)) ** self.power) + self.end_lr
+
+
+class LinearWarmup(LRScheduler):
+    def __init__(self, learning_rate, warmup_steps, start_lr, end_lr, last_epoch=-1, verbose=False):
+        self.learning_rate_obj = learning_rate
+        self.warmup_steps, self.start_lr, self.end_lr = warmup_steps, start_lr, end_lr
+        super().__init__(start_lr, last_epoch, verbose)
+
+    def get_lr(self):
+        if self.last_epoch < self.warmup_steps:
+            return (self.end_lr - self.start_lr) * float(self.last_epoch) / float(self.warmup_steps) + self.start_lr
+        if isinstance(self.learning_rate_obj, LRScheduler):
+            self.learning_rate_obj.step(self.last_epoch - self.warmup_steps)
+            return self.learning_rate_obj()
+        return float(self.learning_rate_obj)
+
+    def state_dict(self):
+        sd = super().state_dict()
+        if isinstance(self.learning_rate_obj, LRScheduler):
+            sd["LinearWarmup_LR"] = self.learning_rate_obj.state_dict()
+        return sd
+
+    def set_state_dict(self, sd):
+        super().set_state_dict(sd)
+        if isinstance(self.learning_rate_obj, LRScheduler) and "LinearWarmup_LR" in sd:
+            self.learning_rate_obj.set_state_dict(sd["LinearWarmup_LR"])
+
+
+class StepDecay(LRScheduler):
+    def __init__(self, learning_rate, step_size, gamma=0.1, last_epoch=-1, verbose=False):
+        self.step_size, self.gamma = step_size, gamma
+        super().__init__(learning_rate, last_epoch, verbose)
+
+    def get_lr(self):
+        return self.base_lr * (self.gamma ** (self.last_epoch // self.step_size))
+
+
+class MultiStepDecay(LRScheduler):
+    def __init__(self, learning_rate, milestones, gamma=0.1, last_epoch=-1, verbose=False):
+        self.milestones, self.gamma = milestones, gamma
+        super().__init__(learning_rate, last_epoch, verbose)
+
+    def get_lr(self):
+        n = sum(1 for m in self.milestones if self.last_epoch >= m)
+        return self.base_lr * (self.gamma ** n)
+
+
+class LambdaDecay(LRScheduler):
+    def __init__(self, learning_rate, lr_lambda, last_epoch=-1, verbose=False):
+        self.lr_lambda = lr_lambda
+        super().__init__(learning_rate, last_epoch, verbose)
+
+    def get_lr(self):
+        return self.base_lr * self.lr_lambda(self.last_epoch)
+
+
+class CosineAnnealingDecay(LRScheduler):
+    def __init__(self, learning_rate, T_max, eta_min=0, last_epoch=-1, verbose=False):
+        self.T_max, self.eta_min = T_max, float(eta_min)
+        super().__init__(learning_rate, last_epoch, verbose)
+
+    def get_lr(self):
+        return self.eta_min + (self.base_lr - self.eta_min) * (1 + math.cos(math.pi * self.last_epoch / self.T_max)) / 2
+
+
+class OneCycleLR(LRScheduler):
+    def __init__(self, max_learning_rate, total_steps, divide_factor=25.0, end_learning_rate=0.0001, phase_pct=0.3,
+                 anneal_strategy="cos", three_phase=False, last_epoch=-1, verbose=False):
+        self.max_lr, self.total, self.init_lr, self.end_lr = max_learning_rate, total_steps, max_learning_rate / divide_factor, end_learning_rate
+        self.up = int(phase_pct * total_steps)
+        self.cos = anneal_strategy == "cos"
+        super().__init__(self.init_lr, last_epoch, verbose)
+
+    def _interp(self, a, b, pct):
+        return b + (a - b) / 2.0 * (math.cos(math.pi * pct) + 1) if self.cos else (b - a) * pct + a
+
+    def get_lr(self):
+        e = self.last_epoch
+        if e <= self.up:
+            return self._interp(self.init_lr, self.max_lr, e / max(self.up, 1))
+        return self._interp(self.max_lr, self.end_lr, (e - self.up) / max(self.total - self.up, 1))
+
+
+class ReduceOnPlateau(LRScheduler):
+    def __init__(self, learning_rate, mode="min", factor=0.1, patience=10, threshold=1e-4, threshold_mode="rel",
+                 cooldown=0, min_lr=0, epsilon=1e-8, verbose=False):
+        self.mode, self.factor, self.patience, self.threshold = mode, factor, patience, threshold
+        self.threshold_mode, self.cooldown, self.min_lr, self.epsilon = threshold_mode, cooldown, min_lr, epsilon
+        self.best, self.num_bad, self.cooldown_counter = None, 0, 0
+        self.base_lr = self.last_lr = float(learning_rate)
+        self.last_epoch = 0
+        self.verbose = verbose
+
+    def step(self, metrics=None, epoch=None):
+        self.last_epoch = self.last_epoch + 1 if epoch is None else epoch
+        if metrics is None:
+            return
+        m = float(metrics.item() if hasattr(metrics, "item") else metrics)
+        better = self.best is None or (m < self.best - (abs(self.best) * self.threshold if self.threshold_mode == "rel" else self.threshold)
+                                       if self.mode == "min" else
+                                       m > self.best + (abs(self.best) * self.threshold if self.threshold_mode == "rel" else self.threshold))
+        if better:
+            self.best, self.num_bad = m, 0
+        else:
+            self.num_bad += 1
+        if self.cooldown_counter > 0:
+            self.cooldown_counter -= 1
+            self.num_bad = 0
+        if self.num_bad > self.patience:
+            new_lr = max(self.last_lr * self.factor, self.min_lr)
+            if self.last_lr - new_lr > self.epsilon:
+                self.last_lr = new_lr
+            self.cooldown_counter, self.num_bad = self.cooldown, 0

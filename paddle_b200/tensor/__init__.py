@@ -1,0 +1,5 @@
+"""paddle.tensor namespace (reference: python/paddle/tensor/__init__.py)."""
+from .creation import *  # noqa: F401,F403
+from .math import *  # noqa: F401,F403
+from .manipulation import *  # noqa: F401,F403
+from . import creation, math, manipulation  # noqa: F401

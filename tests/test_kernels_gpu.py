@@ -1,0 +1,347 @@
+"""Numerics of every hand-written sm_100a kernel against a plain PyTorch fp32 restatement of the same op
+(the reference's op-test strategy, SURVEY §4.1: NumPy/unfused oracle per op)."""
+import math
+
+import pytest
+import torch
+
+import paddle_b200 as paddle
+from paddle_b200 import lib, ops
+from paddle_b200.framework import flags
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _tol(dtype):
+    return dict(rtol=2e-2, atol=2e-2) if dtype != torch.float32 else dict(rtol=1e-4, atol=1e-5)
+
+
+def test_native_library_loaded():
+    assert lib.kernels.available(), lib.kernels._err
+    assert lib.kernels.pdb200_sm_count() >= 100
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("rows,cols", [(64, 4096), (33, 5120), (16, 768), (8, 100), (4, 16384)])
+def test_rms_norm_fwd_bwd(dtype, rows, cols):
+    torch.manual_seed(0)
+    x = torch.randn(rows, cols, device=DEV, dtype=dtype, requires_grad=True)
+    w = (torch.randn(cols, device=DEV, dtype=dtype) * 0.1 + 1).requires_grad_(True)
+    y = ops.rms_norm(x, w, 1e-6)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xr, wr = x.detach().float().requires_grad_(True), w.detach().float().requires_grad_(True)
+    yr = xr * torch.rsqrt(xr.pow(2).mean(-1, keepdim=True) + 1e-6) * wr
+    yr.backward(dy.float())
+    torch.testing.assert_close(y.float(), yr, **_tol(dtype))
+    torch.testing.assert_close(x.grad.float(), xr.grad, **_tol(dtype))
+    wt = dict(rtol=3e-2, atol=3e-2 * math.sqrt(rows)) if dtype != torch.float32 else dict(rtol=1e-3, atol=1e-3)
+    torch.testing.assert_close(w.grad.float(), wr.grad, **wt)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_rms_norm_residual(dtype):
+    torch.manual_seed(1)
+    x = torch.randn(48, 4096, device=DEV, dtype=dtype, requires_grad=True)
+    r = torch.randn(48, 4096, device=DEV, dtype=dtype, requires_grad=True)
+    w = torch.ones(4096, device=DEV, dtype=dtype, requires_grad=True)
+    y, ro = ops.rms_norm(x, w, 1e-5, residual=r)
+    (y.float().sum() + ro.float().pow(2).sum()).backward()
+    xr, rr = x.detach().float().requires_grad_(True), r.detach().float().requires_grad_(True)
+    s = (xr + rr).to(dtype).float() if dtype != torch.float32 else xr + rr
+    s2 = xr + rr
+    yr = s2 * torch.rsqrt(s2.pow(2).mean(-1, keepdim=True) + 1e-5)
+    (yr.sum() + s2.pow(2).sum()).backward()
+    torch.testing.assert_close(ro.float(), s, **_tol(dtype))
+    torch.testing.assert_close(y.float(), yr, **_tol(dtype))
+    torch.testing.assert_close(x.grad.float(), xr.grad, rtol=3e-2, atol=6e-2)
+    torch.testing.assert_close(r.grad.float(), rr.grad, rtol=3e-2, atol=6e-2)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("rows,cols", [(32, 768), (17, 1000), (8, 4096)])
+def test_layer_norm_fwd_bwd(dtype, rows, cols):
+    torch.manual_seed(2)
+    x = torch.randn(rows, cols, device=DEV, dtype=dtype, requires_grad=True)
+    w = torch.randn(cols, device=DEV, dtype=dtype, requires_grad=True)
+    b = torch.randn(cols, device=DEV, dtype=dtype, requires_grad=True)
+    y = ops.layer_norm(x, [cols], w, b, 1e-5)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xr, wr, br = (t.detach().float().requires_grad_(True) for t in (x, w, b))
+    yr = torch.nn.functional.layer_norm(xr, [cols], wr, br, 1e-5)
+    yr.backward(dy.float())
+    torch.testing.assert_close(y.float(), yr, **_tol(dtype))
+    torch.testing.assert_close(x.grad.float(), xr.grad, rtol=3e-2, atol=5e-2)
+    t = dict(rtol=3e-2, atol=3e-2 * math.sqrt(rows)) if dtype != torch.float32 else dict(rtol=1e-3, atol=1e-3)
+    torch.testing.assert_close(w.grad.float(), wr.grad, **t)
+    torch.testing.assert_close(b.grad.float(), br.grad, **t)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("packed", [True, False])
+def test_swiglu(dtype, packed):
+    torch.manual_seed(3)
+    H = 1376
+    if packed:
+        xy = torch.randn(40, 2 * H, device=DEV, dtype=dtype, requires_grad=True)
+        out = ops.swiglu(xy)
+        ref_in = xy.detach().float().requires_grad_(True)
+        a, b = ref_in.chunk(2, -1)
+    else:
+        x = torch.randn(40, H, device=DEV, dtype=dtype, requires_grad=True)
+        y = torch.randn(40, H, device=DEV, dtype=dtype, requires_grad=True)
+        out = ops.swiglu(x, y)
+        a, b = x.detach().float().requires_grad_(True), y.detach().float().requires_grad_(True)
+    g = torch.randn_like(out)
+    out.backward(g)
+    ref = torch.nn.functional.silu(a) * b
+    ref.backward(g.float())
+    torch.testing.assert_close(out.float(), ref, **_tol(dtype))
+    if packed:
+        torch.testing.assert_close(xy.grad.float(), ref_in.grad, **_tol(dtype))
+    else:
+        torch.testing.assert_close(x.grad.float(), a.grad, **_tol(dtype))
+        torch.testing.assert_close(y.grad.float(), b.grad, **_tol(dtype))
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("pairs", [True, False])
+@pytest.mark.parametrize("with_table", [True, False])
+def test_fused_rope(dtype, pairs, with_table):
+    if not with_table and not pairs:
+        pytest.skip("reference asserts use_neox_rotary_style when sin/cos are absent")
+    from paddle_b200.ops.rope import _rope_ref
+    torch.manual_seed(4)
+    b, s, h, d = 2, 64, 4, 128
+    q = torch.randn(b, s, h, d, device=DEV, dtype=dtype, requires_grad=True)
+    k = torch.randn(b, s, 2, d, device=DEV, dtype=dtype, requires_grad=True)
+    sin = cos = None
+    if with_table:
+        ang = torch.rand(1, s, 1, d // 2, device=DEV) * 6.28
+        ang = ang.repeat_interleave(2, -1) if pairs else torch.cat([ang, ang], -1)
+        sin, cos = ang.sin(), ang.cos()
+    oq, ok, _ = ops.fused_rope(q, k, None, sin, cos, None, use_neox_rotary_style=pairs)
+    gq, gk = torch.randn_like(oq), torch.randn_like(ok)
+    torch.autograd.backward([oq, ok], [gq, gk])
+    qr, kr = q.detach().float().requires_grad_(True), k.detach().float().requires_grad_(True)
+    rq = _rope_ref(qr, sin, cos, None, pairs, False, 10000.0)
+    rk = _rope_ref(kr, sin, cos, None, pairs, False, 10000.0)
+    torch.autograd.backward([rq, rk], [gq.float(), gk.float()])
+    tol = dict(rtol=2e-2, atol=3e-2) if dtype != torch.float32 else dict(rtol=1e-3, atol=2e-3)
+    torch.testing.assert_close(oq.float(), rq, **tol)
+    torch.testing.assert_close(ok.float(), rk, **tol)
+    torch.testing.assert_close(q.grad.float(), qr.grad, **tol)
+    torch.testing.assert_close(k.grad.float(), kr.grad, **tol)
+
+
+def test_fused_rope_position_ids():
+    from paddle_b200.ops.rope import _rope_ref
+    torch.manual_seed(5)
+    b, s, h, d = 2, 32, 2, 64
+    q = torch.randn(b, s, h, d, device=DEV)
+    ang = torch.rand(1, s, 1, d // 2, device=DEV).repeat_interleave(2, -1)
+    pid = torch.randint(0, s, (b, s), device=DEV)
+    oq, _, _ = ops.fused_rope(q, None, None, ang.sin(), ang.cos(), pid, use_neox_rotary_style=True)
+    ref = _rope_ref(q, ang.sin(), ang.cos(), pid, True, False, 10000.0)
+    torch.testing.assert_close(oq, ref, rtol=1e-4, atol=1e-4)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("V", [32000, 1000, 50257])
+def test_softmax_cross_entropy(dtype, V):
+    torch.manual_seed(6)
+    N = 257
+    logits = (torch.randn(N, V, device=DEV) * 3).to(dtype).requires_grad_(True)
+    labels = torch.randint(0, V, (N,), device=DEV)
+    labels[::7] = -100
+    loss = ops.softmax_cross_entropy(logits, labels, -100)
+    w = torch.rand(N, device=DEV)
+    (loss * w).sum().backward()
+    lr = logits.detach().double().requires_grad_(True)
+    ref = torch.nn.functional.cross_entropy(lr, labels, ignore_index=-100, reduction="none")
+    (ref * w.double()).sum().backward()
+    torch.testing.assert_close(loss.double(), ref, rtol=1e-3, atol=1e-3 if dtype == torch.float32 else 2e-2)
+    torch.testing.assert_close(logits.grad.double(), lr.grad, rtol=2e-2, atol=1e-3 if dtype != torch.float32 else 1e-5)
+
+
+def test_vocab_parallel_ce_pieces():
+    """Emulate n ranks on one device: per-shard stats -> combine == full-vocab loss; shard backward == slice."""
+    torch.manual_seed(7)
+    N, V, n = 64, 4096, 4
+    logits = torch.randn(N, V, device=DEV).bfloat16()
+    labels = torch.randint(0, V, (N,), device=DEV)
+    labels[3] = -100
+    Vp = V // n
+    stats = torch.stack([ops.ce_local_stats(logits[:, r * Vp:(r + 1) * Vp].contiguous(), labels, r * Vp, -100) for r in range(n)])
+    loss, lse = ops.ce_combine(stats, labels, -100)
+    ref = torch.nn.functional.cross_entropy(logits.float(), labels, ignore_index=-100, reduction="none")
+    torch.testing.assert_close(loss, ref, rtol=1e-3, atol=2e-3)
+    dl = torch.rand(N, device=DEV)
+    lr = logits.float().requires_grad_(True)
+    (torch.nn.functional.cross_entropy(lr, labels, ignore_index=-100, reduction="none") * dl).sum().backward()
+    for r in range(n):
+        g = ops.ce_local_backward(logits[:, r * Vp:(r + 1) * Vp].contiguous(), labels, lse, dl, r * Vp, -100)
+        torch.testing.assert_close(g.float(), lr.grad[:, r * Vp:(r + 1) * Vp], rtol=2e-2, atol=2e-3)
+
+
+@pytest.mark.parametrize("act", ["gelu", "relu", "swiglu", "geglu", "silu"])
+def test_fused_bias_act(act):
+    torch.manual_seed(8)
+    x = torch.randn(33, 1024, device=DEV, dtype=torch.bfloat16)
+    bias = torch.randn(1024, device=DEV, dtype=torch.bfloat16)
+    with torch.no_grad():
+        out = ops.fused_bias_act(x, bias, act)
+    v = x.float() + bias.float()
+    if act in ("swiglu", "geglu"):
+        a, b = v.chunk(2, -1)
+        ref = (torch.nn.functional.silu(a) if act == "swiglu" else torch.nn.functional.gelu(a)) * b
+    else:
+        ref = {"gelu": torch.nn.functional.gelu, "relu": torch.relu, "silu": torch.nn.functional.silu}[act](v)
+    torch.testing.assert_close(out.float(), ref, rtol=2e-2, atol=2e-2)
+
+
+@pytest.mark.parametrize("multi_precision", [True, False])
+def test_fused_adamw_matches_reference(multi_precision):
+    torch.manual_seed(9)
+    shapes = [(1024, 1024), (4096,), (333, 77), (5,), (70000,)]
+    dtype = torch.bfloat16 if multi_precision else torch.float32
+    params = [paddle.framework.Parameter(torch.randn(s, device=DEV).to(dtype)) for s in shapes]
+    ref_params = [p.detach().float().clone().requires_grad_(True) for p in params]
+    opt = paddle.optimizer.AdamW(learning_rate=1e-2, beta1=0.9, beta2=0.95, epsilon=1e-8, weight_decay=0.1,
+                                 parameters=params, multi_precision=multi_precision)
+    ref = torch.optim.AdamW(ref_params, lr=1e-2, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
+    for step in range(4):
+        for p, rp in zip(params, ref_params):
+            g = torch.randn_like(rp)
+            p.grad = g.to(dtype)
+            rp.grad = g.to(dtype).float()
+        opt.step()
+        ref.step()
+    for p, rp in zip(params, ref_params):
+        tgt = opt._master_weights[p.name] if multi_precision else p
+        torch.testing.assert_close(tgt.float(), rp.detach(), rtol=1e-4, atol=1e-5)
+        if multi_precision:
+            torch.testing.assert_close(p.float(), rp.detach().to(dtype).float(), rtol=1e-2, atol=1e-2)
+
+
+def test_adamw_found_inf_skips_and_grad_scale():
+    p = paddle.framework.Parameter(torch.ones(1000, device=DEV))
+    opt = paddle.optimizer.AdamW(1e-1, parameters=[p], weight_decay=0.0)
+    p.grad = torch.ones_like(p)
+    opt._found_inf = torch.ones(1, device=DEV)
+    opt.step()
+    assert torch.equal(p.detach(), torch.ones_like(p))
+    opt._found_inf = torch.zeros(1, device=DEV)
+    opt.step()
+    assert (p.detach() < 1).all()
+
+
+def test_multi_tensor_l2norm():
+    torch.manual_seed(10)
+    ts = [torch.randn(n, device=DEV).to(dt) for n, dt in [(100000, torch.float32), (7, torch.bfloat16), (65537, torch.bfloat16), (16384, torch.float16)]]
+    got = ops.squared_l2_norm(ts)
+    ref = sum(t.float().pow(2).sum() for t in ts)
+    torch.testing.assert_close(got.reshape(()), ref, rtol=1e-4, atol=1e-3)
+
+
+def test_unscale_and_check():
+    gs = [torch.ones(5000, device=DEV) * 4, torch.ones(300, device=DEV, dtype=torch.bfloat16) * 8]
+    tab = ops.grads_table(gs)
+    found = torch.zeros(1, device=DEV)
+    ops.unscale_and_check(tab, torch.full((1,), 0.25, device=DEV), found)
+    assert found.item() == 0 and torch.allclose(gs[0], torch.ones_like(gs[0])) and torch.allclose(gs[1].float(), torch.full_like(gs[1].float(), 2.0))
+    gs[0][17] = float("inf")
+    ops.unscale_and_check(ops.grads_table(gs), torch.ones(1, device=DEV), found)
+    assert found.item() == 1
+
+
+def test_moe_routing_ops():
+    torch.manual_seed(11)
+    n_expert, n_worker, N = 4, 2, 1000
+    gate = torch.randint(-1, n_expert * n_worker, (N,), device=DEV)
+    cnt = ops.number_count(gate, n_expert * n_worker)
+    ref = torch.bincount(gate[gate >= 0].cpu(), minlength=n_expert * n_worker)
+    assert torch.equal(cnt.cpu(), ref)
+    pos = ops.assign_pos(gate, torch.cumsum(cnt, 0))
+    order = torch.argsort(torch.where(gate >= 0, gate, torch.full_like(gate, 99)), stable=True)[: int(ref.sum())]
+    assert torch.equal(pos, order)
+    cap = torch.tensor([100, 50, 200, 10], device=DEV)
+    lim = ops.limit_by_capacity(cnt, cap, n_worker)
+    c = cnt.reshape(n_worker, n_expert)
+    before = torch.cumsum(c, 0) - c
+    assert torch.equal(lim.reshape(n_worker, n_expert), torch.minimum(c, (cap[None] - before).clamp(min=0)))
+    pruned = ops.prune_gate_by_capacity(gate, lim, n_expert, n_worker)
+    kept = torch.bincount(pruned[pruned >= 0].cpu(), minlength=n_expert * n_worker)
+    assert torch.equal(kept, torch.minimum(ref, lim.cpu()))
+    idx = torch.randint(0, 8, (N, 2), device=DEV)
+    val = torch.rand(N, 2, device=DEV)
+    prob = torch.rand(N, device=DEV)
+    rr = ops.random_routing(idx, val, prob)
+    exp = idx.clone()
+    exp[:, 1] = torch.where(2 * val[:, 1] < prob, torch.full_like(idx[:, 1], -1), idx[:, 1])
+    assert torch.equal(rr, exp)
+
+
+def test_topk_softmax_router():
+    torch.manual_seed(12)
+    lg = torch.randn(777, 8, device=DEV, dtype=torch.bfloat16)
+    w, idx, cnt = ops.topk_softmax(lg, 2)
+    p = torch.softmax(lg.float(), -1)
+    rw, ridx = torch.topk(p, 2, -1)
+    rw = rw / rw.sum(-1, keepdim=True)
+    assert torch.equal(idx, ridx)
+    torch.testing.assert_close(w, rw, rtol=1e-3, atol=1e-4)
+    assert torch.equal(cnt.cpu(), torch.bincount(ridx.reshape(-1).cpu(), minlength=8))
+
+
+def test_llama_tiny_trains_on_gpu_with_native_kernels():
+    from paddle_b200.models import LlamaConfig, LlamaForCausalLM
+    paddle.set_device("gpu:0")
+    paddle.seed(0)
+    cfg = LlamaConfig(vocab_size=1024, hidden_size=256, intermediate_size=768, num_hidden_layers=2, num_attention_heads=4)
+    paddle.set_default_dtype("bfloat16")
+    try:
+        m = LlamaForCausalLM(cfg)
+    finally:
+        paddle.set_default_dtype("float32")
+    opt = paddle.optimizer.AdamW(2e-3, parameters=m.parameters(), multi_precision=True, grad_clip=paddle.nn.ClipGradByGlobalNorm(1.0))
+    tok = torch.randint(0, 1024, (4, 129), device=DEV)
+    lib.reset_launch_count()
+    losses = []
+    for _ in range(8):
+        loss = m(tok[:, :-1], labels=tok[:, 1:])
+        loss.backward()
+        opt.step()
+        opt.clear_grad()
+        losses.append(float(loss))
+    assert losses[-1] < losses[0] - 0.5, losses
+    assert lib.launch_count() > 50
+
+
+def test_native_matches_torch_composition_end_to_end():
+    """Same tiny model, native kernels vs FLAGS_use_native_kernels=0 (torch ops): losses track each other."""
+    from paddle_b200.models import LlamaConfig, LlamaForCausalLM
+    paddle.set_device("gpu:0")
+    cfg = LlamaConfig(vocab_size=512, hidden_size=128, intermediate_size=384, num_hidden_layers=2, num_attention_heads=4)
+    tok = torch.randint(0, 512, (2, 65), device=DEV)
+    curves = []
+    for native in (True, False):
+        flags.set_flags({"use_native_kernels": native})
+        try:
+            paddle.seed(3)
+            m = LlamaForCausalLM(cfg)
+            opt = paddle.optimizer.AdamW(1e-3, parameters=m.parameters())
+            c = []
+            for _ in range(5):
+                loss = m(tok[:, :-1], labels=tok[:, 1:])
+                loss.backward()
+                opt.step()
+                opt.clear_grad()
+                c.append(float(loss))
+            curves.append(c)
+        finally:
+            flags.set_flags({"use_native_kernels": True})
+    for a, b in zip(*curves):
+        assert abs(a - b) < 5e-3 * max(1.0, abs(b)), curves
