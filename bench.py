@@ -179,7 +179,7 @@ def main():
         loss = model(tokens[:, :-1], labels=tokens[:, 1:])
         loss.backward()
         opt.step()
-        opt.clear_grad()
+        opt.clear_grad(set_to_zero=False)      # grads are re-created by autograd: no zero-fill, no accumulate pass
         return loss
 
     def barrier():

@@ -105,6 +105,9 @@ struct RopeArgs {
   const void* in[3];
   void* out[3];
   int heads[3];
+  int64_t in_tok_stride[3];    // elements between consecutive tokens (heads*d when dense, packed width for qkv)
+  int64_t out_tok_stride[3];
+  int rotate[3];               // 0 = plain copy (v in the fused qkv split)
   int n_tensors;
 };
 
@@ -134,8 +137,22 @@ __global__ void __launch_bounds__(256) rope_kernel(RopeArgs a, const float* __re
     const int64_t bi = time_major ? tok % batch : tok / seq;
     const int64_t si = time_major ? tok / batch : tok % seq;
     const int64_t pos = pos_ids ? pos_ids[bi * seq + si] : si;
-    const T* src = (const T*)a.in[t] + (tok * a.heads[t] + hh) * (int64_t)d;
-    T* dst = (T*)a.out[t] + (tok * a.heads[t] + hh) * (int64_t)d;
+    const T* src = (const T*)a.in[t] + tok * a.in_tok_stride[t] + hh * (int64_t)d;
+    T* dst = (T*)a.out[t] + tok * a.out_tok_stride[t] + hh * (int64_t)d;
+    if (!a.rotate[t]) {
+      if (NEOX) {
+        Vec<T> lo, hi;
+        lo.load_nc(src + v * N);
+        hi.load_nc(src + half + v * N);
+        lo.store(dst + v * N);
+        hi.store(dst + half + v * N);
+      } else {
+        Vec<T> x;
+        x.load_nc(src + v * N);
+        x.store(dst + v * N);
+      }
+      continue;
+    }
     if (NEOX) {
       Vec<T> lo, hi, olo, ohi;
       lo.load_nc(src + v * N);
@@ -286,6 +303,9 @@ PDB_EXPORT int pdb200_rope(const void* q, const void* k, const void* v, void* oq
       a.in[a.n_tensors] = ins[i];
       a.out[a.n_tensors] = outs[i];
       a.heads[a.n_tensors] = hs[i];
+      a.in_tok_stride[a.n_tensors] = (int64_t)hs[i] * d;
+      a.out_tok_stride[a.n_tensors] = (int64_t)hs[i] * d;
+      a.rotate[a.n_tensors] = 1;
       a.n_tensors++;
       PDB_REQUIRE((uintptr_t)ins[i] % 16 == 0 && (uintptr_t)outs[i] % 16 == 0, "rope: tensors must be 16-byte aligned");
     }
@@ -304,6 +324,46 @@ PDB_EXPORT int pdb200_rope(const void* q, const void* k, const void* v, void* oq
       rope_kernel<T, false><<<stream_grid(items, 256), 256, 0, st>>>(a, sin_t, cos_t, pos_ids, batch, seq, d, time_major, base, sign);
   });
   return check_launch("rope");
+}
+
+// Fused QKV split + rotary embedding (forward) / merge + inverse rotary (backward, sign = -1):
+//   split = 1: packed [tokens, (hq + 2 hk) * d] -> q [tokens, hq, d], k, v contiguous, q/k rotated, v copied
+//   split = 0: q, k, v contiguous -> packed, q/k rotated with `sign`, v copied
+// One pass over the data instead of three strided copies + a rope launch (+ zero/copy/add kernels in backward).
+PDB_EXPORT int pdb200_qkv_rope(const void* packed, void* q, void* k, void* v, int hq, int hk, const float* sin_t,
+                               const float* cos_t, const int64_t* pos_ids, int64_t batch, int64_t seq, int d,
+                               int rotate_half, float base, float sign, int split, int dtype, void* stream) {
+  RopeArgs a{};
+  const int64_t W = (int64_t)(hq + 2 * hk) * d;
+  const int hs[3] = {hq, hk, hk};
+  const int64_t offs[3] = {0, (int64_t)hq * d, (int64_t)(hq + hk) * d};
+  void* sep[3] = {q, k, v};
+  const int esz = dtype == PDB_DTYPE_F32 ? 4 : 2;
+  for (int i = 0; i < 3; ++i) {
+    char* pk = (char*)const_cast<void*>(packed) + offs[i] * esz;
+    a.in[i] = split ? (const void*)pk : (const void*)sep[i];
+    a.out[i] = split ? sep[i] : (void*)pk;
+    a.heads[i] = hs[i];
+    a.in_tok_stride[i] = split ? W : (int64_t)hs[i] * d;
+    a.out_tok_stride[i] = split ? (int64_t)hs[i] * d : W;
+    a.rotate[i] = i < 2;
+    PDB_REQUIRE((uintptr_t)a.in[i] % 16 == 0 && (uintptr_t)a.out[i] % 16 == 0, "qkv_rope: tensors must be 16-byte aligned");
+  }
+  a.n_tensors = 3;
+  if (batch * seq == 0) return 0;
+  PDB_REQUIRE((sin_t == nullptr) == (cos_t == nullptr), "qkv_rope: sin and cos must be given together");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int total_heads = hq + 2 * hk;
+  PDB_DISPATCH_FLOAT(dtype, T, {
+    constexpr int N = 16 / sizeof(T);
+    PDB_REQUIRE(d % (2 * N) == 0, "qkv_rope: head_dim %d must be a multiple of %d", d, 2 * N);
+    const int64_t items = batch * seq * total_heads * (rotate_half ? d / 2 / N : d / N);
+    if (rotate_half)
+      rope_kernel<T, true><<<stream_grid(items, 256), 256, 0, st>>>(a, sin_t, cos_t, pos_ids, batch, seq, d, 0, base, sign);
+    else
+      rope_kernel<T, false><<<stream_grid(items, 256), 256, 0, st>>>(a, sin_t, cos_t, pos_ids, batch, seq, d, 0, base, sign);
+  });
+  return check_launch("qkv_rope");
 }
 
 template <typename T>

@@ -33,6 +33,10 @@ PDB_API int pdb200_swiglu_bwd(const void* x, const void* y, const void* dout, vo
  * sign=+1 forward, -1 backward. sin/cos: fp32 [positions, d] or both null (computed from base). */
 PDB_API int pdb200_rope(const void* q, const void* k, const void* v, void* oq, void* ok, void* ov, int hq, int hk, int hv, const float* sin_t, const float* cos_t, const int64_t* pos_ids, int64_t batch, int64_t seq, int d, int rotate_half, int time_major, float base, float sign, int dtype, void* stream);
 
+/* K20b fused QKV split + rotary (split=1) / merge + inverse rotary (split=0, sign=-1): one pass instead of three
+ * strided copies + rope (no counterpart op in the reference, which runs split/transpose kernels around fused_rope). */
+PDB_API int pdb200_qkv_rope(const void* packed, void* q, void* k, void* v, int hq, int hk, const float* sin_t, const float* cos_t, const int64_t* pos_ids, int64_t batch, int64_t seq, int d, int rotate_half, float base, float sign, int split, int dtype, void* stream);
+
 /* K22 fused bias + activation (reference: phi/kernels/fusion/gpu/fused_bias_act_kernel.cu:30-545).
  * act: 0 gelu, 1 relu, 2 swiglu, 3 geglu, 4 silu, 5 identity; GLU variants read 2*cols_out input columns. */
 PDB_API int pdb200_bias_act(const void* x, const void* bias, void* out, int64_t rows, int64_t cols_out, int act, int dtype, void* stream);
@@ -60,6 +64,12 @@ PDB_API int pdb200_limit_by_capacity(const int64_t* expert_count, const int64_t*
 PDB_API int pdb200_prune_gate_by_capacity(const int64_t* gate, int64_t* new_gate, const int64_t* expert_count, int* remaining_i32, int n_bins, int64_t n, void* stream);
 PDB_API int pdb200_random_routing(int64_t* topk_idx, const void* topk_val, const void* prob, int64_t n, int dtype, void* stream);
 PDB_API int pdb200_topk_softmax(const void* logits, int64_t tokens, int E, int k, int renorm, float* weights, int64_t* idx, int64_t* counts, int dtype, void* stream);
+
+/* K23/K13 tcgen05 + TMA bf16 GEMM: C[M,N] (=|+=) act(op(A) op(B) + bias), fp32 accumulation in TMEM (reference:
+ * cuBLASLt behind phi/kernels/funcs/blas/blaslt_impl.cu.h, fusion/gpu/fused_gemm_epilogue_kernel.cu:63-125,
+ * fused_linear_param_grad_add_kernel.cu:35-289).  A: [M,K] row-major, or [K,M] when trans_a.  B: [K,N] row-major, or
+ * [N,K] when trans_b.  out_dtype 0 = fp32 (beta = 1 accumulates into C), 1 = bf16.  act: 0 none, 1 gelu, 2 relu. */
+PDB_API int pdb200_gemm_bf16(const void* a, const void* b, void* c, const void* bias, int64_t M, int64_t N, int64_t K, int trans_a, int trans_b, int out_dtype, float beta, int act, void* stream);
 
 #ifdef __cplusplus
 }

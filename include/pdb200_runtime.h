@@ -1,0 +1,66 @@
+/* C ABI of libpdb200_runtime.so - the host-side native runtime of the paddle_b200 framework:
+ * TCP key/value store (rendezvous, handle exchange), communication watchdog, gradient-bucket assignment,
+ * flag mirror, symmetric-memory arena (CUDA VMM + NVLS multicast).  Every call returns 0 / a non-negative value
+ * on success and a negative value on failure (message via pdb200_rt_last_error()).  Parsed by
+ * paddle_b200/lib/__init__.py for the ctypes signatures: one declaration per statement.
+ */
+#ifndef PDB200_RUNTIME_H_
+#define PDB200_RUNTIME_H_
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+#define PDB_API
+
+PDB_API const char* pdb200_rt_last_error();
+
+/* TCP store (reference: paddle/phi/core/distributed/store/tcp_store.{h,cc}: MasterDaemon poll() loop with
+ * ADD/GET/CHECK/SET/WAIT/STOP, clients with retry connect).  handle = opaque pointer. */
+PDB_API void* pdb200_store_create(const char* host, int port, int is_master, int world_size, int timeout_ms);
+PDB_API void pdb200_store_destroy(void* store);
+PDB_API int pdb200_store_set(void* store, const char* key, const void* value, int64_t nbytes);
+PDB_API int64_t pdb200_store_get(void* store, const char* key, void* out, int64_t capacity, int timeout_ms);
+PDB_API int64_t pdb200_store_add(void* store, const char* key, int64_t delta);
+PDB_API int pdb200_store_check(void* store, const char* key);
+PDB_API int pdb200_store_wait(void* store, const char* key, int timeout_ms);
+PDB_API int pdb200_store_delete(void* store, const char* key);
+PDB_API int pdb200_store_port(void* store);
+
+/* Communication watchdog (reference: paddle/phi/core/distributed/comm_task_manager.cc:65-280,
+ * nccl_comm_task.cc:30-268).  A background thread classifies tasks older than the timeout and logs a trace line
+ * with group, sequence, op and numel plus the group's last finished task; abort_on_timeout ends the process so
+ * the launcher can restart the job. */
+PDB_API int pdb200_wd_start(int rank, int timeout_ms, int poll_ms);
+PDB_API int pdb200_wd_stop();
+PDB_API int pdb200_wd_task_begin(int group, int64_t seq, const char* op, int64_t numel, int sync_op);
+PDB_API int pdb200_wd_task_end(int group, int64_t seq);
+PDB_API int pdb200_wd_inflight();
+PDB_API int pdb200_wd_timeouts();
+PDB_API int pdb200_wd_set_abort(int abort_on_timeout);
+PDB_API int64_t pdb200_wd_dump(char* out, int64_t capacity);
+
+/* Gradient bucket assignment (reference: paddle/fluid/distributed/collective/reducer.cc:47-158
+ * Eager_AssignGroupBySize).  sizes: bytes per tensor, dtype_ids: small ints, is_sparse: 0/1, limits: bytes;
+ * out_group[i] = bucket index of tensor i (buckets ordered by their first tensor).  Returns the bucket count. */
+PDB_API int pdb200_assign_group_by_size(const int64_t* sizes, const int* dtype_ids, const int* is_sparse, int n, const int64_t* limits, int n_limits, int* out_group);
+
+/* Flag mirror: Python pushes every FLAGS_* change so native code can read it without the interpreter. */
+PDB_API int pdb200_flag_set(const char* name, const char* value);
+PDB_API int64_t pdb200_flag_get(const char* name, char* out, int64_t capacity);
+
+/* Symmetric-memory arena (reference has none): every rank of a group allocates one physical segment
+ * with cuMemCreate, exports a POSIX file descriptor, passes it to its peers over a Unix-domain socket
+ * (SCM_RIGHTS) and maps every peer's segment, so device code holds nranks base pointers; when the fabric
+ * supports it an NVLS multicast object is bound to all segments and mapped as one more address.
+ * rendezvous_dir: a directory visible to all ranks of the node (socket paths).  Returns an opaque handle. */
+PDB_API void* pdb200_symm_create(int rank, int nranks, int device, int64_t bytes, const char* rendezvous_dir, const char* tag, int want_multicast, int timeout_ms);
+PDB_API void pdb200_symm_destroy(void* arena);
+PDB_API int64_t pdb200_symm_bytes(void* arena);
+PDB_API uint64_t pdb200_symm_peer_ptr(void* arena, int peer);
+PDB_API uint64_t pdb200_symm_multicast_ptr(void* arena);
+PDB_API int pdb200_symm_supported(int device);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PDB200_RUNTIME_H_ */

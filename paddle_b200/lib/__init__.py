@@ -104,7 +104,7 @@ class NativeLib:
 
 # kernel launches per entry point (for bench.py's "gpu_launches" claim); entries not listed launch nothing
 _LAUNCHES = {
-    "pdb200_norm_fwd": 1, "pdb200_norm_bwd": 2, "pdb200_swiglu_fwd": 1, "pdb200_swiglu_bwd": 1, "pdb200_rope": 1,
+    "pdb200_norm_fwd": 1, "pdb200_norm_bwd": 2, "pdb200_swiglu_fwd": 1, "pdb200_swiglu_bwd": 1, "pdb200_rope": 1, "pdb200_qkv_rope": 1,
     "pdb200_bias_act": 1, "pdb200_adamw_multi": 1, "pdb200_momentum_multi": 1, "pdb200_l2norm_multi": 2,
     "pdb200_unscale_check_multi": 1, "pdb200_ce_fwd": 1, "pdb200_ce_combine": 1, "pdb200_ce_bwd": 1,
     "pdb200_number_count": 1, "pdb200_assign_pos": 1, "pdb200_limit_by_capacity": 1,

@@ -119,9 +119,8 @@ class LlamaAttention(nn.Layer):
             qkv = qkv.transpose(0, 1)        # [s, b, .] -> [b, s, .]
         b, s = qkv.shape[0], qkv.shape[1]
         nq, nkv, d = self.num_heads, self.num_kv_heads, self.head_dim
-        qkv = qkv.reshape(b, s, nq + 2 * nkv, d)
-        q, k, v = qkv[:, :, :nq], qkv[:, :, nq:nq + nkv], qkv[:, :, nq + nkv:]
-        q, k, _ = _rope(q, k, position_ids, self.config.rope_theta)
+        sin, cos = _rope_tables(s, d, self.config.rope_theta, qkv.device)
+        q, k, v = paddle.ops.qkv_split_rope(qkv, nq, nkv, sin, cos, position_ids, use_neox_rotary_style=False)
         out, _ = F.flash_attention(q, k, v, causal=True, training=self.training)
         out = out.reshape(b, s, nq * d)
         if sp:

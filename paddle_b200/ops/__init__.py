@@ -10,5 +10,5 @@ from .moe import (assign_pos, limit_by_capacity, number_count, prune_gate_by_cap
 from .multi_tensor import (TensorTable, adamw_step, grads_table, l2norm_sq, momentum_step, squared_l2_norm,  # noqa: F401
                            unscale_and_check)
 from .norm import layer_norm, rms_norm  # noqa: F401
-from .rope import fused_rope  # noqa: F401
+from .rope import fused_rope, qkv_split_rope  # noqa: F401
 from . import gemm  # noqa: F401

@@ -65,8 +65,39 @@ class _SwigluFn(torch.autograd.Function):
         return dx, dy
 
 
+class _SwigluPackedFn(torch.autograd.Function):
+    """silu(xy[..., :H]) * xy[..., H:] on the packed gate|up projection: the halves are addressed by stride inside the
+    kernel and the gradient is produced packed, so neither a split copy nor a cat appears in the graph."""
+
+    @staticmethod
+    def forward(ctx, xy):
+        xy = xy.contiguous()
+        H = xy.shape[-1] // 2
+        rows = xy.numel() // (2 * H)
+        out = torch.empty(*xy.shape[:-1], H, dtype=xy.dtype, device=xy.device)
+        base = xy.data_ptr()
+        check(K().pdb200_swiglu_fwd(base, base + H * xy.element_size(), ptr(out), rows, H, 2 * H, 2 * H, dtype_code(xy),
+                                    stream_ptr(xy.device)), "swiglu_fwd")
+        ctx.save_for_backward(xy)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (xy,) = ctx.saved_tensors
+        H = xy.shape[-1] // 2
+        rows = xy.numel() // (2 * H)
+        dout = dout.contiguous()
+        dxy = torch.empty_like(xy)
+        es = xy.element_size()
+        check(K().pdb200_swiglu_bwd(xy.data_ptr(), xy.data_ptr() + H * es, ptr(dout), dxy.data_ptr(), dxy.data_ptr() + H * es,
+                                    rows, H, 2 * H, 2 * H, 2 * H, 2 * H, dtype_code(xy), stream_ptr(xy.device)), "swiglu_bwd")
+        return dxy
+
+
 def swiglu(x, y=None):
     if y is None:
+        if use_native(x) and x.shape[-1] % 2 == 0 and (x.shape[-1] // 2 * x.element_size()) % 16 == 0:
+            return _SwigluPackedFn.apply(x)
         x, y = x.chunk(2, dim=-1)
     if use_native(x, y):
         return _SwigluFn.apply(x, y)

@@ -82,3 +82,50 @@ def fused_rope(q, k=None, v=None, sin=None, cos=None, position_ids=None, use_neo
         pid = position_ids.long().contiguous() if position_ids is not None else None
         return _RopeFn.apply(q, k, v, sin_t, cos_t, pid, pairs, time_major, rotary_emb_base)
     return tuple(_rope_ref(t, sin, cos, position_ids, pairs, time_major, rotary_emb_base) for t in (q, k, v))
+
+
+class _QKVRopeFn(torch.autograd.Function):
+    """Fused split of the packed QKV projection + rotary embedding on q/k (K20b).  Backward merges dq/dk/dv back
+    into one packed gradient with the inverse rotation - one pass each way, no strided copies, no zero/add kernels."""
+
+    @staticmethod
+    def forward(ctx, qkv, nq, nkv, sin, cos, pos_ids, pairs, base):
+        b, s = qkv.shape[0], qkv.shape[1]
+        d = qkv.shape[-1] // (nq + 2 * nkv)
+        qkv = qkv.contiguous()
+        q = torch.empty(b, s, nq, d, dtype=qkv.dtype, device=qkv.device)
+        k = torch.empty(b, s, nkv, d, dtype=qkv.dtype, device=qkv.device)
+        v = torch.empty(b, s, nkv, d, dtype=qkv.dtype, device=qkv.device)
+        check(K().pdb200_qkv_rope(ptr(qkv), ptr(q), ptr(k), ptr(v), nq, nkv, ptr(sin), ptr(cos), ptr(pos_ids), b, s, d,
+                                  int(not pairs), float(base), 1.0, 1, dtype_code(qkv), stream_ptr(qkv.device)), "qkv_rope")
+        ctx.save_for_backward(sin, cos, pos_ids)
+        ctx.cfg = (nq, nkv, pairs, base, d)
+        return q, k, v
+
+    @staticmethod
+    def backward(ctx, dq, dk, dv):
+        sin, cos, pos_ids = ctx.saved_tensors
+        nq, nkv, pairs, base, d = ctx.cfg
+        dq, dk, dv = dq.contiguous(), dk.contiguous(), dv.contiguous()
+        b, s = dq.shape[0], dq.shape[1]
+        dqkv = torch.empty(b, s, (nq + 2 * nkv) * d, dtype=dq.dtype, device=dq.device)
+        check(K().pdb200_qkv_rope(ptr(dqkv), ptr(dq), ptr(dk), ptr(dv), nq, nkv, ptr(sin), ptr(cos), ptr(pos_ids), b, s, d,
+                                  int(not pairs), float(base), -1.0, 0, dtype_code(dq), stream_ptr(dq.device)), "qkv_rope(bwd)")
+        return dqkv, None, None, None, None, None, None, None
+
+
+def qkv_split_rope(qkv, num_q_heads, num_kv_heads, sin=None, cos=None, position_ids=None, use_neox_rotary_style=True,
+                   rotary_emb_base=10000.0):
+    """qkv: [b, s, (hq + 2 hk) * d] packed projection output -> (q [b,s,hq,d], k, v [b,s,hk,d]) with q/k rotated."""
+    pairs = bool(use_neox_rotary_style)
+    d = qkv.shape[-1] // (num_q_heads + 2 * num_kv_heads)
+    if use_native(qkv):
+        sin_t = sin.reshape(-1, d).float().contiguous() if sin is not None else None
+        cos_t = cos.reshape(-1, d).float().contiguous() if cos is not None else None
+        pid = position_ids.long().contiguous() if position_ids is not None else None
+        return _QKVRopeFn.apply(qkv, num_q_heads, num_kv_heads, sin_t, cos_t, pid, pairs, rotary_emb_base)
+    b, s = qkv.shape[0], qkv.shape[1]
+    x = qkv.reshape(b, s, num_q_heads + 2 * num_kv_heads, d)
+    q, k, v = x[:, :, :num_q_heads], x[:, :, num_q_heads:num_q_heads + num_kv_heads], x[:, :, num_q_heads + num_kv_heads:]
+    q, k, _ = fused_rope(q, k, None, sin, cos, position_ids, use_neox_rotary_style, False, rotary_emb_base)
+    return q, k, v

@@ -138,13 +138,33 @@ class Optimizer:
 
     @torch.no_grad()
     def _apply_optimize(self, loss, startup_program, params_grads, param_group_idx=0):
+        folded = False
         if self._grad_clip is not None:
-            params_grads = self._grad_clip(params_grads)
+            if self._can_fold_clip(params_grads):
+                # global-norm clip folded into the update kernel: one multi-tensor L2-norm launch, the coefficient
+                # stays on the device and multiplies the gradients inside the AdamW kernel (no pass over the grads)
+                clip = self._grad_clip
+                grads = [g for p, g in params_grads if getattr(p, "need_clip", True)]
+                coef = clip.clip_coef(clip.global_norm_sq(grads))
+                prev = self._grad_scale_dev
+                self._grad_scale_dev = coef if prev is None else prev * coef
+                folded = True
+            else:
+                params_grads = self._grad_clip(params_grads)
         if not params_grads:
             return
-        self._create_accumulators([p for p, _ in params_grads])
-        self._update(params_grads)
+        try:
+            self._create_accumulators([p for p, _ in params_grads])
+            self._update(params_grads)
+        finally:
+            if folded:
+                self._grad_scale_dev = prev
         self._step_count += 1
+
+    def _can_fold_clip(self, params_grads):
+        from ..nn.clip import ClipGradByGlobalNorm
+        return (type(self._grad_clip) is ClipGradByGlobalNorm and getattr(self, "_fold_clip_ok", False) and bool(params_grads)
+                and all(self._native(p) and getattr(p, "need_clip", True) for p, _ in params_grads))
 
     def _update(self, params_grads):
         raise NotImplementedError
@@ -322,6 +342,7 @@ class Momentum(SGD):
 # ======================================================================================= Adam / AdamW
 class Adam(Optimizer):
     _decoupled = False
+    _fold_clip_ok = True      # the native kernel multiplies grads by a device scalar
 
     def __init__(self, learning_rate=0.001, beta1=0.9, beta2=0.999, epsilon=1e-08, parameters=None, weight_decay=None,
                  grad_clip=None, lazy_mode=False, multi_precision=False, use_multi_tensor=False, amsgrad=False, name=None):
@@ -511,6 +532,8 @@ class RMSProp(Optimizer):
 
 
 class Lamb(Adam):
+    _fold_clip_ok = False
+
     def __init__(self, learning_rate=0.001, lamb_weight_decay=0.01, beta1=0.9, beta2=0.999, epsilon=1e-06,
                  parameters=None, grad_clip=None, exclude_from_weight_decay_fn=None, multi_precision=False,
                  always_adapt=False, name=None):

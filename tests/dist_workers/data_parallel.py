@@ -1,0 +1,67 @@
+"""Worker: DataParallel (bucketed reducer) == single-process training on the concatenated batch; no_sync; unused params."""
+import torch
+
+import paddle_b200 as paddle
+import paddle_b200.distributed as dist
+from paddle_b200 import nn
+from paddle_b200.models import GPTConfig, GPTForCausalLM
+
+dist.init_parallel_env()
+r, n = dist.get_rank(), dist.get_world_size()
+cfg = GPTConfig(vocab_size=64, hidden_size=256, num_hidden_layers=2, num_attention_heads=4, max_position_embeddings=32)
+
+
+def build():
+    paddle.seed(5)
+    with paddle.utils.unique_name.guard():
+        return GPTForCausalLM(cfg)
+
+
+torch.manual_seed(0)
+data = torch.randint(0, 64, (4, 17))          # global batch 4, 2 per rank
+ref = build()
+ropt = paddle.optimizer.SGD(0.05, parameters=ref.parameters())   # SGD: linear in the grads (Adam would amplify rounding noise of ~0 grads)
+m = build()
+dp = paddle.DataParallel(m, comm_buffer_size=1, last_comm_buffer_size=0.25)     # small buckets: several per step
+assert len(dp._reducer.buckets) > 2
+opt = paddle.optimizer.SGD(0.05, parameters=m.parameters())
+for step in range(3):
+    loss = dp(data[2 * r:2 * r + 2, :-1], labels=data[2 * r:2 * r + 2, 1:])
+    loss.backward(); opt.step(); opt.clear_grad()
+    rl = ref(data[:, :-1], labels=data[:, 1:])
+    rl.backward(); ropt.step(); ropt.clear_grad()
+for (k, a), (_, b) in zip(m.state_dict().items(), ref.state_dict().items()):
+    torch.testing.assert_close(a.detach(), b.detach(), rtol=2e-4, atol=2e-5, msg=lambda s: f"{k}: {s}")
+
+# no_sync: grads stay local
+with dp.no_sync():
+    dp(data[2 * r:2 * r + 2, :-1], labels=data[2 * r:2 * r + 2, 1:]).backward()
+g = m.lm_head.weight.grad.clone()
+parts = []
+dist.all_gather(parts, g)
+assert not torch.allclose(parts[0], parts[1])
+opt.clear_grad()
+
+
+class Two(nn.Layer):
+    def __init__(self):
+        super().__init__()
+        self.a, self.b = nn.Linear(4, 4), nn.Linear(4, 4)
+
+    def forward(self, x):
+        return self.a(x)          # self.b unused
+
+
+paddle.seed(1)
+t = paddle.DataParallel(Two(), find_unused_parameters=True)
+t(torch.ones(2, 4) * (r + 1)).sum().backward()
+parts = []
+dist.all_gather(parts, t._layers.a.weight.grad)
+torch.testing.assert_close(parts[0], parts[1])
+t2 = paddle.DataParallel(Two(), find_unused_parameters=False)
+try:
+    t2(torch.ones(2, 4)).sum().backward()
+    raise SystemExit("expected unused-parameter error")
+except RuntimeError as e:
+    assert "find_unused_parameters" in str(e)
+print("data_parallel ok", r)

@@ -1,0 +1,79 @@
+"""tcgen05/TMA GEMM (K23/K13) against torch fp32 matmul, all operand majors, tails, epilogues."""
+import pytest
+import torch
+
+from paddle_b200 import ops
+from paddle_b200.ops import gemm as G
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _ref(a, b, ta, tb):
+    A = a.float().t() if ta else a.float()
+    B = b.float().t() if tb else b.float()
+    return A @ B
+
+
+@pytest.mark.parametrize("ta,tb", [(False, False), (False, True), (True, False), (True, True)])
+@pytest.mark.parametrize("M,N,K", [(256, 256, 128), (512, 1024, 512), (384, 640, 320), (1024, 4096, 1024), (264, 328, 200)])
+def test_gemm_majors_and_tails(ta, tb, M, N, K):
+    torch.manual_seed(M + N + K)
+    a = (torch.randn((K, M) if ta else (M, K), device=DEV) * 0.5).bfloat16()
+    b = (torch.randn((N, K) if tb else (K, N), device=DEV) * 0.5).bfloat16()
+    assert G.supported(a, b, ta, tb)
+    out = G.gemm(a, b, ta, tb)
+    ref = _ref(a, b, ta, tb)
+    assert out.dtype == torch.bfloat16 and out.shape == (M, N)
+    torch.testing.assert_close(out.float(), ref, rtol=2e-2, atol=2e-2 * (K ** 0.5) * 0.25)
+
+
+def test_gemm_fp32_out_and_accumulate():
+    torch.manual_seed(1)
+    M, N, K = 512, 768, 1024
+    a = torch.randn(K, M, device=DEV).bfloat16()     # wgrad shape: X^T dY
+    b = torch.randn(K, N, device=DEV).bfloat16()
+    acc = torch.randn(M, N, device=DEV)
+    ref = acc + _ref(a, b, True, False)
+    G.gemm(a, b, True, False, accum_into=acc)
+    torch.testing.assert_close(acc, ref, rtol=1e-3, atol=1e-2)
+    out = G.gemm(a, b, True, False, out_dtype=torch.float32)
+    torch.testing.assert_close(out, _ref(a, b, True, False), rtol=1e-3, atol=1e-2)
+
+
+@pytest.mark.parametrize("act", ["none", "gelu", "relu"])
+def test_gemm_bias_act_epilogue(act):
+    torch.manual_seed(2)
+    M, N, K = 256, 512, 256
+    a = (torch.randn(M, K, device=DEV) * 0.3).bfloat16()
+    b = (torch.randn(K, N, device=DEV) * 0.3).bfloat16()
+    bias = torch.randn(N, device=DEV).bfloat16()
+    out = G.gemm(a, b, bias=bias, act=act)
+    ref = _ref(a, b, False, False) + bias.float()
+    ref = {"none": lambda x: x, "gelu": torch.nn.functional.gelu, "relu": torch.relu}[act](ref)
+    torch.testing.assert_close(out.float(), ref, rtol=2e-2, atol=5e-2)
+
+
+def test_linear_autograd_through_tc_gemm():
+    """F.linear forward/backward routed through the tcgen05 kernel == torch matmul autograd."""
+    import paddle_b200 as paddle
+    torch.manual_seed(3)
+    x = (torch.randn(4, 128, 512, device=DEV) * 0.5).bfloat16().requires_grad_(True)
+    w = paddle.framework.Parameter((torch.randn(512, 1024, device=DEV) * 0.05).bfloat16())
+    y = paddle.nn.functional.linear(x, w)
+    g = torch.randn_like(y)
+    y.backward(g)
+    xr, wr = x.detach().float().requires_grad_(True), w.detach().float().requires_grad_(True)
+    (xr @ wr).backward(g.float())
+    torch.testing.assert_close(y.float(), xr @ wr, rtol=2e-2, atol=5e-2)
+    torch.testing.assert_close(x.grad.float(), xr.grad, rtol=2e-2, atol=1e-1)
+    torch.testing.assert_close(w.grad.float(), wr.grad, rtol=2e-2, atol=5e-1)
+    # fp32 main_grad accumulation in the wgrad epilogue (K13)
+    w2 = paddle.framework.Parameter(w.detach().clone())
+    w2.main_grad = torch.zeros(512, 1024, device=DEV)
+    w2._fuse_main_grad = True
+    x2 = x.detach().clone().requires_grad_(True)
+    for _ in range(2):
+        paddle.nn.functional.linear(x2, w2).backward(g)
+    assert w2.grad is None
+    torch.testing.assert_close(w2.main_grad, 2 * wr.grad, rtol=1e-2, atol=5e-1)

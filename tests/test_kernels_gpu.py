@@ -291,9 +291,11 @@ def test_topk_softmax_router():
     p = torch.softmax(lg.float(), -1)
     rw, ridx = torch.topk(p, 2, -1)
     rw = rw / rw.sum(-1, keepdim=True)
-    assert torch.equal(idx, ridx)
+    # bf16 logits tie often and tie-breaking is unspecified: compare the picked probabilities, not the indices
+    torch.testing.assert_close(p.gather(1, idx), p.gather(1, ridx), rtol=1e-5, atol=1e-6)
+    assert (idx[:, 0] != idx[:, 1]).all()
     torch.testing.assert_close(w, rw, rtol=1e-3, atol=1e-4)
-    assert torch.equal(cnt.cpu(), torch.bincount(ridx.reshape(-1).cpu(), minlength=8))
+    assert torch.equal(cnt.cpu(), torch.bincount(idx.reshape(-1).cpu(), minlength=8))
 
 
 def test_llama_tiny_trains_on_gpu_with_native_kernels():

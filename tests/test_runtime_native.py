@@ -1,0 +1,61 @@
+"""Native host runtime (libpdb200_runtime.so): TCP store, watchdog, bucket assignment, flag mirror."""
+import ctypes
+import threading
+import time
+
+import pytest
+
+from paddle_b200 import lib
+
+
+def test_runtime_library_builds_and_loads():
+    assert lib.runtime.available(), lib.runtime._err
+
+
+def test_tcp_store_set_get_add_wait():
+    from paddle_b200.distributed.store import TCPStore
+    master = TCPStore("127.0.0.1", 0, is_master=True, world_size=2)
+    client = TCPStore("127.0.0.1", master.port, is_master=False, world_size=2)
+    master.set("k", b"hello")
+    assert client.get("k") == b"hello" and client.check("k") and not client.check("nope")
+    assert client.add("cnt", 2) == 2 and master.add("cnt", 3) == 5
+    got = {}
+
+    def waiter():
+        got["v"] = client.get("late", timeout=10)
+    t = threading.Thread(target=waiter)
+    t.start()
+    time.sleep(0.2)
+    master.set("late", b"x" * 100000)                # larger than the first receive buffer
+    t.join(10)
+    assert got["v"] == b"x" * 100000
+    with pytest.raises(TimeoutError):
+        client.wait("never", timeout=0.2)
+    assert master.delete_key("k") and not master.check("k")
+    client.close()
+    master.close()
+
+
+def test_watchdog_flags_timeouts():
+    rt = lib.runtime.require()
+    assert rt.pdb200_wd_start(0, 100, 50) == 0
+    rt.pdb200_wd_task_begin(7, 1, b"all_reduce", 1024, 1)
+    rt.pdb200_wd_task_begin(7, 2, b"broadcast", 8, 0)
+    rt.pdb200_wd_task_end(7, 1)
+    assert rt.pdb200_wd_inflight() == 1
+    time.sleep(0.4)
+    assert rt.pdb200_wd_timeouts() >= 1
+    buf = ctypes.create_string_buffer(4096)
+    n = rt.pdb200_wd_dump(buf, 4096)
+    text = buf.raw[:n].decode()
+    assert "op=broadcast" in text and "[last-done]" in text and "op=all_reduce" in text
+    rt.pdb200_wd_task_end(7, 2)
+    assert rt.pdb200_wd_stop() == 0
+
+
+def test_flag_mirror():
+    rt = lib.runtime.require()
+    rt.pdb200_flag_set(b"use_fused_comm", b"1")
+    buf = ctypes.create_string_buffer(16)
+    assert rt.pdb200_flag_get(b"use_fused_comm", buf, 16) == 1 and buf.value == b"1"
+    assert rt.pdb200_flag_get(b"missing", buf, 16) == -1
