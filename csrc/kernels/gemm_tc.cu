@@ -46,6 +46,13 @@ int encode_tmap_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t c
     set_error("cuTensorMapEncodeTiled entry point not available");
     return -1;
   }
+  // Driver API calls need a current context on THIS thread; autograd's backward threads only ever used the runtime
+  // API lazily, so bind the primary context once per thread (cuTensorMapEncodeTiled returned INVALID_CONTEXT there).
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    cudaFree(nullptr);
+    ctx_bound = true;
+  }
   cuuint64_t dims[2] = {cols, rows};
   cuuint64_t strides[1] = {row_stride_bytes};
   cuuint32_t box[2] = {box_cols, box_rows};

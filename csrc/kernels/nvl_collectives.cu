@@ -1,0 +1,385 @@
+// Fused collectives over NVLink symmetric memory:
+//   K1  dp_bucket_allreduce : scale + all-reduce of a gradient bucket in ONE kernel (NVLS two-shot: every rank pulls
+//                             its 1/n slice through multimem.ld_reduce - the switch does the sum - scales it and
+//                             multimem.st broadcasts it back).  Replaces concat -> scale_ -> ncclAllReduce -> split
+//                             (paddle/fluid/distributed/collective/reducer.cc:1093-1127).
+//   K2+K3 rs_adamw_ag       : reduce-scatter of the flat gradient buffer + partitioned AdamW on the local shard
+//                             (fp32 master / m / v) + all-gather of the updated bf16 parameters, ONE kernel.
+//                             Replaces ncclReduceScatter + per-parameter adamw launches + ncclAllGather
+//                             (fleet/utils/tensor_fusion_helper.py:559-645, phi/kernels/gpu/adamw_kernel.cu).
+//   K8  ce_combine_symm     : vocab-parallel cross-entropy statistics exchange: every rank reads the 3 floats per
+//                             row of all peers straight from their symmetric scratch (replaces three N x 1
+//                             all-reduces, c_softmax_with_cross_entropy_op.cu:211-314).
+// Cross-GPU ordering uses system-scope flag barriers on a signal pad inside the segment (nvl.cuh).  When the fabric
+// has no multicast support the same kernels fall back to peer loads/stores (P2P two-shot).
+#include "common.cuh"
+#include "nvl.cuh"
+
+namespace pdb {
+namespace nvl {
+
+__global__ void barrier_kernel(Peers P, uint64_t pad_off, uint32_t epoch, unsigned long long spin_limit) {
+  barrier_all(P, pad_off, epoch, spin_limit);
+}
+
+// ---------------------------------------------------------------------------------------------- K1 all-reduce
+template <typename T>
+__global__ void __launch_bounds__(512) allreduce_scale_kernel(Peers P, uint64_t data_off, int64_t nvec, float scale) {
+  // nvec 16-byte vectors in total; rank r owns vectors [r*per, min((r+1)*per, nvec))
+  const int64_t per = (nvec + P.nranks - 1) / P.nranks;
+  const int64_t lo = per * P.rank, hi = (lo + per < nvec) ? lo + per : nvec;
+  constexpr int N = 16 / sizeof(T);
+  for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (int64_t)gridDim.x * blockDim.x) {
+    const uint64_t off = data_off + (uint64_t)i * 16;
+    Vec<T> out;
+    if (P.mc) {
+      if (sizeof(T) == 4) {
+        float v[4];
+        mm_ld_reduce_f32x4(reinterpret_cast<const void*>(P.mc + off), v);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) out.set(j, v[j] * scale);
+      } else {
+        uint32_t r[4];
+        mm_ld_reduce_bf16x8(reinterpret_cast<const void*>(P.mc + off), r);
+        out.raw = make_uint4(r[0], r[1], r[2], r[3]);
+        if (scale != 1.f) {
+#pragma unroll
+          for (int j = 0; j < N; ++j) out.set(j, out.f(j) * scale);
+        }
+      }
+      uint32_t w[4] = {out.raw.x, out.raw.y, out.raw.z, out.raw.w};
+      mm_st_b32x4(reinterpret_cast<void*>(P.mc + off), w);
+    } else {
+      float acc[N];
+#pragma unroll
+      for (int j = 0; j < N; ++j) acc[j] = 0.f;
+      for (int p = 0; p < P.nranks; ++p) {
+        Vec<T> x;
+        x.load(reinterpret_cast<const T*>(P.ptr[p] + off));
+#pragma unroll
+        for (int j = 0; j < N; ++j) acc[j] += x.f(j);
+      }
+#pragma unroll
+      for (int j = 0; j < N; ++j) out.set(j, acc[j] * scale);
+      for (int p = 0; p < P.nranks; ++p) out.store(reinterpret_cast<T*>(P.ptr[p] + off));
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- K2 + K3
+struct AdamArgs {
+  float lr, beta1, beta2, eps, weight_decay;
+  const float* beta_pows;    // device {beta1^t, beta2^t}
+  const float* grad_scale;   // optional device scalar (clip coefficient / inverse loss scale)
+  const float* found_inf;    // optional device flag: skip the whole update when != 0
+};
+
+// Gradients: symmetric flat buffer of G (bf16 or fp32) at grad_off; parameters: symmetric flat bf16 buffer at
+// param_off; this rank's shard is elements [shard_start, shard_start + shard_numel) of both (shard_numel % 8 == 0).
+// master / m / v: local fp32 arrays of shard_numel.
+template <typename G>
+__global__ void __launch_bounds__(256) rs_adamw_ag_kernel(Peers P, uint64_t grad_off, uint64_t param_off,
+                                                         int64_t shard_start, int64_t shard_numel,
+                                                         float* __restrict__ master, float* __restrict__ m,
+                                                         float* __restrict__ v, AdamArgs a,
+                                                         const float* __restrict__ local_grad) {
+  if (a.found_inf && *a.found_inf != 0.f) return;
+  // local_grad != null: the shard's gradient was already reduced (two-pass mode used with global-norm clipping)
+  const float gs = (a.grad_scale ? *a.grad_scale : 1.f) / (local_grad ? 1.f : (float)P.nranks);    // AVG reduce
+  const float bc1 = 1.f - a.beta_pows[0];
+  const float bc2s = sqrtf(1.f - a.beta_pows[1]);
+  const float decay_mul = 1.f - a.lr * a.weight_decay;
+  const float step = a.lr / bc1;
+  const int64_t n8 = shard_numel / 8;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t e = shard_start + i * 8;          // global element index
+    float g[8];
+    if (local_grad) {
+      const float4 x0 = *reinterpret_cast<const float4*>(local_grad + i * 8);
+      const float4 x1 = *reinterpret_cast<const float4*>(local_grad + i * 8 + 4);
+      g[0] = x0.x; g[1] = x0.y; g[2] = x0.z; g[3] = x0.w; g[4] = x1.x; g[5] = x1.y; g[6] = x1.z; g[7] = x1.w;
+    } else if (sizeof(G) == 4) {
+      const uint64_t off = grad_off + (uint64_t)e * 4;
+      if (P.mc) {
+        float t0[4], t1[4];
+        mm_ld_reduce_f32x4(reinterpret_cast<const void*>(P.mc + off), t0);
+        mm_ld_reduce_f32x4(reinterpret_cast<const void*>(P.mc + off + 16), t1);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          g[j] = t0[j];
+          g[4 + j] = t1[j];
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] = 0.f;
+        for (int p = 0; p < P.nranks; ++p) {
+          const float4 x0 = *reinterpret_cast<const float4*>(P.ptr[p] + off);
+          const float4 x1 = *reinterpret_cast<const float4*>(P.ptr[p] + off + 16);
+          g[0] += x0.x; g[1] += x0.y; g[2] += x0.z; g[3] += x0.w;
+          g[4] += x1.x; g[5] += x1.y; g[6] += x1.z; g[7] += x1.w;
+        }
+      }
+    } else {
+      const uint64_t off = grad_off + (uint64_t)e * 2;
+      if (P.mc) {
+        uint32_t r[4];
+        mm_ld_reduce_bf16x8(reinterpret_cast<const void*>(P.mc + off), r);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&r[j]);
+          g[2 * j] = __low2float(h);
+          g[2 * j + 1] = __high2float(h);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] = 0.f;
+        for (int p = 0; p < P.nranks; ++p) {
+          Vec<__nv_bfloat16> x;
+          x.load(reinterpret_cast<const __nv_bfloat16*>(P.ptr[p] + off));
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] += x.f(j);
+        }
+      }
+    }
+    float pw[8], mm_[8], vv[8];
+    {
+      const float4 p0 = *reinterpret_cast<const float4*>(master + i * 8), p1 = *reinterpret_cast<const float4*>(master + i * 8 + 4);
+      const float4 m0 = *reinterpret_cast<const float4*>(m + i * 8), m1 = *reinterpret_cast<const float4*>(m + i * 8 + 4);
+      const float4 v0 = *reinterpret_cast<const float4*>(v + i * 8), v1 = *reinterpret_cast<const float4*>(v + i * 8 + 4);
+      pw[0] = p0.x; pw[1] = p0.y; pw[2] = p0.z; pw[3] = p0.w; pw[4] = p1.x; pw[5] = p1.y; pw[6] = p1.z; pw[7] = p1.w;
+      mm_[0] = m0.x; mm_[1] = m0.y; mm_[2] = m0.z; mm_[3] = m0.w; mm_[4] = m1.x; mm_[5] = m1.y; mm_[6] = m1.z; mm_[7] = m1.w;
+      vv[0] = v0.x; vv[1] = v0.y; vv[2] = v0.z; vv[3] = v0.w; vv[4] = v1.x; vv[5] = v1.y; vv[6] = v1.z; vv[7] = v1.w;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float gj = g[j] * gs;
+      pw[j] *= decay_mul;
+      mm_[j] = a.beta1 * mm_[j] + (1.f - a.beta1) * gj;
+      vv[j] = a.beta2 * vv[j] + (1.f - a.beta2) * gj * gj;
+      pw[j] -= step * (mm_[j] / (sqrtf(vv[j]) / bc2s + a.eps));
+    }
+    *reinterpret_cast<float4*>(master + i * 8) = make_float4(pw[0], pw[1], pw[2], pw[3]);
+    *reinterpret_cast<float4*>(master + i * 8 + 4) = make_float4(pw[4], pw[5], pw[6], pw[7]);
+    *reinterpret_cast<float4*>(m + i * 8) = make_float4(mm_[0], mm_[1], mm_[2], mm_[3]);
+    *reinterpret_cast<float4*>(m + i * 8 + 4) = make_float4(mm_[4], mm_[5], mm_[6], mm_[7]);
+    *reinterpret_cast<float4*>(v + i * 8) = make_float4(vv[0], vv[1], vv[2], vv[3]);
+    *reinterpret_cast<float4*>(v + i * 8 + 4) = make_float4(vv[4], vv[5], vv[6], vv[7]);
+    // all-gather: the updated bf16 parameters go to every rank's copy of the flat parameter buffer
+    Vec<__nv_bfloat16> o;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o.set(j, pw[j]);
+    const uint64_t poff = param_off + (uint64_t)e * 2;
+    if (P.mc) {
+      uint32_t w[4] = {o.raw.x, o.raw.y, o.raw.z, o.raw.w};
+      mm_st_b32x4(reinterpret_cast<void*>(P.mc + poff), w);
+    } else {
+      for (int p = 0; p < P.nranks; ++p) o.store(reinterpret_cast<__nv_bfloat16*>(P.ptr[p] + poff));
+    }
+  }
+}
+
+// Reduce-scatter (AVG) of the flat gradient buffer into a local fp32 shard + per-CTA sum of squares (for the
+// global-norm clip that must see the reduced gradient before the update).
+template <typename G>
+__global__ void __launch_bounds__(256) reduce_scatter_norm_kernel(Peers P, uint64_t grad_off, int64_t shard_start,
+                                                                 int64_t shard_numel, float* __restrict__ out,
+                                                                 float* __restrict__ partial_sq) {
+  __shared__ float red[32];
+  const float inv = 1.f / (float)P.nranks;
+  const int64_t n8 = shard_numel / 8;
+  float acc = 0.f;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t e = shard_start + i * 8;
+    float g[8];
+    if (sizeof(G) == 4) {
+      const uint64_t off = grad_off + (uint64_t)e * 4;
+      if (P.mc) {
+        float t0[4], t1[4];
+        mm_ld_reduce_f32x4(reinterpret_cast<const void*>(P.mc + off), t0);
+        mm_ld_reduce_f32x4(reinterpret_cast<const void*>(P.mc + off + 16), t1);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          g[j] = t0[j];
+          g[4 + j] = t1[j];
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] = 0.f;
+        for (int p = 0; p < P.nranks; ++p) {
+          const float4 x0 = *reinterpret_cast<const float4*>(P.ptr[p] + off);
+          const float4 x1 = *reinterpret_cast<const float4*>(P.ptr[p] + off + 16);
+          g[0] += x0.x; g[1] += x0.y; g[2] += x0.z; g[3] += x0.w;
+          g[4] += x1.x; g[5] += x1.y; g[6] += x1.z; g[7] += x1.w;
+        }
+      }
+    } else {
+      const uint64_t off = grad_off + (uint64_t)e * 2;
+      if (P.mc) {
+        uint32_t r[4];
+        mm_ld_reduce_bf16x8(reinterpret_cast<const void*>(P.mc + off), r);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&r[j]);
+          g[2 * j] = __low2float(h);
+          g[2 * j + 1] = __high2float(h);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] = 0.f;
+        for (int p = 0; p < P.nranks; ++p) {
+          Vec<__nv_bfloat16> x;
+          x.load(reinterpret_cast<const __nv_bfloat16*>(P.ptr[p] + off));
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] += x.f(j);
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      g[j] *= inv;
+      acc += g[j] * g[j];
+    }
+    *reinterpret_cast<float4*>(out + i * 8) = make_float4(g[0], g[1], g[2], g[3]);
+    *reinterpret_cast<float4*>(out + i * 8 + 4) = make_float4(g[4], g[5], g[6], g[7]);
+  }
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0 && partial_sq) partial_sq[blockIdx.x] = acc;
+}
+
+// ---------------------------------------------------------------------------------------------- K8
+constexpr float kLog2e = 1.4426950408889634f;
+__global__ void ce_combine_symm_kernel(Peers P, uint64_t stats_off, const int64_t* __restrict__ labels,
+                                       float* __restrict__ loss, float* __restrict__ lse, int64_t rows,
+                                       int64_t ignore_index) {
+  const int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= rows) return;
+  float mx[kMaxRanks], sm[kMaxRanks], tgt = 0.f, gm = -INFINITY;
+  for (int p = 0; p < P.nranks; ++p) {
+    const float* st = reinterpret_cast<const float*>(P.ptr[p] + stats_off) + row * 3;
+    mx[p] = st[0];
+    sm[p] = st[1];
+    tgt += st[2];
+    gm = fmaxf(gm, mx[p]);
+  }
+  float gs = 0.f;
+  for (int p = 0; p < P.nranks; ++p) gs += sm[p] * exp2f((mx[p] - gm) * kLog2e);
+  const float l = gm + __logf(gs);
+  lse[row] = l;
+  loss[row] = (labels[row] == ignore_index) ? 0.f : l - tgt;
+}
+
+static Peers make_peers(const uint64_t* ptrs, uint64_t mc, int nranks, int rank) {
+  Peers P{};
+  for (int i = 0; i < nranks && i < kMaxRanks; ++i) P.ptr[i] = ptrs[i];
+  P.mc = mc;
+  P.nranks = nranks;
+  P.rank = rank;
+  return P;
+}
+
+}  // namespace nvl
+}  // namespace pdb
+
+using namespace pdb;
+using namespace pdb::nvl;
+
+static const unsigned long long kSpinLimit = 20000000ull;   // ~ tens of seconds of system-scope polling, then trap
+
+// peer_ptrs: host array of nranks device addresses (this process's mappings).  Every entry point brackets its data
+// kernel with signal-pad barriers using epochs `epoch` and `epoch + 1`; callers advance their counter by 2.
+PDB_EXPORT int pdb200_nvl_barrier(const uint64_t* peer_ptrs, int nranks, int rank, int64_t pad_off, int64_t epoch,
+                                  void* stream) {
+  PDB_REQUIRE(nranks >= 1 && nranks <= kMaxRanks, "nvl: nranks %d out of range (1..%d)", nranks, kMaxRanks);
+  Peers P = make_peers(peer_ptrs, 0, nranks, rank);
+  barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+  return check_launch("nvl_barrier");
+}
+
+PDB_EXPORT int pdb200_nvl_allreduce(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t data_off,
+                                    int64_t numel, int dtype, float scale, int64_t pad_off, int64_t epoch, int max_ctas,
+                                    void* stream) {
+  PDB_REQUIRE(nranks >= 1 && nranks <= kMaxRanks, "nvl: nranks %d out of range (1..%d)", nranks, kMaxRanks);
+  const int esz = dtype == PDB_DTYPE_F32 ? 4 : 2;
+  PDB_REQUIRE((numel * esz) % 16 == 0 && data_off % 16 == 0, "nvl_allreduce: buffer must be a multiple of 16 bytes");
+  PDB_REQUIRE(dtype == PDB_DTYPE_F32 || dtype == PDB_DTYPE_BF16, "nvl_allreduce: float32 / bfloat16 only");
+  cudaStream_t st = (cudaStream_t)stream;
+  Peers P = make_peers(peer_ptrs, mc_ptr, nranks, rank);
+  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+  const int64_t nvec = numel * esz / 16;
+  const int64_t per = (nvec + nranks - 1) / nranks;
+  int grid = (int)((per + 511) / 512);
+  const int cap = max_ctas > 0 ? max_ctas : sm_count();     // few CTAs when overlapping with backward compute
+  if (grid > cap) grid = cap;
+  if (grid < 1) grid = 1;
+  if (dtype == PDB_DTYPE_F32)
+    allreduce_scale_kernel<float><<<grid, 512, 0, st>>>(P, (uint64_t)data_off, nvec, scale);
+  else
+    allreduce_scale_kernel<__nv_bfloat16><<<grid, 512, 0, st>>>(P, (uint64_t)data_off, nvec, scale);
+  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
+  return check_launch("nvl_allreduce");
+}
+
+PDB_EXPORT int pdb200_nvl_rs_adamw_ag(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t grad_off,
+                                      int grad_dtype, int64_t param_off, int64_t shard_start, int64_t shard_numel,
+                                      float* master, float* m, float* v, float lr, float beta1, float beta2, float eps,
+                                      float weight_decay, const float* beta_pows, const float* grad_scale,
+                                      const float* found_inf, const float* local_grad, int64_t pad_off, int64_t epoch,
+                                      void* stream) {
+  PDB_REQUIRE(nranks >= 1 && nranks <= kMaxRanks, "nvl: nranks %d out of range (1..%d)", nranks, kMaxRanks);
+  PDB_REQUIRE(shard_numel % 8 == 0 && shard_start % 8 == 0, "rs_adamw_ag: shard must be a multiple of 8 elements");
+  PDB_REQUIRE(grad_dtype == PDB_DTYPE_F32 || grad_dtype == PDB_DTYPE_BF16, "rs_adamw_ag: grads must be fp32 or bf16");
+  PDB_REQUIRE(beta_pows != nullptr, "rs_adamw_ag: beta_pows (device) is required");
+  cudaStream_t st = (cudaStream_t)stream;
+  Peers P = make_peers(peer_ptrs, mc_ptr, nranks, rank);
+  AdamArgs a{lr, beta1, beta2, eps, weight_decay, beta_pows, grad_scale, found_inf};
+  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+  int64_t blocks = (shard_numel / 8 + 255) / 256;
+  const int64_t cap = (int64_t)sm_count() * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  if (grad_dtype == PDB_DTYPE_F32)
+    rs_adamw_ag_kernel<float><<<(int)blocks, 256, 0, st>>>(P, (uint64_t)grad_off, (uint64_t)param_off, shard_start, shard_numel, master, m, v, a, local_grad);
+  else
+    rs_adamw_ag_kernel<__nv_bfloat16><<<(int)blocks, 256, 0, st>>>(P, (uint64_t)grad_off, (uint64_t)param_off, shard_start, shard_numel, master, m, v, a, local_grad);
+  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
+  return check_launch("nvl_rs_adamw_ag");
+}
+
+// Reduce-scatter (AVG) into a local fp32 shard; partial_sq: >= pdb200_nvl_rs_grid(shard_numel) floats of scratch whose
+// sum is the shard's squared L2 norm (fold with pdb200_l2norm / torch.sum).
+PDB_EXPORT int pdb200_nvl_rs_grid(int64_t shard_numel) {
+  int64_t blocks = (shard_numel / 8 + 255) / 256;
+  const int64_t cap = (int64_t)sm_count() * 4;
+  if (blocks > cap) blocks = cap;
+  return (int)(blocks < 1 ? 1 : blocks);
+}
+PDB_EXPORT int pdb200_nvl_reduce_scatter(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t grad_off,
+                                         int grad_dtype, int64_t shard_start, int64_t shard_numel, float* out,
+                                         float* partial_sq, int64_t pad_off, int64_t epoch, void* stream) {
+  PDB_REQUIRE(nranks >= 1 && nranks <= kMaxRanks, "nvl: nranks %d out of range (1..%d)", nranks, kMaxRanks);
+  PDB_REQUIRE(shard_numel % 8 == 0 && shard_start % 8 == 0, "nvl_reduce_scatter: shard must be a multiple of 8 elements");
+  cudaStream_t st = (cudaStream_t)stream;
+  Peers P = make_peers(peer_ptrs, mc_ptr, nranks, rank);
+  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+  const int grid = pdb200_nvl_rs_grid(shard_numel);
+  if (grad_dtype == PDB_DTYPE_F32)
+    reduce_scatter_norm_kernel<float><<<grid, 256, 0, st>>>(P, (uint64_t)grad_off, shard_start, shard_numel, out, partial_sq);
+  else
+    reduce_scatter_norm_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(P, (uint64_t)grad_off, shard_start, shard_numel, out, partial_sq);
+  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
+  return check_launch("nvl_reduce_scatter");
+}
+
+PDB_EXPORT int pdb200_nvl_ce_combine(const uint64_t* peer_ptrs, int nranks, int rank, int64_t stats_off,
+                                     const int64_t* labels, float* loss, float* lse, int64_t rows, int64_t ignore_index,
+                                     int64_t pad_off, int64_t epoch, void* stream) {
+  PDB_REQUIRE(nranks >= 1 && nranks <= kMaxRanks, "nvl: nranks %d out of range (1..%d)", nranks, kMaxRanks);
+  cudaStream_t st = (cudaStream_t)stream;
+  Peers P = make_peers(peer_ptrs, 0, nranks, rank);
+  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+  if (rows > 0)
+    ce_combine_symm_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, st>>>(P, (uint64_t)stats_off, labels, loss, lse, rows, ignore_index);
+  // peers may overwrite their stats only after everyone has read them
+  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
+  return check_launch("nvl_ce_combine");
+}

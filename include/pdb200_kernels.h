@@ -71,6 +71,19 @@ PDB_API int pdb200_topk_softmax(const void* logits, int64_t tokens, int E, int k
  * [N,K] when trans_b.  out_dtype 0 = fp32 (beta = 1 accumulates into C), 1 = bf16.  act: 0 none, 1 gelu, 2 relu. */
 PDB_API int pdb200_gemm_bf16(const void* a, const void* b, void* c, const void* bias, int64_t M, int64_t N, int64_t K, int trans_a, int trans_b, int out_dtype, float beta, int act, void* stream);
 
+/* Fused collectives over NVLink symmetric memory (K1, K2+K3, K8; csrc/kernels/nvl_collectives.cu).  peer_ptrs: host
+ * array of nranks device addresses = every rank's segment as mapped in this process (pdb200_symm_peer_ptr), mc_ptr:
+ * NVLS multicast mapping or 0 (P2P fallback).  *_off: byte offsets inside the segment, identical on all ranks.
+ * pad_off: 32-byte signal pad used by the in-stream barriers; each call consumes epochs `epoch` and `epoch + 1`.
+ * Reference counterparts: reducer.cc:1093-1127 (K1), tensor_fusion_helper.py:559-645 + adamw_kernel.cu (K2+K3),
+ * c_softmax_with_cross_entropy_op.cu:211-314 (K8). */
+PDB_API int pdb200_nvl_barrier(const uint64_t* peer_ptrs, int nranks, int rank, int64_t pad_off, int64_t epoch, void* stream);
+PDB_API int pdb200_nvl_allreduce(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t data_off, int64_t numel, int dtype, float scale, int64_t pad_off, int64_t epoch, int max_ctas, void* stream);
+PDB_API int pdb200_nvl_rs_adamw_ag(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t grad_off, int grad_dtype, int64_t param_off, int64_t shard_start, int64_t shard_numel, float* master, float* m, float* v, float lr, float beta1, float beta2, float eps, float weight_decay, const float* beta_pows, const float* grad_scale, const float* found_inf, const float* local_grad, int64_t pad_off, int64_t epoch, void* stream);
+PDB_API int pdb200_nvl_rs_grid(int64_t shard_numel);
+PDB_API int pdb200_nvl_reduce_scatter(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t grad_off, int grad_dtype, int64_t shard_start, int64_t shard_numel, float* out, float* partial_sq, int64_t pad_off, int64_t epoch, void* stream);
+PDB_API int pdb200_nvl_ce_combine(const uint64_t* peer_ptrs, int nranks, int rank, int64_t stats_off, const int64_t* labels, float* loss, float* lse, int64_t rows, int64_t ignore_index, int64_t pad_off, int64_t epoch, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -146,10 +146,12 @@ class _ParallelCE(torch.autograd.Function):
         stats = ops.ce_local_stats(logits, lab, vocab_start, ignore_index)      # [rows, 3] fp32
         if n > 1:
             from paddle_b200.parallel import symm
-            all_stats = symm.all_gather_small(stats, group)                        # [n, rows, 3]
+            if stats.is_cuda and symm.available(group):
+                loss, lse = symm.ce_exchange_combine(stats, lab, group, ignore_index)      # in-kernel NVLink exchange
+            else:
+                loss, lse = ops.ce_combine(symm.all_gather_small(stats, group), lab, ignore_index)
         else:
-            all_stats = stats.unsqueeze(0)
-        loss, lse = ops.ce_combine(all_stats, lab, ignore_index)
+            loss, lse = ops.ce_combine(stats.unsqueeze(0), lab, ignore_index)
         ctx.save_for_backward(logits, lab, lse)
         ctx.cfg = (vocab_start, ignore_index)
         return loss.reshape(label.shape).to(torch.float32 if logits.dtype != torch.float64 else logits.dtype)

@@ -173,12 +173,14 @@ class DygraphShardingOptimizerV2:
         self._slice_params = []
         self._slice_of = {}
         idx = 0
+        allocator = self._symm_allocator(by_dtype)
         for (_, is_dist), ps in by_dtype.items():
             groups = tfh.assign_group_by_size(ps, self._buffer_bytes)
             for _, gps in groups.items():
                 buf = tfh.FusedCommBuffer(idx, gps, self._group, self._acc_steps, tfh.HOOK_ACTION.REDUCE_SCATTER,
                                           use_main_grad=self._use_main_grad, fuse_param=True,
-                                          use_reduce_avg=self._use_reduce_avg, scale_after_comm=True)
+                                          use_reduce_avg=self._use_reduce_avg, scale_after_comm=True,
+                                          allocator=allocator)
                 idx += 1
                 self._comm_buffers.append(buf)
                 # the local contiguous shard of the parameter buffer becomes ONE optimizer parameter
@@ -199,6 +201,44 @@ class DygraphShardingOptimizerV2:
                 opt._param_groups = [base]
             opt = getattr(opt, "_inner_opt", None)
 
+    def _symm_allocator(self, by_dtype):
+        """Flat parameter/gradient buffers in NVLink symmetric memory so that K2+K3 (reduce-scatter + AdamW +
+        all-gather in one kernel) can run on them; None -> ordinary allocations and the NCCL composition."""
+        self._arena = None
+        from paddle_b200.parallel import symm
+        some = next((p for ps in by_dtype.values() for p in ps), None)
+        if some is None or not some.is_cuda or not symm.available(self._group):
+            return None
+        need = 0
+        for ps in by_dtype.values():
+            elems = sum((p.numel() + 127) // 128 * 128 for p in ps) + 4096 * self._sharding_world_size * 4
+            need += elems * ps[0].element_size() + elems * (4 if self._use_main_grad else ps[0].element_size())
+        try:
+            self._arena = symm.get_arena(self._group, need + (16 << 20), key=f"shardv2_{id(self)}")
+        except Exception:  # noqa: BLE001
+            self._arena = None
+            return None
+        arena = self._arena
+
+        def alloc(numel, dtype, device):
+            t = arena.empty((numel,), dtype)
+            t.zero_()
+            return t
+        return alloc
+
+    def _fused_ready(self):
+        """Fused K2+K3 preconditions: symmetric bf16 buffers, native multi-precision AdamW with uniform decay."""
+        if self._arena is None:
+            return False
+        base = self._inner_opt
+        while hasattr(base, "_inner_opt"):
+            base = base._inner_opt
+        ok = (getattr(base, "_decoupled", False) and base._multi_precision and
+              getattr(base, "_apply_decay_param_fun", None) is None and getattr(base, "_lr_ratio_fn", None) is None and
+              all(b.param_storage.dtype == torch.bfloat16 and b._shard_numel % 8 == 0 for b in self._comm_buffers))
+        self._base_opt = base
+        return ok
+
     def _segments(self, buf):
         """[(param, start_in_shard, start_in_param, length)] overlap of each parameter with this rank's shard."""
         S = buf._shard_numel
@@ -215,6 +255,7 @@ class DygraphShardingOptimizerV2:
 
     @torch.no_grad()
     def reduce_gradients(self, parameter_list, hcg):
+        self._fused_pending = False
         for buf in self._comm_buffers:
             for p in buf._params:
                 g = _grad_of(p)
@@ -227,6 +268,11 @@ class DygraphShardingOptimizerV2:
                         p.main_grad = view
                     else:
                         p.grad = view
+        if self._fused_ready():
+            self._fused_pending = True       # the reduction happens inside the fused update kernel(s) in step()
+            self._hcg_for_step = hcg
+            return
+        for buf in self._comm_buffers:
             buf._params_checked_in = len(buf._params)
             buf._params_step_dict = {}
             buf._comm_grads()
@@ -254,8 +300,70 @@ class DygraphShardingOptimizerV2:
 
     @torch.no_grad()
     def step(self):
+        if getattr(self, "_fused_pending", False):
+            self._fused_step()
+            self._fused_pending = False
+            return
         self._inner_opt.step()
         self._sharding_sync_parameters()
+
+    @torch.no_grad()
+    def _fused_step(self):
+        """K2+K3 over NVLink: no clip -> ONE kernel per buffer (reduce-scatter + AdamW + all-gather); with a
+        global-norm clip (or a dp axis) -> reduce-scatter+norm kernel, scalar exchange, AdamW+all-gather kernel."""
+        from paddle_b200.parallel import symm
+        opt = self._base_opt
+        hcg = self._hcg_for_step
+        opt._create_accumulators(self._slice_params)
+        lr = opt.get_lr()
+        grp = opt._param_groups[0]
+        glr = lr * grp.get("learning_rate", 1.0)
+        coeff = opt._coeff(grp)
+        pows = opt._pows(self._slice_params[0])
+        clip = opt._grad_clip
+        dp = hcg.get_data_parallel_group() if hcg.get_data_parallel_world_size() > 1 else None
+        two_pass = clip is not None or dp is not None
+        S_rank = self._sharding_rank
+        local = {}
+        if two_pass:
+            dev = self._slice_params[0].device
+            dist_sq = torch.zeros(1, device=dev)
+            not_dist_sq = torch.zeros(1, device=dev)
+            for buf in self._comm_buffers:
+                S = buf._shard_numel
+                g32 = torch.empty(S, dtype=torch.float32, device=dev)
+                sq = symm.reduce_scatter_norm(buf.grad_storage, S_rank * S, S, g32)
+                if dp is not None:
+                    comm.all_reduce(g32, ReduceOp.AVG, dp)
+                    sq = (g32 * g32).sum().reshape(1)
+                local[buf._id] = g32
+                if self._slice_of[buf._id].is_distributed:
+                    dist_sq += sq
+                else:
+                    not_dist_sq += sq
+            coef = None
+            if clip is not None:
+                if hasattr(clip, "_global_norm"):
+                    clip._global_norm(dist_sq, not_dist_sq)
+                else:
+                    comm.all_reduce(not_dist_sq, group=self._group)
+                    comm.all_reduce(dist_sq, group=self._group)
+                gnorm = torch.sqrt(dist_sq + not_dist_sq)
+                mx = torch.full_like(gnorm, float(clip.clip_norm))
+                coef = mx / (torch.maximum(gnorm, mx) + 1.0e-6)
+        else:
+            coef = None
+        scale = coef if opt._grad_scale_dev is None else (opt._grad_scale_dev if coef is None else coef * opt._grad_scale_dev)
+        for buf in self._comm_buffers:
+            sp = self._slice_of[buf._id]
+            S = buf._shard_numel
+            symm.rs_adamw_ag(buf.grad_storage, buf.param_storage, S_rank * S, S, opt._master_weights[sp.name],
+                             opt._get_accumulator("moment1", sp), opt._get_accumulator("moment2", sp), glr, opt._beta1,
+                             opt._beta2, opt._epsilon, coeff, pows, grad_scale=scale, found_inf=opt._found_inf,
+                             local_grad=local.get(buf._id))
+        for _, pw in opt._beta_pows.items():
+            opt._advance_pows(pw)
+        opt._step_count += 1
 
     def minimize(self, loss, startup_program=None, parameters=None, no_grad_set=None):
         self.step()

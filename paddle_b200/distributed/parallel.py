@@ -212,8 +212,50 @@ class DataParallel(torch.nn.Module):
             raise ValueError("This model does not have any parameters to train, and does not need to use DataParallel")
         is_sparse = [False] * len(params)
         group_indices = assign_group_by_size(params, is_sparse, [self.last_comm_buffer_size, self.comm_buffer_size])
+        allocator, fused = self._fused_comm_hooks(params)
         self._reducer = EagerReducer(params, list(reversed(group_indices)), is_sparse, self.group,
-                                     [self.last_comm_buffer_size, self.comm_buffer_size], self.find_unused_parameters)
+                                     [self.last_comm_buffer_size, self.comm_buffer_size], self.find_unused_parameters,
+                                     bucket_allocator=allocator, fused_allreduce=fused)
+
+    def _fused_comm_hooks(self, params):
+        """K1: buckets live in NVLink symmetric memory and are reduced by ONE kernel (scale + NVLS all-reduce) on a
+        side stream with a handful of CTAs, so the reduction overlaps the rest of backward.  Falls back to NCCL when
+        the fused path is unavailable (CPU/gloo, multi-node, FLAGS_use_fused_comm=0)."""
+        from ..parallel import symm
+        if not (params and params[0].is_cuda and symm.available(self.group)):
+            return None, None
+        total = sum((p.numel() + 127) // 128 * 128 * p.element_size() for p in params)
+        try:
+            arena = symm.get_arena(self.group, total + (8 << 20), key=f"dp{id(self)}")
+        except Exception:  # noqa: BLE001 - e.g. driver without VMM export; NCCL path still works
+            return None, None
+        side = torch.cuda.Stream()
+
+        def allocator(numel, dtype, device):
+            t = arena.empty((numel,), dtype)
+            t.zero_()
+            return t
+
+        class _EvTask:
+            def __init__(self, ev):
+                self.ev = ev
+
+            def wait(self):
+                torch.cuda.current_stream().wait_event(self.ev)
+
+            def is_completed(self):
+                return self.ev.query()
+
+        def fused(buf, nranks):
+            ready = torch.cuda.Event()
+            ready.record()
+            with torch.cuda.stream(side):
+                side.wait_event(ready)
+                symm.allreduce_(buf, scale=1.0 / nranks, max_ctas=16)
+                done = torch.cuda.Event()
+                done.record(side)
+            return _EvTask(done)
+        return allocator, fused
 
     def forward(self, *inputs, **kwargs):
         outputs = self._layers(*inputs, **kwargs)

@@ -1,23 +1,226 @@
 """Symmetric-memory communication layer.
 
-Baseline implementations (NCCL through ``paddle.distributed``) live here behind the same call signatures the fused
-NVLink kernels use, so every caller is written once and ``FLAGS_use_fused_comm`` switches the transport.
+``SymmArena`` wraps the native arena (csrc/runtime/symm.cc: cuMemCreate + POSIX-FD exchange + peer mappings + NVLS
+multicast) for one process group: a bump allocator hands out byte offsets that are identical on every rank, torch
+tensors view the local mapping, and the fused kernels (csrc/kernels/nvl_*.cu) receive the array of peer base
+pointers plus the multicast pointer.  The first 4 KB of every arena is the signal pad used by the in-stream
+cross-GPU barriers; epochs grow monotonically so the pad is never reset.
+
+Every fused path has its NCCL composition behind the same call signature; ``FLAGS_use_fused_comm`` (and
+availability: GPUs of one node, native libraries built, driver support) picks the transport.
 """
 from __future__ import annotations
 
+import ctypes
+import os
+import tempfile
+
 import torch
 
+from paddle_b200 import lib
+from paddle_b200.distributed import collective as C
 from paddle_b200.distributed import communication as comm
 from paddle_b200.framework.flags import flag
+from paddle_b200.ops._util import dtype_code, stream_ptr
+
+PAD_BYTES = 4096
+_arenas = {}
+_counter = [0]
+_disabled_reason = [None]
 
 
+class _Blob:
+    """Expose raw device memory to torch through __cuda_array_interface__ (zero-copy view)."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3}
+
+
+class SymmArena:
+    def __init__(self, group, nbytes, want_multicast=True):
+        rt = lib.runtime.require()
+        self.group = group
+        self.nranks, self.rank = group.nranks, group.rank
+        dev = torch.cuda.current_device()
+        _counter[0] += 1
+        # rank 0 of the group picks a fresh rendezvous directory; everyone learns it through the group
+        box = [tempfile.mkdtemp(prefix="pdb200_symm_") if self.rank == 0 else None]
+        comm.broadcast_object_list(box, src=group.ranks[0], group=group)
+        self._dir = box[0]
+        tag = f"g{group.id}_{_counter[0]}"
+        self._h = rt.pdb200_symm_create(self.rank, self.nranks, dev, int(nbytes) + PAD_BYTES, self._dir.encode(), tag.encode(),
+                                        int(want_multicast), 60000)
+        if not self._h:
+            raise RuntimeError(f"symmetric arena: {rt.pdb200_rt_last_error().decode()}")
+        self._rt = rt
+        self.nbytes = rt.pdb200_symm_bytes(self._h)
+        self.peer_ptrs = (ctypes.c_uint64 * self.nranks)(*[rt.pdb200_symm_peer_ptr(self._h, p) for p in range(self.nranks)])
+        self.mc_ptr = rt.pdb200_symm_multicast_ptr(self._h)
+        self.local_ptr = self.peer_ptrs[self.rank]
+        self._bytes = torch.as_tensor(_Blob(self.local_ptr, self.nbytes), device=f"cuda:{dev}")
+        self._bytes[:PAD_BYTES].zero_()
+        torch.cuda.synchronize()
+        C.barrier(group)                       # pads are zero everywhere before the first in-stream barrier
+        self._top = PAD_BYTES
+        self._epoch = 1
+
+    @property
+    def peers_arg(self):
+        return ctypes.cast(self.peer_ptrs, ctypes.c_void_p)
+
+    def next_epoch(self):
+        e = self._epoch
+        self._epoch += 2
+        return e
+
+    def alloc(self, nbytes, align=256):
+        off = (self._top + align - 1) // align * align
+        if off + nbytes > self.nbytes:
+            raise MemoryError(f"symmetric arena exhausted: need {nbytes} B at {off}, capacity {self.nbytes}")
+        self._top = off + int(nbytes)
+        return off
+
+    def free_bytes(self):
+        return self.nbytes - self._top
+
+    def tensor(self, offset, shape, dtype):
+        n = 1
+        for s in shape:
+            n *= int(s)
+        nb = n * torch.empty(0, dtype=dtype).element_size()
+        return self._bytes[offset:offset + nb].view(dtype).view(*shape)
+
+    def empty(self, shape, dtype):
+        n = 1
+        for s in shape:
+            n *= int(s)
+        off = self.alloc(n * torch.empty(0, dtype=dtype).element_size())
+        t = self.tensor(off, shape, dtype)
+        t._symm = (self, off)
+        return t
+
+    def close(self):
+        if getattr(self, "_h", None):
+            torch.cuda.synchronize()
+            self._rt.pdb200_symm_destroy(self._h)
+            self._h = None
+
+
+def available(group=None) -> bool:
+    """Fused NVLink paths are usable: flag on, GPUs, NCCL backend, one node, native libs, driver VMM support."""
+    if _disabled_reason[0] is not None or not flag("use_fused_comm"):
+        return False
+    if not torch.cuda.is_available() or C._state.backend != "nccl":
+        return False
+    if group is not None and (group.nranks < 2 or group.nranks > 8 or group.rank < 0):
+        return False
+    if int(os.environ.get("PADDLE_NNODES", "1")) > 1:
+        return False
+    if not (lib.runtime.available() and lib.have_kernels()):
+        return False
+    if not hasattr(lib.kernels.require(), "pdb200_nvl_allreduce"):
+        return False
+    return lib.runtime.pdb200_symm_supported(torch.cuda.current_device()) >= 1
+
+
+def get_arena(group, min_bytes=64 << 20, key="default"):
+    k = (group.id, key)
+    a = _arenas.get(k)
+    if a is None or a.free_bytes() < 0:
+        try:
+            a = SymmArena(group, min_bytes)
+        except Exception as e:  # noqa: BLE001
+            _disabled_reason[0] = str(e)
+            raise
+        _arenas[k] = a
+    return a
+
+
+def release_all():
+    for a in _arenas.values():
+        a.close()
+    _arenas.clear()
+
+
+# --------------------------------------------------------------------------------------------- fused collectives
+def allreduce_(t, scale=1.0, max_ctas=0):
+    """In-place scaled all-reduce of a tensor that lives in a symmetric arena (K1)."""
+    arena, off = t._symm
+    from paddle_b200.lib import check
+    check(lib.kernels.pdb200_nvl_allreduce(arena.peers_arg, arena.mc_ptr, arena.nranks, arena.rank, off, t.numel(),
+                                           dtype_code(t), float(scale), 0, arena.next_epoch(), int(max_ctas),
+                                           stream_ptr(t.device)), "nvl_allreduce")
+    return t
+
+
+def barrier(arena):
+    from paddle_b200.lib import check
+    check(lib.kernels.pdb200_nvl_barrier(arena.peers_arg, arena.nranks, arena.rank, 0, arena.next_epoch(),
+                                         stream_ptr(torch.device("cuda", torch.cuda.current_device()))), "nvl_barrier")
+
+
+def rs_adamw_ag(grad_buf, param_buf, shard_start, shard_numel, master, m, v, lr, beta1, beta2, eps, weight_decay,
+                beta_pows, grad_scale=None, found_inf=None, local_grad=None):
+    """K2+K3: reduce-scatter(AVG) of ``grad_buf`` + AdamW on this rank's shard + all-gather into ``param_buf``.
+    ``local_grad`` (fp32, shard-sized): the gradient was already reduced by ``reduce_scatter_norm`` (two-pass mode
+    needed when a global-norm clip must see the reduced gradient first); the kernel then only updates + gathers."""
+    arena, goff = grad_buf._symm
+    arena2, poff = param_buf._symm
+    assert arena is arena2, "gradient and parameter buffers must live in the same arena"
+    from paddle_b200.lib import check
+    from paddle_b200.ops._util import ptr
+    check(lib.kernels.pdb200_nvl_rs_adamw_ag(arena.peers_arg, arena.mc_ptr, arena.nranks, arena.rank, goff,
+                                             dtype_code(grad_buf), poff, int(shard_start), int(shard_numel), ptr(master),
+                                             ptr(m), ptr(v), float(lr), float(beta1), float(beta2), float(eps),
+                                             float(weight_decay), ptr(beta_pows), ptr(grad_scale), ptr(found_inf),
+                                             ptr(local_grad), 0, arena.next_epoch(), stream_ptr(grad_buf.device)),
+          "nvl_rs_adamw_ag")
+
+
+def reduce_scatter_norm(grad_buf, shard_start, shard_numel, out):
+    """Pass 1 of the clipped update: AVG reduce-scatter into ``out`` (fp32 shard); returns the shard's squared norm
+    as a device scalar."""
+    arena, goff = grad_buf._symm
+    from paddle_b200.lib import check
+    from paddle_b200.ops._util import ptr
+    grid = lib.kernels.pdb200_nvl_rs_grid(int(shard_numel))
+    partial = torch.empty(grid, dtype=torch.float32, device=grad_buf.device)
+    check(lib.kernels.pdb200_nvl_reduce_scatter(arena.peers_arg, arena.mc_ptr, arena.nranks, arena.rank, goff,
+                                                dtype_code(grad_buf), int(shard_start), int(shard_numel), ptr(out),
+                                                ptr(partial), 0, arena.next_epoch(), stream_ptr(grad_buf.device)),
+          "nvl_reduce_scatter")
+    return partial.sum().reshape(1)
+
+
+_ce_scratch = {}
+
+
+def ce_exchange_combine(stats, labels, group, ignore_index):
+    """K8: publish this rank's [rows, 3] statistics in symmetric scratch, read every peer's copy in-kernel."""
+    from paddle_b200.lib import check
+    from paddle_b200.ops._util import ptr
+    arena = get_arena(group)
+    rows = stats.shape[0]
+    key = (group.id, rows)
+    buf = _ce_scratch.get(key)
+    if buf is None:
+        buf = arena.empty((rows, 3), torch.float32)
+        _ce_scratch[key] = buf
+    buf.copy_(stats)
+    lab = labels.reshape(-1).long().contiguous()
+    loss = torch.empty(rows, dtype=torch.float32, device=stats.device)
+    lse = torch.empty(rows, dtype=torch.float32, device=stats.device)
+    check(lib.kernels.pdb200_nvl_ce_combine(arena.peers_arg, arena.nranks, arena.rank, buf._symm[1], ptr(lab), ptr(loss),
+                                            ptr(lse), rows, int(ignore_index), 0, arena.next_epoch(),
+                                            stream_ptr(stats.device)), "nvl_ce_combine")
+    return loss, lse
+
+
+# --------------------------------------------------------------------------------------------- NCCL-shaped helpers
 def all_gather_small(t, group):
-    """[...]-> [nranks, ...] for small payloads (vocab-parallel CE statistics)."""
+    """[...]-> [nranks, ...] for small payloads (NCCL baseline of the CE statistics exchange)."""
     n = group.nranks
     out = torch.empty((n,) + tuple(t.shape), dtype=t.dtype, device=t.device)
-    from . import symm_fused
-    if flag("use_fused_comm") and symm_fused.available(group, t):
-        return symm_fused.all_gather_small(t, group, out)
     comm.all_gather(out, t.contiguous(), group)
     return out
 

@@ -1,0 +1,85 @@
+"""Worker (>= 2 GPUs, NCCL): fused NVLink kernels against their NCCL compositions.
+K1 scaled all-reduce, K2+K3 reduce-scatter + AdamW + all-gather, K8 vocab-parallel CE exchange, native arena."""
+import os
+
+import torch
+
+import paddle_b200 as paddle
+import paddle_b200.distributed as dist
+from paddle_b200.parallel import symm
+
+dist.init_parallel_env()
+r, n = dist.get_rank(), dist.get_world_size()
+dev = torch.device("cuda", torch.cuda.current_device())
+g = dist.collective._get_default_group()
+assert symm.available(g), "fused NVLink path unavailable"
+arena = symm.get_arena(g, 256 << 20, key="test")
+print(f"rank {r}: arena {arena.nbytes >> 20} MiB, multicast={'yes' if arena.mc_ptr else 'no'}", flush=True)
+
+# ---- peer mapping sanity: write my rank into my segment, read peers' through their mappings
+mine = arena.empty((1024,), torch.float32)
+mine.fill_(float(r + 1))
+symm.barrier(arena)
+torch.cuda.synchronize()
+
+# ---- K1: scaled all-reduce, fp32 and bf16, odd sizes (multiple of 16 B)
+for dtype, numel in ((torch.float32, 1 << 20), (torch.bfloat16, (1 << 21) + 8), (torch.float32, 4)):
+    torch.manual_seed(100 + r)
+    t = arena.empty((numel,), dtype)
+    src = torch.randn(numel, device=dev).to(dtype)
+    t.copy_(src)
+    ref = src.clone().float()
+    dist.all_reduce(ref)
+    ref = ref / n
+    symm.allreduce_(t, scale=1.0 / n)
+    torch.cuda.synchronize()
+    tol = dict(rtol=1e-5, atol=1e-5) if dtype == torch.float32 else dict(rtol=2e-2, atol=2e-2)
+    torch.testing.assert_close(t.float(), ref, **tol)
+
+# ---- K2 + K3: flat buffers, shard per rank
+torch.manual_seed(7)
+total = 8 * 4096 * n
+pbuf = arena.empty((total,), torch.bfloat16)
+gbuf = arena.empty((total,), torch.bfloat16)
+master_full = torch.randn(total, device=dev)
+dist.broadcast(master_full, 0)
+pbuf.copy_(master_full.bfloat16())
+S = total // n
+master = master_full[r * S:(r + 1) * S].clone()
+m = torch.zeros(S, device=dev)
+v = torch.zeros(S, device=dev)
+ref_p = master_full.clone().requires_grad_(True)
+ref_opt = torch.optim.AdamW([ref_p], lr=1e-2, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
+pows = torch.tensor([0.9, 0.95], device=dev)
+for step in range(3):
+    torch.manual_seed(1000 * step + r)
+    grad = torch.randn(total, device=dev).bfloat16()
+    gbuf.copy_(grad)
+    gsum = grad.float().clone()
+    dist.all_reduce(gsum)
+    # the switch reduces bf16 inputs with fp32 accumulation and rounds once
+    ref_p.grad = (gsum / n)
+    symm.rs_adamw_ag(gbuf, pbuf, r * S, S, master, m, v, 1e-2, 0.9, 0.95, 1e-8, 0.1, pows)
+    pows.mul_(torch.tensor([0.9, 0.95], device=dev))
+    ref_opt.step()
+    torch.cuda.synchronize()
+torch.testing.assert_close(master, ref_p.detach()[r * S:(r + 1) * S], rtol=2e-2, atol=2e-3)
+torch.testing.assert_close(pbuf.float(), ref_p.detach().bfloat16().float(), rtol=2e-2, atol=2e-2)
+
+# ---- K8 through ParallelCrossEntropy (mp group = world)
+from paddle_b200.distributed.fleet.layers.mpu import mp_ops
+torch.manual_seed(3)
+V, N = 1024 * n, 300
+full = torch.randn(N, V, device=dev)
+dist.broadcast(full, 0)
+labels = torch.randint(0, V, (N, 1), device=dev)
+labels[5] = -100
+dist.broadcast(labels, 0)
+shard = full[:, r * (V // n):(r + 1) * (V // n)].bfloat16().contiguous().requires_grad_(True)
+loss = mp_ops._c_softmax_with_cross_entropy(shard, labels, group=g, ignore_index=-100)
+loss.sum().backward()
+ref = torch.nn.functional.cross_entropy(full.bfloat16().float(), labels.squeeze(-1), ignore_index=-100, reduction="none")
+torch.testing.assert_close(loss.squeeze(-1), ref, rtol=1e-3, atol=2e-3)
+print("nvl_fused ok", r, flush=True)
+symm.release_all()
+dist.destroy_process_group()
