@@ -105,6 +105,7 @@ class HybridParallelOptimizer:
     def __init__(self, optimizer, hcg, strategy):
         from .dygraph_sharding_optimizer import DygraphShardingOptimizer, DygraphShardingOptimizerV2
         from paddle_b200.distributed.fleet.utils.mix_precision_utils import MixPrecisionOptimizer
+        self._all_params = list(_flat_params(optimizer))     # before sharding narrows the inner parameter list
         if hcg.get_sharding_parallel_world_size() > 1:
             split_param = strategy.hybrid_configs["sharding_configs"]["split_param"]
             cls = DygraphShardingOptimizerV2 if split_param else DygraphShardingOptimizer
@@ -161,7 +162,7 @@ class HybridParallelOptimizer:
 
     @torch.no_grad()
     def step(self):
-        parameter_list = list(_flat_params(self._base_opt))
+        parameter_list = self._all_params
         self._hybrid_sync_grad(parameter_list)
         mp = self._hcg.get_model_parallel_world_size() > 1
         if mp and self._mp_sync["grad"]:

@@ -150,29 +150,28 @@ class P2pHelper:
             return x if isinstance(x, tuple) else (x,)
 
         with torch.no_grad():
+            # Order matters when prev and next are the SAME peer (pp == 2 with virtual stages): messages between one
+            # pair match in issue order, and the peer's "send to prev" is this rank's "recv from next".  Issuing
+            # [send_prev, recv_next, send_next, recv_prev] on every rank makes the pairs line up for any pp.
             if tensor_send_prev is not None:
                 for t in each(tensor_send_prev):
                     ops.append(comm.P2POp(comm.isend, t.contiguous(), prev_rank, group))
-            if tensor_recv_prev is not None:
-                for t in each(tensor_recv_prev):
-                    ops.append(comm.P2POp(comm.irecv, t, prev_rank, group))
-            if tensor_send_next is not None:
-                for t in each(tensor_send_next):
-                    ops.append(comm.P2POp(comm.isend, t.detach().contiguous(), next_rank, group))
             if tensor_recv_next is not None:
                 for t in each(tensor_recv_next):
                     ops.append(comm.P2POp(comm.irecv, t, next_rank, group))
+            if tensor_send_next is not None:
+                for t in each(tensor_send_next):
+                    ops.append(comm.P2POp(comm.isend, t.detach().contiguous(), next_rank, group))
+            if tensor_recv_prev is not None:
+                for t in each(tensor_recv_prev):
+                    ops.append(comm.P2POp(comm.irecv, t, prev_rank, group))
             tasks = []
             if ops:
                 if _use_batch_p2p and C._state.backend == "nccl":
                     tasks = comm.batch_isend_irecv(ops)
                 else:
-                    # deterministic ordering by stage parity avoids send/send deadlocks on blocking transports
-                    even = _hcg.get_stage_id() % 2 == 0
-                    sends = [o for o in ops if o.op is comm.isend]
-                    recvs = [o for o in ops if o.op is comm.irecv]
-                    order = sends + recvs if even else recvs + sends
-                    tasks = [o.op(o.tensor, o.peer, o.group) for o in order]
+                    # isend/irecv are non-blocking on gloo and NCCL: issue in list order, wait afterwards
+                    tasks = [o.op(o.tensor, o.peer, o.group) for o in ops]
             if sync_recv:
                 for t in tasks:
                     t.wait()

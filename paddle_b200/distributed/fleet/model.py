@@ -7,8 +7,7 @@ from .base.topology import ParallelMode
 
 
 def distributed_model(model):
-    from . import fleet as _f
-    fleet_env = _f.fleet
+    from .fleet import fleet as fleet_env
     hcg = fleet_env._hcg
     strategy = fleet_env._user_defined_strategy
     if hcg is None:

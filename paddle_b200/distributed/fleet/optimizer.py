@@ -3,8 +3,7 @@ from __future__ import annotations
 
 
 def distributed_optimizer(optimizer, strategy=None):
-    from . import fleet as _f
-    fleet_env = _f.fleet
+    from .fleet import fleet as fleet_env
     hcg = fleet_env._hcg
     st = strategy or fleet_env._user_defined_strategy
     if hcg is None:

@@ -9,8 +9,8 @@ from paddle_b200.distributed.collective import ReduceOp
 
 
 def distributed_scaler(scaler):
-    from . import fleet as _f
-    hcg = _f.fleet._hcg
+    from .fleet import fleet as fleet_env
+    hcg = fleet_env._hcg
 
     def _sync_found_inf(self, optimizer):
         if hcg is None or hcg.nranks == 1:

@@ -17,3 +17,21 @@ def test_data_parallel_reducer_parity():
 
 def test_tp_layers_shard_vs_whole():
     run_dist("tp_layers.py", 2)
+
+
+@pytest.mark.parametrize("mode", ["v1", "v2", "stage2", "stage3"])
+def test_sharding_matches_data_parallel(mode):
+    run_dist("sharding.py", 2, args=(mode,))
+
+
+@pytest.mark.parametrize("mode", ["1f1b", "vpp"])
+def test_pipeline_matches_single_process(mode):
+    run_dist("pipeline.py", 2, args=(mode,))
+
+
+def test_moe_expert_parallel_matches_dense():
+    run_dist("moe.py", 2)
+
+
+def test_dist_checkpoint_reshard(tmp_path):
+    run_dist("dist_ckpt.py", 2, args=(str(tmp_path),))
