@@ -84,6 +84,14 @@ PDB_API int pdb200_nvl_rs_grid(int64_t shard_numel);
 PDB_API int pdb200_nvl_reduce_scatter(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t grad_off, int grad_dtype, int64_t shard_start, int64_t shard_numel, float* out, float* partial_sq, int64_t pad_off, int64_t epoch, void* stream);
 PDB_API int pdb200_nvl_ce_combine(const uint64_t* peer_ptrs, int nranks, int rank, int64_t stats_off, const int64_t* labels, float* loss, float* lse, int64_t rows, int64_t ignore_index, int64_t pad_off, int64_t epoch, void* stream);
 
+/* K5 all-gather -> GEMM and K6 GEMM -> reduce-scatter on the tcgen05 kernel (reference: fleet/utils/
+ * sequence_parallel_utils.py:255-285 ncclAllGather + GEMM, :660-676 GEMM + ncclReduceScatter).  K5: every rank's
+ * [rows_per_rank, K] bf16 shard sits at a_off in its segment; A tiles are TMA-loaded straight from the owning peer.
+ * K6: partial output tiles are stored into the owner's staging slab [nranks][rows_per_rank][N] at stage_off as they
+ * leave TMEM, then folded into out[rows_per_rank, N]. */
+PDB_API int pdb200_gemm_bf16_ag(const uint64_t* peer_ptrs, int nranks, int rank, int64_t a_off, int64_t rows_per_rank, const void* b, void* c, const void* bias, int64_t N, int64_t K, int trans_b, int act, int64_t pad_off, int64_t epoch, void* stream);
+PDB_API int pdb200_gemm_bf16_rs(const uint64_t* peer_ptrs, int nranks, int rank, const void* a, const void* b, int64_t stage_off, void* out, int64_t rows_per_rank, int64_t N, int64_t K, int trans_b, int64_t pad_off, int64_t epoch, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -187,6 +187,64 @@ class _SPColumnFn(torch.autograd.Function):
         return dx, dw, db, None, None, None
 
 
+class _FusedColSP(torch.autograd.Function):
+    """K5 forward (all-gather fused into the GEMM's TMA producer), K6 for dX in backward."""
+
+    @staticmethod
+    def forward(ctx, x, w, group):
+        from paddle_b200.parallel import symm
+        shp = x.shape
+        y = symm.ag_gemm(x.reshape(-1, shp[-1]), w, group)
+        ctx.save_for_backward(x, w)
+        ctx.group = group
+        return y.reshape(shp[0] * group.nranks, *shp[1:-1], w.shape[1])
+
+    @staticmethod
+    def backward(ctx, dy):
+        from paddle_b200.parallel import symm
+        x, w = ctx.saved_tensors
+        g = ctx.group
+        dy2 = dy.reshape(-1, dy.shape[-1]).contiguous()
+        dx = symm.gemm_rs(dy2, w, g, trans_b=True).reshape(x.shape)            # dY W^T -> reduce-scatter, fused
+        full = symm.all_gather_seq(x, g).reshape(-1, x.shape[-1])
+        mg = getattr(w, "main_grad", None)
+        dw = torch.matmul(full.t(), dy2)
+        return dx, dw, None
+
+
+class _FusedRowSP(torch.autograd.Function):
+    """K6 forward (partial tiles pushed to the owner as they leave TMEM), K5 for dX in backward."""
+
+    @staticmethod
+    def forward(ctx, x, w, group):
+        from paddle_b200.parallel import symm
+        shp = x.shape
+        y = symm.gemm_rs(x.reshape(-1, shp[-1]), w, group)
+        ctx.save_for_backward(x, w)
+        ctx.group = group
+        return y.reshape(shp[0] // group.nranks, *shp[1:-1], w.shape[1])
+
+    @staticmethod
+    def backward(ctx, dy):
+        from paddle_b200.parallel import symm
+        x, w = ctx.saved_tensors
+        g = ctx.group
+        dy2 = dy.reshape(-1, dy.shape[-1]).contiguous()
+        dx = symm.ag_gemm(dy2, w, g, trans_b=True).reshape(x.shape)           # all-gather(dY) W^T, fused
+        dfull = symm.all_gather_seq(dy, g).reshape(-1, dy.shape[-1])
+        dw = torch.matmul(x.reshape(-1, x.shape[-1]).t(), dfull)
+        return dx, dw, None
+
+
+def _fused_sp_ok(x, w, group, gathered_rows_from_x):
+    from paddle_b200.parallel import symm
+    if not (x.is_cuda and x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16):
+        return False
+    rows = x.numel() // x.shape[-1]
+    rows_per_rank = rows if gathered_rows_from_x else rows // group.nranks
+    return symm.fused_gemm_ok(group, rows_per_rank, w.shape[0], w.shape[1], x.dtype)
+
+
 class ColumnSequenceParallelLinear(Layer):
     def __init__(self, in_features, out_features, weight_attr=None, has_bias=None, gather_output=True,
                  fuse_matmul_bias=False, mp_group=None, name=None):
@@ -215,6 +273,9 @@ class ColumnSequenceParallelLinear(Layer):
     def forward(self, x):
         if not self.is_mp:
             return F.linear(x, self.weight, self.bias)
+        if _fused_sp_ok(x, self.weight, self.model_parallel_group, True):
+            y = _FusedColSP.apply(x, self.weight, self.model_parallel_group)
+            return y + self.bias if self.bias is not None else y
         if self.overlap:
             return _SPColumnFn.apply(x, self.weight, self.bias, self.model_parallel_group, self.recompute_allgather,
                                      self.fuse_grad_add)
@@ -245,5 +306,8 @@ class RowSequenceParallelLinear(Layer):
     def forward(self, x):
         if not self.is_mp:
             return F.linear(x, self.weight, self.bias)
-        out = ReduceScatterOp.apply(F.linear(x, self.weight))
+        if _fused_sp_ok(x, self.weight, self.model_parallel_group, False):
+            out = _FusedRowSP.apply(x, self.weight, self.model_parallel_group)
+        else:
+            out = ReduceScatterOp.apply(F.linear(x, self.weight))
         return out + self.bias if self.bias is not None else out

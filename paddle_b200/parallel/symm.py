@@ -123,7 +123,7 @@ def available(group=None) -> bool:
     return lib.runtime.pdb200_symm_supported(torch.cuda.current_device()) >= 1
 
 
-def get_arena(group, min_bytes=64 << 20, key="default"):
+def get_arena(group, min_bytes=int(os.environ.get("PDB200_SYMM_ARENA_MB", "512")) << 20, key="default"):
     k = (group.id, key)
     a = _arenas.get(k)
     if a is None or a.free_bytes() < 0:
@@ -214,6 +214,68 @@ def ce_exchange_combine(stats, labels, group, ignore_index):
                                             ptr(lse), rows, int(ignore_index), 0, arena.next_epoch(),
                                             stream_ptr(stats.device)), "nvl_ce_combine")
     return loss, lse
+
+
+_stage = {}
+
+
+def _staging(arena, tag, shape, dtype):
+    key = (id(arena), tag, tuple(shape), dtype)
+    t = _stage.get(key)
+    if t is None:
+        t = arena.empty(shape, dtype)
+        _stage[key] = t
+    return t
+
+
+def ag_gemm(x_shard, weight, group, bias=None, trans_b=False, act=None):
+    """K5: ``all_gather(x_shard, dim 0) @ weight`` without materialising the gathered activation: the GEMM's TMA
+    producer reads every peer's shard in place over NVLink.  x_shard: [rows, K] bf16; returns [nranks*rows, N]."""
+    from paddle_b200.lib import check
+    from paddle_b200.ops._util import ptr
+    arena = get_arena(group)
+    rows, K = x_shard.shape
+    N = weight.shape[0] if trans_b else weight.shape[1]
+    buf = _staging(arena, "ag_a", (rows, K), torch.bfloat16)
+    buf.copy_(x_shard)
+    out = torch.empty(rows * arena.nranks, N, dtype=torch.bfloat16, device=x_shard.device)
+    check(lib.kernels.pdb200_gemm_bf16_ag(arena.peers_arg, arena.nranks, arena.rank, buf._symm[1], rows, ptr(weight),
+                                          ptr(out), ptr(bias), N, K, int(trans_b),
+                                          {"none": 0, None: 0, "gelu": 1, "relu": 2}[act], 0, arena.next_epoch(),
+                                          stream_ptr(x_shard.device)), "gemm_bf16_ag")
+    return out
+
+
+def gemm_rs(x, weight, group, trans_b=False):
+    """K6: ``reduce_scatter(x @ weight, dim 0)``: partial tiles go straight from TMEM to the owner rank's staging slab
+    over NVLink while the remaining tiles are still being computed.  x: [nranks*rows, K] bf16; returns [rows, N]."""
+    from paddle_b200.lib import check
+    from paddle_b200.ops._util import ptr
+    arena = get_arena(group)
+    M, K = x.shape
+    n = arena.nranks
+    rows = M // n
+    N = weight.shape[0] if trans_b else weight.shape[1]
+    stage = _staging(arena, "rs_stage", (n, rows, N), torch.bfloat16)
+    out = torch.empty(rows, N, dtype=torch.bfloat16, device=x.device)
+    xc = x.contiguous()
+    check(lib.kernels.pdb200_gemm_bf16_rs(arena.peers_arg, n, arena.rank, ptr(xc), ptr(weight), stage._symm[1], ptr(out),
+                                          rows, N, K, int(trans_b), 0, arena.next_epoch(), stream_ptr(x.device)),
+          "gemm_bf16_rs")
+    return out
+
+
+def fused_gemm_ok(group, rows_per_rank, K, N, dtype, weight=None):
+    if not (dtype == torch.bfloat16 and rows_per_rank % 128 == 0 and K % 64 == 0 and N % 64 == 0 and available(group)):
+        return False
+    if not hasattr(lib.kernels.require(), "pdb200_gemm_bf16_ag"):
+        return False
+    try:
+        arena = get_arena(group)
+    except Exception:  # noqa: BLE001
+        return False
+    need = max(rows_per_rank * K, group.nranks * rows_per_rank * N) * 2
+    return arena.free_bytes() > need or any(k[0] == id(arena) for k in _stage)
 
 
 # --------------------------------------------------------------------------------------------- NCCL-shaped helpers

@@ -1,0 +1,64 @@
+"""Worker (>= 2 GPUs): one training config, transport chosen by FLAGS_use_fused_comm (env); final parameters are
+written to <out>.<rank>.pt so the driver can compare the fused NVLink run with the NCCL run."""
+import sys
+
+import torch
+
+import paddle_b200 as paddle
+import paddle_b200.distributed as dist
+from paddle_b200 import nn
+from paddle_b200.distributed import fleet
+from paddle_b200.framework.flags import flag
+
+mode, out = sys.argv[1], sys.argv[2]
+H = 512
+
+
+def build():
+    paddle.seed(11)
+    paddle.set_default_dtype("bfloat16")
+    try:
+        with paddle.utils.unique_name.guard():
+            return nn.Sequential(nn.Linear(H, 4 * H, bias_attr=False), nn.GELU(), nn.Linear(4 * H, H, bias_attr=False))
+    finally:
+        paddle.set_default_dtype("float32")
+
+
+def data(step, rank, dev):
+    g = torch.Generator().manual_seed(100 * step + rank)
+    return torch.randn(64, H, generator=g).to(dev).bfloat16(), torch.randn(64, H, generator=g).to(dev).bfloat16()
+
+
+if mode == "dp":
+    dist.init_parallel_env()
+    r = dist.get_rank()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    m = build()
+    model = paddle.DataParallel(m, comm_buffer_size=2, last_comm_buffer_size=1)
+    used_fused = model._reducer._fused is not None
+    opt = paddle.optimizer.AdamW(1e-3, parameters=m.parameters(), multi_precision=True)
+else:
+    st = fleet.DistributedStrategy()
+    st.hybrid_configs = {"dp_degree": 1, "mp_degree": 1, "pp_degree": 1, "sharding_degree": dist.ParallelEnv().world_size,
+                         "sharding_configs": {"split_param": True}}
+    fleet.init(is_collective=True, strategy=st)
+    r = dist.get_rank()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    m = build()
+    clip = nn.ClipGradByGlobalNorm(0.05) if mode == "v2clip" else None
+    opt = paddle.optimizer.AdamW(1e-3, parameters=m.parameters(), multi_precision=True, grad_clip=clip)
+    model = fleet.distributed_model(m)
+    opt = fleet.distributed_optimizer(opt)
+    used_fused = opt._inner_opt._arena is not None
+assert used_fused == bool(flag("use_fused_comm")), (used_fused, flag("use_fused_comm"))
+for s in range(4):
+    x, y = data(s, r, dev)
+    ((model(x) - y).float() ** 2).mean().backward()
+    opt.step()
+    opt.clear_grad()
+torch.cuda.synchronize()
+torch.save({k: v.detach().float().cpu() for k, v in m.state_dict().items()}, f"{out}.{r}.pt")
+print(f"fused_vs_nccl {mode} fused={used_fused} ok", r, flush=True)
+from paddle_b200.parallel import symm
+symm.release_all()
+dist.destroy_process_group()

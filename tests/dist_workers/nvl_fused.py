@@ -80,6 +80,30 @@ loss = mp_ops._c_softmax_with_cross_entropy(shard, labels, group=g, ignore_index
 loss.sum().backward()
 ref = torch.nn.functional.cross_entropy(full.bfloat16().float(), labels.squeeze(-1), ignore_index=-100, reduction="none")
 torch.testing.assert_close(loss.squeeze(-1), ref, rtol=1e-3, atol=2e-3)
+# ---- K5 all-gather -> GEMM and K6 GEMM -> reduce-scatter on the tcgen05 kernel
+torch.manual_seed(50 + r)
+rows, K, N = 256, 512, 768
+xs = (torch.randn(rows, K, device=dev) * 0.5).bfloat16()
+w = (torch.randn(K, N, device=dev) * 0.1).bfloat16()
+dist.broadcast(w, 0)
+parts = []
+dist.all_gather(parts, xs)
+ref = torch.cat(parts, 0).float() @ w.float()
+for _ in range(2):                       # twice: staging reuse + epoch handling
+    got = symm.ag_gemm(xs, w, g)
+    torch.cuda.synchronize()
+    torch.testing.assert_close(got.float(), ref, rtol=2e-2, atol=5e-2)
+xf = (torch.randn(rows * n, K, device=dev) * 0.5).bfloat16()
+partial = xf.float() @ w.float()
+dist.all_reduce(partial)
+ref_rs = partial[r * rows:(r + 1) * rows]
+for _ in range(2):
+    got = symm.gemm_rs(xf, w, g)
+    torch.cuda.synchronize()
+    torch.testing.assert_close(got.float(), ref_rs, rtol=2e-2, atol=1e-1)
+wt = w.t().contiguous()                   # trans_b variants (backward shapes)
+got = symm.ag_gemm(xs, wt, g, trans_b=True)
+torch.testing.assert_close(got.float(), ref, rtol=2e-2, atol=5e-2)
 print("nvl_fused ok", r, flush=True)
 symm.release_all()
 dist.destroy_process_group()

@@ -24,3 +24,28 @@ def _run(script, nproc, timeout=600):
 def test_nvl_fused_kernels_match_nccl():
     out = _run("nvl_fused.py", min(torch.cuda.device_count(), 8))
     assert "nvl_fused ok" in out.stdout
+
+
+def _run_env(script, nproc, args, env_extra, port):
+    env = dict(os.environ)
+    env["PYTHONPATH"] = ROOT + os.pathsep + env.get("PYTHONPATH", "")
+    env.update(env_extra)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}", "--master-addr",
+           "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "dist_workers", script), *args]
+    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert r.returncode == 0, f"{script} {args} failed\n{r.stdout[-3000:]}\n{r.stderr[-6000:]}"
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+@pytest.mark.parametrize("mode", ["dp", "v2", "v2clip"])
+def test_fused_training_matches_nccl_training(mode, tmp_path):
+    """DataParallel (K1) and sharding V2 (K2+K3, with and without global-norm clip): same parameters after 4 steps
+    whether gradients travel through the fused NVLink kernels or through NCCL."""
+    n = 2
+    _run_env("fused_vs_nccl.py", n, (mode, str(tmp_path / "nccl")), {"FLAGS_use_fused_comm": "0"}, 29621)
+    _run_env("fused_vs_nccl.py", n, (mode, str(tmp_path / "fused")), {"FLAGS_use_fused_comm": "1"}, 29622)
+    for r in range(n):
+        a = torch.load(tmp_path / f"nccl.{r}.pt")
+        b = torch.load(tmp_path / f"fused.{r}.pt")
+        for k in a:
+            torch.testing.assert_close(a[k], b[k], rtol=2e-2, atol=2e-3, msg=lambda s: f"{mode} rank {r} {k}: {s}")
