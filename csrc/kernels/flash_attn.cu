@@ -185,8 +185,7 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
       const uint32_t ts = tmem_base + st * BKV + lane_off;
       mbar_wait(&s_full[st], (j >> 1) & 1);
       tc_fence_after();
-      const bool need_mask = p.causal && (j * BKV + BKV - 1 > q_idx + diag - (row) + 0 * row) &&
-                             (j * BKV + BKV - 1 > qt * BQ + diag);   // tile touches the diagonal for some row
+      const bool need_mask = p.causal && (j * BKV + BKV - 1 > qt * BQ + diag);   // tile crosses the diagonal for some row
       // ---- pass 1: row max
       float m_tile = -INFINITY;
 #pragma unroll
@@ -246,10 +245,7 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
         mbar_arrive(&s_empty[st]);
         mbar_arrive(p_ready);
       }
-      // alpha applies to what was accumulated before tile j: it is consumed when O_j is folded (next iteration)
-      alpha_prev = alpha;
-      // O accumulated so far (tiles < j) must be rescaled by alpha when tile j joins: fold_o(j, ...) multiplies first
-      // -> pass the factor that belongs to tile j
+      // alpha rescales what was accumulated before tile j; it is applied when O_j is folded (next iteration)
     }
     // last tile
     fold_o(n_kv - 1, alpha_prev);

@@ -92,6 +92,11 @@ PDB_API int pdb200_nvl_ce_combine(const uint64_t* peer_ptrs, int nranks, int ran
 PDB_API int pdb200_gemm_bf16_ag(const uint64_t* peer_ptrs, int nranks, int rank, int64_t a_off, int64_t rows_per_rank, const void* b, void* c, const void* bias, int64_t N, int64_t K, int trans_b, int act, int64_t pad_off, int64_t epoch, void* stream);
 PDB_API int pdb200_gemm_bf16_rs(const uint64_t* peer_ptrs, int nranks, int rank, const void* a, const void* b, int64_t stage_off, void* out, int64_t rows_per_rank, int64_t N, int64_t K, int trans_b, int64_t pad_off, int64_t epoch, void* stream);
 
+/* K16 flash-attention forward on tcgen05 (reference: phi/kernels/gpu/flash_attn_kernel.cu:305-447 -> FlashAttention-2
+ * sm80 kernels).  q [b,sq,hq,d], k/v [b,sk,hk,d] bf16, d in {64,128}, sq/sk multiples of 128; o like q; lse [b,hq,sq]
+ * fp32 (natural log of the softmax denominator, scaled scores). */
+PDB_API int pdb200_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int64_t b, int64_t sq, int64_t sk, int64_t hq, int64_t hk, int64_t d, float scale, int causal, int dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
