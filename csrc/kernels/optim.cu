@@ -9,6 +9,8 @@
 // device memory, so the step never synchronises with the host.  Bias-correction powers are host scalars.
 #include "common.cuh"
 
+#include <atomic>
+
 namespace pdb {
 
 struct MTDesc {          // 64 bytes, mirrored by paddle_b200/ops/multi_tensor.py (numpy structured dtype)
@@ -273,4 +275,59 @@ PDB_EXPORT int pdb200_unscale_check_multi(const void* table, const void* chunk_m
   unscale_check_kernel<<<n_chunks, kThreads, 0, (cudaStream_t)stream>>>((const MTDesc*)table, (const int2*)chunk_map,
                                                                        inv_scale, found_inf);
   return check_launch("unscale_check_multi");
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// pdb200_l2norm_multi_static: the same sum of squares as pdb200_l2norm_multi, for callers that cannot hand over a
+// scratch buffer because they cannot allocate device memory at the point of the call: a plain C host program that
+// links this library without a tensor framework (so there is no caching allocator to ask), or a step loop that has
+// already handed all free memory to its own pools and must not let cudaMalloc synchronise the device in the middle
+// of a step.  The per-chunk partial sums live in a fixed array inside this library instead.
+//
+//  * Limit: kStaticScratchChunks chunks (1 Mi chunks x 16384 elements = 17.2 G elements, 4 MiB of device memory
+//    per device that loads the library).  A larger n_chunks is refused with an error; nothing is launched.
+//  * Set-up: the first call on each device resolves the array's device address (cudaGetSymbolAddress, with that
+//    device current) and caches it.  That lookup may initialise the module on the device, so make the first call
+//    on every device before any stream capture begins.
+//  * Nothing has to start at zero: the first kernel overwrites partials[0, n_chunks) before the second kernel reads
+//    exactly that range, so whatever the previous call left behind is never observed.
+//  * The array is shared by every caller on the device.  Two calls whose kernels can overlap (different streams
+//    without an ordering between them, or two host threads on different streams) race on it - order them on one
+//    stream or with an event.  Calls on the same stream are safe back to back.
+//  * This entry point performs no allocation of any kind (no cudaMalloc/cudaFree, no library allocator).
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+constexpr int kStaticScratchChunks = 1 << 20;
+constexpr int kMaxDevices = 64;
+static __device__ __align__(256) float g_l2norm_static_partials[kStaticScratchChunks];
+std::atomic<float*> g_static_partials_addr[kMaxDevices];
+}  // namespace
+
+PDB_EXPORT int pdb200_l2norm_multi_static_max_chunks() { return kStaticScratchChunks; }
+
+PDB_EXPORT int pdb200_l2norm_multi_static(const void* table, const void* chunk_map, int n_chunks, float* out,
+                                          int accumulate, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  PDB_REQUIRE(n_chunks >= 0 && n_chunks <= kStaticScratchChunks,
+              "l2norm_multi_static: %d chunks requested, the built-in scratch holds at most %d (use "
+              "pdb200_l2norm_multi with caller-provided scratch for larger inputs)",
+              n_chunks, kStaticScratchChunks);
+  int dev = -1;
+  PDB_CUDA_OK(cudaGetDevice(&dev));
+  PDB_REQUIRE(dev >= 0 && dev < kMaxDevices, "l2norm_multi_static: device ordinal %d out of range", dev);
+  float* partials = g_static_partials_addr[dev].load(std::memory_order_acquire);
+  if (partials == nullptr) {
+    // once per device (a concurrent first call resolves the same address, so the race is benign)
+    void* addr = nullptr;
+    PDB_CUDA_OK(cudaGetSymbolAddress(&addr, g_l2norm_static_partials));
+    PDB_REQUIRE(addr != nullptr, "l2norm_multi_static: cudaGetSymbolAddress returned a null address");
+    partials = (float*)addr;
+    g_static_partials_addr[dev].store(partials, std::memory_order_release);
+  }
+  if (n_chunks > 0) {
+    l2norm_partial_kernel<<<n_chunks, kThreads, 0, st>>>((const MTDesc*)table, (const int2*)chunk_map, partials);
+    if (int e = check_launch("l2norm_partial(static)")) return e;
+  }
+  fold_sum_kernel<<<1, 1024, 0, st>>>(partials, n_chunks, out, accumulate);
+  return check_launch("l2norm_fold(static)");
 }

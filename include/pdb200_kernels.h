@@ -49,6 +49,14 @@ PDB_API int pdb200_adamw_multi(const void* table, const void* chunk_map, int n_c
 PDB_API int pdb200_momentum_multi(const void* table, const void* chunk_map, int n_chunks, float lr, float mu, float l2_decay, int nesterov, const float* grad_scale, const float* found_inf, void* stream);
 PDB_API int pdb200_l2norm_multi(const void* table, const void* chunk_map, int n_chunks, float* scratch, int64_t scratch_floats, float* out, int accumulate, void* stream);
 PDB_API int pdb200_unscale_check_multi(const void* table, const void* chunk_map, int n_chunks, const float* inv_scale, float* found_inf, void* stream);
+/* No counterpart in the reference.  Same result as pdb200_l2norm_multi, but the per-chunk partial sums live in a
+ * fixed 4 MiB array inside the library, for callers that cannot allocate device memory at the call site (a C host
+ * without a tensor allocator; a step loop that must not let cudaMalloc synchronise the device).  Allocates nothing.
+ * n_chunks above pdb200_l2norm_multi_static_max_chunks() is refused.  The first call on each device looks up the
+ * array's address: make it before any stream capture.  The array is shared per device: calls that may overlap
+ * (unordered streams / threads) race - keep them ordered on one stream. */
+PDB_API int pdb200_l2norm_multi_static_max_chunks();
+PDB_API int pdb200_l2norm_multi_static(const void* table, const void* chunk_map, int n_chunks, float* out, int accumulate, void* stream);
 
 /* K8 softmax cross-entropy, local / per-rank part (reference: phi/kernels/gpu/cross_entropy_kernel.cu,
  * fluid/operators/collective/c_softmax_with_cross_entropy_op.cu:47-114,133-340). stats: [rows,3] = max,sumexp,target */
