@@ -421,6 +421,30 @@ __global__ void __launch_bounds__(256) rs_fold_kernel(const __nv_bfloat16* __res
     o.store(out + i * 8);
   }
 }
+// K4 tail: same fold, but the summed rows are stored into every rank's full output (all-gather half of the all-reduce).
+struct OutPtrs { uint64_t p[8]; };
+__global__ void __launch_bounds__(256) ar_fold_kernel(const __nv_bfloat16* __restrict__ staging, OutPtrs outs,
+                                                     int64_t per_rank_elems, int nranks, int rank) {
+  const int64_t nvec = per_rank_elems / 8;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    for (int r = 0; r < nranks; ++r) {
+      Vec<__nv_bfloat16> x;
+      x.load_nc(staging + r * per_rank_elems + i * 8);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += x.f(j);
+    }
+    Vec<__nv_bfloat16> o;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o.set(j, acc[j]);
+    for (int r = 0; r < nranks; ++r) {
+      const int dst = (rank + r) % nranks;   // start with the local copy, then walk the peers
+      o.store((__nv_bfloat16*)outs.p[dst] + (int64_t)rank * per_rank_elems + i * 8);
+    }
+  }
+}
 }  // namespace tc
 }  // namespace pdb
 
@@ -505,4 +529,49 @@ PDB_EXPORT int pdb200_gemm_bf16_rs(const uint64_t* peer_ptrs, int nranks, int ra
   rs_fold_kernel<<<(int)(blocks < 1 ? 1 : blocks), 256, 0, st>>>((const __nv_bfloat16*)(peer_ptrs[rank] + stage_off),
                                                              (__nv_bfloat16*)out, per, nranks);
   return check_launch("gemm_rs");
+}
+
+// K4 GEMM -> all-reduce (RowParallelLinear forward, ColumnParallelLinear dX).  Same tile-by-tile push of partial tiles to
+// the owning rank as K6; the owner then folds its rows and stores the sum into EVERY rank's output, which lives at byte
+// offset out_off ([M, N] bf16) of each symmetric segment.  Uses epochs epoch, epoch+1, epoch+2.
+PDB_EXPORT int pdb200_gemm_bf16_ar(const uint64_t* peer_ptrs, int nranks, int rank, const void* a, const void* b,
+                                   int64_t stage_off, int64_t out_off, int64_t rows_per_rank, int64_t N, int64_t K,
+                                   int trans_b, int64_t pad_off, int64_t epoch, void* stream) {
+  using namespace pdb::tc;
+  PDB_REQUIRE(nranks >= 1 && nranks <= 8, "gemm_ar: nranks %d out of range", nranks);
+  PDB_REQUIRE(rows_per_rank % BM == 0, "gemm_ar: rows per rank (%lld) must be a multiple of %d", (long long)rows_per_rank, BM);
+  PDB_REQUIRE(K % 8 == 0 && N % 8 == 0 && stage_off % 16 == 0 && out_off % 16 == 0 && ((uintptr_t)a & 15) == 0,
+              "gemm_ar: alignment");
+  cudaStream_t st = (cudaStream_t)stream;
+  CommArgs comm{};
+  comm.mode = 2;
+  comm.nranks = nranks;
+  comm.rank = rank;
+  comm.rows_per_rank = (int)rows_per_rank;
+  comm.m_rot = (int)(((rank + 1) % nranks) * (rows_per_rank / BM));
+  for (int p = 0; p < nranks; ++p) comm.out_ptr[p] = peer_ptrs[p] + (uint64_t)stage_off;
+  const int M = (int)(rows_per_rank * nranks);
+  pdb::nvl::Peers P = make_peers_(peer_ptrs, nranks, rank);
+  pdb::nvl::gemm_barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)epoch, kGemmSpinLimit);   // slabs + outputs free
+  int rc;
+  const bool big = (N % 256 == 0) || N >= 1024;
+  if (trans_b)
+    rc = big ? launch<false, false, 256, false>(a, b, nullptr, nullptr, M, (int)N, (int)K, 0.f, 0, st, &comm)
+             : launch<false, false, 128, false>(a, b, nullptr, nullptr, M, (int)N, (int)K, 0.f, 0, st, &comm);
+  else
+    rc = big ? launch<false, true, 256, false>(a, b, nullptr, nullptr, M, (int)N, (int)K, 0.f, 0, st, &comm)
+             : launch<false, true, 128, false>(a, b, nullptr, nullptr, M, (int)N, (int)K, 0.f, 0, st, &comm);
+  if (rc) return rc;
+  pdb::nvl::gemm_barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kGemmSpinLimit);  // partials landed
+  const int64_t per = rows_per_rank * N;
+  int64_t blocks = (per / 8 + 255) / 256;
+  const int64_t cap = (int64_t)sm_count() * 8;
+  if (blocks > cap) blocks = cap;
+  OutPtrs outs{};
+  for (int p = 0; p < nranks; ++p) outs.p[p] = peer_ptrs[p] + (uint64_t)out_off;
+  ar_fold_kernel<<<(int)(blocks < 1 ? 1 : blocks), 256, 0, st>>>((const __nv_bfloat16*)(peer_ptrs[rank] + stage_off), outs, per,
+                                                             nranks, rank);
+  if (int e = check_launch("gemm_ar fold")) return e;
+  pdb::nvl::gemm_barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 2), kGemmSpinLimit);  // every row landed
+  return check_launch("gemm_ar");
 }

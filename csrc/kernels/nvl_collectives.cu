@@ -268,6 +268,30 @@ __global__ void ce_combine_symm_kernel(Peers P, uint64_t stats_off, const int64_
   loss[row] = (labels[row] == ignore_index) ? 0.f : l - tgt;
 }
 
+// ---------------------------------------------------------------------------------------------- K7
+// Vocab-parallel embedding forward.  The reference looks rows up locally (zeros for ids another rank owns) and then
+// all-reduces [tokens, hidden]; since exactly one rank owns each row, the sum is really a gather: every rank reads the
+// row straight from the owner's table shard over NVLink.  One warp per token, 16-byte vectors.
+template <typename T>
+__global__ void __launch_bounds__(256) vocab_embed_gather_kernel(Peers P, uint64_t table_off, const int64_t* __restrict__ ids,
+                                                                T* __restrict__ out, int64_t n_tokens, int hidden,
+                                                                int64_t vocab_per_rank) {
+  constexpr int V = 16 / sizeof(T);
+  const int warps = blockDim.x >> 5, lane = threadIdx.x & 31;
+  for (int64_t t = (int64_t)blockIdx.x * warps + (threadIdx.x >> 5); t < n_tokens; t += (int64_t)gridDim.x * warps) {
+    const int64_t id = ids[t];
+    const int64_t owner = id / vocab_per_rank;
+    T* dst = out + t * hidden;
+    if (id < 0 || owner >= P.nranks) {   // padding ids produce zeros, like the masked lookup they replace
+      for (int c = lane * V; c < hidden; c += 32 * V) *reinterpret_cast<uint4*>(dst + c) = make_uint4(0, 0, 0, 0);
+      continue;
+    }
+    const T* src = reinterpret_cast<const T*>(P.ptr[owner] + table_off) + (id - owner * vocab_per_rank) * hidden;
+    for (int c = lane * V; c < hidden; c += 32 * V)
+      *reinterpret_cast<uint4*>(dst + c) = *reinterpret_cast<const uint4*>(src + c);
+  }
+}
+
 static Peers make_peers(const uint64_t* ptrs, uint64_t mc, int nranks, int rank) {
   Peers P{};
   for (int i = 0; i < nranks && i < kMaxRanks; ++i) P.ptr[i] = ptrs[i];
@@ -382,4 +406,31 @@ PDB_EXPORT int pdb200_nvl_ce_combine(const uint64_t* peer_ptrs, int nranks, int 
   // peers may overwrite their stats only after everyone has read them
   barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
   return check_launch("nvl_ce_combine");
+}
+
+// K7: out[t, :] = table_of_owner(ids[t])[ids[t] - owner * vocab_per_rank, :].  Every rank's table shard
+// [vocab_per_rank, hidden] sits at byte offset table_off of its symmetric segment.  The leading barrier orders the
+// gather after every rank's last write to its shard (optimizer step); the trailing one keeps shards stable while read.
+PDB_EXPORT int pdb200_nvl_vocab_embed(const uint64_t* peer_ptrs, int nranks, int rank, int64_t table_off,
+                                      const int64_t* ids, void* out, int64_t n_tokens, int hidden,
+                                      int64_t vocab_per_rank, int dtype, int64_t pad_off, int64_t epoch, void* stream) {
+  PDB_REQUIRE(nranks >= 1 && nranks <= kMaxRanks, "nvl: nranks %d out of range (1..%d)", nranks, kMaxRanks);
+  const int esz = dtype == PDB_DTYPE_F32 ? 4 : 2;
+  PDB_REQUIRE((hidden * esz) % 16 == 0 && table_off % 16 == 0 && ((uintptr_t)out & 15) == 0,
+              "vocab_embed: rows must be 16-byte multiples and 16-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  Peers P = make_peers(peer_ptrs, 0, nranks, rank);
+  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+  if (n_tokens > 0) {
+    int64_t blocks = (n_tokens + 7) / 8;
+    const int64_t cap = (int64_t)sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    if (dtype == PDB_DTYPE_F32)
+      vocab_embed_gather_kernel<float><<<(unsigned)blocks, 256, 0, st>>>(P, (uint64_t)table_off, ids, (float*)out, n_tokens, hidden, vocab_per_rank);
+    else
+      vocab_embed_gather_kernel<uint16_t><<<(unsigned)blocks, 256, 0, st>>>(P, (uint64_t)table_off, ids, (uint16_t*)out, n_tokens, hidden, vocab_per_rank);
+    if (int e = check_launch("vocab_embed_gather")) return e;
+  }
+  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
+  return check_launch("nvl_vocab_embed");
 }

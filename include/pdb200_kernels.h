@@ -91,6 +91,8 @@ PDB_API int pdb200_nvl_rs_adamw_ag(const uint64_t* peer_ptrs, uint64_t mc_ptr, i
 PDB_API int pdb200_nvl_rs_grid(int64_t shard_numel);
 PDB_API int pdb200_nvl_reduce_scatter(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t grad_off, int grad_dtype, int64_t shard_start, int64_t shard_numel, float* out, float* partial_sq, int64_t pad_off, int64_t epoch, void* stream);
 PDB_API int pdb200_nvl_ce_combine(const uint64_t* peer_ptrs, int nranks, int rank, int64_t stats_off, const int64_t* labels, float* loss, float* lse, int64_t rows, int64_t ignore_index, int64_t pad_off, int64_t epoch, void* stream);
+/* K7 vocab-parallel embedding forward as a gather from the owning rank's table shard (replaces masked lookup + all-reduce). */
+PDB_API int pdb200_nvl_vocab_embed(const uint64_t* peer_ptrs, int nranks, int rank, int64_t table_off, const int64_t* ids, void* out, int64_t n_tokens, int hidden, int64_t vocab_per_rank, int dtype, int64_t pad_off, int64_t epoch, void* stream);
 
 /* K5 all-gather -> GEMM and K6 GEMM -> reduce-scatter on the tcgen05 kernel (reference: fleet/utils/
  * sequence_parallel_utils.py:255-285 ncclAllGather + GEMM, :660-676 GEMM + ncclReduceScatter).  K5: every rank's
@@ -99,6 +101,8 @@ PDB_API int pdb200_nvl_ce_combine(const uint64_t* peer_ptrs, int nranks, int ran
  * leave TMEM, then folded into out[rows_per_rank, N]. */
 PDB_API int pdb200_gemm_bf16_ag(const uint64_t* peer_ptrs, int nranks, int rank, int64_t a_off, int64_t rows_per_rank, const void* b, void* c, const void* bias, int64_t N, int64_t K, int trans_b, int act, int64_t pad_off, int64_t epoch, void* stream);
 PDB_API int pdb200_gemm_bf16_rs(const uint64_t* peer_ptrs, int nranks, int rank, const void* a, const void* b, int64_t stage_off, void* out, int64_t rows_per_rank, int64_t N, int64_t K, int trans_b, int64_t pad_off, int64_t epoch, void* stream);
+/* K4 GEMM -> all-reduce: K6's tile push, then owners fold and store the sum into every rank's [M,N] output at out_off. */
+PDB_API int pdb200_gemm_bf16_ar(const uint64_t* peer_ptrs, int nranks, int rank, const void* a, const void* b, int64_t stage_off, int64_t out_off, int64_t rows_per_rank, int64_t N, int64_t K, int trans_b, int64_t pad_off, int64_t epoch, void* stream);
 
 /* K16 flash-attention forward on tcgen05 (reference: phi/kernels/gpu/flash_attn_kernel.cu:305-447 -> FlashAttention-2
  * sm80 kernels).  q [b,sq,hq,d], k/v [b,sk,hk,d] bf16, d in {64,128}, sq/sk multiples of 128; o like q; lse [b,hq,sq]

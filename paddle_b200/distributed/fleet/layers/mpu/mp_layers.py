@@ -75,9 +75,88 @@ class VocabParallelEmbedding(Layer):
     def forward(self, x):
         if not self.is_mp:
             return F.embedding(x, self.weight)
+        if self.weight.is_cuda and self.weight.shape[1] * self.weight.element_size() % 16 == 0:
+            from paddle_b200.parallel import symm
+            if symm.available(self.model_parallel_group) and hasattr(symm.lib.kernels.require(), "pdb200_nvl_vocab_embed") \
+                    and symm.make_symmetric(self.weight, self.model_parallel_group):
+                return _VocabEmbedFused.apply(x, self.weight, self.weight._symm, self.vocab_start_index)
         out = mp_ops._c_lookup_table(self.weight, x, start_index=self.vocab_start_index,
                                      vocab_size=self.origin_num_embeddings)
         return mp_ops._mp_allreduce(out, group=self.model_parallel_group)
+
+
+class _VocabEmbedFused(torch.autograd.Function):
+    """K7: forward gathers each row from the owning rank's shard over NVLink (no [tokens, hidden] all-reduce);
+    backward needs no communication: activations are replicated across mp, so each rank accumulates its own rows."""
+
+    @staticmethod
+    def forward(ctx, ids, w, where, start):
+        from paddle_b200.parallel import symm
+        ctx.save_for_backward(ids)
+        ctx.start, ctx.rows, ctx.wdtype = start, w.shape[0], w.dtype
+        return symm.vocab_embed(ids, w, where)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (ids,) = ctx.saved_tensors
+        local = ids.reshape(-1) - ctx.start
+        ok = (local >= 0) & (local < ctx.rows)
+        dw = torch.zeros(ctx.rows, dy.shape[-1], dtype=torch.float32, device=dy.device)
+        dw.index_add_(0, local.clamp(0, ctx.rows - 1), dy.reshape(-1, dy.shape[-1]).float() * ok[:, None])
+        return None, dw.to(ctx.wdtype), None, None
+
+
+class _FusedRowAR(torch.autograd.Function):
+    """K4 forward: GEMM whose epilogue pushes partial tiles to the row owner; owners fold and broadcast the sum."""
+
+    @staticmethod
+    def forward(ctx, x, w, group):
+        from paddle_b200.parallel import symm
+        ctx.save_for_backward(x, w)
+        y = symm.gemm_ar(x.reshape(-1, x.shape[-1]), w, group)
+        return y.reshape(*x.shape[:-1], w.shape[1])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        dy2 = dy.reshape(-1, dy.shape[-1])
+        dx = torch.matmul(dy2, w.t()).reshape(x.shape)
+        dw = torch.matmul(x.reshape(-1, x.shape[-1]).t(), dy2)
+        return dx, dw, None
+
+
+class _FusedColAR(torch.autograd.Function):
+    """ColumnParallelLinear with the dX all-reduce fused into the dX GEMM (K4, transposed weight)."""
+
+    @staticmethod
+    def forward(ctx, x, w, group):
+        ctx.save_for_backward(x, w)
+        ctx.group = group
+        return torch.matmul(x, w)
+
+    @staticmethod
+    def backward(ctx, dy):
+        from paddle_b200.parallel import symm
+        x, w = ctx.saved_tensors
+        dy2 = dy.reshape(-1, dy.shape[-1]).contiguous()
+        dx = symm.gemm_ar(dy2, w, ctx.group, trans_b=True).reshape(x.shape)
+        dw = torch.matmul(x.reshape(-1, x.shape[-1]).t(), dy2)
+        return dx, dw, None
+
+
+def _fused_ar_ok(x, w, group, n_out):
+    """rows divisible by nranks*128, bf16, arena with room for staging + output."""
+    if not (x.is_cuda and x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16):
+        return False
+    from paddle_b200.parallel import symm
+    rows = x.numel() // x.shape[-1]
+    if rows % (group.nranks * 128) != 0:
+        return False
+    if not symm.available(group) or not hasattr(symm.lib.kernels.require(), "pdb200_gemm_bf16_ar"):
+        return False
+    return symm.fused_gemm_ok(group, rows // group.nranks, x.shape[-1], n_out, x.dtype) and \
+        (symm.get_arena(group).free_bytes() > 2 * rows * n_out * 2 + (1 << 20) or
+         any(k[1] == "ar_out" for k in symm._stage))
 
 
 class _AsyncColumnLinear(torch.autograd.Function):
@@ -145,9 +224,14 @@ class ColumnParallelLinear(Layer):
             out = _AsyncColumnLinear.apply(x, self.weight, self.bias, self.model_parallel_group,
                                            self.mp_fused_linear_param_grad_add)
         else:
-            inp = mp_ops._c_identity(x, group=self.model_parallel_group,
-                                     skip_c_identity_dynamic=self.mp_skip_c_identity) if self.is_mp else x
-            out = F.linear(inp, self.weight, self.bias)
+            if self.is_mp and not self.mp_skip_c_identity and x.requires_grad and \
+                    _fused_ar_ok(x, self.weight, self.model_parallel_group, x.shape[-1]):
+                out = _FusedColAR.apply(x, self.weight, self.model_parallel_group)
+                out = out + self.bias if self.bias is not None else out
+            else:
+                inp = mp_ops._c_identity(x, group=self.model_parallel_group,
+                                         skip_c_identity_dynamic=self.mp_skip_c_identity) if self.is_mp else x
+                out = F.linear(inp, self.weight, self.bias)
         if self.gather_output and self.is_mp:
             out = mp_ops._c_concat(out, group=self.model_parallel_group)
         return out
@@ -198,6 +282,9 @@ class RowParallelLinear(Layer):
             out_parallel = F.linear(inp, self.weight, MPScale.apply(self.bias, self.world_size))
             return mp_ops._mp_allreduce(out_parallel, group=self.model_parallel_group,
                                         skip_c_identity_dynamic=self.mp_skip_c_identity)
+        if _fused_ar_ok(inp, self.weight, self.model_parallel_group, self.out_features):
+            out = _FusedRowAR.apply(inp, self.weight, self.model_parallel_group)
+            return out + self.bias if self.bias is not None else out
         out_parallel = F.linear(inp, self.weight)
         out = mp_ops._mp_allreduce(out_parallel, group=self.model_parallel_group,
                                    skip_c_identity_dynamic=self.mp_skip_c_identity)

@@ -192,6 +192,29 @@ class SyncBatchNorm(_BatchNormBase):
         return out
 
 
+def _stats_allreduce(t):
+    """K14: the [2C+1] statistics vector is summed with the one-kernel NVLS all-reduce (K1) on a symmetric scratch
+    when the world group has an arena; NCCL otherwise."""
+    import torch.distributed as tdist
+    if t.is_cuda:
+        from ...distributed import collective as C
+        from ...parallel import symm
+        g = C._get_default_group()
+        if symm.available(g):
+            try:
+                n = (t.numel() + 3) // 4 * 4
+                buf = symm._staging(symm.get_arena(g), "syncbn", (n,), torch.float32)
+                buf[:t.numel()].copy_(t)
+                if n != t.numel():
+                    buf[t.numel():].zero_()
+                symm.allreduce_(buf)
+                return buf[:t.numel()].clone()
+            except Exception:  # noqa: BLE001  (arena could not be created: fall through to NCCL on every rank alike)
+                pass
+    tdist.all_reduce(t)
+    return t
+
+
 class _SyncBNFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, b, rmean, rvar, momentum, eps):
@@ -200,7 +223,7 @@ class _SyncBNFn(torch.autograd.Function):
         n_local = x.numel() // x.shape[1]
         xf = x.float()
         stats = torch.cat([xf.sum(dims), (xf * xf).sum(dims), torch.tensor([float(n_local)], device=x.device)])
-        tdist.all_reduce(stats)
+        stats = _stats_allreduce(stats)
         C = x.shape[1]
         n = stats[-1]
         mean = stats[:C] / n
@@ -226,7 +249,7 @@ class _SyncBNFn(torch.autograd.Function):
         db = dyf.sum(dims)
         dw = (dyf * xhat).sum(dims)
         red = torch.cat([db, dw])
-        tdist.all_reduce(red)
+        red = _stats_allreduce(red)
         mean_dy = (red[:C] / n).reshape(shp)
         mean_dyx = (red[C:] / n).reshape(shp)
         dx = (dyf - mean_dy - xhat * mean_dyx) * (w.float() * rstd).reshape(shp)

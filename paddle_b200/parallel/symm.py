@@ -265,6 +265,64 @@ def gemm_rs(x, weight, group, trans_b=False):
     return out
 
 
+def gemm_ar(x, weight, group, trans_b=False):
+    """K4: ``all_reduce(x @ weight)`` for the non-sequence-parallel TP linears: K6's tile push to the owner of each
+    row block, then every owner folds its rows and stores the sum into all ranks' outputs.  x: [M, K] bf16 with
+    M a multiple of nranks*128; returns a private [M, N] copy."""
+    from paddle_b200.lib import check
+    from paddle_b200.ops._util import ptr
+    arena = get_arena(group)
+    M, K = x.shape
+    n = arena.nranks
+    rows = M // n
+    N = weight.shape[0] if trans_b else weight.shape[1]
+    stage = _staging(arena, "rs_stage", (n, rows, N), torch.bfloat16)
+    out = _staging(arena, "ar_out", (M, N), torch.bfloat16)
+    xc = x.contiguous()
+    e = arena.next_epoch()
+    arena.next_epoch()                       # the entry point uses three consecutive epochs
+    check(lib.kernels.pdb200_gemm_bf16_ar(arena.peers_arg, n, arena.rank, ptr(xc), ptr(weight), stage._symm[1],
+                                          out._symm[1], rows, N, K, int(trans_b), 0, e, stream_ptr(x.device)),
+          "gemm_bf16_ar")
+    return out.clone()
+
+
+def vocab_embed(ids, weight, where):
+    """K7: vocab-parallel embedding forward as a gather from the owner's shard; ``where`` = (arena, offset) of the
+    symmetric storage of ``weight`` (see make_symmetric)."""
+    from paddle_b200.lib import check
+    from paddle_b200.ops._util import ptr
+    arena, off = where
+    ids64 = ids.reshape(-1).to(torch.int64).contiguous()
+    out = torch.empty(ids64.numel(), weight.shape[1], dtype=weight.dtype, device=weight.device)
+    check(lib.kernels.pdb200_nvl_vocab_embed(arena.peers_arg, arena.nranks, arena.rank, off, ptr(ids64), ptr(out),
+                                             ids64.numel(), weight.shape[1], weight.shape[0], dtype_code(weight), 0,
+                                             arena.next_epoch(), stream_ptr(weight.device)), "nvl_vocab_embed")
+    return out.reshape(*ids.shape, weight.shape[1])
+
+
+def make_symmetric(param, group):
+    """Move a parameter's storage into the group's symmetric arena (once); returns False when that is not possible
+    (views into flat buffers, no arena space, fused paths off)."""
+    if getattr(param, "_symm", None) is not None and getattr(param, "_symm_ptr", None) == param.data_ptr():
+        return True
+    if not available(group) or param.data._is_view():
+        return False
+    try:
+        arena = get_arena(group)
+        if arena.free_bytes() < param.numel() * param.element_size() + (1 << 20):
+            return False
+        t = arena.empty(tuple(param.shape), param.dtype)
+    except Exception:  # noqa: BLE001
+        return False
+    with torch.no_grad():
+        t.copy_(param.data)
+        param.data = t
+    param._symm = t._symm
+    param._symm_ptr = t.data_ptr()
+    return True
+
+
 def fused_gemm_ok(group, rows_per_rank, K, N, dtype, weight=None):
     if not (dtype == torch.bfloat16 and rows_per_rank % 128 == 0 and K % 64 == 0 and N % 64 == 0 and available(group)):
         return False

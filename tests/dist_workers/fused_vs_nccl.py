@@ -29,6 +29,66 @@ def data(step, rank, dev):
     return torch.randn(64, H, generator=g).to(dev).bfloat16(), torch.randn(64, H, generator=g).to(dev).bfloat16()
 
 
+if mode in ("tp", "sp"):
+    # K4 / K5 / K6 / K7 / K8 inside the TP and sequence-parallel layers
+    from paddle_b200.distributed.fleet.layers.mpu import mp_layers
+    from paddle_b200.distributed.fleet.utils import sequence_parallel_utils as spu
+    n = dist.ParallelEnv().world_size
+    st = fleet.DistributedStrategy()
+    st.hybrid_configs = {"dp_degree": 1, "mp_degree": n, "pp_degree": 1, "sharding_degree": 1}
+    fleet.init(is_collective=True, strategy=st)
+    r = dist.get_rank()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    V = 1024
+
+    class Block(nn.Layer):
+        def __init__(self):
+            super().__init__()
+            self.emb = mp_layers.VocabParallelEmbedding(V, H)
+            if mode == "tp":
+                self.up = mp_layers.ColumnParallelLinear(H, 4 * H, has_bias=False, gather_output=False)
+                self.down = mp_layers.RowParallelLinear(4 * H, H, has_bias=False, input_is_parallel=True)
+            else:
+                self.up = spu.ColumnSequenceParallelLinear(H, 4 * H, has_bias=False, gather_output=False)
+                self.down = spu.RowSequenceParallelLinear(4 * H, H, has_bias=False, input_is_parallel=True)
+            self.head = mp_layers.ColumnParallelLinear(H, V, has_bias=False, gather_output=False)
+            self.ce = mp_layers.ParallelCrossEntropy()
+
+        def forward(self, ids, labels):
+            h = self.emb(ids)                                  # [b, s, H]
+            if mode == "sp":
+                h = spu.ScatterOp.apply(h.transpose([1, 0, 2]).contiguous())   # [s/n, b, H]
+            h = h + self.down(torch.nn.functional.gelu(self.up(h)))
+            if mode == "sp":
+                h = spu.GatherOp.apply(h).transpose([1, 0, 2])
+            return self.ce(self.head(h), labels).mean()
+
+    paddle.seed(11)
+    paddle.set_default_dtype("bfloat16")
+    with paddle.utils.unique_name.guard():
+        m = Block()
+    paddle.set_default_dtype("float32")
+    opt = paddle.optimizer.AdamW(1e-3, parameters=m.parameters(), multi_precision=True)
+    model = fleet.distributed_model(m)
+    opt = fleet.distributed_optimizer(opt)
+    for s in range(4):
+        gen = torch.Generator().manual_seed(500 + s)
+        ids = torch.randint(0, V, (4, 128), generator=gen).to(dev)
+        labels = torch.randint(0, V, (4, 128, 1), generator=gen).to(dev)
+        loss = model(ids, labels)
+        loss.backward()
+        opt.step()
+        opt.clear_grad()
+    torch.cuda.synchronize()
+    if flag("use_fused_comm"):
+        assert getattr(m.emb.weight, "_symm", None) is not None, "K7 path not taken"
+    torch.save({k: v.detach().float().cpu() for k, v in m.state_dict().items()}, f"{out}.{r}.pt")
+    print(f"fused_vs_nccl {mode} loss={float(loss):.4f} ok", r, flush=True)
+    from paddle_b200.parallel import symm
+    symm.release_all()
+    dist.destroy_process_group()
+    sys.exit(0)
+
 if mode == "dp":
     dist.init_parallel_env()
     r = dist.get_rank()

@@ -104,6 +104,48 @@ for _ in range(2):
 wt = w.t().contiguous()                   # trans_b variants (backward shapes)
 got = symm.ag_gemm(xs, wt, g, trans_b=True)
 torch.testing.assert_close(got.float(), ref, rtol=2e-2, atol=5e-2)
+# ---- K4 GEMM -> all-reduce (RowParallel forward / Column dX) incl. the layers that route through it
+for _ in range(2):
+    got = symm.gemm_ar(xf, w, g)
+    torch.cuda.synchronize()
+    torch.testing.assert_close(got.float(), partial, rtol=2e-2, atol=1e-1)
+got = symm.gemm_ar(xf, wt, g, trans_b=True)
+torch.testing.assert_close(got.float(), partial, rtol=2e-2, atol=1e-1)
+
+# ---- K7 vocab-parallel embedding: gather from the owner's shard == masked lookup + all-reduce
+from paddle_b200.distributed.fleet.layers.mpu import mp_layers
+torch.manual_seed(11)
+Vp, H = 512, 256
+table_full = torch.randn(Vp * n, H, device=dev).bfloat16()
+dist.broadcast(table_full, 0)
+emb = mp_layers.VocabParallelEmbedding(Vp * n, H, mp_group=g)
+emb.to(dtype="bfloat16")
+with torch.no_grad():
+    emb.weight.copy_(table_full[r * Vp:(r + 1) * Vp])
+ids = torch.randint(0, Vp * n, (4, 33), device=dev)
+dist.broadcast(ids, 0)
+out = emb(ids)
+assert getattr(emb.weight, "_symm", None) is not None, "K7 path was not taken"
+torch.testing.assert_close(out, table_full[ids], rtol=0, atol=0)
+gout = torch.randn_like(out)
+dist.broadcast(gout, 0)
+out.backward(gout)
+ref_dw = torch.zeros(Vp * n, H, device=dev)
+ref_dw.index_add_(0, ids.reshape(-1), gout.reshape(-1, H).float())
+torch.testing.assert_close(emb.weight.grad.float(), ref_dw[r * Vp:(r + 1) * Vp], rtol=2e-2, atol=2e-2)
+
+# ---- K14 SyncBatchNorm statistics through the NVLS all-reduce
+torch.manual_seed(20 + r)
+bn = paddle.nn.SyncBatchNorm(24).to(dev)
+xb = torch.randn(6, 24, 5, 5, device=dev, requires_grad=True)
+yb = bn(xb)
+allx = []
+dist.all_gather(allx, xb.detach())
+allx = torch.cat(allx, 0)
+ref_bn = torch.nn.functional.batch_norm(allx, None, None, bn.weight.detach(), bn.bias.detach(), True, 0.1, 1e-5)
+torch.testing.assert_close(yb.detach(), ref_bn[r * 6:(r + 1) * 6], rtol=1e-4, atol=1e-4)
+yb.square().sum().backward()
+assert torch.isfinite(xb.grad).all()
 print("nvl_fused ok", r, flush=True)
 symm.release_all()
 dist.destroy_process_group()
