@@ -3,14 +3,20 @@
 // Replaces in the reference: paddle/phi/kernels/gpu/flash_attn_kernel.cu:305-447 -> vendored FlashAttention-2
 // (mma.sync m16n8k16 + cp.async, third_party/flashattn/csrc/flash_attn/src/flash_fwd_kernel.h).
 //
-// One CTA per (batch, q-head, 128-row query tile); K/V tiles of 128 keys stream through a 2-stage TMA ring.
-//   warp 0    TMA producer   Q once, then K_j / V_j (128-B swizzled boxes)
-//   warp 1    MMA issuer     S_j = Q K_j^T into TMEM (double-buffered, so S_{j+1} is computed while the softmax of
-//                            tile j runs), then O_j = P_j V_j into TMEM once P_j is in shared memory
-//   warp 2    TMEM allocator (2 x 128 columns for S, D columns for O_j)
-//   warps 4-7 softmax        one query row per thread: tcgen05.ld the score row, online max / exp2 / row sum in fp32,
-//                            write P_j (bf16) into shared memory in the UMMA K-major swizzled layout, fold the previous
-//                            tile's O_{j-1} from TMEM into the fp32 register accumulator with the running rescale
+// One CTA per (batch, q-head, 128-row query tile); K and V tiles of 128 keys stream through separate 2-stage TMA rings.
+// The softmax is the bottleneck on this machine (one exp2 per score on 16 SFU lanes/clk/SM costs as many cycles as the
+// two 128x128x128 MMAs of a tile), so the CTA runs TWO independent softmax pipelines:
+//   warp 0      TMA producer for Q and the K ring            warp 3   TMA producer for the V ring
+//   warp 1      MMA issuer: S_j = Q K_j^T into TMEM buffer (j & 1); O_(j&1) += P_j V_j once P_j is in shared memory
+//   warp 2      TMEM allocator (S_A | S_B | O_A | O_B = 512 columns)
+//   warps 4-7   softmax group A: even key tiles            warps 8-11   softmax group B: odd key tiles
+// Each group keeps its own running (max, sum) and its own output accumulator IN TMEM (the MMA accumulates across the
+// group's tiles), so the groups never wait for each other; the two partial results are merged once at the end
+// (the split-KV combination, inside the CTA).  A group thread owns one query row: a single tcgen05.ld pass brings the
+// 128 scores into registers (the S buffer is handed back to the MMA warp immediately), then max / exp2 / row sum /
+// bf16 pack, and P is written to shared memory in the UMMA K-major swizzled layout.  The accumulator is rescaled
+// lazily: only when a row's maximum grew by more than 2^8 since the last rescale does the warp read-modify-write its
+// O rows in TMEM (exact: P and the row sum use the same stale maximum until then).
 // K_j and V_j share one TMA box geometry ([keys][64 d-columns]); the descriptor reads the same bytes K-major for
 // Q K^T and MN-major for P V, so V needs no transpose.
 // Outputs: O [b, sq, hq, d] bf16 and LSE [b, hq, sq] fp32 (natural log), the contract of the backward kernels.
@@ -23,14 +29,14 @@ using namespace pdb::tc;
 
 constexpr int BQ = 128;     // query rows per CTA
 constexpr int BKV = 128;    // keys per tile
-constexpr int kThreads = 256;
+constexpr int kThreads = 384;
+constexpr float kRescaleThreshold = 8.f;   // log2 units
 
 template <int D> struct FwdSmem {
   static constexpr int kQBytes = BQ * D * 2;
   static constexpr int kKVBytes = BKV * D * 2;            // one of K or V
   static constexpr int kPBytes = BQ * BKV * 2;
-  static constexpr int kStages = 2;
-  static constexpr int kTotal = kQBytes + kStages * 2 * kKVBytes + kPBytes + 1024 + 256;
+  static constexpr int kTotal = kQBytes + 4 * kKVBytes + 2 * kPBytes + 1024 + 256;
 };
 
 struct FwdParams {
@@ -51,17 +57,20 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sQ = smem;
-  uint8_t* sKV = sQ + S::kQBytes;            // stage s: K at sKV + s*2*kKVBytes, V right after it
-  uint8_t* sP = sKV + S::kStages * 2 * S::kKVBytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + S::kPBytes);
+  uint8_t* sK = sQ + S::kQBytes;             // [2] stages
+  uint8_t* sV = sK + 2 * S::kKVBytes;        // [2] stages
+  uint8_t* sP = sV + 2 * S::kKVBytes;        // [2] one per softmax group
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * S::kPBytes);
   uint64_t* q_full = bars;
-  uint64_t* kv_full = bars + 1;              // [2]
-  uint64_t* kv_empty = bars + 3;             // [2]
-  uint64_t* s_full = bars + 5;               // [2]
-  uint64_t* s_empty = bars + 7;              // [2]
-  uint64_t* p_ready = bars + 9;
-  uint64_t* o_full = bars + 10;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 11);
+  uint64_t* k_full = bars + 1;               // [2]
+  uint64_t* k_empty = bars + 3;              // [2]
+  uint64_t* v_full = bars + 5;               // [2]
+  uint64_t* v_empty = bars + 7;              // [2]
+  uint64_t* s_full = bars + 9;               // [2]
+  uint64_t* s_empty = bars + 11;             // [2]
+  uint64_t* p_ready = bars + 13;             // [2]
+  uint64_t* o_full = bars + 15;              // [2]
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 17);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // heavy (late) causal tiles first so the tail of the grid is made of short CTAs
@@ -82,22 +91,24 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
   if (warp == 1 && lane == 0) {
     mbar_init(q_full, 1);
     for (int i = 0; i < 2; ++i) {
-      mbar_init(&kv_full[i], 1);
-      mbar_init(&kv_empty[i], 1);
+      mbar_init(&k_full[i], 1);
+      mbar_init(&k_empty[i], 1);
+      mbar_init(&v_full[i], 1);
+      mbar_init(&v_empty[i], 1);
       mbar_init(&s_full[i], 1);
       mbar_init(&s_empty[i], 4);
+      mbar_init(&p_ready[i], 4);
+      mbar_init(&o_full[i], 1);
     }
-    mbar_init(p_ready, 4);
-    mbar_init(o_full, 1);
     fence_barrier_init();
   }
-  constexpr int kTmemCols = 512;             // S0 | S1 | O  (2*128 + D, rounded to a power of two)
+  constexpr int kTmemCols = 512;             // S_A | S_B | O_A | O_B
   if (warp == 2) tmem_alloc(tmem_ptr_smem, kTmemCols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
-  const uint32_t tmem_o = tmem_base + 2 * BKV;
+  const uint32_t tmem_o = tmem_base + 2 * BKV;           // group g: tmem_o + g * D
 
   if (warp == 0) {
     if (lane == 0) {
@@ -106,166 +117,208 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
       for (int kb = 0; kb < KB; ++kb) tma_load_2d(sQ + kb * (BQ * 128), &tm_q, q_full, h * D + kb * 64, q_row0);
       for (int j = 0; j < n_kv; ++j) {
         const int st = j & 1;
-        mbar_wait(&kv_empty[st], ((j >> 1) & 1) ^ 1);
-        uint8_t* sK = sKV + st * 2 * S::kKVBytes;
-        uint8_t* sV = sK + S::kKVBytes;
-        mbar_expect_tx(&kv_full[st], 2 * S::kKVBytes);
+        mbar_wait(&k_empty[st], ((j >> 1) & 1) ^ 1);
+        mbar_expect_tx(&k_full[st], S::kKVBytes);
 #pragma unroll
-        for (int kb = 0; kb < KB; ++kb) {
-          tma_load_2d(sK + kb * (BKV * 128), &tm_k, &kv_full[st], hk * D + kb * 64, kv_row0 + j * BKV);
-          tma_load_2d(sV + kb * (BKV * 128), &tm_v, &kv_full[st], hk * D + kb * 64, kv_row0 + j * BKV);
-        }
+        for (int kb = 0; kb < KB; ++kb)
+          tma_load_2d(sK + st * S::kKVBytes + kb * (BKV * 128), &tm_k, &k_full[st], hk * D + kb * 64, kv_row0 + j * BKV);
+      }
+    }
+  } else if (warp == 3) {
+    if (lane == 0) {
+      for (int j = 0; j < n_kv; ++j) {
+        const int st = j & 1;
+        mbar_wait(&v_empty[st], ((j >> 1) & 1) ^ 1);
+        mbar_expect_tx(&v_full[st], S::kKVBytes);
+#pragma unroll
+        for (int kb = 0; kb < KB; ++kb)
+          tma_load_2d(sV + st * S::kKVBytes + kb * (BKV * 128), &tm_v, &v_full[st], hk * D + kb * 64, kv_row0 + j * BKV);
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
       constexpr uint32_t idesc_s = make_idesc_bf16(BQ, BKV, 0, 0);     // Q (K-major) x K (K-major)
       constexpr uint32_t idesc_o = make_idesc_bf16(BQ, D, 0, 1);       // P (K-major) x V (MN-major)
-      auto issue_pv = [&](int j) {
-        const uint32_t sV = smem_u32(sKV + (j & 1) * 2 * S::kKVBytes + S::kKVBytes);
-        const uint32_t sp = smem_u32(sP);
+      auto issue_pv = [&](int t) {
+        const int g = t & 1, ph = (t >> 1) & 1;
+        mbar_wait(&v_full[g], ph);
+        mbar_wait(&p_ready[g], ph);
+        tc_fence_after();
+        const uint32_t sv = smem_u32(sV + g * S::kKVBytes);
+        const uint32_t sp = smem_u32(sP + g * S::kPBytes);
 #pragma unroll
         for (int k = 0; k < BKV / 16; ++k) {
           const uint64_t da = make_smem_desc(sp + (k >> 2) * (BQ * 128) + (k & 3) * 32, 16, 1024);
-          const uint64_t db = make_smem_desc(sV + k * 2048, BKV * 128, 1024);
-          umma_f16(tmem_o, da, db, idesc_o, k != 0 ? 1u : 0u);
+          const uint64_t db = make_smem_desc(sv + k * 2048, BKV * 128, 1024);
+          umma_f16(tmem_o + g * D, da, db, idesc_o, (k != 0 || t >= 2) ? 1u : 0u);
         }
-        umma_commit(o_full);
-        umma_commit(&kv_empty[j & 1]);
+        umma_commit(&o_full[g]);
+        umma_commit(&v_empty[g]);
       };
-      mbar_wait(q_full, 0);
-      for (int j = 0; j < n_kv; ++j) {
-        const int st = j & 1;
-        mbar_wait(&kv_full[st], (j >> 1) & 1);
-        mbar_wait(&s_empty[st], ((j >> 1) & 1) ^ 1);
+      auto issue_qk = [&](int j) {
+        const int g = j & 1, ph = (j >> 1) & 1;
+        mbar_wait(&k_full[g], ph);
+        mbar_wait(&s_empty[g], ph ^ 1);
         tc_fence_after();
         const uint32_t sq_ = smem_u32(sQ);
-        const uint32_t sK = smem_u32(sKV + st * 2 * S::kKVBytes);
+        const uint32_t sk_ = smem_u32(sK + g * S::kKVBytes);
 #pragma unroll
         for (int k = 0; k < D / 16; ++k) {
           const uint64_t da = make_smem_desc(sq_ + (k >> 2) * (BQ * 128) + (k & 3) * 32, 16, 1024);
-          const uint64_t db = make_smem_desc(sK + (k >> 2) * (BKV * 128) + (k & 3) * 32, 16, 1024);
-          umma_f16(tmem_base + st * BKV, da, db, idesc_s, k != 0 ? 1u : 0u);
+          const uint64_t db = make_smem_desc(sk_ + (k >> 2) * (BKV * 128) + (k & 3) * 32, 16, 1024);
+          umma_f16(tmem_base + g * BKV, da, db, idesc_s, k != 0 ? 1u : 0u);
         }
-        umma_commit(&s_full[st]);
-        if (j >= 1) {
-          mbar_wait(p_ready, (j - 1) & 1);
-          tc_fence_after();
-          issue_pv(j - 1);
-        }
+        umma_commit(&s_full[g]);
+        umma_commit(&k_empty[g]);
+      };
+      mbar_wait(q_full, 0);
+      // scores run two tiles ahead of the P V products: a group finds its next S ready when it finishes a tile
+      issue_qk(0);
+      if (n_kv > 1) issue_qk(1);
+      for (int j = 2; j < n_kv; ++j) {
+        issue_qk(j);
+        issue_pv(j - 2);
       }
-      mbar_wait(p_ready, (n_kv - 1) & 1);
-      tc_fence_after();
+      if (n_kv > 1) issue_pv(n_kv - 2);
       issue_pv(n_kv - 1);
     }
   } else if (warp >= 4) {
-    const int q = warp & 3;
+    const int g = (warp - 4) >> 2;                          // softmax group: 0 = even tiles, 1 = odd tiles
+    const int q = warp & 3;                                 // TMEM lane quarter this warp may touch
     const int row = q * 32 + lane;                          // row inside the tile
     const int q_idx = qt * BQ + row;                        // query position in the sequence
     const uint32_t lane_off = (uint32_t)(q * 32) << 16;
-    float o_acc[D];
-#pragma unroll
-    for (int i = 0; i < D; ++i) o_acc[i] = 0.f;
-    float m_run = -INFINITY, l_run = 0.f, alpha_prev = 1.f;
-    auto fold_o = [&](int jprev, float alpha) {
-      // O_acc = O_acc * alpha + O_jprev   (alpha rescales everything accumulated BEFORE tile jprev)
-      mbar_wait(o_full, jprev & 1);
+    const uint32_t ts = tmem_base + g * BKV + lane_off;
+    const uint32_t to = tmem_o + g * D + lane_off;
+    uint8_t* sPg = sP + g * S::kPBytes;
+    float m_used = -INFINITY, l_run = 0.f;
+    int it = 0;
+    for (int j = g; j < n_kv; j += 2, ++it) {
+      mbar_wait(&s_full[g], it & 1);
       tc_fence_after();
+      uint32_t r[BKV];
 #pragma unroll
-      for (int c = 0; c < D / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32(tmem_o + lane_off + c * 32, r);
-        tmem_ld_wait();
+      for (int c = 0; c < BKV / 32; ++c) tmem_ld_32x32(ts + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&r[c * 32]));
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&s_empty[g]);             // scores are in registers: the MMA warp may refill the buffer
+      if (p.causal && (j * BKV + BKV - 1 > qt * BQ + diag)) {   // tile crosses the diagonal for some row
+        const int lim = q_idx + diag - j * BKV;                 // keys with local index > lim are masked
 #pragma unroll
-        for (int i = 0; i < 32; ++i) o_acc[c * 32 + i] = o_acc[c * 32 + i] * alpha + __uint_as_float(r[i]);
+        for (int i = 0; i < BKV; ++i)
+          if (i > lim) r[i] = 0xff800000u;                      // -inf
       }
-    };
-    for (int j = 0; j < n_kv; ++j) {
-      const int st = j & 1;
-      const uint32_t ts = tmem_base + st * BKV + lane_off;
-      mbar_wait(&s_full[st], (j >> 1) & 1);
-      tc_fence_after();
-      const bool need_mask = p.causal && (j * BKV + BKV - 1 > qt * BQ + diag);   // tile crosses the diagonal for some row
-      // ---- pass 1: row max
-      float m_tile = -INFINITY;
+      float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-      for (int c = 0; c < BKV / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32(ts + c * 32, r);
-        tmem_ld_wait();
+      for (int i = 0; i < BKV; i += 4) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float s = __uint_as_float(r[i]);
-          if (need_mask && (j * BKV + c * 32 + i > q_idx + diag)) s = -INFINITY;
-          m_tile = fmaxf(m_tile, s);
+        for (int u = 0; u < 4; ++u) mx[u] = fmaxf(mx[u], __uint_as_float(r[i + u]));
+      }
+      const float m_tile = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+      if (it == 0) {
+        m_used = (m_tile == -INFINITY) ? 0.f : m_tile;
+      } else {
+        // the previous P V of this group must be done before P is overwritten or O is touched
+        mbar_wait(&o_full[g], (it - 1) & 1);
+        tc_fence_after();
+        const bool grow = (m_tile - m_used) * p.scale_log2 > kRescaleThreshold;
+        if (__any_sync(0xffffffffu, grow)) {
+          const float m_new = fmaxf(m_used, m_tile);
+          const float alpha = ex2_approx((m_used - m_new) * p.scale_log2);
+#pragma unroll
+          for (int c = 0; c < D / 32; ++c) {
+            uint32_t o[32];
+            tmem_ld_32x32(to + c * 32, o);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            tmem_st_32x32(to + c * 32, o);
+          }
+          tmem_st_wait();
+          l_run *= alpha;
+          m_used = m_new;
         }
       }
-      const float m_new = fmaxf(m_run, m_tile);
-      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
-      const float alpha = exp2f((m_run - m_use) * p.scale_log2);      // m_run = -inf -> 0
-      // ---- previous tile's P V product joins the accumulator (P buffer becomes free)
-      if (j >= 1) fold_o(j - 1, alpha_prev);
-      // ---- pass 2: probabilities -> shared memory (UMMA K-major, 128-byte swizzle), row sum
-      float l_tile = 0.f;
-      const float mb = m_use * p.scale_log2;
+      // probabilities -> shared memory (UMMA K-major, 128-byte swizzle) + row sum
+      const float mb = m_used * p.scale_log2;
+      float ls[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int c = 0; c < BKV / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32(ts + c * 32, r);
-        tmem_ld_wait();
         uint32_t pk[16];
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
-          float s0 = __uint_as_float(r[i]), s1 = __uint_as_float(r[i + 1]);
-          float p0 = exp2f(s0 * p.scale_log2 - mb), p1 = exp2f(s1 * p.scale_log2 - mb);
-          if (need_mask) {
-            if (j * BKV + c * 32 + i > q_idx + diag) p0 = 0.f;
-            if (j * BKV + c * 32 + i + 1 > q_idx + diag) p1 = 0.f;
-          }
-          l_tile += p0 + p1;
+          const float p0 = ex2_approx(fmaf(__uint_as_float(r[c * 32 + i]), p.scale_log2, -mb));
+          const float p1 = ex2_approx(fmaf(__uint_as_float(r[c * 32 + i + 1]), p.scale_log2, -mb));
+          ls[(i >> 1) & 3] += p0 + p1;
           __nv_bfloat162 h2 = __floats2bfloat162_rn(p0, p1);
           pk[i >> 1] = *reinterpret_cast<uint32_t*>(&h2);
         }
         // 32 keys = 4 chunks of 16 B inside k-block (c / 2), chunk index ((c & 1) * 4 + t), XOR-swizzled by row % 8
-        uint8_t* base = sP + (c >> 1) * (BQ * 128) + row * 128;
+        uint8_t* base = sPg + (c >> 1) * (BQ * 128) + row * 128;
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
           const int chunk = ((c & 1) * 4 + t) ^ (row & 7);
           *reinterpret_cast<uint4*>(base + chunk * 16) = make_uint4(pk[t * 4], pk[t * 4 + 1], pk[t * 4 + 2], pk[t * 4 + 3]);
         }
       }
-      l_run = l_run * alpha + l_tile;
-      m_run = m_new;
-      alpha_prev = alpha;
-      // hand the score buffer back and publish P to the tensor core (async proxy)
+      l_run += (ls[0] + ls[1]) + (ls[2] + ls[3]);
+      // publish P (generic-proxy writes -> async proxy) and any TMEM rescale to the MMA warp
       tc_fence_before();
       fence_proxy_async();
       __syncwarp();
-      if (lane == 0) {
-        mbar_arrive(&s_empty[st]);
-        mbar_arrive(p_ready);
-      }
-      // alpha rescales what was accumulated before tile j; it is applied when O_j is folded (next iteration)
+      if (lane == 0) mbar_arrive(&p_ready[g]);
     }
-    // last tile
-    fold_o(n_kv - 1, alpha_prev);
-    const float inv_l = l_run > 0.f ? 1.f / l_run : 0.f;
-    __nv_bfloat16* orow = p.o + ((int64_t)(b * p.sq + q_idx) * p.hq + h) * D;
+    // ---- merge the two groups' partial results ------------------------------------------------------------
+    if (it > 0) {
+      mbar_wait(&o_full[g], (it - 1) & 1);
+      tc_fence_after();
+    }
+    float* stats = reinterpret_cast<float*>(sP);           // P buffers are free now: [group][row][2]
+    // group B may still be reading... no: each group only touches its own P buffer; the stats live in group A's
+    // buffer, which group A's last P V (awaited above by group A) has finished reading before A writes here, and B
+    // writes only after the named barrier below orders it behind A's wait.
+    named_bar_sync(1, 256);
+    stats[(g * BQ + row) * 2] = (it > 0) ? m_used : -INFINITY;
+    stats[(g * BQ + row) * 2 + 1] = l_run;
+    tc_fence_before();
+    named_bar_sync(1, 256);
+    tc_fence_after();
+    const float m_a = stats[row * 2], l_a = stats[row * 2 + 1];
+    const float m_b = stats[(BQ + row) * 2], l_b = stats[(BQ + row) * 2 + 1];
+    const bool has_b = n_kv > 1;
+    const float m_fin = fmaxf(m_a, m_b);                    // group A always has tile 0, so m_a is finite
+    const float f_a = ex2_approx((m_a - m_fin) * p.scale_log2);
+    const float f_b = has_b ? ex2_approx((m_b - m_fin) * p.scale_log2) : 0.f;
+    const float l_fin = l_a * f_a + l_b * f_b;
+    const float inv_l = l_fin > 0.f ? 1.f / l_fin : 0.f;
+    const float w_a = f_a * inv_l, w_b = f_b * inv_l;
+    // group g writes columns [g * D/2, (g+1) * D/2) of the row
+    __nv_bfloat16* orow = p.o + ((int64_t)(b * p.sq + q_idx) * p.hq + h) * D + g * (D / 2);
 #pragma unroll
-    for (int i = 0; i < D; i += 8) {
-      uint4 v;
-      __nv_bfloat162 a0 = __floats2bfloat162_rn(o_acc[i] * inv_l, o_acc[i + 1] * inv_l);
-      __nv_bfloat162 a1 = __floats2bfloat162_rn(o_acc[i + 2] * inv_l, o_acc[i + 3] * inv_l);
-      __nv_bfloat162 a2 = __floats2bfloat162_rn(o_acc[i + 4] * inv_l, o_acc[i + 5] * inv_l);
-      __nv_bfloat162 a3 = __floats2bfloat162_rn(o_acc[i + 6] * inv_l, o_acc[i + 7] * inv_l);
-      v.x = *reinterpret_cast<uint32_t*>(&a0); v.y = *reinterpret_cast<uint32_t*>(&a1);
-      v.z = *reinterpret_cast<uint32_t*>(&a2); v.w = *reinterpret_cast<uint32_t*>(&a3);
-      *reinterpret_cast<uint4*>(orow + i) = v;
+    for (int c = 0; c < D / 64; ++c) {
+      uint32_t oa[32], ob[32];
+      tmem_ld_32x32(tmem_o + lane_off + g * (D / 2) + c * 32, oa);
+      if (has_b) tmem_ld_32x32(tmem_o + D + lane_off + g * (D / 2) + c * 32, ob);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; i += 8) {
+        float v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          v[u] = __uint_as_float(oa[i + u]) * w_a;
+          if (has_b) v[u] = fmaf(__uint_as_float(ob[i + u]), w_b, v[u]);
+        }
+        uint4 pk;
+        __nv_bfloat162 a0 = __floats2bfloat162_rn(v[0], v[1]), a1 = __floats2bfloat162_rn(v[2], v[3]);
+        __nv_bfloat162 a2 = __floats2bfloat162_rn(v[4], v[5]), a3 = __floats2bfloat162_rn(v[6], v[7]);
+        pk.x = *reinterpret_cast<uint32_t*>(&a0); pk.y = *reinterpret_cast<uint32_t*>(&a1);
+        pk.z = *reinterpret_cast<uint32_t*>(&a2); pk.w = *reinterpret_cast<uint32_t*>(&a3);
+        *reinterpret_cast<uint4*>(orow + c * 32 + i) = pk;
+      }
     }
-    if (p.lse) {
-      const float m_fin = (m_run == -INFINITY) ? 0.f : m_run;
-      p.lse[((int64_t)b * p.hq + h) * p.sq + q_idx] = m_fin * p.scale + __logf(fmaxf(l_run, 1e-37f));
-    }
+    if (g == 0 && p.lse)
+      p.lse[((int64_t)b * p.hq + h) * p.sq + q_idx] = m_fin * p.scale + __logf(fmaxf(l_fin, 1e-37f));
   }
 
   tc_fence_before();
