@@ -28,7 +28,17 @@ for (b, s, h, d) in [(1, 4096, 32, 128), (2, 4096, 32, 128), (4, 2048, 32, 128),
     flags.set_flags({"use_native_kernels": False})
     t_l = timeit(lambda: ops.flash_attention(q, k, v, causal=True))
     flags.set_flags({"use_native_kernels": True})
+    # backward only (forward graph built once, grads recomputed each call); 2.5x the forward FLOPs
+    def bwd_timer(native):
+        flags.set_flags({"use_native_kernels": native})
+        qq, kk, vv = (t.detach().requires_grad_(True) for t in (q, k, v))
+        out = ops.flash_attention(qq, kk, vv, causal=True)
+        g = torch.randn_like(out)
+        return timeit(lambda: torch.autograd.grad(out, (qq, kk, vv), g, retain_graph=True))
+    tb_o, tb_l = bwd_timer(True), bwd_timer(False)
+    flags.set_flags({"use_native_kernels": True})
     rows.append(dict(shape=[b, s, h, d], ours_ms=round(t_o, 4), lib_ms=round(t_l, 4), ours_tflops=round(fl / t_o / 1e9, 1),
-                     lib_tflops=round(fl / t_l / 1e9, 1)))
+                     lib_tflops=round(fl / t_l / 1e9, 1), bwd_ours_ms=round(tb_o, 4), bwd_lib_ms=round(tb_l, 4),
+                     bwd_ours_tflops=round(2.5 * fl / tb_o / 1e9, 1), bwd_lib_tflops=round(2.5 * fl / tb_l / 1e9, 1)))
     print(rows[-1], flush=True)
 json.dump(rows, open(os.path.join(os.path.dirname(__file__), "..", "gpurun_out", "attn_bench.json"), "w"), indent=1)

@@ -1,0 +1,600 @@
+// K17: flash-attention backward on tcgen05 tensor cores for sm_100a (bf16, head_dim 64/128, causal or full, GQA).
+//
+// Replaces in the reference: paddle/phi/kernels/gpu/flash_attn_grad_kernel.cu -> vendored FlashAttention-2 backward
+// (mma.sync, one kernel, fp32 atomic adds for dQ).  Here the work is split so that nothing needs atomics or an fp32
+// dQ buffer and every result is deterministic:
+//   delta_kernel          Delta[b,h,q] = sum_d dO * O                                  (memory-bound pre-pass)
+//   flash_bwd_dq_kernel   one CTA per 128-row query tile, loops over key tiles:   S = Q K^T, dP = dO V^T on the tensor
+//                         core, dS = P o (dP - Delta) * scale in registers, dQ += dS K accumulated in TMEM
+//   flash_bwd_dkv_kernel  one CTA per 128-key tile, loops over the group's query heads x 64-row query tiles, with the
+//                         TRANSPOSED products S^T = K Q^T and dP^T = V dO^T so that P^T and dS^T come out of TMEM with
+//                         keys on the lanes, ready to be the A operand of dV += P^T dO and dK += dS^T Q (both in TMEM).
+//                         GQA needs no reduction across heads: the group's heads are just more loop iterations.
+// The probabilities are recomputed from the forward's LSE (P = exp2(S*scale*log2e - LSE*log2e)); no running max, no
+// rescale, so the score columns of a tile can be split between two softmax warpgroups without any exchange.
+// Warp roles in both kernels: 0 and 3 TMA producers, 1 MMA issuer, 2 TMEM allocator, 4-11 the element-wise stage
+// (lane quarter = warp % 4, column half = (warp - 4) / 4).  Scores are pulled into registers with one tcgen05.ld pass
+// and the TMEM buffers are handed back immediately, so the next tile's MMAs overlap this tile's exponentials.
+#include "common.cuh"
+#include "tc.cuh"
+
+namespace pdb {
+namespace fab {
+using namespace pdb::tc;
+
+constexpr int kThreads = 384;
+constexpr float kLog2e = 1.4426950408889634f;
+
+struct BwdParams {
+  int sq, sk, hq, hk;
+  float scale_log2, scale;
+  int causal;
+  const float* lse;      // [b, hq, sq]
+  const float* delta;    // [b, hq, sq]
+  __nv_bfloat16* dq;     // [b, sq, hq, D]
+  __nv_bfloat16* dk;     // [b, sk, hk, D]
+  __nv_bfloat16* dv;
+};
+
+// ---------------------------------------------------------------------------------------------- Delta
+template <int D>
+__global__ void __launch_bounds__(256) delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
+                                                   float* __restrict__ delta, int sq, int hq, int64_t rows) {
+  constexpr int E = D / 32;                               // elements per lane
+  const int lane = threadIdx.x & 31;
+  const int64_t r = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);     // row of the [b*sq*hq, D] view
+  if (r >= rows) return;
+  const __nv_bfloat16* po = o + r * D + lane * E;
+  const __nv_bfloat16* pd = d_o + r * D + lane * E;
+  float acc = 0.f;
+  if constexpr (E == 4) {
+    const uint2 a = *reinterpret_cast<const uint2*>(po), c = *reinterpret_cast<const uint2*>(pd);
+    const __nv_bfloat162* a2 = reinterpret_cast<const __nv_bfloat162*>(&a);
+    const __nv_bfloat162* c2 = reinterpret_cast<const __nv_bfloat162*>(&c);
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const float2 x = __bfloat1622float2(a2[i]), y = __bfloat1622float2(c2[i]);
+      acc += x.x * y.x + x.y * y.y;
+    }
+  } else {
+    const float2 x = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(po));
+    const float2 y = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(pd));
+    acc = x.x * y.x + x.y * y.y;
+  }
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
+  if (lane == 0) {
+    const int64_t bs = r / hq;                            // b * sq + s
+    const int h = (int)(r - bs * hq);
+    const int64_t bb = bs / sq;
+    const int s = (int)(bs - bb * sq);
+    delta[(bb * hq + h) * sq + s] = acc;
+  }
+}
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+  __nv_bfloat162 h2 = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h2);
+}
+
+// ---------------------------------------------------------------------------------------------- dQ
+template <int D> struct DqSmem {
+  static constexpr int kTile = 128 * D * 2;               // Q, dO, one K or V stage
+  static constexpr int kDS = 128 * 128 * 2;
+  static constexpr int kTotal = 6 * kTile + kDS + 1024 + 256;
+};
+
+template <int D>
+__global__ void __launch_bounds__(kThreads, 1)
+flash_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_do,
+                    const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_v,
+                    const BwdParams p) {
+  using S = DqSmem<D>;
+  constexpr int KB = D / 64;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sDO = sQ + S::kTile;
+  uint8_t* sK = sDO + S::kTile;              // [2]
+  uint8_t* sV = sK + 2 * S::kTile;           // [2]
+  uint8_t* sDS = sV + 2 * S::kTile;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sDS + S::kDS);
+  uint64_t* qdo_full = bars;
+  uint64_t* k_full = bars + 1;               // [2]
+  uint64_t* k_empty = bars + 3;              // [2]
+  uint64_t* v_full = bars + 5;               // [2]
+  uint64_t* v_empty = bars + 7;              // [2]
+  uint64_t* sdp_full = bars + 9;
+  uint64_t* sdp_empty = bars + 10;
+  uint64_t* ds_ready = bars + 11;
+  uint64_t* dq_done = bars + 12;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 13);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_qt = p.sq / 128;
+  const int qt = p.causal ? (n_qt - 1 - (int)blockIdx.x) : (int)blockIdx.x;
+  const int h = blockIdx.y, b = blockIdx.z;
+  const int hk = h / (p.hq / p.hk);
+  const int q_row0 = b * p.sq + qt * 128;
+  const int kv_row0 = b * p.sk;
+  const int diag = p.sk - p.sq;
+  const int n_kv = p.causal ? min((qt * 128 + 128 + diag + 127) / 128, p.sk / 128) : p.sk / 128;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tm_q);
+    prefetch_tmap(&tm_do);
+    prefetch_tmap(&tm_k);
+    prefetch_tmap(&tm_v);
+  }
+  if (warp == 1 && lane == 0) {
+    mbar_init(qdo_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&k_full[i], 1);
+      mbar_init(&k_empty[i], 1);
+      mbar_init(&v_full[i], 1);
+      mbar_init(&v_empty[i], 1);
+    }
+    mbar_init(sdp_full, 1);
+    mbar_init(sdp_empty, 8);
+    mbar_init(ds_ready, 8);
+    mbar_init(dq_done, 1);
+    fence_barrier_init();
+  }
+  constexpr int kTmemCols = 512;             // S | dP | dQ
+  if (warp == 2) tmem_alloc(tmem_ptr_smem, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_s = *tmem_ptr_smem;
+  const uint32_t tmem_dp = tmem_s + 128;
+  const uint32_t tmem_dq = tmem_s + 256;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(qdo_full, 2 * S::kTile);
+#pragma unroll
+      for (int kb = 0; kb < KB; ++kb) {
+        tma_load_2d(sQ + kb * (128 * 128), &tm_q, qdo_full, h * D + kb * 64, q_row0);
+        tma_load_2d(sDO + kb * (128 * 128), &tm_do, qdo_full, h * D + kb * 64, q_row0);
+      }
+      for (int j = 0; j < n_kv; ++j) {
+        const int st = j & 1;
+        mbar_wait(&k_empty[st], ((j >> 1) & 1) ^ 1);
+        mbar_expect_tx(&k_full[st], S::kTile);
+#pragma unroll
+        for (int kb = 0; kb < KB; ++kb)
+          tma_load_2d(sK + st * S::kTile + kb * (128 * 128), &tm_k, &k_full[st], hk * D + kb * 64, kv_row0 + j * 128);
+      }
+    }
+  } else if (warp == 3) {
+    if (lane == 0) {
+      for (int j = 0; j < n_kv; ++j) {
+        const int st = j & 1;
+        mbar_wait(&v_empty[st], ((j >> 1) & 1) ^ 1);
+        mbar_expect_tx(&v_full[st], S::kTile);
+#pragma unroll
+        for (int kb = 0; kb < KB; ++kb)
+          tma_load_2d(sV + st * S::kTile + kb * (128 * 128), &tm_v, &v_full[st], hk * D + kb * 64, kv_row0 + j * 128);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc_s = make_idesc_bf16(128, 128, 0, 0);    // [q][d] x [keys][d]^T
+      constexpr uint32_t idesc_dq = make_idesc_bf16(128, D, 0, 1);     // dS [q][keys] x K [keys][d] (MN-major)
+      auto issue_sdp = [&](int j) {
+        const int st = j & 1, ph = (j >> 1) & 1;
+        mbar_wait(&k_full[st], ph);
+        mbar_wait(&v_full[st], ph);
+        mbar_wait(sdp_empty, (j & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t aq = smem_u32(sQ), ad = smem_u32(sDO);
+        const uint32_t bk = smem_u32(sK + st * S::kTile), bv = smem_u32(sV + st * S::kTile);
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k) {
+          const uint32_t off = (k >> 2) * (128 * 128) + (k & 3) * 32;
+          umma_f16(tmem_s, make_smem_desc(aq + off, 16, 1024), make_smem_desc(bk + off, 16, 1024), idesc_s, k != 0);
+        }
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k) {
+          const uint32_t off = (k >> 2) * (128 * 128) + (k & 3) * 32;
+          umma_f16(tmem_dp, make_smem_desc(ad + off, 16, 1024), make_smem_desc(bv + off, 16, 1024), idesc_s, k != 0);
+        }
+        umma_commit(sdp_full);
+        umma_commit(&v_empty[st]);
+      };
+      auto issue_dq = [&](int j) {
+        const int st = j & 1;
+        mbar_wait(ds_ready, j & 1);
+        tc_fence_after();
+        const uint32_t a = smem_u32(sDS), bk = smem_u32(sK + st * S::kTile);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          umma_f16(tmem_dq, make_smem_desc(a + (k >> 2) * (128 * 128) + (k & 3) * 32, 16, 1024),
+                   make_smem_desc(bk + k * 2048, 128 * 128, 1024), idesc_dq, (j > 0 || k > 0) ? 1u : 0u);
+        umma_commit(dq_done);
+        umma_commit(&k_empty[st]);
+      };
+      mbar_wait(qdo_full, 0);
+      issue_sdp(0);
+      for (int j = 0; j < n_kv; ++j) {
+        if (j + 1 < n_kv) issue_sdp(j + 1);
+        issue_dq(j);
+      }
+    }
+  } else if (warp >= 4) {
+    const int q = warp & 3, half = (warp - 4) >> 2;
+    const int row = q * 32 + lane;
+    const int q_idx = qt * 128 + row;
+    const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+    const int64_t stat = ((int64_t)b * p.hq + h) * p.sq + q_idx;
+    const float lse2 = p.lse[stat] * kLog2e;
+    const float dl = p.delta[stat];
+    for (int j = 0; j < n_kv; ++j) {
+      mbar_wait(sdp_full, j & 1);
+      tc_fence_after();
+      uint32_t rs[64], rd[64];
+      tmem_ld_32x32(tmem_s + lane_off + half * 64, *reinterpret_cast<uint32_t(*)[32]>(&rs[0]));
+      tmem_ld_32x32(tmem_s + lane_off + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&rs[32]));
+      tmem_ld_32x32(tmem_dp + lane_off + half * 64, *reinterpret_cast<uint32_t(*)[32]>(&rd[0]));
+      tmem_ld_32x32(tmem_dp + lane_off + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&rd[32]));
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(sdp_empty);
+      const bool need_mask = p.causal && (j * 128 + 127 > qt * 128 + diag);
+      const int lim = q_idx + diag - j * 128 - half * 64;       // local key index > lim is masked
+      uint32_t pk[32];
+#pragma unroll
+      for (int i = 0; i < 64; i += 2) {
+        float p0 = ex2_approx(fmaf(__uint_as_float(rs[i]), p.scale_log2, -lse2));
+        float p1 = ex2_approx(fmaf(__uint_as_float(rs[i + 1]), p.scale_log2, -lse2));
+        if (need_mask) {
+          if (i > lim) p0 = 0.f;
+          if (i + 1 > lim) p1 = 0.f;
+        }
+        const float d0 = p0 * (__uint_as_float(rd[i]) - dl) * p.scale;
+        const float d1 = p1 * (__uint_as_float(rd[i + 1]) - dl) * p.scale;
+        pk[i >> 1] = pack_bf16(d0, d1);
+      }
+      if (j >= 1) {
+        mbar_wait(dq_done, (j - 1) & 1);                          // previous dS has been consumed
+      }
+      uint8_t* base = sDS + half * (128 * 128) + row * 128;
+#pragma unroll
+      for (int t = 0; t < 8; ++t) {
+        const int chunk = t ^ (row & 7);
+        *reinterpret_cast<uint4*>(base + chunk * 16) = make_uint4(pk[t * 4], pk[t * 4 + 1], pk[t * 4 + 2], pk[t * 4 + 3]);
+      }
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(ds_ready);
+    }
+    mbar_wait(dq_done, (n_kv - 1) & 1);
+    tc_fence_after();
+    __nv_bfloat16* out = p.dq + ((int64_t)(b * p.sq + q_idx) * p.hq + h) * D + half * (D / 2);
+#pragma unroll
+    for (int c = 0; c < D / 64; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32(tmem_dq + lane_off + half * (D / 2) + c * 32, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; i += 8) {
+        uint4 v;
+        v.x = pack_bf16(__uint_as_float(r[i]), __uint_as_float(r[i + 1]));
+        v.y = pack_bf16(__uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]));
+        v.z = pack_bf16(__uint_as_float(r[i + 4]), __uint_as_float(r[i + 5]));
+        v.w = pack_bf16(__uint_as_float(r[i + 6]), __uint_as_float(r[i + 7]));
+        *reinterpret_cast<uint4*>(out + c * 32 + i) = v;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_s, kTmemCols);
+}
+
+// ---------------------------------------------------------------------------------------------- dK, dV
+constexpr int BQI = 64;                                  // query rows per inner iteration
+
+template <int D> struct DkvSmem {
+  static constexpr int kKV = 128 * D * 2;                 // K_j or V_j
+  static constexpr int kQ = BQI * D * 2;                  // one Q or dO stage
+  static constexpr int kPT = 128 * BQI * 2;               // P^T or dS^T
+  static constexpr int kStats = 2 * 2 * BQI * 4;          // [stage][lse2 | delta][BQI]
+  static constexpr int kTotal = 2 * kKV + 4 * kQ + 2 * kPT + kStats + 1024 + 256;
+};
+
+template <int D>
+__global__ void __launch_bounds__(kThreads, 1)
+flash_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_do,
+                     const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_v,
+                     const BwdParams p) {
+  using S = DkvSmem<D>;
+  constexpr int KB = D / 64;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sK = smem;
+  uint8_t* sV = sK + S::kKV;
+  uint8_t* sQ = sV + S::kKV;                 // [2]
+  uint8_t* sDO = sQ + 2 * S::kQ;             // [2]
+  uint8_t* sPT = sDO + 2 * S::kQ;
+  uint8_t* sDST = sPT + S::kPT;
+  float* stats = reinterpret_cast<float*>(sDST + S::kPT);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(stats) + S::kStats);
+  uint64_t* kv_full = bars;
+  uint64_t* q_full = bars + 1;               // [2]
+  uint64_t* q_empty = bars + 3;              // [2]
+  uint64_t* do_full = bars + 5;              // [2]
+  uint64_t* do_empty = bars + 7;             // [2]
+  uint64_t* sdp_full = bars + 9;             // [2]
+  uint64_t* sdp_empty = bars + 11;           // [2]
+  uint64_t* pds_ready = bars + 13;
+  uint64_t* pds_free = bars + 14;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 15);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int jt = blockIdx.x, hk = blockIdx.y, b = blockIdx.z;
+  const int G = p.hq / p.hk;
+  const int diag = p.sk - p.sq;
+  const int i0 = p.causal ? max(0, jt * 128 - diag) / BQI : 0;        // first query tile that sees this key tile
+  const int n_qi = p.sq / BQI - i0;
+  const int T = G * n_qi;
+  const int kv_row0 = b * p.sk + jt * 128;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tm_q);
+    prefetch_tmap(&tm_do);
+    prefetch_tmap(&tm_k);
+    prefetch_tmap(&tm_v);
+  }
+  if (warp == 1 && lane == 0) {
+    mbar_init(kv_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&q_full[i], 1);
+      mbar_init(&q_empty[i], 1);
+      mbar_init(&do_full[i], 1);
+      mbar_init(&do_empty[i], 1);
+      mbar_init(&sdp_full[i], 1);
+      mbar_init(&sdp_empty[i], 8);
+    }
+    mbar_init(pds_ready, 8);
+    mbar_init(pds_free, 1);
+    fence_barrier_init();
+  }
+  constexpr int kTmemCols = 512;             // S^T[2] (64 each) | dP^T[2] | dV (D) | dK (D)
+  if (warp == 2) tmem_alloc(tmem_ptr_smem, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_st = *tmem_ptr_smem;
+  const uint32_t tmem_dpt = tmem_st + 128;
+  const uint32_t tmem_dv = tmem_st + 256;
+  const uint32_t tmem_dk = tmem_st + 256 + D;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(kv_full, 2 * S::kKV);
+#pragma unroll
+      for (int kb = 0; kb < KB; ++kb) {
+        tma_load_2d(sK + kb * (128 * 128), &tm_k, kv_full, hk * D + kb * 64, kv_row0);
+        tma_load_2d(sV + kb * (128 * 128), &tm_v, kv_full, hk * D + kb * 64, kv_row0);
+      }
+      for (int t = 0; t < T; ++t) {
+        const int st = t & 1;
+        const int h = hk * G + t / n_qi, i = i0 + t % n_qi;
+        mbar_wait(&q_empty[st], ((t >> 1) & 1) ^ 1);
+        mbar_expect_tx(&q_full[st], S::kQ);
+#pragma unroll
+        for (int kb = 0; kb < KB; ++kb)
+          tma_load_2d(sQ + st * S::kQ + kb * (BQI * 128), &tm_q, &q_full[st], h * D + kb * 64, b * p.sq + i * BQI);
+      }
+    }
+  } else if (warp == 3) {
+    if (lane == 0) {
+      for (int t = 0; t < T; ++t) {
+        const int st = t & 1;
+        const int h = hk * G + t / n_qi, i = i0 + t % n_qi;
+        mbar_wait(&do_empty[st], ((t >> 1) & 1) ^ 1);
+        mbar_expect_tx(&do_full[st], S::kQ);
+#pragma unroll
+        for (int kb = 0; kb < KB; ++kb)
+          tma_load_2d(sDO + st * S::kQ + kb * (BQI * 128), &tm_do, &do_full[st], h * D + kb * 64, b * p.sq + i * BQI);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc_t = make_idesc_bf16(128, BQI, 0, 0);    // [keys][d] x [q][d]^T
+      constexpr uint32_t idesc_acc = make_idesc_bf16(128, D, 0, 1);    // [keys][q] x [q][d] (MN-major)
+      auto issue_sdp = [&](int t) {
+        const int st = t & 1, ph = (t >> 1) & 1;
+        mbar_wait(&q_full[st], ph);
+        mbar_wait(&do_full[st], ph);
+        mbar_wait(&sdp_empty[st], ph ^ 1);
+        tc_fence_after();
+        const uint32_t ak = smem_u32(sK), av = smem_u32(sV);
+        const uint32_t bq = smem_u32(sQ + st * S::kQ), bd = smem_u32(sDO + st * S::kQ);
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k)
+          umma_f16(tmem_st + st * BQI, make_smem_desc(ak + (k >> 2) * (128 * 128) + (k & 3) * 32, 16, 1024),
+                   make_smem_desc(bq + (k >> 2) * (BQI * 128) + (k & 3) * 32, 16, 1024), idesc_t, k != 0);
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k)
+          umma_f16(tmem_dpt + st * BQI, make_smem_desc(av + (k >> 2) * (128 * 128) + (k & 3) * 32, 16, 1024),
+                   make_smem_desc(bd + (k >> 2) * (BQI * 128) + (k & 3) * 32, 16, 1024), idesc_t, k != 0);
+        umma_commit(&sdp_full[st]);
+      };
+      auto issue_acc = [&](int t) {
+        const int st = t & 1;
+        mbar_wait(pds_ready, t & 1);
+        tc_fence_after();
+        const uint32_t ap = smem_u32(sPT), as = smem_u32(sDST);
+        const uint32_t bd = smem_u32(sDO + st * S::kQ), bq = smem_u32(sQ + st * S::kQ);
+#pragma unroll
+        for (int k = 0; k < BQI / 16; ++k)
+          umma_f16(tmem_dv, make_smem_desc(ap + k * 32, 16, 1024), make_smem_desc(bd + k * 2048, BQI * 128, 1024),
+                   idesc_acc, (t > 0 || k > 0) ? 1u : 0u);
+#pragma unroll
+        for (int k = 0; k < BQI / 16; ++k)
+          umma_f16(tmem_dk, make_smem_desc(as + k * 32, 16, 1024), make_smem_desc(bq + k * 2048, BQI * 128, 1024),
+                   idesc_acc, (t > 0 || k > 0) ? 1u : 0u);
+        umma_commit(pds_free);
+        umma_commit(&q_empty[st]);
+        umma_commit(&do_empty[st]);
+      };
+      mbar_wait(kv_full, 0);
+      issue_sdp(0);
+      for (int t = 0; t < T; ++t) {
+        if (t + 1 < T) issue_sdp(t + 1);
+        issue_acc(t);
+      }
+    }
+  } else if (warp >= 4) {
+    const int q = warp & 3, half = (warp - 4) >> 2;
+    const int row = q * 32 + lane;                       // key row inside the tile
+    const int sidx = (warp - 4) * 32 + lane;             // 0..255
+    const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+    for (int t = 0; t < T; ++t) {
+      const int st = t & 1;
+      const int h = hk * G + t / n_qi, i = i0 + t % n_qi;
+      if (sidx < BQI) {
+        const int64_t at = ((int64_t)b * p.hq + h) * p.sq + i * BQI + sidx;
+        stats[(st * 2) * BQI + sidx] = p.lse[at] * kLog2e;
+        stats[(st * 2 + 1) * BQI + sidx] = p.delta[at];
+      }
+      named_bar_sync(1, 256);
+      mbar_wait(&sdp_full[st], (t >> 1) & 1);
+      tc_fence_after();
+      uint32_t rs[32], rd[32];
+      tmem_ld_32x32(tmem_st + st * BQI + lane_off + half * 32, rs);
+      tmem_ld_32x32(tmem_dpt + st * BQI + lane_off + half * 32, rd);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sdp_empty[st]);
+      const bool need_mask = p.causal && (jt * 128 + 127 > i * BQI + diag);
+      // key (jt*128 + row) is visible to query (i*BQI + c) iff key <= query + diag  <=>  c >= row + jt*128 - diag - i*BQI
+      const int cmin = jt * 128 + row - diag - i * BQI - half * 32;      // local columns below cmin are masked
+      const float* lse2 = stats + (st * 2) * BQI + half * 32;
+      const float* dl = stats + (st * 2 + 1) * BQI + half * 32;
+      uint32_t pp[16], pd[16];
+#pragma unroll
+      for (int c = 0; c < 32; c += 4) {
+        const float4 l4 = *reinterpret_cast<const float4*>(lse2 + c);
+        const float4 d4 = *reinterpret_cast<const float4*>(dl + c);
+        const float ls[4] = {l4.x, l4.y, l4.z, l4.w}, ds[4] = {d4.x, d4.y, d4.z, d4.w};
+        float pv[4], dv[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          pv[u] = ex2_approx(fmaf(__uint_as_float(rs[c + u]), p.scale_log2, -ls[u]));
+          if (need_mask && (c + u < cmin)) pv[u] = 0.f;
+          dv[u] = pv[u] * (__uint_as_float(rd[c + u]) - ds[u]) * p.scale;
+        }
+        pp[c >> 1] = pack_bf16(pv[0], pv[1]);
+        pp[(c >> 1) + 1] = pack_bf16(pv[2], pv[3]);
+        pd[c >> 1] = pack_bf16(dv[0], dv[1]);
+        pd[(c >> 1) + 1] = pack_bf16(dv[2], dv[3]);
+      }
+      if (t >= 1) mbar_wait(pds_free, (t - 1) & 1);              // previous P^T / dS^T consumed
+      uint8_t* bp = sPT + row * 128;
+      uint8_t* bs = sDST + row * 128;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int chunk = (half * 4 + u) ^ (row & 7);
+        *reinterpret_cast<uint4*>(bp + chunk * 16) = make_uint4(pp[u * 4], pp[u * 4 + 1], pp[u * 4 + 2], pp[u * 4 + 3]);
+        *reinterpret_cast<uint4*>(bs + chunk * 16) = make_uint4(pd[u * 4], pd[u * 4 + 1], pd[u * 4 + 2], pd[u * 4 + 3]);
+      }
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(pds_ready);
+    }
+    mbar_wait(pds_free, (T - 1) & 1);
+    tc_fence_after();
+    const int64_t orow = ((int64_t)(kv_row0 + row) * p.hk + hk) * D + half * (D / 2);
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {
+      __nv_bfloat16* out = (which == 0 ? p.dv : p.dk) + orow;
+      const uint32_t src = (which == 0 ? tmem_dv : tmem_dk) + lane_off + half * (D / 2);
+#pragma unroll
+      for (int c = 0; c < D / 64; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(src + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; i += 8) {
+          uint4 v;
+          v.x = pack_bf16(__uint_as_float(r[i]), __uint_as_float(r[i + 1]));
+          v.y = pack_bf16(__uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]));
+          v.z = pack_bf16(__uint_as_float(r[i + 4]), __uint_as_float(r[i + 5]));
+          v.w = pack_bf16(__uint_as_float(r[i + 6]), __uint_as_float(r[i + 7]));
+          *reinterpret_cast<uint4*>(out + c * 32 + i) = v;
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_st, kTmemCols);
+}
+
+template <int D>
+static int launch_bwd(const void* q, const void* k, const void* v, const void* o, const void* d_o, const float* lse,
+                      void* dq, void* dk, void* dv, float* delta, int b, int sq, int sk, int hq, int hk, float scale,
+                      int causal, cudaStream_t st) {
+  const int64_t rows = (int64_t)b * sq * hq;
+  delta_kernel<D><<<(unsigned)((rows + 7) / 8), 256, 0, st>>>((const __nv_bfloat16*)o, (const __nv_bfloat16*)d_o, delta, sq, hq, rows);
+  if (int e = check_launch("flash_attn_bwd delta")) return e;
+  CUtensorMap tq, tdo, tk, tv, tq64, tdo64;
+  const uint64_t qc = (uint64_t)hq * D, kc = (uint64_t)hk * D;
+  if (encode_tmap_2d(&tq, q, (uint64_t)b * sq, qc, qc * 2, 128, 64, 2, true)) return -1;
+  if (encode_tmap_2d(&tdo, d_o, (uint64_t)b * sq, qc, qc * 2, 128, 64, 2, true)) return -1;
+  if (encode_tmap_2d(&tq64, q, (uint64_t)b * sq, qc, qc * 2, BQI, 64, 2, true)) return -1;
+  if (encode_tmap_2d(&tdo64, d_o, (uint64_t)b * sq, qc, qc * 2, BQI, 64, 2, true)) return -1;
+  if (encode_tmap_2d(&tk, k, (uint64_t)b * sk, kc, kc * 2, 128, 64, 2, true)) return -1;
+  if (encode_tmap_2d(&tv, v, (uint64_t)b * sk, kc, kc * 2, 128, 64, 2, true)) return -1;
+  BwdParams p{sq, sk, hq, hk, scale * kLog2e, scale, causal, lse, delta, (__nv_bfloat16*)dq, (__nv_bfloat16*)dk,
+              (__nv_bfloat16*)dv};
+  auto kq = flash_bwd_dq_kernel<D>;
+  auto kkv = flash_bwd_dkv_kernel<D>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    PDB_CUDA_OK(cudaFuncSetAttribute(kq, cudaFuncAttributeMaxDynamicSharedMemorySize, DqSmem<D>::kTotal));
+    PDB_CUDA_OK(cudaFuncSetAttribute(kkv, cudaFuncAttributeMaxDynamicSharedMemorySize, DkvSmem<D>::kTotal));
+    attr_set = true;
+  }
+  kkv<<<dim3(sk / 128, hk, b), kThreads, DkvSmem<D>::kTotal, st>>>(tq64, tdo64, tk, tv, p);
+  if (int e = check_launch("flash_attn_bwd dkv")) return e;
+  kq<<<dim3(sq / 128, hq, b), kThreads, DqSmem<D>::kTotal, st>>>(tq, tdo, tk, tv, p);
+  return check_launch("flash_attn_bwd dq");
+}
+
+}  // namespace fab
+}  // namespace pdb
+
+using namespace pdb;
+
+PDB_EXPORT int64_t pdb200_flash_attn_bwd_workspace_bytes(int64_t b, int64_t sq, int64_t sk, int64_t hq, int64_t hk, int64_t d) {
+  (void)sk; (void)hk; (void)d;
+  return b * hq * sq * (int64_t)sizeof(float);            // Delta
+}
+
+PDB_EXPORT int pdb200_flash_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* d_o,
+                                     const float* lse, void* dq, void* dk, void* dv, void* workspace,
+                                     int64_t workspace_bytes, int64_t b, int64_t sq, int64_t sk, int64_t hq, int64_t hk,
+                                     int64_t d, float scale, int causal, int dtype, void* stream) {
+  PDB_REQUIRE(dtype == PDB_DTYPE_BF16, "flash_attn_bwd: bfloat16 only");
+  PDB_REQUIRE(d == 64 || d == 128, "flash_attn_bwd: head_dim must be 64 or 128 (got %lld)", (long long)d);
+  PDB_REQUIRE(sq % 128 == 0 && sk % 128 == 0 && sq > 0 && sk > 0, "flash_attn_bwd: sequence lengths must be multiples of 128");
+  PDB_REQUIRE(hq % hk == 0, "flash_attn_bwd: q heads must be a multiple of kv heads");
+  PDB_REQUIRE(!causal || sk >= sq, "flash_attn_bwd: causal needs sk >= sq");
+  PDB_REQUIRE(workspace_bytes >= pdb200_flash_attn_bwd_workspace_bytes(b, sq, sk, hq, hk, d) &&
+                  ((uintptr_t)workspace & 15) == 0,
+              "flash_attn_bwd: workspace too small or misaligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (d == 128)
+    return fab::launch_bwd<128>(q, k, v, o, d_o, lse, dq, dk, dv, (float*)workspace, (int)b, (int)sq, (int)sk, (int)hq,
+                                (int)hk, scale, causal, st);
+  return fab::launch_bwd<64>(q, k, v, o, d_o, lse, dq, dk, dv, (float*)workspace, (int)b, (int)sq, (int)sk, (int)hq,
+                             (int)hk, scale, causal, st);
+}

@@ -108,6 +108,10 @@ PDB_API int pdb200_gemm_bf16_ar(const uint64_t* peer_ptrs, int nranks, int rank,
  * sm80 kernels).  q [b,sq,hq,d], k/v [b,sk,hk,d] bf16, d in {64,128}, sq/sk multiples of 128; o like q; lse [b,hq,sq]
  * fp32 (natural log of the softmax denominator, scaled scores). */
 PDB_API int pdb200_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int64_t b, int64_t sq, int64_t sk, int64_t hq, int64_t hk, int64_t d, float scale, int causal, int dtype, void* stream);
+/* K17 backward: Delta pre-pass + dK/dV kernel (transposed products, GQA heads looped in-CTA) + dQ kernel; deterministic,
+ * no atomics.  workspace: pdb200_flash_attn_bwd_workspace_bytes() bytes of device memory (16-byte aligned). */
+PDB_API int64_t pdb200_flash_attn_bwd_workspace_bytes(int64_t b, int64_t sq, int64_t sk, int64_t hq, int64_t hk, int64_t d);
+PDB_API int pdb200_flash_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* d_o, const float* lse, void* dq, void* dk, void* dv, void* workspace, int64_t workspace_bytes, int64_t b, int64_t sq, int64_t sk, int64_t hq, int64_t hk, int64_t d, float scale, int causal, int dtype, void* stream);
 
 #ifdef __cplusplus
 }

@@ -51,15 +51,34 @@ def test_flash_fwd_cross_lengths():
         torch.testing.assert_close(o.float(), ro, rtol=2e-2, atol=2e-2)
 
 
-def test_flash_backward_matches_naive():
-    torch.manual_seed(4)
-    b, s, h, d = 1, 256, 4, 128
-    q, k, v = (torch.randn(b, s, h, d, device=DEV).bfloat16().requires_grad_(True) for _ in range(3))
-    o = ops.flash_attention(q, k, v, causal=True)
+@pytest.mark.parametrize("d", [128, 64])
+@pytest.mark.parametrize("causal", [True, False])
+@pytest.mark.parametrize("b,sq,sk,hq,hk", [(1, 256, 256, 4, 4), (2, 384, 384, 4, 2), (1, 128, 384, 2, 1), (1, 1024, 1024, 2, 2)])
+def test_flash_backward_matches_naive(d, causal, b, sq, sk, hq, hk):
+    assert hasattr(lib.kernels.require(), "pdb200_flash_attn_bwd"), "native backward missing"
+    torch.manual_seed(4 + sq + d)
+    q = torch.randn(b, sq, hq, d, device=DEV).bfloat16().requires_grad_(True)
+    k = torch.randn(b, sk, hk, d, device=DEV).bfloat16().requires_grad_(True)
+    v = torch.randn(b, sk, hk, d, device=DEV).bfloat16().requires_grad_(True)
+    o = ops.flash_attention(q, k, v, causal=causal)
     g = torch.randn_like(o)
     o.backward(g)
     qr, kr, vr = (t.detach().float().requires_grad_(True) for t in (q, k, v))
-    ro, _ = naive(qr, kr, vr, True)
+    ro, _ = naive(qr, kr, vr, causal)
     ro.backward(g.float())
-    for a, r in ((q, qr), (k, kr), (v, vr)):
-        torch.testing.assert_close(a.grad.float(), r.grad, rtol=3e-2, atol=3e-2)
+    for name, a, r in (("dq", q, qr), ("dk", k, kr), ("dv", v, vr)):
+        torch.testing.assert_close(a.grad.float(), r.grad, rtol=3e-2, atol=3e-2, msg=lambda m, n=name: f"{n}: {m}")
+
+
+def test_flash_backward_is_deterministic():
+    torch.manual_seed(0)
+    q, k, v = (torch.randn(1, 512, 4, 128, device=DEV).bfloat16().requires_grad_(True) for _ in range(3))
+    g = torch.randn(1, 512, 4, 128, device=DEV).bfloat16()
+    outs = []
+    for _ in range(2):
+        for t in (q, k, v):
+            t.grad = None
+        ops.flash_attention(q, k, v, causal=True).backward(g)
+        outs.append([t.grad.clone() for t in (q, k, v)])
+    for a, b_ in zip(*outs):
+        assert torch.equal(a, b_)
