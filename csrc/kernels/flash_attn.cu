@@ -190,7 +190,7 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
     const uint32_t lane_off = (uint32_t)(q * 32) << 16;
     const uint32_t ts = tmem_base + g * BKV + lane_off;
     const uint32_t to = tmem_o + g * D + lane_off;
-    uint8_t* sPg = sP + g * S::kPBytes;
+    const uint32_t sPg_u32 = smem_u32(sP + g * S::kPBytes);
     float m_used = -INFINITY, l_run = 0.f;
     int it = 0;
     for (int j = g; j < n_kv; j += 2, ++it) {
@@ -255,11 +255,11 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
           pk[i >> 1] = *reinterpret_cast<uint32_t*>(&h2);
         }
         // 32 keys = 4 chunks of 16 B inside k-block (c / 2), chunk index ((c & 1) * 4 + t), XOR-swizzled by row % 8
-        uint8_t* base = sPg + (c >> 1) * (BQ * 128) + row * 128;
+        const uint32_t base = sPg_u32 + (c >> 1) * (BQ * 128) + row * 128;
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
           const int chunk = ((c & 1) * 4 + t) ^ (row & 7);
-          *reinterpret_cast<uint4*>(base + chunk * 16) = make_uint4(pk[t * 4], pk[t * 4 + 1], pk[t * 4 + 2], pk[t * 4 + 3]);
+          sts128(base + chunk * 16, pk[t * 4], pk[t * 4 + 1], pk[t * 4 + 2], pk[t * 4 + 3]);
         }
       }
       l_run += (ls[0] + ls[1]) + (ls[2] + ls[3]);
@@ -274,18 +274,18 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
       mbar_wait(&o_full[g], (it - 1) & 1);
       tc_fence_after();
     }
-    float* stats = reinterpret_cast<float*>(sP);           // P buffers are free now: [group][row][2]
+    const uint32_t stats = smem_u32(sP);                   // P buffers are free now: [group][row][2] floats
     // group B may still be reading... no: each group only touches its own P buffer; the stats live in group A's
     // buffer, which group A's last P V (awaited above by group A) has finished reading before A writes here, and B
     // writes only after the named barrier below orders it behind A's wait.
     named_bar_sync(1, 256);
-    stats[(g * BQ + row) * 2] = (it > 0) ? m_used : -INFINITY;
-    stats[(g * BQ + row) * 2 + 1] = l_run;
+    sts32f(stats + ((g * BQ + row) * 2) * 4, (it > 0) ? m_used : -INFINITY);
+    sts32f(stats + ((g * BQ + row) * 2 + 1) * 4, l_run);
     tc_fence_before();
     named_bar_sync(1, 256);
     tc_fence_after();
-    const float m_a = stats[row * 2], l_a = stats[row * 2 + 1];
-    const float m_b = stats[(BQ + row) * 2], l_b = stats[(BQ + row) * 2 + 1];
+    const float m_a = lds32f(stats + (row * 2) * 4), l_a = lds32f(stats + (row * 2 + 1) * 4);
+    const float m_b = lds32f(stats + ((BQ + row) * 2) * 4), l_b = lds32f(stats + ((BQ + row) * 2 + 1) * 4);
     const bool has_b = n_kv > 1;
     const float m_fin = fmaxf(m_a, m_b);                    // group A always has tile 0, so m_a is finite
     const float f_a = ex2_approx((m_a - m_fin) * p.scale_log2);

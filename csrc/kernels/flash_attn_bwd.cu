@@ -259,11 +259,11 @@ flash_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
       if (j >= 1) {
         mbar_wait(dq_done, (j - 1) & 1);                          // previous dS has been consumed
       }
-      uint8_t* base = sDS + half * (128 * 128) + row * 128;
+      const uint32_t base = smem_u32(sDS) + half * (128 * 128) + row * 128;
 #pragma unroll
       for (int t = 0; t < 8; ++t) {
         const int chunk = t ^ (row & 7);
-        *reinterpret_cast<uint4*>(base + chunk * 16) = make_uint4(pk[t * 4], pk[t * 4 + 1], pk[t * 4 + 2], pk[t * 4 + 3]);
+        sts128(base + chunk * 16, pk[t * 4], pk[t * 4 + 1], pk[t * 4 + 2], pk[t * 4 + 3]);
       }
       fence_proxy_async();
       __syncwarp();
@@ -454,13 +454,14 @@ flash_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
     const int row = q * 32 + lane;                       // key row inside the tile
     const int sidx = (warp - 4) * 32 + lane;             // 0..255
     const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+    const uint32_t stats_u32 = smem_u32(stats);
     for (int t = 0; t < T; ++t) {
       const int st = t & 1;
       const int h = hk * G + t / n_qi, i = i0 + t % n_qi;
       if (sidx < BQI) {
         const int64_t at = ((int64_t)b * p.hq + h) * p.sq + i * BQI + sidx;
-        stats[(st * 2) * BQI + sidx] = p.lse[at] * kLog2e;
-        stats[(st * 2 + 1) * BQI + sidx] = p.delta[at];
+        sts32f(stats_u32 + ((st * 2) * BQI + sidx) * 4, p.lse[at] * kLog2e);
+        sts32f(stats_u32 + ((st * 2 + 1) * BQI + sidx) * 4, p.delta[at]);
       }
       named_bar_sync(1, 256);
       mbar_wait(&sdp_full[st], (t >> 1) & 1);
@@ -475,13 +476,13 @@ flash_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       const bool need_mask = p.causal && (jt * 128 + 127 > i * BQI + diag);
       // key (jt*128 + row) is visible to query (i*BQI + c) iff key <= query + diag  <=>  c >= row + jt*128 - diag - i*BQI
       const int cmin = jt * 128 + row - diag - i * BQI - half * 32;      // local columns below cmin are masked
-      const float* lse2 = stats + (st * 2) * BQI + half * 32;
-      const float* dl = stats + (st * 2 + 1) * BQI + half * 32;
+      const uint32_t lse2 = stats_u32 + ((st * 2) * BQI + half * 32) * 4;
+      const uint32_t dl = stats_u32 + ((st * 2 + 1) * BQI + half * 32) * 4;
       uint32_t pp[16], pd[16];
 #pragma unroll
       for (int c = 0; c < 32; c += 4) {
-        const float4 l4 = *reinterpret_cast<const float4*>(lse2 + c);
-        const float4 d4 = *reinterpret_cast<const float4*>(dl + c);
+        const float4 l4 = lds128f(lse2 + c * 4);
+        const float4 d4 = lds128f(dl + c * 4);
         const float ls[4] = {l4.x, l4.y, l4.z, l4.w}, ds[4] = {d4.x, d4.y, d4.z, d4.w};
         float pv[4], dv[4];
 #pragma unroll
@@ -496,13 +497,13 @@ flash_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
         pd[(c >> 1) + 1] = pack_bf16(dv[2], dv[3]);
       }
       if (t >= 1) mbar_wait(pds_free, (t - 1) & 1);              // previous P^T / dS^T consumed
-      uint8_t* bp = sPT + row * 128;
-      uint8_t* bs = sDST + row * 128;
+      const uint32_t bp = smem_u32(sPT) + row * 128;
+      const uint32_t bs = smem_u32(sDST) + row * 128;
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const int chunk = (half * 4 + u) ^ (row & 7);
-        *reinterpret_cast<uint4*>(bp + chunk * 16) = make_uint4(pp[u * 4], pp[u * 4 + 1], pp[u * 4 + 2], pp[u * 4 + 3]);
-        *reinterpret_cast<uint4*>(bs + chunk * 16) = make_uint4(pd[u * 4], pd[u * 4 + 1], pd[u * 4 + 2], pd[u * 4 + 3]);
+        sts128(bp + chunk * 16, pp[u * 4], pp[u * 4 + 1], pp[u * 4 + 2], pp[u * 4 + 3]);
+        sts128(bs + chunk * 16, pd[u * 4], pd[u * 4 + 1], pd[u * 4 + 2], pd[u * 4 + 3]);
       }
       fence_proxy_async();
       __syncwarp();
