@@ -110,6 +110,8 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
   const uint32_t tmem_base = *tmem_ptr_smem;
   const uint32_t tmem_o = tmem_base + 2 * BKV;           // group g: tmem_o + g * D
 
+  if (warp < 4) {
+  reg_dealloc<56>();
   if (warp == 0) {
     if (lane == 0) {
       mbar_expect_tx(q_full, S::kQBytes);
@@ -182,7 +184,9 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
       if (n_kv > 1) issue_pv(n_kv - 2);
       issue_pv(n_kv - 1);
     }
-  } else if (warp >= 4) {
+  }
+  } else {
+    reg_alloc<216>();
     const int g = (warp - 4) >> 2;                          // softmax group: 0 = even tiles, 1 = odd tiles
     const int q = warp & 3;                                 // TMEM lane quarter this warp may touch
     const int row = q * 32 + lane;                          // row inside the tile
@@ -216,16 +220,44 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
         for (int u = 0; u < 4; ++u) mx[u] = fmaxf(mx[u], __uint_as_float(r[i + u]));
       }
       const float m_tile = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+      float alpha = 1.f;
+      bool rescale = false;
       if (it == 0) {
         m_used = (m_tile == -INFINITY) ? 0.f : m_tile;
       } else {
+        const bool grow = (m_tile - m_used) * p.scale_log2 > kRescaleThreshold;
+        rescale = __any_sync(0xffffffffu, grow);
+        if (rescale) {
+          const float m_new = fmaxf(m_used, m_tile);
+          alpha = ex2_approx((m_used - m_new) * p.scale_log2);
+          l_run *= alpha;
+          m_used = m_new;
+        }
+      }
+      // probabilities (packed bf16, kept in registers) + row sum; all of this overlaps the previous P V of the group
+      const float mb = m_used * p.scale_log2;
+      float ls[4] = {0.f, 0.f, 0.f, 0.f};
+      uint32_t pk[BKV / 2];
+#pragma unroll
+      for (int i = 0; i < BKV; i += 4) {
+        float x0, x1, x2, x3;
+        ffma2(x0, x1, __uint_as_float(r[i]), __uint_as_float(r[i + 1]), p.scale_log2, -mb);
+        ffma2(x2, x3, __uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]), p.scale_log2, -mb);
+        x0 = ex2_approx(x0);
+        x1 = ex2_approx(x1);
+        x2 = ex2_approx(x2);
+        x3 = ex2_approx(x3);
+        fadd2(ls[0], ls[1], x0, x1);
+        fadd2(ls[2], ls[3], x2, x3);
+        __nv_bfloat162 h0 = __floats2bfloat162_rn(x0, x1), h1 = __floats2bfloat162_rn(x2, x3);
+        pk[i >> 1] = *reinterpret_cast<uint32_t*>(&h0);
+        pk[(i >> 1) + 1] = *reinterpret_cast<uint32_t*>(&h1);
+      }
+      if (it > 0) {
         // the previous P V of this group must be done before P is overwritten or O is touched
         mbar_wait(&o_full[g], (it - 1) & 1);
         tc_fence_after();
-        const bool grow = (m_tile - m_used) * p.scale_log2 > kRescaleThreshold;
-        if (__any_sync(0xffffffffu, grow)) {
-          const float m_new = fmaxf(m_used, m_tile);
-          const float alpha = ex2_approx((m_used - m_new) * p.scale_log2);
+        if (rescale) {
 #pragma unroll
           for (int c = 0; c < D / 32; ++c) {
             uint32_t o[32];
@@ -236,30 +268,17 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
             tmem_st_32x32(to + c * 32, o);
           }
           tmem_st_wait();
-          l_run *= alpha;
-          m_used = m_new;
         }
       }
-      // probabilities -> shared memory (UMMA K-major, 128-byte swizzle) + row sum
-      const float mb = m_used * p.scale_log2;
-      float ls[4] = {0.f, 0.f, 0.f, 0.f};
+      // P -> shared memory (UMMA K-major, 128-byte swizzle): 32 keys = 4 chunks of 16 B inside k-block (c / 2),
+      // chunk index ((c & 1) * 4 + t), XOR-swizzled by row % 8
 #pragma unroll
       for (int c = 0; c < BKV / 32; ++c) {
-        uint32_t pk[16];
-#pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          const float p0 = ex2_approx(fmaf(__uint_as_float(r[c * 32 + i]), p.scale_log2, -mb));
-          const float p1 = ex2_approx(fmaf(__uint_as_float(r[c * 32 + i + 1]), p.scale_log2, -mb));
-          ls[(i >> 1) & 3] += p0 + p1;
-          __nv_bfloat162 h2 = __floats2bfloat162_rn(p0, p1);
-          pk[i >> 1] = *reinterpret_cast<uint32_t*>(&h2);
-        }
-        // 32 keys = 4 chunks of 16 B inside k-block (c / 2), chunk index ((c & 1) * 4 + t), XOR-swizzled by row % 8
         const uint32_t base = sPg_u32 + (c >> 1) * (BQ * 128) + row * 128;
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
           const int chunk = ((c & 1) * 4 + t) ^ (row & 7);
-          sts128(base + chunk * 16, pk[t * 4], pk[t * 4 + 1], pk[t * 4 + 2], pk[t * 4 + 3]);
+          sts128(base + chunk * 16, pk[c * 16 + t * 4], pk[c * 16 + t * 4 + 1], pk[c * 16 + t * 4 + 2], pk[c * 16 + t * 4 + 3]);
         }
       }
       l_run += (ls[0] + ls[1]) + (ls[2] + ls[3]);

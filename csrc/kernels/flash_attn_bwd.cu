@@ -149,6 +149,8 @@ flash_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
   const uint32_t tmem_dp = tmem_s + 128;
   const uint32_t tmem_dq = tmem_s + 256;
 
+  if (warp < 4) {
+  reg_dealloc<56>();
   if (warp == 0) {
     if (lane == 0) {
       mbar_expect_tx(qdo_full, 2 * S::kTile);
@@ -221,14 +223,16 @@ flash_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
         issue_dq(j);
       }
     }
-  } else if (warp >= 4) {
+  }
+  } else {
+    reg_alloc<216>();
     const int q = warp & 3, half = (warp - 4) >> 2;
     const int row = q * 32 + lane;
     const int q_idx = qt * 128 + row;
     const uint32_t lane_off = (uint32_t)(q * 32) << 16;
     const int64_t stat = ((int64_t)b * p.hq + h) * p.sq + q_idx;
     const float lse2 = p.lse[stat] * kLog2e;
-    const float dl = p.delta[stat];
+    const float dls = -p.delta[stat] * p.scale;
     for (int j = 0; j < n_kv; ++j) {
       mbar_wait(sdp_full, j & 1);
       tc_fence_after();
@@ -241,20 +245,22 @@ flash_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(sdp_empty);
-      const bool need_mask = p.causal && (j * 128 + 127 > qt * 128 + diag);
-      const int lim = q_idx + diag - j * 128 - half * 64;       // local key index > lim is masked
+      if (p.causal && (j * 128 + 127 > qt * 128 + diag)) {         // diagonal tile: masked keys get probability 0
+        const int lim = q_idx + diag - j * 128 - half * 64;        // local key index > lim is masked
+#pragma unroll
+        for (int i = 0; i < 64; ++i)
+          if (i > lim) rs[i] = 0xff800000u;
+      }
       uint32_t pk[32];
 #pragma unroll
       for (int i = 0; i < 64; i += 2) {
-        float p0 = ex2_approx(fmaf(__uint_as_float(rs[i]), p.scale_log2, -lse2));
-        float p1 = ex2_approx(fmaf(__uint_as_float(rs[i + 1]), p.scale_log2, -lse2));
-        if (need_mask) {
-          if (i > lim) p0 = 0.f;
-          if (i + 1 > lim) p1 = 0.f;
-        }
-        const float d0 = p0 * (__uint_as_float(rd[i]) - dl) * p.scale;
-        const float d1 = p1 * (__uint_as_float(rd[i + 1]) - dl) * p.scale;
-        pk[i >> 1] = pack_bf16(d0, d1);
+        float x0, x1, t0, t1;
+        ffma2(x0, x1, __uint_as_float(rs[i]), __uint_as_float(rs[i + 1]), p.scale_log2, -lse2);
+        ffma2(t0, t1, __uint_as_float(rd[i]), __uint_as_float(rd[i + 1]), p.scale, dls);     // (dP - Delta) * scale
+        x0 = ex2_approx(x0);
+        x1 = ex2_approx(x1);
+        fmul2(t0, t1, t0, t1, x0, x1);
+        pk[i >> 1] = pack_bf16(t0, t1);
       }
       if (j >= 1) {
         mbar_wait(dq_done, (j - 1) & 1);                          // previous dS has been consumed
@@ -372,6 +378,8 @@ flash_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
   const uint32_t tmem_dv = tmem_st + 256;
   const uint32_t tmem_dk = tmem_st + 256 + D;
 
+  if (warp < 4) {
+  reg_dealloc<56>();
   if (warp == 0) {
     if (lane == 0) {
       mbar_expect_tx(kv_full, 2 * S::kKV);
@@ -449,21 +457,33 @@ flash_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
         issue_acc(t);
       }
     }
-  } else if (warp >= 4) {
+  }
+  } else {
+    reg_alloc<216>();
     const int q = warp & 3, half = (warp - 4) >> 2;
     const int row = q * 32 + lane;                       // key row inside the tile
     const int sidx = (warp - 4) * 32 + lane;             // 0..255
     const uint32_t lane_off = (uint32_t)(q * 32) << 16;
     const uint32_t stats_u32 = smem_u32(stats);
+    // per-query statistics of the NEXT iteration are fetched while the current one computes (global latency hidden)
+    float nxt_l = 0.f, nxt_d = 0.f;
+    auto fetch_stats = [&](int t) {
+      if (sidx < BQI && t < T) {
+        const int64_t at = ((int64_t)b * p.hq + hk * G + t / n_qi) * p.sq + (i0 + t % n_qi) * BQI + sidx;
+        nxt_l = -p.lse[at] * kLog2e;
+        nxt_d = -p.delta[at] * p.scale;
+      }
+    };
+    fetch_stats(0);
     for (int t = 0; t < T; ++t) {
       const int st = t & 1;
-      const int h = hk * G + t / n_qi, i = i0 + t % n_qi;
+      const int i = i0 + t % n_qi;
       if (sidx < BQI) {
-        const int64_t at = ((int64_t)b * p.hq + h) * p.sq + i * BQI + sidx;
-        sts32f(stats_u32 + ((st * 2) * BQI + sidx) * 4, p.lse[at] * kLog2e);
-        sts32f(stats_u32 + ((st * 2 + 1) * BQI + sidx) * 4, p.delta[at]);
+        sts32f(stats_u32 + ((st * 2) * BQI + sidx) * 4, nxt_l);
+        sts32f(stats_u32 + ((st * 2 + 1) * BQI + sidx) * 4, nxt_d);
       }
       named_bar_sync(1, 256);
+      fetch_stats(t + 1);
       mbar_wait(&sdp_full[st], (t >> 1) & 1);
       tc_fence_after();
       uint32_t rs[32], rd[32];
@@ -473,28 +493,35 @@ flash_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&sdp_empty[st]);
-      const bool need_mask = p.causal && (jt * 128 + 127 > i * BQI + diag);
-      // key (jt*128 + row) is visible to query (i*BQI + c) iff key <= query + diag  <=>  c >= row + jt*128 - diag - i*BQI
-      const int cmin = jt * 128 + row - diag - i * BQI - half * 32;      // local columns below cmin are masked
-      const uint32_t lse2 = stats_u32 + ((st * 2) * BQI + half * 32) * 4;
-      const uint32_t dl = stats_u32 + ((st * 2 + 1) * BQI + half * 32) * 4;
+      if (p.causal && (jt * 128 + 127 > i * BQI + diag)) {
+        // key (jt*128 + row) is visible to query (i*BQI + c) iff key <= query + diag  <=>  c >= row + jt*128 - diag - i*BQI
+        const int cmin = jt * 128 + row - diag - i * BQI - half * 32;      // local columns below cmin are masked
+#pragma unroll
+        for (int c = 0; c < 32; ++c)
+          if (c < cmin) rs[c] = 0xff800000u;
+      }
+      const uint32_t lse2 = stats_u32 + ((st * 2) * BQI + half * 32) * 4;       // holds -lse * log2e
+      const uint32_t dl = stats_u32 + ((st * 2 + 1) * BQI + half * 32) * 4;     // holds -delta * scale
       uint32_t pp[16], pd[16];
 #pragma unroll
       for (int c = 0; c < 32; c += 4) {
         const float4 l4 = lds128f(lse2 + c * 4);
         const float4 d4 = lds128f(dl + c * 4);
-        const float ls[4] = {l4.x, l4.y, l4.z, l4.w}, ds[4] = {d4.x, d4.y, d4.z, d4.w};
-        float pv[4], dv[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          pv[u] = ex2_approx(fmaf(__uint_as_float(rs[c + u]), p.scale_log2, -ls[u]));
-          if (need_mask && (c + u < cmin)) pv[u] = 0.f;
-          dv[u] = pv[u] * (__uint_as_float(rd[c + u]) - ds[u]) * p.scale;
-        }
-        pp[c >> 1] = pack_bf16(pv[0], pv[1]);
-        pp[(c >> 1) + 1] = pack_bf16(pv[2], pv[3]);
-        pd[c >> 1] = pack_bf16(dv[0], dv[1]);
-        pd[(c >> 1) + 1] = pack_bf16(dv[2], dv[3]);
+        float x0, x1, x2, x3, t0, t1, t2, t3;
+        ffma2v(x0, x1, __uint_as_float(rs[c]), __uint_as_float(rs[c + 1]), p.scale_log2, p.scale_log2, l4.x, l4.y);
+        ffma2v(x2, x3, __uint_as_float(rs[c + 2]), __uint_as_float(rs[c + 3]), p.scale_log2, p.scale_log2, l4.z, l4.w);
+        ffma2v(t0, t1, __uint_as_float(rd[c]), __uint_as_float(rd[c + 1]), p.scale, p.scale, d4.x, d4.y);
+        ffma2v(t2, t3, __uint_as_float(rd[c + 2]), __uint_as_float(rd[c + 3]), p.scale, p.scale, d4.z, d4.w);
+        x0 = ex2_approx(x0);
+        x1 = ex2_approx(x1);
+        x2 = ex2_approx(x2);
+        x3 = ex2_approx(x3);
+        fmul2(t0, t1, t0, t1, x0, x1);
+        fmul2(t2, t3, t2, t3, x2, x3);
+        pp[c >> 1] = pack_bf16(x0, x1);
+        pp[(c >> 1) + 1] = pack_bf16(x2, x3);
+        pd[c >> 1] = pack_bf16(t0, t1);
+        pd[(c >> 1) + 1] = pack_bf16(t2, t3);
       }
       if (t >= 1) mbar_wait(pds_free, (t - 1) & 1);              // previous P^T / dS^T consumed
       const uint32_t bp = smem_u32(sPT) + row * 128;
