@@ -6,7 +6,7 @@
 //   delta_kernel          Delta[b,h,q] = sum_d dO * O                                  (memory-bound pre-pass)
 //   flash_bwd_dq_kernel   one CTA per 128-row query tile, loops over key tiles:   S = Q K^T, dP = dO V^T on the tensor
 //                         core, dS = P o (dP - Delta) * scale in registers, dQ += dS K accumulated in TMEM
-//   flash_bwd_dkv_kernel  one CTA per 128-key tile, loops over the group's query heads x 64-row query tiles, with the
+//   flash_bwd_dkv_kernel  one CTA per 128-key tile, loops over the group's query heads x 128-row query tiles, with the
 //                         TRANSPOSED products S^T = K Q^T and dP^T = V dO^T so that P^T and dS^T come out of TMEM with
 //                         keys on the lanes, ready to be the A operand of dV += P^T dO and dK += dS^T Q (both in TMEM).
 //                         GQA needs no reduction across heads: the group's heads are just more loop iterations.
@@ -80,8 +80,7 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 // ---------------------------------------------------------------------------------------------- dQ
 template <int D> struct DqSmem {
   static constexpr int kTile = 128 * D * 2;               // Q, dO, one K or V stage
-  static constexpr int kDS = 128 * 128 * 2;
-  static constexpr int kTotal = 6 * kTile + kDS + 1024 + 256;
+  static constexpr int kTotal = 6 * kTile + 1024 + 256;
 };
 
 template <int D>
@@ -97,8 +96,7 @@ flash_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
   uint8_t* sDO = sQ + S::kTile;
   uint8_t* sK = sDO + S::kTile;              // [2]
   uint8_t* sV = sK + 2 * S::kTile;           // [2]
-  uint8_t* sDS = sV + 2 * S::kTile;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sDS + S::kDS);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + 2 * S::kTile);
   uint64_t* qdo_full = bars;
   uint64_t* k_full = bars + 1;               // [2]
   uint64_t* k_empty = bars + 3;              // [2]
@@ -140,7 +138,7 @@ flash_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
     mbar_init(dq_done, 1);
     fence_barrier_init();
   }
-  constexpr int kTmemCols = 512;             // S | dP | dQ
+  constexpr int kTmemCols = 512;             // S | dP | dQ | dS (bf16 pairs, 64 columns)
   if (warp == 2) tmem_alloc(tmem_ptr_smem, kTmemCols);
   tc_fence_before();
   __syncthreads();
@@ -148,6 +146,7 @@ flash_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
   const uint32_t tmem_s = *tmem_ptr_smem;
   const uint32_t tmem_dp = tmem_s + 128;
   const uint32_t tmem_dq = tmem_s + 256;
+  const uint32_t tmem_ds = tmem_s + 384;
 
   if (warp < 4) {
   reg_dealloc<56>();
@@ -208,11 +207,11 @@ flash_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
         const int st = j & 1;
         mbar_wait(ds_ready, j & 1);
         tc_fence_after();
-        const uint32_t a = smem_u32(sDS), bk = smem_u32(sK + st * S::kTile);
+        const uint32_t bk = smem_u32(sK + st * S::kTile);
 #pragma unroll
-        for (int k = 0; k < 8; ++k)
-          umma_f16(tmem_dq, make_smem_desc(a + (k >> 2) * (128 * 128) + (k & 3) * 32, 16, 1024),
-                   make_smem_desc(bk + k * 2048, 128 * 128, 1024), idesc_dq, (j > 0 || k > 0) ? 1u : 0u);
+        for (int k = 0; k < 8; ++k)       // A = dS straight from TMEM: 16 keys per step = 8 packed columns
+          umma_f16_ts(tmem_dq, tmem_ds + k * 8, make_smem_desc(bk + k * 2048, 128 * 128, 1024), idesc_dq,
+                      (j > 0 || k > 0) ? 1u : 0u);
         umma_commit(dq_done);
         umma_commit(&k_empty[st]);
       };
@@ -265,13 +264,9 @@ flash_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
       if (j >= 1) {
         mbar_wait(dq_done, (j - 1) & 1);                          // previous dS has been consumed
       }
-      const uint32_t base = smem_u32(sDS) + half * (128 * 128) + row * 128;
-#pragma unroll
-      for (int t = 0; t < 8; ++t) {
-        const int chunk = t ^ (row & 7);
-        sts128(base + chunk * 16, pk[t * 4], pk[t * 4 + 1], pk[t * 4 + 2], pk[t * 4 + 3]);
-      }
-      fence_proxy_async();
+      tmem_st_32x32(tmem_ds + lane_off + half * 32, pk);           // 64 keys of this row = 32 packed columns
+      tmem_st_wait();
+      tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(ds_ready);
     }
@@ -300,271 +295,13 @@ flash_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
   if (warp == 2) tmem_dealloc(tmem_s, kTmemCols);
 }
 
-// ---------------------------------------------------------------------------------------------- dK, dV
-constexpr int BQI = 64;                                  // query rows per inner iteration
+}  // namespace fab
+}  // namespace pdb
 
-template <int D> struct DkvSmem {
-  static constexpr int kKV = 128 * D * 2;                 // K_j or V_j
-  static constexpr int kQ = BQI * D * 2;                  // one Q or dO stage
-  static constexpr int kPT = 128 * BQI * 2;               // P^T or dS^T
-  static constexpr int kStats = 2 * 2 * BQI * 4;          // [stage][lse2 | delta][BQI]
-  static constexpr int kTotal = 2 * kKV + 4 * kQ + 2 * kPT + kStats + 1024 + 256;
-};
+#include "flash_attn_bwd_dkv.cuh"
 
-template <int D>
-__global__ void __launch_bounds__(kThreads, 1)
-flash_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_do,
-                     const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_v,
-                     const BwdParams p) {
-  using S = DkvSmem<D>;
-  constexpr int KB = D / 64;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sK = smem;
-  uint8_t* sV = sK + S::kKV;
-  uint8_t* sQ = sV + S::kKV;                 // [2]
-  uint8_t* sDO = sQ + 2 * S::kQ;             // [2]
-  uint8_t* sPT = sDO + 2 * S::kQ;
-  uint8_t* sDST = sPT + S::kPT;
-  float* stats = reinterpret_cast<float*>(sDST + S::kPT);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(stats) + S::kStats);
-  uint64_t* kv_full = bars;
-  uint64_t* q_full = bars + 1;               // [2]
-  uint64_t* q_empty = bars + 3;              // [2]
-  uint64_t* do_full = bars + 5;              // [2]
-  uint64_t* do_empty = bars + 7;             // [2]
-  uint64_t* sdp_full = bars + 9;             // [2]
-  uint64_t* sdp_empty = bars + 11;           // [2]
-  uint64_t* pds_ready = bars + 13;
-  uint64_t* pds_free = bars + 14;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 15);
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int jt = blockIdx.x, hk = blockIdx.y, b = blockIdx.z;
-  const int G = p.hq / p.hk;
-  const int diag = p.sk - p.sq;
-  const int i0 = p.causal ? max(0, jt * 128 - diag) / BQI : 0;        // first query tile that sees this key tile
-  const int n_qi = p.sq / BQI - i0;
-  const int T = G * n_qi;
-  const int kv_row0 = b * p.sk + jt * 128;
-
-  if (warp == 0 && lane == 0) {
-    prefetch_tmap(&tm_q);
-    prefetch_tmap(&tm_do);
-    prefetch_tmap(&tm_k);
-    prefetch_tmap(&tm_v);
-  }
-  if (warp == 1 && lane == 0) {
-    mbar_init(kv_full, 1);
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(&q_full[i], 1);
-      mbar_init(&q_empty[i], 1);
-      mbar_init(&do_full[i], 1);
-      mbar_init(&do_empty[i], 1);
-      mbar_init(&sdp_full[i], 1);
-      mbar_init(&sdp_empty[i], 8);
-    }
-    mbar_init(pds_ready, 8);
-    mbar_init(pds_free, 1);
-    fence_barrier_init();
-  }
-  constexpr int kTmemCols = 512;             // S^T[2] (64 each) | dP^T[2] | dV (D) | dK (D)
-  if (warp == 2) tmem_alloc(tmem_ptr_smem, kTmemCols);
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_st = *tmem_ptr_smem;
-  const uint32_t tmem_dpt = tmem_st + 128;
-  const uint32_t tmem_dv = tmem_st + 256;
-  const uint32_t tmem_dk = tmem_st + 256 + D;
-
-  if (warp < 4) {
-  reg_dealloc<56>();
-  if (warp == 0) {
-    if (lane == 0) {
-      mbar_expect_tx(kv_full, 2 * S::kKV);
-#pragma unroll
-      for (int kb = 0; kb < KB; ++kb) {
-        tma_load_2d(sK + kb * (128 * 128), &tm_k, kv_full, hk * D + kb * 64, kv_row0);
-        tma_load_2d(sV + kb * (128 * 128), &tm_v, kv_full, hk * D + kb * 64, kv_row0);
-      }
-      for (int t = 0; t < T; ++t) {
-        const int st = t & 1;
-        const int h = hk * G + t / n_qi, i = i0 + t % n_qi;
-        mbar_wait(&q_empty[st], ((t >> 1) & 1) ^ 1);
-        mbar_expect_tx(&q_full[st], S::kQ);
-#pragma unroll
-        for (int kb = 0; kb < KB; ++kb)
-          tma_load_2d(sQ + st * S::kQ + kb * (BQI * 128), &tm_q, &q_full[st], h * D + kb * 64, b * p.sq + i * BQI);
-      }
-    }
-  } else if (warp == 3) {
-    if (lane == 0) {
-      for (int t = 0; t < T; ++t) {
-        const int st = t & 1;
-        const int h = hk * G + t / n_qi, i = i0 + t % n_qi;
-        mbar_wait(&do_empty[st], ((t >> 1) & 1) ^ 1);
-        mbar_expect_tx(&do_full[st], S::kQ);
-#pragma unroll
-        for (int kb = 0; kb < KB; ++kb)
-          tma_load_2d(sDO + st * S::kQ + kb * (BQI * 128), &tm_do, &do_full[st], h * D + kb * 64, b * p.sq + i * BQI);
-      }
-    }
-  } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc_t = make_idesc_bf16(128, BQI, 0, 0);    // [keys][d] x [q][d]^T
-      constexpr uint32_t idesc_acc = make_idesc_bf16(128, D, 0, 1);    // [keys][q] x [q][d] (MN-major)
-      auto issue_sdp = [&](int t) {
-        const int st = t & 1, ph = (t >> 1) & 1;
-        mbar_wait(&q_full[st], ph);
-        mbar_wait(&do_full[st], ph);
-        mbar_wait(&sdp_empty[st], ph ^ 1);
-        tc_fence_after();
-        const uint32_t ak = smem_u32(sK), av = smem_u32(sV);
-        const uint32_t bq = smem_u32(sQ + st * S::kQ), bd = smem_u32(sDO + st * S::kQ);
-#pragma unroll
-        for (int k = 0; k < D / 16; ++k)
-          umma_f16(tmem_st + st * BQI, make_smem_desc(ak + (k >> 2) * (128 * 128) + (k & 3) * 32, 16, 1024),
-                   make_smem_desc(bq + (k >> 2) * (BQI * 128) + (k & 3) * 32, 16, 1024), idesc_t, k != 0);
-#pragma unroll
-        for (int k = 0; k < D / 16; ++k)
-          umma_f16(tmem_dpt + st * BQI, make_smem_desc(av + (k >> 2) * (128 * 128) + (k & 3) * 32, 16, 1024),
-                   make_smem_desc(bd + (k >> 2) * (BQI * 128) + (k & 3) * 32, 16, 1024), idesc_t, k != 0);
-        umma_commit(&sdp_full[st]);
-      };
-      auto issue_acc = [&](int t) {
-        const int st = t & 1;
-        mbar_wait(pds_ready, t & 1);
-        tc_fence_after();
-        const uint32_t ap = smem_u32(sPT), as = smem_u32(sDST);
-        const uint32_t bd = smem_u32(sDO + st * S::kQ), bq = smem_u32(sQ + st * S::kQ);
-#pragma unroll
-        for (int k = 0; k < BQI / 16; ++k)
-          umma_f16(tmem_dv, make_smem_desc(ap + k * 32, 16, 1024), make_smem_desc(bd + k * 2048, BQI * 128, 1024),
-                   idesc_acc, (t > 0 || k > 0) ? 1u : 0u);
-#pragma unroll
-        for (int k = 0; k < BQI / 16; ++k)
-          umma_f16(tmem_dk, make_smem_desc(as + k * 32, 16, 1024), make_smem_desc(bq + k * 2048, BQI * 128, 1024),
-                   idesc_acc, (t > 0 || k > 0) ? 1u : 0u);
-        umma_commit(pds_free);
-        umma_commit(&q_empty[st]);
-        umma_commit(&do_empty[st]);
-      };
-      mbar_wait(kv_full, 0);
-      issue_sdp(0);
-      for (int t = 0; t < T; ++t) {
-        if (t + 1 < T) issue_sdp(t + 1);
-        issue_acc(t);
-      }
-    }
-  }
-  } else {
-    reg_alloc<216>();
-    const int q = warp & 3, half = (warp - 4) >> 2;
-    const int row = q * 32 + lane;                       // key row inside the tile
-    const int sidx = (warp - 4) * 32 + lane;             // 0..255
-    const uint32_t lane_off = (uint32_t)(q * 32) << 16;
-    const uint32_t stats_u32 = smem_u32(stats);
-    // per-query statistics of the NEXT iteration are fetched while the current one computes (global latency hidden)
-    float nxt_l = 0.f, nxt_d = 0.f;
-    auto fetch_stats = [&](int t) {
-      if (sidx < BQI && t < T) {
-        const int64_t at = ((int64_t)b * p.hq + hk * G + t / n_qi) * p.sq + (i0 + t % n_qi) * BQI + sidx;
-        nxt_l = -p.lse[at] * kLog2e;
-        nxt_d = -p.delta[at] * p.scale;
-      }
-    };
-    fetch_stats(0);
-    for (int t = 0; t < T; ++t) {
-      const int st = t & 1;
-      const int i = i0 + t % n_qi;
-      if (sidx < BQI) {
-        sts32f(stats_u32 + ((st * 2) * BQI + sidx) * 4, nxt_l);
-        sts32f(stats_u32 + ((st * 2 + 1) * BQI + sidx) * 4, nxt_d);
-      }
-      named_bar_sync(1, 256);
-      fetch_stats(t + 1);
-      mbar_wait(&sdp_full[st], (t >> 1) & 1);
-      tc_fence_after();
-      uint32_t rs[32], rd[32];
-      tmem_ld_32x32(tmem_st + st * BQI + lane_off + half * 32, rs);
-      tmem_ld_32x32(tmem_dpt + st * BQI + lane_off + half * 32, rd);
-      tmem_ld_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&sdp_empty[st]);
-      if (p.causal && (jt * 128 + 127 > i * BQI + diag)) {
-        // key (jt*128 + row) is visible to query (i*BQI + c) iff key <= query + diag  <=>  c >= row + jt*128 - diag - i*BQI
-        const int cmin = jt * 128 + row - diag - i * BQI - half * 32;      // local columns below cmin are masked
-#pragma unroll
-        for (int c = 0; c < 32; ++c)
-          if (c < cmin) rs[c] = 0xff800000u;
-      }
-      const uint32_t lse2 = stats_u32 + ((st * 2) * BQI + half * 32) * 4;       // holds -lse * log2e
-      const uint32_t dl = stats_u32 + ((st * 2 + 1) * BQI + half * 32) * 4;     // holds -delta * scale
-      uint32_t pp[16], pd[16];
-#pragma unroll
-      for (int c = 0; c < 32; c += 4) {
-        const float4 l4 = lds128f(lse2 + c * 4);
-        const float4 d4 = lds128f(dl + c * 4);
-        float x0, x1, x2, x3, t0, t1, t2, t3;
-        ffma2v(x0, x1, __uint_as_float(rs[c]), __uint_as_float(rs[c + 1]), p.scale_log2, p.scale_log2, l4.x, l4.y);
-        ffma2v(x2, x3, __uint_as_float(rs[c + 2]), __uint_as_float(rs[c + 3]), p.scale_log2, p.scale_log2, l4.z, l4.w);
-        ffma2v(t0, t1, __uint_as_float(rd[c]), __uint_as_float(rd[c + 1]), p.scale, p.scale, d4.x, d4.y);
-        ffma2v(t2, t3, __uint_as_float(rd[c + 2]), __uint_as_float(rd[c + 3]), p.scale, p.scale, d4.z, d4.w);
-        x0 = ex2_approx(x0);
-        x1 = ex2_approx(x1);
-        x2 = ex2_approx(x2);
-        x3 = ex2_approx(x3);
-        fmul2(t0, t1, t0, t1, x0, x1);
-        fmul2(t2, t3, t2, t3, x2, x3);
-        pp[c >> 1] = pack_bf16(x0, x1);
-        pp[(c >> 1) + 1] = pack_bf16(x2, x3);
-        pd[c >> 1] = pack_bf16(t0, t1);
-        pd[(c >> 1) + 1] = pack_bf16(t2, t3);
-      }
-      if (t >= 1) mbar_wait(pds_free, (t - 1) & 1);              // previous P^T / dS^T consumed
-      const uint32_t bp = smem_u32(sPT) + row * 128;
-      const uint32_t bs = smem_u32(sDST) + row * 128;
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int chunk = (half * 4 + u) ^ (row & 7);
-        sts128(bp + chunk * 16, pp[u * 4], pp[u * 4 + 1], pp[u * 4 + 2], pp[u * 4 + 3]);
-        sts128(bs + chunk * 16, pd[u * 4], pd[u * 4 + 1], pd[u * 4 + 2], pd[u * 4 + 3]);
-      }
-      fence_proxy_async();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(pds_ready);
-    }
-    mbar_wait(pds_free, (T - 1) & 1);
-    tc_fence_after();
-    const int64_t orow = ((int64_t)(kv_row0 + row) * p.hk + hk) * D + half * (D / 2);
-#pragma unroll
-    for (int which = 0; which < 2; ++which) {
-      __nv_bfloat16* out = (which == 0 ? p.dv : p.dk) + orow;
-      const uint32_t src = (which == 0 ? tmem_dv : tmem_dk) + lane_off + half * (D / 2);
-#pragma unroll
-      for (int c = 0; c < D / 64; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32(src + c * 32, r);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; i += 8) {
-          uint4 v;
-          v.x = pack_bf16(__uint_as_float(r[i]), __uint_as_float(r[i + 1]));
-          v.y = pack_bf16(__uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]));
-          v.z = pack_bf16(__uint_as_float(r[i + 4]), __uint_as_float(r[i + 5]));
-          v.w = pack_bf16(__uint_as_float(r[i + 6]), __uint_as_float(r[i + 7]));
-          *reinterpret_cast<uint4*>(out + c * 32 + i) = v;
-        }
-      }
-    }
-  }
-
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 2) tmem_dealloc(tmem_st, kTmemCols);
-}
+namespace pdb {
+namespace fab {
 
 template <int D>
 static int launch_bwd(const void* q, const void* k, const void* v, const void* o, const void* d_o, const float* lse,
@@ -573,12 +310,10 @@ static int launch_bwd(const void* q, const void* k, const void* v, const void* o
   const int64_t rows = (int64_t)b * sq * hq;
   delta_kernel<D><<<(unsigned)((rows + 7) / 8), 256, 0, st>>>((const __nv_bfloat16*)o, (const __nv_bfloat16*)d_o, delta, sq, hq, rows);
   if (int e = check_launch("flash_attn_bwd delta")) return e;
-  CUtensorMap tq, tdo, tk, tv, tq64, tdo64;
+  CUtensorMap tq, tdo, tk, tv;
   const uint64_t qc = (uint64_t)hq * D, kc = (uint64_t)hk * D;
   if (encode_tmap_2d(&tq, q, (uint64_t)b * sq, qc, qc * 2, 128, 64, 2, true)) return -1;
   if (encode_tmap_2d(&tdo, d_o, (uint64_t)b * sq, qc, qc * 2, 128, 64, 2, true)) return -1;
-  if (encode_tmap_2d(&tq64, q, (uint64_t)b * sq, qc, qc * 2, BQI, 64, 2, true)) return -1;
-  if (encode_tmap_2d(&tdo64, d_o, (uint64_t)b * sq, qc, qc * 2, BQI, 64, 2, true)) return -1;
   if (encode_tmap_2d(&tk, k, (uint64_t)b * sk, kc, kc * 2, 128, 64, 2, true)) return -1;
   if (encode_tmap_2d(&tv, v, (uint64_t)b * sk, kc, kc * 2, 128, 64, 2, true)) return -1;
   BwdParams p{sq, sk, hq, hk, scale * kLog2e, scale, causal, lse, delta, (__nv_bfloat16*)dq, (__nv_bfloat16*)dk,
@@ -591,7 +326,7 @@ static int launch_bwd(const void* q, const void* k, const void* v, const void* o
     PDB_CUDA_OK(cudaFuncSetAttribute(kkv, cudaFuncAttributeMaxDynamicSharedMemorySize, DkvSmem<D>::kTotal));
     attr_set = true;
   }
-  kkv<<<dim3(sk / 128, hk, b), kThreads, DkvSmem<D>::kTotal, st>>>(tq64, tdo64, tk, tv, p);
+  kkv<<<dim3(sk / 128, hk, b), kThreads, DkvSmem<D>::kTotal, st>>>(tq, tdo, tk, tv, p);
   if (int e = check_launch("flash_attn_bwd dkv")) return e;
   kq<<<dim3(sq / 128, hq, b), kThreads, DqSmem<D>::kTotal, st>>>(tq, tdo, tk, tv, p);
   return check_launch("flash_attn_bwd dq");
