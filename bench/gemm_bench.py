@@ -7,6 +7,7 @@ import sys
 import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from paddle_b200.framework import flags  # noqa: E402
 from paddle_b200.ops import gemm as G  # noqa: E402
 
 PEAK = json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")))["bf16_tflops"] \
@@ -49,13 +50,19 @@ def main():
             a = As[i[0]].t() if ta else As[i[0]]
             b = Bs[i[0]].t() if tb else Bs[i[0]]
             return torch.matmul(a, b)
+        i[0] = 0
         ref = cublas().float()
+        i[0] = 0
         got = ours().float()
         err = (got - ref).abs().max().item() / max(ref.abs().max().item(), 1e-6)
         t_o, t_c = timeit(ours), timeit(cublas)
+        flags.set_flags({"gemm_cta_pair": False})
+        t_s = timeit(ours)
+        flags.set_flags({"gemm_cta_pair": True})
         fl = 2.0 * M * N * K
         rows.append(dict(name=name, M=M, N=N, K=K, ours_ms=round(t_o, 4), cublas_ms=round(t_c, 4),
-                         ours_tflops=round(fl / t_o / 1e9, 1), cublas_tflops=round(fl / t_c / 1e9, 1),
+                         ours_tflops=round(fl / t_o / 1e9, 1), single_cta_tflops=round(fl / t_s / 1e9, 1),
+                         cublas_tflops=round(fl / t_c / 1e9, 1),
                          frac_of_measured_peak=round(fl / t_o / 1e9 / PEAK, 3), rel_err=err))
         print(rows[-1], flush=True)
     out = os.path.join(os.path.dirname(__file__), "..", "gpurun_out", "gemm_bench.json")

@@ -78,6 +78,8 @@ PDB_API int pdb200_topk_softmax(const void* logits, int64_t tokens, int E, int k
  * fused_linear_param_grad_add_kernel.cu:35-289).  A: [M,K] row-major, or [K,M] when trans_a.  B: [K,N] row-major, or
  * [N,K] when trans_b.  out_dtype 0 = fp32 (beta = 1 accumulates into C), 1 = bf16.  act: 0 none, 1 gelu, 2 relu. */
 PDB_API int pdb200_gemm_bf16(const void* a, const void* b, void* c, const void* bias, int64_t M, int64_t N, int64_t K, int trans_a, int trans_b, int out_dtype, float beta, int act, void* stream);
+/* Same contract, 256x256 output tiles computed by CTA pairs (tcgen05.mma.cta_group::2, cluster of 2). */
+PDB_API int pdb200_gemm_bf16_pair(const void* a, const void* b, void* c, const void* bias, int64_t M, int64_t N, int64_t K, int trans_a, int trans_b, int out_dtype, float beta, int act, void* stream);
 
 /* Fused collectives over NVLink symmetric memory (K1, K2+K3, K8; csrc/kernels/nvl_collectives.cu).  peer_ptrs: host
  * array of nranks device addresses = every rank's segment as mapped in this process (pdb200_symm_peer_ptr), mc_ptr:

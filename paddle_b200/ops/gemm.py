@@ -5,6 +5,7 @@ from __future__ import annotations
 import torch
 
 from .. import lib
+from ..framework.flags import flag
 from ._util import check, ptr, stream_ptr
 
 _MIN_DIM = 256
@@ -40,7 +41,10 @@ def gemm(a, b, trans_a=False, trans_b=False, out_dtype=None, accum_into=None, bi
         od = out_dtype or torch.bfloat16
         out = torch.empty(M, N, dtype=od, device=a.device)
         out_code, beta = (0 if od == torch.float32 else 1), 0.0
-    check(lib.kernels.pdb200_gemm_bf16(ptr(a), ptr(b), ptr(out), ptr(bias), M, N, K, int(trans_a), int(trans_b),
-                                       out_code, float(beta), {"none": 0, None: 0, "gelu": 1, "relu": 2}[act],
-                                       stream_ptr(a.device)), "gemm_bf16")
+    # CTA-pair kernel (256x256 tiles) for the big shapes, single-CTA 128xBN kernel for small / skinny ones
+    fn = lib.kernels.pdb200_gemm_bf16
+    if flag("gemm_cta_pair") and M >= 512 and N >= 512 and hasattr(lib.kernels.require(), "pdb200_gemm_bf16_pair"):
+        fn = lib.kernels.pdb200_gemm_bf16_pair
+    check(fn(ptr(a), ptr(b), ptr(out), ptr(bias), M, N, K, int(trans_a), int(trans_b), out_code, float(beta),
+             {"none": 0, None: 0, "gelu": 1, "relu": 2}[act], stream_ptr(a.device)), "gemm_bf16")
     return out

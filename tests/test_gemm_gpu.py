@@ -77,3 +77,39 @@ def test_linear_autograd_through_tc_gemm():
         paddle.nn.functional.linear(x2, w2).backward(g)
     assert w2.grad is None
     torch.testing.assert_close(w2.main_grad, 2 * wr.grad, rtol=1e-2, atol=5e-1)
+
+
+@pytest.mark.parametrize("ta,tb", [(False, False), (False, True), (True, False), (True, True)])
+@pytest.mark.parametrize("M,N,K", [(512, 512, 64), (640, 768, 320), (520, 1000, 200), (2048, 1536, 4096)])
+def test_gemm_cta_pair_kernel(ta, tb, M, N, K):
+    """256x256 tiles on CTA pairs (cta_group::2), incl. partial pair-tiles in M and N, vs the single-CTA kernel."""
+    from paddle_b200 import lib
+    from paddle_b200.framework import flags
+    assert hasattr(lib.kernels.require(), "pdb200_gemm_bf16_pair")
+    torch.manual_seed(M + N + K + 1)
+    a = (torch.randn((K, M) if ta else (M, K), device=DEV) * 0.5).bfloat16()
+    b = (torch.randn((N, K) if tb else (K, N), device=DEV) * 0.5).bfloat16()
+    flags.set_flags({"gemm_cta_pair": True})
+    out = G.gemm(a, b, ta, tb)
+    flags.set_flags({"gemm_cta_pair": False})
+    single = G.gemm(a, b, ta, tb)
+    flags.set_flags({"gemm_cta_pair": True})
+    ref = _ref(a, b, ta, tb)
+    torch.testing.assert_close(out.float(), ref, rtol=2e-2, atol=2e-2 * (K ** 0.5) * 0.25)
+    torch.testing.assert_close(out.float(), single.float(), rtol=1e-2, atol=1e-2 * (K ** 0.5) * 0.25)
+
+
+def test_gemm_cta_pair_accumulate_and_epilogue():
+    torch.manual_seed(5)
+    M, N, K = 768, 1024, 512
+    a = torch.randn(K, M, device=DEV).bfloat16()
+    b = torch.randn(K, N, device=DEV).bfloat16()
+    acc = torch.randn(M, N, device=DEV)
+    ref = acc + _ref(a, b, True, False)
+    G.gemm(a, b, True, False, accum_into=acc)
+    torch.testing.assert_close(acc, ref, rtol=1e-3, atol=1e-2)
+    x = (torch.randn(M, K, device=DEV) * 0.3).bfloat16()
+    w = (torch.randn(K, N, device=DEV) * 0.3).bfloat16()
+    bias = torch.randn(N, device=DEV).bfloat16()
+    out = G.gemm(x, w, bias=bias, act="gelu")
+    torch.testing.assert_close(out.float(), torch.nn.functional.gelu(_ref(x, w, False, False) + bias.float()), rtol=2e-2, atol=5e-2)
