@@ -39,7 +39,7 @@ def parse():
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="ours", choices=["ours", "reference"])
     p.add_argument("--model", default="llama2-7b", choices=["llama2-7b", "llama2-13b", "llama-tiny", "llama-1b"])
-    p.add_argument("--batch", type=int, default=int(os.environ.get("BENCH_BATCH", "1")), help="sequences per GPU per step")
+    p.add_argument("--batch", type=int, default=int(os.environ.get("BENCH_BATCH", "2")), help="sequences per GPU per step")
     p.add_argument("--seq", type=int, default=4096)
     p.add_argument("--recompute", type=int, default=int(os.environ.get("BENCH_RECOMPUTE", "0")))
     p.add_argument("--no-e2e", action="store_true")

@@ -18,8 +18,8 @@ def short(name):
 
 def family(name):
     n = name.lower()
-    if "pdb::" in n or "pdb200" in n or n.startswith("gemm_tc") or "nvl::" in n or "flash_fwd" in n or "flash_bwd" in n:
-        return "ours"
+    if any(t in n for t in ("pdb::", "pdb200", "tc::", "tc2::", "fa::", "fab::", "nvl::", "gemm_tc", "flash_fwd", "flash_bwd")):
+        return "ours (sm_100a kernels of this repo)"
     if "cutlass" in n or "cublas" in n or "nvjet" in n or "gemm" in n or "xmma" in n:
         return "library GEMM"
     if "cudnn" in n or "fmha" in n or "flash" in n or "sdpa" in n:
