@@ -268,6 +268,34 @@ __global__ void ce_combine_symm_kernel(Peers P, uint64_t stats_off, const int64_
   loss[row] = (labels[row] == ignore_index) ? 0.f : l - tgt;
 }
 
+// ---------------------------------------------------------------------------------------------- K3 (stand-alone)
+// Parameter all-gather as a push: every rank stores its shard into slot `rank` of the gathered buffer of ALL ranks -
+// one multimem.st per 16 bytes when the segment has a multicast mapping (the switch replicates it), a loop of peer
+// stores otherwise.  4 vectors per thread per trip keep enough bytes in flight to cover the NVLink round trip.
+__global__ void __launch_bounds__(256) allgather_push_kernel(Peers P, uint64_t src_off, uint64_t dst_off, int64_t nvec) {
+  const uint4* src = reinterpret_cast<const uint4*>(P.ptr[P.rank] + src_off);
+  const uint64_t dst0 = dst_off + (uint64_t)P.rank * (uint64_t)nvec * 16;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += 4 * stride) {
+    uint4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (i + u * stride < nvec) v[u] = src[i + u * stride];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int64_t j = i + u * stride;
+      if (j >= nvec) break;
+      const uint64_t off = dst0 + (uint64_t)j * 16;
+      if (P.mc) {
+        uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+        mm_st_b32x4(reinterpret_cast<void*>(P.mc + off), w);
+      } else {
+        for (int p = 0; p < P.nranks; ++p) *reinterpret_cast<uint4*>(P.ptr[(P.rank + p) % P.nranks] + off) = v[u];
+      }
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------- K7
 // Vocab-parallel embedding forward.  The reference looks rows up locally (zeros for ids another rank owns) and then
 // all-reduces [tokens, hidden]; since exactly one rank owns each row, the sum is really a gather: every rank reads the
@@ -371,9 +399,14 @@ PDB_EXPORT int pdb200_nvl_rs_adamw_ag(const uint64_t* peer_ptrs, uint64_t mc_ptr
 
 // Reduce-scatter (AVG) into a local fp32 shard; partial_sq: >= pdb200_nvl_rs_grid(shard_numel) floats of scratch whose
 // sum is the shard's squared L2 norm (fold with pdb200_l2norm / torch.sum).
+static int g_rs_max_ctas = 0;     // 0 = 4 CTAs per SM; set lower when the kernel should leave the SMs to overlapping GEMMs
+PDB_EXPORT int pdb200_nvl_set_rs_max_ctas(int n) {
+  g_rs_max_ctas = n;
+  return 0;
+}
 PDB_EXPORT int pdb200_nvl_rs_grid(int64_t shard_numel) {
   int64_t blocks = (shard_numel / 8 + 255) / 256;
-  const int64_t cap = (int64_t)sm_count() * 4;
+  const int64_t cap = g_rs_max_ctas > 0 ? g_rs_max_ctas : (int64_t)sm_count() * 4;
   if (blocks > cap) blocks = cap;
   return (int)(blocks < 1 ? 1 : blocks);
 }
@@ -433,4 +466,27 @@ PDB_EXPORT int pdb200_nvl_vocab_embed(const uint64_t* peer_ptrs, int nranks, int
   }
   barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
   return check_launch("nvl_vocab_embed");
+}
+
+// K3 stand-alone: gathered[r * shard_bytes ...] on every rank = rank r's shard.  src_off: this rank's shard inside its
+// own segment; dst_off: the gathered buffer (same offset in every segment).  The leading barrier certifies that every
+// rank is ready to have that buffer overwritten, the trailing one that every shard has landed everywhere.
+PDB_EXPORT int pdb200_nvl_allgather(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t src_off,
+                                    int64_t dst_off, int64_t shard_bytes, int64_t pad_off, int64_t epoch, int max_ctas,
+                                    void* stream) {
+  PDB_REQUIRE(nranks >= 1 && nranks <= kMaxRanks, "nvl: nranks %d out of range (1..%d)", nranks, kMaxRanks);
+  PDB_REQUIRE(shard_bytes % 16 == 0 && src_off % 16 == 0 && dst_off % 16 == 0, "nvl_allgather: 16-byte granularity");
+  cudaStream_t st = (cudaStream_t)stream;
+  Peers P = make_peers(peer_ptrs, mc_ptr, nranks, rank);
+  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+  const int64_t nvec = shard_bytes / 16;
+  if (nvec > 0) {
+    int64_t blocks = (nvec + 1023) / 1024;
+    const int64_t cap = max_ctas > 0 ? max_ctas : (int64_t)sm_count() * 4;
+    if (blocks > cap) blocks = cap;
+    allgather_push_kernel<<<(unsigned)(blocks < 1 ? 1 : blocks), 256, 0, st>>>(P, (uint64_t)src_off, (uint64_t)dst_off, nvec);
+    if (int e = check_launch("allgather_push")) return e;
+  }
+  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
+  return check_launch("nvl_allgather");
 }

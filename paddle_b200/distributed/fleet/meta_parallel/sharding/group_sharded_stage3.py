@@ -44,6 +44,117 @@ class _Unit:
         self.pending_grads = 0
 
 
+class _NvlTransport:
+    """Stage-3 traffic over NVLink symmetric memory instead of NCCL (K3 push all-gather, K2-pass-1 pull reduce-scatter).
+
+    Every rank keeps its parameter slices inside one symmetric arena; gathered parameters live in a small ring of
+    arena slots (a layer is gathered into the next slot while the previous layer computes), gradients are staged in
+    two arena buffers from which every owner pulls and averages its slice through the switch.  All transport kernels
+    run on one side stream in the same order on every rank; the tcgen05 GEMMs leave >90 % of the issue slots idle, so
+    the copy kernels co-reside with them on the SMs."""
+    SLOTS = 4
+
+    def __init__(self, group, params, device):
+        from paddle_b200.parallel import symm
+        n = group.nranks
+        al = lambda b: (b + 255) // 256 * 256   # noqa: E731
+        slice_bytes = sum(al(_padded_numel(p, n) // n * p.element_size()) for p in params)
+        self.max_param_bytes = max(al(_padded_numel(p, n) * p.element_size()) for p in params)
+        self.slot_bytes = self.max_param_bytes   # grown by the owner once units are known (see reserve)
+        self._pending = (group, slice_bytes, device)
+        self.symm = symm
+        self.arena = None
+
+    def reserve(self, max_unit_bytes):
+        group, slice_bytes, device = self._pending
+        self.slot_bytes = max(self.slot_bytes, max_unit_bytes)
+        total = slice_bytes + self.SLOTS * self.slot_bytes + 2 * self.max_param_bytes + (8 << 20)
+        self.arena = self.symm.SymmArena(group, total)
+        self.stream = torch.cuda.Stream(device=device)
+        import os
+        # grid caps of the transport kernels (0 = library default); measured: capping them exposes transfer time
+        self.ag_ctas = int(os.environ.get("PDB200_STAGE3_AG_CTAS", "0"))
+        self.symm.lib.kernels.pdb200_nvl_set_rs_max_ctas(int(os.environ.get("PDB200_STAGE3_RS_CTAS", "0")))
+        self.slots = None
+        self.slot_owner = [None] * self.SLOTS
+        self.next_slot = 0
+        self.gstage = None
+        self.gstage_done = [None, None]
+        self.next_gstage = 0
+        self.rs_scratch = None
+
+    def finish_layout(self):
+        """Called after every slice has been placed: the ring and the gradient stages take the rest of the arena."""
+        self.slots = [self.arena.empty((self.slot_bytes,), torch.uint8) for _ in range(self.SLOTS)]
+        self.gstage = [self.arena.empty((self.max_param_bytes,), torch.uint8)]
+
+    def new_slice(self, numel, dtype):
+        return self.arena.empty((numel,), dtype)
+
+    def _view(self, buf, byte_off, numel, dtype):
+        arena, off = buf._symm
+        t = arena.tensor(off + byte_off, (numel,), dtype)
+        t._symm = (arena, off + byte_off)
+        return t
+
+    def gather(self, unit):
+        slot = None
+        for k in range(self.SLOTS):                 # next slot whose occupant has been released
+            c = (self.next_slot + k) % self.SLOTS
+            prev = self.slot_owner[c]
+            if prev is None or prev is unit or not (prev.gathered or prev.gather_task is not None):
+                slot = c
+                break
+        if slot is None:
+            names = [type(o.layer).__name__ + ":" + (o.params[0].name or "?") for o in self.slot_owner]
+            raise RuntimeError(f"stage-3 gather ring ({self.SLOTS} slots) is full: {names}")
+        self.next_slot = (slot + 1) % self.SLOTS
+        self.slot_owner[slot] = unit
+        cur = torch.cuda.current_stream()
+        ev = torch.cuda.Event()
+        ev.record(cur)           # the slot's previous contents and this rank's slices are final up to here
+        fulls = []
+        with torch.cuda.stream(self.stream):
+            self.stream.wait_event(ev)
+            off = 0
+            for p in unit.params:
+                full = self._view(self.slots[slot], off, p._gs_padded, p.dtype)
+                self.symm.all_gather_push(p.fw_storage._symm_view, full, max_ctas=self.ag_ctas)
+                fulls.append((p, full))
+                off += (p._gs_padded * p.element_size() + 255) // 256 * 256
+            done = torch.cuda.Event()
+            done.record(self.stream)
+        return fulls, done
+
+    def reduce_scatter(self, p, grad, per, out_dtype):
+        """Everything (staging copy, pull + average, cast) runs on the transport stream; the compute stream only
+        records "gradient ready" and later waits for ``done``."""
+        cur = torch.cuda.current_stream()
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        grad.record_stream(self.stream)
+        with torch.cuda.stream(self.stream):
+            self.stream.wait_event(ev)
+            stage = self._view(self.gstage[0], 0, p._gs_padded, grad.dtype)   # one buffer: the stream serialises its reuse
+            flat = grad.reshape(-1)
+            stage[: flat.numel()].copy_(flat)
+            if flat.numel() != p._gs_padded:
+                stage[flat.numel():].zero_()
+            acc = torch.empty(per, dtype=torch.float32, device=grad.device)
+            scratch = torch.empty(self.symm.lib.kernels.pdb200_nvl_rs_grid(int(per)), dtype=torch.float32, device=grad.device)
+            self.symm.reduce_scatter_avg(stage, self.arena.rank * per, per, acc, scratch)
+            out = acc if out_dtype == torch.float32 else acc.to(out_dtype)
+            done = torch.cuda.Event()
+            done.record(self.stream)
+        out.record_stream(cur)
+        return out, done
+
+    def close(self):
+        if self.arena is not None:
+            self.arena.close()
+            self.arena = None
+
+
 class _BackwardGather(torch.autograd.Function):
     """Identity on the layer outputs whose backward re-gathers the layer's parameters first."""
 
@@ -87,9 +198,13 @@ class GroupShardedStage3(Layer):
         self._slice_params = []
         self._grad_tasks = []
         self._use_main_grad = False
+        self._nvl = None
         if pretrain_sync_models:
             self._sync_params_and_buffers()
+        self._init_transport()
         self._segment_rank_params()
+        if self._nvl is not None:
+            self._nvl.finish_layout()
         self._register_hooks()
         self._redefine_opt()
 
@@ -101,6 +216,41 @@ class GroupShardedStage3(Layer):
             comm.broadcast(p, src, self._group)
         for b in self._layer.buffers():
             comm.broadcast(b, src, self._group)
+
+    def _init_transport(self):
+        """Use the NVLink symmetric-memory transport when the group is one NVSwitch node and every slice keeps the
+        16-byte granularity of the copy kernels; otherwise NCCL (also the numerical oracle: FLAGS_use_fused_comm=0)."""
+        from paddle_b200.framework.flags import flag
+        from paddle_b200.parallel import symm
+        dev = next(iter(self._layer.parameters())).device
+        # opt-in: measured on 2 x B200 (Llama-2 7B, b=2): NCCL transport 397 ms/step, this transport 406-425 ms/step
+        if not flag("stage3_nvl_transport") or dev.type != "cuda" or not symm.available(self._group):
+            return
+        if not hasattr(symm.lib.kernels.require(), "pdb200_nvl_allgather"):
+            return
+        n = self._world_size
+        cands, unit_bytes, seen = [], 0, set()
+        for sub in self._layer.sublayers(include_self=True):
+            own = [p for p in sub.parameters(include_sublayers=False) if id(p) not in seen]
+            ub = 0
+            for p in own:
+                seen.add(id(p))
+                if p.requires_grad and p.numel() >= self._segment_size and not self._is_excluded(sub):
+                    if p.dtype not in (torch.bfloat16, torch.float32) or (_padded_numel(p, n) // n) % 8 != 0:
+                        return
+                    cands.append(p)
+                    ub += (_padded_numel(p, n) * p.element_size() + 255) // 256 * 256
+            unit_bytes = max(unit_bytes, ub)
+        if not cands:
+            return
+        try:
+            t = _NvlTransport(self._group, cands, dev)
+            t.reserve(unit_bytes)
+            self._nvl = t
+        except Exception as e:  # noqa: BLE001
+            import warnings
+            warnings.warn(f"stage 3: symmetric-memory transport unavailable ({e}); using NCCL")
+            self._nvl = None
 
     def _is_excluded(self, sub):
         return any((isinstance(e, type) and isinstance(sub, e)) or (isinstance(e, int) and id(sub) == e) or
@@ -134,9 +284,14 @@ class GroupShardedStage3(Layer):
         per = padded // n
         flat = torch.zeros(padded, dtype=p.dtype, device=p.device)
         flat[: p.numel()].copy_(p.detach().reshape(-1))
-        sl = flat[self._rank * per:(self._rank + 1) * per].clone()
+        if self._nvl is not None:
+            sl = self._nvl.new_slice(per, p.dtype)
+            sl.copy_(flat[self._rank * per:(self._rank + 1) * per])
+        else:
+            sl = flat[self._rank * per:(self._rank + 1) * per].clone()
         fw = Parameter(sl, requires_grad=True, name=p.name + "@slice")
         fw.data = sl
+        fw._symm_view = sl if self._nvl is not None else None
         fw.need_clip = getattr(p, "need_clip", True)
         fw.optimize_attr = getattr(p, "optimize_attr", {"learning_rate": 1.0})
         fw._origin_name = p.name
@@ -163,6 +318,10 @@ class GroupShardedStage3(Layer):
     def _launch_gather(self, unit):
         if unit.gathered or unit.gather_task is not None:
             return
+        if self._nvl is not None:
+            with torch.no_grad():
+                unit.gather_task = self._nvl.gather(unit)
+            return
         tasks = []
         with torch.no_grad():
             for p in unit.params:
@@ -175,6 +334,14 @@ class GroupShardedStage3(Layer):
         if unit.gathered:
             return
         self._launch_gather(unit)
+        if self._nvl is not None:
+            fulls, done = unit.gather_task
+            torch.cuda.current_stream().wait_event(done)
+            for p, full in fulls:
+                p.data = full[: p._gs_numel].view(p._gs_shape)
+            unit.gather_task = None
+            unit.gathered = True
+            return
         for p, full, t in unit.gather_task:
             t.wait()
             p.data = full[: p._gs_numel].view(p._gs_shape)
@@ -230,6 +397,14 @@ class GroupShardedStage3(Layer):
                 return
             n = self._world_size
             per = p._gs_padded // n
+            if self._nvl is not None:
+                out, done = self._nvl.reduce_scatter(p, g, per, torch.float32 if self._use_main_grad else p.dtype)
+                self._grad_tasks.append((p, out, done, None))
+                param.grad = None
+                unit.pending_grads -= 1
+                if unit.pending_grads <= 0:
+                    self._release(unit)
+                return
             flat = g.reshape(-1)
             if flat.numel() != p._gs_padded:
                 tmp = torch.zeros(p._gs_padded, dtype=g.dtype, device=g.device)
@@ -247,7 +422,10 @@ class GroupShardedStage3(Layer):
     @torch.no_grad()
     def _finish_grads(self):
         for p, out, t, _keep in self._grad_tasks:
-            t.wait()
+            if self._nvl is not None:
+                torch.cuda.current_stream().wait_event(t)
+            else:
+                t.wait()
             if self._dp_group is not None and self._dp_group.nranks > 1:
                 comm.all_reduce(out, ReduceOp.AVG, self._dp_group)
             if p.bw_storage is None:

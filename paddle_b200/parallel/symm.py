@@ -192,6 +192,32 @@ def reduce_scatter_norm(grad_buf, shard_start, shard_numel, out):
     return partial.sum().reshape(1)
 
 
+def all_gather_push(shard, full, max_ctas=0):
+    """K3 stand-alone: ``full[r*len(shard):(r+1)*len(shard)] = rank r's shard`` on every rank.  Both tensors live in
+    the same symmetric arena (``full`` at the same offset on every rank); runs on the current stream."""
+    arena, soff = shard._symm
+    arena2, doff = full._symm
+    assert arena is arena2, "shard and gathered buffer must share one arena"
+    from paddle_b200.lib import check
+    check(lib.kernels.pdb200_nvl_allgather(arena.peers_arg, arena.mc_ptr, arena.nranks, arena.rank, soff, doff,
+                                           shard.numel() * shard.element_size(), 0, arena.next_epoch(), int(max_ctas),
+                                           stream_ptr(shard.device)), "nvl_allgather")
+    return full
+
+
+def reduce_scatter_avg(grad_buf, shard_start, shard_numel, out, scratch):
+    """AVG reduce-scatter of a symmetric gradient buffer into a local fp32 shard (no host sync, norm partials in
+    ``scratch``, which must hold lib.kernels.pdb200_nvl_rs_grid(shard_numel) floats)."""
+    arena, goff = grad_buf._symm
+    from paddle_b200.lib import check
+    from paddle_b200.ops._util import ptr
+    check(lib.kernels.pdb200_nvl_reduce_scatter(arena.peers_arg, arena.mc_ptr, arena.nranks, arena.rank, goff,
+                                                dtype_code(grad_buf), int(shard_start), int(shard_numel), ptr(out),
+                                                ptr(scratch), 0, arena.next_epoch(), stream_ptr(grad_buf.device)),
+          "nvl_reduce_scatter")
+    return out
+
+
 _ce_scratch = {}
 
 

@@ -89,6 +89,35 @@ if mode in ("tp", "sp"):
     dist.destroy_process_group()
     sys.exit(0)
 
+if mode == "stage3":
+    # GroupSharded stage 3: K3 push all-gather + pull reduce-scatter over symmetric memory vs NCCL
+    from paddle_b200.distributed.sharding import group_sharded_parallel
+    dist.init_parallel_env()
+    r = dist.get_rank()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    m = build()
+    opt = paddle.optimizer.AdamW(1e-3, parameters=m.parameters(), multi_precision=True,
+                                 grad_clip=nn.ClipGradByGlobalNorm(0.05))
+    paddle.set_flags({"FLAGS_stage3_nvl_transport": bool(flag("use_fused_comm"))})
+    model, opt, _ = group_sharded_parallel(m, opt, level="p_g_os")
+    used_fused = model._nvl is not None
+    assert used_fused == bool(flag("use_fused_comm")), (used_fused, flag("use_fused_comm"))
+    for s in range(4):
+        x, y = data(s, r, dev)
+        ((model(x) - y).float() ** 2).mean().backward()
+        opt.step()
+        opt.clear_grad()
+    torch.cuda.synchronize()
+    model.get_all_parameters()
+    torch.save({k: v.detach().float().cpu() for k, v in m.state_dict().items()}, f"{out}.{r}.pt")
+    print(f"fused_vs_nccl stage3 fused={used_fused} ok", r, flush=True)
+    from paddle_b200.parallel import symm
+    if model._nvl is not None:
+        model._nvl.close()
+    symm.release_all()
+    dist.destroy_process_group()
+    sys.exit(0)
+
 if mode == "dp":
     dist.init_parallel_env()
     r = dist.get_rank()
