@@ -119,6 +119,10 @@ PDB_API int pdb200_flash_attn_fwd(const void* q, const void* k, const void* v, v
 PDB_API int64_t pdb200_flash_attn_bwd_workspace_bytes(int64_t b, int64_t sq, int64_t sk, int64_t hq, int64_t hk, int64_t d);
 PDB_API int pdb200_flash_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* d_o, const float* lse, void* dq, void* dk, void* dv, void* workspace, int64_t workspace_bytes, int64_t b, int64_t sq, int64_t sk, int64_t hq, int64_t hk, int64_t d, float scale, int causal, int dtype, void* stream);
 
+/* K9 / K10 MoE dispatch / combine over NVLink symmetric memory with device-side routing (csrc/kernels/moe_nvl.cu). */
+PDB_API int pdb200_moe_dispatch(const uint64_t* peer_ptrs, int nranks, int rank, int64_t counts_off, int64_t slab_off, int64_t slab_rows, const void* src, const int64_t* pos, int div, const int64_t* lec, int n_expert_local, int64_t n_slots, int row_bytes, int32_t* route_rank, int32_t* route_row, int64_t* recv_counts, int32_t* overflow, int64_t pad_off, int64_t epoch, void* stream);
+PDB_API int pdb200_moe_pull(const uint64_t* peer_ptrs, int nranks, int rank, int64_t slab_off, const int32_t* route_rank, const int32_t* route_row, const int64_t* inv, int64_t n_entries, void* out, int row_bytes, int sum_over_k, int dtype, int64_t pad_off, int64_t epoch, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

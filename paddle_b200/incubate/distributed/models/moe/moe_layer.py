@@ -99,6 +99,40 @@ class MoELayer(Layer):
         for p in self.experts.parameters():
             p.no_sync = True     # experts differ per rank: skipped by sync_params_buffers (Appendix B.12)
 
+    def _forward_fused(self, inp, value, gate, origin_shape, mp_rank, mp_size):
+        """K9 / K10: dispatch and combine through NVLink symmetric memory with device-side routing; the only host
+        read is the per-expert row counts that size the expert GEMMs."""
+        from paddle_b200 import ops
+        from paddle_b200.parallel import moe_fused
+        topk = gate.shape[1] if gate.dim() == 2 else 1
+        assert topk == self.top_k
+        with torch.no_grad():
+            lec = ops.number_count(gate, self.num_expert * self.world_size)
+            pos = ops.assign_pos(gate, torch.cumsum(lec, 0))
+        x, counts, meta = moe_fused.dispatch(inp, pos, lec, self.group, self.num_expert, topk)
+
+        def experts_fwd(x):
+            if x.shape[0] == 0:
+                return x
+            ys, last = [], 0
+            for idx, c in enumerate(counts):
+                if c <= 0:
+                    continue
+                ys.append(self.experts[idx](x[last:last + c]))
+                last += c
+            return torch.cat(ys, 0)
+        if self.recompute_interval <= 0 or x.shape[0] == 0:
+            x = experts_fwd(x)
+        else:
+            from paddle_b200.distributed.fleet.recompute import recompute
+            x = recompute(experts_fwd, x)
+        x = moe_fused.combine(x, meta).reshape(-1, self.top_k, self.d_model)
+        value = value.reshape(x.shape[0], 1, self.top_k).to(x.dtype)
+        x = torch.bmm(value, x).reshape(-1, self.d_model)
+        if mp_size > 1:
+            x = _AllGatherMP.apply(x, mp_rank, mp_size, self.mp_group)
+        return x.reshape(origin_shape)
+
     def forward(self, inp):
         assert inp.dim() == 3
         origin_shape = inp.shape
@@ -109,6 +143,9 @@ class MoELayer(Layer):
         if mp_size > 1:
             inp = _SliceMP.apply(inp, mp_rank, mp_size, self.mp_group)
         value, gate = self.gate(inp)
+        from paddle_b200.parallel import moe_fused
+        if self.world_size > 1 and moe_fused.available(self.group, inp):
+            return self._forward_fused(inp, value, gate, origin_shape, mp_rank, mp_size)
         pos, lec, gec, fwd_expert_count = prepare_forward(gate, self.num_expert, self.world_size, self.group)
         topk = gate.shape[1] if gate.dim() == 2 else 1
         assert topk == self.top_k

@@ -26,6 +26,12 @@ def test_nvl_fused_kernels_match_nccl():
     assert "nvl_fused ok" in out.stdout
 
 
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_moe_fused_dispatch_combine_matches_nccl():
+    out = _run("moe_fused.py", min(torch.cuda.device_count(), 8))
+    assert "moe_fused ok" in out.stdout
+
+
 def _run_env(script, nproc, args, env_extra, port):
     env = dict(os.environ)
     env["PYTHONPATH"] = ROOT + os.pathsep + env.get("PYTHONPATH", "")
