@@ -272,8 +272,7 @@ __global__ void ce_combine_symm_kernel(Peers P, uint64_t stats_off, const int64_
 // Parameter all-gather as a push: every rank stores its shard into slot `rank` of the gathered buffer of ALL ranks -
 // one multimem.st per 16 bytes when the segment has a multicast mapping (the switch replicates it), a loop of peer
 // stores otherwise.  4 vectors per thread per trip keep enough bytes in flight to cover the NVLink round trip.
-__global__ void __launch_bounds__(256) allgather_push_kernel(Peers P, uint64_t src_off, uint64_t dst_off, int64_t nvec) {
-  const uint4* src = reinterpret_cast<const uint4*>(P.ptr[P.rank] + src_off);
+__global__ void __launch_bounds__(256) allgather_push_kernel(Peers P, const uint4* __restrict__ src, uint64_t dst_off, int64_t nvec) {
   const uint64_t dst0 = dst_off + (uint64_t)P.rank * (uint64_t)nvec * 16;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += 4 * stride) {
@@ -484,9 +483,32 @@ PDB_EXPORT int pdb200_nvl_allgather(const uint64_t* peer_ptrs, uint64_t mc_ptr, 
     int64_t blocks = (nvec + 1023) / 1024;
     const int64_t cap = max_ctas > 0 ? max_ctas : (int64_t)sm_count() * 4;
     if (blocks > cap) blocks = cap;
-    allgather_push_kernel<<<(unsigned)(blocks < 1 ? 1 : blocks), 256, 0, st>>>(P, (uint64_t)src_off, (uint64_t)dst_off, nvec);
+    allgather_push_kernel<<<(unsigned)(blocks < 1 ? 1 : blocks), 256, 0, st>>>(
+        P, reinterpret_cast<const uint4*>(peer_ptrs[rank] + (uint64_t)src_off), (uint64_t)dst_off, nvec);
     if (int e = check_launch("allgather_push")) return e;
   }
   barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
   return check_launch("nvl_allgather");
+}
+
+// Same push, but the shard is read from ordinary (non-symmetric) device memory: only the gathered buffer has to live
+// in the symmetric segment.  Used by the sequence-parallel all-gather in front of a GEMM (K5).
+PDB_EXPORT int pdb200_nvl_allgather_from(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, const void* src,
+                                         int64_t dst_off, int64_t shard_bytes, int64_t pad_off, int64_t epoch,
+                                         int max_ctas, void* stream) {
+  PDB_REQUIRE(nranks >= 1 && nranks <= kMaxRanks, "nvl: nranks %d out of range (1..%d)", nranks, kMaxRanks);
+  PDB_REQUIRE(shard_bytes % 16 == 0 && ((uintptr_t)src & 15) == 0 && dst_off % 16 == 0, "nvl_allgather_from: 16-byte granularity");
+  cudaStream_t st = (cudaStream_t)stream;
+  Peers P = make_peers(peer_ptrs, mc_ptr, nranks, rank);
+  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+  const int64_t nvec = shard_bytes / 16;
+  if (nvec > 0) {
+    int64_t blocks = (nvec + 1023) / 1024;
+    const int64_t cap = max_ctas > 0 ? max_ctas : (int64_t)sm_count() * 4;
+    if (blocks > cap) blocks = cap;
+    allgather_push_kernel<<<(unsigned)(blocks < 1 ? 1 : blocks), 256, 0, st>>>(P, reinterpret_cast<const uint4*>(src), (uint64_t)dst_off, nvec);
+    if (int e = check_launch("allgather_push")) return e;
+  }
+  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
+  return check_launch("nvl_allgather_from");
 }

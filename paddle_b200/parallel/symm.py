@@ -262,6 +262,22 @@ def ag_gemm(x_shard, weight, group, bias=None, trans_b=False, act=None):
     arena = get_arena(group)
     rows, K = x_shard.shape
     N = weight.shape[0] if trans_b else weight.shape[1]
+    if flag("ag_gemm_push") and hasattr(lib.kernels.require(), "pdb200_nvl_allgather_from"):
+        # One NVLink pass: every rank multicasts its shard into all ranks' gathered buffer, then the CTA-pair GEMM
+        # runs on local memory.  (Reading peer tiles from inside the GEMM re-fetches each A tile once per N tile
+        # over NVLink - 15x the bytes for the 13B qkv projection - and was NVLink-bound.)
+        from paddle_b200.ops import gemm as G
+        full = _staging(arena, "ag_full", (rows * arena.nranks, K), torch.bfloat16)
+        xs = x_shard.contiguous()
+        check(lib.kernels.pdb200_nvl_allgather_from(arena.peers_arg, arena.mc_ptr, arena.nranks, arena.rank, ptr(xs),
+                                                    full._symm[1], xs.numel() * 2, 0, arena.next_epoch(), 0,
+                                                    stream_ptr(xs.device)), "nvl_allgather_from")
+        if G.supported(full, weight, False, trans_b):
+            return G.gemm(full, weight, False, trans_b, bias=bias, act=act)
+        out = torch.matmul(full, weight.t() if trans_b else weight)
+        if bias is not None:
+            out = out + bias
+        return {"gelu": torch.nn.functional.gelu, "relu": torch.relu}.get(act, lambda t: t)(out)
     buf = _staging(arena, "ag_a", (rows, K), torch.bfloat16)
     buf.copy_(x_shard)
     out = torch.empty(rows * arena.nranks, N, dtype=torch.bfloat16, device=x_shard.device)
