@@ -268,6 +268,39 @@ __global__ void ce_combine_symm_kernel(Peers P, uint64_t stats_off, const int64_
   loss[row] = (labels[row] == ignore_index) ? 0.f : l - tgt;
 }
 
+// Sum (not average) reduce-scatter of a symmetric bf16 buffer into a local bf16 shard: the tail of GEMM ->
+// reduce-scatter when the GEMM wrote its partial product into symmetric memory.  With NVLS the switch adds the n
+// copies (fp32 accumulation) and each GPU only receives its own slice once.
+__global__ void __launch_bounds__(256) rs_sum_bf16_kernel(Peers P, uint64_t src_off, int64_t shard_start, int64_t shard_numel,
+                                                         __nv_bfloat16* __restrict__ out) {
+  const int64_t n8 = shard_numel / 8;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
+    const uint64_t off = src_off + (uint64_t)(shard_start + i * 8) * 2;
+    uint4 o;
+    if (P.mc) {
+      uint32_t r[4];
+      mm_ld_reduce_bf16x8(reinterpret_cast<const void*>(P.mc + off), r);
+      o = make_uint4(r[0], r[1], r[2], r[3]);
+    } else {
+      float acc[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+      for (int p = 0; p < P.nranks; ++p) {
+        Vec<__nv_bfloat16> x;
+        x.load(reinterpret_cast<const __nv_bfloat16*>(P.ptr[p] + off));
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += x.f(j);
+      }
+      Vec<__nv_bfloat16> v;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v.set(j, acc[j]);
+      o = v.raw;
+    }
+    *reinterpret_cast<uint4*>(out + i * 8) = o;
+  }
+}
+
 // ---------------------------------------------------------------------------------------------- K3 (stand-alone)
 // Parameter all-gather as a push: every rank stores its shard into slot `rank` of the gathered buffer of ALL ranks -
 // one multimem.st per 16 bytes when the segment has a multicast mapping (the switch replicates it), a loop of peer
@@ -511,4 +544,27 @@ PDB_EXPORT int pdb200_nvl_allgather_from(const uint64_t* peer_ptrs, uint64_t mc_
   }
   barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
   return check_launch("nvl_allgather_from");
+}
+
+// out[shard_numel] (bf16, local) = sum over ranks of the symmetric bf16 buffer at src_off, elements
+// [shard_start, shard_start + shard_numel).  Leading barrier: every rank's buffer is complete; trailing: all pulled.
+PDB_EXPORT int pdb200_nvl_rs_sum_bf16(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t src_off,
+                                      int64_t shard_start, int64_t shard_numel, void* out, int64_t pad_off, int64_t epoch,
+                                      void* stream) {
+  PDB_REQUIRE(nranks >= 1 && nranks <= kMaxRanks, "nvl: nranks %d out of range (1..%d)", nranks, kMaxRanks);
+  PDB_REQUIRE(shard_numel % 8 == 0 && shard_start % 8 == 0 && src_off % 16 == 0 && ((uintptr_t)out & 15) == 0,
+              "nvl_rs_sum_bf16: 16-byte granularity");
+  cudaStream_t st = (cudaStream_t)stream;
+  Peers P = make_peers(peer_ptrs, mc_ptr, nranks, rank);
+  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+  if (shard_numel > 0) {
+    int64_t blocks = (shard_numel / 8 + 255) / 256;
+    const int64_t cap = (int64_t)sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    rs_sum_bf16_kernel<<<(unsigned)(blocks < 1 ? 1 : blocks), 256, 0, st>>>(P, (uint64_t)src_off, shard_start, shard_numel,
+                                                                          (__nv_bfloat16*)out);
+    if (int e = check_launch("rs_sum_bf16")) return e;
+  }
+  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
+  return check_launch("nvl_rs_sum_bf16");
 }

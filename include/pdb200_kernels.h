@@ -97,6 +97,8 @@ PDB_API int pdb200_nvl_reduce_scatter(const uint64_t* peer_ptrs, uint64_t mc_ptr
 /* K3 stand-alone: parameter all-gather as a multicast push (every rank stores its shard into slot `rank` of all ranks' buffers). */
 PDB_API int pdb200_nvl_allgather(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t src_off, int64_t dst_off, int64_t shard_bytes, int64_t pad_off, int64_t epoch, int max_ctas, void* stream);
 PDB_API int pdb200_nvl_allgather_from(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, const void* src, int64_t dst_off, int64_t shard_bytes, int64_t pad_off, int64_t epoch, int max_ctas, void* stream);
+/* Sum reduce-scatter of a symmetric bf16 buffer into a local bf16 shard (tail of GEMM -> reduce-scatter; NVLS in-switch add). */
+PDB_API int pdb200_nvl_rs_sum_bf16(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t src_off, int64_t shard_start, int64_t shard_numel, void* out, int64_t pad_off, int64_t epoch, void* stream);
 PDB_API int pdb200_nvl_ce_combine(const uint64_t* peer_ptrs, int nranks, int rank, int64_t stats_off, const int64_t* labels, float* loss, float* lse, int64_t rows, int64_t ignore_index, int64_t pad_off, int64_t epoch, void* stream);
 /* K7 vocab-parallel embedding forward as a gather from the owning rank's table shard (replaces masked lookup + all-reduce). */
 PDB_API int pdb200_nvl_vocab_embed(const uint64_t* peer_ptrs, int nranks, int rank, int64_t table_off, const int64_t* ids, void* out, int64_t n_tokens, int hidden, int64_t vocab_per_rank, int dtype, int64_t pad_off, int64_t epoch, void* stream);

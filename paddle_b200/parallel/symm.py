@@ -298,6 +298,15 @@ def gemm_rs(x, weight, group, trans_b=False):
     n = arena.nranks
     rows = M // n
     N = weight.shape[0] if trans_b else weight.shape[1]
+    if flag("gemm_rs_pull") and hasattr(lib.kernels.require(), "pdb200_nvl_rs_sum_bf16"):
+        # CTA-pair GEMM writes the partial product into symmetric memory; every owner then pulls its rows through the
+        # switch (multimem.ld_reduce adds the n copies in flight).  Measured faster than pushing tiles from the epilogue.
+        part = _gemm_into_symmetric(arena, x, weight, trans_b, "rs_part")
+        out = torch.empty(rows, N, dtype=torch.bfloat16, device=x.device)
+        check(lib.kernels.pdb200_nvl_rs_sum_bf16(arena.peers_arg, arena.mc_ptr, n, arena.rank, part._symm[1],
+                                                 arena.rank * rows * N, rows * N, ptr(out), 0, arena.next_epoch(),
+                                                 stream_ptr(x.device)), "nvl_rs_sum_bf16")
+        return out
     stage = _staging(arena, "rs_stage", (n, rows, N), torch.bfloat16)
     out = torch.empty(rows, N, dtype=torch.bfloat16, device=x.device)
     xc = x.contiguous()
@@ -305,6 +314,21 @@ def gemm_rs(x, weight, group, trans_b=False):
                                           rows, N, K, int(trans_b), 0, arena.next_epoch(), stream_ptr(x.device)),
           "gemm_bf16_rs")
     return out
+
+
+def _gemm_into_symmetric(arena, x, weight, trans_b, tag):
+    """x @ weight written straight into a symmetric staging buffer by the tcgen05 GEMM (no copy)."""
+    from paddle_b200.lib import check
+    from paddle_b200.ops._util import ptr
+    M, K = x.shape
+    N = weight.shape[0] if trans_b else weight.shape[1]
+    part = _staging(arena, tag, (M, N), torch.bfloat16)
+    xc = x.contiguous()
+    fn = lib.kernels.pdb200_gemm_bf16_pair if (M >= 512 and N >= 512 and flag("gemm_cta_pair") and
+                                               hasattr(lib.kernels.require(), "pdb200_gemm_bf16_pair")) \
+        else lib.kernels.pdb200_gemm_bf16
+    check(fn(ptr(xc), ptr(weight), ptr(part), None, M, N, K, 0, int(trans_b), 1, 0.0, 0, stream_ptr(x.device)), "gemm_bf16")
+    return part
 
 
 def gemm_ar(x, weight, group, trans_b=False):
@@ -318,6 +342,10 @@ def gemm_ar(x, weight, group, trans_b=False):
     n = arena.nranks
     rows = M // n
     N = weight.shape[0] if trans_b else weight.shape[1]
+    if flag("gemm_rs_pull"):
+        part = _gemm_into_symmetric(arena, x, weight, trans_b, "ar_part")
+        allreduce_(part)                       # K1: NVLS two-shot all-reduce in place
+        return part.clone()
     stage = _staging(arena, "rs_stage", (n, rows, N), torch.bfloat16)
     out = _staging(arena, "ar_out", (M, N), torch.bfloat16)
     xc = x.contiguous()

@@ -54,4 +54,6 @@ def test_fused_training_matches_nccl_training(mode, tmp_path):
         a = torch.load(tmp_path / f"nccl.{r}.pt")
         b = torch.load(tmp_path / f"fused.{r}.pt")
         for k in a:
-            torch.testing.assert_close(a[k], b[k], rtol=2e-2, atol=2e-3, msg=lambda s: f"{mode} rank {r} {k}: {s}")
+            # AdamW moves a weight by +-lr per step whatever the gradient's magnitude, so a near-zero gradient whose
+            # sign differs between the two reduction orders costs up to 2*lr per step: 4 steps x 2e-3 bounds the gap
+            torch.testing.assert_close(a[k], b[k], rtol=2e-2, atol=8e-3, msg=lambda s: f"{mode} rank {r} {k}: {s}")
