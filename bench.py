@@ -43,6 +43,9 @@ def parse():
     p.add_argument("--seq", type=int, default=4096)
     p.add_argument("--recompute", type=int, default=int(os.environ.get("BENCH_RECOMPUTE", "0")))
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--library-baseline", action="store_true",
+                   help="same model and step through cuBLAS / cuDNN / torch kernels and NCCL only (this repo's sm_100a "
+                        "kernels and fused NVLink paths switched off): the 'Baseline B' column of BASELINE.md")
     return p.parse_args()
 
 
@@ -150,6 +153,8 @@ def main():
     if world > 1:
         paddle.distributed.init_parallel_env()
 
+    if args.library_baseline:
+        paddle.set_flags({"FLAGS_use_native_kernels": False, "FLAGS_use_fused_comm": False, "FLAGS_use_tcgen05_gemm": False})
     cfg = build_config(args.model)
     cfg.recompute = bool(args.recompute)
     paddle.seed(1234)
@@ -234,7 +239,8 @@ def main():
             "value": round(value, 1), "unit": "tokens/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": round(ms_per_step, 3), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": (value / BASELINE_TOKENS_PER_S) if BASELINE_TOKENS_PER_S else None,
-            "dtype": "bf16", "data": "synthetic tokens, random-init weights", "impl": "ours",
+            "dtype": "bf16", "data": "synthetic tokens, random-init weights",
+            "impl": "ours" if not args.library_baseline else "library-baseline (cuBLAS/cuDNN/torch + NCCL, our kernels off)",
             "config": {"model": args.model, "global_batch": B * world, "seq_len": S, "parallelism": parallelism,
                        "optimizer": "AdamW multi_precision (fp32 master, fp32 moments) + global-norm clip",
                        "recompute": bool(args.recompute),

@@ -49,12 +49,16 @@ def main():
     ap.add_argument("--layers", type=int, default=0)
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--seq", type=int, default=4096)
+    ap.add_argument("--library-baseline", action="store_true",
+                    help="cuBLAS / cuDNN / torch kernels + NCCL only (Baseline B of BASELINE.md)")
     args = ap.parse_args()
+    if args.library_baseline:
+        paddle.set_flags({"FLAGS_use_native_kernels": False, "FLAGS_use_fused_comm": False, "FLAGS_use_tcgen05_gemm": False})
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
-    res = {"impl": "ours", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "dtype": "bf16",
+    res = {"impl": "library-baseline" if args.library_baseline else "ours", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "dtype": "bf16",
            "data": "synthetic, random-init weights", "higher_is_better": True}
 
     if args.config == "resnet50_dp":
