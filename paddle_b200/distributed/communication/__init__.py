@@ -14,6 +14,8 @@ import numpy as np
 import torch
 import torch.distributed as tdist
 
+from . import check as _chk
+
 from .. import collective as C
 from ..collective import ReduceOp, Task, _finish, _in_group, _resolve, _state
 from .. import watchdog as _wd
@@ -52,6 +54,8 @@ def all_reduce(tensor, op=ReduceOp.SUM, group=None, sync_op=True, use_calc_strea
     g = _resolve(group)
     if not _in_group(g):
         return Task()
+    _chk.same_shape(tensor, tensor, C._state.backend, "all_reduce")
+    _chk.dynamic_check(tensor, 0, g, "all_reduce")
     tag = _wd.task_started(g, "all_reduce", tensor.numel(), sync_op)
     if _trivial(g):
         return _finish(None, sync_op, tag=tag)
@@ -123,8 +127,7 @@ def all_gather(tensor_or_tensor_list, tensor, group=None, sync_op=True, use_calc
     out = tensor_or_tensor_list
     tag = _wd.task_started(g, "all_gather", tensor.numel(), sync_op)
     if isinstance(out, torch.Tensor):
-        if out.numel() != tensor.numel() * n:
-            raise ValueError("all_gather: output tensor must hold nranks x input elements")
+        _chk.gather_like(out, tensor, n, C._state.backend, "all_gather")
         if _trivial(g):
             with torch.no_grad():
                 out.reshape(-1).copy_(tensor.reshape(-1))
@@ -176,8 +179,7 @@ def reduce_scatter(tensor, tensor_or_tensor_list, op=ReduceOp.SUM, group=None, s
     src = tensor_or_tensor_list
     tag = _wd.task_started(g, "reduce_scatter", tensor.numel() * n, sync_op)
     flat_in = torch.cat([t.reshape(-1) for t in src]) if isinstance(src, (list, tuple)) else src.contiguous().view(-1)
-    if flat_in.numel() != tensor.numel() * n:
-        raise ValueError("reduce_scatter: input must hold nranks x output elements")
+    _chk.scatter_like(tensor, flat_in, n, C._state.backend, "reduce_scatter")
     if _trivial(g):
         with torch.no_grad():
             tensor.copy_(flat_in.view_as(tensor))

@@ -1,0 +1,93 @@
+"""Auxiliary subsystems on CPU: comm argument checks (N7), epoch-range auto checkpoint (A3), auto-tuner (P36)."""
+import os
+
+import pytest
+import torch
+
+import paddle_b200 as paddle
+
+
+def test_comm_static_checks():
+    from paddle_b200.distributed.communication import check
+    a, b = torch.zeros(8), torch.zeros(4)
+    check.same_shape(a, a.clone(), "gloo", "all_reduce")
+    with pytest.raises(check.CommCheckError, match="elements"):
+        check.same_shape(a, b, "gloo", "all_reduce")
+    with pytest.raises(check.CommCheckError, match="dtype"):
+        check.same_shape(a, a.double(), "gloo", "broadcast")
+    check.gather_like(a, b, 2, "gloo", "all_gather")
+    with pytest.raises(check.CommCheckError, match="nranks x input"):
+        check.gather_like(a, b, 4, "gloo", "all_gather")
+    check.scatter_like(b, a, 2, "gloo", "reduce_scatter")
+    with pytest.raises(check.CommCheckError, match="nranks x output"):
+        check.scatter_like(b, a, 3, "gloo", "reduce_scatter")
+    with pytest.raises(check.CommCheckError, match="CUDA"):
+        check.check_place(a, "nccl")
+
+
+def test_auto_checkpoint_resumes(tmp_path, monkeypatch):
+    from paddle_b200.base.incubate.checkpoint import auto_checkpoint as acp
+    monkeypatch.setenv("PADDLE_RUNNING_ENV", "PADDLE_EDL_AUTO_CHECKPOINT")
+    monkeypatch.setenv("PADDLE_JOB_ID", "job7")
+    monkeypatch.setenv("PADDLE_EDL_HDFS_CHECKPOINT_PATH", str(tmp_path))
+    monkeypatch.setenv("PADDLE_EDL_SAVE_CHECKPOINT_INTER", "0")
+
+    def build():
+        paddle.seed(3)
+        m = paddle.nn.Linear(4, 4)
+        o = paddle.optimizer.SGD(0.1, parameters=m.parameters())
+        acp.unregister_all()
+        acp.register("model", m)
+        acp.register("opt", o)
+        return m, o
+
+    def train(m, o, epochs, crash_after=None):
+        seen = []
+        for e in acp.train_epoch_range(epochs):
+            x = torch.full((2, 4), float(e + 1))
+            m(x).sum().backward()
+            o.step()
+            o.clear_grad()
+            seen.append(e)
+            if crash_after is not None and e == crash_after:
+                break                       # the "crash": epoch e itself was not recorded as finished
+        return seen
+
+    m1, o1 = build()
+    assert train(m1, o1, 5, crash_after=2) == [0, 1, 2]
+    m2, o2 = build()                        # restart: state of the last finished epoch (1) is restored, resume at 2
+    seen = train(m2, o2, 5)
+    assert seen == [2, 3, 4]
+    # oracle: uninterrupted run
+    monkeypatch.setenv("PADDLE_JOB_ID", "job8")
+    m3, o3 = build()
+    assert train(m3, o3, 5) == [0, 1, 2, 3, 4]
+    torch.testing.assert_close(m2.weight, m3.weight)
+    assert sorted(os.listdir(tmp_path / "job7" / "default")) == ["epoch_3", "epoch_4"]
+
+
+def test_auto_tuner_grid_search_prunes_and_picks_best():
+    from paddle_b200.distributed.auto_tuner import AutoTuner
+    cfg = {"num_gpus": 8, "dp_degree": "auto", "mp_degree": "auto", "pp_degree": "auto", "sharding_degree": [1],
+           "sharding_stage": [1], "micro_batch_size": [1, 2], "use_recompute": [False],
+           "model_cfg": {"num_attention_heads": 32, "num_layers": 32, "hidden_size": 4096, "vocab_size": 32000,
+                         "global_batch_size": 16}}
+    tuner = AutoTuner(cfg)
+    ran = []
+
+    def run_trial(c):
+        ran.append(dict(c))
+        assert c["dp_degree"] * c["mp_degree"] * c["pp_degree"] == 8
+        if c["mp_degree"] == 1 and c["pp_degree"] == 1:
+            return {"error": "oom"}                               # pure DP of a big model does not fit
+        # synthetic throughput: TP costs 10 %/doubling, PP bubble, bigger micro batch helps
+        acc = 16 // c["dp_degree"] // c["micro_batch_size"]
+        thr = 1000.0 * 0.9 ** (c["mp_degree"].bit_length() - 1) * acc / (acc + c["pp_degree"] - 1) * (1 + 0.1 * c["micro_batch_size"])
+        return {"tokens_per_second": thr}
+    best = tuner.tune(run_trial)
+    assert best is not None and not best.get("error")
+    assert all(c["pp_degree"] == 1 or 16 // c["dp_degree"] // c["micro_batch_size"] >= c["pp_degree"] for c in ran)
+    # after (dp8, mbs2) went OOM the heavier-or-equal variants of the same split were pruned, the lighter one still ran
+    dp8 = [c for c in ran if c["dp_degree"] == 8]
+    assert [c["micro_batch_size"] for c in dp8] == [2, 1]
+    assert best["tokens_per_second"] == max(h["tokens_per_second"] for h in tuner.history_cfgs if "tokens_per_second" in h)
