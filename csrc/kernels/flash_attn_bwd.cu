@@ -80,7 +80,8 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 // ---------------------------------------------------------------------------------------------- dQ
 template <int D> struct DqSmem {
   static constexpr int kTile = 128 * D * 2;               // Q, dO, one K or V stage
-  static constexpr int kTotal = 6 * kTile + 1024 + 256;
+  static constexpr int kKStages = 3;                        // a K tile is held from S = Q K^T until dQ += dS K retires
+  static constexpr int kTotal = (4 + kKStages) * kTile + 1024 + 256;
 };
 
 template <int D>
@@ -94,19 +95,19 @@ flash_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sQ = smem;
   uint8_t* sDO = sQ + S::kTile;
-  uint8_t* sK = sDO + S::kTile;              // [2]
-  uint8_t* sV = sK + 2 * S::kTile;           // [2]
+  uint8_t* sK = sDO + S::kTile;              // [3]
+  uint8_t* sV = sK + S::kKStages * S::kTile; // [2]
   uint64_t* bars = reinterpret_cast<uint64_t*>(sV + 2 * S::kTile);
   uint64_t* qdo_full = bars;
-  uint64_t* k_full = bars + 1;               // [2]
-  uint64_t* k_empty = bars + 3;              // [2]
-  uint64_t* v_full = bars + 5;               // [2]
-  uint64_t* v_empty = bars + 7;              // [2]
-  uint64_t* sdp_full = bars + 9;
-  uint64_t* sdp_empty = bars + 10;
-  uint64_t* ds_ready = bars + 11;
-  uint64_t* dq_done = bars + 12;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 13);
+  uint64_t* k_full = bars + 1;               // [3]
+  uint64_t* k_empty = bars + 4;              // [3]
+  uint64_t* v_full = bars + 7;               // [2]
+  uint64_t* v_empty = bars + 9;              // [2]
+  uint64_t* sdp_full = bars + 11;
+  uint64_t* sdp_empty = bars + 12;
+  uint64_t* ds_ready = bars + 13;
+  uint64_t* dq_done = bars + 14;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 15);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_qt = p.sq / 128;
@@ -126,9 +127,11 @@ flash_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
   }
   if (warp == 1 && lane == 0) {
     mbar_init(qdo_full, 1);
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < S::kKStages; ++i) {
       mbar_init(&k_full[i], 1);
       mbar_init(&k_empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
       mbar_init(&v_full[i], 1);
       mbar_init(&v_empty[i], 1);
     }
@@ -159,8 +162,8 @@ flash_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
         tma_load_2d(sDO + kb * (128 * 128), &tm_do, qdo_full, h * D + kb * 64, q_row0);
       }
       for (int j = 0; j < n_kv; ++j) {
-        const int st = j & 1;
-        mbar_wait(&k_empty[st], ((j >> 1) & 1) ^ 1);
+        const int st = j % S::kKStages;
+        mbar_wait(&k_empty[st], ((j / S::kKStages) & 1) ^ 1);
         mbar_expect_tx(&k_full[st], S::kTile);
 #pragma unroll
         for (int kb = 0; kb < KB; ++kb)
@@ -183,13 +186,13 @@ flash_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
       constexpr uint32_t idesc_s = make_idesc_bf16(128, 128, 0, 0);    // [q][d] x [keys][d]^T
       constexpr uint32_t idesc_dq = make_idesc_bf16(128, D, 0, 1);     // dS [q][keys] x K [keys][d] (MN-major)
       auto issue_sdp = [&](int j) {
-        const int st = j & 1, ph = (j >> 1) & 1;
-        mbar_wait(&k_full[st], ph);
+        const int st = j & 1, ph = (j >> 1) & 1, kst = j % S::kKStages;
+        mbar_wait(&k_full[kst], (j / S::kKStages) & 1);
         mbar_wait(&v_full[st], ph);
         mbar_wait(sdp_empty, (j & 1) ^ 1);
         tc_fence_after();
         const uint32_t aq = smem_u32(sQ), ad = smem_u32(sDO);
-        const uint32_t bk = smem_u32(sK + st * S::kTile), bv = smem_u32(sV + st * S::kTile);
+        const uint32_t bk = smem_u32(sK + kst * S::kTile), bv = smem_u32(sV + st * S::kTile);
 #pragma unroll
         for (int k = 0; k < D / 16; ++k) {
           const uint32_t off = (k >> 2) * (128 * 128) + (k & 3) * 32;
@@ -204,7 +207,7 @@ flash_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
         umma_commit(&v_empty[st]);
       };
       auto issue_dq = [&](int j) {
-        const int st = j & 1;
+        const int st = j % S::kKStages;
         mbar_wait(ds_ready, j & 1);
         tc_fence_after();
         const uint32_t bk = smem_u32(sK + st * S::kTile);
