@@ -198,6 +198,10 @@ class GroupShardedStage3(Layer):
         self._slice_params = []
         self._grad_tasks = []
         self._use_main_grad = False
+        import os
+        # how many layers ahead parameters are gathered (the reference prefetches one, :849-896); two hides the
+        # gather of short layers (o_proj) behind the long ones
+        self._prefetch_depth = max(1, int(os.environ.get("PDB200_STAGE3_PREFETCH", "2")))
         self._nvl = None
         if pretrain_sync_models:
             self._sync_params_and_buffers()
@@ -363,8 +367,9 @@ class GroupShardedStage3(Layer):
             else:
                 try:
                     i = self._order_index[id(unit)]
-                    if i + 1 < len(self._order_fw):
-                        self._launch_gather(self._order_fw[i + 1])
+                    for k in range(1, self._prefetch_depth + 1):
+                        if i + k < len(self._order_fw):
+                            self._launch_gather(self._order_fw[i + k])
                 except KeyError:
                     pass
             return None
@@ -386,8 +391,10 @@ class GroupShardedStage3(Layer):
         if not self._order_learned:
             return
         i = self._order_index.get(id(unit))
-        if i is not None and i - 1 >= 0:
-            self._launch_gather(self._order_fw[i - 1])
+        if i is not None:
+            for k in range(1, self._prefetch_depth + 1):
+                if i - k >= 0:
+                    self._launch_gather(self._order_fw[i - k])
 
     def _make_grad_hook(self, unit, p):
         @torch.no_grad()

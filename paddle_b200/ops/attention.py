@@ -71,6 +71,11 @@ class _FlashFn(torch.autograd.Function):
 def _sdpa(q, k, v, causal, scale, dropout, mask, training):
     qt, kt, vt = q.transpose(1, 2), k.transpose(1, 2), v.transpose(1, 2)
     gqa = qt.shape[1] != kt.shape[1]
+    if causal and mask is None and q.shape[1] != k.shape[1]:
+        # flash-attention convention (and the native kernel's): the causal diagonal is aligned to the LAST key, i.e.
+        # query i sees keys <= i + (sk - sq); torch's is_causal aligns it to the first key instead
+        sq, sk = q.shape[1], k.shape[1]
+        mask = torch.ones(sq, sk, dtype=torch.bool, device=q.device).tril(sk - sq)
     out = TF.scaled_dot_product_attention(qt, kt, vt, attn_mask=mask, dropout_p=dropout if training else 0.0,
                                           is_causal=causal and mask is None, scale=scale, enable_gqa=gqa)
     return out.transpose(1, 2)

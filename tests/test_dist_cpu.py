@@ -29,6 +29,10 @@ def test_pipeline_matches_single_process(mode):
     run_dist("pipeline.py", 2, args=(mode,))
 
 
+def test_context_parallel_attention_matches_single_device():
+    run_dist("context_parallel.py", 2)
+
+
 def test_moe_expert_parallel_matches_dense():
     run_dist("moe.py", 2)
 
