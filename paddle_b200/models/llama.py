@@ -34,6 +34,7 @@ class LlamaConfig:
     initializer_range: float = 0.02
     tensor_parallel_degree: int = 1
     sequence_parallel: bool = False
+    context_parallel: str = ""          # "", "ulysses", "ring" or "allgather": attention over the fleet sep group
     recompute: bool = False
     recompute_granularity: str = "full"
     use_flash_attention: bool = True
@@ -119,13 +120,35 @@ class LlamaAttention(nn.Layer):
             qkv = qkv.transpose(0, 1)        # [s, b, .] -> [b, s, .]
         b, s = qkv.shape[0], qkv.shape[1]
         nq, nkv, d = self.num_heads, self.num_kv_heads, self.head_dim
-        sin, cos = _rope_tables(s, d, self.config.rope_theta, qkv.device)
-        q, k, v = paddle.ops.qkv_split_rope(qkv, nq, nkv, sin, cos, position_ids, use_neox_rotary_style=False)
-        out, _ = F.flash_attention(q, k, v, causal=True, training=self.training)
+        cp_group = _sep_group() if self.config.context_parallel else None
+        if cp_group is not None and cp_group.nranks > 1:
+            # this rank holds tokens [rank*s, (rank+1)*s) of the sequence: rotate with the global positions
+            sin, cos = _rope_tables(s * cp_group.nranks, d, self.config.rope_theta, qkv.device)
+            if position_ids is None:
+                position_ids = (torch.arange(s, device=qkv.device) + cp_group.rank * s)[None].expand(b, s)
+            q, k, v = paddle.ops.qkv_split_rope(qkv, nq, nkv, sin, cos, position_ids, use_neox_rotary_style=False)
+            from paddle_b200.distributed.fleet.utils import context_parallel as cp
+            fn = {"ulysses": cp.ulysses_attention, "ring": cp.ring_flash_attention,
+                  "allgather": cp.allgather_kv_attention}[self.config.context_parallel]
+            out = fn(q, k, v, cp_group, causal=True)
+        else:
+            sin, cos = _rope_tables(s, d, self.config.rope_theta, qkv.device)
+            q, k, v = paddle.ops.qkv_split_rope(qkv, nq, nkv, sin, cos, position_ids, use_neox_rotary_style=False)
+            out, _ = F.flash_attention(q, k, v, causal=True, training=self.training)
         out = out.reshape(b, s, nq * d)
         if sp:
             out = out.transpose(0, 1).contiguous()
         return self.o_proj(out)
+
+
+def _sep_group():
+    """The context-parallel (sep) group of the current fleet topology, if any."""
+    try:
+        from paddle_b200.distributed import fleet
+        hcg = fleet.get_hybrid_communicate_group()
+        return hcg.get_sep_parallel_group() if hcg is not None and hcg.get_sep_parallel_world_size() > 1 else None
+    except Exception:  # noqa: BLE001  (fleet not initialised)
+        return None
 
 
 _rope_cache = {}

@@ -33,6 +33,10 @@ def test_context_parallel_attention_matches_single_device():
     run_dist("context_parallel.py", 2)
 
 
+def test_llama_context_parallel_over_sep_group():
+    run_dist("llama_cp.py", 2)
+
+
 def test_moe_expert_parallel_matches_dense():
     run_dist("moe.py", 2)
 
