@@ -1,0 +1,46 @@
+"""paddle.fft (reference: python/paddle/fft.py) on torch.fft; ``axis``/``axes`` argument names kept."""
+from __future__ import annotations
+
+import torch
+
+
+def _1d(fn):
+    def f(x, n=None, axis=-1, norm="backward", name=None):
+        return fn(x, n=n, dim=axis, norm=norm)
+    f.__name__ = fn.__name__
+    return f
+
+
+def _nd(fn):
+    def f(x, s=None, axes=None, norm="backward", name=None):
+        return fn(x, s=s, dim=axes, norm=norm)
+    f.__name__ = fn.__name__
+    return f
+
+
+def _2d(fn):
+    def f(x, s=None, axes=(-2, -1), norm="backward", name=None):
+        return fn(x, s=s, dim=axes, norm=norm)
+    f.__name__ = fn.__name__
+    return f
+
+
+fft, ifft, rfft, irfft, hfft, ihfft = (_1d(getattr(torch.fft, n)) for n in ("fft", "ifft", "rfft", "irfft", "hfft", "ihfft"))
+fftn, ifftn, rfftn, irfftn = (_nd(getattr(torch.fft, n)) for n in ("fftn", "ifftn", "rfftn", "irfftn"))
+fft2, ifft2, rfft2, irfft2 = (_2d(getattr(torch.fft, n)) for n in ("fft2", "ifft2", "rfft2", "irfft2"))
+
+
+def fftfreq(n, d=1.0, dtype=None, name=None):
+    return torch.fft.fftfreq(n, d=d, dtype=dtype)
+
+
+def rfftfreq(n, d=1.0, dtype=None, name=None):
+    return torch.fft.rfftfreq(n, d=d, dtype=dtype)
+
+
+def fftshift(x, axes=None, name=None):
+    return torch.fft.fftshift(x, dim=axes)
+
+
+def ifftshift(x, axes=None, name=None):
+    return torch.fft.ifftshift(x, dim=axes)

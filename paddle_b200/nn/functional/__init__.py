@@ -12,7 +12,8 @@ import torch
 import torch.nn.functional as TF
 
 from ...framework import dtype as _dt
-from .flash_attention import (flash_attention, flash_attn_unpadded, scaled_dot_product_attention,  # noqa: F401
+from . import flash_attention  # noqa: F401  (module, callable)
+from .flash_attention import (flash_attn_unpadded, scaled_dot_product_attention,  # noqa: F401
                               flash_attn_qkvpacked, flash_attn_varlen_qkvpacked, flash_attention_with_sparse_mask,
                               sdp_kernel)
 

@@ -67,3 +67,17 @@ def flash_attention_with_sparse_mask(query, key, value, attn_mask_start_row_indi
     if is_causal:
         allowed = allowed & (rows >= torch.arange(sk, device=query.device)[None, None, None, :])
     return ops.flash_attention(query, key, value, dropout_p, False, attn_mask=allowed, training=training)
+
+
+# ``paddle.nn.functional.flash_attention`` is a MODULE in the reference (``...flash_attention.flash_attention(q, k, v)``);
+# the package-level name must stay the module, but calling it directly is a convenient shorthand, so make it callable.
+import sys as _sys
+import types as _types
+
+
+class _CallableModule(_types.ModuleType):
+    def __call__(self, *args, **kwargs):
+        return flash_attention(*args, **kwargs)
+
+
+_sys.modules[__name__].__class__ = _CallableModule

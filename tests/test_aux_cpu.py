@@ -91,3 +91,32 @@ def test_auto_tuner_grid_search_prunes_and_picks_best():
     dp8 = [c for c in ran if c["dp_degree"] == 8]
     assert [c["micro_batch_size"] for c in dp8] == [2, 1]
     assert best["tokens_per_second"] == max(h["tokens_per_second"] for h in tuner.history_cfgs if "tokens_per_second" in h)
+
+
+def test_secondary_namespaces():
+    """paddle.linalg / fft / distribution / jit / static / callbacks shims and the module-and-callable flash_attention."""
+    import paddle
+    import paddle.nn.functional as F
+    x = torch.randn(4, 4, dtype=torch.float64)
+    a = x @ x.t() + 4 * torch.eye(4, dtype=torch.float64)
+    torch.testing.assert_close(paddle.linalg.inv(a) @ a, torch.eye(4, dtype=torch.float64), rtol=1e-8, atol=1e-8)
+    torch.testing.assert_close(paddle.linalg.norm(x), x.pow(2).sum().sqrt())
+    torch.testing.assert_close(paddle.linalg.norm(x, p=1, axis=1), x.abs().sum(1))
+    torch.testing.assert_close(paddle.fft.ifft(paddle.fft.fft(x, axis=0), axis=0).real, x)
+    n = paddle.distribution.Normal(1.0, 2.0)
+    torch.testing.assert_close(n.log_prob(1.0), torch.tensor(-0.5 * torch.log(torch.tensor(2 * torch.pi)) - torch.log(torch.tensor(2.0))))
+    assert paddle.distribution.kl_divergence(n, paddle.distribution.Normal(1.0, 2.0)).abs() < 1e-7
+    c = paddle.distribution.Categorical(torch.tensor([1.0, 3.0]))
+    torch.testing.assert_close(c.prob(torch.tensor(1)), torch.tensor(0.75))
+
+    @paddle.jit.to_static
+    def f(t):
+        return t * 2
+    assert float(f(torch.tensor(2.0))) == 4.0
+    spec = paddle.static.InputSpec([None, 8], "float32", "x")
+    assert spec.shape == (None, 8)
+    q = torch.randn(1, 8, 2, 4)
+    o1 = F.flash_attention(q, q, q, causal=True)[0]
+    o2 = F.flash_attention.flash_attention(q, q, q, causal=True)[0]
+    torch.testing.assert_close(o1, o2)
+    assert issubclass(paddle.callbacks.EarlyStopping, paddle.callbacks.Callback)
