@@ -15,6 +15,9 @@ memory_reserved = torch.cuda.memory_reserved
 reset_max_memory_allocated = torch.cuda.reset_peak_memory_stats
 reset_max_memory_reserved = torch.cuda.reset_peak_memory_stats
 
+from . import graphs  # noqa: E402,F401
+from .graphs import CUDAGraph, wrap_cuda_graph  # noqa: E402,F401
+
 
 def get_device_properties(device=None):
     return torch.cuda.get_device_properties(device if device is not None else torch.cuda.current_device())

@@ -12,6 +12,7 @@ from __future__ import annotations
 
 import argparse
 import json
+import shutil
 import os
 import signal
 import socket
@@ -305,6 +306,68 @@ class Pod:
             c.terminate(force=True)
 
 
+class Watcher:
+    """GPU utilisation logger (reference: python/paddle/distributed/launch/job/watcher? -> launch/controllers/watcher.py):
+    one ``nvidia-smi`` query every ``interval`` seconds appended to ``<log_dir>/<job_id>.gpu.log`` while the pod runs."""
+    QUERY = "index,utilization.gpu,memory.used,memory.total,power.draw,clocks.sm"
+
+    def __init__(self, args, devices, interval=10):
+        self._stop = threading.Event()
+        self._thread = None
+        self.path = os.path.join(args.log_dir, f"{args.job_id}.gpu.log")
+        self._devices = devices
+        self._interval = interval
+        self._smi = shutil.which("nvidia-smi")
+
+    def start(self):
+        if not self._smi or not self._devices:
+            return self
+        os.makedirs(os.path.dirname(self.path) or ".", exist_ok=True)
+        self._thread = threading.Thread(target=self._run, daemon=True)
+        self._thread.start()
+        return self
+
+    def _run(self):
+        with open(self.path, "a") as f:
+            f.write("time," + self.QUERY + "\n")
+            while not self._stop.is_set():
+                try:
+                    out = subprocess.run([self._smi, f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits",
+                                          "-i", ",".join(self._devices)], capture_output=True, text=True, timeout=10).stdout
+                    now = time.strftime("%Y-%m-%d %H:%M:%S")
+                    for line in out.strip().splitlines():
+                        f.write(f"{now},{line.strip()}\n")
+                    f.flush()
+                except Exception:  # noqa: BLE001  (the logger must never take the job down)
+                    pass
+                self._stop.wait(self._interval)
+
+    def stop(self):
+        self._stop.set()
+        if self._thread is not None:
+            self._thread.join(timeout=5)
+
+
+def run_auto_tuner(args):
+    """``--auto_tuner_json cfg.json``: search the parallel-strategy space by launching the training script once per
+    candidate (reference: launch/main.py auto-tuner branch + distributed/auto_tuner).  The script reads its candidate
+    from ``PADDLE_AUTO_TUNER_CFG`` and prints one JSON line with the metric named in ``metric_cfg.name``."""
+    from paddle_b200.distributed.auto_tuner import AutoTuner
+    from paddle_b200.distributed.auto_tuner.tuner import launch_trial
+    with open(args.auto_tuner_json) as f:
+        cfg = json.load(f)
+    devices = _detect_devices(args)
+    nproc = args.nproc_per_node or (len(devices) if devices else 1)
+    cfg.setdefault("num_gpus", nproc)
+    tuner = AutoTuner(cfg)
+    best = tuner.tune(lambda c: launch_trial(args.training_script, c, nproc, os.path.join(args.log_dir, "auto_tuner"),
+                                             args.training_script_args, timeout=cfg.get("max_time_per_task", 3600)))
+    os.makedirs(args.log_dir, exist_ok=True)
+    tuner.recorder.store_history(os.path.join(args.log_dir, "auto_tuner_history.csv"))
+    sys.stdout.write("AUTO_TUNER best: " + json.dumps(best) + "\n")
+    return 0 if best is not None else 1
+
+
 def build_pod(args, node_rank, nnodes, all_endpoints, local_range, devices, host_ip, master_ep, restart=0):
     pod = Pod()
     global_size = len(all_endpoints)
@@ -333,7 +396,7 @@ def launch(argv=None):
     if args.run_mode not in (None, "collective"):
         raise NotImplementedError(f"run_mode={args.run_mode}: only collective mode is in scope (PS/RPC/IPU are not)")
     if args.auto_tuner_json:
-        raise NotImplementedError("auto-tuner mode is not part of this framework (SURVEY P36)")
+        return run_auto_tuner(args)
     devices = _detect_devices(args)
     nproc = args.nproc_per_node or (len(devices) if devices else 1)
     if devices and nproc > len(devices) and args.devices:
@@ -377,10 +440,13 @@ def launch(argv=None):
         pod = build_pod(args, node_rank, nnodes, all_eps, local_range, devices, host_ip, master_ep, restart)
         pod_holder["pod"] = pod
         pod.deploy()
+        watcher = Watcher(args, devices).start() if args.enable_gpu_log else None
         status = "running"
         while status == "running" and not stop_flag["stop"]:
             time.sleep(2 if nproc > 0 else 0.5)
             status = pod.status()
+        if watcher is not None:
+            watcher.stop()
         if status == "completed":
             if master:
                 master.stop()

@@ -120,3 +120,28 @@ def test_secondary_namespaces():
     o2 = F.flash_attention.flash_attention(q, q, q, causal=True)[0]
     torch.testing.assert_close(o1, o2)
     assert issubclass(paddle.callbacks.EarlyStopping, paddle.callbacks.Callback)
+
+
+def test_launch_auto_tuner_mode(tmp_path):
+    """python -m paddle.distributed.launch --auto_tuner_json: one pod launch per candidate, metric read from the worker."""
+    import json
+    import subprocess
+    import sys
+    script = tmp_path / "train.py"
+    script.write_text("import json, os\n"
+                      "cfg = json.loads(os.environ['PADDLE_AUTO_TUNER_CFG'])\n"
+                      "if int(os.environ.get('PADDLE_TRAINER_ID', '0')) == 0:\n"
+                      "    print(json.dumps({'tokens_per_second': 100.0 / cfg['mp_degree'] + cfg['micro_batch_size']}))\n")
+    cfg = {"dp_degree": "auto", "mp_degree": "auto", "pp_degree": [1], "sharding_degree": [1], "sharding_stage": [1],
+           "micro_batch_size": [1, 2], "use_recompute": [False],
+           "model_cfg": {"global_batch_size": 4, "num_attention_heads": 4, "hidden_size": 16, "vocab_size": 32, "num_layers": 2}}
+    (tmp_path / "at.json").write_text(json.dumps(cfg))
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, PYTHONPATH=root + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    r = subprocess.run([sys.executable, "-m", "paddle_b200.distributed.launch", "--nproc_per_node", "2", "--log_dir",
+                        str(tmp_path / "log"), "--auto_tuner_json", str(tmp_path / "at.json"), str(script)],
+                       env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    best = json.loads(r.stdout.split("AUTO_TUNER best: ")[1].splitlines()[0])
+    assert best["dp_degree"] == 2 and best["mp_degree"] == 1 and best["micro_batch_size"] == 2
+    assert (tmp_path / "log" / "auto_tuner_history.csv").exists()

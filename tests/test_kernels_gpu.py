@@ -347,3 +347,33 @@ def test_native_matches_torch_composition_end_to_end():
             flags.set_flags({"use_native_kernels": True})
     for a, b in zip(*curves):
         assert abs(a - b) < 5e-3 * max(1.0, abs(b)), curves
+
+
+def test_cuda_graph_capture_replays_native_kernels():
+    """paddle.device.cuda.graphs.CUDAGraph: a captured region made of this library's kernels (RMSNorm + tcgen05 GEMM)
+    replays correctly on new input contents (launch-bound loops are captured instead of traced)."""
+    from paddle_b200.device.cuda.graphs import CUDAGraph
+    from paddle_b200.ops import gemm as G
+    torch.manual_seed(0)
+    x = torch.randn(512, 1024, device="cuda").bfloat16()
+    w = torch.ones(1024, device="cuda").bfloat16()
+    W = (torch.randn(1024, 512, device="cuda") * 0.05).bfloat16()
+
+    def region(inp):
+        y = ops.rms_norm(inp, w, 1e-6)
+        y = y[0] if isinstance(y, tuple) else y
+        return G.gemm(y, W)
+    static_x = x.clone()
+    for _ in range(2):
+        region(static_x)
+    torch.cuda.synchronize()
+    g = CUDAGraph()
+    g.capture_begin()
+    out = region(static_x)
+    g.capture_end()
+    x2 = torch.randn_like(x)
+    static_x.copy_(x2)
+    g.replay()
+    torch.cuda.synchronize()
+    ref = region(x2)
+    torch.testing.assert_close(out.float(), ref.float(), rtol=0, atol=0)
