@@ -1,2 +1,3 @@
 from .layers import Layer, LayerList, Sequential, ParameterList, LayerDict, HookRemoveHelper  # noqa: F401
 from .common import *  # noqa: F401,F403
+from .extra import *  # noqa: F401,F403

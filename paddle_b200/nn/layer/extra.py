@@ -1,0 +1,370 @@
+"""Less common ``paddle.nn`` layers (reference: python/paddle/nn/layer/{rnn,transformer,conv,pooling,common,loss,
+activation,vision,distance}.py).  None of them is on a hot path of the training product, so they are thin layers over
+torch's implementations that keep Paddle's constructor arguments, parameter naming scheme and return conventions."""
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as TF
+
+from .. import functional as F
+from .common import Dropout, LayerNorm, Linear, MultiHeadAttention, _act_layer
+from .layers import Layer, LayerList
+
+# ---------------------------------------------------------------------------------------------- activations
+SiLU = _act_layer("SiLU", F.silu)
+ThresholdedReLU = _act_layer("ThresholdedReLU", F.thresholded_relu)
+Maxout = _act_layer("Maxout", F.maxout)
+
+
+class Softmax2D(Layer):
+    def forward(self, x):
+        assert x.dim() in (3, 4), "Softmax2D requires a 3D or 4D tensor as input"
+        return torch.softmax(x, dim=-3)
+
+
+# ---------------------------------------------------------------------------------------------- recurrent layers
+class _RNNBase(Layer):
+    _mode = "LSTM"
+
+    def __init__(self, input_size, hidden_size, num_layers=1, direction="forward", time_major=False, dropout=0.0,
+                 weight_ih_attr=None, weight_hh_attr=None, bias_ih_attr=None, bias_hh_attr=None, name=None, activation="tanh"):
+        super().__init__()
+        bidir = direction in ("bidirect", "bidirectional")
+        kw = dict(input_size=input_size, hidden_size=hidden_size, num_layers=num_layers, batch_first=not time_major,
+                  dropout=dropout, bidirectional=bidir, bias=bias_ih_attr is not False)
+        if self._mode == "RNN":
+            kw["nonlinearity"] = activation
+        self._rnn = getattr(torch.nn, self._mode)(**kw)
+        self.input_size, self.hidden_size, self.num_layers = input_size, hidden_size, num_layers
+        self.num_directions = 2 if bidir else 1
+        self.time_major = time_major
+
+    def forward(self, inputs, initial_states=None, sequence_length=None):
+        if sequence_length is not None:
+            lens = torch.as_tensor(sequence_length).cpu()
+            packed = torch.nn.utils.rnn.pack_padded_sequence(inputs, lens, batch_first=not self.time_major, enforce_sorted=False)
+            out, st = self._rnn(packed, initial_states)
+            out, _ = torch.nn.utils.rnn.pad_packed_sequence(out, batch_first=not self.time_major,
+                                                            total_length=inputs.shape[0 if self.time_major else 1])
+            return out, st
+        return self._rnn(inputs, initial_states)
+
+
+class LSTM(_RNNBase):
+    _mode = "LSTM"
+
+
+class GRU(_RNNBase):
+    _mode = "GRU"
+
+
+class SimpleRNN(_RNNBase):
+    _mode = "RNN"
+
+
+class _CellBase(Layer):
+    _cls = torch.nn.LSTMCell
+
+    def __init__(self, input_size, hidden_size, weight_ih_attr=None, weight_hh_attr=None, bias_ih_attr=None,
+                 bias_hh_attr=None, name=None, **kw):
+        super().__init__()
+        self._cell = self._cls(input_size, hidden_size, bias=bias_ih_attr is not False, **kw)
+        self.input_size, self.hidden_size = input_size, hidden_size
+
+    @property
+    def state_shape(self):
+        return (self.hidden_size,)
+
+
+class LSTMCell(_CellBase):
+    _cls = torch.nn.LSTMCell
+
+    def forward(self, inputs, states=None):
+        h, c = self._cell(inputs, states)
+        return h, (h, c)
+
+    @property
+    def state_shape(self):
+        return ((self.hidden_size,), (self.hidden_size,))
+
+
+class GRUCell(_CellBase):
+    _cls = torch.nn.GRUCell
+
+    def forward(self, inputs, states=None):
+        h = self._cell(inputs, states)
+        return h, h
+
+
+class SimpleRNNCell(_CellBase):
+    _cls = torch.nn.RNNCell
+
+    def __init__(self, input_size, hidden_size, activation="tanh", **kw):
+        super().__init__(input_size, hidden_size, nonlinearity=activation, **{k: v for k, v in kw.items() if k.endswith("_attr")})
+
+    def forward(self, inputs, states=None):
+        h = self._cell(inputs, states)
+        return h, h
+
+
+class RNN(Layer):
+    """Runs a cell over the time dimension (reference: nn.RNN(cell, is_reverse=False, time_major=False))."""
+
+    def __init__(self, cell, is_reverse=False, time_major=False):
+        super().__init__()
+        self.cell, self.is_reverse, self.time_major = cell, is_reverse, time_major
+
+    def forward(self, inputs, initial_states=None, sequence_length=None, **kwargs):
+        x = inputs if self.time_major else inputs.transpose(0, 1)
+        steps = range(x.shape[0] - 1, -1, -1) if self.is_reverse else range(x.shape[0])
+        states, outs = initial_states, [None] * x.shape[0]
+        for t in steps:
+            o, states = self.cell(x[t], states)
+            outs[t] = o
+        out = torch.stack(outs, 0)
+        return (out if self.time_major else out.transpose(0, 1)), states
+
+
+class BiRNN(Layer):
+    def __init__(self, cell_fw, cell_bw, time_major=False):
+        super().__init__()
+        self.fw, self.bw = RNN(cell_fw, False, time_major), RNN(cell_bw, True, time_major)
+
+    def forward(self, inputs, initial_states=None, sequence_length=None, **kwargs):
+        s_fw, s_bw = initial_states if initial_states is not None else (None, None)
+        o1, f1 = self.fw(inputs, s_fw)
+        o2, f2 = self.bw(inputs, s_bw)
+        return torch.cat([o1, o2], -1), (f1, f2)
+
+
+# ---------------------------------------------------------------------------------------------- transformer decoder
+class TransformerDecoderLayer(Layer):
+    def __init__(self, d_model, nhead, dim_feedforward, dropout=0.1, activation="relu", attn_dropout=None,
+                 act_dropout=None, normalize_before=False, weight_attr=None, bias_attr=None, layer_norm_eps=1e-5):
+        super().__init__()
+        self.normalize_before = normalize_before
+        ad = attn_dropout if attn_dropout is not None else dropout
+        self.self_attn = MultiHeadAttention(d_model, nhead, ad)
+        self.cross_attn = MultiHeadAttention(d_model, nhead, ad)
+        self.linear1, self.linear2 = Linear(d_model, dim_feedforward), Linear(dim_feedforward, d_model)
+        self.norm1, self.norm2, self.norm3 = (LayerNorm(d_model, layer_norm_eps) for _ in range(3))
+        self.dropout = Dropout(act_dropout if act_dropout is not None else dropout)
+        self.dropout1, self.dropout2, self.dropout3 = Dropout(dropout), Dropout(dropout), Dropout(dropout)
+        self.activation = getattr(F, activation)
+
+    def _block(self, x, norm, fn, drop):
+        y = norm(x) if self.normalize_before else x
+        x = x + drop(fn(y))
+        return x if self.normalize_before else norm(x)
+
+    def forward(self, tgt, memory, tgt_mask=None, memory_mask=None, cache=None):
+        tgt = self._block(tgt, self.norm1, lambda t: self.self_attn(t, t, t, tgt_mask), self.dropout1)
+        tgt = self._block(tgt, self.norm2, lambda t: self.cross_attn(t, memory, memory, memory_mask), self.dropout2)
+        return self._block(tgt, self.norm3, lambda t: self.linear2(self.dropout(self.activation(self.linear1(t)))), self.dropout3)
+
+
+class TransformerDecoder(Layer):
+    def __init__(self, decoder_layer, num_layers, norm=None):
+        super().__init__()
+        import copy
+        self.layers = LayerList([decoder_layer if i == 0 else copy.deepcopy(decoder_layer) for i in range(num_layers)])
+        self.norm = norm
+
+    def forward(self, tgt, memory, tgt_mask=None, memory_mask=None, cache=None):
+        for l in self.layers:
+            tgt = l(tgt, memory, tgt_mask, memory_mask)
+        return self.norm(tgt) if self.norm is not None else tgt
+
+
+class Transformer(Layer):
+    def __init__(self, d_model=512, nhead=8, num_encoder_layers=6, num_decoder_layers=6, dim_feedforward=2048, dropout=0.1,
+                 activation="relu", attn_dropout=None, act_dropout=None, normalize_before=False, weight_attr=None,
+                 bias_attr=None, custom_encoder=None, custom_decoder=None):
+        super().__init__()
+        from .common import TransformerEncoder, TransformerEncoderLayer
+        self.encoder = custom_encoder or TransformerEncoder(
+            TransformerEncoderLayer(d_model, nhead, dim_feedforward, dropout, activation, attn_dropout, act_dropout,
+                                    normalize_before), num_encoder_layers, LayerNorm(d_model) if normalize_before else None)
+        self.decoder = custom_decoder or TransformerDecoder(
+            TransformerDecoderLayer(d_model, nhead, dim_feedforward, dropout, activation, attn_dropout, act_dropout,
+                                    normalize_before), num_decoder_layers, LayerNorm(d_model) if normalize_before else None)
+        self.d_model, self.nhead = d_model, nhead
+
+    def forward(self, src, tgt, src_mask=None, tgt_mask=None, memory_mask=None):
+        memory = self.encoder(src, src_mask)
+        return self.decoder(tgt, memory, tgt_mask, memory_mask)
+
+    @staticmethod
+    def generate_square_subsequent_mask(length):
+        return torch.full((length, length), float("-inf")).triu(1)
+
+
+# ---------------------------------------------------------------------------------------------- thin torch-backed layers
+def _wrap(name, factory, doc=""):
+    """Layer whose forward is a torch module built from Paddle-style constructor arguments by ``factory``."""
+    class _W(Layer):
+        def __init__(self, *args, **kwargs):
+            super().__init__()
+            kwargs.pop("name", None)
+            self._m = factory(*args, **kwargs)
+
+        def forward(self, *x):
+            return self._m(*x)
+    _W.__name__ = _W.__qualname__ = name
+    _W.__doc__ = doc
+    return _W
+
+
+def _bias(bias_attr):
+    return bias_attr is not False
+
+
+Conv1DTranspose = _wrap("Conv1DTranspose", lambda i, o, k, stride=1, padding=0, output_padding=0, groups=1, dilation=1,
+                        weight_attr=None, bias_attr=None, data_format="NCL": torch.nn.ConvTranspose1d(
+                            i, o, k, stride, padding, output_padding, groups, _bias(bias_attr), dilation))
+Conv3DTranspose = _wrap("Conv3DTranspose", lambda i, o, k, stride=1, padding=0, output_padding=0, dilation=1, groups=1,
+                        weight_attr=None, bias_attr=None, data_format="NCDHW": torch.nn.ConvTranspose3d(
+                            i, o, k, stride, padding, output_padding, groups, _bias(bias_attr), dilation))
+MaxPool3D = _wrap("MaxPool3D", lambda kernel_size, stride=None, padding=0, ceil_mode=False, return_mask=False,
+                  data_format="NCDHW": torch.nn.MaxPool3d(kernel_size, stride, padding, ceil_mode=ceil_mode,
+                                                          return_indices=return_mask))
+AvgPool3D = _wrap("AvgPool3D", lambda kernel_size, stride=None, padding=0, ceil_mode=False, exclusive=True,
+                  divisor_override=None, data_format="NCDHW": torch.nn.AvgPool3d(
+                      kernel_size, stride, padding, ceil_mode, count_include_pad=not exclusive, divisor_override=divisor_override))
+AdaptiveAvgPool3D = _wrap("AdaptiveAvgPool3D", lambda output_size, data_format="NCDHW": torch.nn.AdaptiveAvgPool3d(output_size))
+AdaptiveMaxPool1D = _wrap("AdaptiveMaxPool1D", lambda output_size, return_mask=False: torch.nn.AdaptiveMaxPool1d(
+    output_size, return_indices=return_mask))
+PixelShuffle = _wrap("PixelShuffle", lambda upscale_factor, data_format="NCHW": torch.nn.PixelShuffle(upscale_factor))
+PixelUnshuffle = _wrap("PixelUnshuffle", lambda downscale_factor, data_format="NCHW": torch.nn.PixelUnshuffle(downscale_factor))
+ChannelShuffle = _wrap("ChannelShuffle", lambda groups, data_format="NCHW": torch.nn.ChannelShuffle(groups))
+Unfold = _wrap("Unfold", lambda kernel_sizes, dilations=1, paddings=0, strides=1: torch.nn.Unfold(
+    kernel_sizes, dilations, paddings, strides))
+Fold = _wrap("Fold", lambda output_sizes, kernel_sizes, dilations=1, paddings=0, strides=1: torch.nn.Fold(
+    output_sizes, kernel_sizes, dilations, paddings, strides))
+Unflatten = _wrap("Unflatten", lambda axis, shape: torch.nn.Unflatten(axis, tuple(shape)))
+LocalResponseNorm = _wrap("LocalResponseNorm", lambda size, alpha=1e-4, beta=0.75, k=1.0, data_format="NCHW":
+                          torch.nn.LocalResponseNorm(size, alpha, beta, k))
+InstanceNorm1D = _wrap("InstanceNorm1D", lambda num_features, epsilon=1e-5, momentum=0.9, weight_attr=None, bias_attr=None,
+                       data_format="NCL": torch.nn.InstanceNorm1d(num_features, epsilon, affine=weight_attr is not False))
+InstanceNorm3D = _wrap("InstanceNorm3D", lambda num_features, epsilon=1e-5, momentum=0.9, weight_attr=None, bias_attr=None,
+                       data_format="NCDHW": torch.nn.InstanceNorm3d(num_features, epsilon, affine=weight_attr is not False))
+AlphaDropout = _wrap("AlphaDropout", lambda p=0.5: torch.nn.AlphaDropout(p))
+Dropout3D = _wrap("Dropout3D", lambda p=0.5, data_format="NCDHW": torch.nn.Dropout3d(p))
+Bilinear = _wrap("Bilinear", lambda in1_features, in2_features, out_features, weight_attr=None, bias_attr=None:
+                 torch.nn.Bilinear(in1_features, in2_features, out_features, _bias(bias_attr)))
+PairwiseDistance = _wrap("PairwiseDistance", lambda p=2.0, epsilon=1e-6, keepdim=False: torch.nn.PairwiseDistance(p, epsilon, keepdim))
+CosineEmbeddingLoss = _wrap("CosineEmbeddingLoss", lambda margin=0, reduction="mean": torch.nn.CosineEmbeddingLoss(margin, reduction=reduction))
+MarginRankingLoss = _wrap("MarginRankingLoss", lambda margin=0.0, reduction="mean": torch.nn.MarginRankingLoss(margin, reduction=reduction))
+HingeEmbeddingLoss = _wrap("HingeEmbeddingLoss", lambda margin=1.0, reduction="mean": torch.nn.HingeEmbeddingLoss(margin, reduction=reduction))
+TripletMarginLoss = _wrap("TripletMarginLoss", lambda margin=1.0, p=2.0, epsilon=1e-6, swap=False, reduction="mean":
+                          torch.nn.TripletMarginLoss(margin, p, epsilon, swap, reduction=reduction))
+MultiLabelSoftMarginLoss = _wrap("MultiLabelSoftMarginLoss", lambda weight=None, reduction="mean":
+                                 torch.nn.MultiLabelSoftMarginLoss(weight, reduction=reduction))
+SoftMarginLoss = _wrap("SoftMarginLoss", lambda reduction="mean": torch.nn.SoftMarginLoss(reduction=reduction))
+
+
+class CTCLoss(Layer):
+    def __init__(self, blank=0, reduction="mean"):
+        super().__init__()
+        self.blank, self.reduction = blank, reduction
+
+    def forward(self, log_probs, labels, input_lengths, label_lengths, norm_by_times=False):
+        return F.ctc_loss(log_probs, labels, input_lengths, label_lengths, self.blank, self.reduction)
+
+
+class _PadNd(Layer):
+    _nd = 1
+
+    def __init__(self, padding, mode="constant", value=0.0, data_format=None, name=None):
+        super().__init__()
+        self.padding = [padding] * (2 * self._nd) if isinstance(padding, int) else list(padding)
+        self.mode, self.value = mode, value
+
+    def forward(self, x):
+        mode = {"constant": "constant", "reflect": "reflect", "replicate": "replicate", "circular": "circular"}[self.mode]
+        return TF.pad(x, self.padding, mode=mode, value=self.value) if mode == "constant" else TF.pad(x, self.padding, mode=mode)
+
+
+class Pad1D(_PadNd):
+    _nd = 1
+
+
+class Pad3D(_PadNd):
+    _nd = 3
+
+
+class ZeroPad2D(_PadNd):
+    _nd = 2
+
+    def __init__(self, padding, data_format="NCHW", name=None):
+        super().__init__(padding, "constant", 0.0)
+
+
+class UpsamplingNearest2D(Layer):
+    def __init__(self, size=None, scale_factor=None, data_format="NCHW", name=None):
+        super().__init__()
+        self.size, self.scale_factor = size, scale_factor
+
+    def forward(self, x):
+        return TF.interpolate(x, size=self.size, scale_factor=self.scale_factor, mode="nearest")
+
+
+class UpsamplingBilinear2D(UpsamplingNearest2D):
+    def forward(self, x):
+        return TF.interpolate(x, size=self.size, scale_factor=self.scale_factor, mode="bilinear", align_corners=True)
+
+
+class SpectralNorm(Layer):
+    """Power-iteration spectral normalisation of a weight tensor (reference: nn.SpectralNorm(weight_shape, dim, power_iters))."""
+
+    def __init__(self, weight_shape, dim=0, power_iters=1, epsilon=1e-12, dtype="float32"):
+        super().__init__()
+        self.dim, self.power_iters, self.eps = dim, power_iters, epsilon
+        h = weight_shape[dim]
+        w = 1
+        for i, s in enumerate(weight_shape):
+            if i != dim:
+                w *= s
+        self.register_buffer("weight_u", torch.nn.functional.normalize(torch.randn(h), dim=0))
+        self.register_buffer("weight_v", torch.nn.functional.normalize(torch.randn(w), dim=0))
+
+    def forward(self, weight):
+        mat = weight.transpose(0, self.dim).reshape(weight.shape[self.dim], -1) if self.dim != 0 else weight.reshape(weight.shape[0], -1)
+        u, v = self.weight_u, self.weight_v
+        with torch.no_grad():
+            for _ in range(self.power_iters):
+                v = torch.nn.functional.normalize(mat.t() @ u, dim=0, eps=self.eps)
+                u = torch.nn.functional.normalize(mat @ v, dim=0, eps=self.eps)
+            self.weight_u.copy_(u)
+            self.weight_v.copy_(v)
+        sigma = u @ (mat @ v)
+        return weight / sigma
+
+
+class HSigmoidLoss(Layer):
+    """Hierarchical sigmoid over the default complete binary tree (reference: nn.HSigmoidLoss, non-custom-tree mode)."""
+
+    def __init__(self, feature_size, num_classes, weight_attr=None, bias_attr=None, is_custom=False, is_sparse=False, name=None):
+        super().__init__()
+        if is_custom:
+            raise NotImplementedError("HSigmoidLoss: custom trees are not supported")
+        self.num_classes = num_classes
+        self.weight = self.create_parameter([num_classes - 1, feature_size], attr=weight_attr)
+        self.bias = self.create_parameter([num_classes - 1, 1], attr=bias_attr, is_bias=True) if bias_attr is not False else None
+
+    def forward(self, input, label, path_table=None, path_code=None):
+        # node ids / codes of the complete binary tree: leaf = label + num_classes, walk up to the root (1)
+        lab = label.reshape(-1).long() + self.num_classes
+        depth = int(self.num_classes - 1).bit_length()
+        loss = input.new_zeros(input.shape[0], dtype=torch.float32)
+        for _ in range(depth):
+            parent, code = lab // 2, (lab % 2).float()
+            valid = parent >= 1
+            idx = (parent - 1).clamp(0, self.num_classes - 2)
+            z = (input.float() * self.weight[idx].float()).sum(-1)
+            if self.bias is not None:
+                z = z + self.bias[idx, 0].float()
+            loss = loss + torch.where(valid, TF.binary_cross_entropy_with_logits(z, code, reduction="none"), torch.zeros_like(z))
+            lab = torch.where(valid, parent, lab)
+            lab = torch.where(lab <= 1, torch.zeros_like(lab), lab)
+        return loss.reshape(-1, 1)

@@ -561,3 +561,161 @@ class Lamb(Adam):
                 p.copy_(master)
         for dev, pows in self._beta_pows.items():
             self._advance_pows(pows)
+
+
+# ---------------------------------------------------------------------------------------------- further optimizers
+# (reference: python/paddle/optimizer/{adadelta,adamax,nadam,radam,asgd,rprop}.py; update rules of the phi kernels)
+class Adadelta(Optimizer):
+    def __init__(self, learning_rate=0.001, epsilon=1e-06, rho=0.95, parameters=None, weight_decay=None, grad_clip=None,
+                 name=None):
+        super().__init__(learning_rate, parameters, weight_decay, grad_clip, name)
+        self._epsilon, self._rho = epsilon, rho
+
+    def _create_accumulators(self, params):
+        for p in params:
+            self._add_accumulator("_avg_squared_grad", p)
+            self._add_accumulator("_avg_squared_update", p)
+
+    def _update(self, params_grads):
+        lr = self.get_lr()
+        for p, g in params_grads:
+            eg, eu = self._get_accumulator("_avg_squared_grad", p), self._get_accumulator("_avg_squared_update", p)
+            gf = g.float()
+            eg.mul_(self._rho).add_((1 - self._rho) * gf * gf)
+            upd = -((eu + self._epsilon) / (eg + self._epsilon)).sqrt() * gf
+            eu.mul_(self._rho).add_((1 - self._rho) * upd * upd)
+            p.add_((lr * upd).to(p.dtype))
+
+
+class Adamax(Optimizer):
+    def __init__(self, learning_rate=0.001, beta1=0.9, beta2=0.999, epsilon=1e-08, parameters=None, weight_decay=None,
+                 grad_clip=None, name=None):
+        super().__init__(learning_rate, parameters, weight_decay, grad_clip, name)
+        self._beta1, self._beta2, self._epsilon = beta1, beta2, epsilon
+
+    def _create_accumulators(self, params):
+        for p in params:
+            self._add_accumulator("moment", p)
+            self._add_accumulator("inf_norm", p)
+            self._add_accumulator("beta1_pow_acc", p, shape=[1], fill=self._beta1)
+
+    def _update(self, params_grads):
+        lr = self.get_lr()
+        for p, g in params_grads:
+            m, u, b1p = (self._get_accumulator(n, p) for n in ("moment", "inf_norm", "beta1_pow_acc"))
+            gf = g.float()
+            m.mul_(self._beta1).add_((1 - self._beta1) * gf)
+            torch.maximum(u * self._beta2, gf.abs() + self._epsilon, out=u)
+            p.sub_((lr / (1 - b1p) * m / u).to(p.dtype))
+            b1p.mul_(self._beta1)
+
+
+class NAdam(Optimizer):
+    def __init__(self, learning_rate=0.002, beta1=0.9, beta2=0.999, epsilon=1e-08, momentum_decay=0.004, parameters=None,
+                 weight_decay=None, grad_clip=None, name=None):
+        super().__init__(learning_rate, parameters, weight_decay, grad_clip, name)
+        self._beta1, self._beta2, self._epsilon, self._psi = beta1, beta2, epsilon, momentum_decay
+        self._t = 0
+        self._mu_product = 1.0
+
+    def _create_accumulators(self, params):
+        for p in params:
+            self._add_accumulator("moment1", p)
+            self._add_accumulator("moment2", p)
+
+    def _update(self, params_grads):
+        lr = self.get_lr()
+        self._t += 1
+        t = self._t
+        mu_t = self._beta1 * (1 - 0.5 * 0.96 ** (t * self._psi))
+        mu_next = self._beta1 * (1 - 0.5 * 0.96 ** ((t + 1) * self._psi))
+        self._mu_product *= mu_t
+        for p, g in params_grads:
+            m, v = self._get_accumulator("moment1", p), self._get_accumulator("moment2", p)
+            gf = g.float()
+            m.mul_(self._beta1).add_((1 - self._beta1) * gf)
+            v.mul_(self._beta2).add_((1 - self._beta2) * gf * gf)
+            m_hat = mu_next * m / (1 - self._mu_product * mu_next) + (1 - mu_t) * gf / (1 - self._mu_product)
+            v_hat = v / (1 - self._beta2 ** t)
+            p.sub_((lr * m_hat / (v_hat.sqrt() + self._epsilon)).to(p.dtype))
+
+
+class RAdam(Optimizer):
+    def __init__(self, learning_rate=0.001, beta1=0.9, beta2=0.999, epsilon=1e-08, parameters=None, weight_decay=None,
+                 grad_clip=None, name=None):
+        super().__init__(learning_rate, parameters, weight_decay, grad_clip, name)
+        self._beta1, self._beta2, self._epsilon = beta1, beta2, epsilon
+        self._t = 0
+
+    def _create_accumulators(self, params):
+        for p in params:
+            self._add_accumulator("moment1", p)
+            self._add_accumulator("moment2", p)
+
+    def _update(self, params_grads):
+        lr = self.get_lr()
+        self._t += 1
+        t, b1, b2 = self._t, self._beta1, self._beta2
+        rho_inf = 2.0 / (1 - b2) - 1
+        rho_t = rho_inf - 2.0 * t * b2 ** t / (1 - b2 ** t)
+        for p, g in params_grads:
+            m, v = self._get_accumulator("moment1", p), self._get_accumulator("moment2", p)
+            gf = g.float()
+            m.mul_(b1).add_((1 - b1) * gf)
+            v.mul_(b2).add_((1 - b2) * gf * gf)
+            m_hat = m / (1 - b1 ** t)
+            if rho_t > 5.0:
+                l_t = ((1 - b2 ** t) ** 0.5) / (v.sqrt() + self._epsilon)
+                r_t = (((rho_t - 4) * (rho_t - 2) * rho_inf) / ((rho_inf - 4) * (rho_inf - 2) * rho_t)) ** 0.5
+                p.sub_((lr * m_hat * r_t * l_t).to(p.dtype))
+            else:
+                p.sub_((lr * m_hat).to(p.dtype))
+
+
+class ASGD(Optimizer):
+    """Averaged-gradient SGD over the last ``batch_num`` gradients (reference: python/paddle/optimizer/asgd.py)."""
+
+    def __init__(self, learning_rate=0.001, batch_num=1, parameters=None, weight_decay=None, grad_clip=None,
+                 multi_precision=False, name=None):
+        super().__init__(learning_rate, parameters, weight_decay, grad_clip, name)
+        self._n = int(batch_num)
+        self._step_i = 0
+        self._hist = {}
+
+    def _update(self, params_grads):
+        lr = self.get_lr()
+        slot = self._step_i % self._n
+        self._step_i += 1
+        m = min(self._step_i, self._n)
+        for p, g in params_grads:
+            h = self._hist.setdefault(id(p), dict(sum=torch.zeros_like(p, dtype=torch.float32), ys=[None] * self._n))
+            gf = g.float()
+            if h["ys"][slot] is not None:
+                h["sum"].sub_(h["ys"][slot])
+            h["ys"][slot] = gf.clone()
+            h["sum"].add_(gf)
+            p.sub_((lr * h["sum"] / m).to(p.dtype))
+
+
+class Rprop(Optimizer):
+    def __init__(self, learning_rate=0.001, learning_rate_range=(1e-5, 50), parameters=None, etas=(0.5, 1.2), grad_clip=None,
+                 multi_precision=False, name=None):
+        super().__init__(learning_rate, parameters, None, grad_clip, name)
+        self._range, self._etas = learning_rate_range, etas
+
+    def _create_accumulators(self, params):
+        for p in params:
+            self._add_accumulator("prev", p)
+            self._add_accumulator("learning_rate", p, fill=float(self.get_lr()))
+
+    def _update(self, params_grads):
+        eta_n, eta_p = self._etas
+        lo, hi = self._range
+        for p, g in params_grads:
+            prev, lrs = self._get_accumulator("prev", p), self._get_accumulator("learning_rate", p)
+            gf = g.float().clone()
+            sign = (gf * prev).sign()
+            lrs.mul_(torch.where(sign > 0, eta_p, torch.where(sign < 0, eta_n, 1.0))).clamp_(lo, hi)
+            gf[sign < 0] = 0
+            p.sub_((lrs * gf.sign()).to(p.dtype))
+            prev.copy_(gf)

@@ -2,4 +2,5 @@
 from .creation import *  # noqa: F401,F403
 from .math import *  # noqa: F401,F403
 from .manipulation import *  # noqa: F401,F403
-from . import creation, math, manipulation  # noqa: F401
+from .extra import *  # noqa: F401,F403
+from . import creation, extra, math, manipulation  # noqa: F401

@@ -145,3 +145,44 @@ def test_launch_auto_tuner_mode(tmp_path):
     best = json.loads(r.stdout.split("AUTO_TUNER best: ")[1].splitlines()[0])
     assert best["dp_degree"] == 2 and best["mp_degree"] == 1 and best["micro_batch_size"] == 2
     assert (tmp_path / "log" / "auto_tuner_history.csv").exists()
+
+
+def test_extra_layers_optimizers_and_tensor_functions():
+    import paddle
+    # recurrent / transformer / misc layers keep Paddle's argument names and return conventions
+    out, (h, c) = paddle.nn.LSTM(8, 16, num_layers=2, direction="bidirect")(torch.randn(3, 5, 8))
+    assert out.shape == (3, 5, 32) and h.shape == (4, 3, 16) and c.shape == (4, 3, 16)
+    o, s = paddle.nn.RNN(paddle.nn.GRUCell(8, 16))(torch.randn(3, 5, 8))
+    assert o.shape == (3, 5, 16) and s.shape == (3, 16)
+    tr = paddle.nn.Transformer(32, 4, 1, 1, 64, dropout=0.0)
+    y = tr(torch.randn(2, 5, 32), torch.randn(2, 3, 32), tgt_mask=paddle.nn.Transformer.generate_square_subsequent_mask(3))
+    assert y.shape == (2, 3, 32)
+    assert paddle.nn.Conv1DTranspose(4, 8, 3)(torch.randn(2, 4, 10)).shape == (2, 8, 12)
+    assert paddle.nn.ZeroPad2D([1, 1, 2, 2])(torch.randn(1, 1, 3, 3)).shape == (1, 1, 7, 5)
+    w = torch.randn(4, 6)
+    sn = paddle.nn.SpectralNorm([4, 6], power_iters=30)(w)
+    torch.testing.assert_close(torch.linalg.matrix_norm(sn, ord=2), torch.tensor(1.0), rtol=1e-2, atol=1e-2)
+    # optimizers against torch.optim on a quadratic
+    for mk_p, mk_t in ((lambda p: paddle.optimizer.Adamax(0.01, parameters=p), lambda p: torch.optim.Adamax(p, lr=0.01)),
+                       (lambda p: paddle.optimizer.Adadelta(1.0, parameters=p), lambda p: torch.optim.Adadelta(p, lr=1.0, rho=0.95, eps=1e-6)),
+                       (lambda p: paddle.optimizer.RAdam(0.01, parameters=p), lambda p: torch.optim.RAdam(p, lr=0.01)),
+                       (lambda p: paddle.optimizer.NAdam(0.01, parameters=p), lambda p: torch.optim.NAdam(p, lr=0.01))):
+        torch.manual_seed(0)
+        lin = paddle.nn.Linear(6, 3)
+        tw = lin.weight.detach().clone().requires_grad_(True)
+        tb = lin.bias.detach().clone().requires_grad_(True)
+        po, to = mk_p(lin.parameters()), mk_t([tw, tb])
+        x = torch.randn(4, 6)
+        for _ in range(7):
+            (lin(x) ** 2).sum().backward()
+            po.step()
+            po.clear_grad()
+            ((x @ tw + tb) ** 2).sum().backward()
+            to.step()
+            to.zero_grad()
+        torch.testing.assert_close(lin.weight.detach(), tw.detach(), rtol=1e-5, atol=1e-6)
+    a = torch.arange(6.0).reshape(2, 3)
+    torch.testing.assert_close(paddle.diff(a, axis=1), torch.ones(2, 2))
+    torch.testing.assert_close(paddle.quantile(a, 0.5, axis=1), torch.tensor([1.0, 4.0]))
+    assert paddle.unflatten(a, 1, [3, 1]).shape == (2, 3, 1)
+    torch.testing.assert_close(paddle.nanmean(torch.tensor([1.0, float("nan"), 3.0])), torch.tensor(2.0))
