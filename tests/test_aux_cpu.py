@@ -186,3 +186,16 @@ def test_extra_layers_optimizers_and_tensor_functions():
     torch.testing.assert_close(paddle.quantile(a, 0.5, axis=1), torch.tensor([1.0, 4.0]))
     assert paddle.unflatten(a, 1, [3, 1]).shape == (2, 3, 1)
     torch.testing.assert_close(paddle.nanmean(torch.tensor([1.0, float("nan"), 3.0])), torch.tensor(2.0))
+
+
+def test_vision_models_and_transforms():
+    from paddle_b200.vision import models
+    from paddle_b200.vision import transforms as T
+    x = torch.randn(2, 3, 64, 64)
+    assert models.mobilenet_v2(num_classes=10)(x).shape == (2, 10)
+    assert models.vgg11(num_classes=7)(torch.randn(1, 3, 224, 224)).shape == (1, 7)
+    t = T.Compose([T.RandomResizedCrop(32), T.RandomHorizontalFlip(), T.ColorJitter(0.2, 0.2), T.RandomErasing(1.0),
+                   T.Normalize([0.5] * 3, [0.5] * 3)])
+    assert t(torch.rand(3, 48, 40)).shape == (3, 32, 32)
+    assert T.RandomCrop(32, padding=4)(torch.rand(3, 32, 32)).shape == (3, 32, 32)
+    assert T.Pad([1, 2])(torch.rand(3, 4, 4)).shape == (3, 8, 6)
