@@ -36,7 +36,7 @@ from . import distributed  # noqa: E402,F401
 from .distributed.parallel import DataParallel  # noqa: E402,F401
 from .hapi import Model, summary  # noqa: E402,F401
 from . import models, ops, parallel  # noqa: E402,F401
-from . import callbacks, distribution, fft, jit, linalg, static  # noqa: E402,F401
+from . import callbacks, distribution, fft, geometric, jit, linalg, signal, sparse, static  # noqa: E402,F401
 
 Tensor = _torch.Tensor
 version = type("version", (), {"full_version": __version__, "cuda": staticmethod(lambda: _torch.version.cuda),

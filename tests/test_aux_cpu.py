@@ -199,3 +199,16 @@ def test_vision_models_and_transforms():
     assert t(torch.rand(3, 48, 40)).shape == (3, 32, 32)
     assert T.RandomCrop(32, padding=4)(torch.rand(3, 32, 32)).shape == (3, 32, 32)
     assert T.Pad([1, 2])(torch.rand(3, 4, 4)).shape == (3, 8, 6)
+
+
+def test_geometric_sparse_signal_namespaces():
+    import paddle
+    x = torch.tensor([[1.0, 2.0], [3.0, 4.0], [5.0, 6.0]])
+    torch.testing.assert_close(paddle.geometric.segment_mean(x, torch.tensor([0, 0, 1])), torch.tensor([[2.0, 3.0], [5.0, 6.0]]))
+    out = paddle.geometric.send_u_recv(x, torch.tensor([0, 1, 2, 0]), torch.tensor([1, 2, 1, 0]), "sum")
+    torch.testing.assert_close(out, torch.tensor([[1.0, 2.0], [6.0, 8.0], [3.0, 4.0]]))
+    s = paddle.sparse.sparse_coo_tensor([[0, 1], [1, 0]], [1.0, 2.0], [2, 2])
+    torch.testing.assert_close(paddle.sparse.matmul(s, torch.eye(2)), torch.tensor([[0.0, 1.0], [2.0, 0.0]]))
+    w, sig = torch.hann_window(16), torch.randn(2, 128)
+    rec = paddle.signal.istft(paddle.signal.stft(sig, 16, 4, window=w), 16, 4, window=w, length=128)
+    torch.testing.assert_close(rec, sig, rtol=1e-4, atol=1e-5)
