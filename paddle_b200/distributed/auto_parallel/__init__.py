@@ -194,6 +194,55 @@ def dtensor_from_fn(fn, mesh, placements, *args, **kwargs):
     return shard_tensor(fn(*args, **kwargs), mesh, placements)
 
 
+def dtensor_from_local(local_tensor, mesh, placements):
+    """Wrap this rank's local shard as a distributed tensor (reference: auto_parallel/api.py:499-520): the global
+    shape is the local shape multiplied by the mesh size along every sharded dim."""
+    gshape = list(local_tensor.shape)
+    for ax, pl in enumerate(placements):
+        if isinstance(pl, Shard):
+            gshape[pl.dim] *= mesh.shape[ax]
+    return _attach(local_tensor, mesh, placements, tuple(gshape))
+
+
+def dtensor_to_local(dist_tensor, mesh=None, placements=None):
+    """The local shard of a distributed tensor, as a plain tensor."""
+    out = dist_tensor.detach().clone() if not dist_tensor.requires_grad else dist_tensor * 1
+    for attr in ("process_mesh", "placements", "_global_shape"):
+        if hasattr(out, attr):
+            try:
+                delattr(out, attr)
+            except AttributeError:
+                pass
+    return out
+
+
+_g_mesh = None
+
+
+def get_mesh():
+    return _g_mesh
+
+
+def set_mesh(mesh):
+    global _g_mesh
+    _g_mesh = mesh
+
+
+def create_mesh(mesh_dims):
+    """``create_mesh([("dp", 2), ("mp", 4)])`` -> global ProcessMesh over all ranks (reference: interface.py:326)."""
+    import numpy as np
+    names = [n for n, _ in mesh_dims]
+    shape = [d for _, d in mesh_dims]
+    mesh = ProcessMesh(np.arange(int(np.prod(shape))).reshape(shape).tolist(), names)
+    set_mesh(mesh)
+    return mesh
+
+
+class ReduceType:
+    """Reduce kinds of a Partial placement (reference: paddle.base.core.ReduceType)."""
+    kRedSum, kRedMax, kRedMin, kRedProd, kRedAvg, kRedAny, kRedAll = range(7)
+
+
 def _gather_axis(t, group, dim):
     parts = []
     comm.all_gather(parts, t.contiguous(), group)
