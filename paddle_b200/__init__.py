@@ -38,6 +38,10 @@ from .hapi import Model, summary  # noqa: E402,F401
 from . import models, ops, parallel  # noqa: E402,F401
 from . import callbacks, distribution, fft, geometric, jit, linalg, signal, sparse, static  # noqa: E402,F401
 
+from .tensor.compat import install_inplace_variants as _iiv  # noqa: E402
+from .tensor._inplace_names import INPLACE as _INPLACE  # noqa: E402
+
+_iiv(globals(), _INPLACE)
 Tensor = _torch.Tensor
 version = type("version", (), {"full_version": __version__, "cuda": staticmethod(lambda: _torch.version.cuda),
                                 "show": staticmethod(lambda: print(__version__))})

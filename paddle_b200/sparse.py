@@ -7,7 +7,7 @@ import torch
 def sparse_coo_tensor(indices, values, shape=None, dtype=None, place=None, stop_gradient=True):
     i, v = torch.as_tensor(indices), torch.as_tensor(values)
     if dtype is not None:
-        from .framework.dtype import convert_dtype
+        from .framework.dtype import to_torch_dtype as convert_dtype
         v = v.to(convert_dtype(dtype))
     t = torch.sparse_coo_tensor(i, v, size=tuple(shape) if shape is not None else None).coalesce()
     t.requires_grad_(not stop_gradient and v.is_floating_point())
@@ -17,7 +17,7 @@ def sparse_coo_tensor(indices, values, shape=None, dtype=None, place=None, stop_
 def sparse_csr_tensor(crows, cols, values, shape, dtype=None, place=None, stop_gradient=True):
     v = torch.as_tensor(values)
     if dtype is not None:
-        from .framework.dtype import convert_dtype
+        from .framework.dtype import to_torch_dtype as convert_dtype
         v = v.to(convert_dtype(dtype))
     return torch.sparse_csr_tensor(torch.as_tensor(crows), torch.as_tensor(cols), v, size=tuple(shape))
 

@@ -3,4 +3,5 @@ from .creation import *  # noqa: F401,F403
 from .math import *  # noqa: F401,F403
 from .manipulation import *  # noqa: F401,F403
 from .extra import *  # noqa: F401,F403
-from . import creation, extra, math, manipulation  # noqa: F401
+from .compat import *  # noqa: F401,F403
+from . import compat, creation, extra, math, manipulation  # noqa: F401

@@ -25,7 +25,7 @@ def frac(x, name=None):
 def logcumsumexp(x, axis=None, dtype=None, name=None):
     if axis is None:
         x, axis = x.reshape(-1), 0
-    return torch.logcumsumexp(x if dtype is None else x.to(_dt.convert_dtype(dtype)), axis)
+    return torch.logcumsumexp(x if dtype is None else x.to(_dt.to_torch_dtype(dtype)), axis)
 
 
 def nansum(x, axis=None, dtype=None, keepdim=False, name=None):
@@ -59,11 +59,11 @@ def as_strided(x, shape, stride, offset=0, name=None):
 
 
 def rand_like(x, dtype=None, name=None):
-    return torch.rand_like(x, dtype=_dt.convert_dtype(dtype) if dtype is not None else None)
+    return torch.rand_like(x, dtype=_dt.to_torch_dtype(dtype) if dtype is not None else None)
 
 
 def randn_like(x, dtype=None, name=None):
-    return torch.randn_like(x, dtype=_dt.convert_dtype(dtype) if dtype is not None else None)
+    return torch.randn_like(x, dtype=_dt.to_torch_dtype(dtype) if dtype is not None else None)
 
 
 def heaviside(x, y, name=None):
@@ -102,14 +102,14 @@ def cummax(x, axis=None, dtype="int64", name=None):
     if axis is None:
         x, axis = x.reshape(-1), 0
     v, i = torch.cummax(x, axis)
-    return v, i.to(_dt.convert_dtype(dtype))
+    return v, i.to(_dt.to_torch_dtype(dtype))
 
 
 def cummin(x, axis=None, dtype="int64", name=None):
     if axis is None:
         x, axis = x.reshape(-1), 0
     v, i = torch.cummin(x, axis)
-    return v, i.to(_dt.convert_dtype(dtype))
+    return v, i.to(_dt.to_torch_dtype(dtype))
 
 
 def trapezoid(y, x=None, dx=None, axis=-1, name=None):

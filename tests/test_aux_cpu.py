@@ -212,3 +212,18 @@ def test_geometric_sparse_signal_namespaces():
     w, sig = torch.hann_window(16), torch.randn(2, 128)
     rec = paddle.signal.istft(paddle.signal.stft(sig, 16, 4, window=w), 16, 4, window=w, length=128)
     torch.testing.assert_close(rec, sig, rtol=1e-4, atol=1e-5)
+
+
+def test_top_level_api_long_tail():
+    import paddle
+    x = torch.tensor([1.0, -4.0])
+    assert paddle.abs_(x) is x and x.tolist() == [1.0, 4.0]
+    y = torch.tensor([0.5])
+    y.logit_()
+    assert float(y) == 0.0
+    torch.testing.assert_close(paddle.take(torch.arange(6).reshape(2, 3), torch.tensor([0, 5, -1])), torch.tensor([0, 5, 5]))
+    assert paddle.flops(paddle.nn.Linear(4, 8), [2, 4]) == 2 * 2 * 4 * 8
+    assert paddle.tril_indices(3).shape == (2, 6) and paddle.logspace(0, 2, 3, dtype="float64").dtype == torch.float64
+    assert [t.shape[0] for t in paddle.tensor_split(torch.arange(7), 3)] == [3, 2, 2]
+    torch.testing.assert_close(paddle.reduce_as(torch.ones(2, 3), torch.ones(1, 3)), torch.full((1, 3), 2.0))
+    torch.testing.assert_close(paddle.slice_scatter(torch.zeros(4), torch.ones(2), [0], [0], [4], [2]), torch.tensor([1.0, 0.0, 1.0, 0.0]))
