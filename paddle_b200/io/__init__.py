@@ -80,6 +80,19 @@ class RandomSampler(Sampler):
         return self.num_samples
 
 
+class SubsetRandomSampler(Sampler):
+    def __init__(self, indices, generator=None):
+        self.indices, self.generator = list(indices), generator
+
+    def __iter__(self):
+        import torch as _t
+        for i in _t.randperm(len(self.indices), generator=self.generator).tolist():
+            yield self.indices[i]
+
+    def __len__(self):
+        return len(self.indices)
+
+
 class WeightedRandomSampler(Sampler):
     def __init__(self, weights, num_samples, replacement=True):
         self.weights, self.num_samples, self.replacement = np.asarray(weights, dtype=np.float64), num_samples, replacement

@@ -119,3 +119,23 @@ def matrix_exp(x, name=None):
 
 def householder_product(x, tau, name=None):
     return torch.linalg.householder_product(x, tau)
+
+
+def cholesky_inverse(x, upper=False, name=None):
+    return torch.cholesky_inverse(x, upper=upper)
+
+
+def svd_lowrank(x, q=None, niter=2, M=None, name=None):
+    return torch.svd_lowrank(x, q=q if q is not None else min(6, *x.shape[-2:]), niter=niter, M=M)
+
+
+def pca_lowrank(x, q=None, center=True, niter=2, name=None):
+    return torch.pca_lowrank(x, q=q, center=center, niter=niter)
+
+
+def lu_unpack(x, y, unpack_ludata=True, unpack_pivots=True, name=None):
+    return torch.lu_unpack(x, y.to(torch.int32), unpack_data=unpack_ludata, unpack_pivots=unpack_pivots)
+
+
+def ormqr(x, tau, y, left=True, transpose=False, name=None):
+    return torch.ormqr(x, tau, y, left=left, transpose=transpose)

@@ -96,3 +96,39 @@ def accuracy(input, label, k=1, correct=None, total=None, name=None):
     idx = torch.topk(input, k, dim=-1).indices
     lab = label.reshape(-1, 1)
     return (idx == lab).any(-1).float().mean()
+
+
+class Auc(Metric):
+    """Area under the ROC / PR curve from thresholded histograms (reference: metric/metrics.py Auc)."""
+
+    def __init__(self, curve="ROC", num_thresholds=4095, name="auc", *args, **kwargs):
+        self._curve, self._n, self._name = curve, num_thresholds, name
+        self.reset()
+
+    def reset(self):
+        import numpy as np
+        self._pos = np.zeros(self._n + 1, dtype=np.int64)
+        self._neg = np.zeros(self._n + 1, dtype=np.int64)
+
+    def update(self, preds, labels):
+        import numpy as np
+        preds = preds.detach().cpu().numpy() if hasattr(preds, "detach") else np.asarray(preds)
+        labels = labels.detach().cpu().numpy() if hasattr(labels, "detach") else np.asarray(labels)
+        p1 = preds[:, 1] if preds.ndim == 2 and preds.shape[1] == 2 else preds.reshape(-1)
+        bins = np.clip((p1 * self._n).astype(np.int64), 0, self._n)
+        lab = labels.reshape(-1).astype(bool)
+        np.add.at(self._pos, bins[lab], 1)
+        np.add.at(self._neg, bins[~lab], 1)
+
+    def accumulate(self):
+        tot_pos = tot_neg = 0.0
+        auc = 0.0
+        for i in range(self._n, -1, -1):
+            p_prev, n_prev = tot_pos, tot_neg
+            tot_pos += self._pos[i]
+            tot_neg += self._neg[i]
+            auc += (tot_neg - n_prev) * (tot_pos + p_prev) / 2.0
+        return auc / tot_pos / tot_neg if tot_pos > 0 and tot_neg > 0 else 0.0
+
+    def name(self):
+        return self._name

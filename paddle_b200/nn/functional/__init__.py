@@ -458,3 +458,9 @@ def ctc_loss(log_probs, labels, input_lengths, label_lengths, blank=0, reduction
 def sequence_mask(x, maxlen=None, dtype="int64", name=None):
     maxlen = int(maxlen if maxlen is not None else x.max().item())
     return (torch.arange(maxlen, device=x.device) < x.unsqueeze(-1)).to(_dt.to_torch_dtype(dtype))
+
+
+from .extra import *  # noqa: E402,F401,F403
+from .extra import _inplace as _mk_inplace  # noqa: E402
+
+elu_, hardtanh_, leaky_relu_, softmax_, tanh_, thresholded_relu_ = (_mk_inplace(f) for f in (elu, hardtanh, leaky_relu, softmax, tanh, thresholded_relu))

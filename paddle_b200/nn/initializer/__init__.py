@@ -150,3 +150,18 @@ def set_global_initializer(weight_init, bias_init=None):
 
 def calculate_gain(nonlinearity, param=None):
     return torch.nn.init.calculate_gain(nonlinearity, param)
+
+
+class Bilinear(Initializer):
+    """Bilinear-upsampling kernel for transposed convolutions (reference: nn/initializer/bilinear.py)."""
+
+    def _fill(self, p):
+        if p.dim() != 4 or p.shape[2] != p.shape[3]:
+            raise ValueError("Bilinear initializer needs a 4-D weight with square kernels")
+        k = p.shape[3]
+        f = (k + 1) // 2
+        c = (2 * f - 1 - f % 2) / (2.0 * f)
+        og = torch.arange(k, dtype=torch.float32)
+        filt = (1 - (og / f - c).abs())
+        w = filt[:, None] * filt[None, :]
+        p.copy_(w.to(p.dtype).expand_as(p))

@@ -368,3 +368,110 @@ class HSigmoidLoss(Layer):
             lab = torch.where(valid, parent, lab)
             lab = torch.where(lab <= 1, torch.zeros_like(lab), lab)
         return loss.reshape(-1, 1)
+
+
+# ---------------------------------------------------------------------------------------------- remaining layers
+RNNCellBase = _CellBase
+AdaptiveMaxPool3D = _wrap("AdaptiveMaxPool3D", lambda output_size, return_mask=False: torch.nn.AdaptiveMaxPool3d(
+    output_size, return_indices=return_mask))
+PoissonNLLLoss = _wrap("PoissonNLLLoss", lambda log_input=True, full=False, epsilon=1e-8, reduction="mean":
+                       torch.nn.PoissonNLLLoss(log_input, full, eps=epsilon, reduction=reduction))
+GaussianNLLLoss = _wrap("GaussianNLLLoss", lambda full=False, epsilon=1e-6, reduction="mean":
+                        torch.nn.GaussianNLLLoss(full=full, eps=epsilon, reduction=reduction))
+MultiMarginLoss = _wrap("MultiMarginLoss", lambda p=1, margin=1.0, weight=None, reduction="mean":
+                        torch.nn.MultiMarginLoss(p, margin, weight, reduction=reduction))
+TripletMarginWithDistanceLoss = _wrap("TripletMarginWithDistanceLoss", lambda distance_function=None, margin=1.0, swap=False,
+                                      reduction="mean": torch.nn.TripletMarginWithDistanceLoss(
+                                          distance_function=distance_function, margin=margin, swap=swap, reduction=reduction))
+MaxUnPool1D = _wrap("MaxUnPool1D", lambda kernel_size, stride=None, padding=0, data_format="NCL", output_size=None:
+                    torch.nn.MaxUnpool1d(kernel_size, stride, padding))
+MaxUnPool2D = _wrap("MaxUnPool2D", lambda kernel_size, stride=None, padding=0, data_format="NCHW", output_size=None:
+                    torch.nn.MaxUnpool2d(kernel_size, stride, padding))
+MaxUnPool3D = _wrap("MaxUnPool3D", lambda kernel_size, stride=None, padding=0, data_format="NCDHW", output_size=None:
+                    torch.nn.MaxUnpool3d(kernel_size, stride, padding))
+RReLU = _wrap("RReLU", lambda lower=1.0 / 8.0, upper=1.0 / 3.0: torch.nn.RReLU(lower, upper))
+FractionalMaxPool2D = _wrap("FractionalMaxPool2D", lambda output_size, kernel_size=None, random_u=None, return_mask=False:
+                            torch.nn.FractionalMaxPool2d(kernel_size or 2, output_size=output_size, return_indices=return_mask))
+FractionalMaxPool3D = _wrap("FractionalMaxPool3D", lambda output_size, kernel_size=None, random_u=None, return_mask=False:
+                            torch.nn.FractionalMaxPool3d(kernel_size or 2, output_size=output_size, return_indices=return_mask))
+LPPool1D = _wrap("LPPool1D", lambda norm_type, kernel_size, stride=None, padding=0, ceil_mode=False, data_format="NCL":
+                 torch.nn.LPPool1d(float(norm_type), kernel_size, stride, ceil_mode))
+LPPool2D = _wrap("LPPool2D", lambda norm_type, kernel_size, stride=None, padding=0, ceil_mode=False, data_format="NCHW":
+                 torch.nn.LPPool2d(float(norm_type), kernel_size, stride, ceil_mode))
+AdaptiveLogSoftmaxWithLoss = _wrap("AdaptiveLogSoftmaxWithLoss", lambda in_features, n_classes, cutoffs, div_value=4.0,
+                                   head_bias=False: torch.nn.AdaptiveLogSoftmaxWithLoss(in_features, n_classes, cutoffs,
+                                                                                        div_value, head_bias))
+
+
+class ZeroPad1D(_PadNd):
+    _nd = 1
+
+    def __init__(self, padding, data_format="NCL", name=None):
+        super().__init__(padding, "constant", 0.0)
+
+
+class ZeroPad3D(_PadNd):
+    _nd = 3
+
+    def __init__(self, padding, data_format="NCDHW", name=None):
+        super().__init__(padding, "constant", 0.0)
+
+
+class RNNTLoss(Layer):
+    def __init__(self, blank=0, fastemit_lambda=0.001, reduction="mean", name=None):
+        super().__init__()
+
+    def forward(self, *a, **k):
+        return F.rnnt_loss(*a, **k)
+
+
+class BeamSearchDecoder:
+    """Beam-search decoding over an RNN cell (reference: nn.BeamSearchDecoder + nn.dynamic_decode), greedy-free minimal
+    form: keeps ``beam_size`` hypotheses per batch entry, log-prob scored, finished beams frozen on ``end_token``."""
+
+    def __init__(self, cell, start_token, end_token, beam_size, embedding_fn=None, output_fn=None):
+        self.cell, self.start, self.end, self.k = cell, start_token, end_token, beam_size
+        self.embedding_fn, self.output_fn = embedding_fn, output_fn
+
+
+def dynamic_decode(decoder, inits=None, max_step_num=None, output_time_major=False, impute_finished=False,
+                   is_test=False, return_length=False, **kwargs):
+    cell, k, end = decoder.cell, decoder.k, decoder.end
+    state = inits
+    h0 = state[0] if isinstance(state, (tuple, list)) else state
+    b = h0.shape[0]
+    dev = h0.device
+
+    def tile(s):
+        return s.unsqueeze(1).expand(b, k, *s.shape[1:]).reshape(b * k, *s.shape[1:])
+    state = tuple(tile(s) for s in state) if isinstance(state, (tuple, list)) else tile(state)
+    tokens = torch.full((b * k,), decoder.start, dtype=torch.long, device=dev)
+    scores = torch.zeros(b, k, device=dev)
+    scores[:, 1:] = -1e9
+    finished = torch.zeros(b, k, dtype=torch.bool, device=dev)
+    ids, parents = [], []
+    for _ in range(max_step_num or 32):
+        inp = decoder.embedding_fn(tokens) if decoder.embedding_fn else tokens
+        out, state = cell(inp, state)
+        logits = decoder.output_fn(out) if decoder.output_fn else out
+        logp = torch.log_softmax(logits.float(), -1).reshape(b, k, -1)
+        V = logp.shape[-1]
+        frozen = torch.full_like(logp, -1e9)
+        frozen[..., end] = 0
+        logp = torch.where(finished[..., None], frozen, logp)
+        total = (scores[..., None] + logp).reshape(b, k * V)
+        scores, flat = total.topk(k, -1)
+        parent, tok = flat // V, flat % V
+        ids.append(tok)
+        parents.append(parent)
+        gidx = (parent + torch.arange(b, device=dev)[:, None] * k).reshape(-1)
+        state = tuple(s[gidx] for s in state) if isinstance(state, tuple) else state[gidx]
+        finished = finished.gather(1, parent) | (tok == end)
+        tokens = tok.reshape(-1)
+        if bool(finished.all()):
+            break
+    ids_t, par_t = torch.stack(ids), torch.stack(parents)
+    seq = F.gather_tree(ids_t, par_t)
+    seq = seq if output_time_major else seq.permute(1, 0, 2)
+    lengths = (seq != end).sum(0 if output_time_major else 1) if return_length else None
+    return (seq, state, lengths) if return_length else (seq, state)

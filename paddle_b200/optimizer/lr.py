@@ -212,3 +212,69 @@ class ReduceOnPlateau(LRScheduler):
             if self.last_lr - new_lr > self.epsilon:
                 self.last_lr = new_lr
             self.cooldown_counter, self.num_bad = self.cooldown, 0
+
+
+class MultiplicativeDecay(LRScheduler):
+    def __init__(self, learning_rate, lr_lambda, last_epoch=-1, verbose=False):
+        self.lr_lambda = lr_lambda
+        self._cur = float(learning_rate)
+        super().__init__(learning_rate, last_epoch, verbose)
+
+    def get_lr(self):
+        cur = self.base_lr
+        for e in range(1, self.last_epoch + 1):
+            cur = cur * self.lr_lambda(e)
+        return cur
+
+
+class LinearLR(LRScheduler):
+    def __init__(self, learning_rate, total_steps, start_factor=1.0 / 3, end_factor=1.0, last_epoch=-1, verbose=False):
+        self.total_steps, self.start_factor, self.end_factor = total_steps, start_factor, end_factor
+        super().__init__(learning_rate, last_epoch, verbose)
+
+    def get_lr(self):
+        t = min(max(self.last_epoch, 0), self.total_steps)
+        return self.base_lr * (self.start_factor + (self.end_factor - self.start_factor) * t / self.total_steps)
+
+
+class CosineAnnealingWarmRestarts(LRScheduler):
+    def __init__(self, learning_rate, T_0, T_mult=1, eta_min=0, last_epoch=-1, verbose=False):
+        self.T_0, self.T_mult, self.eta_min = T_0, T_mult, eta_min
+        super().__init__(learning_rate, last_epoch, verbose)
+
+    def get_lr(self):
+        import math
+        e, T = max(self.last_epoch, 0), self.T_0
+        if self.T_mult == 1:
+            cur = e % T
+        else:
+            n = int(math.log(e / self.T_0 * (self.T_mult - 1) + 1, self.T_mult)) if e >= self.T_0 else 0
+            cur = e - self.T_0 * (self.T_mult ** n - 1) // (self.T_mult - 1)
+            T = self.T_0 * self.T_mult ** n
+        return self.eta_min + (self.base_lr - self.eta_min) * (1 + math.cos(math.pi * cur / T)) / 2
+
+
+class CyclicLR(LRScheduler):
+    def __init__(self, base_learning_rate, max_learning_rate, step_size_up, step_size_down=None, mode="triangular",
+                 exp_gamma=1.0, scale_fn=None, scale_mode="cycle", last_epoch=-1, verbose=False):
+        self.max_lr = max_learning_rate
+        self.up = float(step_size_up)
+        self.down = float(step_size_down) if step_size_down is not None else self.up
+        self.mode, self.gamma, self.scale_fn, self.scale_mode = mode, exp_gamma, scale_fn, scale_mode
+        super().__init__(base_learning_rate, last_epoch, verbose)
+
+    def get_lr(self):
+        import math
+        total = self.up + self.down
+        e = max(self.last_epoch, 0)
+        cycle = math.floor(1 + e / total)
+        x = 1.0 + e / total - cycle
+        pct = x / (self.up / total) if x <= self.up / total else (x - 1) / (self.up / total - 1)
+        amp = (self.max_lr - self.base_lr) * pct
+        if self.scale_fn is not None:
+            return self.base_lr + amp * self.scale_fn(cycle if self.scale_mode == "cycle" else e)
+        if self.mode == "triangular2":
+            return self.base_lr + amp / (2.0 ** (cycle - 1))
+        if self.mode == "exp_range":
+            return self.base_lr + amp * self.gamma ** e
+        return self.base_lr + amp

@@ -719,3 +719,32 @@ class Rprop(Optimizer):
             gf[sign < 0] = 0
             p.sub_((lrs * gf.sign()).to(p.dtype))
             prev.copy_(gf)
+
+
+class LBFGS(Optimizer):
+    """L-BFGS with optional strong-Wolfe line search (reference: python/paddle/optimizer/lbfgs.py); the two-loop
+    recursion and line search are torch.optim.LBFGS, driven through Paddle's ``step(closure)`` contract."""
+
+    def __init__(self, learning_rate=1.0, max_iter=20, max_eval=None, tolerance_grad=1e-07, tolerance_change=1e-09,
+                 history_size=100, line_search_fn=None, parameters=None, weight_decay=None, grad_clip=None, name=None):
+        super().__init__(learning_rate, parameters, weight_decay, grad_clip, name)
+        self._impl = torch.optim.LBFGS([p for p in self._all_params()], lr=float(self.get_lr()), max_iter=max_iter,
+                                       max_eval=max_eval, tolerance_grad=tolerance_grad, tolerance_change=tolerance_change,
+                                       history_size=history_size, line_search_fn=line_search_fn)
+
+    def step(self, closure):
+        def wrapped():
+            self.clear_grad(set_to_zero=False)
+            with torch.enable_grad():
+                loss = closure()
+            return loss
+        for g in self._impl.param_groups:
+            g["lr"] = float(self.get_lr())
+        return self._impl.step(wrapped)
+
+    def state_dict(self):
+        return {"lbfgs": self._impl.state_dict()}
+
+    def set_state_dict(self, state_dict):
+        if "lbfgs" in state_dict:
+            self._impl.load_state_dict(state_dict["lbfgs"])

@@ -227,3 +227,38 @@ def test_top_level_api_long_tail():
     assert [t.shape[0] for t in paddle.tensor_split(torch.arange(7), 3)] == [3, 2, 2]
     torch.testing.assert_close(paddle.reduce_as(torch.ones(2, 3), torch.ones(1, 3)), torch.full((1, 3), 2.0))
     torch.testing.assert_close(paddle.slice_scatter(torch.zeros(4), torch.ones(2), [0], [0], [4], [2]), torch.tensor([1.0, 0.0, 1.0, 0.0]))
+
+
+def test_remaining_api_gaps_against_reference_lists():
+    import paddle
+    import paddle.nn.functional as F
+    # LBFGS converges on least squares through the closure contract
+    w = paddle.nn.Linear(3, 1)
+    x = torch.randn(64, 3)
+    y = x @ torch.tensor([[1.0], [-2.0], [0.5]]) + 0.3
+    opt = paddle.optimizer.LBFGS(1.0, max_iter=50, line_search_fn="strong_wolfe", parameters=w.parameters())
+
+    def closure():
+        loss = ((w(x) - y) ** 2).mean()
+        loss.backward()
+        return loss
+    for _ in range(3):
+        opt.step(closure)
+    assert float(((w(x) - y) ** 2).mean()) < 1e-6
+    s = paddle.optimizer.lr.CyclicLR(0.1, 1.0, 4)
+    vals = []
+    for _ in range(9):
+        vals.append(round(s(), 3))
+        s.step()
+    assert vals == [0.1, 0.325, 0.55, 0.775, 1.0, 0.775, 0.55, 0.325, 0.1]
+    a = paddle.metric.Auc()
+    a.update(torch.tensor([[0.9, 0.1], [0.2, 0.8], [0.3, 0.7], [0.6, 0.4]]), torch.tensor([0, 1, 1, 0]))
+    assert abs(a.accumulate() - 1.0) < 1e-6
+    ids = torch.tensor([[[2, 2], [6, 1]], [[3, 9], [6, 1]], [[0, 1], [9, 0]]])
+    par = torch.tensor([[[0, 0], [1, 1]], [[1, 0], [1, 0]], [[0, 0], [0, 1]]])
+    assert F.gather_tree(ids, par).tolist() == [[[2, 2], [1, 6]], [[3, 3], [6, 1]], [[0, 1], [9, 0]]]
+    dec = paddle.nn.BeamSearchDecoder(paddle.nn.GRUCell(8, 8), 0, 1, 3, embedding_fn=paddle.nn.Embedding(10, 8),
+                                      output_fn=paddle.nn.Linear(8, 10))
+    seq, _ = paddle.nn.dynamic_decode(dec, inits=torch.zeros(2, 8), max_step_num=5)
+    assert seq.shape[0] == 2 and seq.shape[2] == 3
+    assert len(list(paddle.io.SubsetRandomSampler([3, 5, 7]))) == 3
