@@ -728,7 +728,7 @@ class LBFGS(Optimizer):
     def __init__(self, learning_rate=1.0, max_iter=20, max_eval=None, tolerance_grad=1e-07, tolerance_change=1e-09,
                  history_size=100, line_search_fn=None, parameters=None, weight_decay=None, grad_clip=None, name=None):
         super().__init__(learning_rate, parameters, weight_decay, grad_clip, name)
-        self._impl = torch.optim.LBFGS([p for p in self._all_params()], lr=float(self.get_lr()), max_iter=max_iter,
+        self._impl = torch.optim.LBFGS([p for p, _ in self._all_params()], lr=float(self.get_lr()), max_iter=max_iter,
                                        max_eval=max_eval, tolerance_grad=tolerance_grad, tolerance_change=tolerance_change,
                                        history_size=history_size, line_search_fn=line_search_fn)
 
