@@ -45,3 +45,43 @@ Stream = torch.cuda.Stream
 Event = torch.cuda.Event
 current_stream = torch.cuda.current_stream
 stream_guard = torch.cuda.stream
+
+
+def get_cudnn_version():
+    import torch
+    v = torch.backends.cudnn.version()
+    return int(v) if v else None
+
+
+def is_compiled_with_ipu():
+    return False
+
+
+def is_compiled_with_cinn():
+    return False
+
+
+def get_all_custom_device_type():
+    return []
+
+
+def get_available_custom_device():
+    return []
+
+
+def set_stream(stream=None):
+    """Make ``stream`` the current CUDA stream; returns the previous one."""
+    import torch
+    prev = torch.cuda.current_stream()
+    if stream is not None:
+        torch.cuda.set_stream(stream)
+    return prev
+
+
+class XPUPlace:
+    def __init__(self, *a, **k):
+        raise NotImplementedError("XPU devices are not supported: this framework targets NVIDIA B200 only")
+
+
+class IPUPlace(XPUPlace):
+    pass

@@ -104,3 +104,58 @@ def fused_multi_head_attention(*a, **k):
 
 def fused_feedforward(*a, **k):
     raise NotImplementedError("fused_feedforward (legacy fused op): compose Linear + swiglu/fused_bias_act")
+
+
+def fused_bias_dropout_residual_layer_norm(x, residual, bias=None, ln_scale=None, ln_bias=None, dropout_rate=0.5,
+                                           ln_epsilon=1e-5, training=True, mode="upscale_in_train", name=None):
+    """layer_norm(residual + dropout(x + bias)) (reference: incubate/nn/functional/fused_transformer.py:236)."""
+    y = x if bias is None else x + bias
+    y = torch.nn.functional.dropout(y, dropout_rate, training) if mode == "upscale_in_train" else \
+        (torch.nn.functional.dropout(y, dropout_rate, training) * (1 - dropout_rate) if training else y * (1 - dropout_rate))
+    return F.layer_norm(residual + y, [x.shape[-1]], ln_scale, ln_bias, ln_epsilon)
+
+
+def fused_ec_moe(x, gate, bmm0_weight, bmm0_bias, bmm1_weight, bmm1_bias, act_type="gelu"):
+    """Expert-choice style dense MoE: every expert FFN is evaluated with batched GEMMs and mixed by softmax(gate)
+    (reference: incubate/nn/functional/fused_ec_moe.py).  x [b,s,d], gate [b,s,e], weights [e,d,f] / [e,f,d]."""
+    b, s, d = x.shape
+    probs = torch.softmax(gate.float(), -1).to(x.dtype)                       # [b, s, e]
+    xe = x.reshape(1, b * s, d).expand(bmm0_weight.shape[0], -1, -1)           # [e, tokens, d]
+    h = torch.baddbmm(bmm0_bias, xe, bmm0_weight)
+    h = {"gelu": torch.nn.functional.gelu, "relu": torch.relu}[act_type](h)
+    y = torch.baddbmm(bmm1_bias, h, bmm1_weight)                               # [e, tokens, d]
+    return torch.einsum("etd,te->td", y, probs.reshape(b * s, -1)).reshape(b, s, d)
+
+
+def variable_length_memory_efficient_attention(query, key, value, seq_lens, kv_seq_lens, mask=None, scale=None,
+                                               causal=False, pre_cache_length=0):
+    """Attention over padded [b, h, s, d] batches with per-sample valid lengths (reference: incubate/nn/functional/
+    variable_length_memory_efficient_attention.py); padded keys are masked, padded query rows return zeros."""
+    b, h, sq, d = query.shape
+    sk = key.shape[2]
+    scale = scale if scale is not None else d ** -0.5
+    kq = torch.arange(sq, device=query.device)[None, :] < seq_lens.reshape(-1, 1)
+    kk = torch.arange(sk, device=query.device)[None, :] < kv_seq_lens.reshape(-1, 1)
+    m = (kq[:, None, :, None] & kk[:, None, None, :])
+    if causal:
+        m = m & torch.ones(sq, sk, dtype=torch.bool, device=query.device).tril(sk - sq)
+    bias = torch.zeros(b, 1, sq, sk, dtype=query.dtype, device=query.device).masked_fill(~m, float("-inf"))
+    if mask is not None:
+        bias = bias + mask
+    sc = torch.matmul(query, key.transpose(-1, -2)) * scale + bias
+    p = torch.nan_to_num(torch.softmax(sc.float(), -1), nan=0.0).to(query.dtype)
+    return torch.matmul(p, value)
+
+
+def _inference_only(name):
+    def f(*a, **k):
+        raise NotImplementedError(f"{name} is a decode-time inference kernel of the reference (fused_multi_transformer / "
+                                  "block attention family); this framework targets training (SURVEY 2.6.b, out of scope)")
+    f.__name__ = name
+    return f
+
+
+fused_multi_transformer = _inference_only("fused_multi_transformer")
+masked_multihead_attention = _inference_only("masked_multihead_attention")
+block_multihead_attention = _inference_only("block_multihead_attention")
+blha_get_max_len = _inference_only("blha_get_max_len")

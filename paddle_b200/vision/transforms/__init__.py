@@ -196,3 +196,201 @@ class RandomErasing:
         i, j = np.random.randint(0, h - eh + 1), np.random.randint(0, w - ew + 1)
         t[..., i:i + eh, j:j + ew] = self.value
         return t
+
+
+# ---- functional API + remaining classes (reference: vision/transforms/functional.py, transforms.py) ---------------
+class BaseTransform:
+    def __init__(self, keys=None):
+        self.keys = keys
+
+    def _apply_image(self, img):
+        raise NotImplementedError
+
+    def __call__(self, inputs):
+        return self._apply_image(inputs)
+
+
+def to_tensor(pic, data_format="CHW"):
+    return ToTensor(data_format)(pic)
+
+
+def hflip(img):
+    return torch.flip(_chw(img), [-1])
+
+
+def vflip(img):
+    return torch.flip(_chw(img), [-2])
+
+
+def resize(img, size, interpolation="bilinear"):
+    return Resize(size, interpolation)(img)
+
+
+def pad(img, padding, fill=0, padding_mode="constant"):
+    return Pad(padding, fill, padding_mode)(img)
+
+
+def crop(img, top, left, height, width):
+    return _chw(img)[..., top:top + height, left:left + width]
+
+
+def center_crop(img, output_size):
+    return CenterCrop(output_size)(img)
+
+
+def to_grayscale(img, num_output_channels=1):
+    return Grayscale(num_output_channels)(img)
+
+
+def normalize(img, mean, std, data_format="CHW", to_rgb=False):
+    return Normalize(mean, std, data_format)(img)
+
+
+def erase(img, i, j, h, w, v, inplace=False):
+    t = _chw(img) if inplace else _chw(img).clone()
+    t[..., i:i + h, j:j + w] = v
+    return t
+
+
+def adjust_brightness(img, brightness_factor):
+    return (_chw(img) * brightness_factor).clamp(0, 1)
+
+
+def adjust_contrast(img, contrast_factor):
+    t = _chw(img)
+    m = to_grayscale(t).mean() if t.shape[0] == 3 else t.mean()
+    return ((t - m) * contrast_factor + m).clamp(0, 1)
+
+
+def _rgb_to_hsv(t):
+    r, g, b = t[0], t[1], t[2]
+    mx, mn = t.max(0).values, t.min(0).values
+    d = mx - mn
+    h = torch.zeros_like(mx)
+    nz = d > 0
+    rc, gc, bc = [(mx - c) / torch.where(nz, d, torch.ones_like(d)) for c in (r, g, b)]
+    h = torch.where((mx == r) & nz, bc - gc, h)
+    h = torch.where((mx == g) & nz, 2.0 + rc - bc, h)
+    h = torch.where((mx == b) & nz & (mx != r) & (mx != g), 4.0 + gc - rc, h)
+    h = (h / 6.0) % 1.0
+    s = torch.where(mx > 0, d / torch.where(mx > 0, mx, torch.ones_like(mx)), torch.zeros_like(mx))
+    return torch.stack([h, s, mx])
+
+
+def _hsv_to_rgb(t):
+    h, s, v = t[0], t[1], t[2]
+    i = torch.floor(h * 6.0)
+    f = h * 6.0 - i
+    p, q, u = v * (1 - s), v * (1 - f * s), v * (1 - (1 - f) * s)
+    i = i.long() % 6
+    sel = lambda a0, a1, a2, a3, a4, a5: torch.where(i == 0, a0, torch.where(i == 1, a1, torch.where(i == 2, a2, torch.where(  # noqa: E731
+        i == 3, a3, torch.where(i == 4, a4, a5)))))
+    return torch.stack([sel(v, q, p, p, u, v), sel(u, v, v, q, p, p), sel(p, p, u, v, v, q)])
+
+
+def adjust_hue(img, hue_factor):
+    hsv = _rgb_to_hsv(_chw(img))
+    hsv[0] = (hsv[0] + hue_factor) % 1.0
+    return _hsv_to_rgb(hsv)
+
+
+def adjust_saturation(img, saturation_factor):
+    t = _chw(img)
+    g = to_grayscale(t)
+    return ((t - g) * saturation_factor + g).clamp(0, 1)
+
+
+def affine(img, angle, translate, scale, shear, interpolation="nearest", fill=0, center=None):
+    import math
+    t = _chw(img)
+    h, w = t.shape[-2:]
+    a = math.radians(angle)
+    sx, sy = (math.radians(s) for s in (shear if isinstance(shear, (list, tuple)) else (shear, 0.0)))
+    # forward matrix (output = M * input), inverted for grid sampling; coordinates normalised to [-1, 1]
+    m = torch.tensor([[math.cos(a - sy) / math.cos(sy), -math.cos(a - sy) * math.tan(sx) / math.cos(sy) - math.sin(a), 0.0],
+                      [math.sin(a - sy) / math.cos(sy), -math.sin(a - sy) * math.tan(sx) / math.cos(sy) + math.cos(a), 0.0],
+                      [0.0, 0.0, 1.0]]) * scale
+    m[2, 2] = 1.0
+    m[0, 2], m[1, 2] = 2.0 * translate[0] / w, 2.0 * translate[1] / h
+    inv = torch.linalg.inv(m)[:2]
+    grid = torch.nn.functional.affine_grid(inv[None], [1, t.shape[0], h, w], align_corners=False)
+    mode = "bilinear" if interpolation == "bilinear" else "nearest"
+    return torch.nn.functional.grid_sample(t[None].float(), grid, mode=mode, padding_mode="zeros", align_corners=False)[0].to(t.dtype)
+
+
+def rotate(img, angle, interpolation="nearest", expand=False, center=None, fill=0):
+    return affine(img, -angle, (0, 0), 1.0, (0.0, 0.0), interpolation, fill, center)
+
+
+def perspective(img, startpoints, endpoints, interpolation="nearest", fill=0):
+    t = _chw(img)
+    h, w = t.shape[-2:]
+    a, bvec = [], []
+    for (sx, sy), (ex, ey) in zip(startpoints, endpoints):
+        a += [[ex, ey, 1, 0, 0, 0, -sx * ex, -sx * ey], [0, 0, 0, ex, ey, 1, -sy * ex, -sy * ey]]
+        bvec += [sx, sy]
+    coef = torch.linalg.lstsq(torch.tensor(a, dtype=torch.float64), torch.tensor(bvec, dtype=torch.float64)[:, None]).solution[:, 0].float()
+    ys, xs = torch.meshgrid(torch.arange(h, dtype=torch.float32), torch.arange(w, dtype=torch.float32), indexing="ij")
+    den = coef[6] * xs + coef[7] * ys + 1
+    gx = (coef[0] * xs + coef[1] * ys + coef[2]) / den
+    gy = (coef[3] * xs + coef[4] * ys + coef[5]) / den
+    grid = torch.stack([2 * gx / max(w - 1, 1) - 1, 2 * gy / max(h - 1, 1) - 1], -1)[None]
+    mode = "bilinear" if interpolation == "bilinear" else "nearest"
+    return torch.nn.functional.grid_sample(t[None].float(), grid, mode=mode, padding_mode="zeros", align_corners=True)[0].to(t.dtype)
+
+
+class SaturationTransform:
+    def __init__(self, value, keys=None):
+        self.value = value
+
+    def __call__(self, img):
+        return adjust_saturation(img, np.random.uniform(max(0, 1 - self.value), 1 + self.value))
+
+
+class HueTransform:
+    def __init__(self, value, keys=None):
+        self.value = value
+
+    def __call__(self, img):
+        return adjust_hue(img, np.random.uniform(-self.value, self.value))
+
+
+class RandomRotation:
+    def __init__(self, degrees, interpolation="nearest", expand=False, center=None, fill=0, keys=None):
+        self.degrees = (-degrees, degrees) if isinstance(degrees, (int, float)) else tuple(degrees)
+        self.interpolation = interpolation
+
+    def __call__(self, img):
+        return rotate(img, np.random.uniform(*self.degrees), self.interpolation)
+
+
+class RandomAffine:
+    def __init__(self, degrees, translate=None, scale=None, shear=None, interpolation="nearest", fill=0, center=None, keys=None):
+        self.degrees = (-degrees, degrees) if isinstance(degrees, (int, float)) else tuple(degrees)
+        self.translate, self.scale, self.shear, self.interpolation = translate, scale, shear, interpolation
+
+    def __call__(self, img):
+        t = _chw(img)
+        h, w = t.shape[-2:]
+        tr = (0, 0) if self.translate is None else (np.random.uniform(-self.translate[0], self.translate[0]) * w,
+                                                     np.random.uniform(-self.translate[1], self.translate[1]) * h)
+        sc = 1.0 if self.scale is None else np.random.uniform(*self.scale)
+        sh = (0.0, 0.0) if self.shear is None else (np.random.uniform(-self.shear, self.shear) if isinstance(self.shear, (int, float))
+                                                    else np.random.uniform(self.shear[0], self.shear[1]), 0.0)
+        return affine(t, np.random.uniform(*self.degrees), tr, sc, sh, self.interpolation)
+
+
+class RandomPerspective:
+    def __init__(self, prob=0.5, distortion_scale=0.5, interpolation="nearest", fill=0, keys=None):
+        self.prob, self.d, self.interpolation = prob, distortion_scale, interpolation
+
+    def __call__(self, img):
+        t = _chw(img)
+        if np.random.rand() >= self.prob:
+            return t
+        h, w = t.shape[-2:]
+        dx, dy = int(self.d * w / 2), int(self.d * h / 2)
+        r = lambda n: np.random.randint(0, n + 1)  # noqa: E731
+        start = [(0, 0), (w - 1, 0), (w - 1, h - 1), (0, h - 1)]
+        end = [(r(dx), r(dy)), (w - 1 - r(dx), r(dy)), (w - 1 - r(dx), h - 1 - r(dy)), (r(dx), h - 1 - r(dy))]
+        return perspective(t, start, end, self.interpolation)
