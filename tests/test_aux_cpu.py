@@ -262,3 +262,32 @@ def test_remaining_api_gaps_against_reference_lists():
     seq, _ = paddle.nn.dynamic_decode(dec, inits=torch.zeros(2, 8), max_step_num=5)
     assert seq.shape[0] == 2 and seq.shape[2] == 3
     assert len(list(paddle.io.SubsetRandomSampler([3, 5, 7]))) == 3
+
+
+def test_incubate_namespace():
+    import paddle
+    from paddle.incubate import nn as inn
+    lin = paddle.nn.Linear(4, 2)
+    la = paddle.incubate.LookAhead(paddle.optimizer.SGD(0.1, parameters=lin.parameters()), alpha=0.5, k=2)
+    w0 = lin.weight.detach().clone()
+    for _ in range(2):
+        lin(torch.ones(1, 4)).sum().backward()
+        la.step()
+        la.clear_grad()
+    torch.testing.assert_close(lin.weight.detach(), w0 - 0.5 * 0.2 * torch.ones_like(w0))
+    ma = paddle.incubate.ModelAverage(0.5, parameters=lin.parameters(), min_average_window=2, max_average_window=4)
+    vals = []
+    for v in (1.0, 3.0):
+        with torch.no_grad():
+            lin.bias.fill_(v)
+        ma.step()
+        vals.append(v)
+    with ma.apply():
+        torch.testing.assert_close(lin.bias.detach(), torch.full((2,), 2.0))
+    torch.testing.assert_close(lin.bias.detach(), torch.full((2,), 3.0))
+    sm = paddle.incubate.softmax_mask_fuse_upper_triangle(torch.zeros(1, 1, 3, 3))[0, 0]
+    torch.testing.assert_close(sm[1], torch.tensor([0.5, 0.5, 0.0]))
+    assert inn.FusedTransformerEncoderLayer(32, 4, 64, dropout_rate=0.0)(torch.randn(2, 6, 32)).shape == (2, 6, 32)
+    assert inn.FusedEcMoe(16, 32, 4, "gelu")(torch.randn(2, 3, 16), torch.randn(2, 3, 4)).shape == (2, 3, 16)
+    y = inn.functional.fused_bias_dropout_residual_layer_norm(torch.randn(2, 8), torch.randn(2, 8), dropout_rate=0.0)
+    torch.testing.assert_close(y.mean(-1), torch.zeros(2), atol=1e-5, rtol=0)
