@@ -116,23 +116,14 @@ def main():
     fl_up = 2.0 * tokens * H * (2 * FF // n)
     fl_down = 2.0 * tokens * (FF // n) * H
     ag_bytes = tokens * H * 2 * (n - 1) / n
-    paddle.set_flags({"FLAGS_ag_gemm_push": True})
     t_push = timeit(lambda: symm.ag_gemm(xs, w_up, g), dev)
-    paddle.set_flags({"FLAGS_ag_gemm_push": False})
-    t_inplace = timeit(lambda: symm.ag_gemm(xs, w_up, g), dev)
-    paddle.set_flags({"FLAGS_ag_gemm_push": True})
     t_n = timeit(nccl_ag_gemm, dev)
-    add("K5 all-gather->GEMM gate_up (multicast push + CTA-pair GEMM)", t_push, t_n, fl_up, ag_bytes)
-    add("K5 all-gather->GEMM gate_up (GEMM reads peer tiles in place)", t_inplace, t_n, fl_up, ag_bytes,
-        note="re-reads every A tile once per N tile over NVLink")
+    add("K5 all-gather->GEMM gate_up (NVLS multimem.st all-gather into local memory + CTA-pair GEMM)", t_push, t_n, fl_up, ag_bytes)
     t_rs_n, t_ar_n = timeit(nccl_gemm_rs, dev), timeit(nccl_gemm_ar, dev)
-    for pull, tag in ((True, "CTA-pair GEMM -> symmetric, NVLS pull-reduce"), (False, "epilogue pushes tiles to owners")):
-        paddle.set_flags({"FLAGS_gemm_rs_pull": pull})
-        add(f"K6 GEMM->reduce-scatter down_proj ({tag})", timeit(lambda: symm.gemm_rs(xf, w_down, g), dev), t_rs_n,
-            fl_down, tokens * H * 2 * (n - 1) / n)
-        add(f"K4 GEMM->all-reduce down_proj ({tag})", timeit(lambda: symm.gemm_ar(xf, w_down, g), dev), t_ar_n,
-            fl_down, 2.0 * tokens * H * 2 * (n - 1) / n)
-    paddle.set_flags({"FLAGS_gemm_rs_pull": True})
+    add("K6 GEMM->reduce-scatter down_proj (CTA-pair GEMM -> local symmetric buffer, NVLS pull-reduce)",
+        timeit(lambda: symm.gemm_rs(xf, w_down, g), dev), t_rs_n, fl_down, tokens * H * 2 * (n - 1) / n)
+    add("K4 GEMM->all-reduce down_proj (CTA-pair GEMM -> local symmetric buffer, NVLS two-shot)",
+        timeit(lambda: symm.gemm_ar(xf, w_down, g), dev), t_ar_n, fl_down, 2.0 * tokens * H * 2 * (n - 1) / n)
 
     # ---- K8 vocab-parallel CE (13B: V = 32000, N = 4096 rows)
     from paddle_b200.distributed.fleet.layers.mpu import mp_ops

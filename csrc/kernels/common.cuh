@@ -7,6 +7,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
+
 #define PDB_DTYPE_F32 0
 #define PDB_DTYPE_BF16 1
 #define PDB_DTYPE_F16 2
@@ -42,6 +44,24 @@ inline int check_launch(const char* what) {
   } while (0)
 
 int sm_count();  // cached multiProcessorCount of the current device
+
+// Local-memory guard (runtime_glue.cu): 0 when [p, p+bytes) touches no registered mapping of another GPU's memory.
+int require_local(const void* p, size_t bytes, const char* what);
+// Slow check (cudaPointerGetAttributes): p is device memory owned by the current GPU.  Run once per new tensor map.
+int require_local_device(const void* p, const char* what);
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) once per (call site, device) - the attribute is per device.
+#define PDB_ENSURE_SMEM(kern, bytes)                                                                       \
+  do {                                                                                                     \
+    static std::atomic<uint64_t> _pdb_done{0};                                                             \
+    int _dev = 0;                                                                                          \
+    PDB_CUDA_OK(cudaGetDevice(&_dev));                                                                     \
+    const uint64_t _bit = 1ull << (_dev & 63);                                                             \
+    if (!(_pdb_done.load(std::memory_order_acquire) & _bit)) {                                             \
+      PDB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes))); \
+      _pdb_done.fetch_or(_bit, std::memory_order_release);                                                 \
+    }                                                                                                      \
+  } while (0)
 
 // ---- conversion -----------------------------------------------------------------------------------------
 template <typename T> __device__ __forceinline__ float to_f32(T v);

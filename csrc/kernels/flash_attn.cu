@@ -350,15 +350,11 @@ static int launch_fwd(const void* q, const void* k, const void* v, void* o, floa
                       int hk, float scale, int causal, cudaStream_t st) {
   using S = FwdSmem<D>;
   CUtensorMap tm_q, tm_k, tm_v;
-  if (encode_tmap_2d(&tm_q, q, (uint64_t)b * sq, (uint64_t)hq * D, (uint64_t)hq * D * 2, BQ, 64, 2, true)) return -1;
-  if (encode_tmap_2d(&tm_k, k, (uint64_t)b * sk, (uint64_t)hk * D, (uint64_t)hk * D * 2, BKV, 64, 2, true)) return -1;
-  if (encode_tmap_2d(&tm_v, v, (uint64_t)b * sk, (uint64_t)hk * D, (uint64_t)hk * D * 2, BKV, 64, 2, true)) return -1;
+  if (get_tmap_2d(&tm_q, q, (uint64_t)b * sq, (uint64_t)hq * D, (uint64_t)hq * D * 2, BQ, 64, 2, true, "flash_attn q")) return -1;
+  if (get_tmap_2d(&tm_k, k, (uint64_t)b * sk, (uint64_t)hk * D, (uint64_t)hk * D * 2, BKV, 64, 2, true, "flash_attn k")) return -1;
+  if (get_tmap_2d(&tm_v, v, (uint64_t)b * sk, (uint64_t)hk * D, (uint64_t)hk * D * 2, BKV, 64, 2, true, "flash_attn v")) return -1;
   auto kern = flash_fwd_kernel<D>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    PDB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
-    attr_set = true;
-  }
+  PDB_ENSURE_SMEM(kern, S::kTotal);
   FwdParams p{sq, sk, hq, hk, scale * 1.4426950408889634f, scale, causal, (__nv_bfloat16*)o, lse};
   dim3 grid(sq / BQ, hq, b);
   kern<<<grid, kThreads, S::kTotal, st>>>(tm_q, tm_k, tm_v, p);

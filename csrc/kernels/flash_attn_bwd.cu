@@ -315,20 +315,16 @@ static int launch_bwd(const void* q, const void* k, const void* v, const void* o
   if (int e = check_launch("flash_attn_bwd delta")) return e;
   CUtensorMap tq, tdo, tk, tv;
   const uint64_t qc = (uint64_t)hq * D, kc = (uint64_t)hk * D;
-  if (encode_tmap_2d(&tq, q, (uint64_t)b * sq, qc, qc * 2, 128, 64, 2, true)) return -1;
-  if (encode_tmap_2d(&tdo, d_o, (uint64_t)b * sq, qc, qc * 2, 128, 64, 2, true)) return -1;
-  if (encode_tmap_2d(&tk, k, (uint64_t)b * sk, kc, kc * 2, 128, 64, 2, true)) return -1;
-  if (encode_tmap_2d(&tv, v, (uint64_t)b * sk, kc, kc * 2, 128, 64, 2, true)) return -1;
+  if (get_tmap_2d(&tq, q, (uint64_t)b * sq, qc, qc * 2, 128, 64, 2, true, "flash_attn q")) return -1;
+  if (get_tmap_2d(&tdo, d_o, (uint64_t)b * sq, qc, qc * 2, 128, 64, 2, true, "flash_attn d_o")) return -1;
+  if (get_tmap_2d(&tk, k, (uint64_t)b * sk, kc, kc * 2, 128, 64, 2, true, "flash_attn k")) return -1;
+  if (get_tmap_2d(&tv, v, (uint64_t)b * sk, kc, kc * 2, 128, 64, 2, true, "flash_attn v")) return -1;
   BwdParams p{sq, sk, hq, hk, scale * kLog2e, scale, causal, lse, delta, (__nv_bfloat16*)dq, (__nv_bfloat16*)dk,
               (__nv_bfloat16*)dv};
   auto kq = flash_bwd_dq_kernel<D>;
   auto kkv = flash_bwd_dkv_kernel<D>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    PDB_CUDA_OK(cudaFuncSetAttribute(kq, cudaFuncAttributeMaxDynamicSharedMemorySize, DqSmem<D>::kTotal));
-    PDB_CUDA_OK(cudaFuncSetAttribute(kkv, cudaFuncAttributeMaxDynamicSharedMemorySize, DkvSmem<D>::kTotal));
-    attr_set = true;
-  }
+  PDB_ENSURE_SMEM(kq, DqSmem<D>::kTotal);
+  PDB_ENSURE_SMEM(kkv, DkvSmem<D>::kTotal);
   kkv<<<dim3(sk / 128, hk, b), kThreads, DkvSmem<D>::kTotal, st>>>(tq, tdo, tk, tv, p);
   if (int e = check_launch("flash_attn_bwd dkv")) return e;
   kq<<<dim3(sq / 128, hq, b), kThreads, DqSmem<D>::kTotal, st>>>(tq, tdo, tk, tv, p);

@@ -17,6 +17,9 @@
 // dgrad (dY W^T) and wgrad (X^T dY) all run without a transpose copy:
 //   A: [M,K] row-major (K-major)  or  [K,M] row-major (M-major, trans_a)
 //   B: [K,N] row-major (N-major)  or  [N,K] row-major (K-major, trans_b)
+#include <mutex>
+#include <unordered_map>
+
 #include "common.cuh"
 #include "tc.cuh"
 
@@ -69,6 +72,54 @@ int encode_tmap_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t c
   return 0;
 }
 
+// Encoded tensor maps are pure functions of (address, shape, box): cache them, a training step re-issues the same
+// ~800 GEMM shapes on recurring allocator addresses.  A miss also runs the slow ownership check; every call runs the
+// cheap foreign-range check, so a map is only ever built over, or used on, this GPU's own memory.
+namespace {
+struct TmapKey {
+  const void* base;
+  uint64_t rows, cols, stride;
+  uint32_t box_rows, box_cols;
+  int esz, swz, dev;
+  bool operator==(const TmapKey& o) const {
+    return base == o.base && rows == o.rows && cols == o.cols && stride == o.stride && box_rows == o.box_rows &&
+           box_cols == o.box_cols && esz == o.esz && swz == o.swz && dev == o.dev;
+  }
+};
+struct TmapKeyHash {
+  size_t operator()(const TmapKey& k) const {
+    uint64_t h = (uint64_t)(uintptr_t)k.base * 0x9E3779B97F4A7C15ull;
+    h ^= (k.rows * 0xC2B2AE3D27D4EB4Full) ^ (k.cols << 17) ^ (k.stride << 3) ^ ((uint64_t)k.box_rows << 40) ^
+         ((uint64_t)k.box_cols << 50) ^ ((uint64_t)k.esz << 60) ^ ((uint64_t)k.swz << 59) ^ ((uint64_t)k.dev << 54);
+    return (size_t)(h ^ (h >> 29));
+  }
+};
+std::mutex g_tmap_mu;
+std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> g_tmap_cache;
+}  // namespace
+
+int get_tmap_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t row_stride_bytes,
+                uint32_t box_rows, uint32_t box_cols, int elem_bytes, bool swizzle128, const char* what) {
+  if (require_local(base, (size_t)(rows * row_stride_bytes), what)) return -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const TmapKey key{base, rows, cols, row_stride_bytes, box_rows, box_cols, elem_bytes, swizzle128 ? 1 : 0, dev};
+  {
+    std::lock_guard<std::mutex> g(g_tmap_mu);
+    auto it = g_tmap_cache.find(key);
+    if (it != g_tmap_cache.end()) {
+      *out = it->second;
+      return 0;
+    }
+  }
+  if (require_local_device(base, what)) return -1;
+  if (encode_tmap_2d(out, base, rows, cols, row_stride_bytes, box_rows, box_cols, elem_bytes, swizzle128)) return -1;
+  std::lock_guard<std::mutex> g(g_tmap_mu);
+  if (g_tmap_cache.size() > 8192) g_tmap_cache.clear();
+  g_tmap_cache.emplace(key, *out);
+  return 0;
+}
+
 constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int kThreads = 256;
@@ -93,21 +144,6 @@ __device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int&
   n_blk = in_group / gsz;
 }
 
-// Communication fused into the GEMM (K5 / K6).  mode 1 = all-gather -> GEMM: the M dimension is the concatenation of
-// every rank's [rows_per_rank, K] activation shard living in symmetric memory; the TMA producer reads each A tile
-// straight from the owning peer through that peer's tensor map (no gathered copy, local tiles first).  mode 2 = GEMM
-// -> reduce-scatter: the epilogue stores each partial tile into the OWNER rank's staging slab [src rank][rows][N]
-// over NVLink as soon as it leaves TMEM; a small follow-up kernel on the owner sums the slabs.
-struct CommArgs {
-  int mode;
-  int nranks;
-  int rank;
-  int rows_per_rank;
-  int m_rot;                    // tile-row rotation so every rank starts on a different chunk
-  uint64_t out_ptr[8];          // mode 2: staging base address on each owner (as mapped in this process)
-  CUtensorMap tm_a_peer[8];     // mode 1: A shard of each peer
-};
-
 __device__ __forceinline__ float apply_act(float v, int act) {
   if (act == 1) return 0.5f * v * (1.f + erff(v * 0.70710678118654752f));
   if (act == 2) return fmaxf(v, 0.f);
@@ -117,8 +153,7 @@ __device__ __forceinline__ float apply_act(float v, int act) {
 template <bool A_MN, bool B_MN, int BN, bool OUT_F32>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b, void* __restrict__ Cptr,
-               const __nv_bfloat16* __restrict__ bias, int M, int N, int K, int64_t ldc, float beta, int act,
-               const __grid_constant__ CommArgs comm) {
+               const __nv_bfloat16* __restrict__ bias, int M, int N, int K, int64_t ldc, float beta, int act) {
   using C = Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -164,11 +199,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         int m_blk, n_blk;
         tile_coords(tile, num_m, num_n, m_blk, n_blk);
-        if (comm.m_rot) m_blk = (m_blk + comm.m_rot) % num_m;
         const int m0 = m_blk * BM, n0 = n_blk * BN;
-        const int a_owner = comm.mode == 1 ? m0 / comm.rows_per_rank : 0;
-        const int a_row = comm.mode == 1 ? m0 - a_owner * comm.rows_per_rank : m0;
-        const CUtensorMap* tma_a = comm.mode == 1 ? &comm.tm_a_peer[a_owner] : &tm_a;
         for (int kb = 0; kb < num_k; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * C::kStageBytes;
@@ -179,7 +210,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
 #pragma unroll
             for (int j = 0; j < BM / 64; ++j) tma_load_2d(sa + j * (BK * 128), &tm_a, &full_bar[stage], m0 + j * 64, k0);
           } else {
-            tma_load_2d(sa, tma_a, &full_bar[stage], k0, a_row);
+            tma_load_2d(sa, &tm_a, &full_bar[stage], k0, m0);
           }
           if (B_MN) {
 #pragma unroll
@@ -238,17 +269,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       int m_blk, n_blk;
       tile_coords(tile, num_m, num_n, m_blk, n_blk);
-      if (comm.m_rot) m_blk = (m_blk + comm.m_rot) % num_m;
       const int row = m_blk * BM + q * 32 + lane;
       const int n0 = n_blk * BN;
-      // mode 2: this row lands in the owner's staging slab, slot = my rank
       void* c_base = Cptr;
-      int64_t c_row = row;
-      if (comm.mode == 2) {
-        const int owner = (m_blk * BM) / comm.rows_per_rank;
-        c_base = reinterpret_cast<void*>(comm.out_ptr[owner]);
-        c_row = (int64_t)comm.rank * comm.rows_per_rank + (row - owner * comm.rows_per_rank);
-      }
+      const int64_t c_row = row;
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
@@ -325,33 +349,26 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
 
 template <bool A_MN, bool B_MN, int BN, bool OUT_F32>
 static int launch(const void* a, const void* b, void* c, const void* bias, int M, int N, int K, float beta, int act,
-                  cudaStream_t st, const CommArgs* comm_in = nullptr) {
+                  cudaStream_t st) {
   using C = Cfg<BN>;
   CUtensorMap tm_a, tm_b;
-  static const CommArgs kNoComm{};
-  const CommArgs& comm = comm_in ? *comm_in : kNoComm;
   // A: K-major [M][K] -> box 128 rows x 64 k ; M-major stored [K][M] -> box 64 k-rows x 64 m
-  if (comm.mode == 1) {
-    tm_a = comm.tm_a_peer[comm.rank];
-  } else if (A_MN) {
-    if (encode_tmap_2d(&tm_a, a, K, M, (uint64_t)M * 2, BK, 64, 2, true)) return -1;
+  if (A_MN) {
+    if (get_tmap_2d(&tm_a, a, K, M, (uint64_t)M * 2, BK, 64, 2, true, "gemm A")) return -1;
   } else {
-    if (encode_tmap_2d(&tm_a, a, M, K, (uint64_t)K * 2, BM, BK, 2, true)) return -1;
+    if (get_tmap_2d(&tm_a, a, M, K, (uint64_t)K * 2, BM, BK, 2, true, "gemm A")) return -1;
   }
   if (B_MN) {
-    if (encode_tmap_2d(&tm_b, b, K, N, (uint64_t)N * 2, BK, 64, 2, true)) return -1;
+    if (get_tmap_2d(&tm_b, b, K, N, (uint64_t)N * 2, BK, 64, 2, true, "gemm B")) return -1;
   } else {
-    if (encode_tmap_2d(&tm_b, b, N, K, (uint64_t)K * 2, BN, BK, 2, true)) return -1;
+    if (get_tmap_2d(&tm_b, b, N, K, (uint64_t)K * 2, BN, BK, 2, true, "gemm B")) return -1;
   }
+  if (require_local(c, (size_t)M * N * (OUT_F32 ? 4 : 2), "gemm C")) return -1;
   auto kern = gemm_tc_kernel<A_MN, B_MN, BN, OUT_F32>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    PDB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    attr_set = true;
-  }
+  PDB_ENSURE_SMEM(kern, C::kSmemBytes);
   const int num_tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
   const int grid = num_tiles < sm_count() ? num_tiles : sm_count();
-  kern<<<grid, kThreads, C::kSmemBytes, st>>>(tm_a, tm_b, c, (const __nv_bfloat16*)bias, M, N, K, (int64_t)N, beta, act, comm);
+  kern<<<grid, kThreads, C::kSmemBytes, st>>>(tm_a, tm_b, c, (const __nv_bfloat16*)bias, M, N, K, (int64_t)N, beta, act);
   return check_launch("gemm_tc");
 }
 
@@ -388,190 +405,4 @@ PDB_EXPORT int pdb200_gemm_bf16(const void* a, const void* b, void* c, const voi
   if (a_mn && !b_mn) return tc::dispatch_bn<true, false>(a, b, c, bias, (int)M, (int)N, (int)K, of, beta, act, st);
   if (!a_mn && b_mn) return tc::dispatch_bn<false, true>(a, b, c, bias, (int)M, (int)N, (int)K, of, beta, act, st);
   return tc::dispatch_bn<false, false>(a, b, c, bias, (int)M, (int)N, (int)K, of, beta, act, st);
-}
-
-
-// ------------------------------------------------------------------------------------------------ K5 / K6 entry points
-#include "nvl.cuh"
-namespace pdb {
-namespace nvl {
-// same body as nvl_collectives.cu's barrier (kernels cannot be shared across translation units without -rdc)
-static __global__ void gemm_barrier_kernel(Peers P, uint64_t pad_off, uint32_t epoch, unsigned long long spin_limit) {
-  barrier_all(P, pad_off, epoch, spin_limit);
-}
-}
-namespace tc {
-// out[rows, N] = sum over src of staging[src][rows][N]   (bf16 in, fp32 sum, bf16 out)
-__global__ void __launch_bounds__(256) rs_fold_kernel(const __nv_bfloat16* __restrict__ staging, __nv_bfloat16* __restrict__ out,
-                                                     int64_t per_rank_elems, int nranks) {
-  const int64_t nvec = per_rank_elems / 8;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
-    float acc[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
-    for (int r = 0; r < nranks; ++r) {
-      Vec<__nv_bfloat16> x;
-      x.load_nc(staging + r * per_rank_elems + i * 8);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) acc[j] += x.f(j);
-    }
-    Vec<__nv_bfloat16> o;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) o.set(j, acc[j]);
-    o.store(out + i * 8);
-  }
-}
-// K4 tail: same fold, but the summed rows are stored into every rank's full output (all-gather half of the all-reduce).
-struct OutPtrs { uint64_t p[8]; };
-__global__ void __launch_bounds__(256) ar_fold_kernel(const __nv_bfloat16* __restrict__ staging, OutPtrs outs,
-                                                     int64_t per_rank_elems, int nranks, int rank) {
-  const int64_t nvec = per_rank_elems / 8;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
-    float acc[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
-    for (int r = 0; r < nranks; ++r) {
-      Vec<__nv_bfloat16> x;
-      x.load_nc(staging + r * per_rank_elems + i * 8);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) acc[j] += x.f(j);
-    }
-    Vec<__nv_bfloat16> o;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) o.set(j, acc[j]);
-    for (int r = 0; r < nranks; ++r) {
-      const int dst = (rank + r) % nranks;   // start with the local copy, then walk the peers
-      o.store((__nv_bfloat16*)outs.p[dst] + (int64_t)rank * per_rank_elems + i * 8);
-    }
-  }
-}
-}  // namespace tc
-}  // namespace pdb
-
-static pdb::nvl::Peers make_peers_(const uint64_t* ptrs, int nranks, int rank) {
-  pdb::nvl::Peers P{};
-  for (int i = 0; i < nranks && i < pdb::nvl::kMaxRanks; ++i) P.ptr[i] = ptrs[i];
-  P.nranks = nranks;
-  P.rank = rank;
-  return P;
-}
-static const unsigned long long kGemmSpinLimit = 20000000ull;
-
-// K5 all-gather -> GEMM.  Every rank's activation shard [rows_per_rank, K] (bf16, row-major) lives at byte offset a_off
-// of its symmetric segment; C[nranks * rows_per_rank, N] = gather(A) @ B is written locally.  B: [K,N] or [N,K] (trans_b).
-PDB_EXPORT int pdb200_gemm_bf16_ag(const uint64_t* peer_ptrs, int nranks, int rank, int64_t a_off, int64_t rows_per_rank,
-                                   const void* b, void* c, const void* bias, int64_t N, int64_t K, int trans_b, int act,
-                                   int64_t pad_off, int64_t epoch, void* stream) {
-  using namespace pdb::tc;
-  PDB_REQUIRE(nranks >= 1 && nranks <= 8, "gemm_ag: nranks %d out of range", nranks);
-  PDB_REQUIRE(rows_per_rank % BM == 0, "gemm_ag: rows per rank (%lld) must be a multiple of %d", (long long)rows_per_rank, BM);
-  PDB_REQUIRE(K % 8 == 0 && N % 8 == 0 && a_off % 16 == 0, "gemm_ag: K, N multiples of 8 and 16-byte aligned shard required");
-  cudaStream_t st = (cudaStream_t)stream;
-  CommArgs comm{};
-  comm.mode = 1;
-  comm.nranks = nranks;
-  comm.rank = rank;
-  comm.rows_per_rank = (int)rows_per_rank;
-  comm.m_rot = (int)(rank * (rows_per_rank / BM));          // start on the local shard: remote latency hides behind it
-  for (int p = 0; p < nranks; ++p)
-    if (encode_tmap_2d(&comm.tm_a_peer[p], (const void*)(peer_ptrs[p] + a_off), rows_per_rank, K, (uint64_t)K * 2, BM, BK, 2, true)) return -1;
-  const int M = (int)(rows_per_rank * nranks);
-  pdb::nvl::Peers P = make_peers_(peer_ptrs, nranks, rank);
-  pdb::nvl::gemm_barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)epoch, kGemmSpinLimit);   // shards are written
-  int rc;
-  const bool big = (N % 256 == 0) || N >= 1024;
-  if (trans_b)
-    rc = big ? launch<false, false, 256, false>(nullptr, b, c, bias, M, (int)N, (int)K, 0.f, act, st, &comm)
-             : launch<false, false, 128, false>(nullptr, b, c, bias, M, (int)N, (int)K, 0.f, act, st, &comm);
-  else
-    rc = big ? launch<false, true, 256, false>(nullptr, b, c, bias, M, (int)N, (int)K, 0.f, act, st, &comm)
-             : launch<false, true, 128, false>(nullptr, b, c, bias, M, (int)N, (int)K, 0.f, act, st, &comm);
-  if (rc) return rc;
-  pdb::nvl::gemm_barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kGemmSpinLimit);  // shards reusable
-  return check_launch("gemm_ag");
-}
-
-// K6 GEMM -> reduce-scatter.  A: local [M, K] (M = nranks * rows_per_rank), B as above.  Partial tiles are pushed into
-// the owner's staging slab at stage_off ([nranks][rows_per_rank][N] bf16 in every segment); out[rows_per_rank, N] (local,
-// bf16) receives the sum.
-PDB_EXPORT int pdb200_gemm_bf16_rs(const uint64_t* peer_ptrs, int nranks, int rank, const void* a, const void* b,
-                                   int64_t stage_off, void* out, int64_t rows_per_rank, int64_t N, int64_t K, int trans_b,
-                                   int64_t pad_off, int64_t epoch, void* stream) {
-  using namespace pdb::tc;
-  PDB_REQUIRE(nranks >= 1 && nranks <= 8, "gemm_rs: nranks %d out of range", nranks);
-  PDB_REQUIRE(rows_per_rank % BM == 0, "gemm_rs: rows per rank (%lld) must be a multiple of %d", (long long)rows_per_rank, BM);
-  PDB_REQUIRE(K % 8 == 0 && N % 8 == 0 && stage_off % 16 == 0 && ((uintptr_t)a & 15) == 0, "gemm_rs: alignment");
-  cudaStream_t st = (cudaStream_t)stream;
-  CommArgs comm{};
-  comm.mode = 2;
-  comm.nranks = nranks;
-  comm.rank = rank;
-  comm.rows_per_rank = (int)rows_per_rank;
-  comm.m_rot = (int)(((rank + 1) % nranks) * (rows_per_rank / BM));   // spread the owners: each rank starts one chunk ahead
-  for (int p = 0; p < nranks; ++p) comm.out_ptr[p] = peer_ptrs[p] + (uint64_t)stage_off;
-  const int M = (int)(rows_per_rank * nranks);
-  pdb::nvl::Peers P = make_peers_(peer_ptrs, nranks, rank);
-  pdb::nvl::gemm_barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)epoch, kGemmSpinLimit);   // slabs free again
-  int rc;
-  const bool big = (N % 256 == 0) || N >= 1024;
-  if (trans_b)
-    rc = big ? launch<false, false, 256, false>(a, b, nullptr, nullptr, M, (int)N, (int)K, 0.f, 0, st, &comm)
-             : launch<false, false, 128, false>(a, b, nullptr, nullptr, M, (int)N, (int)K, 0.f, 0, st, &comm);
-  else
-    rc = big ? launch<false, true, 256, false>(a, b, nullptr, nullptr, M, (int)N, (int)K, 0.f, 0, st, &comm)
-             : launch<false, true, 128, false>(a, b, nullptr, nullptr, M, (int)N, (int)K, 0.f, 0, st, &comm);
-  if (rc) return rc;
-  pdb::nvl::gemm_barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kGemmSpinLimit);  // all partials landed
-  const int64_t per = rows_per_rank * N;
-  int64_t blocks = (per / 8 + 255) / 256;
-  const int64_t cap = (int64_t)sm_count() * 8;
-  if (blocks > cap) blocks = cap;
-  rs_fold_kernel<<<(int)(blocks < 1 ? 1 : blocks), 256, 0, st>>>((const __nv_bfloat16*)(peer_ptrs[rank] + stage_off),
-                                                             (__nv_bfloat16*)out, per, nranks);
-  return check_launch("gemm_rs");
-}
-
-// K4 GEMM -> all-reduce (RowParallelLinear forward, ColumnParallelLinear dX).  Same tile-by-tile push of partial tiles to
-// the owning rank as K6; the owner then folds its rows and stores the sum into EVERY rank's output, which lives at byte
-// offset out_off ([M, N] bf16) of each symmetric segment.  Uses epochs epoch, epoch+1, epoch+2.
-PDB_EXPORT int pdb200_gemm_bf16_ar(const uint64_t* peer_ptrs, int nranks, int rank, const void* a, const void* b,
-                                   int64_t stage_off, int64_t out_off, int64_t rows_per_rank, int64_t N, int64_t K,
-                                   int trans_b, int64_t pad_off, int64_t epoch, void* stream) {
-  using namespace pdb::tc;
-  PDB_REQUIRE(nranks >= 1 && nranks <= 8, "gemm_ar: nranks %d out of range", nranks);
-  PDB_REQUIRE(rows_per_rank % BM == 0, "gemm_ar: rows per rank (%lld) must be a multiple of %d", (long long)rows_per_rank, BM);
-  PDB_REQUIRE(K % 8 == 0 && N % 8 == 0 && stage_off % 16 == 0 && out_off % 16 == 0 && ((uintptr_t)a & 15) == 0,
-              "gemm_ar: alignment");
-  cudaStream_t st = (cudaStream_t)stream;
-  CommArgs comm{};
-  comm.mode = 2;
-  comm.nranks = nranks;
-  comm.rank = rank;
-  comm.rows_per_rank = (int)rows_per_rank;
-  comm.m_rot = (int)(((rank + 1) % nranks) * (rows_per_rank / BM));
-  for (int p = 0; p < nranks; ++p) comm.out_ptr[p] = peer_ptrs[p] + (uint64_t)stage_off;
-  const int M = (int)(rows_per_rank * nranks);
-  pdb::nvl::Peers P = make_peers_(peer_ptrs, nranks, rank);
-  pdb::nvl::gemm_barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)epoch, kGemmSpinLimit);   // slabs + outputs free
-  int rc;
-  const bool big = (N % 256 == 0) || N >= 1024;
-  if (trans_b)
-    rc = big ? launch<false, false, 256, false>(a, b, nullptr, nullptr, M, (int)N, (int)K, 0.f, 0, st, &comm)
-             : launch<false, false, 128, false>(a, b, nullptr, nullptr, M, (int)N, (int)K, 0.f, 0, st, &comm);
-  else
-    rc = big ? launch<false, true, 256, false>(a, b, nullptr, nullptr, M, (int)N, (int)K, 0.f, 0, st, &comm)
-             : launch<false, true, 128, false>(a, b, nullptr, nullptr, M, (int)N, (int)K, 0.f, 0, st, &comm);
-  if (rc) return rc;
-  pdb::nvl::gemm_barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kGemmSpinLimit);  // partials landed
-  const int64_t per = rows_per_rank * N;
-  int64_t blocks = (per / 8 + 255) / 256;
-  const int64_t cap = (int64_t)sm_count() * 8;
-  if (blocks > cap) blocks = cap;
-  OutPtrs outs{};
-  for (int p = 0; p < nranks; ++p) outs.p[p] = peer_ptrs[p] + (uint64_t)out_off;
-  ar_fold_kernel<<<(int)(blocks < 1 ? 1 : blocks), 256, 0, st>>>((const __nv_bfloat16*)(peer_ptrs[rank] + stage_off), outs, per,
-                                                             nranks, rank);
-  if (int e = check_launch("gemm_ar fold")) return e;
-  pdb::nvl::gemm_barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 2), kGemmSpinLimit);  // every row landed
-  return check_launch("gemm_ar");
 }

@@ -8,7 +8,7 @@
 // memory instead of 48 KB (6 stages deep instead of 4).
 //
 // Cluster = (2,1,1).  Roles per CTA (256 threads): warp 0 TMA producer (own A rows, own half of B; both CTAs' loads
-// complete on the LEADER's "full" mbarrier), warp 1 MMA issuer (leader CTA only; the commit is multicast so both
+// complete on the LEADER's "full" mbarrier), warp 1 MMA issuer (leader CTA only; tcgen05.commit arrives on both CTAs' barriers, so both
 // CTAs see "slab free" / "accumulator ready"), warp 2 TMEM allocator (cta_group::2), warps 4-7 epilogue of the CTA's
 // own 128 rows (accumulator double-buffered in TMEM: 2 x 256 columns; the partner's epilogue warps arrive remotely on
 // the leader's "accumulator free" barrier).  Operand majors as in gemm_tc.cu (both, via descriptor bits).
@@ -97,8 +97,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant_
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);
   uint64_t* full_bar = bars;                       // used on the leader: both CTAs' TMA bytes land here
-  uint64_t* empty_bar = bars + kStages;            // each CTA has its own, fed by the multicast commit
-  uint64_t* tmem_full = bars + 2 * kStages;        // [2] each CTA its own (multicast commit)
+  uint64_t* empty_bar = bars + kStages;            // each CTA has its own, fed by the two-CTA tcgen05.commit
+  uint64_t* tmem_full = bars + 2 * kStages;        // [2] each CTA its own (two-CTA tcgen05.commit)
   uint64_t* tmem_empty = tmem_full + 2;            // [2] used on the leader: 8 epilogue warps of the pair arrive
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
@@ -295,22 +295,20 @@ template <bool A_MN, bool B_MN, bool OUT_F32>
 static int launch(const void* a, const void* b, void* c, const void* bias, int M, int N, int K, float beta, int act,
                   cudaStream_t st) {
   CUtensorMap tm_a, tm_b;
+  // Both operands and the output must be this GPU's own memory (get_tmap_2d / require_local refuse anything else).
   if (A_MN) {
-    if (encode_tmap_2d(&tm_a, a, K, M, (uint64_t)M * 2, BK, 64, 2, true)) return -1;
+    if (get_tmap_2d(&tm_a, a, K, M, (uint64_t)M * 2, BK, 64, 2, true, "gemm_pair A")) return -1;
   } else {
-    if (encode_tmap_2d(&tm_a, a, M, K, (uint64_t)K * 2, BM, BK, 2, true)) return -1;
+    if (get_tmap_2d(&tm_a, a, M, K, (uint64_t)K * 2, BM, BK, 2, true, "gemm_pair A")) return -1;
   }
   if (B_MN) {
-    if (encode_tmap_2d(&tm_b, b, K, N, (uint64_t)N * 2, BK, 64, 2, true)) return -1;
+    if (get_tmap_2d(&tm_b, b, K, N, (uint64_t)N * 2, BK, 64, 2, true, "gemm_pair B")) return -1;
   } else {
-    if (encode_tmap_2d(&tm_b, b, N, K, (uint64_t)K * 2, BNH, BK, 2, true)) return -1;
+    if (get_tmap_2d(&tm_b, b, N, K, (uint64_t)K * 2, BNH, BK, 2, true, "gemm_pair B")) return -1;
   }
+  if (require_local(c, (size_t)M * N * (OUT_F32 ? 4 : 2), "gemm_pair C")) return -1;
   auto kern = gemm_tc2_kernel<A_MN, B_MN, OUT_F32>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    PDB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    attr_set = true;
-  }
+  PDB_ENSURE_SMEM(kern, kSmemBytes);
   const int num_tiles = ((M + 2 * BM - 1) / (2 * BM)) * ((N + BN - 1) / BN);
   const int pairs = sm_count() / 2;
   const int grid = 2 * (num_tiles < pairs ? num_tiles : pairs);

@@ -52,6 +52,67 @@ __device__ __forceinline__ void barrier_all(const Peers& P, uint64_t pad_off, ui
   __syncthreads();
 }
 
+// ---- barriers embedded in multi-CTA data kernels ---------------------------------------------------------------
+// Same pad protocol as barrier_all, callable from EVERY CTA of a grid so that a collective needs one launch instead
+// of barrier + data + barrier.  pad layout: [0, 32) the kMaxRanks epoch flags, [64, 68) a CTA-arrival counter that
+// is zero between launches.  All launches that share a pad must be ordered on one stream.
+//
+// grid_barrier_begin: CTA 0 announces "this rank reached epoch" to every peer; every CTA then waits until all peers
+// have announced it (each CTA polls its own GPU's pad, which is local memory).
+__device__ __forceinline__ void grid_barrier_begin(const Peers& P, uint64_t pad_off, uint32_t epoch, unsigned long long spin_limit) {
+  const int t = threadIdx.x;
+  if (t < P.nranks) {
+    if (blockIdx.x == 0) {
+      fence_sys();
+      st_release_sys(reinterpret_cast<uint32_t*>(P.ptr[t] + pad_off) + P.rank, epoch);
+    }
+    const uint32_t* mine = reinterpret_cast<const uint32_t*>(P.ptr[P.rank] + pad_off) + t;
+    unsigned long long spins = 0;
+    while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
+      if (spin_limit && ++spins > spin_limit) {
+        printf("[pdb200 nvl] rank %d cta %d: begin-barrier epoch %u timed out waiting for rank %d (saw %u)\n", P.rank,
+               (int)blockIdx.x, epoch, t, ld_acquire_sys(mine));
+        __trap();
+      }
+    }
+    fence_sys();
+  }
+  __syncthreads();
+}
+// grid_barrier_end: every CTA calls it after its last store.  The last CTA of this rank to arrive announces "all my
+// stores are issued and fenced" (epoch) to every peer and waits for the same announcement from all of them, so when
+// the kernel completes, every peer's stores into this GPU have landed and every peer has finished reading from it.
+__device__ __forceinline__ void grid_barrier_end(const Peers& P, uint64_t pad_off, uint32_t epoch, unsigned long long spin_limit) {
+  __shared__ int s_last;
+  __threadfence_system();                       // this thread's stores (peer / multimem) before the arrival below
+  __syncthreads();
+  unsigned int* counter = reinterpret_cast<unsigned int*>(P.ptr[P.rank] + pad_off + 64);
+  if (threadIdx.x == 0) {
+    __threadfence_system();                     // cumulative: covers the whole CTA's stores (ordered by the barrier)
+    const unsigned int prev = atomicAdd(counter, 1u);
+    s_last = (prev == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!s_last) return;
+  const int t = threadIdx.x;
+  if (t == 0) *counter = 0;                     // ready for the next launch on this pad (stream-ordered)
+  if (t < P.nranks) {
+    fence_sys();                                // acquire the other CTAs' arrivals, then release to the peers
+    st_release_sys(reinterpret_cast<uint32_t*>(P.ptr[t] + pad_off) + P.rank, epoch);
+    const uint32_t* mine = reinterpret_cast<const uint32_t*>(P.ptr[P.rank] + pad_off) + t;
+    unsigned long long spins = 0;
+    while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
+      if (spin_limit && ++spins > spin_limit) {
+        printf("[pdb200 nvl] rank %d: end-barrier epoch %u timed out waiting for rank %d (saw %u)\n", P.rank, epoch, t,
+               ld_acquire_sys(mine));
+        __trap();
+      }
+    }
+    fence_sys();
+  }
+  __syncthreads();
+}
+
 // ---- NVLS multimem ------------------------------------------------------------------------------------------
 // 16-byte in-switch reductions over all ranks bound to the multicast object.
 __device__ __forceinline__ void mm_ld_reduce_f32x4(const void* mc_addr, float (&v)[4]) {

@@ -352,6 +352,118 @@ __global__ void __launch_bounds__(256) vocab_embed_gather_kernel(Peers P, uint64
   }
 }
 
+// ---------------------------------------------------------------------------------------------- stage-3 unit transport
+// One launch moves every parameter (all-gather) or every gradient (reduce-scatter) of a ZeRO-3 unit: a table of up to
+// kMaxSegs segments is passed by value, and the cross-GPU barriers run inside the kernel (grid_barrier_begin / _end),
+// so a unit costs one launch instead of 3 per parameter.  Replaces the per-parameter all_gather / all_reduce + slice
+// of the reference (group_sharded_stage3.py:741-803, 849-1118).
+constexpr int kMaxSegs = 16;
+struct AgSeg { uint64_t src_off, dst_off; int64_t nvec; };      // nvec 16-byte vectors per rank shard
+struct AgSegs { AgSeg s[kMaxSegs]; int n; };
+__global__ void __launch_bounds__(512) allgather_multi_kernel(Peers P, AgSegs S, uint64_t pad_off, uint32_t epoch,
+                                                             unsigned long long spin_limit) {
+  grid_barrier_begin(P, pad_off, epoch, spin_limit);         // every rank may have its gathered buffer overwritten
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int k = 0; k < S.n; ++k) {
+    const uint4* src = reinterpret_cast<const uint4*>(P.ptr[P.rank] + S.s[k].src_off);
+    const int64_t nvec = S.s[k].nvec;
+    const uint64_t dst0 = S.s[k].dst_off + (uint64_t)P.rank * (uint64_t)nvec * 16;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += 4 * stride) {
+      uint4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (i + u * stride < nvec) v[u] = src[i + u * stride];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int64_t j = i + u * stride;
+        if (j >= nvec) break;
+        const uint64_t off = dst0 + (uint64_t)j * 16;
+        if (P.mc) {
+          uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+          mm_st_b32x4(reinterpret_cast<void*>(P.mc + off), w);
+        } else {
+          for (int p = 0; p < P.nranks; ++p) *reinterpret_cast<uint4*>(P.ptr[(P.rank + p) % P.nranks] + off) = v[u];
+        }
+      }
+    }
+  }
+  grid_barrier_end(P, pad_off, epoch + 1, spin_limit);       // all shards have landed everywhere
+}
+
+// Reduce-scatter of a unit: segment k is a padded gradient [nranks * shard_numel] (G = bf16 or fp32) staged at stage_off
+// of every rank's segment; this rank's shard is summed over the ranks (in the switch with NVLS), scaled and written -
+// or, with accumulate, added - to its local fp32 accumulator `out` (the optimizer's main_grad slice).
+struct RsSeg { uint64_t stage_off; int64_t shard_numel; float* out; };
+struct RsSegs { RsSeg s[kMaxSegs]; int n; };
+template <typename G>
+__global__ void __launch_bounds__(512) reduce_scatter_multi_kernel(Peers P, RsSegs S, float scale, int accumulate,
+                                                                  uint64_t pad_off, uint32_t epoch,
+                                                                  unsigned long long spin_limit) {
+  grid_barrier_begin(P, pad_off, epoch, spin_limit);         // every rank's staged gradients are complete
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int k = 0; k < S.n; ++k) {
+    const int64_t n8 = S.s[k].shard_numel / 8;
+    float* __restrict__ out = S.s[k].out;
+    const uint64_t base = S.s[k].stage_off + (uint64_t)P.rank * (uint64_t)S.s[k].shard_numel * sizeof(G);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
+      float g[8];
+      if (sizeof(G) == 4) {
+        const uint64_t off = base + (uint64_t)i * 32;
+        if (P.mc) {
+          float t0[4], t1[4];
+          mm_ld_reduce_f32x4(reinterpret_cast<const void*>(P.mc + off), t0);
+          mm_ld_reduce_f32x4(reinterpret_cast<const void*>(P.mc + off + 16), t1);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            g[j] = t0[j];
+            g[4 + j] = t1[j];
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] = 0.f;
+          for (int p = 0; p < P.nranks; ++p) {
+            const float4 x0 = *reinterpret_cast<const float4*>(P.ptr[p] + off);
+            const float4 x1 = *reinterpret_cast<const float4*>(P.ptr[p] + off + 16);
+            g[0] += x0.x; g[1] += x0.y; g[2] += x0.z; g[3] += x0.w;
+            g[4] += x1.x; g[5] += x1.y; g[6] += x1.z; g[7] += x1.w;
+          }
+        }
+      } else {
+        const uint64_t off = base + (uint64_t)i * 16;
+        if (P.mc) {
+          uint32_t r[4];
+          mm_ld_reduce_bf16x8(reinterpret_cast<const void*>(P.mc + off), r);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&r[j]);
+            g[2 * j] = __low2float(h);
+            g[2 * j + 1] = __high2float(h);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] = 0.f;
+          for (int p = 0; p < P.nranks; ++p) {
+            Vec<__nv_bfloat16> x;
+            x.load(reinterpret_cast<const __nv_bfloat16*>(P.ptr[p] + off));
+#pragma unroll
+            for (int j = 0; j < 8; ++j) g[j] += x.f(j);
+          }
+        }
+      }
+      float4 o0 = make_float4(g[0] * scale, g[1] * scale, g[2] * scale, g[3] * scale);
+      float4 o1 = make_float4(g[4] * scale, g[5] * scale, g[6] * scale, g[7] * scale);
+      if (accumulate) {
+        const float4 a0 = *reinterpret_cast<const float4*>(out + i * 8), a1 = *reinterpret_cast<const float4*>(out + i * 8 + 4);
+        o0.x += a0.x; o0.y += a0.y; o0.z += a0.z; o0.w += a0.w;
+        o1.x += a1.x; o1.y += a1.y; o1.z += a1.z; o1.w += a1.w;
+      }
+      *reinterpret_cast<float4*>(out + i * 8) = o0;
+      *reinterpret_cast<float4*>(out + i * 8 + 4) = o1;
+    }
+  }
+  grid_barrier_end(P, pad_off, epoch + 1, spin_limit);       // every rank has pulled: the stages may be rewritten
+}
+
 static Peers make_peers(const uint64_t* ptrs, uint64_t mc, int nranks, int rank) {
   Peers P{};
   for (int i = 0; i < nranks && i < kMaxRanks; ++i) P.ptr[i] = ptrs[i];
@@ -567,4 +679,61 @@ PDB_EXPORT int pdb200_nvl_rs_sum_bf16(const uint64_t* peer_ptrs, uint64_t mc_ptr
   }
   barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
   return check_launch("nvl_rs_sum_bf16");
+}
+
+// Stage-3 unit transport.  segs (HOST memory): nseg triples of int64.
+//   all-gather:      {src_off, dst_off, shard_bytes}: this rank's shard at src_off of its own segment goes to
+//                    [dst_off + r * shard_bytes) of every rank's segment (r = sender's rank).
+//   reduce-scatter:  {stage_off, shard_numel, out_ptr}: see reduce_scatter_multi_kernel; out_ptr is a local fp32 pointer.
+// Both use epochs `epoch` and `epoch + 1` of the pad and run their cross-GPU barriers inside the one kernel.
+PDB_EXPORT int pdb200_nvl_allgather_multi(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank,
+                                          const int64_t* segs, int nseg, int64_t pad_off, int64_t epoch, int max_ctas,
+                                          void* stream) {
+  PDB_REQUIRE(nranks >= 1 && nranks <= kMaxRanks, "nvl: nranks %d out of range (1..%d)", nranks, kMaxRanks);
+  PDB_REQUIRE(nseg >= 1 && nseg <= kMaxSegs, "nvl_allgather_multi: 1..%d segments per launch (got %d)", kMaxSegs, nseg);
+  AgSegs S{};
+  S.n = nseg;
+  int64_t most = 0;
+  for (int k = 0; k < nseg; ++k) {
+    const int64_t so = segs[3 * k], dof = segs[3 * k + 1], nb = segs[3 * k + 2];
+    PDB_REQUIRE(nb >= 0 && nb % 16 == 0 && so % 16 == 0 && dof % 16 == 0, "nvl_allgather_multi: segment %d breaks the 16-byte granularity", k);
+    S.s[k] = AgSeg{(uint64_t)so, (uint64_t)dof, nb / 16};
+    if (nb / 16 > most) most = nb / 16;
+  }
+  Peers P = make_peers(peer_ptrs, mc_ptr, nranks, rank);
+  int64_t blocks = (most + 2047) / 2048;
+  const int64_t cap = max_ctas > 0 ? max_ctas : (int64_t)sm_count();
+  if (blocks > cap) blocks = cap;
+  allgather_multi_kernel<<<(unsigned)(blocks < 1 ? 1 : blocks), 512, 0, (cudaStream_t)stream>>>(P, S, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+  return check_launch("nvl_allgather_multi");
+}
+
+PDB_EXPORT int pdb200_nvl_reduce_scatter_multi(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank,
+                                               const int64_t* segs, int nseg, int grad_dtype, float scale, int accumulate,
+                                               int64_t pad_off, int64_t epoch, int max_ctas, void* stream) {
+  PDB_REQUIRE(nranks >= 1 && nranks <= kMaxRanks, "nvl: nranks %d out of range (1..%d)", nranks, kMaxRanks);
+  PDB_REQUIRE(nseg >= 1 && nseg <= kMaxSegs, "nvl_reduce_scatter_multi: 1..%d segments per launch (got %d)", kMaxSegs, nseg);
+  PDB_REQUIRE(grad_dtype == PDB_DTYPE_F32 || grad_dtype == PDB_DTYPE_BF16, "nvl_reduce_scatter_multi: grads must be fp32 or bf16");
+  RsSegs S{};
+  S.n = nseg;
+  int64_t most = 0;
+  for (int k = 0; k < nseg; ++k) {
+    const int64_t so = segs[3 * k], ne = segs[3 * k + 1];
+    float* out = reinterpret_cast<float*>((uintptr_t)segs[3 * k + 2]);
+    PDB_REQUIRE(ne >= 0 && ne % 8 == 0 && so % 16 == 0 && ((uintptr_t)out & 15) == 0 && out != nullptr,
+                "nvl_reduce_scatter_multi: segment %d: shard must be a multiple of 8 elements, 16-byte aligned", k);
+    S.s[k] = RsSeg{(uint64_t)so, ne, out};
+    if (ne / 8 > most) most = ne / 8;
+  }
+  Peers P = make_peers(peer_ptrs, mc_ptr, nranks, rank);
+  int64_t blocks = (most + 511) / 512;
+  const int64_t cap = max_ctas > 0 ? max_ctas : (int64_t)sm_count();
+  if (blocks > cap) blocks = cap;
+  const unsigned grid = (unsigned)(blocks < 1 ? 1 : blocks);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (grad_dtype == PDB_DTYPE_F32)
+    reduce_scatter_multi_kernel<float><<<grid, 512, 0, st>>>(P, S, scale, accumulate, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+  else
+    reduce_scatter_multi_kernel<__nv_bfloat16><<<grid, 512, 0, st>>>(P, S, scale, accumulate, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+  return check_launch("nvl_reduce_scatter_multi");
 }

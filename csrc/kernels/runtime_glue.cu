@@ -2,6 +2,9 @@
 #include <stdarg.h>
 #include <stdio.h>
 
+#include <mutex>
+#include <vector>
+
 #include "common.cuh"
 
 namespace pdb {
@@ -23,8 +26,67 @@ int sm_count() {
   }
   return cached[dev];
 }
+
+// ---- local-memory guard ------------------------------------------------------------------------------------------
+// Address ranges of this process that map ANOTHER GPU's memory (peer segments of a symmetric arena, NVLS multicast
+// windows).  The symmetric-memory layer registers them; every launcher that builds a TMA tensor map or hands a buffer
+// to a tensor-core kernel refuses operands that touch one of them.  Rule of this library: TMA tensor maps cover this
+// GPU's own memory only; a peer's data is first landed in local memory and loaded from there.
+namespace {
+struct Range { uintptr_t lo, hi; };
+std::mutex g_foreign_mu;
+std::vector<Range> g_foreign;
+}  // namespace
+int require_local(const void* p, size_t bytes, const char* what) {
+  if (p == nullptr) return 0;
+  const uintptr_t lo = (uintptr_t)p, hi = lo + (bytes ? bytes : 1);
+  std::lock_guard<std::mutex> g(g_foreign_mu);
+  for (const Range& r : g_foreign)
+    if (lo < r.hi && r.lo < hi) {
+      set_error("%s: operand %p (+%zu B) lies in a mapping of another GPU's memory [%p, %p); tensor-core / TMA operands "
+                "must be local - copy or gather the data into this GPU's memory first", what, p, bytes, (void*)r.lo, (void*)r.hi);
+      return -1;
+    }
+  return 0;
+}
+int require_local_device(const void* p, const char* what) {
+  if (p == nullptr) return 0;
+  cudaPointerAttributes at{};
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) {
+    set_error("%s: no current CUDA device", what);
+    return -1;
+  }
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+    cudaGetLastError();
+    set_error("%s: operand %p is not a CUDA allocation", what, p);
+    return -1;
+  }
+  if (at.type != cudaMemoryTypeDevice || at.device != dev) {
+    set_error("%s: operand %p is not device memory of the current GPU %d (type %d, device %d)", what, p, dev, (int)at.type, at.device);
+    return -1;
+  }
+  return 0;
+}
 }  // namespace pdb
 
+PDB_EXPORT int pdb200_register_foreign_range(uint64_t base, uint64_t bytes) {
+  PDB_REQUIRE(base != 0 && bytes != 0, "register_foreign_range: empty range");
+  std::lock_guard<std::mutex> g(pdb::g_foreign_mu);
+  pdb::g_foreign.push_back({(uintptr_t)base, (uintptr_t)(base + bytes)});
+  return 0;
+}
+PDB_EXPORT int pdb200_unregister_foreign_range(uint64_t base) {
+  std::lock_guard<std::mutex> g(pdb::g_foreign_mu);
+  for (size_t i = 0; i < pdb::g_foreign.size(); ++i)
+    if (pdb::g_foreign[i].lo == (uintptr_t)base) {
+      pdb::g_foreign.erase(pdb::g_foreign.begin() + i);
+      return 0;
+    }
+  return 0;
+}
+PDB_EXPORT int pdb200_check_local(const void* p, int64_t bytes) { return pdb::require_local(p, (size_t)bytes, "check_local"); }
+
 PDB_EXPORT const char* pdb200_last_error() { return pdb::g_err; }
-PDB_EXPORT int pdb200_abi_version() { return 1; }
+PDB_EXPORT int pdb200_abi_version() { return 2; }
 PDB_EXPORT int pdb200_sm_count() { return pdb::sm_count(); }

@@ -230,6 +230,10 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N, int a_mn_ma
 // Returns 0 on success.  The driver entry point is resolved once through the runtime (no -lcuda at link time).
 int encode_tmap_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t row_stride_bytes,
                    uint32_t box_rows, uint32_t box_cols, int elem_bytes, bool swizzle128);
+// Cached + guarded variant used by every launcher: refuses a base that is not this GPU's own memory (`what` names the
+// operand in the error message).
+int get_tmap_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t row_stride_bytes,
+                uint32_t box_rows, uint32_t box_cols, int elem_bytes, bool swizzle128, const char* what);
 
 }  // namespace tc
 }  // namespace pdb

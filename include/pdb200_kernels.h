@@ -18,6 +18,15 @@ PDB_API const char* pdb200_last_error();
 PDB_API int pdb200_abi_version();
 PDB_API int pdb200_sm_count();
 
+/* Local-memory guard (no counterpart in the reference).  Rule of this library: every TMA tensor map and every
+ * tensor-core operand is this GPU's own memory; data of another GPU is first landed in local memory.  The
+ * symmetric-memory layer registers each address range that maps another GPU's memory (peer segments, NVLS windows);
+ * the GEMM / attention launchers refuse operands that overlap a registered range, and additionally verify with
+ * cudaPointerGetAttributes that a base address belongs to the current device when they first build a map for it. */
+PDB_API int pdb200_register_foreign_range(uint64_t base, uint64_t bytes);
+PDB_API int pdb200_unregister_foreign_range(uint64_t base);
+PDB_API int pdb200_check_local(const void* p, int64_t bytes);
+
 /* K18/K19 fused RMSNorm / LayerNorm (reference: phi/kernels/gpu/rms_norm_kernel.cu:420-520, rms_norm_funcs.h:507-942,
  * layer_norm_kernel.cu).  residual (optional): y = norm(x + residual), residual_out = x + residual. */
 PDB_API int pdb200_norm_fwd(const void* x, const void* residual, const void* w, const void* b, void* y, void* residual_out, float* mean, float* rstd, int64_t rows, int64_t cols, float eps, int x_dtype, int w_is_f32, int is_layernorm, void* stream);
@@ -83,7 +92,7 @@ PDB_API int pdb200_gemm_bf16_pair(const void* a, const void* b, void* c, const v
 
 /* Fused collectives over NVLink symmetric memory (K1, K2+K3, K8; csrc/kernels/nvl_collectives.cu).  peer_ptrs: host
  * array of nranks device addresses = every rank's segment as mapped in this process (pdb200_symm_peer_ptr), mc_ptr:
- * NVLS multicast mapping or 0 (P2P fallback).  *_off: byte offsets inside the segment, identical on all ranks.
+ * NVLS (multimem) mapping of the segment or 0 (P2P fallback).  *_off: byte offsets inside the segment, identical on all ranks.
  * pad_off: 32-byte signal pad used by the in-stream barriers; each call consumes epochs `epoch` and `epoch + 1`.
  * Reference counterparts: reducer.cc:1093-1127 (K1), tensor_fusion_helper.py:559-645 + adamw_kernel.cu (K2+K3),
  * c_softmax_with_cross_entropy_op.cu:211-314 (K8). */
@@ -94,24 +103,20 @@ PDB_API int pdb200_nvl_rs_grid(int64_t shard_numel);
 /* Cap the grid of the reduce-scatter kernels (0 = default 4 CTAs per SM); affects pdb200_nvl_rs_grid too. */
 PDB_API int pdb200_nvl_set_rs_max_ctas(int n);
 PDB_API int pdb200_nvl_reduce_scatter(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t grad_off, int grad_dtype, int64_t shard_start, int64_t shard_numel, float* out, float* partial_sq, int64_t pad_off, int64_t epoch, void* stream);
-/* K3 stand-alone: parameter all-gather as a multicast push (every rank stores its shard into slot `rank` of all ranks' buffers). */
+/* K3 stand-alone: parameter all-gather as a push (every rank stores its shard into slot `rank` of all ranks' buffers: one NVLS multimem.st per 16 bytes, or a loop of peer stores). */
 PDB_API int pdb200_nvl_allgather(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t src_off, int64_t dst_off, int64_t shard_bytes, int64_t pad_off, int64_t epoch, int max_ctas, void* stream);
 PDB_API int pdb200_nvl_allgather_from(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, const void* src, int64_t dst_off, int64_t shard_bytes, int64_t pad_off, int64_t epoch, int max_ctas, void* stream);
+/* ZeRO-3 unit transport (K3 / K2 pass 1 for GroupSharded stage 3; reference: group_sharded_stage3.py:741-803, 849-1118
+ * per-parameter all_gather / all_reduce + slice).  One launch per unit: `segs` is a HOST array of nseg (<= 16) int64
+ * triples and the cross-GPU barriers run inside the kernel.  all-gather triple = {src_off, dst_off, shard_bytes};
+ * reduce-scatter triple = {stage_off, shard_numel, local fp32 out pointer}: out (+)= scale * sum_r stage_r[shard]. */
+PDB_API int pdb200_nvl_allgather_multi(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, const int64_t* segs, int nseg, int64_t pad_off, int64_t epoch, int max_ctas, void* stream);
+PDB_API int pdb200_nvl_reduce_scatter_multi(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, const int64_t* segs, int nseg, int grad_dtype, float scale, int accumulate, int64_t pad_off, int64_t epoch, int max_ctas, void* stream);
 /* Sum reduce-scatter of a symmetric bf16 buffer into a local bf16 shard (tail of GEMM -> reduce-scatter; NVLS in-switch add). */
 PDB_API int pdb200_nvl_rs_sum_bf16(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t src_off, int64_t shard_start, int64_t shard_numel, void* out, int64_t pad_off, int64_t epoch, void* stream);
 PDB_API int pdb200_nvl_ce_combine(const uint64_t* peer_ptrs, int nranks, int rank, int64_t stats_off, const int64_t* labels, float* loss, float* lse, int64_t rows, int64_t ignore_index, int64_t pad_off, int64_t epoch, void* stream);
 /* K7 vocab-parallel embedding forward as a gather from the owning rank's table shard (replaces masked lookup + all-reduce). */
 PDB_API int pdb200_nvl_vocab_embed(const uint64_t* peer_ptrs, int nranks, int rank, int64_t table_off, const int64_t* ids, void* out, int64_t n_tokens, int hidden, int64_t vocab_per_rank, int dtype, int64_t pad_off, int64_t epoch, void* stream);
-
-/* K5 all-gather -> GEMM and K6 GEMM -> reduce-scatter on the tcgen05 kernel (reference: fleet/utils/
- * sequence_parallel_utils.py:255-285 ncclAllGather + GEMM, :660-676 GEMM + ncclReduceScatter).  K5: every rank's
- * [rows_per_rank, K] bf16 shard sits at a_off in its segment; A tiles are TMA-loaded straight from the owning peer.
- * K6: partial output tiles are stored into the owner's staging slab [nranks][rows_per_rank][N] at stage_off as they
- * leave TMEM, then folded into out[rows_per_rank, N]. */
-PDB_API int pdb200_gemm_bf16_ag(const uint64_t* peer_ptrs, int nranks, int rank, int64_t a_off, int64_t rows_per_rank, const void* b, void* c, const void* bias, int64_t N, int64_t K, int trans_b, int act, int64_t pad_off, int64_t epoch, void* stream);
-PDB_API int pdb200_gemm_bf16_rs(const uint64_t* peer_ptrs, int nranks, int rank, const void* a, const void* b, int64_t stage_off, void* out, int64_t rows_per_rank, int64_t N, int64_t K, int trans_b, int64_t pad_off, int64_t epoch, void* stream);
-/* K4 GEMM -> all-reduce: K6's tile push, then owners fold and store the sum into every rank's [M,N] output at out_off. */
-PDB_API int pdb200_gemm_bf16_ar(const uint64_t* peer_ptrs, int nranks, int rank, const void* a, const void* b, int64_t stage_off, int64_t out_off, int64_t rows_per_rank, int64_t N, int64_t K, int trans_b, int64_t pad_off, int64_t epoch, void* stream);
 
 /* K16 flash-attention forward on tcgen05 (reference: phi/kernels/gpu/flash_attn_kernel.cu:305-447 -> FlashAttention-2
  * sm80 kernels).  q [b,sq,hq,d], k/v [b,sk,hk,d] bf16, d in {64,128}, sq/sk multiples of 128; o like q; lse [b,hq,sq]

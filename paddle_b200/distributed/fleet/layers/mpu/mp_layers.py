@@ -152,11 +152,11 @@ def _fused_ar_ok(x, w, group, n_out):
     rows = x.numel() // x.shape[-1]
     if rows % (group.nranks * 128) != 0:
         return False
-    if not symm.available(group) or not hasattr(symm.lib.kernels.require(), "pdb200_gemm_bf16_ar"):
+    if not symm.available(group):
         return False
     return symm.fused_gemm_ok(group, rows // group.nranks, x.shape[-1], n_out, x.dtype) and \
-        (symm.get_arena(group).free_bytes() > 2 * rows * n_out * 2 + (1 << 20) or
-         any(k[1] == "ar_out" for k in symm._stage))
+        (symm.get_arena(group).free_bytes() > rows * n_out * 2 + (1 << 20) or
+         any(k[1] == "ar_part" for k in symm._stage))
 
 
 class _AsyncColumnLinear(torch.autograd.Function):

@@ -9,8 +9,12 @@ fp32 master weights; ``get_all_parameters`` rebuilds full tensors for saving.
 
 Changed by design (B200): the gradient path is a reduce-scatter (AVG) of the padded gradient straight into the
 slice accumulator - half the wire volume of the reference's all-reduce-then-slice (:741-803); communication runs
-async on the group's comm stream and is only awaited where its result is consumed, so gather / scatter overlap the
-neighbouring layers' GEMMs.
+async on a side stream and is only awaited where its result is consumed, so gather / scatter overlap the
+neighbouring layers' GEMMs.  A unit (what is gathered / released / reduced together) is the largest sub-layer whose
+sliced parameters stay under ``PDB200_STAGE3_UNIT_NUMEL`` (default 2^29 elements) - a whole decoder layer - instead
+of every leaf layer: with 180 GB of HBM a resident layer is cheap and NVSwitch wants few, large transfers.  On one
+NVSwitch node the default transport is the symmetric-memory one (``_NvlTransport``); NCCL is the fallback and the
+numerical oracle (``FLAGS_use_fused_comm=0`` or ``FLAGS_stage3_nvl_transport=0``).
 """
 from __future__ import annotations
 
@@ -42,51 +46,54 @@ class _Unit:
         self.gather_task = None      # list of (param, full_buffer, Task) while an async gather is in flight
         self.gathered = False
         self.pending_grads = 0
+        self.gstage = None           # gradient stage of the symmetric transport during this unit's backward
+        self.reduced = False         # a reduce-scatter has written main_grad since the last clear_grad
 
 
 class _NvlTransport:
-    """Stage-3 traffic over NVLink symmetric memory instead of NCCL (K3 push all-gather, K2-pass-1 pull reduce-scatter).
+    """Stage-3 traffic over NVLink symmetric memory instead of NCCL.
 
-    Every rank keeps its parameter slices inside one symmetric arena; gathered parameters live in a small ring of
-    arena slots (a layer is gathered into the next slot while the previous layer computes), gradients are staged in
-    two arena buffers from which every owner pulls and averages its slice through the switch.  All transport kernels
-    run on one side stream in the same order on every rank; the tcgen05 GEMMs leave >90 % of the issue slots idle, so
-    the copy kernels co-reside with them on the SMs."""
-    SLOTS = 4
+    One launch per unit and direction (csrc/kernels/nvl_collectives.cu): ``allgather_multi`` pushes every parameter
+    slice of the unit into all ranks' gathered slot (NVLS ``multimem.st``), ``reduce_scatter_multi`` pulls this rank's
+    shard of every staged gradient through the switch (``multimem.ld_reduce``), averages it and writes / accumulates
+    it into the fp32 ``main_grad`` slice the fused AdamW reads.  The cross-GPU barriers run inside those kernels.
 
-    def __init__(self, group, params, device):
+    Layout of the arena: [parameter slices | SLOTS gathered-parameter slots | GSTAGES gradient stages].  Gathered
+    parameters are consumed by the tcgen05 GEMMs in place (the slot is local memory), weight-gradient GEMMs write
+    straight into the gradient stage (``param._grad_dst``), so neither direction has a staging copy.  All transport
+    kernels run on one side stream, in the same order on every rank, with a capped grid so they co-reside with the
+    GEMMs instead of displacing them."""
+
+    def __init__(self, group, units_params, device):
+        import os
         from paddle_b200.parallel import symm
+        self.symm = symm
         n = group.nranks
         al = lambda b: (b + 255) // 256 * 256   # noqa: E731
-        slice_bytes = sum(al(_padded_numel(p, n) // n * p.element_size()) for p in params)
-        self.max_param_bytes = max(al(_padded_numel(p, n) * p.element_size()) for p in params)
-        self.slot_bytes = self.max_param_bytes   # grown by the owner once units are known (see reserve)
-        self._pending = (group, slice_bytes, device)
-        self.symm = symm
-        self.arena = None
-
-    def reserve(self, max_unit_bytes):
-        group, slice_bytes, device = self._pending
-        self.slot_bytes = max(self.slot_bytes, max_unit_bytes)
-        total = slice_bytes + self.SLOTS * self.slot_bytes + 2 * self.max_param_bytes + (8 << 20)
-        self.arena = self.symm.SymmArena(group, total)
-        self.stream = torch.cuda.Stream(device=device)
-        import os
-        # grid caps of the transport kernels (0 = library default); measured: capping them exposes transfer time
-        self.ag_ctas = int(os.environ.get("PDB200_STAGE3_AG_CTAS", "0"))
-        self.symm.lib.kernels.pdb200_nvl_set_rs_max_ctas(int(os.environ.get("PDB200_STAGE3_RS_CTAS", "0")))
+        self.al = al
+        self.SLOTS = max(2, int(os.environ.get("PDB200_STAGE3_SLOTS", "4")))
+        self.GSTAGES = max(1, int(os.environ.get("PDB200_STAGE3_GSTAGES", "3")))
+        slice_bytes = sum(al(_padded_numel(p, n) // n * p.element_size()) for ps in units_params for p in ps)
+        self.slot_bytes = max(sum(al(_padded_numel(p, n) * p.element_size()) for p in ps) for ps in units_params)
+        total = slice_bytes + (self.SLOTS + self.GSTAGES) * self.slot_bytes + (8 << 20)
+        self.arena = symm.SymmArena(group, total)
+        self.stream = torch.cuda.Stream(device=device, priority=-1)
+        # grid caps of the transport kernels (CTAs of 512 threads); few CTAs already saturate the links
+        self.ag_ctas = int(os.environ.get("PDB200_STAGE3_AG_CTAS", "32"))
+        self.rs_ctas = int(os.environ.get("PDB200_STAGE3_RS_CTAS", "32"))
+        self.noop = bool(int(os.environ.get("PDB200_STAGE3_COMM_NOOP", "0")))   # timing experiments only
         self.slots = None
         self.slot_owner = [None] * self.SLOTS
         self.next_slot = 0
-        self.gstage = None
-        self.gstage_done = [None, None]
+        self.gstages = None
+        self.gstage_free = [None] * self.GSTAGES
         self.next_gstage = 0
-        self.rs_scratch = None
+        self.last_rs = None
 
     def finish_layout(self):
-        """Called after every slice has been placed: the ring and the gradient stages take the rest of the arena."""
+        """Called after every slice has been placed: the slot ring and the gradient stages take the rest."""
         self.slots = [self.arena.empty((self.slot_bytes,), torch.uint8) for _ in range(self.SLOTS)]
-        self.gstage = [self.arena.empty((self.max_param_bytes,), torch.uint8)]
+        self.gstages = [self.arena.empty((self.slot_bytes,), torch.uint8) for _ in range(self.GSTAGES)]
 
     def new_slice(self, numel, dtype):
         return self.arena.empty((numel,), dtype)
@@ -96,6 +103,18 @@ class _NvlTransport:
         t = arena.tensor(off + byte_off, (numel,), dtype)
         t._symm = (arena, off + byte_off)
         return t
+
+    def _launch(self, fn_name, segs, *tail):
+        import ctypes
+        from paddle_b200.lib import check
+        a = self.arena
+        k = self.symm.lib.kernels
+        fn = getattr(k, fn_name)
+        for i in range(0, len(segs), 16):
+            chunk = segs[i:i + 16]
+            flat = (ctypes.c_int64 * (3 * len(chunk)))(*[int(v) for s in chunk for v in s])
+            check(fn(a.peers_arg, a.mc_ptr, a.nranks, a.rank, ctypes.cast(flat, ctypes.c_void_p), len(chunk), *tail[:-2],
+                     0, a.next_epoch(), *tail[-2:]), fn_name)
 
     def gather(self, unit):
         slot = None
@@ -113,41 +132,59 @@ class _NvlTransport:
         cur = torch.cuda.current_stream()
         ev = torch.cuda.Event()
         ev.record(cur)           # the slot's previous contents and this rank's slices are final up to here
-        fulls = []
+        fulls, segs, off = [], [], 0
+        for p in unit.params:
+            full = self._view(self.slots[slot], off, p._gs_padded, p.dtype)
+            per_bytes = p._gs_padded // self.arena.nranks * p.element_size()
+            segs.append((p.fw_storage._symm_view._symm[1], full._symm[1], per_bytes))
+            fulls.append((p, full))
+            off += self.al(p._gs_padded * p.element_size())
         with torch.cuda.stream(self.stream):
             self.stream.wait_event(ev)
-            off = 0
-            for p in unit.params:
-                full = self._view(self.slots[slot], off, p._gs_padded, p.dtype)
-                self.symm.all_gather_push(p.fw_storage._symm_view, full, max_ctas=self.ag_ctas)
-                fulls.append((p, full))
-                off += (p._gs_padded * p.element_size() + 255) // 256 * 256
+            if not self.noop:
+                self._launch("pdb200_nvl_allgather_multi", segs, self.ag_ctas, self.stream.cuda_stream)
             done = torch.cuda.Event()
             done.record(self.stream)
         return fulls, done
 
-    def reduce_scatter(self, p, grad, per, out_dtype):
-        """Everything (staging copy, pull + average, cast) runs on the transport stream; the compute stream only
-        records "gradient ready" and later waits for ``done``."""
+    def begin_backward(self, unit):
+        """Give the unit a gradient stage: weight-gradient GEMMs write into ``p._grad_dst`` (a view of it)."""
+        g = self.next_gstage
+        self.next_gstage = (g + 1) % self.GSTAGES
+        free = self.gstage_free[g]
+        if free is not None:
+            torch.cuda.current_stream().wait_event(free)       # the previous reduce-scatter out of this stage is done
+        unit.gstage = g
+        off = 0
+        for p in unit.params:
+            st = self._view(self.gstages[g], off, p._gs_padded, p.dtype)
+            p._grad_stage = st
+            p._grad_dst = st[: p._gs_numel].view(p._gs_shape)
+            if p._gs_padded != p._gs_numel:
+                st[p._gs_numel:].zero_()
+            off += self.al(p._gs_padded * p.element_size())
+
+    def reduce_scatter(self, unit, accumulate):
+        """All gradients of the unit sit in its stage: one pull kernel averages this rank's shards into main_grad."""
         cur = torch.cuda.current_stream()
         ev = torch.cuda.Event()
         ev.record(cur)
-        grad.record_stream(self.stream)
+        n = self.arena.nranks
+        segs = [(p._grad_stage._symm[1], p._gs_padded // n, p.fw_storage.main_grad.data_ptr()) for p in unit.params
+                if p.requires_grad]
+        from paddle_b200.ops._util import dtype_code
         with torch.cuda.stream(self.stream):
             self.stream.wait_event(ev)
-            stage = self._view(self.gstage[0], 0, p._gs_padded, grad.dtype)   # one buffer: the stream serialises its reuse
-            flat = grad.reshape(-1)
-            stage[: flat.numel()].copy_(flat)
-            if flat.numel() != p._gs_padded:
-                stage[flat.numel():].zero_()
-            acc = torch.empty(per, dtype=torch.float32, device=grad.device)
-            scratch = torch.empty(self.symm.lib.kernels.pdb200_nvl_rs_grid(int(per)), dtype=torch.float32, device=grad.device)
-            self.symm.reduce_scatter_avg(stage, self.arena.rank * per, per, acc, scratch)
-            out = acc if out_dtype == torch.float32 else acc.to(out_dtype)
+            if not self.noop and segs:
+                self._launch("pdb200_nvl_reduce_scatter_multi", segs, dtype_code(unit.params[0]), 1.0 / n, int(accumulate),
+                             self.rs_ctas, self.stream.cuda_stream)
             done = torch.cuda.Event()
             done.record(self.stream)
-        out.record_stream(cur)
-        return out, done
+        self.gstage_free[unit.gstage] = done
+        self.last_rs = done
+        for p in unit.params:
+            p._grad_dst = None
+            p._grad_stage = None
 
     def close(self):
         if self.arena is not None:
@@ -169,6 +206,8 @@ class _BackwardGather(torch.autograd.Function):
         s3._ensure_gathered(unit)
         s3._prefetch_backward(unit)
         unit.pending_grads = sum(1 for p in unit.params if p.requires_grad)
+        if s3._nvl is not None:
+            s3._nvl.begin_backward(unit)
         return (None, None, *grads)
 
 
@@ -176,6 +215,7 @@ class GroupShardedStage3(Layer):
     def __init__(self, layer, optimizer, group=None, sync_buffers=False, device="gpu", segment_size=2 ** 20,
                  pretrain_sync_models=True, offload=False, sync_comm=False, dp_group=None, exclude_layer=None):
         super().__init__()
+        import os
         from paddle_b200.distributed import collective as C
         self._layer = layer
         self._optim = optimizer
@@ -187,8 +227,6 @@ class GroupShardedStage3(Layer):
         self._sync_buffers = sync_buffers
         self._sync_comm = sync_comm
         self._offload = offload
-        if offload:
-            raise NotImplementedError("offload=True: CPU offload of optimizer state is not implemented in this build")
         self._exclude = list(exclude_layer or [])
         self._units = []
         self._unit_of_layer = {}
@@ -198,19 +236,21 @@ class GroupShardedStage3(Layer):
         self._slice_params = []
         self._grad_tasks = []
         self._use_main_grad = False
-        import os
-        # how many layers ahead parameters are gathered (the reference prefetches one, :849-896); two hides the
-        # gather of short layers (o_proj) behind the long ones
+        self._unit_numel = int(os.environ.get("PDB200_STAGE3_UNIT_NUMEL", str(2 ** 29)))
+        # how many units ahead parameters are gathered (the reference prefetches one, :849-896)
         self._prefetch_depth = max(1, int(os.environ.get("PDB200_STAGE3_PREFETCH", "2")))
         self._nvl = None
         if pretrain_sync_models:
             self._sync_params_and_buffers()
-        self._init_transport()
-        self._segment_rank_params()
+        plan = self._plan_units()
+        self._init_transport(plan)
+        self._segment_rank_params(plan)
         if self._nvl is not None:
             self._nvl.finish_layout()
         self._register_hooks()
         self._redefine_opt()
+        if offload:
+            self._enable_offload()
 
     # ------------------------------------------------------------------ setup
     @torch.no_grad()
@@ -221,36 +261,71 @@ class GroupShardedStage3(Layer):
         for b in self._layer.buffers():
             comm.broadcast(b, src, self._group)
 
-    def _init_transport(self):
+    def _sliceable(self, p, sub):
+        return p.requires_grad and p.numel() >= self._segment_size and not self._is_excluded(sub)
+
+    def _plan_units(self):
+        """-> [(layer, [sliced params]), ...] and fills ``_unslice_params``.  Top-down: a sub-layer becomes one unit
+        with all the sliceable parameters below it when they fit the unit budget; otherwise its own parameters form a
+        unit and its children are planned recursively.  The root is never a unit (its parameters must be released
+        between its children)."""
+        plan, seen = [], set()
+
+        def below(sub):
+            out = []
+            for m in sub.sublayers(include_self=True):
+                if self._is_excluded(m):
+                    continue
+                for q in m.parameters(include_sublayers=False):
+                    if id(q) not in seen and self._sliceable(q, m) and not any(q is o for o in out):
+                        out.append(q)
+            return out
+
+        def visit(sub, is_root):
+            cand = below(sub)
+            if not is_root and cand and sum(q.numel() for q in cand) <= self._unit_numel and \
+                    len({q.dtype for q in cand}) == 1:
+                for q in cand:
+                    seen.add(id(q))
+                plan.append((sub, cand))
+                return
+            own = [q for q in sub.parameters(include_sublayers=False) if id(q) not in seen and self._sliceable(q, sub)]
+            if own:
+                for q in own:
+                    seen.add(id(q))
+                plan.append((sub, own))
+            for child in sub.children():
+                visit(child, False)
+
+        visit(self._layer, True)
+        for q in self._layer.parameters():
+            if id(q) not in seen:
+                seen.add(id(q))
+                q._gs_unslice = True
+                self._unslice_params.append(q)
+        return plan
+
+    def _init_transport(self, plan):
         """Use the NVLink symmetric-memory transport when the group is one NVSwitch node and every slice keeps the
         16-byte granularity of the copy kernels; otherwise NCCL (also the numerical oracle: FLAGS_use_fused_comm=0)."""
         from paddle_b200.framework.flags import flag
         from paddle_b200.parallel import symm
-        dev = next(iter(self._layer.parameters())).device
-        # opt-in: measured on 2 x B200 (Llama-2 7B, b=2): NCCL transport 397 ms/step, this transport 406-425 ms/step
+        if not plan:
+            return
+        dev = plan[0][1][0].device
         if not flag("stage3_nvl_transport") or dev.type != "cuda" or not symm.available(self._group):
             return
-        if not hasattr(symm.lib.kernels.require(), "pdb200_nvl_allgather"):
+        if not hasattr(symm.lib.kernels.require(), "pdb200_nvl_allgather_multi"):
             return
         n = self._world_size
-        cands, unit_bytes, seen = [], 0, set()
-        for sub in self._layer.sublayers(include_self=True):
-            own = [p for p in sub.parameters(include_sublayers=False) if id(p) not in seen]
-            ub = 0
-            for p in own:
-                seen.add(id(p))
-                if p.requires_grad and p.numel() >= self._segment_size and not self._is_excluded(sub):
-                    if p.dtype not in (torch.bfloat16, torch.float32) or (_padded_numel(p, n) // n) % 8 != 0:
-                        return
-                    cands.append(p)
-                    ub += (_padded_numel(p, n) * p.element_size() + 255) // 256 * 256
-            unit_bytes = max(unit_bytes, ub)
-        if not cands:
-            return
+        for _, ps in plan:
+            if len({p.dtype for p in ps}) != 1:
+                return
+            for p in ps:
+                if p.dtype not in (torch.bfloat16, torch.float32) or (_padded_numel(p, n) // n) % 8 != 0:
+                    return
         try:
-            t = _NvlTransport(self._group, cands, dev)
-            t.reserve(unit_bytes)
-            self._nvl = t
+            self._nvl = _NvlTransport(self._group, [ps for _, ps in plan], dev)
         except Exception as e:  # noqa: BLE001
             import warnings
             warnings.warn(f"stage 3: symmetric-memory transport unavailable ({e}); using NCCL")
@@ -261,26 +336,13 @@ class GroupShardedStage3(Layer):
                    (isinstance(e, str) and type(sub).__name__ == e) for e in self._exclude)
 
     @torch.no_grad()
-    def _segment_rank_params(self):
-        seen = set()
-        for sub in self._layer.sublayers(include_self=True):
-            own = [p for p in sub.parameters(include_sublayers=False) if id(p) not in seen]
-            for p in own:
-                seen.add(id(p))
-            if not own:
-                continue
-            sliced = []
-            for p in own:
-                if not p.requires_grad or p.numel() < self._segment_size or self._is_excluded(sub):
-                    p._gs_unslice = True
-                    self._unslice_params.append(p)
-                    continue
+    def _segment_rank_params(self, plan):
+        for sub, ps in plan:
+            for p in ps:
                 self._slice_param(p)
-                sliced.append(p)
-            if sliced:
-                u = _Unit(sub, sliced)
-                self._units.append(u)
-                self._unit_of_layer[id(sub)] = u
+            u = _Unit(sub, ps)
+            self._units.append(u)
+            self._unit_of_layer[id(sub)] = u
 
     def _slice_param(self, p):
         n = self._world_size
@@ -296,6 +358,9 @@ class GroupShardedStage3(Layer):
         fw = Parameter(sl, requires_grad=True, name=p.name + "@slice")
         fw.data = sl
         fw._symm_view = sl if self._nvl is not None else None
+        if self._nvl is not None:
+            # the reduce-scatter kernel averages straight into this fp32 accumulator; the fused AdamW reads it
+            fw.main_grad = torch.zeros(per, dtype=torch.float32, device=p.device)
         fw.need_clip = getattr(p, "need_clip", True)
         fw.optimize_attr = getattr(p, "optimize_attr", {"learning_rate": 1.0})
         fw._origin_name = p.name
@@ -304,6 +369,7 @@ class GroupShardedStage3(Layer):
         p._gs_numel = p.numel()
         p._gs_padded = padded
         p._gs_unslice = False
+        p._grad_dst = None
         p.bw_storage = None
         p.data = torch.empty(0, dtype=p.dtype, device=p.device)   # release the full tensor
         self._slice_params.append(p)
@@ -314,9 +380,6 @@ class GroupShardedStage3(Layer):
             u.layer.register_forward_post_hook(self._make_post_hook(u))
             for p in u.params:
                 p.register_post_accumulate_grad_hook(self._make_grad_hook(u, p))
-        for p in self._unslice_params:
-            if p.requires_grad:
-                pass
 
     # ------------------------------------------------------------------ gather / release
     def _launch_gather(self, unit):
@@ -363,15 +426,14 @@ class GroupShardedStage3(Layer):
         def hook(layer, inputs):
             self._ensure_gathered(unit)
             if not self._order_learned:
-                self._order_fw.append(unit)
+                if unit not in self._order_fw:
+                    self._order_fw.append(unit)
             else:
-                try:
-                    i = self._order_index[id(unit)]
+                i = self._order_index.get(id(unit))
+                if i is not None:
                     for k in range(1, self._prefetch_depth + 1):
                         if i + k < len(self._order_fw):
                             self._launch_gather(self._order_fw[i + k])
-                except KeyError:
-                    pass
             return None
         return hook
 
@@ -405,11 +467,18 @@ class GroupShardedStage3(Layer):
             n = self._world_size
             per = p._gs_padded // n
             if self._nvl is not None:
-                out, done = self._nvl.reduce_scatter(p, g, per, torch.float32 if self._use_main_grad else p.dtype)
-                self._grad_tasks.append((p, out, done, None))
+                if unit.gstage is None:          # backward reached the parameter without passing _BackwardGather
+                    self._nvl.begin_backward(unit)
+                    unit.pending_grads = sum(1 for q in unit.params if q.requires_grad)
+                dst = p._grad_dst
+                if g.data_ptr() != dst.data_ptr():   # not written in place by the weight-gradient GEMM: stage it
+                    dst.copy_(g.reshape(dst.shape))
                 param.grad = None
                 unit.pending_grads -= 1
                 if unit.pending_grads <= 0:
+                    self._nvl.reduce_scatter(unit, accumulate=unit.reduced)
+                    unit.reduced = True
+                    unit.gstage = None
                     self._release(unit)
                 return
             flat = g.reshape(-1)
@@ -428,12 +497,20 @@ class GroupShardedStage3(Layer):
 
     @torch.no_grad()
     def _finish_grads(self):
+        dp = self._dp_group is not None and self._dp_group.nranks > 1
+        if self._nvl is not None:
+            if self._nvl.last_rs is not None:
+                torch.cuda.current_stream().wait_event(self._nvl.last_rs)     # the transport stream is in order
+            for u in self._units:
+                for p in u.params:
+                    mg = p.fw_storage.main_grad
+                    if not u.reduced:
+                        mg.zero_()                    # no gradient reached this unit in this step
+                    elif dp:
+                        comm.all_reduce(mg, ReduceOp.AVG, self._dp_group)
         for p, out, t, _keep in self._grad_tasks:
-            if self._nvl is not None:
-                torch.cuda.current_stream().wait_event(t)
-            else:
-                t.wait()
-            if self._dp_group is not None and self._dp_group.nranks > 1:
+            t.wait()
+            if dp:
                 comm.all_reduce(out, ReduceOp.AVG, self._dp_group)
             if p.bw_storage is None:
                 p.bw_storage = out.float() if self._use_main_grad else out
@@ -443,7 +520,7 @@ class GroupShardedStage3(Layer):
         for p in self._unslice_params:
             if p.requires_grad and p.grad is not None:
                 comm.all_reduce(p.grad, ReduceOp.AVG, self._group)
-                if self._dp_group is not None and self._dp_group.nranks > 1:
+                if dp:
                     comm.all_reduce(p.grad, ReduceOp.AVG, self._dp_group)
 
     # ------------------------------------------------------------------ optimizer redefinition (:819-838)
@@ -460,16 +537,23 @@ class GroupShardedStage3(Layer):
             opt._grad_clip = GroupShardedClipGrad(opt._grad_clip, None, self._group)
         stage3 = self
         inner_step = opt.step
-        inner_clear = opt.clear_grad
+        inner_clear = opt.clear_grad  # noqa: F841
 
         def step():
             stage3._finish_grads()
-            for p in stage3._slice_params:
-                fw = p.fw_storage
-                fw.grad = p.bw_storage
-            inner_step()
+            if stage3._nvl is None:
+                for p in stage3._slice_params:
+                    p.fw_storage.grad = p.bw_storage
+            if getattr(opt, "_offload_pre", None) is not None:
+                opt._offload_pre()
+                inner_step()
+                opt._offload_post()
+            else:
+                inner_step()
 
         def clear_grad(set_to_zero=True):
+            for u in stage3._units:
+                u.reduced = False               # the next reduce-scatter overwrites main_grad: no zero-fill pass
             for p in stage3._slice_params:
                 p.bw_storage = None
                 p.fw_storage.grad = None
@@ -483,6 +567,12 @@ class GroupShardedStage3(Layer):
         opt.step = step
         opt.clear_grad = clear_grad
         opt.clear_gradients = clear_grad
+
+    def _enable_offload(self):
+        """``offload=True`` (reference :98-127, :294): fp32 master weights and optimizer moments of the slices live in
+        pinned host memory; the step runs on the CPU and the updated slices are copied back."""
+        from .group_sharded_utils import offload_optimizer_state
+        offload_optimizer_state(self._optim, [p.fw_storage for p in self._slice_params], wrap_step=False)
 
     # ------------------------------------------------------------------ forward / utilities
     def forward(self, *inputs, **kwargs):

@@ -94,9 +94,7 @@ define_flag("enable_nccl_dynamic_check", False, "")
 # product-specific switches
 define_flag("use_fused_comm", True, "use in-kernel NVLink collectives where available; 0 = NCCL-only baseline path")
 define_flag("use_native_kernels", True, "use hand-written sm_100a kernels; 0 = torch composition (oracle)")
-define_flag("stage3_nvl_transport", False, "GroupSharded stage 3: move parameters/gradients with the NVLink symmetric-memory kernels (K3 push all-gather, pull reduce-scatter) instead of NCCL")
-define_flag("gemm_rs_pull", True, "K6/K4: GEMM writes its partial product into symmetric memory and owners pull-reduce through the switch (False: epilogue pushes tiles to the owners)")
-define_flag("ag_gemm_push", True, "K5: gather the sequence shards with one multicast push, then run the CTA-pair GEMM locally (False: GEMM reads peer tiles in place)")
+define_flag("stage3_nvl_transport", True, "GroupSharded stage 3: move parameters/gradients with the NVLink symmetric-memory kernels (K3 push all-gather, pull reduce-scatter) instead of NCCL")
 define_flag("gemm_cta_pair", True, "use the CTA-pair (cta_group::2, 256x256 tile) GEMM kernel for large shapes")
 define_flag("use_tcgen05_gemm", True, "route Linear GEMMs through the tcgen05/TMA kernel when shapes allow")
 define_flag("comm_watchdog_timeout_ms", 1800000, "")

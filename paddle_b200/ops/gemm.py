@@ -1,5 +1,6 @@
-"""tcgen05 / TMA GEMM entry (K23/K13).  Until the kernel library exports ``pdb200_gemm_bf16`` the dispatcher
-reports "unsupported" and Linear uses cuBLAS; see csrc/kernels/gemm_tc.cu."""
+"""tcgen05 / TMA GEMM entry (K23/K13): dispatch between the CTA-pair kernel (csrc/kernels/gemm_tc2.cu, 256x256 tiles)
+and the single-CTA kernel (gemm_tc.cu, 128xBN tiles).  ``supported`` is the shape / layout gate Linear consults;
+unsupported shapes go to cuBLAS through torch.matmul."""
 from __future__ import annotations
 
 import torch
@@ -30,13 +31,17 @@ def supported(a, b, trans_a=False, trans_b=False, accum_into=None) -> bool:
         a.data_ptr() % 16 == 0 and b.data_ptr() % 16 == 0
 
 
-def gemm(a, b, trans_a=False, trans_b=False, out_dtype=None, accum_into=None, bias=None, act=None):
-    """C[M,N] = op(A) @ op(B) with A,B bf16 row-major storage.  accum_into: fp32 C += (K13)."""
+def gemm(a, b, trans_a=False, trans_b=False, out_dtype=None, accum_into=None, bias=None, act=None, out=None):
+    """C[M,N] = op(A) @ op(B) with A,B bf16 row-major storage.  accum_into: fp32 C += (K13).  out: preallocated
+    contiguous [M,N] bf16 / fp32 result buffer."""
     M, K = (a.shape[1], a.shape[0]) if trans_a else a.shape
     N = b.shape[0] if trans_b else b.shape[1]
     if accum_into is not None:
         out = accum_into
         out_code, beta = 0, 1.0
+    elif out is not None:
+        assert out.is_contiguous() and out.numel() == M * N and out.dtype in (torch.bfloat16, torch.float32)
+        out_code, beta = (0 if out.dtype == torch.float32 else 1), 0.0
     else:
         od = out_dtype or torch.bfloat16
         out = torch.empty(M, N, dtype=od, device=a.device)

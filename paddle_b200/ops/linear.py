@@ -13,12 +13,14 @@ from ..framework.flags import flag
 from . import gemm as _gemm
 
 
-def _mm(a, b, trans_a=False, trans_b=False, out_dtype=None, accum_into=None):
-    """2-D GEMM dispatcher; accum_into (fp32) += result when given."""
+def _mm(a, b, trans_a=False, trans_b=False, out_dtype=None, accum_into=None, out=None):
+    """2-D GEMM dispatcher; accum_into (fp32) += result when given; ``out``: preallocated contiguous result."""
     if a.is_cuda and flag("use_tcgen05_gemm") and _gemm.supported(a, b, trans_a, trans_b, accum_into):
-        return _gemm.gemm(a, b, trans_a, trans_b, out_dtype=out_dtype, accum_into=accum_into)
+        return _gemm.gemm(a, b, trans_a, trans_b, out_dtype=out_dtype, accum_into=accum_into, out=out)
     A = a.t() if trans_a else a
     B = b.t() if trans_b else b
+    if out is not None:
+        return torch.matmul(A, B, out=out)
     if accum_into is not None:
         if accum_into.dtype == A.dtype:
             accum_into.addmm_(A, B)
@@ -54,7 +56,13 @@ class _LinearFn(torch.autograd.Function):
                 _mm(x2, dy2, trans_a=True, accum_into=mg)
                 dw = None
             else:
-                dw = _mm(x2, dy2, trans_a=True)
+                # a sharding wrapper may name the landing buffer of this gradient (ZeRO-3 gradient stage in symmetric
+                # memory): the GEMM writes there and autograd adopts a fresh alias of it - no staging copy
+                dst = getattr(ctx.wref, "_grad_dst", None)
+                if dst is not None and dst.dtype == dy2.dtype and tuple(dst.shape) == (x2.shape[1], dy2.shape[1]):
+                    dw = _mm(x2, dy2, trans_a=True, out=dst).view(dst.shape)
+                else:
+                    dw = _mm(x2, dy2, trans_a=True)
         db = dy2.sum(0) if (ctx.has_b and ctx.needs_input_grad[2]) else None
         return dx, dw, db
 

@@ -144,8 +144,11 @@ class Optimizer:
                 # global-norm clip folded into the update kernel: one multi-tensor L2-norm launch, the coefficient
                 # stays on the device and multiplies the gradients inside the AdamW kernel (no pass over the grads)
                 clip = self._grad_clip
-                grads = [g for p, g in params_grads if getattr(p, "need_clip", True)]
-                coef = clip.clip_coef(clip.global_norm_sq(grads))
+                if hasattr(clip, "fold_coef"):          # sharded clip: its own (collective) coefficient
+                    coef = clip.fold_coef(params_grads)
+                else:
+                    grads = [g for p, g in params_grads if getattr(p, "need_clip", True)]
+                    coef = clip.clip_coef(clip.global_norm_sq(grads))
                 prev = self._grad_scale_dev
                 self._grad_scale_dev = coef if prev is None else prev * coef
                 folded = True
@@ -163,7 +166,8 @@ class Optimizer:
 
     def _can_fold_clip(self, params_grads):
         from ..nn.clip import ClipGradByGlobalNorm
-        return (type(self._grad_clip) is ClipGradByGlobalNorm and getattr(self, "_fold_clip_ok", False) and bool(params_grads)
+        return ((type(self._grad_clip) is ClipGradByGlobalNorm or hasattr(self._grad_clip, "fold_coef"))
+                and getattr(self, "_fold_clip_ok", False) and bool(params_grads)
                 and all(self._native(p) and getattr(p, "need_clip", True) for p, _ in params_grads))
 
     def _update(self, params_grads):

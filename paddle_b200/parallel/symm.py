@@ -1,9 +1,11 @@
 """Symmetric-memory communication layer.
 
-``SymmArena`` wraps the native arena (csrc/runtime/symm.cc: cuMemCreate + POSIX-FD exchange + peer mappings + NVLS
-multicast) for one process group: a bump allocator hands out byte offsets that are identical on every rank, torch
-tensors view the local mapping, and the fused kernels (csrc/kernels/nvl_*.cu) receive the array of peer base
-pointers plus the multicast pointer.  The first 4 KB of every arena is the signal pad used by the in-stream
+``SymmArena`` wraps the native arena (csrc/runtime/symm.cc: cuMemCreate + POSIX-FD exchange + peer mappings + an NVLS
+multimem window) for one process group: an allocator hands out byte offsets that are identical on every rank, torch
+tensors view the LOCAL mapping only, and the fused SIMT kernels (csrc/kernels/nvl_*.cu) receive the array of peer base
+pointers plus the NVLS pointer.  Peer mappings and the NVLS window are registered with the kernel library as foreign
+ranges: the tensor-core launchers (TMA tensor maps) refuse any operand inside them, so GEMM / attention operands are
+always this GPU's own memory.  The first 4 KB of every arena is the signal pad used by the in-stream
 cross-GPU barriers; epochs grow monotonically so the pad is never reset.
 
 Every fused path has its NCCL composition behind the same call signature; ``FLAGS_use_fused_comm`` (and
@@ -57,6 +59,13 @@ class SymmArena:
         self.peer_ptrs = (ctypes.c_uint64 * self.nranks)(*[rt.pdb200_symm_peer_ptr(self._h, p) for p in range(self.nranks)])
         self.mc_ptr = rt.pdb200_symm_multicast_ptr(self._h)
         self.local_ptr = self.peer_ptrs[self.rank]
+        # every mapping of somebody else's memory is off limits for TMA / tensor-core operands
+        self._foreign = [int(self.peer_ptrs[p]) for p in range(self.nranks) if p != self.rank]
+        if self.mc_ptr:
+            self._foreign.append(int(self.mc_ptr))
+        if lib.have_kernels():
+            for base in self._foreign:
+                lib.kernels.pdb200_register_foreign_range(base, self.nbytes)
         self._bytes = torch.as_tensor(_Blob(self.local_ptr, self.nbytes), device=f"cuda:{dev}")
         self._bytes[:PAD_BYTES].zero_()
         torch.cuda.synchronize()
@@ -102,6 +111,9 @@ class SymmArena:
     def close(self):
         if getattr(self, "_h", None):
             torch.cuda.synchronize()
+            if lib.have_kernels():
+                for base in self._foreign:
+                    lib.kernels.pdb200_unregister_foreign_range(base)
             self._rt.pdb200_symm_destroy(self._h)
             self._h = None
 
@@ -254,43 +266,45 @@ def _staging(arena, tag, shape, dtype):
     return t
 
 
+def _assert_local(arena, *tensors):
+    """Tensor-core operands must be this GPU's memory: arena tensors are views of the LOCAL mapping by construction
+    (SymmArena.tensor), anything else is ordinary device memory.  The native launchers re-check against the
+    registered foreign ranges."""
+    for t in tensors:
+        if t is None:
+            continue
+        p = t.data_ptr()
+        for base in arena._foreign:
+            assert not (base <= p < base + arena.nbytes), "tensor-core operand inside a mapping of another GPU's memory"
+
+
 def ag_gemm(x_shard, weight, group, bias=None, trans_b=False, act=None):
-    """K5: ``all_gather(x_shard, dim 0) @ weight`` without materialising the gathered activation: the GEMM's TMA
-    producer reads every peer's shard in place over NVLink.  x_shard: [rows, K] bf16; returns [nranks*rows, N]."""
+    """K5: ``all_gather(x_shard, dim 0) @ weight``.  Every rank pushes its shard into all ranks' gathered buffer
+    (NVLS ``multimem.st`` all-gather, one NVLink pass), and the CTA-pair tcgen05 GEMM reads the gathered activation
+    from LOCAL memory.  x_shard: [rows, K] bf16; returns [nranks*rows, N]."""
     from paddle_b200.lib import check
+    from paddle_b200.ops import gemm as G
     from paddle_b200.ops._util import ptr
     arena = get_arena(group)
     rows, K = x_shard.shape
-    N = weight.shape[0] if trans_b else weight.shape[1]
-    if flag("ag_gemm_push") and hasattr(lib.kernels.require(), "pdb200_nvl_allgather_from"):
-        # One NVLink pass: every rank multicasts its shard into all ranks' gathered buffer, then the CTA-pair GEMM
-        # runs on local memory.  (Reading peer tiles from inside the GEMM re-fetches each A tile once per N tile
-        # over NVLink - 15x the bytes for the 13B qkv projection - and was NVLink-bound.)
-        from paddle_b200.ops import gemm as G
-        full = _staging(arena, "ag_full", (rows * arena.nranks, K), torch.bfloat16)
-        xs = x_shard.contiguous()
-        check(lib.kernels.pdb200_nvl_allgather_from(arena.peers_arg, arena.mc_ptr, arena.nranks, arena.rank, ptr(xs),
-                                                    full._symm[1], xs.numel() * 2, 0, arena.next_epoch(), 0,
-                                                    stream_ptr(xs.device)), "nvl_allgather_from")
-        if G.supported(full, weight, False, trans_b):
-            return G.gemm(full, weight, False, trans_b, bias=bias, act=act)
-        out = torch.matmul(full, weight.t() if trans_b else weight)
-        if bias is not None:
-            out = out + bias
-        return {"gelu": torch.nn.functional.gelu, "relu": torch.relu}.get(act, lambda t: t)(out)
-    buf = _staging(arena, "ag_a", (rows, K), torch.bfloat16)
-    buf.copy_(x_shard)
-    out = torch.empty(rows * arena.nranks, N, dtype=torch.bfloat16, device=x_shard.device)
-    check(lib.kernels.pdb200_gemm_bf16_ag(arena.peers_arg, arena.nranks, arena.rank, buf._symm[1], rows, ptr(weight),
-                                          ptr(out), ptr(bias), N, K, int(trans_b),
-                                          {"none": 0, None: 0, "gelu": 1, "relu": 2}[act], 0, arena.next_epoch(),
-                                          stream_ptr(x_shard.device)), "gemm_bf16_ag")
-    return out
+    full = _staging(arena, "ag_full", (rows * arena.nranks, K), torch.bfloat16)
+    xs = x_shard.contiguous()
+    check(lib.kernels.pdb200_nvl_allgather_from(arena.peers_arg, arena.mc_ptr, arena.nranks, arena.rank, ptr(xs),
+                                                full._symm[1], xs.numel() * 2, 0, arena.next_epoch(), 0,
+                                                stream_ptr(xs.device)), "nvl_allgather_from")
+    _assert_local(arena, full, weight)
+    if G.supported(full, weight, False, trans_b):
+        return G.gemm(full, weight, False, trans_b, bias=bias, act=act)
+    out = torch.matmul(full, weight.t() if trans_b else weight)
+    if bias is not None:
+        out = out + bias
+    return {"gelu": torch.nn.functional.gelu, "relu": torch.relu}.get(act, lambda t: t)(out)
 
 
 def gemm_rs(x, weight, group, trans_b=False):
-    """K6: ``reduce_scatter(x @ weight, dim 0)``: partial tiles go straight from TMEM to the owner rank's staging slab
-    over NVLink while the remaining tiles are still being computed.  x: [nranks*rows, K] bf16; returns [rows, N]."""
+    """K6: ``reduce_scatter(x @ weight, dim 0)``.  The CTA-pair GEMM writes its partial product into (local)
+    symmetric memory; every owner then pulls its rows through the switch (``multimem.ld_reduce`` adds the n copies in
+    flight).  x: [nranks*rows, K] bf16; returns [rows, N]."""
     from paddle_b200.lib import check
     from paddle_b200.ops._util import ptr
     arena = get_arena(group)
@@ -298,63 +312,37 @@ def gemm_rs(x, weight, group, trans_b=False):
     n = arena.nranks
     rows = M // n
     N = weight.shape[0] if trans_b else weight.shape[1]
-    if flag("gemm_rs_pull") and hasattr(lib.kernels.require(), "pdb200_nvl_rs_sum_bf16"):
-        # CTA-pair GEMM writes the partial product into symmetric memory; every owner then pulls its rows through the
-        # switch (multimem.ld_reduce adds the n copies in flight).  Measured faster than pushing tiles from the epilogue.
-        part = _gemm_into_symmetric(arena, x, weight, trans_b, "rs_part")
-        out = torch.empty(rows, N, dtype=torch.bfloat16, device=x.device)
-        check(lib.kernels.pdb200_nvl_rs_sum_bf16(arena.peers_arg, arena.mc_ptr, n, arena.rank, part._symm[1],
-                                                 arena.rank * rows * N, rows * N, ptr(out), 0, arena.next_epoch(),
-                                                 stream_ptr(x.device)), "nvl_rs_sum_bf16")
-        return out
-    stage = _staging(arena, "rs_stage", (n, rows, N), torch.bfloat16)
+    part = _gemm_into_symmetric(arena, x, weight, trans_b, "rs_part")
     out = torch.empty(rows, N, dtype=torch.bfloat16, device=x.device)
-    xc = x.contiguous()
-    check(lib.kernels.pdb200_gemm_bf16_rs(arena.peers_arg, n, arena.rank, ptr(xc), ptr(weight), stage._symm[1], ptr(out),
-                                          rows, N, K, int(trans_b), 0, arena.next_epoch(), stream_ptr(x.device)),
-          "gemm_bf16_rs")
+    check(lib.kernels.pdb200_nvl_rs_sum_bf16(arena.peers_arg, arena.mc_ptr, n, arena.rank, part._symm[1],
+                                             arena.rank * rows * N, rows * N, ptr(out), 0, arena.next_epoch(),
+                                             stream_ptr(x.device)), "nvl_rs_sum_bf16")
     return out
 
 
 def _gemm_into_symmetric(arena, x, weight, trans_b, tag):
-    """x @ weight written straight into a symmetric staging buffer by the tcgen05 GEMM (no copy)."""
+    """x @ weight written straight into a (local) symmetric staging buffer by the tcgen05 GEMM (no copy)."""
     from paddle_b200.lib import check
     from paddle_b200.ops._util import ptr
     M, K = x.shape
     N = weight.shape[0] if trans_b else weight.shape[1]
     part = _staging(arena, tag, (M, N), torch.bfloat16)
     xc = x.contiguous()
-    fn = lib.kernels.pdb200_gemm_bf16_pair if (M >= 512 and N >= 512 and flag("gemm_cta_pair") and
-                                               hasattr(lib.kernels.require(), "pdb200_gemm_bf16_pair")) \
+    _assert_local(arena, xc, weight, part)
+    fn = lib.kernels.pdb200_gemm_bf16_pair if (M >= 512 and N >= 512 and flag("gemm_cta_pair")) \
         else lib.kernels.pdb200_gemm_bf16
     check(fn(ptr(xc), ptr(weight), ptr(part), None, M, N, K, 0, int(trans_b), 1, 0.0, 0, stream_ptr(x.device)), "gemm_bf16")
     return part
 
 
 def gemm_ar(x, weight, group, trans_b=False):
-    """K4: ``all_reduce(x @ weight)`` for the non-sequence-parallel TP linears: K6's tile push to the owner of each
-    row block, then every owner folds its rows and stores the sum into all ranks' outputs.  x: [M, K] bf16 with
-    M a multiple of nranks*128; returns a private [M, N] copy."""
-    from paddle_b200.lib import check
-    from paddle_b200.ops._util import ptr
+    """K4: ``all_reduce(x @ weight)`` for the non-sequence-parallel TP linears: the GEMM writes its partial product
+    into symmetric memory and the NVLS two-shot all-reduce (K1) sums it in place.  x: [M, K] bf16; returns a private
+    [M, N] copy (the staging buffer is reused by the next call of the same shape)."""
     arena = get_arena(group)
-    M, K = x.shape
-    n = arena.nranks
-    rows = M // n
-    N = weight.shape[0] if trans_b else weight.shape[1]
-    if flag("gemm_rs_pull"):
-        part = _gemm_into_symmetric(arena, x, weight, trans_b, "ar_part")
-        allreduce_(part)                       # K1: NVLS two-shot all-reduce in place
-        return part.clone()
-    stage = _staging(arena, "rs_stage", (n, rows, N), torch.bfloat16)
-    out = _staging(arena, "ar_out", (M, N), torch.bfloat16)
-    xc = x.contiguous()
-    e = arena.next_epoch()
-    arena.next_epoch()                       # the entry point uses three consecutive epochs
-    check(lib.kernels.pdb200_gemm_bf16_ar(arena.peers_arg, n, arena.rank, ptr(xc), ptr(weight), stage._symm[1],
-                                          out._symm[1], rows, N, K, int(trans_b), 0, e, stream_ptr(x.device)),
-          "gemm_bf16_ar")
-    return out.clone()
+    part = _gemm_into_symmetric(arena, x, weight, trans_b, "ar_part")
+    allreduce_(part)
+    return part.clone()
 
 
 def vocab_embed(ids, weight, where):
@@ -396,7 +384,7 @@ def make_symmetric(param, group):
 def fused_gemm_ok(group, rows_per_rank, K, N, dtype, weight=None):
     if not (dtype == torch.bfloat16 and rows_per_rank % 128 == 0 and K % 64 == 0 and N % 64 == 0 and available(group)):
         return False
-    if not hasattr(lib.kernels.require(), "pdb200_gemm_bf16_ag"):
+    if not hasattr(lib.kernels.require(), "pdb200_nvl_allgather_from"):
         return False
     try:
         arena = get_arena(group)
