@@ -12,6 +12,8 @@
 //                             all-reduces, c_softmax_with_cross_entropy_op.cu:211-314).
 // Cross-GPU ordering uses system-scope flag barriers on a signal pad inside the segment (nvl.cuh).  When the fabric
 // has no multicast support the same kernels fall back to peer loads/stores (P2P two-shot).
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "nvl.cuh"
 
@@ -360,29 +362,39 @@ __global__ void __launch_bounds__(256) vocab_embed_gather_kernel(Peers P, uint64
 constexpr int kMaxSegs = 16;
 struct AgSeg { uint64_t src_off, dst_off; int64_t nvec; };      // nvec 16-byte vectors per rank shard
 struct AgSegs { AgSeg s[kMaxSegs]; int n; };
-__global__ void __launch_bounds__(512) allgather_multi_kernel(Peers P, AgSegs S, uint64_t pad_off, uint32_t epoch,
+__global__ void __launch_bounds__(256, 2) allgather_multi_kernel(Peers P, AgSegs S, uint64_t pad_off, uint32_t epoch,
                                                              unsigned long long spin_limit) {
   grid_barrier_begin(P, pad_off, epoch, spin_limit);         // every rank may have its gathered buffer overwritten
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  constexpr int U = 8;                                       // 128 B per thread in flight
   for (int k = 0; k < S.n; ++k) {
     const uint4* src = reinterpret_cast<const uint4*>(P.ptr[P.rank] + S.s[k].src_off);
     const int64_t nvec = S.s[k].nvec;
     const uint64_t dst0 = S.s[k].dst_off + (uint64_t)P.rank * (uint64_t)nvec * 16;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += 4 * stride) {
-      uint4 v[4];
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += U * stride) {
+      uint4 v[U];
 #pragma unroll
-      for (int u = 0; u < 4; ++u)
-        if (i + u * stride < nvec) v[u] = src[i + u * stride];
+      for (int u = 0; u < U; ++u)
+        if (i + u * stride < nvec) v[u] = __ldcs(src + i + u * stride);
+      if (P.mc) {
+        // NVLS: one store per vector, the switch replicates it into every rank's buffer (this one included)
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int64_t j = i + u * stride;
-        if (j >= nvec) break;
-        const uint64_t off = dst0 + (uint64_t)j * 16;
-        if (P.mc) {
-          uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
-          mm_st_b32x4(reinterpret_cast<void*>(P.mc + off), w);
-        } else {
-          for (int p = 0; p < P.nranks; ++p) *reinterpret_cast<uint4*>(P.ptr[(P.rank + p) % P.nranks] + off) = v[u];
+        for (int u = 0; u < U; ++u) {
+          const int64_t j = i + u * stride;
+          if (j < nvec) {
+            uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+            mm_st_b32x4(reinterpret_cast<void*>(P.mc + dst0 + (uint64_t)j * 16), w);
+          }
+        }
+      } else {
+        // P2P: the local copy stays on this GPU, one store per peer crosses NVLink (no loop back through the switch)
+        for (int p = 0; p < P.nranks; ++p) {
+          uint8_t* base = reinterpret_cast<uint8_t*>(P.ptr[(P.rank + p) % P.nranks] + dst0);
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const int64_t j = i + u * stride;
+            if (j < nvec) *reinterpret_cast<uint4*>(base + (uint64_t)j * 16) = v[u];
+          }
         }
       }
     }
@@ -391,77 +403,156 @@ __global__ void __launch_bounds__(512) allgather_multi_kernel(Peers P, AgSegs S,
 }
 
 // Reduce-scatter of a unit: segment k is a padded gradient [nranks * shard_numel] (G = bf16 or fp32) staged at stage_off
-// of every rank's segment; this rank's shard is summed over the ranks (in the switch with NVLS), scaled and written -
-// or, with accumulate, added - to its local fp32 accumulator `out` (the optimizer's main_grad slice).
+// of every rank's segment; this rank's shard is summed over the ranks (in the switch with NVLS, by peer loads without),
+// scaled and written - or, with accumulate, added - to its local fp32 accumulator `out` (the optimizer's main_grad
+// slice).  U independent 16-byte loads per thread are in flight before the first is consumed: the loads cross NVLink
+// (~2-3 us round trip), so bytes in flight, not CTAs, set the bandwidth.
 struct RsSeg { uint64_t stage_off; int64_t shard_numel; float* out; };
 struct RsSegs { RsSeg s[kMaxSegs]; int n; };
+
+template <typename G> struct RsTraits;
+template <> struct RsTraits<__nv_bfloat16> { static constexpr int kElems = 8; };   // per 16-byte vector
+template <> struct RsTraits<float> { static constexpr int kElems = 4; };
+
+template <typename G> __device__ __forceinline__ void rs_unpack(const uint4& r, float* g);
+template <> __device__ __forceinline__ void rs_unpack<__nv_bfloat16>(const uint4& r, float* g) {
+  const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&w[j]);
+    g[2 * j] = __low2float(h);
+    g[2 * j + 1] = __high2float(h);
+  }
+}
+template <> __device__ __forceinline__ void rs_unpack<float>(const uint4& r, float* g) {
+  g[0] = __uint_as_float(r.x); g[1] = __uint_as_float(r.y); g[2] = __uint_as_float(r.z); g[3] = __uint_as_float(r.w);
+}
+__device__ __forceinline__ uint4 ld_peer_v4(const void* p) {       // streaming 16-byte load (peer or local)
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+
 template <typename G>
-__global__ void __launch_bounds__(512) reduce_scatter_multi_kernel(Peers P, RsSegs S, float scale, int accumulate,
-                                                                  uint64_t pad_off, uint32_t epoch,
-                                                                  unsigned long long spin_limit) {
+__device__ __forceinline__ void rs_store(float* __restrict__ o, const float* g, float scale, int accumulate) {
+  constexpr int E = RsTraits<G>::kElems;
+#pragma unroll
+  for (int e = 0; e < E; e += 4) {
+    float4 v = make_float4(g[e] * scale, g[e + 1] * scale, g[e + 2] * scale, g[e + 3] * scale);
+    if (accumulate) {
+      const float4 a = *reinterpret_cast<const float4*>(o + e);
+      v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
+    }
+    __stcs(reinterpret_cast<float4*>(o + e), v);
+  }
+}
+
+template <typename G>
+__global__ void __launch_bounds__(256, 2) reduce_scatter_multi_kernel(Peers P, RsSegs S, float scale, int accumulate,
+                                                                     uint64_t pad_off, uint32_t epoch,
+                                                                     unsigned long long spin_limit) {
   grid_barrier_begin(P, pad_off, epoch, spin_limit);         // every rank's staged gradients are complete
+  constexpr int E = RsTraits<G>::kElems;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int k = 0; k < S.n; ++k) {
-    const int64_t n8 = S.s[k].shard_numel / 8;
+    const int64_t nvec = S.s[k].shard_numel / E;
     float* __restrict__ out = S.s[k].out;
     const uint64_t base = S.s[k].stage_off + (uint64_t)P.rank * (uint64_t)S.s[k].shard_numel * sizeof(G);
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
-      float g[8];
-      if (sizeof(G) == 4) {
-        const uint64_t off = base + (uint64_t)i * 32;
-        if (P.mc) {
-          float t0[4], t1[4];
-          mm_ld_reduce_f32x4(reinterpret_cast<const void*>(P.mc + off), t0);
-          mm_ld_reduce_f32x4(reinterpret_cast<const void*>(P.mc + off + 16), t1);
+    if (P.mc) {
+      // NVLS: the switch returns the sum; 8 requests per thread in flight
+      constexpr int U = 8;
+      for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += U * stride) {
+        uint4 r[U];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            g[j] = t0[j];
-            g[4 + j] = t1[j];
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) g[j] = 0.f;
-          for (int p = 0; p < P.nranks; ++p) {
-            const float4 x0 = *reinterpret_cast<const float4*>(P.ptr[p] + off);
-            const float4 x1 = *reinterpret_cast<const float4*>(P.ptr[p] + off + 16);
-            g[0] += x0.x; g[1] += x0.y; g[2] += x0.z; g[3] += x0.w;
-            g[4] += x1.x; g[5] += x1.y; g[6] += x1.z; g[7] += x1.w;
+        for (int u = 0; u < U; ++u) {
+          const int64_t j = i + u * stride;
+          if (j < nvec) {
+            const void* a = reinterpret_cast<const void*>(P.mc + base + (uint64_t)j * 16);
+            if (sizeof(G) == 4) {
+              float t[4];
+              mm_ld_reduce_f32x4(a, t);
+              r[u] = make_uint4(__float_as_uint(t[0]), __float_as_uint(t[1]), __float_as_uint(t[2]), __float_as_uint(t[3]));
+            } else {
+              uint32_t t[4];
+              mm_ld_reduce_bf16x8(a, t);
+              r[u] = make_uint4(t[0], t[1], t[2], t[3]);
+            }
           }
         }
-      } else {
-        const uint64_t off = base + (uint64_t)i * 16;
-        if (P.mc) {
-          uint32_t r[4];
-          mm_ld_reduce_bf16x8(reinterpret_cast<const void*>(P.mc + off), r);
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&r[j]);
-            g[2 * j] = __low2float(h);
-            g[2 * j + 1] = __high2float(h);
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) g[j] = 0.f;
-          for (int p = 0; p < P.nranks; ++p) {
-            Vec<__nv_bfloat16> x;
-            x.load(reinterpret_cast<const __nv_bfloat16*>(P.ptr[p] + off));
-#pragma unroll
-            for (int j = 0; j < 8; ++j) g[j] += x.f(j);
+        for (int u = 0; u < U; ++u) {
+          const int64_t j = i + u * stride;
+          if (j < nvec) {
+            float g[E];
+            rs_unpack<G>(r[u], g);
+            rs_store<G>(out + j * E, g, scale, accumulate);
           }
         }
       }
-      float4 o0 = make_float4(g[0] * scale, g[1] * scale, g[2] * scale, g[3] * scale);
-      float4 o1 = make_float4(g[4] * scale, g[5] * scale, g[6] * scale, g[7] * scale);
-      if (accumulate) {
-        const float4 a0 = *reinterpret_cast<const float4*>(out + i * 8), a1 = *reinterpret_cast<const float4*>(out + i * 8 + 4);
-        o0.x += a0.x; o0.y += a0.y; o0.z += a0.z; o0.w += a0.w;
-        o1.x += a1.x; o1.y += a1.y; o1.z += a1.z; o1.w += a1.w;
+    } else if (P.nranks <= 4) {
+      // peer loads, up to 4 ranks: all ranks' copies of 4 vectors are requested before the first is consumed
+      constexpr int U = 4;
+      for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += U * stride) {
+        uint4 r[4][U];
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+          if (p < P.nranks) {
+            const uint8_t* src = reinterpret_cast<const uint8_t*>(P.ptr[(P.rank + p) % P.nranks] + base);
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+              const int64_t j = i + u * stride;
+              if (j < nvec) r[p][u] = ld_peer_v4(src + (uint64_t)j * 16);
+            }
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int64_t j = i + u * stride;
+          if (j >= nvec) continue;
+          float g[E];
+          rs_unpack<G>(r[0][u], g);
+#pragma unroll
+          for (int p = 1; p < 4; ++p) {
+            if (p < P.nranks) {
+              float t[E];
+              rs_unpack<G>(r[p][u], t);
+#pragma unroll
+              for (int e = 0; e < E; ++e) g[e] += t[e];
+            }
+          }
+          rs_store<G>(out + j * E, g, scale, accumulate);
+        }
       }
-      *reinterpret_cast<float4*>(out + i * 8) = o0;
-      *reinterpret_cast<float4*>(out + i * 8 + 4) = o1;
+    } else {
+      // peer loads, more than 4 ranks and no NVLS: one vector at a time per rank pair (fallback, not tuned)
+      for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < nvec; j += stride) {
+        float g[E];
+#pragma unroll
+        for (int e = 0; e < E; ++e) g[e] = 0.f;
+        for (int p = 0; p < P.nranks; ++p) {
+          float t[E];
+          rs_unpack<G>(ld_peer_v4(reinterpret_cast<const uint8_t*>(P.ptr[(P.rank + p) % P.nranks] + base) + (uint64_t)j * 16), t);
+#pragma unroll
+          for (int e = 0; e < E; ++e) g[e] += t[e];
+        }
+        rs_store<G>(out + j * E, g, scale, accumulate);
+      }
     }
   }
   grid_barrier_end(P, pad_off, epoch + 1, spin_limit);       // every rank has pulled: the stages may be rewritten
+}
+
+// NVLS or plain peer access?  An all-gather through the switch loops this rank's own shard back over NVLink and a
+// switch reduction pulls every rank's full buffer out of its memory, so with few ranks peer loads / stores move
+// fewer bytes; with many ranks the switch saves (n-1)x the store / load instructions and, for the reduction, the
+// ingress.  PDB200_NVL_P2P_MAX_RANKS (default 4): groups up to this size use peer access.
+static int p2p_max_ranks() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("PDB200_NVL_P2P_MAX_RANKS");
+    v = e ? atoi(e) : 4;
+  }
+  return v;
 }
 
 static Peers make_peers(const uint64_t* ptrs, uint64_t mc, int nranks, int rank) {
@@ -700,11 +791,11 @@ PDB_EXPORT int pdb200_nvl_allgather_multi(const uint64_t* peer_ptrs, uint64_t mc
     S.s[k] = AgSeg{(uint64_t)so, (uint64_t)dof, nb / 16};
     if (nb / 16 > most) most = nb / 16;
   }
-  Peers P = make_peers(peer_ptrs, mc_ptr, nranks, rank);
+  Peers P = make_peers(peer_ptrs, nranks > p2p_max_ranks() ? mc_ptr : 0, nranks, rank);
   int64_t blocks = (most + 2047) / 2048;
   const int64_t cap = max_ctas > 0 ? max_ctas : (int64_t)sm_count();
   if (blocks > cap) blocks = cap;
-  allgather_multi_kernel<<<(unsigned)(blocks < 1 ? 1 : blocks), 512, 0, (cudaStream_t)stream>>>(P, S, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+  allgather_multi_kernel<<<(unsigned)(blocks < 1 ? 1 : blocks), 256, 0, (cudaStream_t)stream>>>(P, S, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
   return check_launch("nvl_allgather_multi");
 }
 
@@ -723,17 +814,17 @@ PDB_EXPORT int pdb200_nvl_reduce_scatter_multi(const uint64_t* peer_ptrs, uint64
     PDB_REQUIRE(ne >= 0 && ne % 8 == 0 && so % 16 == 0 && ((uintptr_t)out & 15) == 0 && out != nullptr,
                 "nvl_reduce_scatter_multi: segment %d: shard must be a multiple of 8 elements, 16-byte aligned", k);
     S.s[k] = RsSeg{(uint64_t)so, ne, out};
-    if (ne / 8 > most) most = ne / 8;
+    if (ne / (grad_dtype == PDB_DTYPE_F32 ? 4 : 8) > most) most = ne / (grad_dtype == PDB_DTYPE_F32 ? 4 : 8);
   }
-  Peers P = make_peers(peer_ptrs, mc_ptr, nranks, rank);
-  int64_t blocks = (most + 511) / 512;
+  Peers P = make_peers(peer_ptrs, nranks > p2p_max_ranks() ? mc_ptr : 0, nranks, rank);
+  int64_t blocks = (most + 2047) / 2048;
   const int64_t cap = max_ctas > 0 ? max_ctas : (int64_t)sm_count();
   if (blocks > cap) blocks = cap;
   const unsigned grid = (unsigned)(blocks < 1 ? 1 : blocks);
   cudaStream_t st = (cudaStream_t)stream;
   if (grad_dtype == PDB_DTYPE_F32)
-    reduce_scatter_multi_kernel<float><<<grid, 512, 0, st>>>(P, S, scale, accumulate, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+    reduce_scatter_multi_kernel<float><<<grid, 256, 0, st>>>(P, S, scale, accumulate, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
   else
-    reduce_scatter_multi_kernel<__nv_bfloat16><<<grid, 512, 0, st>>>(P, S, scale, accumulate, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+    reduce_scatter_multi_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(P, S, scale, accumulate, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
   return check_launch("nvl_reduce_scatter_multi");
 }

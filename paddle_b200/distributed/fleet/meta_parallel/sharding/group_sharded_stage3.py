@@ -78,10 +78,12 @@ class _NvlTransport:
         total = slice_bytes + (self.SLOTS + self.GSTAGES) * self.slot_bytes + (8 << 20)
         self.arena = symm.SymmArena(group, total)
         self.stream = torch.cuda.Stream(device=device, priority=-1)
-        # grid caps of the transport kernels (CTAs of 512 threads); few CTAs already saturate the links
-        self.ag_ctas = int(os.environ.get("PDB200_STAGE3_AG_CTAS", "32"))
-        self.rs_ctas = int(os.environ.get("PDB200_STAGE3_RS_CTAS", "32"))
-        self.noop = bool(int(os.environ.get("PDB200_STAGE3_COMM_NOOP", "0")))   # timing experiments only
+        # grid caps of the transport kernels (CTAs of 256 threads, 32 KB in flight each, <= 32 K registers so that
+        # they co-reside with a GEMM CTA): bytes in flight, not CTAs, set the link bandwidth
+        self.ag_ctas = int(os.environ.get("PDB200_STAGE3_AG_CTAS", "64"))
+        self.rs_ctas = int(os.environ.get("PDB200_STAGE3_RS_CTAS", "64"))
+        # timing experiments only: skip the transport kernels ("ag", "rs" or "all"); numerics become garbage
+        self.noop = {"0": "", "1": "all"}.get(os.environ.get("PDB200_STAGE3_COMM_NOOP", ""), os.environ.get("PDB200_STAGE3_COMM_NOOP", ""))
         self.slots = None
         self.slot_owner = [None] * self.SLOTS
         self.next_slot = 0
@@ -104,20 +106,11 @@ class _NvlTransport:
         t._symm = (arena, off + byte_off)
         return t
 
-    def _launch(self, fn_name, segs, *tail):
-        import ctypes
-        from paddle_b200.lib import check
-        a = self.arena
-        k = self.symm.lib.kernels
-        fn = getattr(k, fn_name)
-        for i in range(0, len(segs), 16):
-            chunk = segs[i:i + 16]
-            flat = (ctypes.c_int64 * (3 * len(chunk)))(*[int(v) for s in chunk for v in s])
-            check(fn(a.peers_arg, a.mc_ptr, a.nranks, a.rank, ctypes.cast(flat, ctypes.c_void_p), len(chunk), *tail[:-2],
-                     0, a.next_epoch(), *tail[-2:]), fn_name)
-
     def gather(self, unit):
         slot = None
+        for c in range(self.SLOTS):                 # a unit occupies one slot: forget where it was gathered before
+            if self.slot_owner[c] is unit:
+                self.slot_owner[c] = None
         for k in range(self.SLOTS):                 # next slot whose occupant has been released
             c = (self.next_slot + k) % self.SLOTS
             prev = self.slot_owner[c]
@@ -141,8 +134,8 @@ class _NvlTransport:
             off += self.al(p._gs_padded * p.element_size())
         with torch.cuda.stream(self.stream):
             self.stream.wait_event(ev)
-            if not self.noop:
-                self._launch("pdb200_nvl_allgather_multi", segs, self.ag_ctas, self.stream.cuda_stream)
+            if self.noop not in ("ag", "all", True):
+                self.symm.allgather_multi(self.arena, segs, self.ag_ctas, self.stream.cuda_stream)
             done = torch.cuda.Event()
             done.record(self.stream)
         return fulls, done
@@ -172,12 +165,11 @@ class _NvlTransport:
         n = self.arena.nranks
         segs = [(p._grad_stage._symm[1], p._gs_padded // n, p.fw_storage.main_grad.data_ptr()) for p in unit.params
                 if p.requires_grad]
-        from paddle_b200.ops._util import dtype_code
         with torch.cuda.stream(self.stream):
             self.stream.wait_event(ev)
-            if not self.noop and segs:
-                self._launch("pdb200_nvl_reduce_scatter_multi", segs, dtype_code(unit.params[0]), 1.0 / n, int(accumulate),
-                             self.rs_ctas, self.stream.cuda_stream)
+            if self.noop not in ("rs", "all", True) and segs:
+                self.symm.reduce_scatter_multi(self.arena, segs, unit.params[0].dtype, 1.0 / n, accumulate, self.rs_ctas,
+                                               self.stream.cuda_stream)
             done = torch.cuda.Event()
             done.record(self.stream)
         self.gstage_free[unit.gstage] = done

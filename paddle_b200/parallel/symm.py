@@ -217,6 +217,32 @@ def all_gather_push(shard, full, max_ctas=0):
     return full
 
 
+def _multi(arena, fn_name, segs, mid, max_ctas, stream):
+    """Launch a multi-segment transport kernel, 16 segments per launch; each launch takes two pad epochs."""
+    from paddle_b200.lib import check
+    fn = getattr(lib.kernels, fn_name)
+    for i in range(0, len(segs), 16):
+        chunk = segs[i:i + 16]
+        flat = (ctypes.c_int64 * (3 * len(chunk)))(*[int(v) for seg in chunk for v in seg])
+        check(fn(arena.peers_arg, arena.mc_ptr, arena.nranks, arena.rank, ctypes.cast(flat, ctypes.c_void_p), len(chunk),
+                 *mid, 0, arena.next_epoch(), int(max_ctas), stream), fn_name)
+
+
+def allgather_multi(arena, segs, max_ctas=0, stream=None):
+    """One launch all-gathers several shards: segs = [(src_off, dst_off, shard_bytes), ...] (byte offsets inside the
+    arena, identical on all ranks); rank r's shard lands at ``dst_off + r * shard_bytes`` on every rank."""
+    st = stream if stream is not None else stream_ptr(torch.device("cuda", torch.cuda.current_device()))
+    _multi(arena, "pdb200_nvl_allgather_multi", segs, (), max_ctas, st)
+
+
+def reduce_scatter_multi(arena, segs, grad_dtype, scale, accumulate=False, max_ctas=0, stream=None):
+    """One launch reduce-scatters several staged buffers: segs = [(stage_off, shard_numel, out_ptr), ...];
+    ``out (+)= scale * sum over ranks of stage[rank * shard_numel : (rank + 1) * shard_numel]`` (fp32, local)."""
+    st = stream if stream is not None else stream_ptr(torch.device("cuda", torch.cuda.current_device()))
+    code = {torch.float32: 0, torch.bfloat16: 1}[grad_dtype]
+    _multi(arena, "pdb200_nvl_reduce_scatter_multi", segs, (code, float(scale), int(bool(accumulate))), max_ctas, st)
+
+
 def reduce_scatter_avg(grad_buf, shard_start, shard_numel, out, scratch):
     """AVG reduce-scatter of a symmetric gradient buffer into a local fp32 shard (no host sync, norm partials in
     ``scratch``, which must hold lib.kernels.pdb200_nvl_rs_grid(shard_numel) floats)."""
