@@ -32,7 +32,7 @@ constexpr int kBBytes = BNH * BK * 2;
 constexpr int kStageBytes = kABytes + kBBytes;
 constexpr int kTmemCols = 2 * BN;
 constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256;
-constexpr int kGroupM = 4;       // pair-tiles (256 rows) per rasterisation group
+static int g_group_m = 0;        // pair-tiles (256 rows) per rasterisation group; 0 = pick per shape (see launch)
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
@@ -73,11 +73,11 @@ __device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {      // arrive
                : "memory");
 }
 
-__device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int& m_blk, int& n_blk) {
-  const int per_group = kGroupM * num_n;
+__device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int group_m, int& m_blk, int& n_blk) {
+  const int per_group = group_m * num_n;
   const int group = tile / per_group;
-  const int first_m = group * kGroupM;
-  const int gsz = min(num_m - first_m, kGroupM);
+  const int first_m = group * group_m;
+  const int gsz = min(num_m - first_m, group_m);
   const int in_group = tile - group * per_group;
   m_blk = first_m + in_group % gsz;
   n_blk = in_group / gsz;
@@ -92,7 +92,7 @@ __device__ __forceinline__ float apply_act(float v, int act) {
 template <bool A_MN, bool B_MN, bool OUT_F32>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm_tc2_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b, void* __restrict__ Cptr,
-                const __nv_bfloat16* __restrict__ bias, int M, int N, int K, int64_t ldc, float beta, int act) {
+                const __nv_bfloat16* __restrict__ bias, int M, int N, int K, int64_t ldc, float beta, int act, int group_m) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);
@@ -142,7 +142,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant_
       uint32_t phase = 0;
       for (int tile = first_tile; tile < num_tiles; tile += tile_step) {
         int m_blk, n_blk;
-        tile_coords(tile, num_m, num_n, m_blk, n_blk);
+        tile_coords(tile, num_m, num_n, group_m, m_blk, n_blk);
         const int m0 = m_blk * (2 * BM) + (int)rank * BM;        // this CTA's rows
         const int n0 = n_blk * BN + (int)rank * BNH;             // this CTA's half of B
         for (int kb = 0; kb < num_k; ++kb) {
@@ -214,7 +214,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant_
     uint32_t acc_phase = 0;
     for (int tile = first_tile; tile < num_tiles; tile += tile_step) {
       int m_blk, n_blk;
-      tile_coords(tile, num_m, num_n, m_blk, n_blk);
+      tile_coords(tile, num_m, num_n, group_m, m_blk, n_blk);
       const int row = m_blk * (2 * BM) + (int)rank * BM + q * 32 + lane;
       const int n0 = n_blk * BN;
       mbar_wait(&tmem_full[acc], acc_phase);
@@ -312,7 +312,13 @@ static int launch(const void* a, const void* b, void* c, const void* bias, int M
   const int num_tiles = ((M + 2 * BM - 1) / (2 * BM)) * ((N + BN - 1) / BN);
   const int pairs = sm_count() / 2;
   const int grid = 2 * (num_tiles < pairs ? num_tiles : pairs);
-  kern<<<grid, kThreads, kSmemBytes, st>>>(tm_a, tm_b, c, (const __nv_bfloat16*)bias, M, N, K, (int64_t)N, beta, act);
+  // Raster: tiles walk down a band of group_m pair-rows, then step one tile column.  A band's A rows stay in L2 while B
+  // streams, so B is re-read from HBM once per band: the taller the band, the less HBM traffic (and power), as long
+  // as one wave (pairs tiles) still spans enough columns to keep its B tiles shared.  Default: about sqrt(pairs).
+  int group_m = g_group_m > 0 ? g_group_m : 8;
+  const int num_m = (M + 2 * BM - 1) / (2 * BM);
+  if (group_m > num_m) group_m = num_m;
+  kern<<<grid, kThreads, kSmemBytes, st>>>(tm_a, tm_b, c, (const __nv_bfloat16*)bias, M, N, K, (int64_t)N, beta, act, group_m);
   return check_launch("gemm_tc2");
 }
 
@@ -320,6 +326,11 @@ static int launch(const void* a, const void* b, void* c, const void* bias, int M
 }  // namespace pdb
 
 using namespace pdb;
+
+PDB_EXPORT int pdb200_gemm_set_group_m(int n) {     // tuning knob: raster band height of the CTA-pair kernel (0 = default)
+  pdb::tc2::g_group_m = n;
+  return 0;
+}
 
 // Same contract as pdb200_gemm_bf16 (gemm_tc.cu); 256 x 256 tiles on CTA pairs.
 PDB_EXPORT int pdb200_gemm_bf16_pair(const void* a, const void* b, void* c, const void* bias, int64_t M, int64_t N, int64_t K,

@@ -90,6 +90,13 @@ PDB_API int pdb200_gemm_bf16(const void* a, const void* b, void* c, const void* 
 /* Same contract, 256x256 output tiles computed by CTA pairs (tcgen05.mma.cta_group::2, cluster of 2). */
 PDB_API int pdb200_gemm_bf16_pair(const void* a, const void* b, void* c, const void* bias, int64_t M, int64_t N, int64_t K, int trans_a, int trans_b, int out_dtype, float beta, int act, void* stream);
 
+/* Same contract (beta must be 0 or 1): 256x512 blocks per CTA pair - two tcgen05 accumulators sharing A - with a
+ * swizzled-smem + TMA-store epilogue; fp32 C += is a TMA reduce-add (csrc/kernels/gemm_tc3.cu). */
+PDB_API int pdb200_gemm_bf16_macro(const void* a, const void* b, void* c, const void* bias, int64_t M, int64_t N, int64_t K, int trans_a, int trans_b, int out_dtype, float beta, int act, void* stream);
+PDB_API int pdb200_gemm_set_band(int n);
+/* Tuning knob: raster band height (in 256-row pair tiles) of the CTA-pair kernel; 0 restores the default. */
+PDB_API int pdb200_gemm_set_group_m(int n);
+
 /* Fused collectives over NVLink symmetric memory (K1, K2+K3, K8; csrc/kernels/nvl_collectives.cu).  peer_ptrs: host
  * array of nranks device addresses = every rank's segment as mapped in this process (pdb200_symm_peer_ptr), mc_ptr:
  * NVLS (multimem) mapping of the segment or 0 (P2P fallback).  *_off: byte offsets inside the segment, identical on all ranks.

@@ -94,6 +94,8 @@ define_flag("enable_nccl_dynamic_check", False, "")
 # product-specific switches
 define_flag("use_fused_comm", True, "use in-kernel NVLink collectives where available; 0 = NCCL-only baseline path")
 define_flag("use_native_kernels", True, "use hand-written sm_100a kernels; 0 = torch composition (oracle)")
+define_flag("gemm_macro_tile", True, "large bf16 GEMMs use the 256x512 macro-tile CTA-pair kernel with the TMA-store epilogue (gemm_tc3.cu)")
+define_flag("gemm_kernel", "", "force one GEMM kernel: macro | pair | single (empty: pick per shape)")
 define_flag("stage3_nvl_transport", True, "GroupSharded stage 3: move parameters/gradients with the NVLink symmetric-memory kernels (K3 push all-gather, pull reduce-scatter) instead of NCCL")
 define_flag("gemm_cta_pair", True, "use the CTA-pair (cta_group::2, 256x256 tile) GEMM kernel for large shapes")
 define_flag("use_tcgen05_gemm", True, "route Linear GEMMs through the tcgen05/TMA kernel when shapes allow")

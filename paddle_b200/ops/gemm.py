@@ -31,6 +31,19 @@ def supported(a, b, trans_a=False, trans_b=False, accum_into=None) -> bool:
         a.data_ptr() % 16 == 0 and b.data_ptr() % 16 == 0
 
 
+def _pick(M, N, K, beta):
+    """Kernel choice: "macro" (gemm_tc3: 256x512 blocks per CTA pair, TMA-store epilogue) for the large shapes,
+    "pair" (gemm_tc2: 256x256) and "single" (gemm_tc: 128xBN) below that."""
+    forced = flag("gemm_kernel")
+    if forced in ("macro", "pair", "single"):
+        return forced
+    if not flag("gemm_cta_pair") or M < 512 or N < 512:
+        return "single"
+    if flag("gemm_macro_tile") and beta in (0.0, 1.0) and hasattr(lib.kernels.require(), "pdb200_gemm_bf16_macro"):
+        return "macro"
+    return "pair"
+
+
 def gemm(a, b, trans_a=False, trans_b=False, out_dtype=None, accum_into=None, bias=None, act=None, out=None):
     """C[M,N] = op(A) @ op(B) with A,B bf16 row-major storage.  accum_into: fp32 C += (K13).  out: preallocated
     contiguous [M,N] bf16 / fp32 result buffer."""
@@ -46,10 +59,10 @@ def gemm(a, b, trans_a=False, trans_b=False, out_dtype=None, accum_into=None, bi
         od = out_dtype or torch.bfloat16
         out = torch.empty(M, N, dtype=od, device=a.device)
         out_code, beta = (0 if od == torch.float32 else 1), 0.0
-    # CTA-pair kernel (256x256 tiles) for the big shapes, single-CTA 128xBN kernel for small / skinny ones
-    fn = lib.kernels.pdb200_gemm_bf16
-    if flag("gemm_cta_pair") and M >= 512 and N >= 512 and hasattr(lib.kernels.require(), "pdb200_gemm_bf16_pair"):
-        fn = lib.kernels.pdb200_gemm_bf16_pair
+    kind = _pick(M, N, K, beta)
+    fn = {"macro": lib.kernels.pdb200_gemm_bf16_macro, "pair": lib.kernels.pdb200_gemm_bf16_pair,
+          "single": lib.kernels.pdb200_gemm_bf16}[kind] if kind != "macro" or hasattr(lib.kernels.require(), "pdb200_gemm_bf16_macro") \
+        else lib.kernels.pdb200_gemm_bf16_pair
     check(fn(ptr(a), ptr(b), ptr(out), ptr(bias), M, N, K, int(trans_a), int(trans_b), out_code, float(beta),
              {"none": 0, None: 0, "gelu": 1, "relu": 2}[act], stream_ptr(a.device)), "gemm_bf16")
     return out

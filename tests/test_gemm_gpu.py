@@ -113,3 +113,49 @@ def test_gemm_cta_pair_accumulate_and_epilogue():
     bias = torch.randn(N, device=DEV).bfloat16()
     out = G.gemm(x, w, bias=bias, act="gelu")
     torch.testing.assert_close(out.float(), torch.nn.functional.gelu(_ref(x, w, False, False) + bias.float()), rtol=2e-2, atol=5e-2)
+
+
+@pytest.mark.parametrize("ta,tb", [(False, False), (False, True), (True, False), (True, True)])
+@pytest.mark.parametrize("M,N,K", [(512, 512, 64), (512, 1024, 128), (640, 768, 320), (520, 1000, 200), (2048, 1536, 4096),
+                                   (4096, 2816, 512), (8192, 4096, 256)])
+def test_gemm_macro_tile_kernel(ta, tb, M, N, K):
+    """256x512 blocks per CTA pair with the TMA-store epilogue: full rounds, half-block tail rounds, partial blocks in
+    M and N (the TMA clips them), every operand major; against fp32 matmul."""
+    from paddle_b200.framework import flags
+    torch.manual_seed(M + N + K + 7)
+    a = (torch.randn((K, M) if ta else (M, K), device=DEV) * 0.5).bfloat16()
+    b = (torch.randn((N, K) if tb else (K, N), device=DEV) * 0.5).bfloat16()
+    flags.set_flags({"gemm_kernel": "macro"})
+    try:
+        out = torch.full((M, N), float("nan"), dtype=torch.bfloat16, device=DEV)
+        G.gemm(a, b, ta, tb, out=out)
+    finally:
+        flags.set_flags({"gemm_kernel": ""})
+    ref = _ref(a, b, ta, tb)
+    assert not torch.isnan(out.float()).any(), "part of C was never written"
+    torch.testing.assert_close(out.float(), ref, rtol=2e-2, atol=2e-2 * (K ** 0.5) * 0.25)
+
+
+def test_gemm_macro_tile_accumulate_bias_act():
+    from paddle_b200.framework import flags
+    torch.manual_seed(11)
+    M, N, K = 768, 1280, 512
+    a = torch.randn(K, M, device=DEV).bfloat16()
+    b = torch.randn(K, N, device=DEV).bfloat16()
+    acc = torch.randn(M, N, device=DEV)
+    ref = acc + _ref(a, b, True, False)
+    flags.set_flags({"gemm_kernel": "macro"})
+    try:
+        G.gemm(a, b, True, False, accum_into=acc)            # C += through the TMA reduce-add
+        G.gemm(a, b, True, False, accum_into=acc)
+        ref = ref + _ref(a, b, True, False)
+        torch.testing.assert_close(acc, ref, rtol=1e-3, atol=2e-2)
+        f32 = G.gemm(a, b, True, False, out_dtype=torch.float32)
+        torch.testing.assert_close(f32, _ref(a, b, True, False), rtol=1e-3, atol=1e-2)
+        x = (torch.randn(M, K, device=DEV) * 0.3).bfloat16()
+        w = (torch.randn(K, N, device=DEV) * 0.3).bfloat16()
+        bias = torch.randn(N, device=DEV).bfloat16()
+        out = G.gemm(x, w, bias=bias, act="gelu")
+    finally:
+        flags.set_flags({"gemm_kernel": ""})
+    torch.testing.assert_close(out.float(), torch.nn.functional.gelu(_ref(x, w, False, False) + bias.float()), rtol=2e-2, atol=5e-2)
