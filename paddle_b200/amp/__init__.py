@@ -86,6 +86,17 @@ def decorate(models, optimizers=None, level="O1", dtype="float16", master_weight
     return (models, optimizers)
 
 
+def _optimizer_chain(optimizer):
+    """The optimizer and every optimizer it wraps (HybridParallelOptimizer -> sharding -> base ...)."""
+    out, o, seen = [], optimizer, set()
+    while o is not None and id(o) not in seen:
+        seen.add(id(o))
+        out.append(o)
+        d = getattr(o, "__dict__", {})
+        o = d.get("_inner_opt") or d.get("_optim") or d.get("_inner_optimizer")
+    return out
+
+
 class GradScaler:
     def __init__(self, enable=True, init_loss_scaling=2.0 ** 16, incr_ratio=2.0, decr_ratio=0.5,
                  incr_every_n_steps=2000, decr_every_n_nan_or_inf=1, use_dynamic_loss_scaling=True):
@@ -119,7 +130,22 @@ class GradScaler:
     def unscale_(self, optimizer):
         if not self._enable or id(optimizer) in self._unscaled:
             return
+        # A sharding optimizer whose gradients are not reduced yet (ZeRO flat buffers) takes over: unscaling a local
+        # shard of an unreduced buffer would corrupt the reduction, so it unscales + checks the REDUCED shard in step().
+        defer = getattr(optimizer, "_amp_defer_unscale", None)
+        if defer is not None and defer(self):
+            self._unscaled.add(id(optimizer))
+            return
         grads = [g for _, g in optimizer._collect_params_grads()]
+        if not grads:
+            return
+        self._unscale_grads(grads)
+        self._sync_found_inf(optimizer)
+        self._unscaled.add(id(optimizer))
+
+    @torch.no_grad()
+    def _unscale_grads(self, grads):
+        """grads *= 1/scale in place; found_inf |= any non-finite value (device flag, no host sync)."""
         if not grads:
             return
         self._init_state(grads[0].device)
@@ -133,8 +159,6 @@ class GradScaler:
                 bad = ~torch.isfinite(g.float()).all()
                 self._found_inf.copy_(torch.maximum(self._found_inf, bad.float().reshape(1).to(self._found_inf.device)))
                 g.mul_(inv.to(g.dtype).to(g.device))
-        self._sync_found_inf(optimizer)
-        self._unscaled.add(id(optimizer))
 
     def _sync_found_inf(self, optimizer):
         """Hook for HybridParallelGradScaler: all-reduce MAX of found_inf across the check group."""
@@ -143,11 +167,14 @@ class GradScaler:
         if not self._enable:
             return optimizer.step()
         self.unscale_(optimizer)
-        optimizer._found_inf = self._found_inf
+        chain = _optimizer_chain(optimizer)      # wrappers forward reads, not writes: set the flag on every level
+        for o in chain:
+            o._found_inf = self._found_inf
         try:
             optimizer.step()
         finally:
-            optimizer._found_inf = None
+            for o in chain:
+                o._found_inf = None
         self._unscaled.discard(id(optimizer))
 
     def minimize(self, optimizer, *args, **kwargs):

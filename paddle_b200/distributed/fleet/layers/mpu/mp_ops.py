@@ -37,7 +37,9 @@ class _CIdentity(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy):
-        if ctx.skip or _nranks(ctx.group) == 1:
+        # ``skip_c_identity_dynamic`` only drops the forward identity op (a no-op view here); the gradient of the
+        # replicated input is ALWAYS summed over the group (reference mp_ops.py c_identity_eager.backward)
+        if _nranks(ctx.group) == 1:
             return dy, None, None
         dy = dy.contiguous().clone() if not dy.is_contiguous() else dy.clone()
         comm.all_reduce(dy, ReduceOp.SUM, ctx.group)
@@ -54,7 +56,9 @@ class _MpAllReduce(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, group, skip):
         ctx.group = group
-        if skip or _nranks(group) == 1:
+        # the forward all-reduce is unconditional; ``skip_c_identity_dynamic`` only drops the identity op of the
+        # backward pass, which is already a pass-through here (reference mp_ops.py mp_allreduce_eager)
+        if _nranks(group) == 1:
             return x.view_as(x)
         out = x.contiguous().clone()
         comm.all_reduce(out, ReduceOp.SUM, group)

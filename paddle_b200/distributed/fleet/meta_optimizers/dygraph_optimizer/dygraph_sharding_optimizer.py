@@ -117,8 +117,22 @@ class DygraphShardingOptimizer:
 
     clear_gradients = clear_grad
 
+    def _amp_defer_unscale(self, scaler):
+        """GradScaler.unscale_ hook: gradients are reduced to their owner in ``reduce_gradients`` after
+        ``scaler.step`` called ``unscale_``; unscaling only the owned ones before that would mix scaled and unscaled
+        contributions.  ``step`` unscales + checks the owned, reduced gradients instead."""
+        self.__dict__["_amp_scaler"] = scaler
+        return True
+
     @torch.no_grad()
     def step(self):
+        scaler = self.__dict__.pop("_amp_scaler", None)
+        if scaler is not None:
+            grads = [g for g in (_grad_of(p) for p in self._rank2params[self._sharding_rank]) if g is not None]
+            scaler._unscale_grads(grads)
+            if scaler._found_inf is not None:
+                comm.all_reduce(scaler._found_inf, ReduceOp.MAX, self._group)
+            scaler._sync_found_inf(self)
         # gradients of parameters owned elsewhere are not needed for the update
         self._inner_opt.step()
         self._sharding_sync_parameters()
@@ -298,19 +312,35 @@ class DygraphShardingOptimizerV2:
             if t is not None:
                 t.wait()
 
+    def _amp_defer_unscale(self, scaler):
+        """GradScaler.unscale_ hook: when ``scaler.step`` runs, the flat gradient buffers still hold this rank's
+        unreduced gradients (the reduce-scatter happens in ``reduce_gradients`` / the fused kernel).  Remember the
+        scaler; ``step`` unscales and checks the reduced shard instead."""
+        self.__dict__["_amp_scaler"] = scaler
+        return True
+
     @torch.no_grad()
     def step(self):
+        scaler = self.__dict__.pop("_amp_scaler", None)
         if getattr(self, "_fused_pending", False):
-            self._fused_step()
+            self._fused_step(scaler)
             self._fused_pending = False
             return
+        if scaler is not None:
+            grads = [g for g in (_grad_of(sp) for sp in self._slice_params) if g is not None]
+            scaler._unscale_grads(grads)
+            if scaler._found_inf is not None:
+                comm.all_reduce(scaler._found_inf, ReduceOp.MAX, self._group)
+            scaler._sync_found_inf(self)
         self._inner_opt.step()
         self._sharding_sync_parameters()
 
     @torch.no_grad()
-    def _fused_step(self):
+    def _fused_step(self, scaler=None):
         """K2+K3 over NVLink: no clip -> ONE kernel per buffer (reduce-scatter + AdamW + all-gather); with a
-        global-norm clip (or a dp axis) -> reduce-scatter+norm kernel, scalar exchange, AdamW+all-gather kernel."""
+        global-norm clip, a dp axis or a loss scaler -> reduce-scatter+norm kernel, scalar exchange, AdamW+all-gather
+        kernel.  With a scaler the squared norm of the reduced (still scaled) shard doubles as the inf/nan check, and
+        1/scale is folded into the kernel's gradient multiplier."""
         from paddle_b200.parallel import symm
         opt = self._base_opt
         hcg = self._hcg_for_step
@@ -322,7 +352,7 @@ class DygraphShardingOptimizerV2:
         pows = opt._pows(self._slice_params[0])
         clip = opt._grad_clip
         dp = hcg.get_data_parallel_group() if hcg.get_data_parallel_world_size() > 1 else None
-        two_pass = clip is not None or dp is not None
+        two_pass = clip is not None or dp is not None or scaler is not None
         S_rank = self._sharding_rank
         local = {}
         if two_pass:
@@ -342,6 +372,16 @@ class DygraphShardingOptimizerV2:
                 else:
                     not_dist_sq += sq
             coef = None
+            inv = None
+            if scaler is not None:
+                scaler._init_state(dev)
+                inv = (1.0 / scaler._scale).float()
+                bad = (~torch.isfinite(dist_sq + not_dist_sq)).float()
+                scaler._found_inf.copy_(torch.maximum(scaler._found_inf, bad))
+                comm.all_reduce(scaler._found_inf, ReduceOp.MAX, self._group)
+                scaler._sync_found_inf(self)
+                dist_sq = dist_sq * inv * inv          # norms of the unscaled gradients for the clip
+                not_dist_sq = not_dist_sq * inv * inv
             if clip is not None:
                 if hasattr(clip, "_global_norm"):
                     clip._global_norm(dist_sq, not_dist_sq)
@@ -351,18 +391,24 @@ class DygraphShardingOptimizerV2:
                 gnorm = torch.sqrt(dist_sq + not_dist_sq)
                 mx = torch.full_like(gnorm, float(clip.clip_norm))
                 coef = mx / (torch.maximum(gnorm, mx) + 1.0e-6)
+            if inv is not None:
+                coef = inv if coef is None else coef * inv
         else:
             coef = None
+        found_inf = scaler._found_inf if scaler is not None else opt._found_inf
+        prev_found = opt._found_inf
+        opt._found_inf = found_inf                # _advance_pows must skip the step too
         scale = coef if opt._grad_scale_dev is None else (opt._grad_scale_dev if coef is None else coef * opt._grad_scale_dev)
         for buf in self._comm_buffers:
             sp = self._slice_of[buf._id]
             S = buf._shard_numel
             symm.rs_adamw_ag(buf.grad_storage, buf.param_storage, S_rank * S, S, opt._master_weights[sp.name],
                              opt._get_accumulator("moment1", sp), opt._get_accumulator("moment2", sp), glr, opt._beta1,
-                             opt._beta2, opt._epsilon, coeff, pows, grad_scale=scale, found_inf=opt._found_inf,
+                             opt._beta2, opt._epsilon, coeff, pows, grad_scale=scale, found_inf=found_inf,
                              local_grad=local.get(buf._id))
         for _, pw in opt._beta_pows.items():
             opt._advance_pows(pw)
+        opt._found_inf = prev_found
         opt._step_count += 1
 
     def minimize(self, loss, startup_program=None, parameters=None, no_grad_set=None):

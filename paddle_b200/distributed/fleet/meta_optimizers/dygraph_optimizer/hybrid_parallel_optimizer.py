@@ -76,7 +76,9 @@ class HybridParallelClipGrad:
         clip_var = max_norm / (torch.maximum(gnorm, max_norm) + 1.0e-6)
         self._last_global_norm = gnorm
         tgt = self._fold_target
-        if tgt is not None and all(tgt._native(p) for p, _ in params_grads) and hasattr(tgt, "_beta1"):
+        # folding multiplies EVERY gradient inside the update kernel, so it is only exact when every parameter is clipped
+        if tgt is not None and all(tgt._native(p) and getattr(p, "need_clip", True) for p, _ in params_grads) \
+                and hasattr(tgt, "_beta1"):
             prev = tgt._grad_scale_dev
             tgt._grad_scale_dev = clip_var if prev is None else prev * clip_var
             tgt._fold_reset = True
@@ -140,7 +142,7 @@ class HybridParallelOptimizer:
         if getattr(p, "is_distributed", False):
             return False
         names = self._mp_sync["names"]
-        return not names or any(n in p.name for n in names) or True
+        return not names or any(n in p.name for n in names)
 
     def _mp_sync_tensors(self, tensors):
         g = self._hcg.get_model_parallel_group()
@@ -173,7 +175,7 @@ class HybridParallelOptimizer:
             if getattr(self._base_opt, "_fold_reset", False):
                 self._base_opt._grad_scale_dev = None
                 self._base_opt._fold_reset = False
-        if mp and self._mp_sync["param"] and self._mp_sync.get("force", False):
+        if mp and self._mp_sync["param"]:
             self._mp_sync_tensors([p for p in parameter_list if self._filter_fn(p)])
         if mp and self._mp_sync["moment"]:
             ms = []

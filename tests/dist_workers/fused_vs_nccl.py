@@ -134,17 +134,33 @@ else:
     r = dist.get_rank()
     dev = torch.device("cuda", torch.cuda.current_device())
     m = build()
-    clip = nn.ClipGradByGlobalNorm(0.05) if mode == "v2clip" else None
+    clip = nn.ClipGradByGlobalNorm(0.05) if mode in ("v2clip", "v2amp") else None
     opt = paddle.optimizer.AdamW(1e-3, parameters=m.parameters(), multi_precision=True, grad_clip=clip)
     model = fleet.distributed_model(m)
     opt = fleet.distributed_optimizer(opt)
     used_fused = opt._inner_opt._arena is not None
 assert used_fused == bool(flag("use_fused_comm")), (used_fused, flag("use_fused_comm"))
-for s in range(4):
-    x, y = data(s, r, dev)
-    ((model(x) - y).float() ** 2).mean().backward()
-    opt.step()
-    opt.clear_grad()
+if mode == "v2amp":
+    # loss scaling through the fused K2+K3 path: 1/scale rides in the kernel's gradient multiplier, the squared norm of
+    # the reduced shard is the inf check; step 2 overflows on rank 1 and must be skipped everywhere
+    scaler = fleet.distributed_scaler(paddle.amp.GradScaler(init_loss_scaling=256.0, decr_every_n_nan_or_inf=1))
+    for s in range(5):
+        x, y = data(s if s < 2 else s - 1, r, dev)
+        loss = ((model(x) - y).float() ** 2).mean()
+        if s == 2 and r == 1:
+            loss = loss * float("inf")
+        scaler.scale(loss).backward()
+        scaler.step(opt)
+        scaler.update()
+        opt.clear_grad()
+    torch.cuda.synchronize()
+    assert float(scaler._scale) == 128.0, float(scaler._scale)
+else:
+    for s in range(4):
+        x, y = data(s, r, dev)
+        ((model(x) - y).float() ** 2).mean().backward()
+        opt.step()
+        opt.clear_grad()
 torch.cuda.synchronize()
 torch.save({k: v.detach().float().cpu() for k, v in m.state_dict().items()}, f"{out}.{r}.pt")
 print(f"fused_vs_nccl {mode} fused={used_fused} ok", r, flush=True)

@@ -39,7 +39,30 @@ def reference(steps, n, clip):
 
 
 STEPS = 4
-if mode in ("v1", "v2"):
+if mode in ("v1amp", "v2amp"):
+    # sharding V2 + GradScaler: the unscale / inf check must see the REDUCED shard; one step carries an inf
+    st = fleet.DistributedStrategy()
+    st.hybrid_configs = {"dp_degree": 1, "mp_degree": 1, "pp_degree": 1, "sharding_degree": 2,
+                         "sharding_configs": {"split_param": mode == "v2amp"}}
+    fleet.init(is_collective=True, strategy=st)
+    r, n = dist.get_rank(), dist.get_world_size()
+    m = build()
+    opt = paddle.optimizer.AdamW(1e-2, parameters=m.parameters(), weight_decay=0.01, grad_clip=nn.ClipGradByGlobalNorm(0.5))
+    model = fleet.distributed_model(m)
+    opt = fleet.distributed_optimizer(opt)
+    scaler = fleet.distributed_scaler(paddle.amp.GradScaler(init_loss_scaling=1024.0, decr_every_n_nan_or_inf=1))
+    for s in range(STEPS + 1):
+        x, y = data(s if s < 2 else s - 1, r)
+        loss = ((model(x) - y) ** 2).mean()
+        if s == 2 and r == 1:
+            loss = loss * float("inf")          # rank 1 overflows in step 2: every rank must skip it
+        scaler.scale(loss).backward()
+        scaler.step(opt)
+        scaler.update()
+        opt.clear_grad()
+    assert float(scaler._scale) == 512.0, float(scaler._scale)      # one decrease, on every rank
+    ref = reference(STEPS, n, clip=True)
+elif mode in ("v1", "v2"):
     st = fleet.DistributedStrategy()
     st.hybrid_configs = {"dp_degree": 1, "mp_degree": 1, "pp_degree": 1, "sharding_degree": 2,
                          "sharding_configs": {"split_param": mode == "v2"}}

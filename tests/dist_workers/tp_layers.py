@@ -87,6 +87,20 @@ for overlap in (False, True):
     torch.testing.assert_close(gather(out, 0), outr, rtol=1e-4, atol=1e-5)
     torch.testing.assert_close(gather(local.grad, 0), xr.grad, rtol=1e-4, atol=1e-5)
 
+# ---- mp_skip_c_identity: only the identity ops disappear, every all-reduce stays (results equal the whole layer)
+st.hybrid_configs = {"mp_configs": {"mp_async_allreduce": False, "mp_skip_c_identity": True}}
+col = mpu.ColumnParallelLinear(16, 8, has_bias=False, gather_output=False)
+row = mpu.RowParallelLinear(8, 16, has_bias=False, input_is_parallel=True)
+assert col.mp_skip_c_identity and row.mp_skip_c_identity
+W1, W2 = gather(col.weight, 1), gather(row.weight, 0)
+xi = x.clone().requires_grad_(True)
+y = row(torch.tanh(col(xi))); y.pow(2).sum().backward()
+xr = x.clone().requires_grad_(True)
+yr = torch.tanh(xr @ W1) @ W2; yr.pow(2).sum().backward()
+torch.testing.assert_close(y, yr, rtol=1e-5, atol=1e-5)           # Row forward still sums the partial products
+torch.testing.assert_close(xi.grad, xr.grad, rtol=1e-5, atol=1e-5)  # Column backward still sums the partial dX
+st.hybrid_configs = {"mp_configs": {"mp_skip_c_identity": False}}
+
 # ---- RNG tracker: sharded init differs, replicated init matches
 a = mpu.ColumnParallelLinear(8, 8, has_bias=False, gather_output=False).weight.detach()
 parts = []; dist.all_gather(parts, a); assert not torch.allclose(parts[0], parts[1])

@@ -43,7 +43,7 @@ def _run_env(script, nproc, args, env_extra, port):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
-@pytest.mark.parametrize("mode", ["dp", "v2", "v2clip", "tp", "sp", "stage3"])
+@pytest.mark.parametrize("mode", ["dp", "v2", "v2clip", "v2amp", "tp", "sp", "stage3"])
 def test_fused_training_matches_nccl_training(mode, tmp_path):
     """DataParallel (K1) and sharding V2 (K2+K3, with and without global-norm clip): same parameters after 4 steps
     whether gradients travel through the fused NVLink kernels or through NCCL."""
