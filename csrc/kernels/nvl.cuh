@@ -59,7 +59,9 @@ __device__ __forceinline__ void barrier_all(const Peers& P, uint64_t pad_off, ui
 //
 // grid_barrier_begin: CTA 0 announces "this rank reached epoch" to every peer; every CTA then waits until all peers
 // have announced it (each CTA polls its own GPU's pad, which is local memory).
+constexpr unsigned long long kNoBarrier = ~0ull;     // spin_limit value that turns the grid barriers into no-ops
 __device__ __forceinline__ void grid_barrier_begin(const Peers& P, uint64_t pad_off, uint32_t epoch, unsigned long long spin_limit) {
+  if (spin_limit == kNoBarrier) return;              // single-GPU emulation: the launches of the ranks are serialised
   const int t = threadIdx.x;
   if (t < P.nranks) {
     if (blockIdx.x == 0) {
@@ -83,6 +85,7 @@ __device__ __forceinline__ void grid_barrier_begin(const Peers& P, uint64_t pad_
 // stores are issued and fenced" (epoch) to every peer and waits for the same announcement from all of them, so when
 // the kernel completes, every peer's stores into this GPU have landed and every peer has finished reading from it.
 __device__ __forceinline__ void grid_barrier_end(const Peers& P, uint64_t pad_off, uint32_t epoch, unsigned long long spin_limit) {
+  if (spin_limit == kNoBarrier) return;
   __shared__ int s_last;
   __threadfence_system();                       // this thread's stores (peer / multimem) before the arrival below
   __syncthreads();

@@ -572,13 +572,26 @@ using namespace pdb::nvl;
 
 static const unsigned long long kSpinLimit = 20000000ull;   // ~ tens of seconds of system-scope polling, then trap
 
+// Single-GPU emulation (tests): all "ranks" are segments of one GPU's memory and the entry points are called once per
+// rank, one after the other, on one stream.  Nothing may wait for another rank then (the launches are serialised), so
+// every cross-rank barrier is skipped; the data movement and arithmetic are the real kernels (peer-access paths).
+static int g_emulate = 0;
+PDB_EXPORT int pdb200_nvl_set_emulation(int on) {
+  g_emulate = on;
+  return 0;
+}
+#define PDB_BARRIER(...)                                    \
+  do {                                                      \
+    if (!g_emulate) barrier_kernel<<<1, 32, 0, st>>>(__VA_ARGS__); \
+  } while (0)
+
 // peer_ptrs: host array of nranks device addresses (this process's mappings).  Every entry point brackets its data
 // kernel with signal-pad barriers using epochs `epoch` and `epoch + 1`; callers advance their counter by 2.
 PDB_EXPORT int pdb200_nvl_barrier(const uint64_t* peer_ptrs, int nranks, int rank, int64_t pad_off, int64_t epoch,
                                   void* stream) {
   PDB_REQUIRE(nranks >= 1 && nranks <= kMaxRanks, "nvl: nranks %d out of range (1..%d)", nranks, kMaxRanks);
   Peers P = make_peers(peer_ptrs, 0, nranks, rank);
-  barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+  if (!g_emulate) barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
   return check_launch("nvl_barrier");
 }
 
@@ -591,7 +604,7 @@ PDB_EXPORT int pdb200_nvl_allreduce(const uint64_t* peer_ptrs, uint64_t mc_ptr, 
   PDB_REQUIRE(dtype == PDB_DTYPE_F32 || dtype == PDB_DTYPE_BF16, "nvl_allreduce: float32 / bfloat16 only");
   cudaStream_t st = (cudaStream_t)stream;
   Peers P = make_peers(peer_ptrs, mc_ptr, nranks, rank);
-  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+  PDB_BARRIER(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
   const int64_t nvec = numel * esz / 16;
   const int64_t per = (nvec + nranks - 1) / nranks;
   int grid = (int)((per + 511) / 512);
@@ -602,7 +615,7 @@ PDB_EXPORT int pdb200_nvl_allreduce(const uint64_t* peer_ptrs, uint64_t mc_ptr, 
     allreduce_scale_kernel<float><<<grid, 512, 0, st>>>(P, (uint64_t)data_off, nvec, scale);
   else
     allreduce_scale_kernel<__nv_bfloat16><<<grid, 512, 0, st>>>(P, (uint64_t)data_off, nvec, scale);
-  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
+  PDB_BARRIER(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
   return check_launch("nvl_allreduce");
 }
 
@@ -619,7 +632,7 @@ PDB_EXPORT int pdb200_nvl_rs_adamw_ag(const uint64_t* peer_ptrs, uint64_t mc_ptr
   cudaStream_t st = (cudaStream_t)stream;
   Peers P = make_peers(peer_ptrs, mc_ptr, nranks, rank);
   AdamArgs a{lr, beta1, beta2, eps, weight_decay, beta_pows, grad_scale, found_inf};
-  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+  PDB_BARRIER(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
   int64_t blocks = (shard_numel / 8 + 255) / 256;
   const int64_t cap = (int64_t)sm_count() * 8;
   if (blocks > cap) blocks = cap;
@@ -628,7 +641,7 @@ PDB_EXPORT int pdb200_nvl_rs_adamw_ag(const uint64_t* peer_ptrs, uint64_t mc_ptr
     rs_adamw_ag_kernel<float><<<(int)blocks, 256, 0, st>>>(P, (uint64_t)grad_off, (uint64_t)param_off, shard_start, shard_numel, master, m, v, a, local_grad);
   else
     rs_adamw_ag_kernel<__nv_bfloat16><<<(int)blocks, 256, 0, st>>>(P, (uint64_t)grad_off, (uint64_t)param_off, shard_start, shard_numel, master, m, v, a, local_grad);
-  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
+  PDB_BARRIER(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
   return check_launch("nvl_rs_adamw_ag");
 }
 
@@ -652,13 +665,13 @@ PDB_EXPORT int pdb200_nvl_reduce_scatter(const uint64_t* peer_ptrs, uint64_t mc_
   PDB_REQUIRE(shard_numel % 8 == 0 && shard_start % 8 == 0, "nvl_reduce_scatter: shard must be a multiple of 8 elements");
   cudaStream_t st = (cudaStream_t)stream;
   Peers P = make_peers(peer_ptrs, mc_ptr, nranks, rank);
-  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+  PDB_BARRIER(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
   const int grid = pdb200_nvl_rs_grid(shard_numel);
   if (grad_dtype == PDB_DTYPE_F32)
     reduce_scatter_norm_kernel<float><<<grid, 256, 0, st>>>(P, (uint64_t)grad_off, shard_start, shard_numel, out, partial_sq);
   else
     reduce_scatter_norm_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(P, (uint64_t)grad_off, shard_start, shard_numel, out, partial_sq);
-  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
+  PDB_BARRIER(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
   return check_launch("nvl_reduce_scatter");
 }
 
@@ -668,11 +681,11 @@ PDB_EXPORT int pdb200_nvl_ce_combine(const uint64_t* peer_ptrs, int nranks, int 
   PDB_REQUIRE(nranks >= 1 && nranks <= kMaxRanks, "nvl: nranks %d out of range (1..%d)", nranks, kMaxRanks);
   cudaStream_t st = (cudaStream_t)stream;
   Peers P = make_peers(peer_ptrs, 0, nranks, rank);
-  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+  PDB_BARRIER(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
   if (rows > 0)
     ce_combine_symm_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, st>>>(P, (uint64_t)stats_off, labels, loss, lse, rows, ignore_index);
   // peers may overwrite their stats only after everyone has read them
-  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
+  PDB_BARRIER(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
   return check_launch("nvl_ce_combine");
 }
 
@@ -688,7 +701,7 @@ PDB_EXPORT int pdb200_nvl_vocab_embed(const uint64_t* peer_ptrs, int nranks, int
               "vocab_embed: rows must be 16-byte multiples and 16-byte aligned");
   cudaStream_t st = (cudaStream_t)stream;
   Peers P = make_peers(peer_ptrs, 0, nranks, rank);
-  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+  PDB_BARRIER(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
   if (n_tokens > 0) {
     int64_t blocks = (n_tokens + 7) / 8;
     const int64_t cap = (int64_t)sm_count() * 8;
@@ -699,7 +712,7 @@ PDB_EXPORT int pdb200_nvl_vocab_embed(const uint64_t* peer_ptrs, int nranks, int
       vocab_embed_gather_kernel<uint16_t><<<(unsigned)blocks, 256, 0, st>>>(P, (uint64_t)table_off, ids, (uint16_t*)out, n_tokens, hidden, vocab_per_rank);
     if (int e = check_launch("vocab_embed_gather")) return e;
   }
-  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
+  PDB_BARRIER(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
   return check_launch("nvl_vocab_embed");
 }
 
@@ -713,7 +726,7 @@ PDB_EXPORT int pdb200_nvl_allgather(const uint64_t* peer_ptrs, uint64_t mc_ptr, 
   PDB_REQUIRE(shard_bytes % 16 == 0 && src_off % 16 == 0 && dst_off % 16 == 0, "nvl_allgather: 16-byte granularity");
   cudaStream_t st = (cudaStream_t)stream;
   Peers P = make_peers(peer_ptrs, mc_ptr, nranks, rank);
-  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+  PDB_BARRIER(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
   const int64_t nvec = shard_bytes / 16;
   if (nvec > 0) {
     int64_t blocks = (nvec + 1023) / 1024;
@@ -723,7 +736,7 @@ PDB_EXPORT int pdb200_nvl_allgather(const uint64_t* peer_ptrs, uint64_t mc_ptr, 
         P, reinterpret_cast<const uint4*>(peer_ptrs[rank] + (uint64_t)src_off), (uint64_t)dst_off, nvec);
     if (int e = check_launch("allgather_push")) return e;
   }
-  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
+  PDB_BARRIER(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
   return check_launch("nvl_allgather");
 }
 
@@ -736,7 +749,7 @@ PDB_EXPORT int pdb200_nvl_allgather_from(const uint64_t* peer_ptrs, uint64_t mc_
   PDB_REQUIRE(shard_bytes % 16 == 0 && ((uintptr_t)src & 15) == 0 && dst_off % 16 == 0, "nvl_allgather_from: 16-byte granularity");
   cudaStream_t st = (cudaStream_t)stream;
   Peers P = make_peers(peer_ptrs, mc_ptr, nranks, rank);
-  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+  PDB_BARRIER(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
   const int64_t nvec = shard_bytes / 16;
   if (nvec > 0) {
     int64_t blocks = (nvec + 1023) / 1024;
@@ -745,7 +758,7 @@ PDB_EXPORT int pdb200_nvl_allgather_from(const uint64_t* peer_ptrs, uint64_t mc_
     allgather_push_kernel<<<(unsigned)(blocks < 1 ? 1 : blocks), 256, 0, st>>>(P, reinterpret_cast<const uint4*>(src), (uint64_t)dst_off, nvec);
     if (int e = check_launch("allgather_push")) return e;
   }
-  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
+  PDB_BARRIER(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
   return check_launch("nvl_allgather_from");
 }
 
@@ -759,7 +772,7 @@ PDB_EXPORT int pdb200_nvl_rs_sum_bf16(const uint64_t* peer_ptrs, uint64_t mc_ptr
               "nvl_rs_sum_bf16: 16-byte granularity");
   cudaStream_t st = (cudaStream_t)stream;
   Peers P = make_peers(peer_ptrs, mc_ptr, nranks, rank);
-  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+  PDB_BARRIER(P, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
   if (shard_numel > 0) {
     int64_t blocks = (shard_numel / 8 + 255) / 256;
     const int64_t cap = (int64_t)sm_count() * 8;
@@ -768,7 +781,7 @@ PDB_EXPORT int pdb200_nvl_rs_sum_bf16(const uint64_t* peer_ptrs, uint64_t mc_ptr
                                                                           (__nv_bfloat16*)out);
     if (int e = check_launch("rs_sum_bf16")) return e;
   }
-  barrier_kernel<<<1, 32, 0, st>>>(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
+  PDB_BARRIER(P, (uint64_t)pad_off, (uint32_t)(epoch + 1), kSpinLimit);
   return check_launch("nvl_rs_sum_bf16");
 }
 
@@ -795,7 +808,7 @@ PDB_EXPORT int pdb200_nvl_allgather_multi(const uint64_t* peer_ptrs, uint64_t mc
   int64_t blocks = (most + 2047) / 2048;
   const int64_t cap = max_ctas > 0 ? max_ctas : (int64_t)sm_count();
   if (blocks > cap) blocks = cap;
-  allgather_multi_kernel<<<(unsigned)(blocks < 1 ? 1 : blocks), 256, 0, (cudaStream_t)stream>>>(P, S, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+  allgather_multi_kernel<<<(unsigned)(blocks < 1 ? 1 : blocks), 256, 0, (cudaStream_t)stream>>>(P, S, (uint64_t)pad_off, (uint32_t)epoch, g_emulate ? kNoBarrier : kSpinLimit);
   return check_launch("nvl_allgather_multi");
 }
 
@@ -823,8 +836,8 @@ PDB_EXPORT int pdb200_nvl_reduce_scatter_multi(const uint64_t* peer_ptrs, uint64
   const unsigned grid = (unsigned)(blocks < 1 ? 1 : blocks);
   cudaStream_t st = (cudaStream_t)stream;
   if (grad_dtype == PDB_DTYPE_F32)
-    reduce_scatter_multi_kernel<float><<<grid, 256, 0, st>>>(P, S, scale, accumulate, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+    reduce_scatter_multi_kernel<float><<<grid, 256, 0, st>>>(P, S, scale, accumulate, (uint64_t)pad_off, (uint32_t)epoch, g_emulate ? kNoBarrier : kSpinLimit);
   else
-    reduce_scatter_multi_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(P, S, scale, accumulate, (uint64_t)pad_off, (uint32_t)epoch, kSpinLimit);
+    reduce_scatter_multi_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(P, S, scale, accumulate, (uint64_t)pad_off, (uint32_t)epoch, g_emulate ? kNoBarrier : kSpinLimit);
   return check_launch("nvl_reduce_scatter_multi");
 }

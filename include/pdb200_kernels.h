@@ -103,6 +103,9 @@ PDB_API int pdb200_gemm_set_group_m(int n);
  * pad_off: 32-byte signal pad used by the in-stream barriers; each call consumes epochs `epoch` and `epoch + 1`.
  * Reference counterparts: reducer.cc:1093-1127 (K1), tensor_fusion_helper.py:559-645 + adamw_kernel.cu (K2+K3),
  * c_softmax_with_cross_entropy_op.cu:211-314 (K8). */
+/* Tests on one GPU: emulation mode skips every cross-rank barrier, so the entry points can be called once per
+ * emulated rank (segments of one GPU's memory as peer_ptrs, mc_ptr = 0), one after the other on one stream. */
+PDB_API int pdb200_nvl_set_emulation(int on);
 PDB_API int pdb200_nvl_barrier(const uint64_t* peer_ptrs, int nranks, int rank, int64_t pad_off, int64_t epoch, void* stream);
 PDB_API int pdb200_nvl_allreduce(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t data_off, int64_t numel, int dtype, float scale, int64_t pad_off, int64_t epoch, int max_ctas, void* stream);
 PDB_API int pdb200_nvl_rs_adamw_ag(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t grad_off, int grad_dtype, int64_t param_off, int64_t shard_start, int64_t shard_numel, float* master, float* m, float* v, float lr, float beta1, float beta2, float eps, float weight_decay, const float* beta_pows, const float* grad_scale, const float* found_inf, const float* local_grad, int64_t pad_off, int64_t epoch, void* stream);
