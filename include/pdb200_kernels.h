@@ -94,6 +94,12 @@ PDB_API int pdb200_gemm_bf16_pair(const void* a, const void* b, void* c, const v
  * swizzled-smem + TMA-store epilogue; fp32 C += is a TMA reduce-add (csrc/kernels/gemm_tc3.cu). */
 PDB_API int pdb200_gemm_bf16_macro(const void* a, const void* b, void* c, const void* bias, int64_t M, int64_t N, int64_t K, int trans_a, int trans_b, int out_dtype, float beta, int act, void* stream);
 PDB_API int pdb200_gemm_set_band(int n);
+/* K9/K10 grouped GEMMs for the local experts of an MoE layer, scheduled on the device from int64 row counts (reference:
+ * per-expert loop after blocking count reads, incubate/distributed/models/moe/moe_layer.py:441-470).  Rows are
+ * expert-major in slabs of rows_cap rows.  forward/dgrad: C[r,:] = A[r,:] . B[e] (B stacked [E][K][N], or [E][N][K] when
+ * trans_b).  wgrad: dW[e] (=|+=) A_e^T . G_e over the rows of expert e (out_dtype 0 = fp32, beta 1 accumulates). */
+PDB_API int pdb200_gemm_grouped(const void* a, const void* b, void* c, const int64_t* counts, int E, int64_t rows_cap, int64_t N, int64_t K, int trans_b, int act, void* stream);
+PDB_API int pdb200_gemm_grouped_wgrad(const void* a, const void* g, void* dw, const int64_t* counts, int E, int64_t rows_cap, int64_t Kin, int64_t N, int out_dtype, float beta, void* stream);
 /* Tuning knob: raster band height (in 256-row pair tiles) of the CTA-pair kernel; 0 restores the default. */
 PDB_API int pdb200_gemm_set_group_m(int n);
 

@@ -72,6 +72,8 @@ class MoELayer(Layer):
         assert isinstance(gate, (dict, BaseGate)), "gate config' type must be dict or an instance of BaseGate"
         self.group = moe_group
         self.world_size = moe_group.nranks if moe_group is not None else 1
+        from .grouped_experts import GroupedExpertsFFN
+        self._grouped = isinstance(experts, GroupedExpertsFFN)
         self.num_expert = len(experts)
         self.recompute_interval = recompute_interval
         assert experts is not None
@@ -108,7 +110,18 @@ class MoELayer(Layer):
         assert topk == self.top_k
         with torch.no_grad():
             lec = ops.number_count(gate, self.num_expert * self.world_size)
-            pos = ops.assign_pos(gate, torch.cumsum(lec, 0))
+            pos = ops.assign_pos(gate, torch.cumsum(lec, 0), padded=self._grouped)   # padded: no host read of the total
+        if self._grouped:
+            # device-scheduled grouped GEMMs: the slab is used at its provisioned capacity and the row counts never
+            # leave the device - zero host synchronisations in this layer's forward and backward
+            x, counts_dev, meta = moe_fused.dispatch(inp, pos, lec, self.group, self.num_expert, topk, sync=False)
+            x = self.experts(x, counts_dev)
+            x = moe_fused.combine(x, meta).reshape(-1, self.top_k, self.d_model)
+            value = value.reshape(x.shape[0], 1, self.top_k).to(x.dtype)
+            x = torch.bmm(value, x).reshape(-1, self.d_model)
+            if mp_size > 1:
+                x = _AllGatherMP.apply(x, mp_rank, mp_size, self.mp_group)
+            return x.reshape(origin_shape)
         x, counts, meta = moe_fused.dispatch(inp, pos, lec, self.group, self.num_expert, topk)
 
         def experts_fwd(x):
@@ -154,11 +167,15 @@ class MoELayer(Layer):
         x = _local_scatter(inp, temp_pos)
         if self.world_size > 1:
             x = global_scatter(x, lec, gec, group=self.group)
-        # ---- experts: one host read of the counts per layer
-        counts = fwd_expert_count.tolist()
+        # ---- experts
+        if self._grouped:
+            x = self.experts(x, fwd_expert_count) if x.shape[0] else x
+            counts = None
+        else:
+            counts = fwd_expert_count.tolist()      # one host read of the counts per layer
 
         def experts_fwd(x):
-            if x.shape[0] == 0:
+            if x.shape[0] == 0 or counts is None:
                 return x
             ys, last = [], 0
             for idx, c in enumerate(counts):

@@ -15,6 +15,7 @@ class MoEConfig(LlamaConfig):
     num_experts: int = 8
     top_k: int = 2
     gate_type: str = "naive"
+    grouped_experts: bool = True      # stacked expert weights + device-scheduled grouped GEMMs (no per-expert launches)
 
     @staticmethod
     def mixtral_8x7b(**kw):
@@ -48,7 +49,12 @@ class MoEDecoderLayer(nn.Layer):
         self.input_layernorm = nn.RMSNorm(config.hidden_size, config.rms_norm_eps)
         self.self_attn = LlamaAttention(config)
         self.post_attention_layernorm = nn.RMSNorm(config.hidden_size, config.rms_norm_eps)
-        experts = nn.LayerList([ExpertFFN(config) for _ in range(config.num_experts // world)])
+        if config.grouped_experts:
+            from paddle_b200.incubate.distributed.models.moe import GroupedExpertsFFN
+            experts = GroupedExpertsFFN(config.num_experts // world, config.hidden_size, config.intermediate_size,
+                                        weight_attr=_init(config.initializer_range))
+        else:
+            experts = nn.LayerList([ExpertFFN(config) for _ in range(config.num_experts // world)])
         self.moe = MoELayer(config.hidden_size, experts, gate={"type": config.gate_type, "top_k": config.top_k},
                             moe_group=moe_group)
 

@@ -5,7 +5,7 @@ from .activation import fused_bias_act, swiglu  # noqa: F401
 from .attention import flash_attention, flash_attn_varlen  # noqa: F401
 from .linear import linear  # noqa: F401
 from .loss import (ce_combine, ce_local_backward, ce_local_stats, softmax_cross_entropy)  # noqa: F401
-from .moe import (assign_pos, limit_by_capacity, number_count, prune_gate_by_capacity, random_routing,  # noqa: F401
+from .moe import (assign_pos, grouped_linear, limit_by_capacity, number_count, prune_gate_by_capacity, random_routing,  # noqa: F401
                   topk_softmax)
 from .multi_tensor import (TensorTable, adamw_step, grads_table, l2norm_sq, momentum_step, squared_l2_norm,  # noqa: F401
                            unscale_and_check)

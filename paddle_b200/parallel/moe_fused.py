@@ -94,11 +94,18 @@ def _slab_view(meta, rows):
 class _Dispatch(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, meta):
-        _push(meta, x.contiguous(), meta.topk)
+        meta.overflow = _push(meta, x.contiguous(), meta.topk)
+        slab_rows = meta.slab.numel() // meta.row_bytes
+        if not meta.sync:
+            # grouped-GEMM consumers take the slab at full capacity plus the device-side counts: no host read.  Rows
+            # that did not fit were dropped by the kernel and flagged in meta.overflow (checked by check_overflow()).
+            meta.R = slab_rows
+            meta.counts_host = None
+            ctx.meta = meta
+            return _slab_view(meta, meta.R).clone()
         rc = meta.recv_counts.tolist()                      # the one host read of the layer (expert GEMM shapes)
         meta.R = int(rc[-1])
         meta.counts_host = rc[:-1]
-        slab_rows = meta.slab.numel() // meta.row_bytes
         if meta.R > slab_rows:
             raise RuntimeError(f"MoE receive slab too small: {meta.R} rows routed to this rank, {slab_rows} provisioned; "
                                f"raise PDB200_MOE_SLAB_FACTOR (now {os.environ.get('PDB200_MOE_SLAB_FACTOR', '2.0')})")
@@ -130,11 +137,14 @@ class _Combine(torch.autograd.Function):
         return _slab_view(meta, meta.R).clone(), None
 
 
-def dispatch(x, pos, lec, group, num_expert, topk):
+def dispatch(x, pos, lec, group, num_expert, topk, sync=True):
     """x: [T, d]; pos: [S] int64 (sorted slot -> token*topk + k); lec: [W*E] int64 send counts.  Returns
-    (rows [R, d] expert-major, per-expert counts as a python list, meta for ``combine``)."""
+    (rows [R, d] expert-major, per-expert counts, meta for ``combine``).  ``sync=True``: R is the exact row count and
+    the counts are a python list (one host read).  ``sync=False``: R is the slab capacity, the counts stay on the
+    device (int64[num_expert]) and nothing is read back - for consumers that schedule on the device."""
     T, d = x.shape
     meta = _Meta()
+    meta.sync = bool(sync)
     nb = group.nranks * num_expert
     meta.row_bytes = d * x.element_size()
     st = _buffers(group, _slab_rows(group, max(T * topk, 1)), meta.row_bytes, nb)
@@ -142,15 +152,26 @@ def dispatch(x, pos, lec, group, num_expert, topk):
     meta.pos, meta.lec = pos.contiguous(), lec.to(torch.int64).contiguous()
     meta.E, meta.topk, meta.T, meta.d, meta.dtype = num_expert, topk, T, d, x.dtype
     S = pos.numel()
-    inv = torch.full((T * topk,), -1, dtype=torch.int64, device=x.device)
+    # inverse map entry -> sorted slot; padded position lists carry -1 past the routed entries: those go to a dummy cell
+    inv = torch.full((T * topk + 1,), -1, dtype=torch.int64, device=x.device)
     if S:
-        inv[pos] = torch.arange(S, dtype=torch.int64, device=x.device)
-    meta.inv = inv
+        safe = torch.where(pos >= 0, pos, torch.full_like(pos, T * topk))
+        inv.scatter_(0, safe, torch.arange(S, dtype=torch.int64, device=x.device))
+    meta.inv = inv[: T * topk].contiguous()
     meta.route_rank = torch.empty(max(S, 1), dtype=torch.int32, device=x.device)
     meta.route_row = torch.empty(max(S, 1), dtype=torch.int32, device=x.device)
     meta.recv_counts = torch.zeros(num_expert + 1, dtype=torch.int64, device=x.device)
     rows = _Dispatch.apply(x, meta)
+    if not sync:
+        return rows, meta.recv_counts[:num_expert], meta
     return rows, meta.counts_host, meta
+
+
+def check_overflow(meta):
+    """Host-side check (synchronises) that no routed row was dropped for lack of slab space; optional in the no-sync mode."""
+    if int(meta.overflow.item()) != 0:
+        raise RuntimeError("MoE receive slab too small: raise PDB200_MOE_SLAB_FACTOR "
+                           f"(now {os.environ.get('PDB200_MOE_SLAB_FACTOR', '2.0')})")
 
 
 def combine(y, meta):

@@ -46,3 +46,30 @@ torch.testing.assert_close(y.reshape(-1, D), out, rtol=1e-4, atol=1e-5)
 torch.testing.assert_close(x.grad, xr.grad, rtol=1e-4, atol=1e-5)
 assert all(getattr(p, "no_sync", False) for p in local.parameters())
 print("moe ok", r)
+
+# ---- grouped experts (stacked weights, one module for all local experts) == the same experts as a LayerList
+from paddle_b200.incubate.distributed.models.moe import GroupedExpertsFFN
+from paddle_b200.models.moe import ExpertFFN, MoEConfig
+
+cfg = MoEConfig.tiny(hidden_size=D, intermediate_size=16)
+paddle.seed(9)
+with paddle.utils.unique_name.guard():
+    ffns = [ExpertFFN(cfg) for _ in range(E_LOCAL * n)]
+    mine = [ffns[r * E_LOCAL + i] for i in range(E_LOCAL)]
+    moe_list = MoELayer(D, nn.LayerList(mine), gate={"type": "naive", "top_k": 2}, moe_group=g)
+    moe_grp = MoELayer(D, GroupedExpertsFFN.from_experts(mine), gate={"type": "naive", "top_k": 2}, moe_group=g)
+for a, b in ((moe_grp.gate.gate.weight, moe_list.gate.gate.weight), (moe_grp.gate.gate.bias, moe_list.gate.gate.bias)):
+    a.detach().copy_(b.detach())
+    dist.broadcast(a.detach(), 0)
+    dist.broadcast(b.detach(), 0)
+xa = x.detach().clone().requires_grad_(True)
+xb = x.detach().clone().requires_grad_(True)
+ya, yb = moe_list(xa), moe_grp(xb)
+ya.sum().backward()
+yb.sum().backward()
+torch.testing.assert_close(yb, ya, rtol=1e-4, atol=1e-5)
+torch.testing.assert_close(xb.grad, xa.grad, rtol=1e-4, atol=1e-5)
+for i, e in enumerate(mine):
+    torch.testing.assert_close(moe_grp.experts.gate_up_weight.grad[i], e.gate_up_proj.weight.grad, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(moe_grp.experts.down_weight.grad[i], e.down_proj.weight.grad, rtol=1e-4, atol=1e-5)
+print("moe grouped ok", r)

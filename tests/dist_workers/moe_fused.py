@@ -55,6 +55,49 @@ for dtype, tol in ((torch.float32, dict(rtol=1e-4, atol=1e-5)), (torch.bfloat16,
     assert len(a[2]) == len(b[2]) and len(a[2]) > 0
     for ga, gb in zip(a[2], b[2]):
         torch.testing.assert_close(gb, ga, rtol=tol["rtol"], atol=tol["atol"] * 4)
+
+# ---- grouped experts on the fused path: device-scheduled grouped GEMMs, no host synchronisation in the layer
+from paddle_b200.incubate.distributed.models.moe import GroupedExpertsFFN
+from paddle_b200.models.moe import ExpertFFN, MoEConfig
+
+DG = 256
+cfg = MoEConfig.tiny(hidden_size=DG, intermediate_size=512)
+paddle.seed(50 + r)
+paddle.set_default_dtype("bfloat16")
+with paddle.utils.unique_name.guard():
+    ffns = [ExpertFFN(cfg).to(dev) for _ in range(E_LOCAL)]
+    moe_list = MoELayer(DG, nn.LayerList(ffns), gate={"type": "naive", "top_k": TOPK}, moe_group=g).to(dev)
+    moe_grp = MoELayer(DG, GroupedExpertsFFN.from_experts(ffns).to(dev), gate={"type": "naive", "top_k": TOPK}, moe_group=g).to(dev)
+paddle.set_default_dtype("float32")
+for m in (moe_list, moe_grp):
+    m.gate.gate.weight.detach().copy_(moe_list.gate.gate.weight.detach())
+    m.gate.gate.bias.detach().copy_(moe_list.gate.gate.bias.detach())
+    dist.broadcast(m.gate.gate.weight.detach(), 0)
+    dist.broadcast(m.gate.gate.bias.detach(), 0)
+paddle.set_flags({"FLAGS_use_fused_comm": True})
+torch.manual_seed(70 + r)
+x0 = (torch.randn(4, 96, DG, device=dev) * 0.5).bfloat16()
+gout = (torch.randn(4, 96, DG, device=dev) * 0.5).bfloat16()
+xa = x0.clone().requires_grad_(True)
+ya = moe_list(xa)
+ya.backward(gout)
+xb = x0.clone().requires_grad_(True)
+moe_grp(xb.detach())                                # warm-up: arenas / tensor maps are created outside the checked region
+torch.cuda.synchronize()
+torch.cuda.set_sync_debug_mode("error")            # any host synchronisation inside the layer raises
+try:
+    yb = moe_grp(xb)
+    yb.backward(gout)
+finally:
+    torch.cuda.set_sync_debug_mode("default")
+torch.cuda.synchronize()
+tol = dict(rtol=3e-2, atol=3e-2)
+torch.testing.assert_close(yb.float(), ya.float(), **tol)
+torch.testing.assert_close(xb.grad.float(), xa.grad.float(), **tol)
+for i, e in enumerate(ffns):
+    torch.testing.assert_close(moe_grp.experts.gate_up_weight.grad[i].float(), e.gate_up_proj.weight.grad.float(), rtol=3e-2, atol=6e-2)
+    torch.testing.assert_close(moe_grp.experts.down_weight.grad[i].float(), e.down_proj.weight.grad.float(), rtol=3e-2, atol=6e-2)
+print("moe grouped fused ok", r, flush=True)
 print("moe_fused ok", r, flush=True)
 moe_fused.release_all()
 symm.release_all()
