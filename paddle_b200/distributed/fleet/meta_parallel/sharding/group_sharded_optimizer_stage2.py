@@ -1,6 +1,9 @@
 """GroupShardedOptimizerStage2 (reference: .../sharding/group_sharded_optimizer_stage2.py:53-700): ZeRO-2 optimizer
 side - parameters are assigned to ranks greedily by size per dtype (:347-366), each rank updates only the ones it
-owns (optimizer state exists only there), then owners broadcast the updated parameters (:630-644)."""
+owns (optimizer state exists only there), then owners broadcast the updated parameters (:630-644).  Every owner's
+parameters are packed per dtype into a flat ``ParamStorage`` (reference :368-409), so that exchange is one broadcast
+per (owner, dtype); ``offload=True`` keeps fp32 master copies and moments of the owned parameters in pinned host
+memory and steps on the CPU (reference :120-160, 580-620)."""
 from __future__ import annotations
 
 import torch
@@ -21,8 +24,7 @@ class GroupShardedOptimizerStage2:
         self.world_size = self._group.nranks
         self._rank = self._group.rank
         self._global_root_rank = self._group.ranks[0]
-        if offload:
-            raise NotImplementedError("offload=True is not implemented in this build")
+        self.offload = bool(offload)
         self._local_params = list(params)
         self._all_params = list(params)
         self.__segment_params = None
@@ -38,6 +40,31 @@ class GroupShardedOptimizerStage2:
         optim._group = self._group
         if isinstance(optim._grad_clip, ClipGradByGlobalNorm):
             optim._grad_clip = GroupShardedClipGrad(optim._grad_clip, None, self._group)
+        self._param_storages = {}      # (owner index, dtype) -> ParamStorage
+        self._model = None
+        self._build_param_storages()
+        if self.offload:
+            from .group_sharded_utils import offload_optimizer_state
+            offload_optimizer_state(optim, [p for p in local if p.requires_grad], wrap_step=False)
+
+    def _attach_model(self, model):
+        self._model = model
+
+    @torch.no_grad()
+    def _build_param_storages(self):
+        """Pack every owner's trainable parameters into flat per-dtype buffers (all ranks build all of them: stage 2
+        keeps full parameter replicas).  Views of non-contiguous / already-viewed parameters are left alone."""
+        from .group_sharded_storage import ParamStorage, _aligned_numel
+        for r, ps in enumerate(self.__segment_params):
+            by_dtype = {}
+            for p in ps:
+                if p.requires_grad and p.is_contiguous() and not p.data._is_view():
+                    by_dtype.setdefault(p.dtype, []).append(p)
+            for dtype, group_ps in by_dtype.items():
+                size = sum(_aligned_numel(p) for p in group_ps)
+                st = ParamStorage(size, dtype, group_ps[0].device)
+                st.add_rank_params(group_ps)
+                self._param_storages[(r, dtype)] = st
 
     def _segment(self):
         segs = [[] for _ in range(self.world_size)]
@@ -68,7 +95,12 @@ class GroupShardedOptimizerStage2:
 
     @torch.no_grad()
     def step(self):
-        self._optim.step()
+        if getattr(self._optim, "_offload_pre", None) is not None:
+            self._optim._offload_pre()
+            self._optim.step()
+            self._optim._offload_post()
+        else:
+            self._optim.step()
         self._broadcast_params()
 
     def minimize(self, *a, **k):
@@ -76,14 +108,20 @@ class GroupShardedOptimizerStage2:
 
     @torch.no_grad()
     def _broadcast_params(self):
-        tasks = []
+        tasks, packed = [], set()
+        for (r, _dtype), st in self._param_storages.items():
+            tasks.append(comm.broadcast(st.buffer, self._group.ranks[r], self._group, sync_op=False))
+            packed.update(id(p) for p in st._params)
         for r, ps in enumerate(self.__segment_params):
             for p in ps:
-                tasks.append(comm.broadcast(p, self._group.ranks[r], self._group, sync_op=False))
+                if id(p) not in packed:
+                    tasks.append(comm.broadcast(p, self._group.ranks[r], self._group, sync_op=False))
         for t in tasks:
             t.wait()
 
     def clear_grad(self, set_to_zero=True):
+        if self._model is not None:
+            return self._model._clear_grads(set_to_zero)
         for p in self._all_params:
             if p.grad is not None:
                 if set_to_zero:

@@ -83,20 +83,33 @@ else:
     r, n = dist.get_rank(), dist.get_world_size()
     m = build()
     opt = paddle.optimizer.AdamW(1e-2, parameters=m.parameters(), weight_decay=0.01, grad_clip=nn.ClipGradByGlobalNorm(0.5))
-    level = {"stage2": "os_g", "stage3": "p_g_os"}[mode]
-    model, opt, _ = dist.group_sharded_parallel(m, opt, level, segment_size=256)
+    level = {"stage2": "os_g", "stage3": "p_g_os"}[mode.split("_")[0]]
+    offload = mode.endswith("_offload")
+    model, opt, _ = dist.group_sharded_parallel(m, opt, level, segment_size=256, offload=offload,
+                                                buffer_max_size=2 ** 12 if mode.startswith("stage2") else 2 ** 23)
+    if mode.startswith("stage2"):
+        # small gradients ride in per-destination buckets: grads are views of them, owners' params are packed flat
+        sts = model._grad_storage_list
+        assert sts and all(st._params for st in sts), "no GradStorage bucket was filled"
+        bucketed = [p for p in m.parameters() if getattr(p, "_gs_grad_bucket", None) is not None]
+        assert bucketed and all(p.grad is not None and p.grad.data_ptr() >= p._gs_grad_bucket.buffer.data_ptr() for p in bucketed)
+        assert any(getattr(p, "_gs_grad_bucket", None) is None for p in m.parameters()), "expected one oversized parameter"
+        assert opt._param_storages, "owners' parameters were not packed into ParamStorage"
+    if offload:
+        inner = opt._optim if hasattr(opt, "_optim") else opt
+        assert inner._offload_pairs and all(sh.device.type == "cpu" and sh.dtype == torch.float32 for _, sh in inner._offload_pairs)
     for s in range(STEPS):
         x, y = data(s, r)
         ((model(x) - y) ** 2).mean().backward()
         opt.step()
         opt.clear_grad()
-    if mode == "stage3":
+    if mode.startswith("stage3"):
         assert m[0].weight.numel() == 0, "stage 3 must release full parameters between steps"
         model.get_all_parameters()
     ref = reference(STEPS, n, clip=True)
 for (k, a), (_, b) in zip(m.state_dict().items(), ref.state_dict().items()):
     torch.testing.assert_close(a.detach(), b.detach(), rtol=1e-4, atol=1e-5, msg=lambda s: f"{mode} {k}: {s}")
-if mode == "stage3":
+if mode.startswith("stage3"):
     import tempfile, os
     d = tempfile.mkdtemp() if r == 0 else None
     box = [d]
