@@ -67,6 +67,10 @@ PDB_API int pdb200_unscale_check_multi(const void* table, const void* chunk_map,
 PDB_API int pdb200_l2norm_multi_static_max_chunks();
 PDB_API int pdb200_l2norm_multi_static(const void* table, const void* chunk_map, int n_chunks, float* out, int accumulate, void* stream);
 
+/* A2 tensor check (reference: phi/kernels/gpu/check_numerics_kernel.cu): stats = device int64[3] {nan, inf, zero counts},
+ * values = device float[3] {max, min, sum} over the finite elements.  Nothing is read back by the library. */
+PDB_API int pdb200_check_numerics(const void* x, int64_t numel, int dtype, int64_t* stats, float* values, void* stream);
+
 /* K8 softmax cross-entropy, local / per-rank part (reference: phi/kernels/gpu/cross_entropy_kernel.cu,
  * fluid/operators/collective/c_softmax_with_cross_entropy_op.cu:47-114,133-340). stats: [rows,3] = max,sumexp,target */
 PDB_API int pdb200_ce_fwd(const void* logits, const int64_t* labels, float* stats, float* loss, float* lse, int64_t rows, int64_t V, int64_t ld, int64_t vocab_start, int64_t ignore_index, int dtype, void* stream);
