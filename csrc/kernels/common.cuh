@@ -44,6 +44,7 @@ inline int check_launch(const char* what) {
   } while (0)
 
 int sm_count();  // cached multiProcessorCount of the current device
+extern uint32_t* g_nvl_progress;   // mapped host word for the barrier-progress trace (runtime_glue.cu), nullptr = off
 
 // Local-memory guard (runtime_glue.cu): 0 when [p, p+bytes) touches no registered mapping of another GPU's memory.
 int require_local(const void* p, size_t bytes, const char* what);

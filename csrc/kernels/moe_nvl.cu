@@ -138,6 +138,7 @@ __global__ void __launch_bounds__(256) pull_sum_kernel(Peers P, uint64_t slab_of
 static Peers make_peers(const uint64_t* ptrs, int nranks, int rank) {
   Peers P{};
   for (int i = 0; i < nranks && i < kMaxRanks; ++i) P.ptr[i] = ptrs[i];
+  P.progress = g_nvl_progress;
   P.nranks = nranks;
   P.rank = rank;
   return P;

@@ -13,6 +13,7 @@ constexpr int kMaxRanks = 8;
 struct Peers {              // passed by value to kernels
   uint64_t ptr[kMaxRanks];  // base address of every rank's symmetric segment as mapped in THIS process
   uint64_t mc;              // multicast mapping of the same segment (0 when NVLS is unavailable)
+  uint32_t* progress;       // optional mapped host word: last barrier epoch this rank passed (watchdog trace)
   int nranks;
   int rank;
 };
@@ -50,6 +51,7 @@ __device__ __forceinline__ void barrier_all(const Peers& P, uint64_t pad_off, ui
     fence_sys();
   }
   __syncthreads();
+  if (t == 0 && P.progress) *reinterpret_cast<volatile uint32_t*>(P.progress) = epoch;
 }
 
 // ---- barriers embedded in multi-CTA data kernels ---------------------------------------------------------------

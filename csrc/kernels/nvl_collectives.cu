@@ -559,6 +559,7 @@ static Peers make_peers(const uint64_t* ptrs, uint64_t mc, int nranks, int rank)
   Peers P{};
   for (int i = 0; i < nranks && i < kMaxRanks; ++i) P.ptr[i] = ptrs[i];
   P.mc = mc;
+  P.progress = g_nvl_progress;
   P.nranks = nranks;
   P.rank = rank;
   return P;

@@ -87,6 +87,13 @@ PDB_EXPORT int pdb200_unregister_foreign_range(uint64_t base) {
 }
 PDB_EXPORT int pdb200_check_local(const void* p, int64_t bytes) { return pdb::require_local(p, (size_t)bytes, "check_local"); }
 
+// Mapped host word the fused kernels' barriers write their last epoch to (watchdog trace); 0 = off.
+namespace pdb { uint32_t* g_nvl_progress = nullptr; }
+PDB_EXPORT int pdb200_nvl_set_progress(uint64_t host_mapped_ptr) {
+  pdb::g_nvl_progress = reinterpret_cast<uint32_t*>((uintptr_t)host_mapped_ptr);
+  return 0;
+}
+
 PDB_EXPORT const char* pdb200_last_error() { return pdb::g_err; }
 PDB_EXPORT int pdb200_abi_version() { return 2; }
 PDB_EXPORT int pdb200_sm_count() { return pdb::sm_count(); }

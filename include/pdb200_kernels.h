@@ -116,6 +116,9 @@ PDB_API int pdb200_gemm_set_group_m(int n);
 /* Tests on one GPU: emulation mode skips every cross-rank barrier, so the entry points can be called once per
  * emulated rank (segments of one GPU's memory as peer_ptrs, mc_ptr = 0), one after the other on one stream. */
 PDB_API int pdb200_nvl_set_emulation(int on);
+/* Optional trace: a mapped pinned host word (from pdb200_wd_progress_ptr of the runtime library) that every stand-alone
+ * barrier of the fused kernels overwrites with the epoch it just passed; 0 switches it off. */
+PDB_API int pdb200_nvl_set_progress(uint64_t host_mapped_ptr);
 PDB_API int pdb200_nvl_barrier(const uint64_t* peer_ptrs, int nranks, int rank, int64_t pad_off, int64_t epoch, void* stream);
 PDB_API int pdb200_nvl_allreduce(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t data_off, int64_t numel, int dtype, float scale, int64_t pad_off, int64_t epoch, int max_ctas, void* stream);
 PDB_API int pdb200_nvl_rs_adamw_ag(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t grad_off, int grad_dtype, int64_t param_off, int64_t shard_start, int64_t shard_numel, float* master, float* m, float* v, float lr, float beta1, float beta2, float eps, float weight_decay, const float* beta_pows, const float* grad_scale, const float* found_inf, const float* local_grad, int64_t pad_off, int64_t epoch, void* stream);

@@ -34,6 +34,15 @@ PDB_API int pdb200_wd_start(int rank, int timeout_ms, int poll_ms);
 PDB_API int pdb200_wd_stop();
 PDB_API int pdb200_wd_task_begin(int group, int64_t seq, const char* op, int64_t numel, int sync_op);
 PDB_API int pdb200_wd_task_end(int group, int64_t seq);
+/* Device-truth variants: begin records a CUDA start event on `stream` (returns 1 when events are in use), end records
+ * the end event; the polling thread / pdb200_wd_sweep retire tasks whose end event the GPU has passed, and timeouts are
+ * classified "not started" / "started, not finished" from the events (reference: nccl_comm_task.cc:90-140, 238-268). */
+PDB_API int pdb200_wd_task_begin_ev(int group, int64_t seq, const char* op, int64_t numel, int sync_op, void* stream);
+PDB_API int pdb200_wd_task_end_ev(int group, int64_t seq, void* stream);
+PDB_API int pdb200_wd_sweep();
+/* 64 bytes of mapped pinned host memory (UVA pointer, 0 without a GPU): word 0 = last barrier epoch passed by the fused
+ * NVLink kernels of this process (pass it to pdb200_nvl_set_progress of the kernel library). */
+PDB_API uint64_t pdb200_wd_progress_ptr();
 PDB_API int pdb200_wd_inflight();
 PDB_API int pdb200_wd_timeouts();
 PDB_API int pdb200_wd_set_abort(int abort_on_timeout);

@@ -238,6 +238,9 @@ class Task:
 
 
 def _finish(work, sync_op, post=None, tag=""):
+    if tag:
+        from . import watchdog
+        watchdog.task_enqueued(tag, work)
     t = Task(work, post, tag)
     if sync_op:
         t.wait()

@@ -43,24 +43,83 @@ def start(rank):
         return
     rt = _rt()
     if rt:
-        rt.pdb200_wd_start(int(rank), int(flag("comm_watchdog_timeout_ms")), 10000)
+        import atexit
+        atexit.register(shutdown)
+        poll = int(flag("comm_watchdog_poll_ms")) if "comm_watchdog_poll_ms" in _all_flags() else 10000
+        rt.pdb200_wd_start(int(rank), int(flag("comm_watchdog_timeout_ms")), poll)
+        rt.pdb200_wd_set_abort(int(bool(flag("comm_watchdog_abort"))) if "comm_watchdog_abort" in _all_flags() else 0)
+        # the fused kernels' barriers publish the last epoch they passed in a pinned host word the trace prints
+        if hasattr(rt.require(), "pdb200_wd_progress_ptr") and lib.have_kernels() and _cuda():
+            p = rt.pdb200_wd_progress_ptr()
+            if p:
+                lib.kernels.pdb200_nvl_set_progress(p)
+
+
+def _all_flags():
+    from ..framework import flags as F
+    return F._REGISTRY
+
+
+def _cuda():
+    import torch
+    return torch.cuda.is_available()
+
+
+def _stream():
+    import torch
+    return torch.cuda.current_stream().cuda_stream
 
 
 def task_started(group, op, numel, sync_op):
+    """Register a collective.  On a GPU the native manager records a CUDA start event on the current stream, so the
+    task's state ("not started" / "started, not finished" / done) is read from the device."""
     if not enabled():
         return ""
     with _lock:
         s = _seq.get(group.id, 0) + 1
         _seq[group.id] = s
         tag = f"{group.id}:{s}"
-        _inflight[tag] = (group.id, s, op, int(numel), bool(sync_op), time.time())
+        _inflight[tag] = [group.id, s, op, int(numel), bool(sync_op), time.time(), None, False]
     rt = _rt()
     if rt:
-        rt.pdb200_wd_task_begin(int(group.id), int(s), op.encode(), int(numel), int(bool(sync_op)))
+        if _cuda() and hasattr(rt.require(), "pdb200_wd_task_begin_ev"):
+            ev = rt.pdb200_wd_task_begin_ev(int(group.id), int(s), op.encode(), int(numel), int(bool(sync_op)), _stream())
+            _inflight[tag][7] = bool(ev)
+        else:
+            rt.pdb200_wd_task_begin(int(group.id), int(s), op.encode(), int(numel), int(bool(sync_op)))
+    _sweep()
     return tag
 
 
-def task_finished(tag):
+def task_enqueued(tag, work=None):
+    """The collective has been handed to the backend: remember its work handle so that an async task nobody waits on
+    can still be retired (``_sweep``)."""
+    rec = _inflight.get(tag) if tag else None
+    if rec is not None:
+        rec[6] = work
+
+
+def _sweep():
+    """Retire async tasks whose backend work handle reports completion (nobody has to call wait() on them)."""
+    done = []
+    with _lock:
+        for tag, rec in _inflight.items():
+            w = rec[6]
+            if w is not None and not rec[4]:
+                try:
+                    if w.is_completed():
+                        done.append(tag)
+                except Exception:  # noqa: BLE001
+                    pass
+    for tag in done:
+        task_finished(tag, device_done=True)
+
+
+def task_finished(tag, device_done=False):
+    """Called when ``wait()`` has made the current stream depend on the collective (or, ``device_done``, when the work
+    handle already reports completion).  With device events the end event is recorded on the current stream now and
+    the native manager retires the task once the GPU has passed it - so a collective that hangs on the device stays
+    "started, not finished" although the host returned from wait()."""
     if not tag:
         return
     with _lock:
@@ -69,18 +128,22 @@ def task_finished(tag):
             _last_done[rec[0]] = rec
     rt = _rt()
     if rt and rec:
-        rt.pdb200_wd_task_end(int(rec[0]), int(rec[1]))
+        if rec[7] and not device_done:
+            rt.pdb200_wd_task_end_ev(int(rec[0]), int(rec[1]), _stream())
+        else:
+            rt.pdb200_wd_task_end(int(rec[0]), int(rec[1]))
 
 
 def dump():
     """Trace lines for tasks still in flight (oldest first) and the last finished task per group."""
+    _sweep()
     now = time.time()
     lines = []
     with _lock:
-        for tag, (gid, s, op, numel, sync, t0) in sorted(_inflight.items(), key=lambda kv: kv[1][5]):
+        for tag, (gid, s, op, numel, sync, t0, _w, _e) in sorted(_inflight.items(), key=lambda kv: kv[1][5]):
             lines.append(f"[in-flight] group={gid} ranks={_groups.get(gid)} seq={s} op={op} numel={numel} sync={sync} "
                          f"age={now - t0:.1f}s")
-        for gid, (g, s, op, numel, sync, t0) in _last_done.items():
+        for gid, (g, s, op, numel, sync, t0, _w, _e) in _last_done.items():
             lines.append(f"[last-done] group={gid} seq={s} op={op} numel={numel}")
     return lines
 

@@ -12,6 +12,7 @@ never synchronises with the host.  On CPU the same math runs as torch ops (oracl
 """
 from __future__ import annotations
 
+import os
 from collections import OrderedDict, defaultdict
 
 import numpy as np
@@ -133,6 +134,9 @@ class Optimizer:
 
     @torch.no_grad()
     def step(self):
+        if os.environ.get("FAULT_INJECT"):
+            from ..distributed import fault
+            fault.tick()
         params_grads = self._collect_params_grads()
         self._apply_optimize(None, None, params_grads)
 

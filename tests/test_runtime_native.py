@@ -59,3 +59,34 @@ def test_flag_mirror():
     buf = ctypes.create_string_buffer(16)
     assert rt.pdb200_flag_get(b"use_fused_comm", buf, 16) == 1 and buf.value == b"1"
     assert rt.pdb200_flag_get(b"missing", buf, 16) == -1
+
+
+@pytest.mark.gpu
+def test_watchdog_reads_task_state_from_cuda_events():
+    """Device truth: a task stays in flight until the GPU passes its end event (nobody calls wait()), a task queued
+    behind a long kernel reads "not started", and the trace says which."""
+    import ctypes
+    import time
+    import torch
+    rt = lib.runtime.require()
+    st = torch.cuda.current_stream().cuda_stream
+    assert rt.pdb200_wd_start(0, 60000, 50) == 0
+    try:
+        torch.cuda.synchronize()
+        torch.cuda._sleep(int(2e9))                                   # ~1 s of GPU time ahead of both tasks
+        assert rt.pdb200_wd_task_begin_ev(3, 1, b"all_reduce", 4096, 0, st) == 1
+        torch.cuda._sleep(int(2e8))
+        assert rt.pdb200_wd_task_end_ev(3, 1, st) == 1
+        assert rt.pdb200_wd_inflight() == 1                            # enqueued, not finished on the device
+        buf = ctypes.create_string_buffer(4096)
+        rt.pdb200_wd_dump(buf, 4096)
+        assert b"state=not started" in buf.value, buf.value
+        torch.cuda.synchronize()
+        rt.pdb200_wd_sweep()
+        assert rt.pdb200_wd_inflight() == 0                            # retired by the end event, without any wait()
+        rt.pdb200_wd_dump(buf, 4096)
+        assert b"[last-done] rank=0 group=3 seq=1" in buf.value
+        p = rt.pdb200_wd_progress_ptr()
+        assert p != 0
+    finally:
+        rt.pdb200_wd_stop()
