@@ -210,7 +210,7 @@ class DataParallel(torch.nn.Module):
         params = [p for p in self._layers.parameters() if p.requires_grad]
         if not params:
             raise ValueError("This model does not have any parameters to train, and does not need to use DataParallel")
-        is_sparse = [False] * len(params)
+        is_sparse = [bool(getattr(p, "_is_sparse_grad", False)) for p in params]
         group_indices = assign_group_by_size(params, is_sparse, [self.last_comm_buffer_size, self.comm_buffer_size])
         allocator, fused = self._fused_comm_hooks(params)
         self._reducer = EagerReducer(params, list(reversed(group_indices)), is_sparse, self.group,

@@ -11,6 +11,12 @@ Differences by design (B200-first):
 * buckets launch strictly in order (Appendix B.3) from post-accumulate hooks; the tail is awaited in a callback
   queued on the autograd engine, which only makes the compute stream wait - the host never blocks.
 Bucket assignment itself is native (libpdb200_runtime.so ``pdb200_assign_group_by_size``) with a Python mirror.
+
+Sparse gradients (``Embedding(sparse=True)``; reference AllReduceSparse :1129-1350) live in singleton buckets and are
+reduced by gathering every rank's (row ids, values) and coalescing them - the dense bucket machinery never sees them.
+With ``find_unused_parameters`` every rank contributes a "used in this backward" bitmap that is MAX-reduced over the
+group (reference local_used_vars_ :996-1067): a parameter no rank used keeps ``grad = None`` (so weight decay or
+momentum do not move it), one that any rank used takes part in the all-reduce with zeros where it was unused.
 """
 from __future__ import annotations
 
@@ -115,11 +121,18 @@ class EagerReducer:
         self._fused = fused_allreduce          # callable(bucket_buffer, nranks) -> Task, or None for NCCL
         self.buckets = [_Bucket(i, [self.params[j] for j in idxs], self.params[idxs[0]].device)
                         for i, idxs in enumerate(group_indices)]
+        sparse = list(is_sparse_gradient) if is_sparse_gradient is not None else [False] * len(self.params)
+        self._sparse_ids = {id(p) for p, sp in zip(self.params, sparse) if sp}
         self._where = {}
         for b in self.buckets:
-            b.allocate(self._allocator)
+            b.sparse = len(b.params) == 1 and id(b.params[0]) in self._sparse_ids
+            if not b.sparse:
+                b.allocate(self._allocator)
             for i, p in enumerate(b.params):
                 self._where[id(p)] = (b, i)
+        self._index_of = {id(p): i for i, p in enumerate(self.params)}
+        self._used_task = None
+        self._used_bitmap = None
         self.next_bucket = 0
         self._armed = False
         self._callback_queued = False
@@ -149,6 +162,14 @@ class EagerReducer:
         if id(p) in b.marked:
             return
         b.marked.add(id(p))
+        if not self._callback_queued:
+            self._callback_queued = True
+            torch.autograd.Variable._execution_engine.queue_callback(self.finalize_backward)
+        if b.sparse:
+            b.pending = 0
+            b.ready = True
+            self._launch_ready()
+            return
         view = b.view(i)
         g = p.grad
         if g is not None and g.data_ptr() != view.data_ptr():
@@ -171,14 +192,60 @@ class EagerReducer:
             self.next_bucket += 1
 
     def _all_reduce(self, b):
+        if b.sparse:
+            return self._all_reduce_sparse(b.params[0])
         if self._fused is not None and flag("use_fused_comm"):
             return self._fused(b.buffer, self.nranks)
         return comm.all_reduce(b.buffer, op=ReduceOp.AVG, group=self.group, sync_op=False)
 
     @torch.no_grad()
+    def _all_reduce_sparse(self, p):
+        """AVG all-reduce of a sparse (COO) gradient: every rank's (row ids, values) are gathered - padded to the
+        largest count - concatenated and coalesced (reference: reducer.cc AllReduceSparse gathers rows and values of
+        the SelectedRows).  A rank without a gradient contributes zero rows."""
+        g = p.grad
+        dev = p.device
+        if g is None:
+            idx = torch.zeros(1, 0, dtype=torch.int64, device=dev)
+            val = torch.zeros((0,) + tuple(p.shape[1:]), dtype=p.dtype, device=dev)
+        else:
+            g = g.coalesce() if g.is_sparse else g.to_sparse(1)
+            idx, val = g.indices(), g.values()
+        n = self.nranks
+        cnt = torch.tensor([idx.shape[1]], dtype=torch.int64, device=dev)
+        cnts = [torch.zeros_like(cnt) for _ in range(n)]
+        comm.all_gather(cnts, cnt, self.group)
+        cnts = [int(c) for c in cnts]               # row counts are data dependent: one host read per sparse gradient
+        mx = max(max(cnts), 1)
+        pad_i = torch.zeros(mx, dtype=torch.int64, device=dev)
+        pad_i[: idx.shape[1]] = idx[0]
+        pad_v = torch.zeros((mx,) + tuple(p.shape[1:]), dtype=p.dtype, device=dev)
+        pad_v[: val.shape[0]] = val
+        all_i = [torch.empty_like(pad_i) for _ in range(n)]
+        all_v = [torch.empty_like(pad_v) for _ in range(n)]
+        comm.all_gather(all_i, pad_i, self.group)
+        comm.all_gather(all_v, pad_v, self.group)
+        rows = torch.cat([all_i[r][: cnts[r]] for r in range(n)])
+        vals = torch.cat([all_v[r][: cnts[r]] for r in range(n)]) / n
+        p.grad = torch.sparse_coo_tensor(rows[None], vals, size=tuple(p.shape), device=dev).coalesce()
+        return None
+
+    @torch.no_grad()
+    def _reduce_used_bitmap(self):
+        """MAX all-reduce of "received a gradient in this backward" over the group."""
+        dev = self.params[0].device
+        used = torch.zeros(len(self.params), dtype=torch.int32, device=dev)
+        marked = [self._index_of[id(p)] for b in self.buckets for p in b.params if id(p) in b.marked]
+        if marked:
+            used[torch.tensor(marked, dtype=torch.int64, device=dev)] = 1
+        comm.all_reduce(used, op=ReduceOp.MAX, group=self.group)
+        return used
+
+    @torch.no_grad()
     def finalize_backward(self):
         if not self._armed:
             return
+        globally_unused = []
         # buckets that never became ready hold unused parameters
         for b in self.buckets[self.next_bucket:]:
             if not b.ready:
@@ -188,16 +255,24 @@ class EagerReducer:
                     raise RuntimeError(
                         "DataParallel: some parameters did not receive a gradient in this backward "
                         f"({missing[:4]}...). Construct DataParallel with find_unused_parameters=True.")
-                for i, p in enumerate(b.params):
-                    if self._is_missing(b, p):
-                        b.view(i).zero_()
-                        p.grad = b.view(i)
+                if not b.sparse:
+                    for i, p in enumerate(b.params):
+                        if self._is_missing(b, p):
+                            b.view(i).zero_()
+                            p.grad = b.view(i)
                 b.ready = True
         self._launch_ready()
+        if self.find_unused:
+            # after the last bucket so that every rank issues its collectives in the same order; every rank takes part
+            # every step, because which parameters are unused may differ from rank to rank
+            self._used_bitmap = self._reduce_used_bitmap()
+            globally_unused = [self.params[i] for i, u in enumerate(self._used_bitmap.tolist()) if not u]
         for b in self.buckets:
             if b.task is not None:
                 b.task.wait()
                 b.task = None
+        for p in globally_unused:            # nobody produced a gradient for it: keep "no gradient", not zeros
+            p.grad = None
         self._armed = False
 
     def _is_missing(self, b, p):

@@ -28,7 +28,8 @@ def linear(x, weight, bias=None, name=None):
 def embedding(x, weight, padding_idx=None, sparse=False, name=None, max_norm=None, norm_type=2.0, scale_grad_by_freq=False):
     if padding_idx is not None and padding_idx < 0:
         padding_idx = weight.shape[0] + padding_idx
-    return TF.embedding(x.long() if x.dtype not in (torch.int32, torch.int64) else x, weight, padding_idx=padding_idx)
+    return TF.embedding(x.long() if x.dtype not in (torch.int32, torch.int64) else x, weight, padding_idx=padding_idx,
+                        sparse=bool(sparse))
 
 
 def one_hot(x, num_classes, name=None):

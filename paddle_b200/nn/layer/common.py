@@ -37,14 +37,16 @@ class Embedding(Layer):
         super().__init__()
         self._num_embeddings, self._embedding_dim = num_embeddings, embedding_dim
         self._padding_idx = None if padding_idx is None else (padding_idx if padding_idx >= 0 else num_embeddings + padding_idx)
+        self._sparse = bool(sparse)
         self.weight = self.create_parameter([num_embeddings, embedding_dim], attr=weight_attr, dtype=self._dtype,
                                             default_initializer=I.Normal(0.0, 1.0) if weight_attr is None else None)
+        self.weight._is_sparse_grad = self._sparse      # DataParallel's reducer routes it through the sparse path
         if self._padding_idx is not None:
             with torch.no_grad():
                 self.weight[self._padding_idx].zero_()
 
     def forward(self, x):
-        return F.embedding(x, self.weight, padding_idx=self._padding_idx)
+        return F.embedding(x, self.weight, padding_idx=self._padding_idx, sparse=self._sparse)
 
 
 class Dropout(Layer):

@@ -64,4 +64,55 @@ try:
     raise SystemExit("expected unused-parameter error")
 except RuntimeError as e:
     assert "find_unused_parameters" in str(e)
+
+# unused-parameter bitmap: `b` is unused on EVERY rank -> its gradient stays None (not zeros); a parameter used on
+# one rank only still takes part in the all-reduce everywhere
+assert t._layers.b.weight.grad is None and t._layers.a.weight.grad is not None
+
+
+class Sometimes(nn.Layer):
+    def __init__(self):
+        super().__init__()
+        self.a, self.b = nn.Linear(4, 4), nn.Linear(4, 4)
+
+    def forward(self, x, use_b):
+        y = self.a(x)
+        return y + self.b(x) if use_b else y
+
+
+paddle.seed(2)
+s = paddle.DataParallel(Sometimes(), find_unused_parameters=True)
+s(torch.ones(2, 4), use_b=(r == 0)).sum().backward()
+parts = []
+dist.all_gather(parts, s._layers.b.weight.grad)
+torch.testing.assert_close(parts[0], parts[1])            # rank 1 contributed zeros, both hold the average
+assert float(parts[0].abs().sum()) > 0
+
+# sparse gradients (Embedding(sparse=True)): rows are gathered and coalesced, result == dense all-reduce
+paddle.seed(4)
+
+
+class Emb(nn.Layer):
+    def __init__(self, sparse):
+        super().__init__()
+        self.e = nn.Embedding(50, 8, sparse=sparse)
+        self.fc = nn.Linear(8, 1)
+
+    def forward(self, ids):
+        return self.fc(self.e(ids)).sum()
+
+
+with paddle.utils.unique_name.guard():
+    es = Emb(True)
+with paddle.utils.unique_name.guard():
+    ed = Emb(False)
+ed.set_state_dict(es.state_dict())
+ds, dd = paddle.DataParallel(es), paddle.DataParallel(ed)
+assert any(b.sparse for b in ds._reducer.buckets)
+ids = torch.tensor([[1, 7, 7], [3 + r, 9, 1]])
+ds(ids).backward()
+dd(ids).backward()
+assert es.e.weight.grad.is_sparse
+torch.testing.assert_close(es.e.weight.grad.to_dense(), ed.e.weight.grad, rtol=1e-5, atol=1e-6)
+torch.testing.assert_close(es.fc.weight.grad, ed.fc.weight.grad, rtol=1e-5, atol=1e-6)
 print("data_parallel ok", r)
