@@ -24,19 +24,29 @@ def _to_numpy(t: torch.Tensor) -> np.ndarray:
     return t.numpy()  # patched: detach + cpu + bf16->uint16
 
 
+def _contains_tensor(obj):
+    if isinstance(obj, torch.Tensor):
+        return True
+    if isinstance(obj, dict):
+        return any(_contains_tensor(v) for v in obj.values())
+    if isinstance(obj, (list, tuple)):
+        return any(_contains_tensor(v) for v in obj)
+    return False
+
+
 def _is_state_dict(obj):
+    """The reference's predicate (io.py:130-150): a dict whose values are Tensors, or dicts that hold no Tensor at
+    any depth.  Anything else - an optimizer state with ``master_weights: {name: Tensor}``, a dict with a scalar at
+    the top level - is NOT a state dict and goes through the generic pickler (Tensors become (name, ndarray))."""
     if not isinstance(obj, dict):
         return False
-
-    def ok(v):
-        if isinstance(v, torch.Tensor):
-            return True
+    for v in obj.values():
         if isinstance(v, dict):
-            return all(ok(x) for x in v.values())
-        return isinstance(v, (int, float, str, bool, type(None), np.ndarray, list, tuple))
-    has_tensor = any(isinstance(v, torch.Tensor) or (isinstance(v, dict) and any(isinstance(x, torch.Tensor) for x in v.values()))
-                     for v in obj.values())
-    return has_tensor and all(ok(v) for v in obj.values())
+            if any(_contains_tensor(x) for x in v.values()):
+                return False
+        elif not isinstance(v, torch.Tensor):
+            return False
+    return True
 
 
 def _build_saved_state_dict(state_dict):
