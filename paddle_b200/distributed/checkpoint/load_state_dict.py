@@ -17,7 +17,10 @@ from .utils import flatten_state_dict
 
 
 def _load_metadata(path):
-    files = sorted(f for f in os.listdir(path) if f.endswith(".metadata"))
+    def uid(f):                                  # "<unique id>.metadata": numeric order, so save 10 comes after save 2
+        stem = f[: -len(".metadata")]
+        return (0, int(stem)) if stem.isdigit() else (1, stem)
+    files = sorted((f for f in os.listdir(path) if f.endswith(".metadata")), key=uid)
     assert files, f"no .metadata file found under {path}"
     mds = []
     for f in files:
@@ -55,7 +58,10 @@ def load_state_dict(state_dict, path, process_group=None, coordinator_rank=0):
                 continue
             gshape, goff = shard_info(target)
             filled = False
-            for md in mds:
+            # coverage of the target shard: every element must come from some stored shard (the newest save of a key
+            # wins, older ones only fill what it does not cover)
+            covered = torch.zeros(tuple(target.shape), dtype=torch.bool) if target.dim() > 0 else None
+            for md in reversed(mds):
                 if key not in md.state_dict_metadata:
                     continue
                 for ltm in md.state_dict_metadata[key]:
@@ -73,8 +79,18 @@ def load_state_dict(state_dict, path, process_group=None, coordinator_rank=0):
                         target.copy_(stored.to(target.device, target.dtype))
                     else:
                         cur_sl, st_sl = ov
-                        target[cur_sl].copy_(stored[st_sl].to(target.device, target.dtype))
+                        fresh = ~covered[cur_sl]
+                        if bool(fresh.all()):
+                            target[cur_sl].copy_(stored[st_sl].to(target.device, target.dtype))
+                        elif bool(fresh.any()):
+                            piece = target[cur_sl]
+                            m = fresh.to(target.device)
+                            piece[m] = stored[st_sl].to(target.device, target.dtype)[m]
+                        covered[cur_sl] = True
                     filled = True
             assert filled, f"key {key} not found in checkpoint {path}"
+            if covered is not None:
+                assert bool(covered.all()), (f"checkpoint {path} covers only {int(covered.sum())} of {covered.numel()} "
+                                             f"elements of {key} (target offset {goff}, shape {tuple(target.shape)})")
     if C.is_initialized() and C.get_world_size() > 1:
         C.barrier(process_group)
