@@ -4,8 +4,10 @@ process_mesh.py, placement_type.py; native DistTensor/reshard under paddle/phi/c
 A ``DistTensor`` here is a local torch tensor plus ``(process_mesh, placements)`` metadata: ``shard_tensor`` cuts the
 local shard out of the global value, ``reshard`` moves between placements with the matching collective
 (r->s slice, s->r all-gather, p->r all-reduce, p->s reduce-scatter, s->s all-to-all), ``unshard_dtensor`` rebuilds
-the global value.  SPMD propagation through ops (N13) is not implemented: layers are sharded explicitly with
-``shard_layer`` / the fleet TP layers."""
+the global value, and a change of mesh (same shape, other ranks) is a send / recv pair.  SPMD propagation (N13) lives
+in ``spmd_rules``: ``dist_op(name, fn, *dtensors)`` infers the shardings with the op's rule, reshards the inputs the
+rule asks for, runs ``fn`` on the local shards and labels the outputs (partial outputs stay ``Partial`` until someone
+reshards them)."""
 from __future__ import annotations
 
 import numpy as np
@@ -249,8 +251,29 @@ def _gather_axis(t, group, dim):
     return torch.cat(parts, dim=dim)
 
 
+def _cross_mesh(dist_tensor, mesh):
+    """Same placements on another mesh of the same shape: rank i of the source mesh sends its shard to rank i of the
+    destination mesh (reference: same_status_reshard_function.cc)."""
+    src_mesh = dist_tensor.process_mesh
+    assert list(src_mesh.shape) == list(mesh.shape), "cross-mesh reshard needs meshes of the same shape"
+    me = C.get_rank()
+    t = dist_tensor.detach()
+    out = t
+    for s_rank, d_rank in zip(src_mesh.process_ids, mesh.process_ids):
+        if s_rank == d_rank:
+            continue
+        if me == s_rank:
+            comm.send(t.contiguous(), d_rank)
+        elif me == d_rank:
+            out = torch.empty_like(t)
+            comm.recv(out, s_rank)
+    return _attach(out, mesh, dist_tensor.placements, dist_tensor._global_shape)
+
+
 def reshard(dist_tensor, mesh, placements):
     assert is_dist(dist_tensor), "reshard expects a tensor produced by shard_tensor"
+    if dist_tensor.process_mesh != mesh and C.get_world_size() > 1:
+        dist_tensor = _cross_mesh(dist_tensor, mesh)
     src = dist_tensor.placements
     gshape = dist_tensor._global_shape
     t = dist_tensor.detach() if not dist_tensor.requires_grad else dist_tensor
@@ -269,13 +292,27 @@ def reshard(dist_tensor, mesh, placements):
             if n > 1:
                 comm.all_reduce(t, a.reduce_type, g)
         elif isinstance(a, Partial) and isinstance(b, Shard):
-            t = t.clone()
-            if n > 1:
-                comm.all_reduce(t, a.reduce_type, g)
-            t = t.chunk(n, dim=b.dim)[coord[ax]].contiguous()
+            # p -> s: one reduce-scatter (reference p_to_s_reshard_function.cc), not all-reduce + slice
+            if n > 1 and t.shape[b.dim] % n == 0:
+                moved = t.movedim(b.dim, 0).contiguous()
+                out = torch.empty((moved.shape[0] // n,) + tuple(moved.shape[1:]), dtype=t.dtype, device=t.device)
+                comm.reduce_scatter(out, moved, a.reduce_type, g)
+                t = out.movedim(0, b.dim).contiguous()
+            else:
+                t = t.clone()
+                if n > 1:
+                    comm.all_reduce(t, a.reduce_type, g)
+                t = t.chunk(n, dim=b.dim)[coord[ax]].contiguous()
         elif isinstance(a, Shard) and isinstance(b, Shard):
-            full = _gather_axis(t, g, a.dim) if n > 1 else t
-            t = full.chunk(n, dim=b.dim)[coord[ax]].contiguous()
+            # s -> s on another dim: one all-to-all (reference s_to_s_reshard_function.cc)
+            if n > 1 and t.shape[b.dim] % n == 0:
+                pieces = [c.contiguous() for c in t.chunk(n, dim=b.dim)]
+                recv = [torch.empty_like(pieces[0]) for _ in range(n)]
+                comm.alltoall(recv, pieces, g)
+                t = torch.cat(recv, dim=a.dim)
+            else:
+                full = _gather_axis(t, g, a.dim) if n > 1 else t
+                t = full.chunk(n, dim=b.dim)[coord[ax]].contiguous()
         elif isinstance(a, Replicate) and isinstance(b, Partial):
             t = t if coord[ax] == 0 else torch.zeros_like(t)
         elif isinstance(a, Shard) and isinstance(b, Partial):
@@ -284,6 +321,30 @@ def reshard(dist_tensor, mesh, placements):
         else:
             raise NotImplementedError(f"reshard {a} -> {b}")
     return _attach(t, mesh, placements, gshape)
+
+
+def dist_op(op_name, fn, *dtensors, **attrs):
+    """Run ``fn`` on the local shards of ``dtensors`` under the SPMD rule ``op_name`` (see ``spmd_rules``): inputs are
+    resharded to what the rule requires, outputs come back labelled with the inferred placements."""
+    from . import spmd_rules as R
+    mesh = next(t.process_mesh for t in dtensors if is_dist(t))
+    specs = []
+    for t in dtensors:
+        assert is_dist(t), "dist_op takes distributed tensors (see shard_tensor)"
+        specs.append(R.DistTensorSpec.from_placements(t._global_shape, t.placements))
+    new_specs, out_specs = R.infer_forward(op_name, *specs, **attrs)
+    locals_ = []
+    for t, want in zip(dtensors, new_specs):
+        pl = want.placements(mesh.ndim)
+        # a partial input the rule did not ask to keep partial is reduced first
+        cur = [p if not p.is_partial() else Replicate() for p in t.placements] if any(p.is_partial() for p in t.placements) else t.placements
+        if any(p.is_partial() for p in t.placements):
+            t = reshard(t, mesh, cur)
+        locals_.append(t if list(t.placements) == list(pl) else reshard(t, mesh, pl))
+    res = fn(*locals_)
+    outs = res if isinstance(res, (tuple, list)) else [res]
+    labelled = [_attach(o, mesh, sp.placements(mesh.ndim), sp.shape) for o, sp in zip(outs, out_specs)]
+    return labelled if isinstance(res, (tuple, list)) else labelled[0]
 
 
 def unshard_dtensor(dist_tensor):

@@ -15,6 +15,10 @@ def test_data_parallel_reducer_parity():
     run_dist("data_parallel.py", 2)
 
 
+def test_auto_parallel_reshard_and_spmd_ops():
+    run_dist("auto_parallel.py", 2)
+
+
 def test_tp_layers_shard_vs_whole():
     run_dist("tp_layers.py", 2)
 
