@@ -53,8 +53,10 @@ def parse_header(path: Path):
 
 
 class NativeLib:
-    def __init__(self, so_name: str, header: str):
+    def __init__(self, so_name: str, header: str, env_override: str = ""):
         self.so_path = _LIB_DIR / so_name
+        if env_override and os.environ.get(env_override):      # sanitizer builds (tools/sanitize.sh)
+            self.so_path = Path(os.environ[env_override])
         self.header = _ROOT / "include" / header
         self._dll = None
         self._err = None
@@ -126,7 +128,7 @@ def reset_launch_count():
 
 
 kernels = NativeLib("libpdb200_kernels.so", "pdb200_kernels.h")
-runtime = NativeLib("libpdb200_runtime.so", "pdb200_runtime.h")
+runtime = NativeLib("libpdb200_runtime.so", "pdb200_runtime.h", env_override="PDB200_RUNTIME_LIB")
 
 
 class KernelError(RuntimeError):
