@@ -30,6 +30,8 @@
 
 #include "rt_common.h"
 
+extern "C" int pdb200_pg_check_async_errors();      // process_group.cc: ncclCommGetAsyncError over the live communicators
+
 namespace pdbrt {
 
 struct TaskRec {
@@ -170,6 +172,9 @@ class Watchdog {
       auto now = std::chrono::steady_clock::now();
       bool fatal = false;
       sweep_locked();
+      lk.unlock();
+      pdb200_pg_check_async_errors();               // a communicator in error is aborted so blocked kernels return
+      lk.lock();
       for (auto& kv : inflight_) {
         TaskRec& t = kv.second;
         auto age = std::chrono::duration_cast<std::chrono::milliseconds>(now - t.start).count();

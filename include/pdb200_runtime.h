@@ -48,6 +48,34 @@ PDB_API int pdb200_wd_timeouts();
 PDB_API int pdb200_wd_set_abort(int abort_on_timeout);
 PDB_API int64_t pdb200_wd_dump(char* out, int64_t capacity);
 
+/* Native process group over NCCL (reference: fluid/distributed/collective/process_group_nccl.cc:160-1016,
+ * phi/core/distributed/nccl_comm_context.cc, comm_context_manager.cc:61-110).  pdb200_pg_create is collective over the
+ * group: rank 0 publishes the NCCL unique id in the given pdb200_store under "<prefix>/nccl_id/<gid>".  Every collective
+ * returns a task handle (null on failure).  use_calc_stream = 1 runs on `calc_stream` itself; otherwise the group's
+ * communication stream runs it after an event recorded on `calc_stream`, and pdb200_pg_task_wait makes a stream wait
+ * for the result ON THE DEVICE.  dtype: 0 f32, 1 bf16, 2 f16, 3 f64, 4 i32, 5 i64, 6 u8, 7 i8.  op: 0 sum, 1 max, 2 min,
+ * 3 prod, 4 avg.  Tasks are registered with the watchdog (CUDA events); its thread polls ncclCommGetAsyncError and
+ * aborts a communicator in error. */
+PDB_API int pdb200_pg_available();
+PDB_API int pdb200_pg_nccl_version();
+PDB_API void* pdb200_pg_create(void* store, const char* prefix, int gid, int rank, int nranks, int timeout_ms);
+PDB_API int pdb200_pg_destroy(void* pg);
+PDB_API uint64_t pdb200_pg_comm_stream(void* pg);
+PDB_API int pdb200_pg_abort(void* pg);
+PDB_API int pdb200_pg_check_async_errors();
+PDB_API void* pdb200_pg_all_reduce(void* pg, const void* in, void* out, int64_t numel, int dtype, int op, void* calc_stream, int use_calc_stream, int sync_op);
+PDB_API void* pdb200_pg_broadcast(void* pg, const void* in, void* out, int64_t numel, int dtype, int root, void* calc_stream, int use_calc_stream, int sync_op);
+PDB_API void* pdb200_pg_reduce(void* pg, const void* in, void* out, int64_t numel, int dtype, int op, int root, void* calc_stream, int use_calc_stream, int sync_op);
+PDB_API void* pdb200_pg_all_gather(void* pg, const void* in, void* out, int64_t numel_per_rank, int dtype, void* calc_stream, int use_calc_stream, int sync_op);
+PDB_API void* pdb200_pg_reduce_scatter(void* pg, const void* in, void* out, int64_t numel_per_rank, int dtype, int op, void* calc_stream, int use_calc_stream, int sync_op);
+PDB_API void* pdb200_pg_all_to_all(void* pg, const void* in, void* out, int64_t numel_per_rank, int dtype, void* calc_stream, int use_calc_stream, int sync_op);
+PDB_API void* pdb200_pg_send(void* pg, const void* in, int64_t numel, int dtype, int peer, void* calc_stream, int use_calc_stream, int sync_op);
+PDB_API void* pdb200_pg_recv(void* pg, void* out, int64_t numel, int dtype, int peer, void* calc_stream, int use_calc_stream, int sync_op);
+PDB_API int pdb200_pg_task_wait(void* task, void* calc_stream);
+PDB_API int pdb200_pg_task_is_completed(void* task);
+PDB_API int pdb200_pg_task_synchronize(void* task);
+PDB_API int pdb200_pg_task_free(void* pg, void* task);
+
 /* Gradient bucket assignment (reference: paddle/fluid/distributed/collective/reducer.cc:47-158
  * Eager_AssignGroupBySize).  sizes: bytes per tensor, dtype_ids: small ints, is_sparse: 0/1, limits: bytes;
  * out_group[i] = bucket index of tensor i (buckets ordered by their first tensor).  Returns the bucket count. */

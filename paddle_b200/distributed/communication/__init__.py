@@ -25,6 +25,27 @@ def _trivial(g):
     return g.nranks == 1 or not tdist.is_initialized()
 
 
+def _native(g, *tensors):
+    """The native process group of ``g`` when FLAGS_use_native_process_group routes these tensors through it."""
+    from .. import native_pg
+    if _state.backend != "nccl" or not all(native_pg.enabled_for(t) and t.is_contiguous() for t in tensors):
+        return None
+    return native_pg.NativeProcessGroup.for_group(g)
+
+
+class _NativeWork:
+    """Adapts a NativeTask to the torch Work interface ``Task`` expects."""
+
+    def __init__(self, task):
+        self._t = task
+
+    def wait(self):
+        return self._t.wait()
+
+    def is_completed(self):
+        return self._t.is_completed()
+
+
 def _is_gloo():
     return _state.backend == "gloo"
 
@@ -59,6 +80,10 @@ def all_reduce(tensor, op=ReduceOp.SUM, group=None, sync_op=True, use_calc_strea
     tag = _wd.task_started(g, "all_reduce", tensor.numel(), sync_op)
     if _trivial(g):
         return _finish(None, sync_op, tag=tag)
+    npg = _native(g, tensor)
+    if npg is not None:
+        with torch.no_grad():
+            return _finish(_NativeWork(npg.all_reduce(tensor, op, sync_op=False, use_calc_stream=use_calc_stream)), sync_op, tag=tag)
     px = _F32Proxy(tensor)
     top = op
     post_scale = None
@@ -86,6 +111,10 @@ def broadcast(tensor, src, group=None, sync_op=True, use_calc_stream=False):
         return _finish(None, sync_op, tag=tag)
     if src not in g.ranks:
         raise ValueError(f"src rank {src} is not in group {g.ranks}")
+    npg = _native(g, tensor)
+    if npg is not None:
+        with torch.no_grad():
+            return _finish(_NativeWork(npg.broadcast(tensor, src, sync_op=False, use_calc_stream=use_calc_stream)), sync_op, tag=tag)
     with torch.no_grad():
         work = tdist.broadcast(tensor, src=src, group=g.process_group, async_op=True)
     return _finish(work, sync_op, tag=tag)
@@ -132,6 +161,10 @@ def all_gather(tensor_or_tensor_list, tensor, group=None, sync_op=True, use_calc
             with torch.no_grad():
                 out.reshape(-1).copy_(tensor.reshape(-1))
             return _finish(None, sync_op, tag=tag)
+        npg = _native(g, out, tensor)
+        if npg is not None:
+            with torch.no_grad():
+                return _finish(_NativeWork(npg.all_gather(out, tensor, sync_op=False, use_calc_stream=use_calc_stream)), sync_op, tag=tag)
         with torch.no_grad():
             work = tdist.all_gather_into_tensor(out.view(-1) if out.is_contiguous() else out, tensor.contiguous().view(-1),
                                                 group=g.process_group, async_op=True) \
@@ -196,6 +229,11 @@ def reduce_scatter(tensor, tensor_or_tensor_list, op=ReduceOp.SUM, group=None, s
                     part = part / n
                 tensor.copy_(part.view_as(tensor).to(tensor.dtype))
         return _finish(work, sync_op, post, tag)
+    npg = _native(g, tensor, flat_in)
+    if npg is not None:
+        with torch.no_grad():
+            return _finish(_NativeWork(npg.reduce_scatter(tensor, flat_in, op, sync_op=False, use_calc_stream=use_calc_stream)),
+                           sync_op, tag=tag)
     with torch.no_grad():
         out = tensor if tensor.is_contiguous() else tensor.contiguous()
         work = tdist.reduce_scatter_tensor(out.view(-1), flat_in, op=C._TORCH_OP[op], group=g.process_group, async_op=True)

@@ -27,6 +27,12 @@ def test_nvl_fused_kernels_match_nccl():
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_native_process_group_matches_torch_distributed():
+    out = _run("native_pg.py", 2)
+    assert "native_pg ok" in out.stdout
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
 def test_moe_fused_dispatch_combine_matches_nccl():
     out = _run("moe_fused.py", min(torch.cuda.device_count(), 8))
     assert "moe_fused ok" in out.stdout
