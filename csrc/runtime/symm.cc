@@ -19,6 +19,8 @@
 #include <sys/un.h>
 #include <unistd.h>
 
+#include <cuda_runtime.h>
+
 #include <atomic>
 #include <chrono>
 #include <string>
@@ -251,6 +253,8 @@ class Arena {
 
   int64_t bytes() const { return (int64_t)size_; }
   uint64_t peer(int p) const { return (p >= 0 && p < n_) ? (uint64_t)ptrs_[p] : 0; }
+  int nranks() const { return n_; }
+  int rank() const { return rank_; }
   uint64_t mc() const { return (uint64_t)mc_ptr_; }
 
  private:
@@ -370,4 +374,31 @@ PDB_RT_EXPORT int pdb200_symm_supported(int device) {
   d.cuDeviceGetAttribute(&fd, CU_DEVICE_ATTRIBUTE_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR_SUPPORTED, dev);
   d.cuDeviceGetAttribute(&mc, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, dev);
   return (vmm && fd) ? (mc ? 2 : 1) : 0;
+}
+
+// Copy-engine all-gather over the arena's peer mappings: for every segment {src_off, dst_off, shard_bytes} this rank's
+// shard (at src_off of its own segment) is copied to [dst_off + rank * shard_bytes) of EVERY rank's segment with plain
+// device-to-device copies on `stream` - the DMA engines move the bytes over NVLink, no SM runs a copy kernel, so the
+// transfer does not take issue slots or L2 bandwidth from the GEMMs it overlaps.  The caller brackets the call with
+// the cross-rank barriers (pdb200_nvl_barrier of the kernel library) like every other collective on the arena.
+// (The reference moves parameters with ncclAllGather kernels on SMs: group_sharded_stage3.py:849-896.)
+PDB_RT_EXPORT int pdb200_symm_allgather_ce(void* a, const int64_t* segs, int nseg, void* stream) {
+  pdbrt::Arena* A = (pdbrt::Arena*)a;
+  const int n = A->nranks(), r = A->rank();
+  cudaStream_t st = (cudaStream_t)stream;
+  for (int k = 0; k < nseg; ++k) {
+    const int64_t so = segs[3 * k], dof = segs[3 * k + 1], nb = segs[3 * k + 2];
+    if (nb <= 0) continue;
+    const char* src = (const char*)(uintptr_t)A->peer(r) + so;
+    for (int i = 0; i < n; ++i) {
+      const int p = (r + i) % n;                       // local copy first, then walk the peers (spreads the ingress)
+      char* dst = (char*)(uintptr_t)A->peer(p) + dof + (int64_t)r * nb;
+      cudaError_t e = cudaMemcpyAsync(dst, src, (size_t)nb, cudaMemcpyDeviceToDevice, st);
+      if (e != cudaSuccess) {
+        pdbrt::set_error("symm_allgather_ce: cudaMemcpyAsync to rank %d failed: %s", p, cudaGetErrorString(e));
+        return -1;
+      }
+    }
+  }
+  return 0;
 }

@@ -96,6 +96,10 @@ PDB_API int64_t pdb200_symm_bytes(void* arena);
 PDB_API uint64_t pdb200_symm_peer_ptr(void* arena, int peer);
 PDB_API uint64_t pdb200_symm_multicast_ptr(void* arena);
 PDB_API int pdb200_symm_supported(int device);
+/* All-gather on the copy engines: segs = HOST array of nseg int64 triples {src_off, dst_off, shard_bytes}; this rank's
+ * shard goes to [dst_off + rank * shard_bytes) of every rank's segment with cudaMemcpyAsync on `stream` (no SM work).
+ * Bracket it with the arena's cross-rank barriers like the kernel collectives. */
+PDB_API int pdb200_symm_allgather_ce(void* arena, const int64_t* segs, int nseg, void* stream);
 
 #ifdef __cplusplus
 }

@@ -81,7 +81,11 @@ class _NvlTransport:
         # grid caps of the transport kernels (CTAs of 256 threads, 32 KB in flight each, <= 32 K registers so that
         # they co-reside with a GEMM CTA): bytes in flight, not CTAs, set the link bandwidth
         self.ag_ctas = int(os.environ.get("PDB200_STAGE3_AG_CTAS", "64"))
-        self.rs_ctas = int(os.environ.get("PDB200_STAGE3_RS_CTAS", "64"))
+        self.rs_ctas = int(os.environ.get("PDB200_STAGE3_RS_CTAS", "128"))
+        # parameter all-gather: "ce" = copy engines (no SM work at all), "kernel" = the multimem / peer-store kernel
+        self.ag_mode = os.environ.get("PDB200_STAGE3_AG", "ce")
+        if not hasattr(symm.lib.runtime.require(), "pdb200_symm_allgather_ce"):
+            self.ag_mode = "kernel"
         # timing experiments only: skip the transport kernels ("ag", "rs" or "all"); numerics become garbage
         self.noop = {"0": "", "1": "all"}.get(os.environ.get("PDB200_STAGE3_COMM_NOOP", ""), os.environ.get("PDB200_STAGE3_COMM_NOOP", ""))
         self.slots = None
@@ -135,7 +139,10 @@ class _NvlTransport:
         with torch.cuda.stream(self.stream):
             self.stream.wait_event(ev)
             if self.noop not in ("ag", "all", True):
-                self.symm.allgather_multi(self.arena, segs, self.ag_ctas, self.stream.cuda_stream)
+                if self.ag_mode == "ce":
+                    self.symm.allgather_copy_engine(self.arena, segs, self.stream.cuda_stream)
+                else:
+                    self.symm.allgather_multi(self.arena, segs, self.ag_ctas, self.stream.cuda_stream)
             done = torch.cuda.Event()
             done.record(self.stream)
         return fulls, done

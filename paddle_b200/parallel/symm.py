@@ -235,6 +235,21 @@ def allgather_multi(arena, segs, max_ctas=0, stream=None):
     _multi(arena, "pdb200_nvl_allgather_multi", segs, (), max_ctas, st)
 
 
+def allgather_copy_engine(arena, segs, stream=None):
+    """The same all-gather on the copy engines: one device-to-device copy per (segment, peer) through the arena's peer
+    mappings, bracketed by the arena's cross-rank barriers.  No SM runs a copy loop, so the transfer takes neither
+    issue slots nor L2 bandwidth from the kernels it overlaps; the price is 2 tiny barrier launches and
+    ``len(segs) * nranks`` copy submissions (issued from native code)."""
+    from paddle_b200.lib import check
+    st = stream if stream is not None else stream_ptr(torch.device("cuda", torch.cuda.current_device()))
+    e = arena.next_epoch()
+    check(lib.kernels.pdb200_nvl_barrier(arena.peers_arg, arena.nranks, arena.rank, 0, e, st), "nvl_barrier")
+    flat = (ctypes.c_int64 * (3 * len(segs)))(*[int(v) for seg in segs for v in seg])
+    if arena._rt.pdb200_symm_allgather_ce(arena._h, ctypes.cast(flat, ctypes.c_void_p), len(segs), st) != 0:
+        raise RuntimeError(f"symm_allgather_ce: {arena._rt.pdb200_rt_last_error().decode()}")
+    check(lib.kernels.pdb200_nvl_barrier(arena.peers_arg, arena.nranks, arena.rank, 0, e + 1, st), "nvl_barrier")
+
+
 def reduce_scatter_multi(arena, segs, grad_dtype, scale, accumulate=False, max_ctas=0, stream=None):
     """One launch reduce-scatters several staged buffers: segs = [(stage_off, shard_numel, out_ptr), ...];
     ``out (+)= scale * sum over ranks of stage[rank * shard_numel : (rank + 1) * shard_numel]`` (fp32, local)."""
