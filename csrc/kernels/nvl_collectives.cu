@@ -542,6 +542,43 @@ __global__ void __launch_bounds__(256, 2) reduce_scatter_multi_kernel(Peers P, R
   grid_barrier_end(P, pad_off, epoch + 1, spin_limit);       // every rank has pulled: the stages may be rewritten
 }
 
+// Local half of the copy-engine reduce-scatter: slot r of `recv` holds rank r's contribution to this rank's shard
+// (landed there by pdb200_symm_alltoall_ce); out (+)= scale * sum of the nranks slots.  Reads local memory only.
+struct SlotSeg { const void* recv; int64_t shard_numel; float* out; };
+struct SlotSegs { SlotSeg s[kMaxSegs]; int n; };
+template <typename G>
+__global__ void __launch_bounds__(256, 2) reduce_slots_multi_kernel(SlotSegs S, int nranks, float scale, int accumulate) {
+  constexpr int E = RsTraits<G>::kElems;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int k = 0; k < S.n; ++k) {
+    const int64_t nvec = S.s[k].shard_numel / E;
+    const uint8_t* base = reinterpret_cast<const uint8_t*>(S.s[k].recv);
+    const int64_t slot_bytes = S.s[k].shard_numel * (int64_t)sizeof(G);
+    float* __restrict__ out = S.s[k].out;
+    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < nvec; j += stride) {
+      float g[E];
+#pragma unroll
+      for (int e = 0; e < E; ++e) g[e] = 0.f;
+      for (int p0 = 0; p0 < nranks; p0 += 4) {             // 4 slots' loads in flight together
+        uint4 r[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (p0 + u < nranks) r[u] = ld_peer_v4(base + (int64_t)(p0 + u) * slot_bytes + j * 16);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          if (p0 + u < nranks) {
+            float t[E];
+            rs_unpack<G>(r[u], t);
+#pragma unroll
+            for (int e = 0; e < E; ++e) g[e] += t[e];
+          }
+        }
+      }
+      rs_store<G>(out + j * E, g, scale, accumulate);
+    }
+  }
+}
+
 // NVLS or plain peer access?  An all-gather through the switch loops this rank's own shard back over NVLink and a
 // switch reduction pulls every rank's full buffer out of its memory, so with few ranks peer loads / stores move
 // fewer bytes; with many ranks the switch saves (n-1)x the store / load instructions and, for the reduction, the
@@ -841,4 +878,33 @@ PDB_EXPORT int pdb200_nvl_reduce_scatter_multi(const uint64_t* peer_ptrs, uint64
   else
     reduce_scatter_multi_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(P, S, scale, accumulate, (uint64_t)pad_off, (uint32_t)epoch, g_emulate ? kNoBarrier : kSpinLimit);
   return check_launch("nvl_reduce_scatter_multi");
+}
+
+// Local sum of receive slots: segs (HOST) = nseg triples {recv_ptr (local device pointer), shard_numel, out_ptr (fp32)}.
+PDB_EXPORT int pdb200_reduce_slots_multi(const int64_t* segs, int nseg, int nranks, int grad_dtype, float scale, int accumulate,
+                                         int max_ctas, void* stream) {
+  PDB_REQUIRE(nseg >= 1 && nseg <= kMaxSegs, "reduce_slots_multi: 1..%d segments per launch (got %d)", kMaxSegs, nseg);
+  PDB_REQUIRE(nranks >= 1 && nranks <= kMaxRanks, "reduce_slots_multi: nranks %d out of range", nranks);
+  PDB_REQUIRE(grad_dtype == PDB_DTYPE_F32 || grad_dtype == PDB_DTYPE_BF16, "reduce_slots_multi: grads must be fp32 or bf16");
+  SlotSegs S{};
+  S.n = nseg;
+  int64_t most = 0;
+  const int E = grad_dtype == PDB_DTYPE_F32 ? 4 : 8;
+  for (int k = 0; k < nseg; ++k) {
+    const void* recv = reinterpret_cast<const void*>((uintptr_t)segs[3 * k]);
+    const int64_t ne = segs[3 * k + 1];
+    float* out = reinterpret_cast<float*>((uintptr_t)segs[3 * k + 2]);
+    PDB_REQUIRE(ne >= 0 && ne % 8 == 0 && ((uintptr_t)recv & 15) == 0 && ((uintptr_t)out & 15) == 0 && out && recv,
+                "reduce_slots_multi: segment %d: shard must be a multiple of 8 elements, 16-byte aligned", k);
+    S.s[k] = SlotSeg{recv, ne, out};
+    if (ne / E > most) most = ne / E;
+  }
+  int64_t blocks = (most + 255) / 256;
+  const int64_t cap = max_ctas > 0 ? max_ctas : (int64_t)sm_count() * 2;
+  if (blocks > cap) blocks = cap;
+  const unsigned grid = (unsigned)(blocks < 1 ? 1 : blocks);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (grad_dtype == PDB_DTYPE_F32) reduce_slots_multi_kernel<float><<<grid, 256, 0, st>>>(S, nranks, scale, accumulate);
+  else reduce_slots_multi_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(S, nranks, scale, accumulate);
+  return check_launch("reduce_slots_multi");
 }

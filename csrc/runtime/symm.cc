@@ -402,3 +402,28 @@ PDB_RT_EXPORT int pdb200_symm_allgather_ce(void* a, const int64_t* segs, int nse
   }
   return 0;
 }
+
+// Copy-engine all-to-all, the transfer half of a reduce-scatter: for every segment {src_off, dst_off, shard_bytes} shard p
+// of this rank's buffer (src_off + p * shard_bytes) is copied into slot `rank` of rank p's receive buffer
+// (dst_off + rank * shard_bytes).  A local kernel then sums the nranks slots (pdb200_reduce_slots_multi of the kernel
+// library), so the only SM work of the reduce-scatter reads local memory.
+PDB_RT_EXPORT int pdb200_symm_alltoall_ce(void* a, const int64_t* segs, int nseg, void* stream) {
+  pdbrt::Arena* A = (pdbrt::Arena*)a;
+  const int n = A->nranks(), r = A->rank();
+  cudaStream_t st = (cudaStream_t)stream;
+  for (int k = 0; k < nseg; ++k) {
+    const int64_t so = segs[3 * k], dof = segs[3 * k + 1], nb = segs[3 * k + 2];
+    if (nb <= 0) continue;
+    for (int i = 0; i < n; ++i) {
+      const int p = (r + i) % n;
+      const char* src = (const char*)(uintptr_t)A->peer(r) + so + (int64_t)p * nb;
+      char* dst = (char*)(uintptr_t)A->peer(p) + dof + (int64_t)r * nb;
+      cudaError_t e = cudaMemcpyAsync(dst, src, (size_t)nb, cudaMemcpyDeviceToDevice, st);
+      if (e != cudaSuccess) {
+        pdbrt::set_error("symm_alltoall_ce: cudaMemcpyAsync to rank %d failed: %s", p, cudaGetErrorString(e));
+        return -1;
+      }
+    }
+  }
+  return 0;
+}

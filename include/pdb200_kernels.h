@@ -135,6 +135,9 @@ PDB_API int pdb200_nvl_allgather_from(const uint64_t* peer_ptrs, uint64_t mc_ptr
  * reduce-scatter triple = {stage_off, shard_numel, local fp32 out pointer}: out (+)= scale * sum_r stage_r[shard]. */
 PDB_API int pdb200_nvl_allgather_multi(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, const int64_t* segs, int nseg, int64_t pad_off, int64_t epoch, int max_ctas, void* stream);
 PDB_API int pdb200_nvl_reduce_scatter_multi(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, const int64_t* segs, int nseg, int grad_dtype, float scale, int accumulate, int64_t pad_off, int64_t epoch, int max_ctas, void* stream);
+/* Local half of the copy-engine reduce-scatter: out (+)= scale * sum over the nranks receive slots; segs = HOST triples
+ * {recv pointer (local), shard_numel, fp32 out pointer}. */
+PDB_API int pdb200_reduce_slots_multi(const int64_t* segs, int nseg, int nranks, int grad_dtype, float scale, int accumulate, int max_ctas, void* stream);
 /* Sum reduce-scatter of a symmetric bf16 buffer into a local bf16 shard (tail of GEMM -> reduce-scatter; NVLS in-switch add). */
 PDB_API int pdb200_nvl_rs_sum_bf16(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t src_off, int64_t shard_start, int64_t shard_numel, void* out, int64_t pad_off, int64_t epoch, void* stream);
 PDB_API int pdb200_nvl_ce_combine(const uint64_t* peer_ptrs, int nranks, int rank, int64_t stats_off, const int64_t* labels, float* loss, float* lse, int64_t rows, int64_t ignore_index, int64_t pad_off, int64_t epoch, void* stream);

@@ -75,7 +75,12 @@ class _NvlTransport:
         self.GSTAGES = max(1, int(os.environ.get("PDB200_STAGE3_GSTAGES", "3")))
         slice_bytes = sum(al(_padded_numel(p, n) // n * p.element_size()) for ps in units_params for p in ps)
         self.slot_bytes = max(sum(al(_padded_numel(p, n) * p.element_size()) for p in ps) for ps in units_params)
-        total = slice_bytes + (self.SLOTS + self.GSTAGES) * self.slot_bytes + (8 << 20)
+        # gradient reduce-scatter: "ce" = copy-engine all-to-all + local sum kernel, "kernel" = multimem / peer-load kernel
+        self.rs_mode = os.environ.get("PDB200_STAGE3_RS", "ce")
+        if not hasattr(symm.lib.runtime.require(), "pdb200_symm_alltoall_ce"):
+            self.rs_mode = "kernel"
+        n_recv = self.GSTAGES if self.rs_mode == "ce" else 0
+        total = slice_bytes + (self.SLOTS + self.GSTAGES + n_recv) * self.slot_bytes + (8 << 20)
         self.arena = symm.SymmArena(group, total)
         self.stream = torch.cuda.Stream(device=device, priority=-1)
         # grid caps of the transport kernels (CTAs of 256 threads, 32 KB in flight each, <= 32 K registers so that
@@ -100,6 +105,7 @@ class _NvlTransport:
         """Called after every slice has been placed: the slot ring and the gradient stages take the rest."""
         self.slots = [self.arena.empty((self.slot_bytes,), torch.uint8) for _ in range(self.SLOTS)]
         self.gstages = [self.arena.empty((self.slot_bytes,), torch.uint8) for _ in range(self.GSTAGES)]
+        self.grecv = [self.arena.empty((self.slot_bytes,), torch.uint8) for _ in range(self.GSTAGES)] if self.rs_mode == "ce" else []
 
     def new_slice(self, numel, dtype):
         return self.arena.empty((numel,), dtype)
@@ -175,8 +181,15 @@ class _NvlTransport:
         with torch.cuda.stream(self.stream):
             self.stream.wait_event(ev)
             if self.noop not in ("rs", "all", True) and segs:
-                self.symm.reduce_scatter_multi(self.arena, segs, unit.params[0].dtype, 1.0 / n, accumulate, self.rs_ctas,
-                                               self.stream.cuda_stream)
+                if self.rs_mode == "ce":
+                    # same layout in the receive buffer as in the stage: parameter k's slots start where its stage starts
+                    roff = self.grecv[unit.gstage]._symm[1] - self.gstages[unit.gstage]._symm[1]
+                    segs4 = [(so, so + roff, ne, o) for (so, ne, o) in segs]
+                    self.symm.reduce_scatter_copy_engine(self.arena, segs4, unit.params[0].dtype, 1.0 / n, accumulate, 0,
+                                                         self.stream.cuda_stream)
+                else:
+                    self.symm.reduce_scatter_multi(self.arena, segs, unit.params[0].dtype, 1.0 / n, accumulate, self.rs_ctas,
+                                                   self.stream.cuda_stream)
             done = torch.cuda.Event()
             done.record(self.stream)
         self.gstage_free[unit.gstage] = done

@@ -258,6 +258,27 @@ def reduce_scatter_multi(arena, segs, grad_dtype, scale, accumulate=False, max_c
     _multi(arena, "pdb200_nvl_reduce_scatter_multi", segs, (code, float(scale), int(bool(accumulate))), max_ctas, st)
 
 
+def reduce_scatter_copy_engine(arena, segs, grad_dtype, scale, accumulate=False, max_ctas=0, stream=None):
+    """Reduce-scatter whose transfer runs on the copy engines: segs = [(stage_off, recv_off, shard_numel, out_ptr), ...];
+    shard p of every staged buffer is copied into slot ``rank`` of rank p's receive buffer (``recv_off``, nranks slots),
+    then a local kernel writes ``out (+)= scale * sum of the slots``.  Only that local sum runs on SMs."""
+    from paddle_b200.lib import check
+    st = stream if stream is not None else stream_ptr(torch.device("cuda", torch.cuda.current_device()))
+    esz = 4 if grad_dtype == torch.float32 else 2
+    e = arena.next_epoch()
+    check(lib.kernels.pdb200_nvl_barrier(arena.peers_arg, arena.nranks, arena.rank, 0, e, st), "nvl_barrier")   # receive slots free
+    flat = (ctypes.c_int64 * (3 * len(segs)))(*[int(v) for (so, ro, ne, _o) in segs for v in (so, ro, ne * esz)])
+    if arena._rt.pdb200_symm_alltoall_ce(arena._h, ctypes.cast(flat, ctypes.c_void_p), len(segs), st) != 0:
+        raise RuntimeError(f"symm_alltoall_ce: {arena._rt.pdb200_rt_last_error().decode()}")
+    check(lib.kernels.pdb200_nvl_barrier(arena.peers_arg, arena.nranks, arena.rank, 0, e + 1, st), "nvl_barrier")   # all slots landed
+    code = {torch.float32: 0, torch.bfloat16: 1}[grad_dtype]
+    for i in range(0, len(segs), 16):
+        chunk = segs[i:i + 16]
+        tri = (ctypes.c_int64 * (3 * len(chunk)))(*[int(v) for (_so, ro, ne, o) in chunk for v in (arena.local_ptr + ro, ne, o)])
+        check(lib.kernels.pdb200_reduce_slots_multi(ctypes.cast(tri, ctypes.c_void_p), len(chunk), arena.nranks, code, float(scale),
+                                                    int(bool(accumulate)), int(max_ctas), st), "reduce_slots_multi")
+
+
 def reduce_scatter_avg(grad_buf, shard_start, shard_numel, out, scratch):
     """AVG reduce-scatter of a symmetric gradient buffer into a local fp32 shard (no host sync, norm partials in
     ``scratch``, which must hold lib.kernels.pdb200_nvl_rs_grid(shard_numel) floats)."""
