@@ -21,6 +21,7 @@
 // CTAs' barriers), warp 2 TMEM allocator, warps 4-7 epilogue of the CTA's own 128 rows.
 // Every tensor map (A, B and C) covers this GPU's own memory only (get_tmap_2d refuses anything else).
 #include <cooperative_groups.h>
+#include <stdio.h>
 
 #include "common.cuh"
 #include "tc.cuh"
@@ -123,6 +124,25 @@ __device__ __noinline__ void epilogue_math(uint32_t (&r)[32], const __nv_bfloat1
   }
 }
 
+// K5 gate: spin (bounded) until the chunk holding pair-row `row0` has landed in local memory, then order the TMA
+// (async proxy) reads after the flag's acquire.
+struct Shape;
+__device__ __forceinline__ void gate_wait_impl(const uint32_t* flags, int gate_rows, uint32_t epoch, int row0) {
+  const uint32_t* f = flags + row0 / gate_rows;
+  unsigned long long spins = 0;
+  while (true) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+    if ((int32_t)(v - epoch) >= 0) break;
+    if (++spins > 400000000ull) {
+      printf("[pdb200 gemm gate] chunk %d never arrived (flag %u, want %u)\n", row0 / gate_rows, v, epoch);
+      __trap();
+    }
+    __nanosleep(100);
+  }
+  asm volatile("fence.proxy.async.global;" ::: "memory");
+}
+
 // ---- work list -------------------------------------------------------------------------------------------------
 struct Shape {
   int M, N, K;
@@ -131,6 +151,14 @@ struct Shape {
   int band;         // pair-rows per raster band
   int full;         // macro blocks handled in full rounds: (num_m * num_c / pairs) * pairs
   int total;        // num_m * num_c
+  // Optional gate on the A operand (K5 all-gather -> GEMM): rows [i * gate_rows, (i + 1) * gate_rows) of A may only be
+  // loaded once gate_flags[i] has reached gate_epoch.  The flags live in THIS GPU's memory; peers set them after
+  // their copy of that row chunk into this GPU's gathered buffer has landed.  m_rot rotates the pair-row order so
+  // that the rows this rank contributed itself come first.
+  const uint32_t* gate_flags;
+  int gate_rows;
+  uint32_t gate_epoch;
+  int m_rot;
 };
 struct Item {
   int m_blk, n_base, nslots;
@@ -145,6 +173,8 @@ __device__ __forceinline__ void block_coords(const Shape& s, int t, int& m_blk, 
   m_blk = first_m + in_band % h;
   c_blk = in_band / h;
 }
+__device__ __forceinline__ void gate_wait(const Shape& s, int row0) { gate_wait_impl(s.gate_flags, s.gate_rows, s.gate_epoch, row0); }
+
 // Work item number w of this pair's list (w = pair, pair + pairs, ...); false when the list is exhausted.
 __device__ __forceinline__ bool get_item(const Shape& s, int w, Item& it) {
   int t, half = -1;
@@ -158,6 +188,7 @@ __device__ __forceinline__ bool get_item(const Shape& s, int w, Item& it) {
   }
   int c_blk;
   block_coords(s, t, it.m_blk, c_blk);
+  if (s.m_rot) it.m_blk = (it.m_blk + s.m_rot) % s.num_m;
   it.n_base = c_blk * (2 * BN);
   it.nslots = 2;
   if (half >= 0) {
@@ -225,6 +256,7 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant_
       for (int w = pair; get_item(shape, w, it); w += pairs) {
         if (it.nslots == 0) continue;
         const int m0 = it.m_blk * (2 * BM) + (int)rank * BM;        // this CTA's rows
+        if (shape.gate_flags != nullptr) gate_wait(shape, it.m_blk * (2 * BM));
         const uint32_t tx = 2u * (uint32_t)(kABytes + it.nslots * kBBytes);
         for (int kb = 0; kb < num_k; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -437,9 +469,16 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant_
   if (warp == 2) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
 }
 
+struct Gate {
+  const uint32_t* flags = nullptr;
+  int rows = 0;
+  uint32_t epoch = 0;
+  int m_rot = 0;
+};
+
 template <bool A_MN, bool B_MN, bool OUT_F32>
 static int launch(const void* a, const void* b, void* c, const void* bias, int M, int N, int K, float beta, int act,
-                  cudaStream_t st) {
+                  cudaStream_t st, const Gate& gate = Gate()) {
   CUtensorMap tm_a, tm_b, tm_c;
   // All three tensor maps are built through get_tmap_2d: local memory of the current device or an error.
   if (A_MN) {
@@ -470,6 +509,11 @@ static int launch(const void* a, const void* b, void* c, const void* bias, int M
   s.full = (s.total / pairs) * pairs;
   s.band = g_band > 0 ? g_band : 16;
   if (s.band > s.num_m) s.band = s.num_m;
+  s.gate_flags = gate.flags;
+  s.gate_rows = gate.rows;
+  s.gate_epoch = gate.epoch;
+  s.m_rot = gate.m_rot;
+  if (gate.flags && require_local(gate.flags, sizeof(uint32_t) * (size_t)((M + gate.rows - 1) / gate.rows), "gemm gate flags")) return -1;
   kern<<<2 * pairs, kThreads, kSmemBytes, st>>>(tm_a, tm_b, tm_c, (const __nv_bfloat16*)bias, s, beta != 0.f ? 1 : 0, act);
   return check_launch("gemm_tc3");
 }
@@ -504,4 +548,26 @@ PDB_EXPORT int pdb200_gemm_bf16_macro(const void* a, const void* b, void* c, con
   if (!a_mn && b_mn) { PDB_TC3(false, true); }
   PDB_TC3(false, false);
 #undef PDB_TC3
+}
+
+// K5 all-gather -> GEMM, compute half: C = A . op(B) where A [M, K] is the gathered activation in LOCAL memory that
+// peers fill chunk by chunk; rows [i * gate_rows, (i+1) * gate_rows) are loaded only after gate_flags[i] (local uint32
+// array) has reached gate_epoch, and the row blocks are visited starting at pair-row m_rot (the caller passes the first
+// block of this rank's own shard, which is there from the start).  gate_rows must be a multiple of 256.  Reference
+// sequence: ncclAllGather, then GEMM (fleet/utils/sequence_parallel_utils.py:255-285).
+PDB_EXPORT int pdb200_gemm_bf16_gated(const void* a, const void* b, void* c, const void* bias, int64_t M, int64_t N, int64_t K,
+                                      int trans_b, int act, const void* gate_flags, int gate_rows, int64_t gate_epoch,
+                                      int m_rot, void* stream) {
+  PDB_REQUIRE(M > 0 && N > 0 && K > 0 && M < (1ll << 31) && N < (1ll << 31) && K < (1ll << 31), "gemm_gated: bad shape");
+  PDB_REQUIRE(((uintptr_t)a & 15) == 0 && ((uintptr_t)b & 15) == 0 && ((uintptr_t)c & 15) == 0, "gemm_gated: 16-byte alignment");
+  PDB_REQUIRE(K % 8 == 0 && N % 8 == 0, "gemm_gated: K and N must be multiples of 8");
+  PDB_REQUIRE(gate_flags != nullptr && gate_rows > 0 && gate_rows % 256 == 0, "gemm_gated: gate_rows must be a positive multiple of 256");
+  tc3::Gate g;
+  g.flags = (const uint32_t*)gate_flags;
+  g.rows = gate_rows;
+  g.epoch = (uint32_t)gate_epoch;
+  g.m_rot = m_rot;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (trans_b) return tc3::launch<false, false, false>(a, b, c, bias, (int)M, (int)N, (int)K, 0.f, act, st, g);
+  return tc3::launch<false, true, false>(a, b, c, bias, (int)M, (int)N, (int)K, 0.f, act, st, g);
 }

@@ -908,3 +908,22 @@ PDB_EXPORT int pdb200_reduce_slots_multi(const int64_t* segs, int nseg, int nran
   else reduce_slots_multi_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(S, nranks, scale, accumulate);
   return check_launch("reduce_slots_multi");
 }
+
+// One-thread-per-peer signal: flag word `flag_off + 4 * index` of EVERY rank's segment <- value, released at system
+// scope.  Enqueued behind the copies of a chunk (stream order = the copies have completed), it tells the consumers -
+// a gated GEMM polling its local flag, or a later kernel - that the chunk is in their memory.
+namespace pdb { namespace nvl {
+__global__ void signal_peers_kernel(Peers P, uint64_t flag_off, int index, uint32_t value) {
+  const int t = threadIdx.x;
+  if (t < P.nranks) {
+    fence_sys();
+    st_release_sys(reinterpret_cast<uint32_t*>(P.ptr[t] + flag_off) + index, value);
+  }
+}
+} }
+PDB_EXPORT int pdb200_nvl_signal(const uint64_t* peer_ptrs, int nranks, int rank, int64_t flag_off, int index, int64_t value, void* stream) {
+  PDB_REQUIRE(nranks >= 1 && nranks <= kMaxRanks, "nvl_signal: nranks %d out of range", nranks);
+  Peers P = make_peers(peer_ptrs, 0, nranks, rank);
+  signal_peers_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(P, (uint64_t)flag_off, index, (uint32_t)value);
+  return check_launch("nvl_signal");
+}

@@ -427,3 +427,25 @@ PDB_RT_EXPORT int pdb200_symm_alltoall_ce(void* a, const int64_t* segs, int nseg
   }
   return 0;
 }
+
+// Copy-engine broadcast of raw byte ranges: {src_off, dst_off, nbytes}: [src_off, +nbytes) of this rank's segment goes to
+// [dst_off, +nbytes) of every rank's segment (this one included).
+PDB_RT_EXPORT int pdb200_symm_bcast_ce(void* a, const int64_t* segs, int nseg, void* stream) {
+  pdbrt::Arena* A = (pdbrt::Arena*)a;
+  const int n = A->nranks(), r = A->rank();
+  cudaStream_t st = (cudaStream_t)stream;
+  for (int k = 0; k < nseg; ++k) {
+    const int64_t so = segs[3 * k], dof = segs[3 * k + 1], nb = segs[3 * k + 2];
+    if (nb <= 0) continue;
+    const char* src = (const char*)(uintptr_t)A->peer(r) + so;
+    for (int i = 0; i < n; ++i) {
+      const int p = (r + i) % n;
+      cudaError_t e = cudaMemcpyAsync((char*)(uintptr_t)A->peer(p) + dof, src, (size_t)nb, cudaMemcpyDeviceToDevice, st);
+      if (e != cudaSuccess) {
+        pdbrt::set_error("symm_bcast_ce: cudaMemcpyAsync to rank %d failed: %s", p, cudaGetErrorString(e));
+        return -1;
+      }
+    }
+  }
+  return 0;
+}

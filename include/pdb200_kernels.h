@@ -98,6 +98,10 @@ PDB_API int pdb200_gemm_bf16_pair(const void* a, const void* b, void* c, const v
  * swizzled-smem + TMA-store epilogue; fp32 C += is a TMA reduce-add (csrc/kernels/gemm_tc3.cu). */
 PDB_API int pdb200_gemm_bf16_macro(const void* a, const void* b, void* c, const void* bias, int64_t M, int64_t N, int64_t K, int trans_a, int trans_b, int out_dtype, float beta, int act, void* stream);
 PDB_API int pdb200_gemm_set_band(int n);
+/* K5 all-gather -> GEMM, compute half: A is the gathered activation in LOCAL memory; rows [i*gate_rows, (i+1)*gate_rows)
+ * are loaded only after the local uint32 gate_flags[i] has reached gate_epoch (set by the peer whose chunk landed, see
+ * pdb200_nvl_signal); row blocks are visited from pair-row m_rot on (this rank's own rows first).  gate_rows % 256 == 0. */
+PDB_API int pdb200_gemm_bf16_gated(const void* a, const void* b, void* c, const void* bias, int64_t M, int64_t N, int64_t K, int trans_b, int act, const void* gate_flags, int gate_rows, int64_t gate_epoch, int m_rot, void* stream);
 /* K9/K10 grouped GEMMs for the local experts of an MoE layer, scheduled on the device from int64 row counts (reference:
  * per-expert loop after blocking count reads, incubate/distributed/models/moe/moe_layer.py:441-470).  Rows are
  * expert-major in slabs of rows_cap rows.  forward/dgrad: C[r,:] = A[r,:] . B[e] (B stacked [E][K][N], or [E][N][K] when
@@ -119,6 +123,9 @@ PDB_API int pdb200_nvl_set_emulation(int on);
 /* Optional trace: a mapped pinned host word (from pdb200_wd_progress_ptr of the runtime library) that every stand-alone
  * barrier of the fused kernels overwrites with the epoch it just passed; 0 switches it off. */
 PDB_API int pdb200_nvl_set_progress(uint64_t host_mapped_ptr);
+/* flag word (flag_off + 4*index) of every rank's segment <- value, system-scope release; enqueue it behind the copies it
+ * announces. */
+PDB_API int pdb200_nvl_signal(const uint64_t* peer_ptrs, int nranks, int rank, int64_t flag_off, int index, int64_t value, void* stream);
 PDB_API int pdb200_nvl_barrier(const uint64_t* peer_ptrs, int nranks, int rank, int64_t pad_off, int64_t epoch, void* stream);
 PDB_API int pdb200_nvl_allreduce(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t data_off, int64_t numel, int dtype, float scale, int64_t pad_off, int64_t epoch, int max_ctas, void* stream);
 PDB_API int pdb200_nvl_rs_adamw_ag(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t grad_off, int grad_dtype, int64_t param_off, int64_t shard_start, int64_t shard_numel, float* master, float* m, float* v, float lr, float beta1, float beta2, float eps, float weight_decay, const float* beta_pows, const float* grad_scale, const float* found_inf, const float* local_grad, int64_t pad_off, int64_t epoch, void* stream);

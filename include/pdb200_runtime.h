@@ -100,6 +100,9 @@ PDB_API int pdb200_symm_supported(int device);
  * shard goes to [dst_off + rank * shard_bytes) of every rank's segment with cudaMemcpyAsync on `stream` (no SM work).
  * Bracket it with the arena's cross-rank barriers like the kernel collectives. */
 PDB_API int pdb200_symm_allgather_ce(void* arena, const int64_t* segs, int nseg, void* stream);
+/* Broadcast of byte ranges on the copy engines: [src_off, +nbytes) of this rank's segment to [dst_off, +nbytes) of every
+ * rank's segment. */
+PDB_API int pdb200_symm_bcast_ce(void* arena, const int64_t* segs, int nseg, void* stream);
 /* All-to-all on the copy engines (transfer half of a reduce-scatter): shard p of this rank's buffer at src_off goes to
  * slot `rank` of rank p's receive buffer at dst_off; a local kernel sums the slots afterwards. */
 PDB_API int pdb200_symm_alltoall_ce(void* arena, const int64_t* segs, int nseg, void* stream);

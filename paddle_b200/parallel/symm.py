@@ -340,27 +340,99 @@ def _assert_local(arena, *tensors):
             assert not (base <= p < base + arena.nbytes), "tensor-core operand inside a mapping of another GPU's memory"
 
 
+_ag_state = {}
+
+
+def _ag_buffers(arena, rows, K, n):
+    """Per (arena, shape): two gathered buffers (alternating per call, so a peer may already push the next call's rows
+    while this rank still reads the previous ones), one flag word per 256-row chunk and buffer, a side stream, a
+    monotonic call counter that doubles as the flag epoch."""
+    key = (id(arena), rows, K)
+    st = _ag_state.get(key)
+    if st is None:
+        chunk = 256 if rows % 256 == 0 else 0
+        nchunks = (rows // chunk) * n if chunk else 0
+        st = dict(full=[arena.empty((rows * n, K), torch.bfloat16) for _ in range(2)],
+                  flags=[arena.empty((max(nchunks, 1),), torch.int32) for _ in range(2)],
+                  stream=torch.cuda.Stream(priority=-1), calls=0, chunk=chunk, per_rank=rows // chunk if chunk else 0)
+        for f in st["flags"]:
+            f.zero_()
+        torch.cuda.current_stream().synchronize()
+        C.barrier(arena.group)                     # flags are zero everywhere before anybody signals
+        _ag_state[key] = st
+    return st
+
+
 def ag_gemm(x_shard, weight, group, bias=None, trans_b=False, act=None):
-    """K5: ``all_gather(x_shard, dim 0) @ weight``.  Every rank pushes its shard into all ranks' gathered buffer
-    (NVLS ``multimem.st`` all-gather, one NVLink pass), and the CTA-pair tcgen05 GEMM reads the gathered activation
-    from LOCAL memory.  x_shard: [rows, K] bf16; returns [nranks*rows, N]."""
+    """K5: ``all_gather(x_shard, dim 0) @ weight`` with the transfer hidden behind the GEMM.
+
+    Every rank copies its shard, in 256-row chunks, into all ranks' gathered buffer with the copy engines (a side stream;
+    no SM runs a copy loop) and announces each chunk with a system-scope flag write into the receivers' memory.  The
+    CTA-pair tcgen05 GEMM starts at once on this rank's own rows and its TMA producer waits, chunk by chunk, for the flag
+    of the rows it is about to load - from LOCAL memory, where the peers' copies land.  Two gathered buffers alternate,
+    so no rank has to wait for the others before it starts pushing.  x_shard: [rows, K] bf16; returns [nranks*rows, N].
+    Falls back to gather-then-GEMM (one NVLS ``multimem.st`` kernel, then the GEMM) when the shape cannot be chunked."""
     from paddle_b200.lib import check
     from paddle_b200.ops import gemm as G
     from paddle_b200.ops._util import ptr
     arena = get_arena(group)
     rows, K = x_shard.shape
-    full = _staging(arena, "ag_full", (rows * arena.nranks, K), torch.bfloat16)
+    n = arena.nranks
+    N = weight.shape[0] if trans_b else weight.shape[1]
+    st = _ag_buffers(arena, rows, K, n)
     xs = x_shard.contiguous()
-    check(lib.kernels.pdb200_nvl_allgather_from(arena.peers_arg, arena.mc_ptr, arena.nranks, arena.rank, ptr(xs),
-                                                full._symm[1], xs.numel() * 2, 0, arena.next_epoch(), 0,
-                                                stream_ptr(xs.device)), "nvl_allgather_from")
-    _assert_local(arena, full, weight)
-    if G.supported(full, weight, False, trans_b):
-        return G.gemm(full, weight, False, trans_b, bias=bias, act=act)
-    out = torch.matmul(full, weight.t() if trans_b else weight)
-    if bias is not None:
-        out = out + bias
-    return {"gelu": torch.nn.functional.gelu, "relu": torch.relu}.get(act, lambda t: t)(out)
+    gated = (st["chunk"] > 0 and flag("ag_gemm_overlap") and hasattr(lib.kernels.require(), "pdb200_gemm_bf16_gated")
+             and hasattr(arena._rt, "pdb200_symm_allgather_ce") and K % 64 == 0 and N % 8 == 0 and weight.is_contiguous())
+    if not gated:
+        full = st["full"][0]
+        check(lib.kernels.pdb200_nvl_allgather_from(arena.peers_arg, arena.mc_ptr, n, arena.rank, ptr(xs),
+                                                    full._symm[1], xs.numel() * 2, 0, arena.next_epoch(), 0,
+                                                    stream_ptr(xs.device)), "nvl_allgather_from")
+        _assert_local(arena, full, weight)
+        if G.supported(full, weight, False, trans_b):
+            return G.gemm(full, weight, False, trans_b, bias=bias, act=act)
+        out = torch.matmul(full, weight.t() if trans_b else weight)
+        if bias is not None:
+            out = out + bias
+        return {"gelu": torch.nn.functional.gelu, "relu": torch.relu}.get(act, lambda t: t)(out)
+    st["calls"] += 1
+    epoch = st["calls"]
+    buf = epoch & 1
+    full, flags = st["full"][buf], st["flags"][buf]
+    cur = torch.cuda.current_stream()
+    side = st["stream"]
+    ready = torch.cuda.Event()
+    ready.record(cur)                                  # x_shard is final; earlier readers of this buffer are enqueued
+    chunk, per_rank = st["chunk"], st["per_rank"]
+    chunk_bytes = chunk * K * 2
+    # the shard has to sit in the arena for the copy engines to reach the peers' mappings from it: stage it once
+    stage = _staging(arena, "ag_src", (rows, K), torch.bfloat16)
+    with torch.cuda.stream(side):
+        side.wait_event(ready)
+        stage.copy_(xs, non_blocking=True)
+        xs.record_stream(side)
+        for c in range(per_rank):
+            # chunk c of rank r lands at row r * rows + c * chunk of every rank's gathered buffer
+            _ce_chunk(arena, stage._symm[1] + c * chunk_bytes, full._symm[1] + (arena.rank * rows + c * chunk) * K * 2,
+                      chunk_bytes, side.cuda_stream)
+            check(lib.kernels.pdb200_nvl_signal(arena.peers_arg, n, arena.rank, flags._symm[1], arena.rank * per_rank + c, epoch,
+                                                side.cuda_stream), "nvl_signal")
+    out = torch.empty(rows * n, N, dtype=torch.bfloat16, device=xs.device)
+    _assert_local(arena, full, weight, out)
+    check(lib.kernels.pdb200_gemm_bf16_gated(ptr(full), ptr(weight), ptr(out), ptr(bias), rows * n, N, K, int(trans_b),
+                                             {"none": 0, None: 0, "gelu": 1, "relu": 2}[act], ptr(flags), chunk, epoch,
+                                             (arena.rank * rows) // 256, stream_ptr(xs.device)), "gemm_bf16_gated")
+    done = torch.cuda.Event()
+    done.record(side)
+    cur.wait_event(done)          # the side stream's work of this call is ordered before whatever follows the GEMM
+    return out
+
+
+def _ce_chunk(arena, src_off, dst_off, nbytes, stream):
+    """Copy ``nbytes`` from ``src_off`` of this rank's segment to ``dst_off`` of EVERY rank's segment (copy engines)."""
+    seg = (ctypes.c_int64 * 3)(src_off, dst_off, nbytes)
+    if arena._rt.pdb200_symm_bcast_ce(arena._h, ctypes.cast(seg, ctypes.c_void_p), 1, stream) != 0:
+        raise RuntimeError(f"symm_bcast_ce: {arena._rt.pdb200_rt_last_error().decode()}")
 
 
 def gemm_rs(x, weight, group, trans_b=False):

@@ -101,6 +101,20 @@ for _ in range(2):
     got = symm.gemm_rs(xf, w, g)
     torch.cuda.synchronize()
     torch.testing.assert_close(got.float(), ref_rs, rtol=2e-2, atol=1e-1)
+# overlapped K5 on a shape with several chunks per rank; 5 calls with fresh data walk both gathered buffers and the
+# flag epochs; oracle = fp32 matmul of the NCCL-gathered activation
+rows2, K2, N2 = 768, 1024, 1536
+w2 = (torch.randn(K2, N2, device=dev) * 0.05).bfloat16()
+dist.broadcast(w2, 0)
+for it in range(5):
+    torch.manual_seed(900 + 10 * it + r)
+    xs2 = (torch.randn(rows2, K2, device=dev) * 0.5).bfloat16()
+    parts = []
+    dist.all_gather(parts, xs2)
+    ref2 = torch.cat(parts, 0).float() @ w2.float()
+    got = symm.ag_gemm(xs2, w2, g)
+    torch.testing.assert_close(got.float(), ref2, rtol=2e-2, atol=1e-1, msg=lambda m: f"overlapped ag_gemm call {it}: {m}")
+assert any(v["calls"] >= 5 for v in symm._ag_state.values()), "the gated (overlapped) path did not run"
 wt = w.t().contiguous()                   # trans_b variants (backward shapes)
 got = symm.ag_gemm(xs, wt, g, trans_b=True)
 torch.testing.assert_close(got.float(), ref, rtol=2e-2, atol=5e-2)
