@@ -159,6 +159,11 @@ struct Shape {
   int gate_rows;
   uint32_t gate_epoch;
   int m_rot;
+  // Optional completion counters (K6 GEMM -> reduce-scatter): after the stores of a work item have completed, every
+  // epilogue warp adds the item's number of 256-column tiles to done_counters[row / done_rows] (device scope).  A row
+  // block of done_rows rows is complete when its counter has grown by (done_rows / 256) * ceil(N / 256) * 8.
+  unsigned int* done_counters;
+  int done_rows;
 };
 struct Item {
   int m_blk, n_base, nslots;
@@ -459,6 +464,16 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant_
           }
         }
       }
+      if (shape.done_counters != nullptr) {
+        // this warp's part of the item is in global memory once its bulk stores have completed: count it
+        if (lane == 0) {
+          tma_store_wait<0>();
+          asm volatile("fence.proxy.async.global;" ::: "memory");
+          __threadfence();
+          atomicAdd(shape.done_counters + (it.m_blk * (2 * BM)) / shape.done_rows, (unsigned int)it.nslots);
+        }
+        __syncwarp();
+      }
     }
     if (lane == 0) tma_store_wait<0>();               // all of this warp's stores have completed
     __syncwarp();
@@ -474,6 +489,9 @@ struct Gate {
   int rows = 0;
   uint32_t epoch = 0;
   int m_rot = 0;
+  unsigned int* done = nullptr;     // completion counters, one per done_rows rows
+  int done_rows = 0;
+  int band = 0;                     // raster band override (pair-rows), 0 = default
 };
 
 template <bool A_MN, bool B_MN, bool OUT_F32>
@@ -509,6 +527,10 @@ static int launch(const void* a, const void* b, void* c, const void* bias, int M
   s.full = (s.total / pairs) * pairs;
   s.band = g_band > 0 ? g_band : 16;
   if (s.band > s.num_m) s.band = s.num_m;
+  if (gate.band > 0) s.band = gate.band < s.num_m ? gate.band : s.num_m;
+  s.done_counters = gate.done;
+  s.done_rows = gate.done_rows;
+  if (gate.done && require_local(gate.done, sizeof(unsigned int) * (size_t)((M + gate.done_rows - 1) / gate.done_rows), "gemm done counters")) return -1;
   s.gate_flags = gate.flags;
   s.gate_rows = gate.rows;
   s.gate_epoch = gate.epoch;
@@ -570,4 +592,24 @@ PDB_EXPORT int pdb200_gemm_bf16_gated(const void* a, const void* b, void* c, con
   cudaStream_t st = (cudaStream_t)stream;
   if (trans_b) return tc3::launch<false, false, false>(a, b, c, bias, (int)M, (int)N, (int)K, 0.f, act, st, g);
   return tc3::launch<false, true, false>(a, b, c, bias, (int)M, (int)N, (int)K, 0.f, act, st, g);
+}
+
+// K6 GEMM -> reduce-scatter, compute half: C = A . op(B) (bf16, local memory) visiting the row blocks of block_rows rows
+// in the order m_rot, m_rot+1, ... (the caller starts one block after its own, so its own block comes last) and
+// counting finished work into done_counters[row / block_rows] (see Shape::done_counters).  block_rows % 256 == 0.
+PDB_EXPORT int pdb200_gemm_bf16_counted(const void* a, const void* b, void* c, int64_t M, int64_t N, int64_t K, int trans_b,
+                                        void* done_counters, int block_rows, int m_rot, void* stream) {
+  PDB_REQUIRE(M > 0 && N > 0 && K > 0 && M < (1ll << 31) && N < (1ll << 31) && K < (1ll << 31), "gemm_counted: bad shape");
+  PDB_REQUIRE(((uintptr_t)a & 15) == 0 && ((uintptr_t)b & 15) == 0 && ((uintptr_t)c & 15) == 0, "gemm_counted: 16-byte alignment");
+  PDB_REQUIRE(K % 8 == 0 && N % 8 == 0, "gemm_counted: K and N must be multiples of 8");
+  PDB_REQUIRE(done_counters != nullptr && block_rows > 0 && block_rows % 256 == 0 && M % block_rows == 0,
+              "gemm_counted: block_rows must be a positive multiple of 256 that divides M");
+  tc3::Gate g;
+  g.done = (unsigned int*)done_counters;
+  g.done_rows = block_rows;
+  g.m_rot = m_rot;
+  g.band = block_rows / 256;                 // finish one owner's block before starting the next
+  cudaStream_t st = (cudaStream_t)stream;
+  if (trans_b) return tc3::launch<false, false, false>(a, b, c, nullptr, (int)M, (int)N, (int)K, 0.f, 0, st, g);
+  return tc3::launch<false, true, false>(a, b, c, nullptr, (int)M, (int)N, (int)K, 0.f, 0, st, g);
 }

@@ -547,7 +547,7 @@ __global__ void __launch_bounds__(256, 2) reduce_scatter_multi_kernel(Peers P, R
 struct SlotSeg { const void* recv; int64_t shard_numel; float* out; };
 struct SlotSegs { SlotSeg s[kMaxSegs]; int n; };
 template <typename G>
-__global__ void __launch_bounds__(256, 2) reduce_slots_multi_kernel(SlotSegs S, int nranks, float scale, int accumulate) {
+__global__ void __launch_bounds__(256, 2) reduce_slots_multi_kernel(SlotSegs S, int nranks, float scale, int accumulate, int out_bf16) {
   constexpr int E = RsTraits<G>::kElems;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int k = 0; k < S.n; ++k) {
@@ -574,7 +574,13 @@ __global__ void __launch_bounds__(256, 2) reduce_slots_multi_kernel(SlotSegs S, 
           }
         }
       }
-      rs_store<G>(out + j * E, g, scale, accumulate);
+      if (out_bf16) {                                      // K6: the reduced activation goes back to bf16
+        __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(out) + j * E;
+#pragma unroll
+        for (int e = 0; e < E; e += 2) *reinterpret_cast<__nv_bfloat162*>(ob + e) = __floats2bfloat162_rn(g[e] * scale, g[e + 1] * scale);
+      } else {
+        rs_store<G>(out + j * E, g, scale, accumulate);
+      }
     }
   }
 }
@@ -880,9 +886,18 @@ PDB_EXPORT int pdb200_nvl_reduce_scatter_multi(const uint64_t* peer_ptrs, uint64
   return check_launch("nvl_reduce_scatter_multi");
 }
 
+PDB_EXPORT int pdb200_reduce_slots_multi2(const int64_t* segs, int nseg, int nranks, int grad_dtype, float scale, int accumulate,
+                                          int out_dtype, int max_ctas, void* stream);
 // Local sum of receive slots: segs (HOST) = nseg triples {recv_ptr (local device pointer), shard_numel, out_ptr (fp32)}.
 PDB_EXPORT int pdb200_reduce_slots_multi(const int64_t* segs, int nseg, int nranks, int grad_dtype, float scale, int accumulate,
                                          int max_ctas, void* stream) {
+  return pdb200_reduce_slots_multi2(segs, nseg, nranks, grad_dtype, scale, accumulate, 0, max_ctas, stream);
+}
+// Same with the output precision chosen: out_dtype 0 = fp32 (accumulate allowed), 1 = bf16 (out pointers are bf16).
+PDB_EXPORT int pdb200_reduce_slots_multi2(const int64_t* segs, int nseg, int nranks, int grad_dtype, float scale, int accumulate,
+                                          int out_dtype, int max_ctas, void* stream) {
+  PDB_REQUIRE(out_dtype == 0 || (out_dtype == 1 && !accumulate), "reduce_slots_multi: bf16 output cannot accumulate");
+  const int out_bf16 = out_dtype == 1;
   PDB_REQUIRE(nseg >= 1 && nseg <= kMaxSegs, "reduce_slots_multi: 1..%d segments per launch (got %d)", kMaxSegs, nseg);
   PDB_REQUIRE(nranks >= 1 && nranks <= kMaxRanks, "reduce_slots_multi: nranks %d out of range", nranks);
   PDB_REQUIRE(grad_dtype == PDB_DTYPE_F32 || grad_dtype == PDB_DTYPE_BF16, "reduce_slots_multi: grads must be fp32 or bf16");
@@ -904,8 +919,8 @@ PDB_EXPORT int pdb200_reduce_slots_multi(const int64_t* segs, int nseg, int nran
   if (blocks > cap) blocks = cap;
   const unsigned grid = (unsigned)(blocks < 1 ? 1 : blocks);
   cudaStream_t st = (cudaStream_t)stream;
-  if (grad_dtype == PDB_DTYPE_F32) reduce_slots_multi_kernel<float><<<grid, 256, 0, st>>>(S, nranks, scale, accumulate);
-  else reduce_slots_multi_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(S, nranks, scale, accumulate);
+  if (grad_dtype == PDB_DTYPE_F32) reduce_slots_multi_kernel<float><<<grid, 256, 0, st>>>(S, nranks, scale, accumulate, out_bf16);
+  else reduce_slots_multi_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(S, nranks, scale, accumulate, out_bf16);
   return check_launch("reduce_slots_multi");
 }
 
@@ -913,9 +928,9 @@ PDB_EXPORT int pdb200_reduce_slots_multi(const int64_t* segs, int nseg, int nran
 // scope.  Enqueued behind the copies of a chunk (stream order = the copies have completed), it tells the consumers -
 // a gated GEMM polling its local flag, or a later kernel - that the chunk is in their memory.
 namespace pdb { namespace nvl {
-__global__ void signal_peers_kernel(Peers P, uint64_t flag_off, int index, uint32_t value) {
+__global__ void signal_peers_kernel(Peers P, uint64_t flag_off, int index, uint32_t value, int only) {
   const int t = threadIdx.x;
-  if (t < P.nranks) {
+  if (t < P.nranks && (only < 0 || t == only)) {
     fence_sys();
     st_release_sys(reinterpret_cast<uint32_t*>(P.ptr[t] + flag_off) + index, value);
   }
@@ -924,6 +939,59 @@ __global__ void signal_peers_kernel(Peers P, uint64_t flag_off, int index, uint3
 PDB_EXPORT int pdb200_nvl_signal(const uint64_t* peer_ptrs, int nranks, int rank, int64_t flag_off, int index, int64_t value, void* stream) {
   PDB_REQUIRE(nranks >= 1 && nranks <= kMaxRanks, "nvl_signal: nranks %d out of range", nranks);
   Peers P = make_peers(peer_ptrs, 0, nranks, rank);
-  signal_peers_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(P, (uint64_t)flag_off, index, (uint32_t)value);
+  signal_peers_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(P, (uint64_t)flag_off, index, (uint32_t)value, -1);
   return check_launch("nvl_signal");
+}
+PDB_EXPORT int pdb200_nvl_signal_one(const uint64_t* peer_ptrs, int nranks, int rank, int target, int64_t flag_off, int index, int64_t value,
+                                     void* stream) {
+  PDB_REQUIRE(nranks >= 1 && nranks <= kMaxRanks && target >= 0 && target < nranks, "nvl_signal_one: bad rank");
+  Peers P = make_peers(peer_ptrs, 0, nranks, rank);
+  signal_peers_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(P, (uint64_t)flag_off, index, (uint32_t)value, target);
+  return check_launch("nvl_signal_one");
+}
+
+// Stream-ordered waits used to chain copy-engine transfers behind in-kernel progress:
+//   wait_counter: spin until *counter (this GPU's memory, written with device-scope atomics by a running kernel) has
+//                 reached `target`; what follows on the stream (copies of the finished block) starts only then.
+//   wait_flags:   spin until every one of `count` local flag words has reached `epoch` (set by peers' signal kernels).
+namespace pdb { namespace nvl {
+__global__ void wait_counter_kernel(const unsigned int* counter, unsigned int target, unsigned long long spin_limit) {
+  unsigned long long spins = 0;
+  while (true) {
+    unsigned int v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
+    if ((int)(v - target) >= 0) break;
+    if (spin_limit && ++spins > spin_limit) {
+      printf("[pdb200 nvl] wait_counter timed out (saw %u, want %u)\n", v, target);
+      __trap();
+    }
+    __nanosleep(200);
+  }
+  __threadfence_system();
+}
+__global__ void wait_flags_kernel(const uint32_t* flags, int count, uint32_t epoch, int skip, unsigned long long spin_limit) {
+  const int t = threadIdx.x;
+  if (t < count && t != skip) {
+    unsigned long long spins = 0;
+    while ((int32_t)(ld_acquire_sys(flags + t) - epoch) < 0) {
+      if (spin_limit && ++spins > spin_limit) {
+        printf("[pdb200 nvl] wait_flags timed out on flag %d (saw %u, want %u)\n", t, ld_acquire_sys(flags + t), epoch);
+        __trap();
+      }
+      __nanosleep(200);
+    }
+  }
+  __syncthreads();
+  __threadfence_system();
+}
+} }
+PDB_EXPORT int pdb200_nvl_wait_counter(const void* counter, int64_t target, void* stream) {
+  wait_counter_kernel<<<1, 1, 0, (cudaStream_t)stream>>>((const unsigned int*)counter, (unsigned int)target, 200000000ull);
+  return check_launch("nvl_wait_counter");
+}
+PDB_EXPORT int pdb200_nvl_wait_flags(const void* flags, int count, int64_t epoch, int skip_index, void* stream) {
+  PDB_REQUIRE(count >= 1 && count <= 1024, "nvl_wait_flags: 1..1024 flags (got %d)", count);
+  wait_flags_kernel<<<1, (count + 31) / 32 * 32, 0, (cudaStream_t)stream>>>((const uint32_t*)flags, count, (uint32_t)epoch, skip_index,
+                                                                        200000000ull);
+  return check_launch("nvl_wait_flags");
 }

@@ -54,6 +54,8 @@ struct Driver {
   PDB_DRV(cuMulticastBindMem)
   PDB_DRV(cuMulticastGetGranularity)
   PDB_DRV(cuGetErrorString)
+  PDB_DRV(cuMemsetD32Async)
+  PDB_DRV(cuStreamWaitValue32)
 #undef PDB_DRV
   bool ok = false;
 };
@@ -91,6 +93,10 @@ static Driver& drv() {
   d.cuMulticastAddDevice = (decltype(d.cuMulticastAddDevice))dlsym(d.lib, "cuMulticastAddDevice");
   d.cuMulticastBindMem = (decltype(d.cuMulticastBindMem))dlsym(d.lib, "cuMulticastBindMem");
   d.cuMulticastGetGranularity = (decltype(d.cuMulticastGetGranularity))dlsym(d.lib, "cuMulticastGetGranularity");
+  // stream-ordered flag writes / waits (optional: the overlapped GEMM+collective paths need them)
+  d.cuMemsetD32Async = (decltype(d.cuMemsetD32Async))dlsym(d.lib, "cuMemsetD32Async");
+  d.cuStreamWaitValue32 = (decltype(d.cuStreamWaitValue32))dlsym(d.lib, "cuStreamWaitValue32_v2");
+  if (!d.cuStreamWaitValue32) d.cuStreamWaitValue32 = (decltype(d.cuStreamWaitValue32))dlsym(d.lib, "cuStreamWaitValue32");
 #undef PDB_LOAD
   return d;
 }
@@ -445,6 +451,125 @@ PDB_RT_EXPORT int pdb200_symm_bcast_ce(void* a, const int64_t* segs, int nseg, v
         pdbrt::set_error("symm_bcast_ce: cudaMemcpyAsync to rank %d failed: %s", p, cudaGetErrorString(e));
         return -1;
       }
+    }
+  }
+  return 0;
+}
+
+// Copy-engine point-to-point: {src_off, dst_off, nbytes} from this rank's segment into rank `peer`'s segment.
+PDB_RT_EXPORT int pdb200_symm_put_ce(void* a, int peer, int64_t src_off, int64_t dst_off, int64_t nbytes, void* stream) {
+  pdbrt::Arena* A = (pdbrt::Arena*)a;
+  if (peer < 0 || peer >= A->nranks() || nbytes < 0) {
+    pdbrt::set_error("symm_put_ce: bad arguments");
+    return -1;
+  }
+  if (nbytes == 0) return 0;
+  cudaError_t e = cudaMemcpyAsync((char*)(uintptr_t)A->peer(peer) + dst_off, (const char*)(uintptr_t)A->peer(A->rank()) + src_off, (size_t)nbytes,
+                                  cudaMemcpyDeviceToDevice, (cudaStream_t)stream);
+  if (e != cudaSuccess) {
+    pdbrt::set_error("symm_put_ce: cudaMemcpyAsync to rank %d failed: %s", peer, cudaGetErrorString(e));
+    return -1;
+  }
+  return 0;
+}
+
+
+// ---- overlapped GEMM + collective plumbing: everything below is enqueued from ONE native call per collective -------
+// Flags are 32-bit words in the arena; a flag write is a stream-ordered 32-bit memset into the receiver's mapping, so it
+// becomes visible after the copies enqueued before it on the same stream have completed.
+PDB_RT_EXPORT int pdb200_symm_streamops_supported() {
+  pdbrt::Driver& d = pdbrt::drv();
+  return (d.cuMemsetD32Async && d.cuStreamWaitValue32) ? 1 : 0;
+}
+
+// K5 push: chunk c (c < nchunks) = [src_off + c*chunk_bytes, +chunk_bytes) of this rank's segment goes to
+// [dst_off + c*chunk_bytes, +chunk_bytes) of EVERY rank's segment, then flag word (flag_off + 4*(flag_index0 + c)) of
+// every rank <- value.
+PDB_RT_EXPORT int pdb200_symm_push_signal(void* a, int64_t src_off, int64_t dst_off, int64_t chunk_bytes, int nchunks, int64_t flag_off,
+                                          int flag_index0, int64_t value, void* stream) {
+  pdbrt::Arena* A = (pdbrt::Arena*)a;
+  pdbrt::Driver& d = pdbrt::drv();
+  if (!d.cuMemsetD32Async) {
+    pdbrt::set_error("symm_push_signal: cuMemsetD32Async unavailable");
+    return -1;
+  }
+  const int n = A->nranks(), r = A->rank();
+  cudaStream_t st = (cudaStream_t)stream;
+  for (int c = 0; c < nchunks; ++c) {
+    const char* src = (const char*)(uintptr_t)A->peer(r) + src_off + (int64_t)c * chunk_bytes;
+    for (int i = 0; i < n; ++i) {
+      const int p = (r + i) % n;
+      if (cudaMemcpyAsync((char*)(uintptr_t)A->peer(p) + dst_off + (int64_t)c * chunk_bytes, src, (size_t)chunk_bytes,
+                          cudaMemcpyDeviceToDevice, st) != cudaSuccess) {
+        pdbrt::set_error("symm_push_signal: copy to rank %d failed: %s", p, cudaGetErrorString(cudaGetLastError()));
+        return -1;
+      }
+    }
+    for (int i = 0; i < n; ++i) {
+      const int p = (r + i) % n;
+      CUresult e = d.cuMemsetD32Async((CUdeviceptr)(A->peer(p) + flag_off + 4ull * (uint64_t)(flag_index0 + c)), (unsigned int)value, 1,
+                                      (CUstream)st);
+      if (e != CUDA_SUCCESS) {
+        pdbrt::set_error("symm_push_signal: flag write to rank %d failed: %s", p, pdbrt::cu_err(e).c_str());
+        return -1;
+      }
+    }
+  }
+  return 0;
+}
+
+// K6 ship: for the owners o = rank+1, rank+2, ... (n-1 of them): wait until the local 32-bit counter
+// counters_off[o] has reached `target` (a running GEMM counts finished work there), copy block o
+// ([part_off + o*blk_bytes, +blk_bytes) of this rank) into slot `rank` of owner o's receive buffer
+// ([recv_off + rank*blk_bytes)), then owner o's flag word (flag_off + 4*rank) <- value.
+PDB_RT_EXPORT int pdb200_symm_ship_blocks(void* a, int64_t counters_off, int64_t target, int64_t part_off, int64_t recv_off,
+                                          int64_t blk_bytes, int64_t flag_off, int64_t value, void* stream) {
+  pdbrt::Arena* A = (pdbrt::Arena*)a;
+  pdbrt::Driver& d = pdbrt::drv();
+  if (!d.cuMemsetD32Async || !d.cuStreamWaitValue32) {
+    pdbrt::set_error("symm_ship_blocks: stream memory operations unavailable");
+    return -1;
+  }
+  const int n = A->nranks(), r = A->rank();
+  cudaStream_t st = (cudaStream_t)stream;
+  for (int t = 0; t < n - 1; ++t) {
+    const int o = (r + 1 + t) % n;
+    CUresult e = d.cuStreamWaitValue32((CUstream)st, (CUdeviceptr)(A->peer(r) + counters_off + 4ull * (uint64_t)o), (cuuint32_t)target,
+                                       CU_STREAM_WAIT_VALUE_GEQ);
+    if (e != CUDA_SUCCESS) {
+      pdbrt::set_error("symm_ship_blocks: cuStreamWaitValue32 failed: %s", pdbrt::cu_err(e).c_str());
+      return -1;
+    }
+    if (cudaMemcpyAsync((char*)(uintptr_t)A->peer(o) + recv_off + (int64_t)r * blk_bytes,
+                        (const char*)(uintptr_t)A->peer(r) + part_off + (int64_t)o * blk_bytes, (size_t)blk_bytes, cudaMemcpyDeviceToDevice,
+                        st) != cudaSuccess) {
+      pdbrt::set_error("symm_ship_blocks: copy to rank %d failed: %s", o, cudaGetErrorString(cudaGetLastError()));
+      return -1;
+    }
+    e = d.cuMemsetD32Async((CUdeviceptr)(A->peer(o) + flag_off + 4ull * (uint64_t)r), (unsigned int)value, 1, (CUstream)st);
+    if (e != CUDA_SUCCESS) {
+      pdbrt::set_error("symm_ship_blocks: flag write to rank %d failed: %s", o, pdbrt::cu_err(e).c_str());
+      return -1;
+    }
+  }
+  return 0;
+}
+
+// Stream waits until every local flag word flag_off[i], i < nranks, i != skip, has reached `value`.
+PDB_RT_EXPORT int pdb200_symm_wait_flags(void* a, int64_t flag_off, int64_t value, int skip, void* stream) {
+  pdbrt::Arena* A = (pdbrt::Arena*)a;
+  pdbrt::Driver& d = pdbrt::drv();
+  if (!d.cuStreamWaitValue32) {
+    pdbrt::set_error("symm_wait_flags: cuStreamWaitValue32 unavailable");
+    return -1;
+  }
+  for (int i = 0; i < A->nranks(); ++i) {
+    if (i == skip) continue;
+    CUresult e = d.cuStreamWaitValue32((CUstream)stream, (CUdeviceptr)(A->peer(A->rank()) + flag_off + 4ull * (uint64_t)i), (cuuint32_t)value,
+                                       CU_STREAM_WAIT_VALUE_GEQ);
+    if (e != CUDA_SUCCESS) {
+      pdbrt::set_error("symm_wait_flags: cuStreamWaitValue32 failed: %s", pdbrt::cu_err(e).c_str());
+      return -1;
     }
   }
   return 0;

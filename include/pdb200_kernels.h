@@ -98,6 +98,10 @@ PDB_API int pdb200_gemm_bf16_pair(const void* a, const void* b, void* c, const v
  * swizzled-smem + TMA-store epilogue; fp32 C += is a TMA reduce-add (csrc/kernels/gemm_tc3.cu). */
 PDB_API int pdb200_gemm_bf16_macro(const void* a, const void* b, void* c, const void* bias, int64_t M, int64_t N, int64_t K, int trans_a, int trans_b, int out_dtype, float beta, int act, void* stream);
 PDB_API int pdb200_gemm_set_band(int n);
+/* K6 GEMM -> reduce-scatter, compute half: row blocks of block_rows rows are finished one after the other starting at pair-row
+ * m_rot, and every finished piece is counted into done_counters[row / block_rows] (device uint32, +ceil(N/256)*8 per
+ * 256 rows), so a stream can wait for a block (pdb200_nvl_wait_counter) and ship it while the rest is computed. */
+PDB_API int pdb200_gemm_bf16_counted(const void* a, const void* b, void* c, int64_t M, int64_t N, int64_t K, int trans_b, void* done_counters, int block_rows, int m_rot, void* stream);
 /* K5 all-gather -> GEMM, compute half: A is the gathered activation in LOCAL memory; rows [i*gate_rows, (i+1)*gate_rows)
  * are loaded only after the local uint32 gate_flags[i] has reached gate_epoch (set by the peer whose chunk landed, see
  * pdb200_nvl_signal); row blocks are visited from pair-row m_rot on (this rank's own rows first).  gate_rows % 256 == 0. */
@@ -126,6 +130,11 @@ PDB_API int pdb200_nvl_set_progress(uint64_t host_mapped_ptr);
 /* flag word (flag_off + 4*index) of every rank's segment <- value, system-scope release; enqueue it behind the copies it
  * announces. */
 PDB_API int pdb200_nvl_signal(const uint64_t* peer_ptrs, int nranks, int rank, int64_t flag_off, int index, int64_t value, void* stream);
+PDB_API int pdb200_nvl_signal_one(const uint64_t* peer_ptrs, int nranks, int rank, int target, int64_t flag_off, int index, int64_t value, void* stream);
+/* Stream-ordered waits: until *counter (local, device-scope atomics of a running kernel) >= target; until `count` local
+ * flag words (peers' signals) have all reached epoch (skip_index < 0: none skipped). */
+PDB_API int pdb200_nvl_wait_counter(const void* counter, int64_t target, void* stream);
+PDB_API int pdb200_nvl_wait_flags(const void* flags, int count, int64_t epoch, int skip_index, void* stream);
 PDB_API int pdb200_nvl_barrier(const uint64_t* peer_ptrs, int nranks, int rank, int64_t pad_off, int64_t epoch, void* stream);
 PDB_API int pdb200_nvl_allreduce(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t data_off, int64_t numel, int dtype, float scale, int64_t pad_off, int64_t epoch, int max_ctas, void* stream);
 PDB_API int pdb200_nvl_rs_adamw_ag(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t grad_off, int grad_dtype, int64_t param_off, int64_t shard_start, int64_t shard_numel, float* master, float* m, float* v, float lr, float beta1, float beta2, float eps, float weight_decay, const float* beta_pows, const float* grad_scale, const float* found_inf, const float* local_grad, int64_t pad_off, int64_t epoch, void* stream);
@@ -145,6 +154,7 @@ PDB_API int pdb200_nvl_reduce_scatter_multi(const uint64_t* peer_ptrs, uint64_t 
 /* Local half of the copy-engine reduce-scatter: out (+)= scale * sum over the nranks receive slots; segs = HOST triples
  * {recv pointer (local), shard_numel, fp32 out pointer}. */
 PDB_API int pdb200_reduce_slots_multi(const int64_t* segs, int nseg, int nranks, int grad_dtype, float scale, int accumulate, int max_ctas, void* stream);
+PDB_API int pdb200_reduce_slots_multi2(const int64_t* segs, int nseg, int nranks, int grad_dtype, float scale, int accumulate, int out_dtype, int max_ctas, void* stream);
 /* Sum reduce-scatter of a symmetric bf16 buffer into a local bf16 shard (tail of GEMM -> reduce-scatter; NVLS in-switch add). */
 PDB_API int pdb200_nvl_rs_sum_bf16(const uint64_t* peer_ptrs, uint64_t mc_ptr, int nranks, int rank, int64_t src_off, int64_t shard_start, int64_t shard_numel, void* out, int64_t pad_off, int64_t epoch, void* stream);
 PDB_API int pdb200_nvl_ce_combine(const uint64_t* peer_ptrs, int nranks, int rank, int64_t stats_off, const int64_t* labels, float* loss, float* lse, int64_t rows, int64_t ignore_index, int64_t pad_off, int64_t epoch, void* stream);

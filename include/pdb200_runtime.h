@@ -103,6 +103,17 @@ PDB_API int pdb200_symm_allgather_ce(void* arena, const int64_t* segs, int nseg,
 /* Broadcast of byte ranges on the copy engines: [src_off, +nbytes) of this rank's segment to [dst_off, +nbytes) of every
  * rank's segment. */
 PDB_API int pdb200_symm_bcast_ce(void* arena, const int64_t* segs, int nseg, void* stream);
+/* One copy-engine put: [src_off, +nbytes) of this rank's segment -> [dst_off, +nbytes) of rank `peer`'s segment. */
+PDB_API int pdb200_symm_put_ce(void* arena, int peer, int64_t src_off, int64_t dst_off, int64_t nbytes, void* stream);
+/* Overlapped GEMM + collective plumbing, one native call per collective (flags are 32-bit words in the arena; a flag
+ * write is a stream-ordered 32-bit memset into the receiver's mapping, a wait is cuStreamWaitValue32 on a local word).
+ * push_signal (K5): nchunks chunks of this rank go to every rank at the same offsets, each followed by its flag.
+ * ship_blocks (K6): for every other owner, wait for the local counter of its block, copy the block into slot `rank` of
+ * the owner's receive buffer, raise the owner's flag[rank].  wait_flags: the stream waits for all local flags. */
+PDB_API int pdb200_symm_streamops_supported();
+PDB_API int pdb200_symm_push_signal(void* arena, int64_t src_off, int64_t dst_off, int64_t chunk_bytes, int nchunks, int64_t flag_off, int flag_index0, int64_t value, void* stream);
+PDB_API int pdb200_symm_ship_blocks(void* arena, int64_t counters_off, int64_t target, int64_t part_off, int64_t recv_off, int64_t blk_bytes, int64_t flag_off, int64_t value, void* stream);
+PDB_API int pdb200_symm_wait_flags(void* arena, int64_t flag_off, int64_t value, int skip, void* stream);
 /* All-to-all on the copy engines (transfer half of a reduce-scatter): shard p of this rank's buffer at src_off goes to
  * slot `rank` of rank p's receive buffer at dst_off; a local kernel sums the slots afterwards. */
 PDB_API int pdb200_symm_alltoall_ce(void* arena, const int64_t* segs, int nseg, void* stream);

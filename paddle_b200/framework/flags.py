@@ -100,6 +100,7 @@ define_flag("comm_watchdog_poll_ms", 10000, "polling interval of the communicati
 define_flag("comm_watchdog_abort", False, "the watchdog ends the process (exit code 113) when a collective times out, so the launcher can restart the pod")
 define_flag("use_native_process_group", False, "route paddle.distributed collectives on CUDA tensors through the native NCCL process group of libpdb200_runtime.so (own communicators, comm stream, event-based tasks) instead of torch.distributed")
 define_flag("ag_gemm_overlap", True, "K5: chunked copy-engine all-gather with per-chunk flags, consumed by the gated CTA-pair GEMM while later chunks are still in flight (False: gather, then GEMM)")
+define_flag("gemm_rs_overlap", True, "K6: the GEMM counts finished owner blocks, a side stream ships each block to its owner with the copy engines while the GEMM continues, a local kernel sums the n partial blocks (False: GEMM, then one NVLS pull-reduce kernel)")
 define_flag("stage3_nvl_transport", True, "GroupSharded stage 3: move parameters/gradients with the NVLink symmetric-memory kernels (K3 push all-gather, pull reduce-scatter) instead of NCCL")
 define_flag("gemm_cta_pair", True, "use the CTA-pair (cta_group::2, 256x256 tile) GEMM kernel for large shapes")
 define_flag("use_tcgen05_gemm", True, "route Linear GEMMs through the tcgen05/TMA kernel when shapes allow")

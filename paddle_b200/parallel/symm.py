@@ -350,7 +350,15 @@ def _ag_buffers(arena, rows, K, n):
     key = (id(arena), rows, K)
     st = _ag_state.get(key)
     if st is None:
-        chunk = 256 if rows % 256 == 0 else 0
+        # chunks of >= 256 rows and ~4 MB or more (a copy-engine transfer has a few microseconds of fixed cost), at most
+        # 4 per rank; the gate granularity of the GEMM is the chunk
+        chunk = 0
+        if rows % 256 == 0:
+            chunk = rows
+            for parts in (4, 2):
+                if rows % (parts * 256) == 0 and (rows // parts) * K * 2 >= (4 << 20):
+                    chunk = rows // parts
+                    break
         nchunks = (rows // chunk) * n if chunk else 0
         st = dict(full=[arena.empty((rows * n, K), torch.bfloat16) for _ in range(2)],
                   flags=[arena.empty((max(nchunks, 1),), torch.int32) for _ in range(2)],
@@ -382,7 +390,8 @@ def ag_gemm(x_shard, weight, group, bias=None, trans_b=False, act=None):
     st = _ag_buffers(arena, rows, K, n)
     xs = x_shard.contiguous()
     gated = (st["chunk"] > 0 and flag("ag_gemm_overlap") and hasattr(lib.kernels.require(), "pdb200_gemm_bf16_gated")
-             and hasattr(arena._rt, "pdb200_symm_allgather_ce") and K % 64 == 0 and N % 8 == 0 and weight.is_contiguous())
+             and hasattr(arena._rt, "pdb200_symm_push_signal") and arena._rt.pdb200_symm_streamops_supported() == 1
+             and K % 64 == 0 and N % 8 == 0 and weight.is_contiguous())
     if not gated:
         full = st["full"][0]
         check(lib.kernels.pdb200_nvl_allgather_from(arena.peers_arg, arena.mc_ptr, n, arena.rank, ptr(xs),
@@ -411,12 +420,10 @@ def ag_gemm(x_shard, weight, group, bias=None, trans_b=False, act=None):
         side.wait_event(ready)
         stage.copy_(xs, non_blocking=True)
         xs.record_stream(side)
-        for c in range(per_rank):
-            # chunk c of rank r lands at row r * rows + c * chunk of every rank's gathered buffer
-            _ce_chunk(arena, stage._symm[1] + c * chunk_bytes, full._symm[1] + (arena.rank * rows + c * chunk) * K * 2,
-                      chunk_bytes, side.cuda_stream)
-            check(lib.kernels.pdb200_nvl_signal(arena.peers_arg, n, arena.rank, flags._symm[1], arena.rank * per_rank + c, epoch,
-                                                side.cuda_stream), "nvl_signal")
+        # chunk c of rank r lands at row r * rows + c * chunk of every rank's gathered buffer, then its flag is raised
+        if arena._rt.pdb200_symm_push_signal(arena._h, stage._symm[1], full._symm[1] + arena.rank * rows * K * 2, chunk_bytes, per_rank,
+                                             flags._symm[1], arena.rank * per_rank, epoch, side.cuda_stream) != 0:
+            raise RuntimeError(f"symm_push_signal: {arena._rt.pdb200_rt_last_error().decode()}")
     out = torch.empty(rows * n, N, dtype=torch.bfloat16, device=xs.device)
     _assert_local(arena, full, weight, out)
     check(lib.kernels.pdb200_gemm_bf16_gated(ptr(full), ptr(weight), ptr(out), ptr(bias), rows * n, N, K, int(trans_b),
@@ -435,10 +442,35 @@ def _ce_chunk(arena, src_off, dst_off, nbytes, stream):
         raise RuntimeError(f"symm_bcast_ce: {arena._rt.pdb200_rt_last_error().decode()}")
 
 
-def gemm_rs(x, weight, group, trans_b=False):
-    """K6: ``reduce_scatter(x @ weight, dim 0)``.  The CTA-pair GEMM writes its partial product into (local)
-    symmetric memory; every owner then pulls its rows through the switch (``multimem.ld_reduce`` adds the n copies in
-    flight).  x: [nranks*rows, K] bf16; returns [rows, N]."""
+_rs_state = {}
+
+
+def _rs_buffers(arena, rows, N, n):
+    key = (id(arena), rows, N)
+    st = _rs_state.get(key)
+    if st is None:
+        st = dict(part=[arena.empty((rows * n, N), torch.bfloat16) for _ in range(2)],
+                  recv=[arena.empty((n, rows, N), torch.bfloat16) for _ in range(2)],
+                  counters=[arena.empty((max(n, 8),), torch.int32) for _ in range(2)],
+                  flags=[arena.empty((max(n, 8),), torch.int32) for _ in range(2)],
+                  stream=torch.cuda.Stream(priority=-1), calls=0, uses=[0, 0])
+        for t in st["counters"] + st["flags"]:
+            t.zero_()
+        torch.cuda.current_stream().synchronize()
+        C.barrier(arena.group)
+        _rs_state[key] = st
+    return st
+
+
+def gemm_rs(x, weight, group, trans_b=False, _out=None):
+    """K6: ``reduce_scatter(x @ weight, dim 0)`` with the transfer hidden behind the GEMM.
+
+    The CTA-pair GEMM works through the owners' row blocks one after the other, its own block last, and counts every
+    finished piece into a per-block counter.  A side stream waits for a block's counter, ships the block to its owner
+    with the copy engines and raises the owner's arrival flag - while the GEMM is still computing the later blocks.
+    When the GEMM ends only the last remote block is still in flight; a local kernel then sums the n partial blocks
+    (its own and the n-1 received ones).  Falls back to GEMM + one NVLS pull-reduce kernel for shapes that cannot be
+    blocked.  x: [nranks*rows, K] bf16; returns [rows, N] bf16."""
     from paddle_b200.lib import check
     from paddle_b200.ops._util import ptr
     arena = get_arena(group)
@@ -446,11 +478,49 @@ def gemm_rs(x, weight, group, trans_b=False):
     n = arena.nranks
     rows = M // n
     N = weight.shape[0] if trans_b else weight.shape[1]
-    part = _gemm_into_symmetric(arena, x, weight, trans_b, "rs_part")
-    out = torch.empty(rows, N, dtype=torch.bfloat16, device=x.device)
-    check(lib.kernels.pdb200_nvl_rs_sum_bf16(arena.peers_arg, arena.mc_ptr, n, arena.rank, part._symm[1],
-                                             arena.rank * rows * N, rows * N, ptr(out), 0, arena.next_epoch(),
-                                             stream_ptr(x.device)), "nvl_rs_sum_bf16")
+    overlapped = (flag("gemm_rs_overlap") and rows % 256 == 0 and K % 8 == 0 and N % 8 == 0 and weight.is_contiguous()
+                  and hasattr(lib.kernels.require(), "pdb200_gemm_bf16_counted") and hasattr(arena._rt, "pdb200_symm_ship_blocks")
+                  and arena._rt.pdb200_symm_streamops_supported() == 1)
+    if not overlapped:
+        part = _gemm_into_symmetric(arena, x, weight, trans_b, "rs_part")
+        out = _out if _out is not None else torch.empty(rows, N, dtype=torch.bfloat16, device=x.device)
+        check(lib.kernels.pdb200_nvl_rs_sum_bf16(arena.peers_arg, arena.mc_ptr, n, arena.rank, part._symm[1],
+                                                 arena.rank * rows * N, rows * N, ptr(out), 0, arena.next_epoch(),
+                                                 stream_ptr(x.device)), "nvl_rs_sum_bf16")
+        return out
+    st = _rs_buffers(arena, rows, N, n)
+    st["calls"] += 1
+    epoch = st["calls"]
+    b = epoch & 1
+    st["uses"][b] += 1
+    part, recv, counters, flags = st["part"][b], st["recv"][b], st["counters"][b], st["flags"][b]
+    per_block = (rows // 256) * ((N + 255) // 256) * 8           # counter growth per finished block
+    target = st["uses"][b] * per_block
+    cur, side = torch.cuda.current_stream(), st["stream"]
+    xc = x.contiguous()
+    _assert_local(arena, xc, weight, part)
+    start = torch.cuda.Event()
+    start.record(cur)                                             # everything before this call is enqueued ahead
+    r = arena.rank
+    check(lib.kernels.pdb200_gemm_bf16_counted(ptr(xc), ptr(weight), ptr(part), M, N, K, int(trans_b), ptr(counters), rows,
+                                               (((r + 1) % n) * rows) // 256, stream_ptr(x.device)), "gemm_bf16_counted")
+    blk = rows * N * 2
+    with torch.cuda.stream(side):
+        side.wait_event(start)
+        if arena._rt.pdb200_symm_ship_blocks(arena._h, counters._symm[1], target, part._symm[1], recv._symm[1], blk, flags._symm[1],
+                                             epoch, side.cuda_stream) != 0:
+            raise RuntimeError(f"symm_ship_blocks: {arena._rt.pdb200_rt_last_error().decode()}")
+        sent = torch.cuda.Event()
+        sent.record(side)
+    # own block: after the GEMM (stream order) copy it next to the received ones, wait for the n-1 arrivals, sum
+    recv[r].copy_(part[r * rows:(r + 1) * rows], non_blocking=True)
+    if arena._rt.pdb200_symm_wait_flags(arena._h, flags._symm[1], epoch, r, stream_ptr(x.device)) != 0:
+        raise RuntimeError(f"symm_wait_flags: {arena._rt.pdb200_rt_last_error().decode()}")
+    out = _out if _out is not None else torch.empty(rows, N, dtype=torch.bfloat16, device=x.device)
+    tri = (ctypes.c_int64 * 3)(recv.data_ptr(), rows * N, out.data_ptr())
+    check(lib.kernels.pdb200_reduce_slots_multi2(ctypes.cast(tri, ctypes.c_void_p), 1, n, 1, 1.0, 0, 1, 0, stream_ptr(x.device)),
+          "reduce_slots")
+    cur.wait_event(sent)          # this rank's puts are done before part[b] can be written again (two calls from now)
     return out
 
 
@@ -469,14 +539,49 @@ def _gemm_into_symmetric(arena, x, weight, trans_b, tag):
     return part
 
 
+_ar_state = {}
+
+
 def gemm_ar(x, weight, group, trans_b=False):
-    """K4: ``all_reduce(x @ weight)`` for the non-sequence-parallel TP linears: the GEMM writes its partial product
-    into symmetric memory and the NVLS two-shot all-reduce (K1) sums it in place.  x: [M, K] bf16; returns a private
-    [M, N] copy (the staging buffer is reused by the next call of the same shape)."""
+    """K4: ``all_reduce(x @ weight)`` for the non-sequence-parallel TP linears = the overlapped GEMM -> reduce-scatter of
+    ``gemm_rs`` (row blocks leave for their owners while the GEMM still runs) followed by a copy-engine all-gather of the
+    reduced blocks, each announced by a flag.  x: [M, K] bf16, M divisible by nranks*256 for the overlapped path
+    (otherwise: GEMM into a symmetric buffer + the NVLS two-shot all-reduce kernel).  Returns a private [M, N] tensor."""
+    from paddle_b200.lib import check
+    from paddle_b200.ops._util import ptr
     arena = get_arena(group)
-    part = _gemm_into_symmetric(arena, x, weight, trans_b, "ar_part")
-    allreduce_(part)
-    return part.clone()
+    M, K = x.shape
+    n = arena.nranks
+    N = weight.shape[0] if trans_b else weight.shape[1]
+    rows = M // n
+    if not (flag("gemm_rs_overlap") and M % n == 0 and rows % 256 == 0 and hasattr(arena._rt, "pdb200_symm_push_signal")
+            and arena._rt.pdb200_symm_streamops_supported() == 1 and hasattr(lib.kernels.require(), "pdb200_gemm_bf16_counted")):
+        part = _gemm_into_symmetric(arena, x, weight, trans_b, "ar_part")
+        allreduce_(part)
+        return part.clone()
+    key = (id(arena), M, N)
+    st = _ar_state.get(key)
+    if st is None:
+        st = dict(red=[arena.empty((rows, N), torch.bfloat16) for _ in range(2)],
+                  full=[arena.empty((M, N), torch.bfloat16) for _ in range(2)],
+                  flags=[arena.empty((max(n, 8),), torch.int32) for _ in range(2)], calls=0)
+        for t in st["flags"]:
+            t.zero_()
+        torch.cuda.current_stream().synchronize()
+        C.barrier(arena.group)
+        _ar_state[key] = st
+    st["calls"] += 1
+    epoch = st["calls"]
+    b = epoch & 1
+    red, full, flags = st["red"][b], st["full"][b], st["flags"][b]
+    gemm_rs(x, weight, group, trans_b, _out=red)                 # my reduced block, in the arena
+    stream = stream_ptr(x.device)
+    blk = rows * N * 2
+    if arena._rt.pdb200_symm_push_signal(arena._h, red._symm[1], full._symm[1] + arena.rank * blk, blk, 1, flags._symm[1], arena.rank,
+                                         epoch, stream) != 0 or \
+            arena._rt.pdb200_symm_wait_flags(arena._h, flags._symm[1], epoch, -1, stream) != 0:
+        raise RuntimeError(f"gemm_ar: {arena._rt.pdb200_rt_last_error().decode()}")
+    return full.clone()
 
 
 def vocab_embed(ids, weight, where):

@@ -115,6 +115,26 @@ for it in range(5):
     got = symm.ag_gemm(xs2, w2, g)
     torch.testing.assert_close(got.float(), ref2, rtol=2e-2, atol=1e-1, msg=lambda m: f"overlapped ag_gemm call {it}: {m}")
 assert any(v["calls"] >= 5 for v in symm._ag_state.values()), "the gated (overlapped) path did not run"
+# overlapped K6: blocks leave for their owners while the GEMM still computes the later ones; 5 calls, fresh data
+w3 = (torch.randn(K2, N2, device=dev) * 0.05).bfloat16()
+dist.broadcast(w3, 0)
+for it in range(5):
+    torch.manual_seed(700 + 10 * it + r)
+    xf2 = (torch.randn(rows2 * n, K2, device=dev) * 0.5).bfloat16()
+    partial2 = xf2.float() @ w3.float()
+    dist.all_reduce(partial2)
+    got = symm.gemm_rs(xf2, w3, g)
+    torch.testing.assert_close(got.float(), partial2[r * rows2:(r + 1) * rows2], rtol=2e-2, atol=2e-1,
+                               msg=lambda m: f"overlapped gemm_rs call {it}: {m}")
+assert any(v["calls"] >= 5 for v in symm._rs_state.values()), "the overlapped reduce-scatter path did not run"
+for it in range(4):                       # overlapped K4 = overlapped K6 + copy-engine all-gather of the reduced blocks
+    torch.manual_seed(300 + 10 * it + r)
+    xf2 = (torch.randn(rows2 * n, K2, device=dev) * 0.5).bfloat16()
+    partial2 = xf2.float() @ w3.float()
+    dist.all_reduce(partial2)
+    got = symm.gemm_ar(xf2, w3, g)
+    torch.testing.assert_close(got.float(), partial2, rtol=2e-2, atol=2e-1, msg=lambda m: f"overlapped gemm_ar call {it}: {m}")
+assert any(v["calls"] >= 4 for v in symm._ar_state.values()), "the overlapped all-reduce path did not run"
 wt = w.t().contiguous()                   # trans_b variants (backward shapes)
 got = symm.ag_gemm(xs, wt, g, trans_b=True)
 torch.testing.assert_close(got.float(), ref, rtol=2e-2, atol=5e-2)
