@@ -308,7 +308,10 @@ def main():
     transport = "none"
     if world > 1:
         nvl = getattr(model, "_nvl", None)
-        transport = "nvlink-symmetric (multimem all-gather / ld_reduce reduce-scatter)" if nvl is not None else "nccl"
+        transport = "nccl"
+        if nvl is not None:
+            transport = (f"nvlink-symmetric arena: all-gather={'copy engines' if nvl.ag_mode == 'ce' else 'multimem/peer-store kernel'}, "
+                         f"reduce-scatter={'copy-engine all-to-all + local sum kernel' if nvl.rs_mode == 'ce' else 'multimem/peer-load kernel'}")
         if nvl is not None and not args.no_exposed:
             nvl.noop = True
             train_step(dev_ring[0])

@@ -134,7 +134,8 @@ def main():
         g = dist.collective._get_default_group()
         cfg = MoEConfig.mixtral_8x7b()
         cfg.num_hidden_layers = args.layers or 8
-        cfg.grouped_experts = os.environ.get("PDB200_MOE_GROUPED", "1") != "0"   # 0: per-expert loop after a host read
+        if os.environ.get("PDB200_MOE_GROUPED"):          # 1 / 0 force the grouped GEMM path on / off (default: automatic)
+            cfg.grouped_experts = os.environ["PDB200_MOE_GROUPED"] != "0"
         B, S = args.batch or 1, args.seq
         paddle.seed(1234 + dist.get_rank())
         paddle.set_default_dtype("bfloat16")
@@ -162,7 +163,7 @@ def main():
                    value=round(B * S * world / ms * 1e3, 1), unit="tokens/s",
                    config={"model": "mixtral-8x7b widths", "layers": cfg.num_hidden_layers, "global_batch": B * world, "seq_len": S,
                            "parallelism": f"ep{world} + dp{world} (dense)", "experts": cfg.num_experts, "top_k": cfg.top_k,
-                           "fused_dispatch_combine": bool(moe_fused._state), "grouped_expert_gemm": cfg.grouped_experts})
+                           "fused_dispatch_combine": bool(moe_fused._state), "grouped_expert_gemm": cfg.grouped_experts if cfg.grouped_experts is not None else cfg.num_experts // max(world, 1) > 1})
 
     res.update(ms_per_step=round(ms, 3), final_loss=round(float(loss), 4), gpu_launches=launches)
     if dist.get_rank() == 0:

@@ -15,7 +15,10 @@ class MoEConfig(LlamaConfig):
     num_experts: int = 8
     top_k: int = 2
     gate_type: str = "naive"
-    grouped_experts: bool = True      # stacked expert weights + device-scheduled grouped GEMMs (no per-expert launches)
+    # stacked expert weights + device-scheduled grouped GEMMs (one launch for all local experts, no host read of the
+    # counts).  None = automatic: on when a rank holds several experts; with a single local expert the "group" is one
+    # GEMM and the CTA-pair kernel behind Linear is the faster way to run it.
+    grouped_experts: bool | None = None
 
     @staticmethod
     def mixtral_8x7b(**kw):
@@ -49,7 +52,9 @@ class MoEDecoderLayer(nn.Layer):
         self.input_layernorm = nn.RMSNorm(config.hidden_size, config.rms_norm_eps)
         self.self_attn = LlamaAttention(config)
         self.post_attention_layernorm = nn.RMSNorm(config.hidden_size, config.rms_norm_eps)
-        if config.grouped_experts:
+        n_local = config.num_experts // world
+        grouped = config.grouped_experts if config.grouped_experts is not None else n_local > 1
+        if grouped:
             from paddle_b200.incubate.distributed.models.moe import GroupedExpertsFFN
             experts = GroupedExpertsFFN(config.num_experts // world, config.hidden_size, config.intermediate_size,
                                         weight_attr=_init(config.initializer_range))

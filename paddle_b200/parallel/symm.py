@@ -343,6 +343,13 @@ def _assert_local(arena, *tensors):
 _ag_state = {}
 
 
+def _worth_overlapping(M, N, K):
+    """The overlapped K4/K5/K6 paths pay a fixed price per call (n-1 copy-engine transfers of a few microseconds each,
+    stream memory operations, a second stream): below ~0.15 ms of GEMM the two-kernel path (one NVLS collective kernel +
+    the GEMM) is faster.  Threshold in GFLOP per rank, PDB200_OVERLAP_MIN_GFLOP (default 200)."""
+    return 2.0 * M * N * K >= float(os.environ.get("PDB200_OVERLAP_MIN_GFLOP", "200")) * 1e9
+
+
 def _ag_buffers(arena, rows, K, n):
     """Per (arena, shape): two gathered buffers (alternating per call, so a peer may already push the next call's rows
     while this rank still reads the previous ones), one flag word per 256-row chunk and buffer, a side stream, a
@@ -389,7 +396,7 @@ def ag_gemm(x_shard, weight, group, bias=None, trans_b=False, act=None):
     N = weight.shape[0] if trans_b else weight.shape[1]
     st = _ag_buffers(arena, rows, K, n)
     xs = x_shard.contiguous()
-    gated = (st["chunk"] > 0 and flag("ag_gemm_overlap") and hasattr(lib.kernels.require(), "pdb200_gemm_bf16_gated")
+    gated = (st["chunk"] > 0 and flag("ag_gemm_overlap") and _worth_overlapping(rows * n, N, K) and hasattr(lib.kernels.require(), "pdb200_gemm_bf16_gated")
              and hasattr(arena._rt, "pdb200_symm_push_signal") and arena._rt.pdb200_symm_streamops_supported() == 1
              and K % 64 == 0 and N % 8 == 0 and weight.is_contiguous())
     if not gated:
@@ -478,7 +485,7 @@ def gemm_rs(x, weight, group, trans_b=False, _out=None):
     n = arena.nranks
     rows = M // n
     N = weight.shape[0] if trans_b else weight.shape[1]
-    overlapped = (flag("gemm_rs_overlap") and rows % 256 == 0 and K % 8 == 0 and N % 8 == 0 and weight.is_contiguous()
+    overlapped = (flag("gemm_rs_overlap") and (_out is not None or _worth_overlapping(M, N, K)) and rows % 256 == 0 and K % 8 == 0 and N % 8 == 0 and weight.is_contiguous()
                   and hasattr(lib.kernels.require(), "pdb200_gemm_bf16_counted") and hasattr(arena._rt, "pdb200_symm_ship_blocks")
                   and arena._rt.pdb200_symm_streamops_supported() == 1)
     if not overlapped:
@@ -554,7 +561,7 @@ def gemm_ar(x, weight, group, trans_b=False):
     n = arena.nranks
     N = weight.shape[0] if trans_b else weight.shape[1]
     rows = M // n
-    if not (flag("gemm_rs_overlap") and M % n == 0 and rows % 256 == 0 and hasattr(arena._rt, "pdb200_symm_push_signal")
+    if not (flag("gemm_rs_overlap") and _worth_overlapping(M, N, K) and M % n == 0 and rows % 256 == 0 and hasattr(arena._rt, "pdb200_symm_push_signal")
             and arena._rt.pdb200_symm_streamops_supported() == 1 and hasattr(lib.kernels.require(), "pdb200_gemm_bf16_counted")):
         part = _gemm_into_symmetric(arena, x, weight, trans_b, "ar_part")
         allreduce_(part)
