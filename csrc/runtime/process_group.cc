@@ -228,6 +228,35 @@ PDB_RT_EXPORT int pdb200_pg_nccl_version() {
 // Create the communicator of group `gid` (ranks 0..nranks-1 of the group; `rank` is this process's index in it) on the
 // current device.  `store`: a pdb200_store handle shared by the ranks; the group's first rank publishes the NCCL unique
 // id under "<prefix>/nccl_id/<gid>".  Collective: every rank of the group must call it.
+// Comm streams live as long as the process.  A caching allocator that was told "this block is in use on the comm
+// stream" records an event on that stream when the block is freed, which can be long after the group is gone; a
+// destroyed stream handle there is a use-after-free.  So a closed group hands its stream back to a per-device pool
+// and the next group on that device takes it from there.
+static std::mutex g_stream_mu;
+static std::vector<std::pair<int, cudaStream_t>> g_stream_pool;
+
+static cudaStream_t acquire_comm_stream(int device) {
+  {
+    std::lock_guard<std::mutex> g(g_stream_mu);
+    for (size_t i = 0; i < g_stream_pool.size(); ++i)
+      if (g_stream_pool[i].first == device) {
+        cudaStream_t s = g_stream_pool[i].second;
+        g_stream_pool.erase(g_stream_pool.begin() + i);
+        return s;
+      }
+  }
+  int lo = 0, hi = 0;
+  cudaStream_t s = nullptr;
+  cudaDeviceGetStreamPriorityRange(&lo, &hi);
+  cudaStreamCreateWithPriority(&s, cudaStreamNonBlocking, hi);     // highest priority: comm kernels go first
+  return s;
+}
+
+static void release_comm_stream(int device, cudaStream_t s) {
+  std::lock_guard<std::mutex> g(g_stream_mu);
+  g_stream_pool.emplace_back(device, s);
+}
+
 PDB_RT_EXPORT void* pdb200_pg_create(void* store, const char* prefix, int gid, int rank, int nranks, int timeout_ms) {
   NcclApi* n = nccl();
   if (!n) {
@@ -263,9 +292,7 @@ PDB_RT_EXPORT void* pdb200_pg_create(void* store, const char* prefix, int gid, i
     delete c;
     return nullptr;
   }
-  int lo = 0, hi = 0;
-  cudaDeviceGetStreamPriorityRange(&lo, &hi);
-  cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, hi);     // highest priority: comm kernels go first
+  c->stream = acquire_comm_stream(c->device);
   cudaEventCreateWithFlags(&c->ready, cudaEventDisableTiming);
   CommContextManager::get().put(gid, c);
   return c;
@@ -286,7 +313,7 @@ PDB_RT_EXPORT int pdb200_pg_destroy(void* pg) {
   }
   for (cudaEvent_t e : c->pool) cudaEventDestroy(e);
   if (c->ready) cudaEventDestroy(c->ready);
-  if (c->stream) cudaStreamDestroy(c->stream);
+  if (c->stream) release_comm_stream(c->device, c->stream);
   delete c;
   return 0;
 }
