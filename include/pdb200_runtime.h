@@ -118,6 +118,15 @@ PDB_API int pdb200_symm_wait_flags(void* arena, int64_t flag_off, int64_t value,
  * slot `rank` of rank p's receive buffer at dst_off; a local kernel sums the slots afterwards. */
 PDB_API int pdb200_symm_alltoall_ce(void* arena, const int64_t* segs, int nseg, void* stream);
 
+/* Offset heap of a symmetric arena: best fit, coalescing free; offsets depend on the call sequence only, so ranks that
+ * allocate and free in the same order agree on every offset.  alloc returns -1 when nothing fits.
+ * stat: 0 free bytes, 1 largest free block, 2 live blocks, 3 bytes in use, 4 peak bytes in use, 5 free blocks, 6 capacity. */
+PDB_API void* pdb200_heap_create(int64_t capacity, int64_t reserved);
+PDB_API void pdb200_heap_destroy(void* heap);
+PDB_API int64_t pdb200_heap_alloc(void* heap, int64_t nbytes, int64_t align);
+PDB_API int pdb200_heap_free(void* heap, int64_t offset);
+PDB_API int64_t pdb200_heap_stat(void* heap, int what);
+
 #ifdef __cplusplus
 }
 #endif

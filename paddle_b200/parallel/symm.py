@@ -70,7 +70,9 @@ class SymmArena:
         self._bytes[:PAD_BYTES].zero_()
         torch.cuda.synchronize()
         C.barrier(group)                       # pads are zero everywhere before the first in-stream barrier
-        self._top = PAD_BYTES
+        # offsets come from a native best-fit heap with coalescing free (csrc/runtime/heap.cc); it is a pure function of
+        # the alloc/free call sequence, so ranks running the same program agree on every offset
+        self._heap = rt.pdb200_heap_create(self.nbytes, PAD_BYTES)
         self._epoch = 1
 
     @property
@@ -83,14 +85,31 @@ class SymmArena:
         return e
 
     def alloc(self, nbytes, align=256):
-        off = (self._top + align - 1) // align * align
-        if off + nbytes > self.nbytes:
-            raise MemoryError(f"symmetric arena exhausted: need {nbytes} B at {off}, capacity {self.nbytes}")
-        self._top = off + int(nbytes)
+        off = self._rt.pdb200_heap_alloc(self._heap, int(nbytes), int(align))
+        if off < 0 and _evict_cached(self, int(nbytes) + align):
+            off = self._rt.pdb200_heap_alloc(self._heap, int(nbytes), int(align))
+        if off < 0:
+            raise MemoryError(f"symmetric arena exhausted: need {nbytes} B, largest free block {self.largest_free()} B of "
+                              f"{self.free_bytes()} B free, capacity {self.nbytes} B (PDB200_SYMM_ARENA_MB sets the size)")
         return off
 
+    def free(self, t_or_offset):
+        """Give a buffer back (the tensor from ``empty`` or its offset).  Collective in the same sense as ``empty``: every
+        rank must free in the same order, and nobody - no kernel of this rank, no peer - may still be using the bytes."""
+        off = t_or_offset._symm[1] if hasattr(t_or_offset, "_symm") else int(t_or_offset)
+        if self._rt.pdb200_heap_free(self._heap, off) != 0:
+            raise ValueError(f"symmetric arena: offset {off} is not a live allocation")
+
     def free_bytes(self):
-        return self.nbytes - self._top
+        return self._rt.pdb200_heap_stat(self._heap, 0)
+
+    def largest_free(self):
+        return self._rt.pdb200_heap_stat(self._heap, 1)
+
+    def stats(self):
+        st = self._rt.pdb200_heap_stat
+        return dict(capacity=self.nbytes, free=st(self._heap, 0), largest_free=st(self._heap, 1), live_blocks=st(self._heap, 2),
+                    in_use=st(self._heap, 3), peak_in_use=st(self._heap, 4), free_blocks=st(self._heap, 5))
 
     def tensor(self, offset, shape, dtype):
         n = 1
@@ -116,6 +135,11 @@ class SymmArena:
                     lib.kernels.pdb200_unregister_foreign_range(base)
             self._rt.pdb200_symm_destroy(self._h)
             self._h = None
+            self._rt.pdb200_heap_destroy(self._heap)
+            self._heap = None
+            for cache in _caches:
+                for k in [k for k in cache if k[0] == id(self)]:
+                    del cache[k]
 
 
 def available(group=None) -> bool:
@@ -138,7 +162,7 @@ def available(group=None) -> bool:
 def get_arena(group, min_bytes=int(os.environ.get("PDB200_SYMM_ARENA_MB", "512")) << 20, key="default"):
     k = (group.id, key)
     a = _arenas.get(k)
-    if a is None or a.free_bytes() < 0:
+    if a is None:
         try:
             a = SymmArena(group, min_bytes)
         except Exception as e:  # noqa: BLE001
@@ -316,15 +340,83 @@ def ce_exchange_combine(stats, labels, group, ignore_index):
     return loss, lse
 
 
-_stage = {}
+class _ShapeCache(dict):
+    """Per-shape staging state in an arena, least recently used first.  ``touch`` on every hit; ``_evict_cached`` pops
+    from the front when the arena runs out.  Keys start with id(arena)."""
+
+    def __init__(self):
+        super().__init__()
+        self._used = {}
+
+    def touch(self, key):
+        _tick[0] += 1
+        self._used[key] = _tick[0]
+        return self[key]
+
+    def __setitem__(self, key, value):
+        _tick[0] += 1
+        self._used[key] = _tick[0]
+        super().__setitem__(key, value)
+
+    def __delitem__(self, key):
+        self._used.pop(key, None)
+        super().__delitem__(key)
+
+    def pop(self, key, *default):
+        self._used.pop(key, None)
+        return super().pop(key, *default)
+
+    def lookup(self, key):
+        return self.touch(key) if key in self else None
+
+
+_tick = [0]
+_stage = _ShapeCache()
+_caches = [_stage]
+
+
+def _state_tensors(v):
+    if isinstance(v, torch.Tensor):
+        return [v] if hasattr(v, "_symm") else []
+    if isinstance(v, dict):
+        v = list(v.values())
+    if isinstance(v, (list, tuple)):
+        return [t for x in v for t in _state_tensors(x)]
+    return []
+
+
+def _evict_cached(arena, need):
+    """The arena is out of room: drop least-recently-used staging states (gathered buffers, partial-sum buffers, flag
+    words cached per shape) until a block of ``need`` bytes exists.  Every rank runs the same call sequence, so every
+    rank evicts the same entries here; a peer may still be writing into a buffer of an earlier call, hence the device
+    synchronisation and the group barrier before anything is reused.  Returns True if something was freed."""
+    victims = []
+    for cache in _caches:
+        for k in cache:
+            if k[0] == id(arena):
+                victims.append((cache._used.get(k, 0), id(cache), cache, k))
+    if not victims:
+        return False
+    victims = [(c, k) for _, _, c, k in sorted(victims, key=lambda v: v[:2])]      # least recently used first
+    torch.cuda.synchronize()
+    C.barrier(arena.group)
+    freed = False
+    for cache, k in victims:
+        for t in _state_tensors(cache.pop(k)):
+            arena.free(t)
+            freed = True
+        if arena.largest_free() >= need:
+            break
+    return freed
 
 
 def _staging(arena, tag, shape, dtype):
     key = (id(arena), tag, tuple(shape), dtype)
-    t = _stage.get(key)
-    if t is None:
-        t = arena.empty(shape, dtype)
-        _stage[key] = t
+    t = _stage.lookup(key)
+    if t is not None:
+        return t
+    t = arena.empty(shape, dtype)
+    _stage[key] = t
     return t
 
 
@@ -340,7 +432,8 @@ def _assert_local(arena, *tensors):
             assert not (base <= p < base + arena.nbytes), "tensor-core operand inside a mapping of another GPU's memory"
 
 
-_ag_state = {}
+_ag_state = _ShapeCache()
+_caches.append(_ag_state)
 
 
 def _worth_overlapping(M, N, K):
@@ -355,7 +448,7 @@ def _ag_buffers(arena, rows, K, n):
     while this rank still reads the previous ones), one flag word per 256-row chunk and buffer, a side stream, a
     monotonic call counter that doubles as the flag epoch."""
     key = (id(arena), rows, K)
-    st = _ag_state.get(key)
+    st = _ag_state.lookup(key)
     if st is None:
         # chunks of >= 256 rows and ~4 MB or more (a copy-engine transfer has a few microseconds of fixed cost), at most
         # 4 per rank; the gate granularity of the GEMM is the chunk
@@ -449,12 +542,13 @@ def _ce_chunk(arena, src_off, dst_off, nbytes, stream):
         raise RuntimeError(f"symm_bcast_ce: {arena._rt.pdb200_rt_last_error().decode()}")
 
 
-_rs_state = {}
+_rs_state = _ShapeCache()
+_caches.append(_rs_state)
 
 
 def _rs_buffers(arena, rows, N, n):
     key = (id(arena), rows, N)
-    st = _rs_state.get(key)
+    st = _rs_state.lookup(key)
     if st is None:
         st = dict(part=[arena.empty((rows * n, N), torch.bfloat16) for _ in range(2)],
                   recv=[arena.empty((n, rows, N), torch.bfloat16) for _ in range(2)],
@@ -546,7 +640,8 @@ def _gemm_into_symmetric(arena, x, weight, trans_b, tag):
     return part
 
 
-_ar_state = {}
+_ar_state = _ShapeCache()
+_caches.append(_ar_state)
 
 
 def gemm_ar(x, weight, group, trans_b=False):
@@ -567,7 +662,7 @@ def gemm_ar(x, weight, group, trans_b=False):
         allreduce_(part)
         return part.clone()
     key = (id(arena), M, N)
-    st = _ar_state.get(key)
+    st = _ar_state.lookup(key)
     if st is None:
         st = dict(red=[arena.empty((rows, N), torch.bfloat16) for _ in range(2)],
                   full=[arena.empty((M, N), torch.bfloat16) for _ in range(2)],

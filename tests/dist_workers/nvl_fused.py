@@ -182,6 +182,33 @@ ref_bn = torch.nn.functional.batch_norm(allx, None, None, bn.weight.detach(), bn
 torch.testing.assert_close(yb.detach(), ref_bn[r * 6:(r + 1) * 6], rtol=1e-4, atol=1e-4)
 yb.square().sum().backward()
 assert torch.isfinite(xb.grad).all()
+# ---- arena heap: free gives the bytes back at the same offset on every rank; exhaustion evicts cached staging buffers
+small = symm.SymmArena(g, 8 << 20)
+t1 = small.empty((3 << 20,), torch.uint8)
+t2 = small.empty((1 << 20,), torch.uint8)
+off1 = t1._symm[1]
+small.free(t1)
+t3 = small.empty((2 << 20,), torch.uint8)
+assert t3._symm[1] == off1, "freed block was not reused"
+offs = [None] * n
+dist.all_gather_object(offs, (t2._symm[1], t3._symm[1]))
+assert len(set(offs)) == 1, f"ranks disagree on offsets: {offs}"
+small.free(t2)
+small.free(t3)
+s1 = symm._staging(small, "evict_a", (3 << 20,), torch.uint8)
+s2 = symm._staging(small, "evict_b", (3 << 20,), torch.uint8)
+s3 = symm._staging(small, "evict_c", (3 << 20,), torch.uint8)          # does not fit next to a and b: a (least recent) goes
+assert (id(small), "evict_a", (3 << 20,), torch.uint8) not in symm._stage
+assert (id(small), "evict_b", (3 << 20,), torch.uint8) in symm._stage
+st = small.stats()
+assert st["live_blocks"] == 2 and st["in_use"] == 6 << 20, st
+s3.fill_(r + 1)
+try:
+    small.empty((9 << 20,), torch.uint8)
+    raise AssertionError("oversize allocation must fail")
+except MemoryError:
+    pass
+small.close()
 print("nvl_fused ok", r, flush=True)
 symm.release_all()
 dist.destroy_process_group()

@@ -90,3 +90,32 @@ def test_watchdog_reads_task_state_from_cuda_events():
         assert p != 0
     finally:
         rt.pdb200_wd_stop()
+
+
+def test_arena_heap_best_fit_coalesce_and_determinism():
+    """csrc/runtime/heap.cc: the symmetric arena's offset heap.  Offsets depend on the call sequence only."""
+    rt = lib.runtime.require()
+
+    def run():
+        h = rt.pdb200_heap_create(1 << 20, 4096)
+        offs = [rt.pdb200_heap_alloc(h, n, 256) for n in (1000, 70000, 300, 200000, 5000)]
+        assert all(o >= 4096 and o % 256 == 0 for o in offs)
+        spans = sorted(zip(offs, (1000, 70000, 300, 200000, 5000)))
+        assert all(a + n <= b for (a, n), (b, _) in zip(spans, spans[1:])), "allocations overlap"
+        # free two neighbours -> one coalesced hole that takes a request neither piece could hold alone
+        assert rt.pdb200_heap_free(h, offs[1]) == 0 and rt.pdb200_heap_free(h, offs[2]) == 0
+        assert rt.pdb200_heap_free(h, offs[2]) == -1, "double free must be refused"
+        big = rt.pdb200_heap_alloc(h, 70200, 256)
+        assert big == offs[1], "the coalesced hole is the best fit"
+        # best fit: a small request goes to the smallest hole that holds it, not to the big tail
+        rt.pdb200_heap_free(h, offs[4])
+        small = rt.pdb200_heap_alloc(h, 4000, 256)
+        assert small == offs[4]
+        assert rt.pdb200_heap_alloc(h, 1 << 21, 256) == -1
+        seq = offs + [big, small]
+        stats = [rt.pdb200_heap_stat(h, i) for i in range(7)]
+        assert stats[6] == 1 << 20 and stats[3] <= stats[4] and stats[0] + stats[3] <= (1 << 20) - 4096
+        rt.pdb200_heap_destroy(h)
+        return seq, stats
+
+    assert run() == run()
