@@ -1,7 +1,8 @@
-// K16: flash-attention forward on tcgen05 tensor cores for sm_100a (bf16, head_dim 64/128, causal or full, GQA).
+// K16: flash-attention forward on tcgen05 tensor cores for sm_100a (bf16 / fp16, head_dim 64/128, causal or full, GQA,
+// dense [b, s, h, d] batches of any length and packed variable-length batches with cu_seqlens, dropout).
 //
-// Replaces in the reference: paddle/phi/kernels/gpu/flash_attn_kernel.cu:305-447 -> vendored FlashAttention-2
-// (mma.sync m16n8k16 + cp.async, third_party/flashattn/csrc/flash_attn/src/flash_fwd_kernel.h).
+// Replaces in the reference: paddle/phi/kernels/gpu/flash_attn_kernel.cu:36-170 (unpadded), :305-447 (dense + dropout)
+// -> vendored FlashAttention-2 (mma.sync m16n8k16 + cp.async, third_party/flashattn/csrc/flash_attn/src/flash_fwd_kernel.h).
 //
 // One CTA per (batch, q-head, 128-row query tile); K and V tiles of 128 keys stream through separate 2-stage TMA rings.
 // The softmax is the bottleneck on this machine (one exp2 per score on 16 SFU lanes/clk/SM costs as many cycles as the
@@ -21,11 +22,13 @@
 // Q K^T and MN-major for P V, so V needs no transpose.
 // Outputs: O [b, sq, hq, d] bf16 and LSE [b, hq, sq] fp32 (natural log), the contract of the backward kernels.
 #include "common.cuh"
+#include "flash_common.cuh"
 #include "tc.cuh"
 
 namespace pdb {
 namespace fa {
 using namespace pdb::tc;
+using namespace pdb::fac;
 
 constexpr int BQ = 128;     // query rows per CTA
 constexpr int BKV = 128;    // keys per tile
@@ -40,15 +43,17 @@ template <int D> struct FwdSmem {
 };
 
 struct FwdParams {
-  int sq, sk, hq, hk;
+  SeqArgs seq;
+  int hq, hk;
   float scale_log2;     // softmax_scale * log2(e)
   float scale;          // softmax_scale
   int causal;
-  __nv_bfloat16* o;
+  uint16_t* o;          // bf16 or fp16
   float* lse;
+  Dropout drop;
 };
 
-template <int D>
+template <int D, bool kHalf, bool kDrop>
 __global__ void __launch_bounds__(kThreads, 1)
 flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                  const __grid_constant__ CUtensorMap tm_v, const FwdParams p) {
@@ -74,14 +79,31 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // heavy (late) causal tiles first so the tail of the grid is made of short CTAs
-  const int n_qt = p.sq / BQ;
+  const int n_qt = (int)gridDim.x;
   const int qt = p.causal ? (n_qt - 1 - (int)blockIdx.x) : (int)blockIdx.x;
   const int h = blockIdx.y, b = blockIdx.z;
   const int hk = h / (p.hq / p.hk);
-  const int q_row0 = b * p.sq + qt * BQ;                 // row in the [b*sq, hq*D] view
-  const int kv_row0 = b * p.sk;
-  const int diag = p.sk - p.sq;                          // key index aligned with query index 0
-  const int n_kv = p.causal ? min((qt * BQ + BQ + diag + BKV - 1) / BKV, p.sk / BKV) : p.sk / BKV;
+  const Seq sq_ = seq_of(p.seq, b);
+  if (qt * BQ >= sq_.q_len) return;                      // packed batch: this sequence is shorter than the longest
+  const int q_len = sq_.q_len, k_len = sq_.k_len;
+  const int q_row0 = sq_.q_start + qt * BQ;              // row in the [rows, hq*D] view
+  const int kv_row0 = sq_.k_start;
+  const int diag = k_len - q_len;                        // key index aligned with query index 0
+  const int n_kv_all = (k_len + BKV - 1) / BKV;
+  const int n_kv = p.causal ? min((qt * BQ + BQ + diag + BKV - 1) / BKV, n_kv_all) : n_kv_all;
+  const int64_t stat_row0 = sq_.stat0 + (int64_t)h * p.seq.stat_hs + qt * BQ;
+  if (n_kv <= 0) {
+    // no key is visible to any row of this tile (causal with fewer keys than queries, or an empty key sequence)
+    for (int i = threadIdx.x; i < BQ * (D / 8); i += kThreads) {
+      const int row = i / (D / 8), c8 = i % (D / 8);
+      if (qt * BQ + row < q_len)
+        *reinterpret_cast<uint4*>(p.o + ((int64_t)(q_row0 + row) * p.hq + h) * D + c8 * 8) = make_uint4(0, 0, 0, 0);
+    }
+    if (p.lse)
+      for (int row = threadIdx.x; row < BQ; row += kThreads)
+        if (qt * BQ + row < q_len) p.lse[stat_row0 + row] = -INFINITY;
+    return;
+  }
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tm_q);
@@ -139,8 +161,8 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc_s = make_idesc_bf16(BQ, BKV, 0, 0);     // Q (K-major) x K (K-major)
-      constexpr uint32_t idesc_o = make_idesc_bf16(BQ, D, 0, 1);       // P (K-major) x V (MN-major)
+      constexpr uint32_t idesc_s = make_idesc_16(kHalf, BQ, BKV, 0, 0);     // Q (K-major) x K (K-major)
+      constexpr uint32_t idesc_o = make_idesc_16(kHalf, BQ, D, 0, 1);       // P (K-major) x V (MN-major)
       auto issue_pv = [&](int t) {
         const int g = t & 1, ph = (t >> 1) & 1;
         mbar_wait(&v_full[g], ph);
@@ -207,8 +229,10 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&s_empty[g]);             // scores are in registers: the MMA warp may refill the buffer
-      if (p.causal && (j * BKV + BKV - 1 > qt * BQ + diag)) {   // tile crosses the diagonal for some row
-        const int lim = q_idx + diag - j * BKV;                 // keys with local index > lim are masked
+      const bool on_diag = p.causal && (j * BKV + BKV - 1 > qt * BQ + diag);   // tile crosses the diagonal for some row
+      if (on_diag || j * BKV + BKV > k_len) {                   // ... or holds the end of the key sequence
+        int lim = k_len - 1 - j * BKV;                          // keys with local index > lim are masked
+        if (on_diag) lim = min(lim, q_idx + diag - j * BKV);
 #pragma unroll
         for (int i = 0; i < BKV; ++i)
           if (i > lim) r[i] = 0xff800000u;                      // -inf
@@ -223,19 +247,19 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
       float alpha = 1.f;
       bool rescale = false;
       if (it == 0) {
-        m_used = (m_tile == -INFINITY) ? 0.f : m_tile;
+        m_used = m_tile;                                        // may be -inf: no visible key for this row so far
       } else {
         const bool grow = (m_tile - m_used) * p.scale_log2 > kRescaleThreshold;
         rescale = __any_sync(0xffffffffu, grow);
         if (rescale) {
           const float m_new = fmaxf(m_used, m_tile);
-          alpha = ex2_approx((m_used - m_new) * p.scale_log2);
+          alpha = (m_new == -INFINITY) ? 1.f : ex2_approx((m_used - m_new) * p.scale_log2);
           l_run *= alpha;
           m_used = m_new;
         }
       }
       // probabilities (packed bf16, kept in registers) + row sum; all of this overlaps the previous P V of the group
-      const float mb = m_used * p.scale_log2;
+      const float mb = (m_used == -INFINITY) ? 0.f : m_used * p.scale_log2;   // all scores are -inf then: exp2 -> 0
       float ls[4] = {0.f, 0.f, 0.f, 0.f};
       uint32_t pk[BKV / 2];
 #pragma unroll
@@ -249,9 +273,22 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
         x3 = ex2_approx(x3);
         fadd2(ls[0], ls[1], x0, x1);
         fadd2(ls[2], ls[3], x2, x3);
-        __nv_bfloat162 h0 = __floats2bfloat162_rn(x0, x1), h1 = __floats2bfloat162_rn(x2, x3);
-        pk[i >> 1] = *reinterpret_cast<uint32_t*>(&h0);
-        pk[(i >> 1) + 1] = *reinterpret_cast<uint32_t*>(&h1);
+        pk[i >> 1] = pack2<kHalf>(x0, x1);
+        pk[(i >> 1) + 1] = pack2<kHalf>(x2, x3);
+      }
+      if constexpr (kDrop) {
+        // the row sum above is of the undropped probabilities; the P that multiplies V loses its dropped entries
+        // (the 1 / keep factor is applied to the output once, at the end)
+        const uint32_t bh = (uint32_t)(b * p.hq + h);
+        const int sh = (q_idx & 1) * 16;
+#pragma unroll
+        for (int i = 0; i < BKV; i += 2) {
+          const uint32_t w = dropout_patch(p.drop, bh, (uint32_t)q_idx, (uint32_t)(j * BKV + i)) >> sh;
+          uint32_t m = 0;
+          if ((w & 0xffu) < p.drop.threshold) m |= 0x0000ffffu;
+          if (((w >> 8) & 0xffu) < p.drop.threshold) m |= 0xffff0000u;
+          pk[i >> 1] &= m;
+        }
       }
       if (it > 0) {
         // the previous P V of this group must be done before P is overwritten or O is touched
@@ -306,14 +343,15 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
     const float m_a = lds32f(stats + (row * 2) * 4), l_a = lds32f(stats + (row * 2 + 1) * 4);
     const float m_b = lds32f(stats + ((BQ + row) * 2) * 4), l_b = lds32f(stats + ((BQ + row) * 2 + 1) * 4);
     const bool has_b = n_kv > 1;
-    const float m_fin = fmaxf(m_a, m_b);                    // group A always has tile 0, so m_a is finite
-    const float f_a = ex2_approx((m_a - m_fin) * p.scale_log2);
-    const float f_b = has_b ? ex2_approx((m_b - m_fin) * p.scale_log2) : 0.f;
+    const float m_fin = fmaxf(m_a, m_b);                    // -inf only for a row that sees no key at all
+    const float f_a = (m_a == -INFINITY) ? 0.f : ex2_approx((m_a - m_fin) * p.scale_log2);
+    const float f_b = (m_b == -INFINITY) ? 0.f : ex2_approx((m_b - m_fin) * p.scale_log2);
     const float l_fin = l_a * f_a + l_b * f_b;
-    const float inv_l = l_fin > 0.f ? 1.f / l_fin : 0.f;
+    const float inv_l = (l_fin > 0.f ? 1.f / l_fin : 0.f) * (kDrop ? p.drop.inv_keep : 1.f);
     const float w_a = f_a * inv_l, w_b = f_b * inv_l;
+    const bool row_ok = q_idx < q_len;
     // group g writes columns [g * D/2, (g+1) * D/2) of the row
-    __nv_bfloat16* orow = p.o + ((int64_t)(b * p.sq + q_idx) * p.hq + h) * D + g * (D / 2);
+    uint16_t* orow = p.o + ((int64_t)(q_row0 + row) * p.hq + h) * D + g * (D / 2);
 #pragma unroll
     for (int c = 0; c < D / 64; ++c) {
       uint32_t oa[32], ob[32];
@@ -329,15 +367,15 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
           if (has_b) v[u] = fmaf(__uint_as_float(ob[i + u]), w_b, v[u]);
         }
         uint4 pk;
-        __nv_bfloat162 a0 = __floats2bfloat162_rn(v[0], v[1]), a1 = __floats2bfloat162_rn(v[2], v[3]);
-        __nv_bfloat162 a2 = __floats2bfloat162_rn(v[4], v[5]), a3 = __floats2bfloat162_rn(v[6], v[7]);
-        pk.x = *reinterpret_cast<uint32_t*>(&a0); pk.y = *reinterpret_cast<uint32_t*>(&a1);
-        pk.z = *reinterpret_cast<uint32_t*>(&a2); pk.w = *reinterpret_cast<uint32_t*>(&a3);
-        *reinterpret_cast<uint4*>(orow + c * 32 + i) = pk;
+        pk.x = pack2<kHalf>(v[0], v[1]);
+        pk.y = pack2<kHalf>(v[2], v[3]);
+        pk.z = pack2<kHalf>(v[4], v[5]);
+        pk.w = pack2<kHalf>(v[6], v[7]);
+        if (row_ok) *reinterpret_cast<uint4*>(orow + c * 32 + i) = pk;
       }
     }
-    if (g == 0 && p.lse)
-      p.lse[((int64_t)b * p.hq + h) * p.sq + q_idx] = m_fin * p.scale + __logf(fmaxf(l_fin, 1e-37f));
+    if (g == 0 && p.lse && row_ok)
+      p.lse[stat_row0 + row] = l_fin > 0.f ? m_fin * p.scale + __logf(l_fin) : -INFINITY;
   }
 
   tc_fence_before();
@@ -345,20 +383,49 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
   if (warp == 2) tmem_dealloc(tmem_base, kTmemCols);
 }
 
-template <int D>
-static int launch_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int b, int sq, int sk, int hq,
-                      int hk, float scale, int causal, cudaStream_t st) {
+template <int D, bool kHalf>
+static int launch_fwd(const void* q, const void* k, const void* v, void* o, float* lse, const SeqArgs& seq, int64_t rows_q,
+                      int64_t rows_k, int b, int hq, int hk, float scale, int causal, const Dropout& drop, cudaStream_t st) {
   using S = FwdSmem<D>;
   CUtensorMap tm_q, tm_k, tm_v;
-  if (get_tmap_2d(&tm_q, q, (uint64_t)b * sq, (uint64_t)hq * D, (uint64_t)hq * D * 2, BQ, 64, 2, true, "flash_attn q")) return -1;
-  if (get_tmap_2d(&tm_k, k, (uint64_t)b * sk, (uint64_t)hk * D, (uint64_t)hk * D * 2, BKV, 64, 2, true, "flash_attn k")) return -1;
-  if (get_tmap_2d(&tm_v, v, (uint64_t)b * sk, (uint64_t)hk * D, (uint64_t)hk * D * 2, BKV, 64, 2, true, "flash_attn v")) return -1;
-  auto kern = flash_fwd_kernel<D>;
-  PDB_ENSURE_SMEM(kern, S::kTotal);
-  FwdParams p{sq, sk, hq, hk, scale * 1.4426950408889634f, scale, causal, (__nv_bfloat16*)o, lse};
-  dim3 grid(sq / BQ, hq, b);
-  kern<<<grid, kThreads, S::kTotal, st>>>(tm_q, tm_k, tm_v, p);
+  if (get_tmap_2d(&tm_q, q, (uint64_t)rows_q, (uint64_t)hq * D, (uint64_t)hq * D * 2, BQ, 64, 2, true, "flash_attn q")) return -1;
+  if (get_tmap_2d(&tm_k, k, (uint64_t)rows_k, (uint64_t)hk * D, (uint64_t)hk * D * 2, BKV, 64, 2, true, "flash_attn k")) return -1;
+  if (get_tmap_2d(&tm_v, v, (uint64_t)rows_k, (uint64_t)hk * D, (uint64_t)hk * D * 2, BKV, 64, 2, true, "flash_attn v")) return -1;
+  FwdParams p{seq, hq, hk, scale * 1.4426950408889634f, scale, causal, (uint16_t*)o, lse, drop};
+  dim3 grid((seq.sq + BQ - 1) / BQ, hq, b);
+  if (drop.threshold) {
+    auto kern = flash_fwd_kernel<D, kHalf, true>;
+    PDB_ENSURE_SMEM(kern, S::kTotal);
+    kern<<<grid, kThreads, S::kTotal, st>>>(tm_q, tm_k, tm_v, p);
+  } else {
+    auto kern = flash_fwd_kernel<D, kHalf, false>;
+    PDB_ENSURE_SMEM(kern, S::kTotal);
+    kern<<<grid, kThreads, S::kTotal, st>>>(tm_q, tm_k, tm_v, p);
+  }
   return check_launch("flash_attn_fwd");
+}
+
+// keep probability -> 8-bit threshold + scale; the (seed, offset) pair of the caller's generator is folded into two words
+Dropout make_dropout(float p_drop, uint64_t seed, uint64_t offset) {
+  Dropout d{0, 0, 0, 1.f};
+  if (p_drop > 0.f) {
+    int thr = (int)((1.0 - (double)p_drop) * 256.0 + 0.5);
+    thr = thr < 1 ? 1 : (thr > 255 ? 255 : thr);
+    const uint64_t z = seed * 0x9e3779b97f4a7c15ull + offset * 0xbf58476d1ce4e5b9ull + 0x94d049bb133111ebull;
+    d.seed_lo = (uint32_t)z;
+    d.seed_hi = (uint32_t)(z >> 32);
+    d.threshold = (uint32_t)thr;
+    d.inv_keep = 256.f / (float)thr;
+  }
+  return d;
+}
+
+template <int D>
+static int launch_fwd_dt(bool half, const void* q, const void* k, const void* v, void* o, float* lse, const SeqArgs& seq,
+                         int64_t rows_q, int64_t rows_k, int b, int hq, int hk, float scale, int causal, const Dropout& drop,
+                         cudaStream_t st) {
+  return half ? launch_fwd<D, true>(q, k, v, o, lse, seq, rows_q, rows_k, b, hq, hk, scale, causal, drop, st)
+              : launch_fwd<D, false>(q, k, v, o, lse, seq, rows_q, rows_k, b, hq, hk, scale, causal, drop, st);
 }
 
 }  // namespace fa
@@ -366,15 +433,47 @@ static int launch_fwd(const void* q, const void* k, const void* v, void* o, floa
 
 using namespace pdb;
 
+static int fa_fwd_common(const void* q, const void* k, const void* v, void* o, float* lse, const fac::SeqArgs& seq,
+                         int64_t rows_q, int64_t rows_k, int64_t b, int64_t hq, int64_t hk, int64_t d, float scale, int causal,
+                         float p_drop, uint64_t seed, uint64_t offset, int dtype, void* stream) {
+  PDB_REQUIRE(dtype == PDB_DTYPE_BF16 || dtype == PDB_DTYPE_F16, "flash_attn_fwd: bfloat16 or float16 only");
+  PDB_REQUIRE(d == 64 || d == 128, "flash_attn_fwd: head_dim must be 64 or 128 (got %lld)", (long long)d);
+  PDB_REQUIRE(b > 0 && seq.sq > 0 && seq.sk > 0 && rows_q > 0 && rows_k > 0, "flash_attn_fwd: empty problem");
+  PDB_REQUIRE(hq % hk == 0, "flash_attn_fwd: q heads must be a multiple of kv heads");
+  PDB_REQUIRE(p_drop >= 0.f && p_drop < 1.f, "flash_attn_fwd: dropout must be in [0, 1)");
+  PDB_REQUIRE(rows_q < (1ll << 31) && rows_k < (1ll << 31), "flash_attn_fwd: more than 2^31 tokens");
+  const fac::Dropout drop = fa::make_dropout(p_drop, seed, offset);
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool half = dtype == PDB_DTYPE_F16;
+  if (d == 128) return fa::launch_fwd_dt<128>(half, q, k, v, o, lse, seq, rows_q, rows_k, (int)b, (int)hq, (int)hk, scale, causal, drop, st);
+  return fa::launch_fwd_dt<64>(half, q, k, v, o, lse, seq, rows_q, rows_k, (int)b, (int)hq, (int)hk, scale, causal, drop, st);
+}
+
+// Dense [b, s, h, d]; any sq / sk >= 1.  LSE [b, hq, sq].  Causal masks are aligned to the last key (query i sees keys
+// <= i + sk - sq); rows that see no key get output 0 and LSE -inf.
 PDB_EXPORT int pdb200_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int64_t b,
                                      int64_t sq, int64_t sk, int64_t hq, int64_t hk, int64_t d, float scale, int causal,
                                      int dtype, void* stream) {
-  PDB_REQUIRE(dtype == PDB_DTYPE_BF16, "flash_attn_fwd: bfloat16 only");
-  PDB_REQUIRE(d == 64 || d == 128, "flash_attn_fwd: head_dim must be 64 or 128 (got %lld)", (long long)d);
-  PDB_REQUIRE(sq % 128 == 0 && sk % 128 == 0 && sq > 0 && sk > 0, "flash_attn_fwd: sequence lengths must be multiples of 128");
-  PDB_REQUIRE(hq % hk == 0, "flash_attn_fwd: q heads must be a multiple of kv heads");
-  PDB_REQUIRE(!causal || sk >= sq, "flash_attn_fwd: causal needs sk >= sq");
-  cudaStream_t st = (cudaStream_t)stream;
-  if (d == 128) return fa::launch_fwd<128>(q, k, v, o, lse, (int)b, (int)sq, (int)sk, (int)hq, (int)hk, scale, causal, st);
-  return fa::launch_fwd<64>(q, k, v, o, lse, (int)b, (int)sq, (int)sk, (int)hq, (int)hk, scale, causal, st);
+  fac::SeqArgs seq{nullptr, nullptr, (int)sq, (int)sk, hq * sq, sq};
+  return fa_fwd_common(q, k, v, o, lse, seq, b * sq, b * sk, b, hq, hk, d, scale, causal, 0.f, 0, 0, dtype, stream);
+}
+
+PDB_EXPORT int pdb200_flash_attn_fwd_dropout(const void* q, const void* k, const void* v, void* o, float* lse, int64_t b,
+                                             int64_t sq, int64_t sk, int64_t hq, int64_t hk, int64_t d, float scale,
+                                             int causal, float p_drop, uint64_t seed, uint64_t offset, int dtype,
+                                             void* stream) {
+  fac::SeqArgs seq{nullptr, nullptr, (int)sq, (int)sk, hq * sq, sq};
+  return fa_fwd_common(q, k, v, o, lse, seq, b * sq, b * sk, b, hq, hk, d, scale, causal, p_drop, seed, offset, dtype, stream);
+}
+
+// Packed [total, h, d] with device-side int32 prefix sums cu_seqlens_q / cu_seqlens_k of b + 1 entries each; the grid
+// is sized from max_seqlen_q, nothing is read back to the host.  LSE [hq, total_q].
+PDB_EXPORT int pdb200_flash_attn_varlen_fwd(const void* q, const void* k, const void* v, void* o, float* lse,
+                                            const int* cu_seqlens_q, const int* cu_seqlens_k, int64_t b, int64_t total_q,
+                                            int64_t total_k, int64_t max_seqlen_q, int64_t max_seqlen_k, int64_t hq,
+                                            int64_t hk, int64_t d, float scale, int causal, float p_drop, uint64_t seed,
+                                            uint64_t offset, int dtype, void* stream) {
+  PDB_REQUIRE(cu_seqlens_q && cu_seqlens_k, "flash_attn_varlen_fwd: cu_seqlens are required");
+  fac::SeqArgs seq{cu_seqlens_q, cu_seqlens_k, (int)max_seqlen_q, (int)max_seqlen_k, 0, total_q};
+  return fa_fwd_common(q, k, v, o, lse, seq, total_q, total_k, b, hq, hk, d, scale, causal, p_drop, seed, offset, dtype, stream);
 }

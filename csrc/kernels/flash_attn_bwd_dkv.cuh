@@ -20,7 +20,7 @@ template <int D> struct DkvSmem {
   static constexpr int kTotal = 6 * kTile + kStats + 1024 + 256;
 };
 
-template <int D>
+template <int D, bool kHalf, bool kDrop>
 __global__ void __launch_bounds__(kThreads, 1)
 flash_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_do,
                      const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_v,
@@ -50,11 +50,26 @@ flash_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int jt = blockIdx.x, hk = blockIdx.y, b = blockIdx.z;
   const int G = p.hq / p.hk;
-  const int diag = p.sk - p.sq;
+  const Seq sq_ = seq_of(p.seq, b);
+  if (jt * 128 >= sq_.k_len) return;                                   // packed batch: shorter key sequence
+  const int q_len = sq_.q_len, k_len = sq_.k_len;
+  const int diag = k_len - q_len;
   const int i0 = p.causal ? max(0, jt * 128 - diag) / 128 : 0;        // first query tile that sees this key tile
-  const int n_qi = p.sq / 128 - i0;
+  const int n_qi = (q_len + 127) / 128 - i0;
   const int T = G * n_qi;
-  const int kv_row0 = b * p.sk + jt * 128;
+  const int kv_row0 = sq_.k_start + jt * 128;
+  const int q_base = sq_.q_start;
+  if (n_qi <= 0) {                                                     // no query sees these keys: dK = dV = 0
+    for (int i = threadIdx.x; i < 128 * (D / 8); i += kThreads) {
+      const int row = i / (D / 8), c8 = i % (D / 8);
+      if (jt * 128 + row < k_len) {
+        const int64_t at = ((int64_t)(kv_row0 + row) * p.hk + hk) * D + c8 * 8;
+        *reinterpret_cast<uint4*>(p.dk + at) = make_uint4(0, 0, 0, 0);
+        *reinterpret_cast<uint4*>(p.dv + at) = make_uint4(0, 0, 0, 0);
+      }
+    }
+    return;
+  }
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tm_q);
@@ -104,7 +119,7 @@ flash_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
           mbar_expect_tx(&q_full[st], S::kTile);
 #pragma unroll
           for (int kb = 0; kb < KB; ++kb)
-            tma_load_2d(sQ + st * S::kTile + kb * (128 * 128), &tm_q, &q_full[st], h * D + kb * 64, b * p.sq + i * 128);
+            tma_load_2d(sQ + st * S::kTile + kb * (128 * 128), &tm_q, &q_full[st], h * D + kb * 64, q_base + i * 128);
         }
       }
     } else if (warp == 3) {
@@ -116,13 +131,13 @@ flash_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
           mbar_expect_tx(&do_full[st], S::kTile);
 #pragma unroll
           for (int kb = 0; kb < KB; ++kb)
-            tma_load_2d(sDO + st * S::kTile + kb * (128 * 128), &tm_do, &do_full[st], h * D + kb * 64, b * p.sq + i * 128);
+            tma_load_2d(sDO + st * S::kTile + kb * (128 * 128), &tm_do, &do_full[st], h * D + kb * 64, q_base + i * 128);
         }
       }
     } else if (warp == 1) {
       if (lane == 0) {
-        constexpr uint32_t idesc_t = make_idesc_bf16(128, 128, 0, 0);    // [keys][d] x [q][d]^T
-        constexpr uint32_t idesc_acc = make_idesc_bf16(128, D, 0, 1);    // [keys][q] (TMEM) x [q][d] (MN-major smem)
+        constexpr uint32_t idesc_t = make_idesc_16(kHalf, 128, 128, 0, 0);    // [keys][d] x [q][d]^T
+        constexpr uint32_t idesc_acc = make_idesc_16(kHalf, 128, D, 0, 1);    // [keys][q] (TMEM) x [q][d] (MN-major smem)
         auto issue_s = [&](int t) {
           const int st = t & 1;
           mbar_wait(&q_full[st], (t >> 1) & 1);
@@ -187,14 +202,22 @@ flash_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
     float nxt = 0.f;
     auto fetch_stats = [&](int t) {
       if (t < T) {
-        const int64_t at = ((int64_t)b * p.hq + hk * G + t / n_qi) * p.sq + (i0 + t % n_qi) * 128 + (sidx & 127);
-        nxt = (sidx < 128) ? -p.lse[at] * kLog2e : -p.delta[at] * p.scale;
+        const int qi = (i0 + t % n_qi) * 128 + (sidx & 127);
+        const int64_t at = sq_.stat0 + (int64_t)(hk * G + t / n_qi) * p.seq.stat_hs + qi;
+        if (qi < q_len) {
+          nxt = (sidx < 128) ? -p.lse[at] * kLog2e : -p.delta[at] * p.scale;
+          if (nxt == INFINITY) nxt = -INFINITY;           // LSE = -inf (row saw no key): probability 0, not inf
+        } else {
+          nxt = (sidx < 128) ? -INFINITY : 0.f;           // queries past the end of the sequence: probability 0
+        }
       }
     };
     fetch_stats(0);
     for (int t = 0; t < T; ++t) {
       const int st = t & 1;
       const int i = i0 + t % n_qi;
+      const int h = hk * G + t / n_qi;
+      (void)h;
       sts32f(stats_u32 + (st * 256 + sidx) * 4, nxt);     // threads 0-127: -lse*log2e, threads 128-255: -delta*scale
       named_bar_sync(1, 256);
       fetch_stats(t + 1);
@@ -217,6 +240,24 @@ flash_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
         for (int c = 0; c < 64; ++c)
           if (c < cmin) rs[c] = 0xff800000u;
       }
+      uint32_t keep[2] = {0xffffffffu, 0xffffffffu};     // bit c: score (key row, query column c) survived dropout
+      if constexpr (kDrop) {
+        // dP^T of a dropped score is 0 here; its P^T entry (the dV operand) is zeroed after the exponentials
+        const uint32_t bh = (uint32_t)(b * p.hq + h);
+        const uint32_t key = (uint32_t)(jt * 128 + row);
+        const int sh = (int)(key & 1) * 8;
+        keep[0] = keep[1] = 0u;
+#pragma unroll
+        for (int c = 0; c < 64; c += 2) {
+          // patch (q >> 1, k >> 1): byte (q & 1) * 2 + (k & 1); q = even column c -> byte (k & 1), c + 1 -> byte 2 + (k & 1)
+          const uint32_t w = dropout_patch(p.drop, bh, (uint32_t)(i * 128 + half * 64 + c), key) >> sh;
+          if ((w & 0xffu) < p.drop.threshold) keep[c >> 5] |= 1u << (c & 31);
+          else rd[c] = 0u;
+          if (((w >> 16) & 0xffu) < p.drop.threshold) keep[c >> 5] |= 1u << ((c + 1) & 31);
+          else rd[c + 1] = 0u;
+        }
+      }
+      const float dp_scale = kDrop ? p.scale * p.drop.inv_keep : p.scale;
       const uint32_t lse2 = stats_u32 + (st * 256 + half * 64) * 4;
       const uint32_t dl = stats_u32 + (st * 256 + 128 + half * 64) * 4;
       uint32_t pp[32], pd[32];
@@ -227,18 +268,25 @@ flash_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
         float x0, x1, x2, x3, t0, t1, t2, t3;
         ffma2v(x0, x1, __uint_as_float(rs[c]), __uint_as_float(rs[c + 1]), p.scale_log2, p.scale_log2, l4.x, l4.y);
         ffma2v(x2, x3, __uint_as_float(rs[c + 2]), __uint_as_float(rs[c + 3]), p.scale_log2, p.scale_log2, l4.z, l4.w);
-        ffma2v(t0, t1, __uint_as_float(rd[c]), __uint_as_float(rd[c + 1]), p.scale, p.scale, d4.x, d4.y);
-        ffma2v(t2, t3, __uint_as_float(rd[c + 2]), __uint_as_float(rd[c + 3]), p.scale, p.scale, d4.z, d4.w);
+        ffma2v(t0, t1, __uint_as_float(rd[c]), __uint_as_float(rd[c + 1]), dp_scale, dp_scale, d4.x, d4.y);
+        ffma2v(t2, t3, __uint_as_float(rd[c + 2]), __uint_as_float(rd[c + 3]), dp_scale, dp_scale, d4.z, d4.w);
         x0 = ex2_approx(x0);
         x1 = ex2_approx(x1);
         x2 = ex2_approx(x2);
         x3 = ex2_approx(x3);
         fmul2(t0, t1, t0, t1, x0, x1);
         fmul2(t2, t3, t2, t3, x2, x3);
-        pp[c >> 1] = pack_bf16(x0, x1);
-        pp[(c >> 1) + 1] = pack_bf16(x2, x3);
-        pd[c >> 1] = pack_bf16(t0, t1);
-        pd[(c >> 1) + 1] = pack_bf16(t2, t3);
+        if constexpr (kDrop) {
+          const uint32_t kb = keep[c >> 5] >> (c & 31);
+          x0 = (kb & 1u) ? x0 : 0.f;
+          x1 = (kb & 2u) ? x1 : 0.f;
+          x2 = (kb & 4u) ? x2 : 0.f;
+          x3 = (kb & 8u) ? x3 : 0.f;
+        }
+        pp[c >> 1] = pack2<kHalf>(x0, x1);
+        pp[(c >> 1) + 1] = pack2<kHalf>(x2, x3);
+        pd[c >> 1] = pack2<kHalf>(t0, t1);
+        pd[(c >> 1) + 1] = pack2<kHalf>(t2, t3);
       }
       // over the dP^T columns this warp has just read (no other warp touches them): P^T then dS^T
       tmem_st_32x32(tmem_b + lane_off + half * 64, pp);
@@ -251,9 +299,11 @@ flash_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
     mbar_wait(all_done, 0);
     tc_fence_after();
     const int64_t orow = ((int64_t)(kv_row0 + row) * p.hk + hk) * D + half * (D / 2);
+    const bool row_ok = jt * 128 + row < k_len;
 #pragma unroll
     for (int which = 0; which < 2; ++which) {
-      __nv_bfloat16* out = (which == 0 ? p.dv : p.dk) + orow;
+      uint16_t* out = (which == 0 ? p.dv : p.dk) + orow;
+      const float osc = (kDrop && which == 0) ? p.drop.inv_keep : 1.f;       // dV = (mask o P / keep)^T dO
       const uint32_t src = (which == 0 ? tmem_dv : tmem_dk) + lane_off + half * (D / 2);
 #pragma unroll
       for (int c = 0; c < D / 64; ++c) {
@@ -263,11 +313,11 @@ flash_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
 #pragma unroll
         for (int i = 0; i < 32; i += 8) {
           uint4 v;
-          v.x = pack_bf16(__uint_as_float(r[i]), __uint_as_float(r[i + 1]));
-          v.y = pack_bf16(__uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]));
-          v.z = pack_bf16(__uint_as_float(r[i + 4]), __uint_as_float(r[i + 5]));
-          v.w = pack_bf16(__uint_as_float(r[i + 6]), __uint_as_float(r[i + 7]));
-          *reinterpret_cast<uint4*>(out + c * 32 + i) = v;
+          v.x = pack2<kHalf>(__uint_as_float(r[i]) * osc, __uint_as_float(r[i + 1]) * osc);
+          v.y = pack2<kHalf>(__uint_as_float(r[i + 2]) * osc, __uint_as_float(r[i + 3]) * osc);
+          v.z = pack2<kHalf>(__uint_as_float(r[i + 4]) * osc, __uint_as_float(r[i + 5]) * osc);
+          v.w = pack2<kHalf>(__uint_as_float(r[i + 6]) * osc, __uint_as_float(r[i + 7]) * osc);
+          if (row_ok) *reinterpret_cast<uint4*>(out + c * 32 + i) = v;
         }
       }
     }

@@ -224,6 +224,11 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N, int a_mn_ma
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
          ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
+// Same for fp16 (half = true) or bf16 operands.
+__host__ __device__ constexpr uint32_t make_idesc_16(bool half, int M, int N, int a_mn_major, int b_mn_major) {
+  return (1u << 4) | (half ? 0u : ((1u << 7) | (1u << 10))) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
+         ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
 
 // ---- host: tensor maps -------------------------------------------------------------------------------------
 // 2-D row-major bf16 tensor [rows][cols] (cols contiguous), box = [box_rows][box_cols], 128-B swizzle.

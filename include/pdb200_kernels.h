@@ -161,14 +161,24 @@ PDB_API int pdb200_nvl_ce_combine(const uint64_t* peer_ptrs, int nranks, int ran
 /* K7 vocab-parallel embedding forward as a gather from the owning rank's table shard (replaces masked lookup + all-reduce). */
 PDB_API int pdb200_nvl_vocab_embed(const uint64_t* peer_ptrs, int nranks, int rank, int64_t table_off, const int64_t* ids, void* out, int64_t n_tokens, int hidden, int64_t vocab_per_rank, int dtype, int64_t pad_off, int64_t epoch, void* stream);
 
-/* K16 flash-attention forward on tcgen05 (reference: phi/kernels/gpu/flash_attn_kernel.cu:305-447 -> FlashAttention-2
- * sm80 kernels).  q [b,sq,hq,d], k/v [b,sk,hk,d] bf16, d in {64,128}, sq/sk multiples of 128; o like q; lse [b,hq,sq]
- * fp32 (natural log of the softmax denominator, scaled scores). */
+/* K16 flash-attention forward on tcgen05 (reference: phi/kernels/gpu/flash_attn_kernel.cu:36-170, 305-447 ->
+ * FlashAttention-2 sm80 kernels).  bf16 or fp16, d in {64,128}, GQA, causal aligned to the last key.
+ * Dense: q [b,sq,hq,d], k/v [b,sk,hk,d], any sq/sk >= 1; o like q; lse [b,hq,sq] fp32 (natural log of the softmax
+ * denominator of the scaled scores; -inf for a row that sees no key, whose output is 0).
+ * Packed (varlen): q [total_q,hq,d], k/v [total_k,hk,d], cu_seqlens_* int32 [b+1] ON THE DEVICE (nothing is read
+ * back), lse [hq,total_q].
+ * Dropout: score (b*hq+h, q, k) is kept iff an 8-bit hash of (seed, offset, b*hq+h, q, k) is below round((1-p)*256);
+ * the backward regenerates the same mask from the same (p_drop, seed, offset). */
 PDB_API int pdb200_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int64_t b, int64_t sq, int64_t sk, int64_t hq, int64_t hk, int64_t d, float scale, int causal, int dtype, void* stream);
+PDB_API int pdb200_flash_attn_fwd_dropout(const void* q, const void* k, const void* v, void* o, float* lse, int64_t b, int64_t sq, int64_t sk, int64_t hq, int64_t hk, int64_t d, float scale, int causal, float p_drop, uint64_t seed, uint64_t offset, int dtype, void* stream);
+PDB_API int pdb200_flash_attn_varlen_fwd(const void* q, const void* k, const void* v, void* o, float* lse, const int* cu_seqlens_q, const int* cu_seqlens_k, int64_t b, int64_t total_q, int64_t total_k, int64_t max_seqlen_q, int64_t max_seqlen_k, int64_t hq, int64_t hk, int64_t d, float scale, int causal, float p_drop, uint64_t seed, uint64_t offset, int dtype, void* stream);
 /* K17 backward: Delta pre-pass + dK/dV kernel (transposed products, GQA heads looped in-CTA) + dQ kernel; deterministic,
- * no atomics.  workspace: pdb200_flash_attn_bwd_workspace_bytes() bytes of device memory (16-byte aligned). */
+ * no atomics.  workspace: pdb200_flash_attn_bwd_workspace_bytes() bytes of device memory (16-byte aligned); for the
+ * packed layout call it with b = 1, sq = total_q. */
 PDB_API int64_t pdb200_flash_attn_bwd_workspace_bytes(int64_t b, int64_t sq, int64_t sk, int64_t hq, int64_t hk, int64_t d);
 PDB_API int pdb200_flash_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* d_o, const float* lse, void* dq, void* dk, void* dv, void* workspace, int64_t workspace_bytes, int64_t b, int64_t sq, int64_t sk, int64_t hq, int64_t hk, int64_t d, float scale, int causal, int dtype, void* stream);
+PDB_API int pdb200_flash_attn_bwd_dropout(const void* q, const void* k, const void* v, const void* o, const void* d_o, const float* lse, void* dq, void* dk, void* dv, void* workspace, int64_t workspace_bytes, int64_t b, int64_t sq, int64_t sk, int64_t hq, int64_t hk, int64_t d, float scale, int causal, float p_drop, uint64_t seed, uint64_t offset, int dtype, void* stream);
+PDB_API int pdb200_flash_attn_varlen_bwd(const void* q, const void* k, const void* v, const void* o, const void* d_o, const float* lse, void* dq, void* dk, void* dv, void* workspace, int64_t workspace_bytes, const int* cu_seqlens_q, const int* cu_seqlens_k, int64_t b, int64_t total_q, int64_t total_k, int64_t max_seqlen_q, int64_t max_seqlen_k, int64_t hq, int64_t hk, int64_t d, float scale, int causal, float p_drop, uint64_t seed, uint64_t offset, int dtype, void* stream);
 
 /* K9 / K10 MoE dispatch / combine over NVLink symmetric memory with device-side routing (csrc/kernels/moe_nvl.cu). */
 PDB_API int pdb200_moe_dispatch(const uint64_t* peer_ptrs, int nranks, int rank, int64_t counts_off, int64_t slab_off, int64_t slab_rows, const void* src, const int64_t* pos, int div, const int64_t* lec, int n_expert_local, int64_t n_slots, int row_bytes, int32_t* route_rank, int32_t* route_row, int64_t* recv_counts, int32_t* overflow, int64_t pad_off, int64_t epoch, void* stream);

@@ -112,7 +112,7 @@ _LAUNCHES = {
     "pdb200_unscale_check_multi": 1, "pdb200_ce_fwd": 1, "pdb200_ce_combine": 1, "pdb200_ce_bwd": 1,
     "pdb200_number_count": 1, "pdb200_assign_pos": 1, "pdb200_limit_by_capacity": 1,
     "pdb200_prune_gate_by_capacity": 2, "pdb200_random_routing": 1, "pdb200_topk_softmax": 1,
-    "pdb200_gemm_bf16": 1, "pdb200_gemm_bf16_pair": 1, "pdb200_gemm_bf16_macro": 1, "pdb200_gemm_bf16_gated": 1, "pdb200_gemm_bf16_counted": 1, "pdb200_nvl_wait_counter": 1, "pdb200_nvl_wait_flags": 1, "pdb200_nvl_signal": 1, "pdb200_check_numerics": 2, "pdb200_gemm_grouped": 1, "pdb200_gemm_grouped_wgrad": 1, "pdb200_flash_attn_fwd": 1, "pdb200_flash_attn_bwd": 3,
+    "pdb200_gemm_bf16": 1, "pdb200_gemm_bf16_pair": 1, "pdb200_gemm_bf16_macro": 1, "pdb200_gemm_bf16_gated": 1, "pdb200_gemm_bf16_counted": 1, "pdb200_nvl_wait_counter": 1, "pdb200_nvl_wait_flags": 1, "pdb200_nvl_signal": 1, "pdb200_check_numerics": 2, "pdb200_gemm_grouped": 1, "pdb200_gemm_grouped_wgrad": 1, "pdb200_flash_attn_fwd": 1, "pdb200_flash_attn_bwd": 3, "pdb200_flash_attn_fwd_dropout": 1, "pdb200_flash_attn_bwd_dropout": 3, "pdb200_flash_attn_varlen_fwd": 1, "pdb200_flash_attn_varlen_bwd": 3,
     "pdb200_nvl_barrier": 1, "pdb200_nvl_allreduce": 3, "pdb200_nvl_rs_adamw_ag": 3, "pdb200_nvl_reduce_scatter": 3,
     "pdb200_nvl_ce_combine": 3, "pdb200_nvl_vocab_embed": 3, "pdb200_nvl_allgather": 3, "pdb200_nvl_allgather_multi": 1, "pdb200_nvl_reduce_scatter_multi": 1, "pdb200_reduce_slots_multi": 1, "pdb200_reduce_slots_multi2": 1, "pdb200_nvl_signal_one": 1, "pdb200_nvl_allgather_from": 3, "pdb200_nvl_rs_sum_bf16": 3, "pdb200_moe_dispatch": 5, "pdb200_moe_pull": 3,
 }

@@ -23,21 +23,22 @@ def flash_attention(query, key, value, dropout=0.0, causal=False, return_softmax
             s = s.masked_fill(~m, float("-inf"))
         p = torch.softmax(s, -1)
         return torch.einsum("bhqk,bkhd->bqhd", p, value.float()).to(query.dtype), p.to(query.dtype)
-    return ops.flash_attention(query, key, value, dropout, causal, training=training), None
+    return ops.flash_attention(query, key, value, dropout, causal, training=training, fixed_seed_offset=fixed_seed_offset), None
 
 
 def flash_attn_qkvpacked(qkv, dropout=0.0, causal=False, return_softmax=False, *, fixed_seed_offset=None, rng_name="",
                          training=True, name=None):
     # qkv: [b, s, 2 + hq/hk, hk, d] (last two groups are k and v)
     q = qkv[:, :, :-2].reshape(qkv.shape[0], qkv.shape[1], -1, qkv.shape[-1])
-    return flash_attention(q, qkv[:, :, -2], qkv[:, :, -1], dropout, causal, return_softmax, training=training)
+    return flash_attention(q, qkv[:, :, -2], qkv[:, :, -1], dropout, causal, return_softmax, fixed_seed_offset=fixed_seed_offset,
+                           training=training)
 
 
 def flash_attn_unpadded(query, key, value, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, scale, dropout=0.0,
                         causal=False, return_softmax=False, fixed_seed_offset=None, rng_name="", training=True, name=None):
     from ... import ops
     return ops.flash_attn_varlen(query, key, value, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, scale,
-                                 dropout, causal, training), None
+                                 dropout, causal, training, fixed_seed_offset), None
 
 
 def flash_attn_varlen_qkvpacked(qkv, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, scale, dropout=0.0,
@@ -45,7 +46,7 @@ def flash_attn_varlen_qkvpacked(qkv, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, m
                                 training=True, name=None):
     q = qkv[:, :-2].reshape(qkv.shape[0], -1, qkv.shape[-1])
     return flash_attn_unpadded(q, qkv[:, -2], qkv[:, -1], cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, scale,
-                               dropout, causal, training=training)
+                               dropout, causal, fixed_seed_offset=fixed_seed_offset, training=training)
 
 
 def scaled_dot_product_attention(query, key, value, attn_mask=None, dropout_p=0.0, is_causal=False, training=True,
