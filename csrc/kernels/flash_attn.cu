@@ -4,31 +4,56 @@
 // Replaces in the reference: paddle/phi/kernels/gpu/flash_attn_kernel.cu:36-170 (unpadded), :305-447 (dense + dropout)
 // -> vendored FlashAttention-2 (mma.sync m16n8k16 + cp.async, third_party/flashattn/csrc/flash_attn/src/flash_fwd_kernel.h).
 //
-// One CTA per (batch, q-head, 128-row query tile); K and V tiles of 128 keys stream through separate 2-stage TMA rings.
-// The softmax is the bottleneck on this machine (one exp2 per score on 16 SFU lanes/clk/SM costs as many cycles as the
-// two 128x128x128 MMAs of a tile), so the CTA runs TWO independent softmax pipelines:
+// One CTA per (batch, q-head, 128-row query tile); K tiles of 128 keys stream through a 3-stage TMA ring, V tiles
+// through a 2-stage ring.  What shapes the kernel (clock-stamp timelines in profiles/flash_attn_timeline.md):
+//  * the softmax of a tile costs more than its two MMAs (one exp2 per score on 16 SFU lanes/clk/SM alone is as long),
+//    so the softmax warps must never wait for scores.  There are THREE score buffers in TMEM: Q K^T runs up to three
+//    key tiles ahead of the softmax, and all eight softmax warps work on the same tile, half a row per thread, then
+//    move straight to the next one.
+//  * shared-memory bandwidth.  A 128x128x16 tcgen05.mma with both operands in shared memory reads 8 KB per 64 clocks,
+//    which is the whole 128 B/clk of the SM.  P therefore never goes through shared memory: each thread writes its
+//    half row of P with tcgen05.st over the score columns it has just read, and P V takes its A operand from TMEM.
 //   warp 0      TMA producer for Q and the K ring            warp 3   TMA producer for the V ring
-//   warp 1      MMA issuer: S_j = Q K_j^T into TMEM buffer (j & 1); O_(j&1) += P_j V_j once P_j is in shared memory
-//   warp 2      TMEM allocator (S_A | S_B | O_A | O_B = 512 columns)
-//   warps 4-7   softmax group A: even key tiles            warps 8-11   softmax group B: odd key tiles
-// Each group keeps its own running (max, sum) and its own output accumulator IN TMEM (the MMA accumulates across the
-// group's tiles), so the groups never wait for each other; the two partial results are merged once at the end
-// (the split-KV combination, inside the CTA).  A group thread owns one query row: a single tcgen05.ld pass brings the
-// 128 scores into registers (the S buffer is handed back to the MMA warp immediately), then max / exp2 / row sum /
-// bf16 pack, and P is written to shared memory in the UMMA K-major swizzled layout.  The accumulator is rescaled
-// lazily: only when a row's maximum grew by more than 2^8 since the last rescale does the warp read-modify-write its
-// O rows in TMEM (exact: P and the row sum use the same stale maximum until then).
+//   warp 1      MMA issuer: S_j = Q K_j^T into score buffer j % 3; O += P_j V_j once P_j is in TMEM
+//   warp 2      TMEM allocator (S_0 | S_1 | S_2 | O = 512 columns)
+//   warps 4-11  softmax: lane quarter = warp % 4, column half = (warp - 4) / 4; a thread owns 64 keys of one query row
+// The two threads of a row must use the same reference maximum.  They do not exchange it per tile: the probabilities
+// are computed against a stale shared maximum, which is exact as long as no score exceeds it by more than 2^8, and one
+// barrier-with-OR over the 256 softmax threads per tile tells whether any row outgrew that bound.  Only then (and on the
+// first tile) are the half-row maxima exchanged through shared memory, the accumulator rescaled in TMEM and the row
+// sums corrected.  The half-row sums are combined once, at the end.
+// The tensor pipe executes in issue order, so S_(j+3) (issued behind P_j V_j) cannot overwrite P_j before it is read.
 // K_j and V_j share one TMA box geometry ([keys][64 d-columns]); the descriptor reads the same bytes K-major for
 // Q K^T and MN-major for P V, so V needs no transpose.
-// Outputs: O [b, sq, hq, d] bf16 and LSE [b, hq, sq] fp32 (natural log), the contract of the backward kernels.
+// Outputs: O [rows, hq, d] and LSE fp32 (natural log), the contract of the backward kernels.
 #include "common.cuh"
 #include "flash_common.cuh"
 #include "tc.cuh"
+
+#ifndef PDB_FA_POLY
+#define PDB_FA_POLY 2      // share of the exponentials computed on the FMA pipe: 0 none, 1: 1/8, 2: 1/4, 3: 1/2
+#endif
+#ifndef PDB_FA_DIAG
+#define PDB_FA_DIAG 0      // 1: timing experiment only, no exponentials (wrong results)
+#endif
 
 namespace pdb {
 namespace fa {
 using namespace pdb::tc;
 using namespace pdb::fac;
+
+// -DPDB_FA_TRACE: CTA 0 stamps clock64() at the hand-off points of its MMA thread (role 0) and of lane 0 of the first
+// warp of each softmax group (roles 1, 2) into a caller-provided buffer [3][4096] (pdb200_flash_attn_set_trace);
+// bench/attn_trace.py turns the stamps into a per-tile timeline.  Not compiled into the product library.
+#ifdef PDB_FA_TRACE
+__device__ unsigned long long* g_trace = nullptr;
+#define PDB_TR(role, tag)                                                                              \
+  do {                                                                                                 \
+    if (blockIdx.x == 1 && blockIdx.y == 0 && blockIdx.z == 0 && g_trace && tr_n < 4096) g_trace[(role) * 4096 + tr_n++] = ((unsigned long long)(tag) << 56) | (clock64() & 0xffffffffffffffull); \
+  } while (0)
+#else
+#define PDB_TR(role, tag) do { } while (0)
+#endif
 
 constexpr int BQ = 128;     // query rows per CTA
 constexpr int BKV = 128;    // keys per tile
@@ -38,8 +63,10 @@ constexpr float kRescaleThreshold = 8.f;   // log2 units
 template <int D> struct FwdSmem {
   static constexpr int kQBytes = BQ * D * 2;
   static constexpr int kKVBytes = BKV * D * 2;            // one of K or V
-  static constexpr int kPBytes = BQ * BKV * 2;
-  static constexpr int kTotal = kQBytes + 4 * kKVBytes + 2 * kPBytes + 1024 + 256;
+  static constexpr int kKStages = 3;                     // K_j is needed two tiles before V_j
+  static constexpr int kVStages = 2;
+  static constexpr int kStatsBytes = 2 * BQ * 4;          // [column half][row]: half-row maxima / sums in flight
+  static constexpr int kTotal = kQBytes + (kKStages + kVStages) * kKVBytes + kStatsBytes + 1024 + 256;
 };
 
 struct FwdParams {
@@ -62,20 +89,19 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sQ = smem;
-  uint8_t* sK = sQ + S::kQBytes;             // [2] stages
-  uint8_t* sV = sK + 2 * S::kKVBytes;        // [2] stages
-  uint8_t* sP = sV + 2 * S::kKVBytes;        // [2] one per softmax group
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * S::kPBytes);
+  uint8_t* sK = sQ + S::kQBytes;             // [3] stages
+  uint8_t* sV = sK + S::kKStages * S::kKVBytes;   // [2] stages
+  uint8_t* sStats = sV + S::kVStages * S::kKVBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sStats + S::kStatsBytes);
   uint64_t* q_full = bars;
-  uint64_t* k_full = bars + 1;               // [2]
-  uint64_t* k_empty = bars + 3;              // [2]
-  uint64_t* v_full = bars + 5;               // [2]
-  uint64_t* v_empty = bars + 7;              // [2]
-  uint64_t* s_full = bars + 9;               // [2]
-  uint64_t* s_empty = bars + 11;             // [2]
-  uint64_t* p_ready = bars + 13;             // [2]
-  uint64_t* o_full = bars + 15;              // [2]
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 17);
+  uint64_t* k_full = bars + 1;               // [3]
+  uint64_t* k_empty = bars + 4;              // [3]
+  uint64_t* v_full = bars + 7;               // [2]
+  uint64_t* v_empty = bars + 9;              // [2]
+  uint64_t* s_full = bars + 11;              // [3]
+  uint64_t* p_ready = bars + 14;             // [3]
+  uint64_t* o_full = bars + 17;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 18);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // heavy (late) causal tiles first so the tail of the grid is made of short CTAs
@@ -112,36 +138,39 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
   }
   if (warp == 1 && lane == 0) {
     mbar_init(q_full, 1);
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < S::kKStages; ++i) {
       mbar_init(&k_full[i], 1);
       mbar_init(&k_empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
       mbar_init(&v_full[i], 1);
       mbar_init(&v_empty[i], 1);
-      mbar_init(&s_full[i], 1);
-      mbar_init(&s_empty[i], 4);
-      mbar_init(&p_ready[i], 4);
-      mbar_init(&o_full[i], 1);
     }
+    for (int i = 0; i < 3; ++i) {
+      mbar_init(&s_full[i], 1);
+      mbar_init(&p_ready[i], 8);
+    }
+    mbar_init(o_full, 1);
     fence_barrier_init();
   }
-  constexpr int kTmemCols = 512;             // S_A | S_B | O_A | O_B
+  constexpr int kTmemCols = 512;             // S_0 | S_1 | S_2 | O
   if (warp == 2) tmem_alloc(tmem_ptr_smem, kTmemCols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
-  const uint32_t tmem_o = tmem_base + 2 * BKV;           // group g: tmem_o + g * D
+  const uint32_t tmem_o = tmem_base + 3 * BKV;
 
   if (warp < 4) {
   reg_dealloc<56>();
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_expect_tx(q_full, S::kQBytes);
 #pragma unroll
       for (int kb = 0; kb < KB; ++kb) tma_load_2d(sQ + kb * (BQ * 128), &tm_q, q_full, h * D + kb * 64, q_row0);
       for (int j = 0; j < n_kv; ++j) {
-        const int st = j & 1;
-        mbar_wait(&k_empty[st], ((j >> 1) & 1) ^ 1);
+        const int st = j % S::kKStages;
+        mbar_wait(&k_empty[st], ((j / S::kKStages) & 1) ^ 1);
         mbar_expect_tx(&k_full[st], S::kKVBytes);
 #pragma unroll
         for (int kb = 0; kb < KB; ++kb)
@@ -149,7 +178,7 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
       }
     }
   } else if (warp == 3) {
-    if (lane == 0) {
+    if (elect_one()) {
       for (int j = 0; j < n_kv; ++j) {
         const int st = j & 1;
         mbar_wait(&v_empty[st], ((j >> 1) & 1) ^ 1);
@@ -160,117 +189,145 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (elect_one()) {   // elect.sync, not a lane test: ptxas then knows one lane runs this and issues UTCHMMA / UTCBAR from uniform registers
+      [[maybe_unused]] int tr_n = 0;
       constexpr uint32_t idesc_s = make_idesc_16(kHalf, BQ, BKV, 0, 0);     // Q (K-major) x K (K-major)
       constexpr uint32_t idesc_o = make_idesc_16(kHalf, BQ, D, 0, 1);       // P (K-major) x V (MN-major)
-      auto issue_pv = [&](int t) {
-        const int g = t & 1, ph = (t >> 1) & 1;
-        mbar_wait(&v_full[g], ph);
-        mbar_wait(&p_ready[g], ph);
+      auto issue_pv = [&](int j) {
+        const int sb = j % 3, vst = j & 1;
+        PDB_TR(0, 8);
+        mbar_wait(&v_full[vst], (j >> 1) & 1);
+        PDB_TR(0, 9);
+        mbar_wait(&p_ready[sb], (j / 3) & 1);
         tc_fence_after();
-        const uint32_t sv = smem_u32(sV + g * S::kKVBytes);
-        const uint32_t sp = smem_u32(sP + g * S::kPBytes);
+        PDB_TR(0, 10);
+        const uint32_t sv = smem_u32(sV + vst * S::kKVBytes);
+        // P_j: 16 keys = 8 packed columns; keys 0-63 sit at columns 0-31 of S_sb, keys 64-127 at columns 64-95 (each
+        // softmax thread writes over the start of the 64 score columns it has read itself)
 #pragma unroll
         for (int k = 0; k < BKV / 16; ++k) {
-          const uint64_t da = make_smem_desc(sp + (k >> 2) * (BQ * 128) + (k & 3) * 32, 16, 1024);
           const uint64_t db = make_smem_desc(sv + k * 2048, BKV * 128, 1024);
-          umma_f16(tmem_o + g * D, da, db, idesc_o, (k != 0 || t >= 2) ? 1u : 0u);
+          umma_f16_ts(tmem_o, tmem_base + sb * BKV + (k >> 2) * 64 + (k & 3) * 8, db, idesc_o, (k != 0 || j > 0) ? 1u : 0u);
         }
-        umma_commit(&o_full[g]);
-        umma_commit(&v_empty[g]);
+        umma_commit(o_full);
+        umma_commit(&v_empty[vst]);
+        PDB_TR(0, 11);
       };
       auto issue_qk = [&](int j) {
-        const int g = j & 1, ph = (j >> 1) & 1;
-        mbar_wait(&k_full[g], ph);
-        mbar_wait(&s_empty[g], ph ^ 1);
+        // S_(j%3) is free: every thread read S_(j-3) before it produced P_(j-3), and P_(j-3) V was issued ahead of this
+        const int sb = j % 3, kst = j % S::kKStages;
+        mbar_wait(&k_full[kst], (j / S::kKStages) & 1);
         tc_fence_after();
-        const uint32_t sq_ = smem_u32(sQ);
-        const uint32_t sk_ = smem_u32(sK + g * S::kKVBytes);
+        PDB_TR(0, 12);
+        const uint32_t sq_a = smem_u32(sQ);
+        const uint32_t sk_ = smem_u32(sK + kst * S::kKVBytes);
 #pragma unroll
         for (int k = 0; k < D / 16; ++k) {
-          const uint64_t da = make_smem_desc(sq_ + (k >> 2) * (BQ * 128) + (k & 3) * 32, 16, 1024);
+          const uint64_t da = make_smem_desc(sq_a + (k >> 2) * (BQ * 128) + (k & 3) * 32, 16, 1024);
           const uint64_t db = make_smem_desc(sk_ + (k >> 2) * (BKV * 128) + (k & 3) * 32, 16, 1024);
-          umma_f16(tmem_base + g * BKV, da, db, idesc_s, k != 0 ? 1u : 0u);
+          umma_f16(tmem_base + sb * BKV, da, db, idesc_s, k != 0 ? 1u : 0u);
         }
-        umma_commit(&s_full[g]);
-        umma_commit(&k_empty[g]);
+        umma_commit(&s_full[sb]);
+        umma_commit(&k_empty[kst]);
+        PDB_TR(0, 13);
       };
       mbar_wait(q_full, 0);
-      // scores run two tiles ahead of the P V products: a group finds its next S ready when it finishes a tile
       issue_qk(0);
       if (n_kv > 1) issue_qk(1);
-      for (int j = 2; j < n_kv; ++j) {
-        issue_qk(j);
-        issue_pv(j - 2);
+      if (n_kv > 2) issue_qk(2);
+      for (int j = 0; j < n_kv; ++j) {
+        issue_pv(j);
+        if (j + 3 < n_kv) issue_qk(j + 3);
       }
-      if (n_kv > 1) issue_pv(n_kv - 2);
-      issue_pv(n_kv - 1);
     }
   }
   } else {
     reg_alloc<216>();
-    const int g = (warp - 4) >> 2;                          // softmax group: 0 = even tiles, 1 = odd tiles
+    const int half = (warp - 4) >> 2;                       // column half of the tile this thread works on
     const int q = warp & 3;                                 // TMEM lane quarter this warp may touch
     const int row = q * 32 + lane;                          // row inside the tile
     const int q_idx = qt * BQ + row;                        // query position in the sequence
     const uint32_t lane_off = (uint32_t)(q * 32) << 16;
-    const uint32_t ts = tmem_base + g * BKV + lane_off;
-    const uint32_t to = tmem_o + g * D + lane_off;
-    const uint32_t sPg_u32 = smem_u32(sP + g * S::kPBytes);
-    float m_used = -INFINITY, l_run = 0.f;
-    int it = 0;
-    for (int j = g; j < n_kv; j += 2, ++it) {
-      mbar_wait(&s_full[g], it & 1);
+    const uint32_t to = tmem_o + lane_off + half * (D / 2); // this thread's half of the accumulator row
+    const uint32_t xch = smem_u32(sStats);                  // [half][row] floats
+    float m_used = -INFINITY, l_part = 0.f;
+    [[maybe_unused]] int tr_n = 0;
+    [[maybe_unused]] const bool tr_on = (q == 0 && lane == 0);
+    for (int j = 0; j < n_kv; ++j) {
+      const int sb = j % 3;
+      const uint32_t ts = tmem_base + sb * BKV + half * 64 + lane_off;
+      if (tr_on) PDB_TR(1 + half, 0);
+      mbar_wait(&s_full[sb], (j / 3) & 1);
       tc_fence_after();
-      uint32_t r[BKV];
-#pragma unroll
-      for (int c = 0; c < BKV / 32; ++c) tmem_ld_32x32(ts + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&r[c * 32]));
+      if (tr_on) PDB_TR(1 + half, 1);
+      uint32_t r[64];
+      tmem_ld_32x32(ts, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
+      tmem_ld_32x32(ts + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
       tmem_ld_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&s_empty[g]);             // scores are in registers: the MMA warp may refill the buffer
+      if (tr_on) PDB_TR(1 + half, 2);
+      const int key0 = j * BKV + half * 64;                     // first key of this thread's 64
       const bool on_diag = p.causal && (j * BKV + BKV - 1 > qt * BQ + diag);   // tile crosses the diagonal for some row
       if (on_diag || j * BKV + BKV > k_len) {                   // ... or holds the end of the key sequence
-        int lim = k_len - 1 - j * BKV;                          // keys with local index > lim are masked
-        if (on_diag) lim = min(lim, q_idx + diag - j * BKV);
+        int lim = k_len - 1 - key0;                             // keys with local index > lim are masked
+        if (on_diag) lim = min(lim, q_idx + diag - key0);
 #pragma unroll
-        for (int i = 0; i < BKV; ++i)
+        for (int i = 0; i < 64; ++i)
           if (i > lim) r[i] = 0xff800000u;                      // -inf
       }
       float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-      for (int i = 0; i < BKV; i += 4) {
+      for (int i = 0; i < 64; i += 4) {
 #pragma unroll
         for (int u = 0; u < 4; ++u) mx[u] = fmaxf(mx[u], __uint_as_float(r[i + u]));
       }
-      const float m_tile = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
-      float alpha = 1.f;
-      bool rescale = false;
-      if (it == 0) {
-        m_used = m_tile;                                        // may be -inf: no visible key for this row so far
-      } else {
-        const bool grow = (m_tile - m_used) * p.scale_log2 > kRescaleThreshold;
-        rescale = __any_sync(0xffffffffu, grow);
-        if (rescale) {
-          const float m_new = fmaxf(m_used, m_tile);
-          alpha = (m_new == -INFINITY) ? 1.f : ex2_approx((m_used - m_new) * p.scale_log2);
-          l_run *= alpha;
-          m_used = m_new;
+      const float m_half = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+      // does any row of the tile exceed the shared stale maximum by more than the bound?  (-inf - -inf = NaN: false)
+      const bool grow = (m_half - m_used) * p.scale_log2 > kRescaleThreshold;
+      const bool resync = (j == 0) || bar_red_or(1, 256, grow);
+      if (resync) {
+        // rare after the first tile: agree on the row maximum, rescale what has been accumulated under the old one
+        sts32f(xch + (half * BQ + row) * 4, m_half);
+        named_bar_sync(2, 256);
+        const float m_new = fmaxf(m_used, fmaxf(lds32f(xch + row * 4), lds32f(xch + (BQ + row) * 4)));
+        named_bar_sync(2, 256);                                 // the exchange words may be written again
+        if (j > 0) {
+          const float alpha = (m_new == -INFINITY) ? 1.f : ex2_approx((m_used - m_new) * p.scale_log2);
+          l_part *= alpha;
+          mbar_wait(o_full, (j - 1) & 1);                       // P_(j-1) V has been accumulated
+          tc_fence_after();
+#pragma unroll
+          for (int c = 0; c < D / 64; ++c) {
+            uint32_t o[32];
+            tmem_ld_32x32(to + c * 32, o);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            tmem_st_32x32(to + c * 32, o);
+          }
+          tmem_st_wait();
         }
+        m_used = m_new;
       }
-      // probabilities (packed bf16, kept in registers) + row sum; all of this overlaps the previous P V of the group
+      // probabilities (packed, kept in registers) + partial row sum
       const float mb = (m_used == -INFINITY) ? 0.f : m_used * p.scale_log2;   // all scores are -inf then: exp2 -> 0
       float ls[4] = {0.f, 0.f, 0.f, 0.f};
-      uint32_t pk[BKV / 2];
+      uint32_t pk[32];
 #pragma unroll
-      for (int i = 0; i < BKV; i += 4) {
+      for (int i = 0; i < 64; i += 4) {
         float x0, x1, x2, x3;
         ffma2(x0, x1, __uint_as_float(r[i]), __uint_as_float(r[i + 1]), p.scale_log2, -mb);
         ffma2(x2, x3, __uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]), p.scale_log2, -mb);
+#if PDB_FA_DIAG == 0
         x0 = ex2_approx(x0);
         x1 = ex2_approx(x1);
-        x2 = ex2_approx(x2);
-        x3 = ex2_approx(x3);
+        // PDB_FA_POLY: share of the exponentials computed on the FMA pipe (1: 1/8, 2: 1/4, 3: 1/2)
+        if ((PDB_FA_POLY == 3) || (PDB_FA_POLY == 2 && (i & 4)) || (PDB_FA_POLY == 1 && (i & 12) == 12)) {
+          ex2_poly2(x2, x3, x2, x3);
+        } else {
+          x2 = ex2_approx(x2);
+          x3 = ex2_approx(x3);
+        }
+#endif
         fadd2(ls[0], ls[1], x0, x1);
         fadd2(ls[2], ls[3], x2, x3);
         pk[i >> 1] = pack2<kHalf>(x0, x1);
@@ -282,100 +339,61 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
         const uint32_t bh = (uint32_t)(b * p.hq + h);
         const int sh = (q_idx & 1) * 16;
 #pragma unroll
-        for (int i = 0; i < BKV; i += 2) {
-          const uint32_t w = dropout_patch(p.drop, bh, (uint32_t)q_idx, (uint32_t)(j * BKV + i)) >> sh;
+        for (int i = 0; i < 64; i += 2) {
+          const uint32_t w = dropout_patch(p.drop, bh, (uint32_t)q_idx, (uint32_t)(key0 + i)) >> sh;
           uint32_t m = 0;
           if ((w & 0xffu) < p.drop.threshold) m |= 0x0000ffffu;
           if (((w >> 8) & 0xffu) < p.drop.threshold) m |= 0xffff0000u;
           pk[i >> 1] &= m;
         }
       }
-      if (it > 0) {
-        // the previous P V of this group must be done before P is overwritten or O is touched
-        mbar_wait(&o_full[g], (it - 1) & 1);
-        tc_fence_after();
-        if (rescale) {
-#pragma unroll
-          for (int c = 0; c < D / 32; ++c) {
-            uint32_t o[32];
-            tmem_ld_32x32(to + c * 32, o);
-            tmem_ld_wait();
-#pragma unroll
-            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-            tmem_st_32x32(to + c * 32, o);
-          }
-          tmem_st_wait();
-        }
+      l_part += (ls[0] + ls[1]) + (ls[2] + ls[3]);
+      if (tr_on) PDB_TR(1 + half, 3);
+      // P -> TMEM over the first 32 of the 64 score columns this thread has read (its own lanes and columns only)
+      tmem_st_32x32(ts, pk);
+      tmem_st_wait();
+      if (j > 0) {
+        // keeps the parity of o_full unambiguous (one completion per tile, observed every tile); P_(j-1) V was issued a
+        // whole softmax ago, so this does not wait in practice
+        mbar_wait(o_full, (j - 1) & 1);
       }
-      // P -> shared memory (UMMA K-major, 128-byte swizzle): 32 keys = 4 chunks of 16 B inside k-block (c / 2),
-      // chunk index ((c & 1) * 4 + t), XOR-swizzled by row % 8
-#pragma unroll
-      for (int c = 0; c < BKV / 32; ++c) {
-        const uint32_t base = sPg_u32 + (c >> 1) * (BQ * 128) + row * 128;
-#pragma unroll
-        for (int t = 0; t < 4; ++t) {
-          const int chunk = ((c & 1) * 4 + t) ^ (row & 7);
-          sts128(base + chunk * 16, pk[c * 16 + t * 4], pk[c * 16 + t * 4 + 1], pk[c * 16 + t * 4 + 2], pk[c * 16 + t * 4 + 3]);
-        }
-      }
-      l_run += (ls[0] + ls[1]) + (ls[2] + ls[3]);
-      // publish P (generic-proxy writes -> async proxy) and any TMEM rescale to the MMA warp
+      // publish P and any rescale of O to the MMA warp
       tc_fence_before();
-      fence_proxy_async();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&p_ready[g]);
+      if (lane == 0) mbar_arrive(&p_ready[sb]);
+      if (tr_on) PDB_TR(1 + half, 5);
     }
-    // ---- merge the two groups' partial results ------------------------------------------------------------
-    if (it > 0) {
-      mbar_wait(&o_full[g], (it - 1) & 1);
-      tc_fence_after();
-    }
-    const uint32_t stats = smem_u32(sP);                   // P buffers are free now: [group][row][2] floats
-    // group B may still be reading... no: each group only touches its own P buffer; the stats live in group A's
-    // buffer, which group A's last P V (awaited above by group A) has finished reading before A writes here, and B
-    // writes only after the named barrier below orders it behind A's wait.
-    named_bar_sync(1, 256);
-    sts32f(stats + ((g * BQ + row) * 2) * 4, (it > 0) ? m_used : -INFINITY);
-    sts32f(stats + ((g * BQ + row) * 2 + 1) * 4, l_run);
-    tc_fence_before();
-    named_bar_sync(1, 256);
+    // ---- combine the half-row sums, normalise, store --------------------------------------------------------
+    mbar_wait(o_full, (n_kv - 1) & 1);
     tc_fence_after();
-    const float m_a = lds32f(stats + (row * 2) * 4), l_a = lds32f(stats + (row * 2 + 1) * 4);
-    const float m_b = lds32f(stats + ((BQ + row) * 2) * 4), l_b = lds32f(stats + ((BQ + row) * 2 + 1) * 4);
-    const bool has_b = n_kv > 1;
-    const float m_fin = fmaxf(m_a, m_b);                    // -inf only for a row that sees no key at all
-    const float f_a = (m_a == -INFINITY) ? 0.f : ex2_approx((m_a - m_fin) * p.scale_log2);
-    const float f_b = (m_b == -INFINITY) ? 0.f : ex2_approx((m_b - m_fin) * p.scale_log2);
-    const float l_fin = l_a * f_a + l_b * f_b;
-    const float inv_l = (l_fin > 0.f ? 1.f / l_fin : 0.f) * (kDrop ? p.drop.inv_keep : 1.f);
-    const float w_a = f_a * inv_l, w_b = f_b * inv_l;
+    sts32f(xch + (half * BQ + row) * 4, l_part);
+    named_bar_sync(2, 256);
+    const float l_fin = lds32f(xch + row * 4) + lds32f(xch + (BQ + row) * 4);
+    // a row with a visible key has a sum of at least 2^-8 (its largest probability); a row without one only collects
+    // the ~1e-38 that the polynomial exp2 returns for -inf
+    const bool seen = l_fin > 1e-20f;
+    const float inv_l = (seen ? 1.f / l_fin : 0.f) * (kDrop ? p.drop.inv_keep : 1.f);
     const bool row_ok = q_idx < q_len;
-    // group g writes columns [g * D/2, (g+1) * D/2) of the row
-    uint16_t* orow = p.o + ((int64_t)(q_row0 + row) * p.hq + h) * D + g * (D / 2);
+    // this thread stores columns [half * D/2, (half+1) * D/2) of its row
+    uint16_t* orow = p.o + ((int64_t)(q_row0 + row) * p.hq + h) * D + half * (D / 2);
 #pragma unroll
     for (int c = 0; c < D / 64; ++c) {
-      uint32_t oa[32], ob[32];
-      tmem_ld_32x32(tmem_o + lane_off + g * (D / 2) + c * 32, oa);
-      if (has_b) tmem_ld_32x32(tmem_o + D + lane_off + g * (D / 2) + c * 32, ob);
+      uint32_t oa[32];
+      tmem_ld_32x32(to + c * 32, oa);
       tmem_ld_wait();
 #pragma unroll
       for (int i = 0; i < 32; i += 8) {
-        float v[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          v[u] = __uint_as_float(oa[i + u]) * w_a;
-          if (has_b) v[u] = fmaf(__uint_as_float(ob[i + u]), w_b, v[u]);
-        }
         uint4 pk;
-        pk.x = pack2<kHalf>(v[0], v[1]);
-        pk.y = pack2<kHalf>(v[2], v[3]);
-        pk.z = pack2<kHalf>(v[4], v[5]);
-        pk.w = pack2<kHalf>(v[6], v[7]);
+        pk.x = pack2<kHalf>(__uint_as_float(oa[i]) * inv_l, __uint_as_float(oa[i + 1]) * inv_l);
+        pk.y = pack2<kHalf>(__uint_as_float(oa[i + 2]) * inv_l, __uint_as_float(oa[i + 3]) * inv_l);
+        pk.z = pack2<kHalf>(__uint_as_float(oa[i + 4]) * inv_l, __uint_as_float(oa[i + 5]) * inv_l);
+        pk.w = pack2<kHalf>(__uint_as_float(oa[i + 6]) * inv_l, __uint_as_float(oa[i + 7]) * inv_l);
         if (row_ok) *reinterpret_cast<uint4*>(orow + c * 32 + i) = pk;
       }
     }
-    if (g == 0 && p.lse && row_ok)
-      p.lse[stat_row0 + row] = l_fin > 0.f ? m_fin * p.scale + __logf(l_fin) : -INFINITY;
+    if (tr_on) PDB_TR(1 + half, 7);
+    if (half == 0 && p.lse && row_ok)
+      p.lse[stat_row0 + row] = seen ? m_used * p.scale + __logf(l_fin) : -INFINITY;
   }
 
   tc_fence_before();
@@ -432,6 +450,13 @@ static int launch_fwd_dt(bool half, const void* q, const void* k, const void* v,
 }  // namespace pdb
 
 using namespace pdb;
+
+#ifdef PDB_FA_TRACE
+PDB_EXPORT int pdb200_flash_attn_set_trace(void* buf) {
+  unsigned long long* p = (unsigned long long*)buf;
+  return cudaMemcpyToSymbol(fa::g_trace, &p, sizeof(p)) == cudaSuccess ? 0 : -1;
+}
+#endif
 
 static int fa_fwd_common(const void* q, const void* k, const void* v, void* o, float* lse, const fac::SeqArgs& seq,
                          int64_t rows_q, int64_t rows_k, int64_t b, int64_t hq, int64_t hk, int64_t d, float scale, int causal,

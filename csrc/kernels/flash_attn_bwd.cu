@@ -168,7 +168,7 @@ flash_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
   if (warp < 4) {
   reg_dealloc<56>();
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_expect_tx(qdo_full, 2 * S::kTile);
 #pragma unroll
       for (int kb = 0; kb < KB; ++kb) {
@@ -185,7 +185,7 @@ flash_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
       }
     }
   } else if (warp == 3) {
-    if (lane == 0) {
+    if (elect_one()) {
       for (int j = 0; j < n_kv; ++j) {
         const int st = j & 1;
         mbar_wait(&v_empty[st], ((j >> 1) & 1) ^ 1);
@@ -196,7 +196,7 @@ flash_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (elect_one()) {   // elect.sync, not a lane test: ptxas then knows one lane runs this and issues UTCHMMA / UTCBAR from uniform registers
       constexpr uint32_t idesc_s = make_idesc_16(kHalf, 128, 128, 0, 0);    // [q][d] x [keys][d]^T
       constexpr uint32_t idesc_dq = make_idesc_16(kHalf, 128, D, 0, 1);     // dS [q][keys] x K [keys][d] (MN-major)
       auto issue_sdp = [&](int j) {

@@ -105,7 +105,7 @@ flash_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
   if (warp < 4) {
     reg_dealloc<56>();
     if (warp == 0) {
-      if (lane == 0) {
+      if (elect_one()) {
         mbar_expect_tx(kv_full, 2 * S::kTile);
 #pragma unroll
         for (int kb = 0; kb < KB; ++kb) {
@@ -123,7 +123,7 @@ flash_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
         }
       }
     } else if (warp == 3) {
-      if (lane == 0) {
+      if (elect_one()) {
         for (int t = 0; t < T; ++t) {
           const int st = t & 1;
           const int h = hk * G + t / n_qi, i = i0 + t % n_qi;
@@ -135,7 +135,7 @@ flash_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
         }
       }
     } else if (warp == 1) {
-      if (lane == 0) {
+      if (elect_one()) {   // elect.sync, not a lane test: ptxas then knows one lane runs this and issues UTCHMMA / UTCBAR from uniform registers
         constexpr uint32_t idesc_t = make_idesc_16(kHalf, 128, 128, 0, 0);    // [keys][d] x [q][d]^T
         constexpr uint32_t idesc_acc = make_idesc_16(kHalf, 128, D, 0, 1);    // [keys][q] (TMEM) x [q][d] (MN-major smem)
         auto issue_s = [&](int t) {

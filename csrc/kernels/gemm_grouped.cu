@@ -124,7 +124,7 @@ gemm_grouped_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
   };
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       int stage = 0, seg_i = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
@@ -153,7 +153,7 @@ gemm_grouped_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (elect_one()) {   // elect.sync, not a lane test: ptxas then issues UTCHMMA / UTCBAR from uniform registers
       constexpr uint32_t idesc = make_idesc_bf16(BM, BN, 0, B_MN ? 1 : 0);
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
@@ -306,7 +306,7 @@ gemm_grouped_wgrad_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid
   };
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
@@ -363,7 +363,7 @@ gemm_grouped_wgrad_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid
           fence_proxy_async();                     // generic-proxy zeros visible to the tensor core's reads
           __syncwarp();
         }
-        if (lane == 0) {
+        if (elect_one()) {
           const uint32_t sa = smem_u32(sa_ptr);
           const uint32_t sb = sa + kABytes;
 #pragma unroll

@@ -199,11 +199,42 @@ __device__ __forceinline__ void ffma2v(float& d0, float& d1, float a0, float a1,
   asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
   asm("mov.b64 {%0, %1}, %2;" : "=f"(d0), "=f"(d1) : "l"(d));
 }
+// 2^x for a pair of values on the FMA pipe instead of the 16-lane/clk/SM special-function unit: round-to-nearest split
+// x = n + f with the 1.5 * 2^23 trick (n sits in the low mantissa bits of t), degree-3 minimax polynomial for 2^f on
+// [-0.5, 0.5] (relative error 7.5e-5, well under bf16/fp16 rounding of the probabilities), then n is added to the
+// exponent field.  x is clamped to >= -126 (-inf scores of masked keys come out as ~1e-38, i.e. 0 after rounding).
+__device__ __forceinline__ void ex2_poly2(float& r0, float& r1, float x0, float x1) {
+  constexpr float kMagic = 12582912.f;
+  x0 = fmaxf(x0, -126.f);
+  x1 = fmaxf(x1, -126.f);
+  float t0, t1, n0, n1, f0, f1, p0, p1;
+  ffma2(t0, t1, x0, x1, 1.f, kMagic);
+  ffma2(n0, n1, t0, t1, 1.f, -kMagic);
+  ffma2v(f0, f1, n0, n1, -1.f, -1.f, x0, x1);
+  ffma2(p0, p1, f0, f1, 0.05517143756151199f, 0.24261081218719482f);
+  ffma2v(p0, p1, p0, p1, f0, f1, 0.6932609677314758f, 0.6932609677314758f);
+  ffma2v(p0, p1, p0, p1, f0, f1, 0.9999281167984009f, 0.9999281167984009f);
+  r0 = __int_as_float(__float_as_int(p0) + (__float_as_int(t0) << 23));
+  r1 = __int_as_float(__float_as_int(p1) + (__float_as_int(t1) << 23));
+}
 // Give registers back (producer / issuer warpgroups) or take more (math warpgroups); whole warpgroup must execute it.
 template <int N> __device__ __forceinline__ void reg_dealloc() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
 template <int N> __device__ __forceinline__ void reg_alloc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+// Named barrier that also ORs a predicate over the participating threads (one instruction, no shared memory).
+__device__ __forceinline__ bool bar_red_or(int id, int nthreads, bool pred) {
+  uint32_t out;
+  asm volatile(
+      "{\n\t.reg .pred pi, po;\n\t"
+      "setp.ne.u32 pi, %1, 0;\n\t"
+      "bar.red.or.pred po, %2, %3, pi;\n\t"
+      "selp.u32 %0, 1, 0, po;\n\t}\n"
+      : "=r"(out)
+      : "r"((uint32_t)pred), "r"(id), "r"(nthreads)
+      : "memory");
+  return out != 0;
 }
 
 // ---- descriptors -------------------------------------------------------------------------------------------

@@ -127,7 +127,7 @@ def reset_launch_count():
     _count[0] = 0
 
 
-kernels = NativeLib("libpdb200_kernels.so", "pdb200_kernels.h")
+kernels = NativeLib("libpdb200_kernels.so", "pdb200_kernels.h", env_override="PDB200_KERNELS_LIB")
 runtime = NativeLib("libpdb200_runtime.so", "pdb200_runtime.h", env_override="PDB200_RUNTIME_LIB")
 
 
