@@ -86,8 +86,8 @@ class SymmArena:
 
     def alloc(self, nbytes, align=256):
         off = self._rt.pdb200_heap_alloc(self._heap, int(nbytes), int(align))
-        if off < 0 and _evict_cached(self, int(nbytes) + align):
-            off = self._rt.pdb200_heap_alloc(self._heap, int(nbytes), int(align))
+        if off < 0:
+            off = _evict_cached(self, int(nbytes), int(align))
         if off < 0:
             raise MemoryError(f"symmetric arena exhausted: need {nbytes} B, largest free block {self.largest_free()} B of "
                               f"{self.free_bytes()} B free, capacity {self.nbytes} B (PDB200_SYMM_ARENA_MB sets the size)")
@@ -385,29 +385,28 @@ def _state_tensors(v):
     return []
 
 
-def _evict_cached(arena, need):
+def _evict_cached(arena, nbytes, align):
     """The arena is out of room: drop least-recently-used staging states (gathered buffers, partial-sum buffers, flag
-    words cached per shape) until a block of ``need`` bytes exists.  Every rank runs the same call sequence, so every
-    rank evicts the same entries here; a peer may still be writing into a buffer of an earlier call, hence the device
-    synchronisation and the group barrier before anything is reused.  Returns True if something was freed."""
+    words cached per shape) one by one until the request fits, and return its offset (-1: nothing left to drop).  Every
+    rank runs the same call sequence, so every rank evicts the same entries here; a peer may still be writing into a
+    buffer of an earlier call, hence the device synchronisation and the group barrier before anything is reused."""
     victims = []
     for cache in _caches:
         for k in cache:
             if k[0] == id(arena):
                 victims.append((cache._used.get(k, 0), id(cache), cache, k))
     if not victims:
-        return False
+        return -1
     victims = [(c, k) for _, _, c, k in sorted(victims, key=lambda v: v[:2])]      # least recently used first
     torch.cuda.synchronize()
     C.barrier(arena.group)
-    freed = False
     for cache, k in victims:
         for t in _state_tensors(cache.pop(k)):
             arena.free(t)
-            freed = True
-        if arena.largest_free() >= need:
-            break
-    return freed
+        off = arena._rt.pdb200_heap_alloc(arena._heap, nbytes, align)
+        if off >= 0:
+            return off
+    return -1
 
 
 def _staging(arena, tag, shape, dtype):

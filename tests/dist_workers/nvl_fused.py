@@ -195,16 +195,18 @@ dist.all_gather_object(offs, (t2._symm[1], t3._symm[1]))
 assert len(set(offs)) == 1, f"ranks disagree on offsets: {offs}"
 small.free(t2)
 small.free(t3)
-s1 = symm._staging(small, "evict_a", (3 << 20,), torch.uint8)
-s2 = symm._staging(small, "evict_b", (3 << 20,), torch.uint8)
-s3 = symm._staging(small, "evict_c", (3 << 20,), torch.uint8)          # does not fit next to a and b: a (least recent) goes
-assert (id(small), "evict_a", (3 << 20,), torch.uint8) not in symm._stage
-assert (id(small), "evict_b", (3 << 20,), torch.uint8) in symm._stage
+cap = small.free_bytes()                      # the driver rounds the arena up to its mapping granularity
+chunk = cap // 8 * 3 // 4096 * 4096           # two of these fit, three do not
+s1 = symm._staging(small, "evict_a", (chunk,), torch.uint8)
+s2 = symm._staging(small, "evict_b", (chunk,), torch.uint8)
+s3 = symm._staging(small, "evict_c", (chunk,), torch.uint8)            # does not fit next to a and b: a (least recent) goes
+assert (id(small), "evict_a", (chunk,), torch.uint8) not in symm._stage
+assert (id(small), "evict_b", (chunk,), torch.uint8) in symm._stage
 st = small.stats()
-assert st["live_blocks"] == 2 and st["in_use"] == 6 << 20, st
+assert st["live_blocks"] == 2 and st["in_use"] == 2 * chunk, st
 s3.fill_(r + 1)
 try:
-    small.empty((9 << 20,), torch.uint8)
+    small.empty((cap + (1 << 20),), torch.uint8)
     raise AssertionError("oversize allocation must fail")
 except MemoryError:
     pass
