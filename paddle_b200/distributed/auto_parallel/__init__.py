@@ -1,13 +1,15 @@
 """Semi-auto parallel dygraph API (reference: python/paddle/distributed/auto_parallel/api.py:131-2846,
 process_mesh.py, placement_type.py; native DistTensor/reshard under paddle/phi/core/distributed/auto_parallel/).
 
-A ``DistTensor`` here is a local torch tensor plus ``(process_mesh, placements)`` metadata: ``shard_tensor`` cuts the
-local shard out of the global value, ``reshard`` moves between placements with the matching collective
-(r->s slice, s->r all-gather, p->r all-reduce, p->s reduce-scatter, s->s all-to-all), ``unshard_dtensor`` rebuilds
-the global value, and a change of mesh (same shape, other ranks) is a send / recv pair.  SPMD propagation (N13) lives
-in ``spmd_rules``: ``dist_op(name, fn, *dtensors)`` infers the shardings with the op's rule, reshards the inputs the
-rule asks for, runs ``fn`` on the local shards and labels the outputs (partial outputs stay ``Partial`` until someone
-reshards them)."""
+A ``DistTensor`` (``dtensor.py``) is the local shard as a ``torch.Tensor`` subclass carrying ``(process_mesh,
+placements)``: ``shard_tensor`` cuts the local shard out of the global value, ``reshard`` moves between placements with
+the matching collective (r->s slice, s->r all-gather, p->r all-reduce, p->s reduce-scatter, s->s all-to-all; every step
+differentiable, its backward is the dual transfer), ``unshard_dtensor`` rebuilds the global value, and a change of mesh
+(same shape, other ranks) is a send / recv pair.  Ordinary ops on DistTensors propagate the sharding by themselves:
+``__torch_function__`` looks up the op's SPMD rule (N13, ``spmd_rules``), reshards the inputs the rule asks for, runs the
+op on the local shards and labels the outputs (partial outputs stay ``Partial`` until someone needs them whole);
+``dist_op(name, fn, *dtensors)`` is the same machinery for ops that are not torch functions.  ``shard_layer`` /
+``shard_optimizer`` / ``shard_dataloader`` / ``shard_scaler`` build a semi-auto training step out of it."""
 from __future__ import annotations
 
 import numpy as np
@@ -154,42 +156,36 @@ class DistAttr:
 
 
 def _attach(t, mesh, placements, global_shape):
-    t.process_mesh = mesh
-    t.placements = list(placements)
-    coord = mesh.coord_of(C.get_rank()) or tuple([0] * mesh.ndim)
-    off = [0] * len(global_shape)
-    for ax, pl in enumerate(placements):
-        if isinstance(pl, Shard):
-            off[pl.dim] += coord[ax] * t.shape[pl.dim]
-    t._dist_meta = (tuple(global_shape), tuple(off))
-    t._global_shape = tuple(global_shape)
-    return t
+    from . import dtensor as D
+    return D._attach(t, mesh, placements, global_shape)
 
 
 def is_dist(t):
-    return hasattr(t, "placements") and hasattr(t, "process_mesh")
+    return isinstance(t, torch.Tensor) and hasattr(t, "placements") and hasattr(t, "process_mesh")
 
 
 def shard_tensor(data, mesh, placements, dtype=None, place=None, stop_gradient=None):
+    """Cut this rank's shard out of the global ``data`` (reference: api.py:131-300).  Parameters come back as
+    parameters (``DistParameter``), other tensors as leaf ``DistTensor``s."""
     from paddle_b200.tensor.creation import to_tensor
+    from . import dtensor as D
     t = data if isinstance(data, torch.Tensor) else to_tensor(data, dtype=dtype, place=place)
     gshape = tuple(t.shape)
     coord = mesh.coord_of(C.get_rank()) or tuple([0] * mesh.ndim)
-    local = t.detach()
+    local = D.local_of(t).detach()
     for ax, pl in enumerate(placements):
         if isinstance(pl, Shard):
             n = mesh.shape[ax]
             assert local.shape[pl.dim] % n == 0, f"dim {pl.dim} ({local.shape[pl.dim]}) not divisible by mesh axis {n}"
             local = local.chunk(n, dim=pl.dim)[coord[ax]]
+        elif isinstance(pl, Partial) and coord[ax] != 0:
+            local = torch.zeros_like(local)
     local = local.contiguous().clone()
     if isinstance(data, torch.nn.Parameter):
-        from paddle_b200.framework.tensor_patch import Parameter
-        out = Parameter(local, data.requires_grad, name=getattr(data, "name", None))
-    else:
-        out = local
-        sg = stop_gradient if stop_gradient is not None else not getattr(data, "requires_grad", False)
-        out.stop_gradient = sg
-    return _attach(out, mesh, placements, gshape)
+        return D.make_parameter(local, mesh, placements, gshape, like=data)
+    sg = stop_gradient if stop_gradient is not None else not getattr(data, "requires_grad", False)
+    out = D.make_leaf(local, mesh, placements, gshape, requires_grad=not sg and local.is_floating_point())
+    return out
 
 
 def dtensor_from_fn(fn, mesh, placements, *args, **kwargs):
@@ -198,24 +194,22 @@ def dtensor_from_fn(fn, mesh, placements, *args, **kwargs):
 
 def dtensor_from_local(local_tensor, mesh, placements):
     """Wrap this rank's local shard as a distributed tensor (reference: auto_parallel/api.py:499-520): the global
-    shape is the local shape multiplied by the mesh size along every sharded dim."""
+    shape is the local shape multiplied by the mesh size along every sharded dim.  Differentiable: the result stays
+    attached to ``local_tensor``'s autograd graph."""
+    from . import dtensor as D
     gshape = list(local_tensor.shape)
     for ax, pl in enumerate(placements):
         if isinstance(pl, Shard):
             gshape[pl.dim] *= mesh.shape[ax]
-    return _attach(local_tensor, mesh, placements, tuple(gshape))
+    return D.wrap(D.local_of(local_tensor).view_as(local_tensor) if local_tensor.requires_grad else local_tensor,
+                  mesh, placements, tuple(gshape))
 
 
 def dtensor_to_local(dist_tensor, mesh=None, placements=None):
-    """The local shard of a distributed tensor, as a plain tensor."""
-    out = dist_tensor.detach().clone() if not dist_tensor.requires_grad else dist_tensor * 1
-    for attr in ("process_mesh", "placements", "_global_shape"):
-        if hasattr(out, attr):
-            try:
-                delattr(out, attr)
-            except AttributeError:
-                pass
-    return out
+    """The local shard of a distributed tensor, as a plain tensor (same autograd graph)."""
+    from . import dtensor as D
+    loc = D.local_of(dist_tensor)
+    return loc.view_as(loc) if loc.requires_grad else loc.detach()
 
 
 _g_mesh = None
@@ -271,93 +265,36 @@ def _cross_mesh(dist_tensor, mesh):
 
 
 def reshard(dist_tensor, mesh, placements):
+    """Move a distributed tensor to other placements (and, for a mesh of the same shape, other ranks).  One collective
+    per mesh axis that changes (reference: reshard/{r_to_s,s_to_r,p_to_r,p_to_s,s_to_s,r_to_p,same_status}_reshard_function.cc);
+    differentiable - the backward of each step is the dual transfer."""
+    from . import dtensor as D
     assert is_dist(dist_tensor), "reshard expects a tensor produced by shard_tensor"
     if dist_tensor.process_mesh != mesh and C.get_world_size() > 1:
         dist_tensor = _cross_mesh(dist_tensor, mesh)
-    src = dist_tensor.placements
     gshape = dist_tensor._global_shape
-    t = dist_tensor.detach() if not dist_tensor.requires_grad else dist_tensor
-    coord = mesh.coord_of(C.get_rank()) or tuple([0] * mesh.ndim)
-    for ax, (a, b) in enumerate(zip(src, placements)):
-        if a == b:
-            continue
-        n = mesh.shape[ax]
-        g = mesh.axis_group(ax) if n > 1 else None
-        if isinstance(a, Shard) and isinstance(b, Replicate):
-            t = _gather_axis(t, g, a.dim) if n > 1 else t
-        elif isinstance(a, Replicate) and isinstance(b, Shard):
-            t = t.chunk(n, dim=b.dim)[coord[ax]].contiguous()
-        elif isinstance(a, Partial) and isinstance(b, Replicate):
-            t = t.clone()
-            if n > 1:
-                comm.all_reduce(t, a.reduce_type, g)
-        elif isinstance(a, Partial) and isinstance(b, Shard):
-            # p -> s: one reduce-scatter (reference p_to_s_reshard_function.cc), not all-reduce + slice
-            if n > 1 and t.shape[b.dim] % n == 0:
-                moved = t.movedim(b.dim, 0).contiguous()
-                out = torch.empty((moved.shape[0] // n,) + tuple(moved.shape[1:]), dtype=t.dtype, device=t.device)
-                comm.reduce_scatter(out, moved, a.reduce_type, g)
-                t = out.movedim(0, b.dim).contiguous()
-            else:
-                t = t.clone()
-                if n > 1:
-                    comm.all_reduce(t, a.reduce_type, g)
-                t = t.chunk(n, dim=b.dim)[coord[ax]].contiguous()
-        elif isinstance(a, Shard) and isinstance(b, Shard):
-            # s -> s on another dim: one all-to-all (reference s_to_s_reshard_function.cc)
-            if n > 1 and t.shape[b.dim] % n == 0:
-                pieces = [c.contiguous() for c in t.chunk(n, dim=b.dim)]
-                recv = [torch.empty_like(pieces[0]) for _ in range(n)]
-                comm.alltoall(recv, pieces, g)
-                t = torch.cat(recv, dim=a.dim)
-            else:
-                full = _gather_axis(t, g, a.dim) if n > 1 else t
-                t = full.chunk(n, dim=b.dim)[coord[ax]].contiguous()
-        elif isinstance(a, Replicate) and isinstance(b, Partial):
-            t = t if coord[ax] == 0 else torch.zeros_like(t)
-        elif isinstance(a, Shard) and isinstance(b, Partial):
-            full = _gather_axis(t, g, a.dim) if n > 1 else t
-            t = full if coord[ax] == 0 else torch.zeros_like(full)
-        else:
-            raise NotImplementedError(f"reshard {a} -> {b}")
-    return _attach(t, mesh, placements, gshape)
+    loc = D.reshard_local(D.local_of(dist_tensor), mesh, list(dist_tensor.placements), list(placements))
+    if loc is D.local_of(dist_tensor) or loc.data_ptr() == dist_tensor.data_ptr():
+        loc = loc.view_as(loc) if loc.requires_grad else loc.detach()        # a fresh label, not a relabelled input
+    return D.wrap(loc, mesh, placements, gshape)
 
 
 def dist_op(op_name, fn, *dtensors, **attrs):
     """Run ``fn`` on the local shards of ``dtensors`` under the SPMD rule ``op_name`` (see ``spmd_rules``): inputs are
-    resharded to what the rule requires, outputs come back labelled with the inferred placements."""
-    from . import spmd_rules as R
-    mesh = next(t.process_mesh for t in dtensors if is_dist(t))
-    specs = []
-    for t in dtensors:
-        assert is_dist(t), "dist_op takes distributed tensors (see shard_tensor)"
-        specs.append(R.DistTensorSpec.from_placements(t._global_shape, t.placements))
-    new_specs, out_specs = R.infer_forward(op_name, *specs, **attrs)
-    locals_ = []
-    for t, want in zip(dtensors, new_specs):
-        pl = want.placements(mesh.ndim)
-        # a partial input the rule did not ask to keep partial is reduced first
-        cur = [p if not p.is_partial() else Replicate() for p in t.placements] if any(p.is_partial() for p in t.placements) else t.placements
-        if any(p.is_partial() for p in t.placements):
-            t = reshard(t, mesh, cur)
-        locals_.append(t if list(t.placements) == list(pl) else reshard(t, mesh, pl))
-    res = fn(*locals_)
-    outs = res if isinstance(res, (tuple, list)) else [res]
-    labelled = [_attach(o, mesh, sp.placements(mesh.ndim), sp.shape) for o, sp in zip(outs, out_specs)]
-    return labelled if isinstance(res, (tuple, list)) else labelled[0]
+    resharded to what the rule requires, outputs come back labelled with the inferred placements.  This is what every
+    torch function does by itself on DistTensors; use it for ops that are not torch functions."""
+    from . import dtensor as D
+    return D.run_rule(op_name, fn, list(dtensors), attrs)
 
 
 def unshard_dtensor(dist_tensor):
+    """The global value as a plain tensor (reference: api.py unshard_dtensor)."""
+    from . import dtensor as D
     if not is_dist(dist_tensor):
         return dist_tensor
     mesh = dist_tensor.process_mesh
-    out = reshard(dist_tensor, mesh, [Replicate() for _ in dist_tensor.placements])
-    for attr in ("placements", "process_mesh", "_dist_meta", "_global_shape"):
-        try:
-            delattr(out, attr)
-        except AttributeError:
-            pass
-    return out
+    loc = D.reshard_local(D.local_of(dist_tensor), mesh, list(dist_tensor.placements), [Replicate() for _ in range(mesh.ndim)])
+    return loc.view_as(loc) if loc.requires_grad else loc.detach().clone()
 
 
 def shard_layer(layer, process_mesh, shard_fn=None, input_fn=None, output_fn=None):
@@ -377,8 +314,22 @@ def shard_layer(layer, process_mesh, shard_fn=None, input_fn=None, output_fn=Non
 
 
 class _ShardingStage:
-    def __init__(self, mesh=None, sharding_mesh_dim=None):
+    """``shard_fn`` objects of ``shard_optimizer`` (reference: api.py ShardingStage1/2/3): partition the optimizer work
+    for parameters that are REPLICATED along mesh dim ``sharding_mesh_dim``.  Here all three levels partition the
+    optimizer states and the update (each rank along the dim owns every n-th such parameter, updates it and broadcasts
+    the result); gradients and parameters themselves stay whole on every rank, which is stage-1 memory behaviour."""
+    level = "os"
+
+    def __init__(self, sharding_mesh_dim=None, mesh=None):
+        if isinstance(sharding_mesh_dim, ProcessMesh):                   # the older (mesh, dim) argument order
+            sharding_mesh_dim, mesh = mesh, sharding_mesh_dim
         self.mesh, self.sharding_mesh_dim = mesh, sharding_mesh_dim
+
+    def axis(self, mesh):
+        d = self.sharding_mesh_dim
+        if d is None:
+            return 0
+        return mesh.dim_names.index(d) if isinstance(d, str) else int(d)
 
 
 class ShardingStage1(_ShardingStage):
@@ -393,17 +344,183 @@ class ShardingStage3(_ShardingStage):
     level = "p_g_os"
 
 
+def _sharded_axes(p):
+    return tuple(ax for ax, pl in enumerate(p.placements) if isinstance(pl, Shard)) if is_dist(p) else ()
+
+
+class _DistGlobalNormClip:
+    """ClipGradByGlobalNorm over distributed parameters: the squared norm of a sharded gradient is summed over the mesh
+    axes it is sharded on; replicated gradients count once (reference: auto_parallel clip handling in
+    python/paddle/nn/clip.py ``_dygraph_clip`` for dist tensors)."""
+
+    def __init__(self, inner):
+        self.inner = inner
+        self.clip_norm = inner.clip_norm
+
+    @torch.no_grad()
+    def __call__(self, params_grads):
+        from . import dtensor as D
+        buckets = {}
+        mesh = None
+        for p, g in params_grads:
+            if g is None or not getattr(p, "need_clip", True):
+                continue
+            mesh = mesh or (p.process_mesh if is_dist(p) else None)
+            key = _sharded_axes(p)
+            sq = D.local_of(g).float().pow(2).sum()
+            buckets[key] = buckets.get(key, 0) + sq
+        if not buckets:
+            return params_grads
+        total = None
+        for axes, sq in buckets.items():
+            sq = sq.reshape(1).clone()
+            for ax in axes:
+                if mesh.shape[ax] > 1:
+                    comm.all_reduce(sq, C.ReduceOp.SUM, mesh.axis_group(ax))
+            total = sq if total is None else total + sq
+        coef = self.inner.clip_coef(total)
+        for p, g in params_grads:
+            if g is not None and getattr(p, "need_clip", True):
+                D.local_of(g).mul_(coef.to(g.dtype))
+        return params_grads
+
+    _dygraph_clip = __call__
+
+
+class _ShardOptimizer:
+    """``shard_optimizer`` result: the wrapped optimizer sees local shards (its accumulators are created with the local
+    shapes, so they are sharded exactly like their parameters); this wrapper adds what needs the mesh - the global-norm
+    clip over sharded gradients and, with a ShardingStage ``shard_fn``, the partition of the update."""
+
+    def __init__(self, optimizer, shard_fn=None, gradient_accumulation_steps=1):
+        self.__dict__["_inner"] = optimizer
+        self.__dict__["_shard_fn"] = shard_fn
+        self.__dict__["_gradient_accumulation_steps"] = gradient_accumulation_steps
+        self.__dict__["_acc"] = 0
+        from paddle_b200.nn.clip import ClipGradByGlobalNorm
+        clip = getattr(optimizer, "_grad_clip", None)
+        if isinstance(clip, ClipGradByGlobalNorm):
+            optimizer._grad_clip = _DistGlobalNormClip(clip)
+
+    def __getattr__(self, k):
+        return getattr(self._inner, k)
+
+    def __setattr__(self, k, v):
+        setattr(self._inner, k, v)
+
+    def _params(self):
+        return [p for p in self._inner._parameter_list if isinstance(p, torch.Tensor)]
+
+    @torch.no_grad()
+    def step(self):
+        from . import dtensor as D
+        self.__dict__["_acc"] += 1
+        if self._acc % max(int(self._gradient_accumulation_steps), 1) != 0:
+            return                                                      # keep accumulating into .grad
+        stage = self._shard_fn if isinstance(self._shard_fn, _ShardingStage) else None
+        if stage is None:
+            return self._inner.step()
+        params = [p for p in self._params() if is_dist(p)]
+        mesh = stage.mesh or (params[0].process_mesh if params else None)
+        if mesh is None:
+            return self._inner.step()
+        ax = stage.axis(mesh)
+        n = mesh.shape[ax]
+        if n == 1:
+            return self._inner.step()
+        me = mesh.coord_of(C.get_rank())[ax]
+        group = mesh.axis_group(ax)
+        clip = getattr(self._inner, "_grad_clip", None)
+        if clip is not None:                                            # the norm needs every gradient: clip first
+            clip([(p, p.grad) for p in self._params() if p.grad is not None])
+        owned = {}
+        k = 0
+        for p in params:
+            if isinstance(p.placements[ax], Replicate):
+                owned[id(p)] = k % n
+                k += 1
+        hidden = []
+        for p in params:
+            o = owned.get(id(p))
+            if o is not None and o != me and p.grad is not None:
+                hidden.append((p, p.grad))
+                p.grad = None
+        self._inner._grad_clip = None
+        try:
+            self._inner.step()
+        finally:
+            self._inner._grad_clip = clip
+            for p, g in hidden:
+                p.grad = g
+        for p in params:
+            o = owned.get(id(p))
+            if o is not None:
+                comm.broadcast(D.local_of(p).data, group.ranks[o], group)
+
+    def clear_grad(self, *a, **kw):
+        if self._acc % max(int(self._gradient_accumulation_steps), 1) == 0:
+            return self._inner.clear_grad(*a, **kw)
+
+    def state_dict(self):
+        return self._inner.state_dict()
+
+    def set_state_dict(self, sd):
+        return self._inner.set_state_dict(sd)
+
+
 def shard_optimizer(optimizer, shard_fn=None, gradient_accumulation_steps=1):
-    optimizer._shard_fn = shard_fn
-    optimizer._gradient_accumulation_steps = gradient_accumulation_steps
-    return optimizer
+    """Reference: api.py shard_optimizer (:1034-1500)."""
+    return _ShardOptimizer(optimizer, shard_fn, gradient_accumulation_steps)
+
+
+class _ShardDataLoader:
+    """``shard_dataloader`` result: every tensor of a batch becomes a DistTensor sharded along its batch dim over mesh
+    dim ``shard_dims`` (reference: api.py ShardDataloader :2560-2846).  ``is_dataset_splitted``: the wrapped loader
+    already yields this rank's part; otherwise it yields the global batch and the local part is cut out."""
+
+    def __init__(self, loader, meshes, input_keys=None, shard_dims=None, is_dataset_splitted=False):
+        self._loader = loader
+        self._meshes = meshes if isinstance(meshes, (list, tuple)) else [meshes]
+        self._keys = input_keys
+        self._dims = shard_dims if isinstance(shard_dims, (list, tuple)) else [shard_dims] * len(self._meshes)
+        self._split = is_dataset_splitted
+
+    def __len__(self):
+        return len(self._loader)
+
+    def _one(self, t, mesh, dim):
+        if not isinstance(t, torch.Tensor):
+            return t
+        pl = [Replicate() for _ in range(mesh.ndim)]
+        if dim is not None:
+            ax = mesh.dim_names.index(dim) if isinstance(dim, str) else int(dim)
+            pl[ax] = Shard(0)
+        return dtensor_from_local(t, mesh, pl) if self._split else shard_tensor(t, mesh, pl)
+
+    def __iter__(self):
+        for batch in self._loader:
+            if isinstance(batch, dict):
+                keys = self._keys or list(batch)
+                yield {k: (self._one(v, self._meshes[min(i, len(self._meshes) - 1)], self._dims[min(i, len(self._dims) - 1)])
+                           if k in keys else v) for i, (k, v) in enumerate(batch.items())}
+            elif isinstance(batch, (list, tuple)):
+                yield type(batch)(self._one(v, self._meshes[min(i, len(self._meshes) - 1)], self._dims[min(i, len(self._dims) - 1)])
+                                  for i, v in enumerate(batch))
+            else:
+                yield self._one(batch, self._meshes[0], self._dims[0])
 
 
 def shard_dataloader(dataloader, meshes, input_keys=None, shard_dims=None, is_dataset_splitted=False):
-    return dataloader
+    return _ShardDataLoader(dataloader, meshes, input_keys, shard_dims, is_dataset_splitted)
 
 
 def shard_scaler(scaler):
+    """A GradScaler whose found-inf flag is agreed on by every rank (reference: api.py shard_scaler :1562-1640): with
+    sharded gradients an overflow is visible only on the rank that holds the offending shard."""
+    def sync(optimizer, _scaler=scaler):
+        if C.get_world_size() > 1 and _scaler._found_inf is not None:
+            comm.all_reduce(_scaler._found_inf, C.ReduceOp.MAX)
+    scaler._sync_found_inf = sync
     return scaler
 
 

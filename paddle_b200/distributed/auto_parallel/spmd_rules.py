@@ -84,7 +84,7 @@ def _merge(notations, specs):
 
 def einsum_infer(notation, specs, out_shapes=None):
     lhs, rhs = notation.replace(" ", "").split("->")
-    in_notes, out_notes = lhs.split(","), [r for r in rhs.split(",")] if rhs else []
+    in_notes, out_notes = lhs.split(","), rhs.split(",")          # "ab->" has one output, a scalar
     assert len(in_notes) == len(specs), (notation, len(specs))
     axis_of = _merge(in_notes, specs)
     new_inputs = []

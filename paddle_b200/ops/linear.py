@@ -68,6 +68,10 @@ class _LinearFn(torch.autograd.Function):
 
 
 def linear(x, weight, bias=None):
+    if hasattr(x, "placements") or hasattr(weight, "placements"):
+        # distributed tensors (auto_parallel): the matmul SPMD rule decides resharding, the local product comes back here
+        from ..distributed.auto_parallel import dtensor as D
+        return D.dist_linear(x, weight, bias)
     if x.is_cuda and torch.is_autocast_enabled("cuda"):
         dt = torch.get_autocast_dtype("cuda")
         x = x.to(dt)

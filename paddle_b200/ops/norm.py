@@ -78,6 +78,13 @@ class _NormFn(torch.autograd.Function):
 
 
 def rms_norm(x, weight=None, epsilon=1e-6, bias=None, residual=None):
+    if hasattr(x, "placements") or hasattr(weight, "placements"):
+        from ..distributed.auto_parallel import dtensor as D
+        if residual is not None:
+            x = x + residual                      # element-wise rule; the fused form is a local optimisation only
+            y = D.run_rule("rms_norm", lambda a, w, b: (rms_norm(a, w, epsilon, b),), [x, weight, bias], {"begin_norm_axis": -1})[0]
+            return y, x
+        return D.run_rule("rms_norm", lambda a, w, b: (rms_norm(a, w, epsilon, b),), [x, weight, bias], {"begin_norm_axis": -1})[0]
     if use_native(x):
         return _NormFn.apply(x, weight, bias, residual, epsilon, False)
     return _norm_ref(x, weight, bias, epsilon, False, residual)

@@ -138,6 +138,10 @@ class Optimizer:
             from ..distributed import fault
             fault.tick()
         params_grads = self._collect_params_grads()
+        if any(hasattr(p, "placements") for p, _ in params_grads):
+            # auto_parallel DistParameters: the update is shard-local arithmetic, not an op on distributed tensors
+            with torch._C.DisableTorchFunctionSubclass():
+                return self._apply_optimize(None, None, params_grads)
         self._apply_optimize(None, None, params_grads)
 
     @torch.no_grad()

@@ -19,6 +19,15 @@ def test_auto_parallel_reshard_and_spmd_ops():
     run_dist("auto_parallel.py", 2)
 
 
+def test_auto_parallel_dist_tensors_train_like_single_process():
+    """DistTensor propagation through ordinary ops + autograd: tp / dp / vocab-parallel / layer training parity."""
+    run_dist("auto_parallel_train.py", 2)
+
+
+def test_auto_parallel_2d_mesh():
+    run_dist("auto_parallel_2d.py", 4)
+
+
 def test_tp_layers_shard_vs_whole():
     run_dist("tp_layers.py", 2)
 
