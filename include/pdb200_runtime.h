@@ -127,6 +127,15 @@ PDB_API int64_t pdb200_heap_alloc(void* heap, int64_t nbytes, int64_t align);
 PDB_API int pdb200_heap_free(void* heap, int64_t offset);
 PDB_API int64_t pdb200_heap_stat(void* heap, int what);
 
+/* Bookkeeping of the data-parallel reducer: which buckets may be reduced, in bucket order, as gradients arrive from
+ * autograd hooks; unused-parameter detection at the end of backward.  Tensor work and collectives stay with the caller. */
+PDB_API void* pdb200_reducer_create(const int32_t* bucket_of_param, int n_params, const uint8_t* bucket_sparse, int n_buckets);
+PDB_API void pdb200_reducer_destroy(void* reducer);
+PDB_API void pdb200_reducer_prepare(void* reducer);
+PDB_API int pdb200_reducer_mark_ready(void* reducer, int param, int32_t* out_launch, int cap);
+PDB_API int pdb200_reducer_finalize(void* reducer, int tolerate_unused, int32_t* out_missing, int cap_missing, int32_t* out_launch, int cap_launch, int32_t* n_launch);
+PDB_API void pdb200_reducer_used_bitmap(void* reducer, int32_t* out);
+
 #ifdef __cplusplus
 }
 #endif

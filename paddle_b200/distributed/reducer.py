@@ -10,7 +10,10 @@ Differences by design (B200-first):
   the bucket lives in symmetric memory);
 * buckets launch strictly in order (Appendix B.3) from post-accumulate hooks; the tail is awaited in a callback
   queued on the autograd engine, which only makes the compute stream wait - the host never blocks.
-Bucket assignment itself is native (libpdb200_runtime.so ``pdb200_assign_group_by_size``) with a Python mirror.
+Bucket assignment and the per-iteration bookkeeping (which parameter was marked, which bucket filled, which buckets may
+be reduced now - strictly in bucket order - and which parameters stayed unused) are native
+(libpdb200_runtime.so ``pdb200_assign_group_by_size``, ``pdb200_reducer_*`` in csrc/runtime/reducer.cc); this module does
+the tensor work and issues the collectives.  A Python mirror of the bookkeeping serves builds without the library.
 
 Sparse gradients (``Embedding(sparse=True)``; reference AllReduceSparse :1129-1350) live in singleton buckets and are
 reduced by gathering every rank's (row ids, values) and coalescing them - the dense bucket machinery never sees them.
@@ -131,6 +134,16 @@ class EagerReducer:
             for i, p in enumerate(b.params):
                 self._where[id(p)] = (b, i)
         self._index_of = {id(p): i for i, p in enumerate(self.params)}
+        self._core = None
+        if lib.runtime.available() and hasattr(lib.runtime.require(), "pdb200_reducer_create"):
+            n = len(self.params)
+            bucket_of = (ctypes.c_int32 * max(n, 1))(*[self._where[id(p)][0].index for p in self.params])
+            sparse_b = (ctypes.c_uint8 * max(len(self.buckets), 1))(*[int(b.sparse) for b in self.buckets])
+            self._core = lib.runtime.pdb200_reducer_create(ctypes.cast(bucket_of, ctypes.c_void_p), n,
+                                                           ctypes.cast(sparse_b, ctypes.c_void_p), len(self.buckets))
+            self._launch_buf = (ctypes.c_int32 * max(len(self.buckets), 1))()
+            self._missing_buf = (ctypes.c_int32 * max(n, 1))()
+            self._n_launch = ctypes.c_int32(0)
         self._used_task = None
         self._used_bitmap = None
         self.next_bucket = 0
@@ -143,6 +156,8 @@ class EagerReducer:
         self._armed = True
         self._callback_queued = False
         self.next_bucket = 0
+        if self._core:
+            lib.runtime.pdb200_reducer_prepare(self._core)
         for b in self.buckets:
             b.pending = len(b.params)
             b.ready = False
@@ -158,6 +173,8 @@ class EagerReducer:
 
     @torch.no_grad()
     def _mark_ready(self, p):
+        if self._core:
+            return self._mark_ready_native(p)
         b, i = self._where[id(p)]
         if id(p) in b.marked:
             return
@@ -184,6 +201,34 @@ class EagerReducer:
         if b.pending == 0:
             b.ready = True
             self._launch_ready()
+
+    def _adopt(self, b, i, p):
+        """The gradient of p lives in (or moves into) its slot of the bucket buffer."""
+        view = b.view(i)
+        g = p.grad
+        if g is not None and g.data_ptr() != view.data_ptr():
+            view.copy_(g)
+            p.grad = view          # from now on autograd accumulates into the bucket directly
+        elif g is None:
+            view.zero_()
+
+    def _mark_ready_native(self, p):
+        b, i = self._where[id(p)]
+        if id(p) not in b.marked and not b.sparse:
+            self._adopt(b, i, p)                          # before the core may release the bucket
+        n = lib.runtime.pdb200_reducer_mark_ready(self._core, self._index_of[id(p)],
+                                                  ctypes.cast(self._launch_buf, ctypes.c_void_p), len(self.buckets))
+        if n < 0:
+            return                                        # not armed, or marked before in this iteration
+        b.marked.add(id(p))
+        if not self._callback_queued:
+            self._callback_queued = True
+            torch.autograd.Variable._execution_engine.queue_callback(self.finalize_backward)
+        for k in range(n):
+            bk = self.buckets[self._launch_buf[k]]
+            bk.ready = True
+            bk.task = self._all_reduce(bk)
+            self.next_bucket = bk.index + 1
 
     def _launch_ready(self):
         while self.next_bucket < len(self.buckets) and self.buckets[self.next_bucket].ready:
@@ -242,9 +287,51 @@ class EagerReducer:
         return used
 
     @torch.no_grad()
+    def _finalize_native(self):
+        n_params = len(self.params)
+        missing = lib.runtime.pdb200_reducer_finalize(self._core, int(self.find_unused),
+                                                      ctypes.cast(self._missing_buf, ctypes.c_void_p), n_params,
+                                                      ctypes.cast(self._launch_buf, ctypes.c_void_p), len(self.buckets),
+                                                      ctypes.byref(self._n_launch))
+        if missing and not self.find_unused:
+            names = [self.params[self._missing_buf[k]].name for k in range(min(missing, 4))]
+            self._armed = False
+            raise RuntimeError(
+                "DataParallel: some parameters did not receive a gradient in this backward "
+                f"({names}...). Construct DataParallel with find_unused_parameters=True.")
+        for k in range(min(missing, n_params)):           # unused here: zeros take part in the reduction
+            p = self.params[self._missing_buf[k]]
+            b, i = self._where[id(p)]
+            if not b.sparse:
+                b.view(i).zero_()
+                p.grad = b.view(i)
+        for k in range(self._n_launch.value):
+            bk = self.buckets[self._launch_buf[k]]
+            bk.ready = True
+            bk.task = self._all_reduce(bk)
+            self.next_bucket = bk.index + 1
+        globally_unused = []
+        if self.find_unused:
+            used = (ctypes.c_int32 * max(n_params, 1))()
+            lib.runtime.pdb200_reducer_used_bitmap(self._core, ctypes.cast(used, ctypes.c_void_p))
+            bitmap = torch.tensor(list(used)[:n_params], dtype=torch.int32, device=self.params[0].device)
+            comm.all_reduce(bitmap, op=ReduceOp.MAX, group=self.group)
+            self._used_bitmap = bitmap
+            globally_unused = [self.params[i] for i, u in enumerate(bitmap.tolist()) if not u]
+        for b in self.buckets:
+            if b.task is not None:
+                b.task.wait()
+                b.task = None
+        for p in globally_unused:            # nobody produced a gradient for it: keep "no gradient", not zeros
+            p.grad = None
+        self._armed = False
+
+    @torch.no_grad()
     def finalize_backward(self):
         if not self._armed:
             return
+        if self._core:
+            return self._finalize_native()
         globally_unused = []
         # buckets that never became ready hold unused parameters
         for b in self.buckets[self.next_bucket:]:
@@ -282,3 +369,11 @@ class EagerReducer:
         for h in self._hooks:
             h.remove()
         self._hooks = []
+
+    def __del__(self):
+        core, self._core = getattr(self, "_core", None), None
+        if core:
+            try:
+                lib.runtime.pdb200_reducer_destroy(core)
+            except Exception:  # noqa: BLE001  (interpreter shutdown)
+                pass

@@ -21,6 +21,7 @@ _CTYPES = {
     "int*": ctypes.c_void_p, "const int*": ctypes.c_void_p,
     "int32_t*": ctypes.c_void_p, "const int32_t*": ctypes.c_void_p,
     "uint64_t*": ctypes.c_void_p, "const uint64_t*": ctypes.c_void_p,
+    "uint8_t*": ctypes.c_void_p, "const uint8_t*": ctypes.c_void_p,
     "char*": ctypes.c_char_p, "const char*": ctypes.c_char_p,
     "int": ctypes.c_int, "int64_t": ctypes.c_int64, "uint64_t": ctypes.c_uint64, "float": ctypes.c_float,
     "double": ctypes.c_double, "void": None,

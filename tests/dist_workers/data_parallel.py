@@ -109,6 +109,9 @@ with paddle.utils.unique_name.guard():
 ed.set_state_dict(es.state_dict())
 ds, dd = paddle.DataParallel(es), paddle.DataParallel(ed)
 assert any(b.sparse for b in ds._reducer.buckets)
+from paddle_b200 import lib as _lib
+if _lib.runtime.available() and hasattr(_lib.runtime.require(), "pdb200_reducer_create"):
+    assert ds._reducer._core, "the reducer's bookkeeping must run in libpdb200_runtime.so when it is built"
 ids = torch.tensor([[1, 7, 7], [3 + r, 9, 1]])
 ds(ids).backward()
 dd(ids).backward()

@@ -119,3 +119,44 @@ def test_arena_heap_best_fit_coalesce_and_determinism():
         return seq, stats
 
     assert run() == run()
+
+
+def test_reducer_core_releases_buckets_in_order_and_reports_unused():
+    """csrc/runtime/reducer.cc: gradients arrive in any order, buckets are released strictly in bucket order."""
+    import ctypes
+    rt = lib.runtime.require()
+    # 5 parameters: bucket 0 = {0, 1}, bucket 1 = {2} (sparse), bucket 2 = {3, 4}
+    bucket_of = (ctypes.c_int32 * 5)(0, 0, 1, 2, 2)
+    sparse = (ctypes.c_uint8 * 3)(0, 1, 0)
+    h = rt.pdb200_reducer_create(ctypes.cast(bucket_of, ctypes.c_void_p), 5, ctypes.cast(sparse, ctypes.c_void_p), 3)
+    assert h
+    out = (ctypes.c_int32 * 3)()
+    miss = (ctypes.c_int32 * 5)()
+    nl = ctypes.c_int32(0)
+
+    def mark(p):
+        n = rt.pdb200_reducer_mark_ready(h, p, ctypes.cast(out, ctypes.c_void_p), 3)
+        return n if n < 0 else list(out)[:n]
+
+    assert mark(0) == -1                                  # not armed yet
+    rt.pdb200_reducer_prepare(h)
+    assert mark(4) == [] and mark(3) == []                # bucket 2 is full but buckets 0 and 1 come first
+    assert mark(2) == []                                  # the sparse bucket is ready at once, still behind bucket 0
+    assert mark(0) == [] and mark(0) == -1                # second mark of the same parameter is refused
+    assert mark(1) == [0, 1, 2]                           # everything is released, in order
+    assert rt.pdb200_reducer_finalize(h, 0, ctypes.cast(miss, ctypes.c_void_p), 5, ctypes.cast(out, ctypes.c_void_p), 3,
+                                      ctypes.byref(nl)) == 0 and nl.value == 0
+    # an iteration where parameter 1 stays unused
+    rt.pdb200_reducer_prepare(h)
+    assert mark(0) == [] and mark(3) == [] and mark(4) == [] and mark(2) == []
+    n = rt.pdb200_reducer_finalize(h, 0, ctypes.cast(miss, ctypes.c_void_p), 5, ctypes.cast(out, ctypes.c_void_p), 3, ctypes.byref(nl))
+    assert n == 1 and miss[0] == 1 and nl.value == 0      # not tolerated: reported, nothing released
+    rt.pdb200_reducer_prepare(h)
+    for p in (0, 3, 4, 2):
+        mark(p)
+    n = rt.pdb200_reducer_finalize(h, 1, ctypes.cast(miss, ctypes.c_void_p), 5, ctypes.cast(out, ctypes.c_void_p), 3, ctypes.byref(nl))
+    assert n == 1 and miss[0] == 1 and list(out)[:nl.value] == [0, 1, 2]
+    used = (ctypes.c_int32 * 5)()
+    rt.pdb200_reducer_used_bitmap(h, ctypes.cast(used, ctypes.c_void_p))
+    assert list(used) == [1, 0, 1, 1, 1]
+    rt.pdb200_reducer_destroy(h)
