@@ -384,156 +384,154 @@ class PipelineParallel(MetaParallelBase):
         raise RuntimeError("call train_batch / eval_batch on a PipelineParallel model")
 
 
+def interleave_slots(num_stages, num_chunks, acc_steps, stage, mode="1f1b", forward_only=False):
+    """The schedule of ONE pipeline stage with virtual stages, as a table.
+
+    Work is counted in virtual micro-steps k = 0 .. acc_steps * num_chunks - 1.  Forward k runs model chunk
+    (k mod (P V)) div P, backward k runs the mirror chunk V - 1 - that: micro-batches travel through the chunks in
+    groups of P, and gradients come back through the chunks in reverse.  A slot is ``(forward step or None, backward
+    step or None)``:
+      * warm-up  - forward-only slots.  Stage s must be 2 (P - s - 1) forwards ahead of its first backward (the usual
+        1F1B lead, doubled because the gradient of a group returns only after the later stages have also run it) plus
+        (V - 1) P for the earlier chunks of the first groups;
+      * steady   - one forward and one backward per slot;
+      * cool-down - the remaining backwards.
+    "fthenb" is all warm-up followed by all cool-down; ``forward_only`` keeps the forward slots.
+    (Reference schedule: fleet/meta_parallel/pipeline_parallel.py:1010-1828 interleave, :1831-2060 FthenB.)"""
+    P, V = num_stages, num_chunks
+    total = acc_steps * V
+    if forward_only or mode == "fthenb":
+        lead = total
+    else:
+        lead = min(2 * (P - stage - 1) + (V - 1) * P, total)
+    slots = [(k, None) for k in range(lead)]
+    slots += [(lead + i, i) for i in range(total - lead)]
+    if not forward_only:
+        slots += [(None, i) for i in range(total - lead, total)]
+    return slots
+
+
 class PipelineParallelWithInterleave(PipelineParallel):
-    """Interleaved 1F1B with virtual stages (reference :1010-1828); requires accumulate_steps % pp == 0."""
+    """Interleaved 1F1B with virtual stages; requires accumulate_steps % pp == 0.
+
+    The schedule is data (``interleave_slots``); ``_run_slots`` executes any such table with one rule for the
+    communication: after a slot's compute, send what the slot produced (an activation unless the forward ran the last
+    virtual stage, an input gradient unless the backward ran the first one) and receive what the NEXT slot will
+    consume (an activation unless its forward is the first virtual stage, an output gradient unless its backward is the
+    last one) - in one fused p2p call.  Every stage derives the same pairing of sends and receives from its own table."""
+
+    schedule_mode = "1f1b"
 
     def __init__(self, layers, hcg, strategy):
         super().__init__(layers, hcg, strategy)
         assert layers.get_num_virtual_stages() > 1
-        assert self.num_stages > 2 or True
         self.num_model_chunks = layers.get_num_virtual_stages()
         self.model_chunks = layers.get_model_chunks()
         assert self.model_chunks is not None and len(self.model_chunks) == self.num_model_chunks
         self._virtual_pp_world_size = self.num_model_chunks
         self._virtual_pp_rank = 0
-        self._reset_counter()
 
-    def _reset_counter(self):
-        self._forward_micro_step_counter = {}
-        self._backward_micro_step_counter = {}
+    # ---- the geometry of a virtual micro-step
+    def _chunk_of(self, k, forward):
+        c = (k % (self.num_stages * self.num_model_chunks)) // self.num_stages
+        return c if forward else self.num_model_chunks - 1 - c
 
-    def _get_virtual_pp_rank(self, micro_step, forward):
-        group = self.num_stages * self.num_model_chunks
-        in_group = micro_step % group
-        vpp = in_group // self.num_stages
-        return vpp if forward else self.num_model_chunks - vpp - 1
+    _get_virtual_pp_rank = _chunk_of          # the reference's name for it
 
-    def _forward_step_helper(self, micro_dataset, micro_step):
-        vpp = self._get_virtual_pp_rank(micro_step, True)
-        self.set_virtual_pipeline_rank(vpp)
-        if self.is_pipeline_first_stage():
-            if len(self.input_tensors[vpp]) == len(self.output_tensors[vpp]):
-                self.input_tensors[vpp].append(None)
-        input_tensor = self.input_tensors[vpp][-1]
-        output_tensor = self._forward_step(input_tensor, micro_dataset[vpp], vpp)
-        self.output_tensors[vpp].append(output_tensor)
-        if self._forward_only:
-            self.input_tensors[vpp].pop()
-            self.output_tensors[vpp].pop()
-        return output_tensor
+    def _is_first_virtual(self, chunk):
+        return self.is_pipeline_first_stage_ and chunk == 0
 
-    def _backward_step_helper(self, micro_step):
-        vpp = self._get_virtual_pp_rank(micro_step, False)
-        self.set_virtual_pipeline_rank(vpp)
-        if self.is_pipeline_last_stage():
-            if len(self.output_tensor_grads[vpp]) == 0:
-                self.output_tensor_grads[vpp].append(None)
-        input_tensor = self.input_tensors[vpp].pop(0)
-        output_tensor = self.output_tensors[vpp].pop(0)
-        output_tensor_grad = self.output_tensor_grads[vpp].pop(0)
-        return self._backward_step(input_tensor, output_tensor, output_tensor_grad)
+    def _is_last_virtual(self, chunk):
+        return self.is_pipeline_last_stage_ and chunk == self.num_model_chunks - 1
 
     def _wrap_data_v(self, data):
         return [FakeMicroDataset(data, self.is_pipeline_first_stage_, self.is_pipeline_last_stage_, self.accumulate_steps,
                                  self.micro_batch_size) for _ in range(self.num_model_chunks)]
 
+    def _describe(self, slots):
+        out = []
+        for f, b in slots:
+            if f is not None:
+                out.append(f"f{f}_vp{self._chunk_of(f, True)}")
+            if b is not None:
+                out.append(f"b{b}_vp{self._chunk_of(b, False)}")
+        return ";".join(out) + ";"
+
+    def _run_slots(self, slots, micro_dataset, forward_only, split_turn=False):
+        """Execute a slot table.  ``split_turn``: where a forward-only slot is followed by a backward-only one, the
+        gradient is received in a call of its own instead of riding on the forward exchange (FthenB)."""
+        V = self.num_model_chunks
+        helper = self._p2p_helper
+        acts_in = [[] for _ in range(V)]        # per chunk: inputs waiting for (or kept since) their forward
+        acts_out = [[] for _ in range(V)]       # per chunk: outputs kept for their backward
+        grads_in = [[] for _ in range(V)]       # per chunk: output gradients waiting for their backward
+        self.input_tensors, self.output_tensors, self.output_tensor_grads = acts_in, acts_out, grads_in
+
+        def wants_act(slot):
+            return slot is not None and slot[0] is not None and not self._is_first_virtual(self._chunk_of(slot[0], True))
+
+        def wants_grad(slot):
+            return slot is not None and slot[1] is not None and not self._is_last_virtual(self._chunk_of(slot[1], False))
+
+        first = slots[0] if slots else None
+        if first is not None and first[0] is not None:
+            self.set_virtual_pipeline_rank(self._chunk_of(first[0], True))
+            acts_in[self._chunk_of(first[0], True)].append(helper.recv_forward(not wants_act(first)))
+        for idx, (f, b) in enumerate(slots):
+            nxt = slots[idx + 1] if idx + 1 < len(slots) else None
+            send_act = send_grad = None
+            if f is not None:
+                c = self._chunk_of(f, True)
+                self.set_virtual_pipeline_rank(c)
+                if len(acts_in[c]) == len(acts_out[c]):          # first virtual stage: nothing was received for it
+                    acts_in[c].append(None)
+                out = self._forward_step(acts_in[c][-1], micro_dataset[c], c)
+                acts_out[c].append(out)
+                if forward_only:
+                    acts_in[c].pop()
+                    acts_out[c].pop()
+                send_act = None if self._is_last_virtual(c) else out
+            if b is not None:
+                c = self._chunk_of(b, False)
+                self.set_virtual_pipeline_rank(c)
+                if not grads_in[c]:                              # last virtual stage: the loss starts the gradient
+                    grads_in[c].append(None)
+                gin = self._backward_step(acts_in[c].pop(0), acts_out[c].pop(0), grads_in[c].pop(0))
+                send_grad = None if self._is_first_virtual(c) else gin
+            recv_prev, recv_next = wants_act(nxt), wants_grad(nxt)
+            turn = split_turn and b is None and nxt is not None and nxt[0] is None
+            if b is None and (nxt is None or nxt[1] is None or turn):
+                got_act, got_grad = helper.send_forward_recv_forward(send_act, recv_prev=recv_prev), None
+                if turn:
+                    c = self._chunk_of(nxt[1], False)
+                    self.set_virtual_pipeline_rank(c)
+                    got_grad = helper.recv_backward(not recv_next)
+            elif f is None:
+                got_act, got_grad = None, helper.send_backward_recv_backward(send_grad, recv_next=recv_next)
+            else:
+                got_act, got_grad = helper.send_forward_backward_recv_forward_backward(
+                    send_act, send_grad, recv_prev=recv_prev, recv_next=recv_next)
+            if recv_prev:
+                acts_in[self._chunk_of(nxt[0], True)].append(got_act)
+            if recv_next:
+                grads_in[self._chunk_of(nxt[1], False)].append(got_grad)
+
     def forward_backward_pipeline(self, data, scaler=None, forward_only=False, compute_loss=True, static_scheduler=False,
                                   return_micro_batch_loss=False):
-        assert self.accumulate_steps % self.num_stages == 0 or forward_only, \
-            "accumulate_steps should be evenly divisible by num_stages for pipeline with interleave"
+        if self.schedule_mode == "1f1b":
+            assert self.accumulate_steps % self.num_stages == 0 or forward_only, \
+                "accumulate_steps should be evenly divisible by num_stages for pipeline with interleave"
         self._forward_only = forward_only
         self._compute_loss = compute_loss
         self.scaler = scaler
         self.total_loss = None
         self.micro_batch_id = 0
-        num_steps = self.accumulate_steps * self.num_model_chunks
-        if forward_only:
-            startup_steps = num_steps
-        else:
-            startup_steps = (self.num_stages - self.stage_id - 1) * 2 + (self.num_model_chunks - 1) * self.num_stages
-            startup_steps = min(startup_steps, num_steps)
-        steady_steps = num_steps - startup_steps
+        slots = interleave_slots(self.num_stages, self.num_model_chunks, self.accumulate_steps, self.stage_id,
+                                 self.schedule_mode, forward_only)
         if static_scheduler:
-            s = ""
-            for i in range(startup_steps):
-                s += f"f{i % self.accumulate_steps if False else i}_vp{self._get_virtual_pp_rank(i, True)};"
-            for i in range(steady_steps):
-                s += f"f{startup_steps + i}_vp{self._get_virtual_pp_rank(startup_steps + i, True)};"
-                s += f"b{i}_vp{self._get_virtual_pp_rank(i, False)};"
-            for i in range(steady_steps, num_steps):
-                s += f"b{i}_vp{self._get_virtual_pp_rank(i, False)};"
-            return s
-        micro_dataset = self._wrap_data_v(data)
-        self.input_tensors = [[] for _ in range(self.num_model_chunks)]
-        self.output_tensors = [[] for _ in range(self.num_model_chunks)]
-        self.output_tensor_grads = [[] for _ in range(self.num_model_chunks)]
-        helper = self._p2p_helper
-        self.set_virtual_pipeline_rank(0)
-        self.input_tensors[0].append(helper.recv_forward(self.is_pipeline_first_stage()))
-        for micro_step in range(startup_steps):
-            output_tensor = self._forward_step_helper(micro_dataset, micro_step)
-            next_vpp = self._get_virtual_pp_rank(micro_step + 1, True)
-            recv_prev = True
-            if self.is_pipeline_first_stage(ignore_virtual=True) and next_vpp == 0:
-                recv_prev = False
-            if micro_step == num_steps - 1:
-                recv_prev = False
-            if self.is_pipeline_last_stage():
-                output_tensor = None
-            if micro_step == startup_steps - 1 and not forward_only:
-                input_tensor_grad = None
-                recv_next = not self.is_pipeline_last_stage(ignore_virtual=True)
-                input_tensor, out_grad = helper.send_forward_backward_recv_forward_backward(
-                    output_tensor, input_tensor_grad, recv_prev=recv_prev, recv_next=recv_next)
-                self.output_tensor_grads[self.num_model_chunks - 1].append(out_grad)
-            else:
-                input_tensor = helper.send_forward_recv_forward(output_tensor, recv_prev=recv_prev)
-            if recv_prev:
-                self.input_tensors[next_vpp].append(input_tensor)
-        for micro_step in range(steady_steps):
-            fwd_id = micro_step + startup_steps
-            output_tensor = self._forward_step_helper(micro_dataset, fwd_id)
-            input_tensor_grad = self._backward_step_helper(micro_step)
-            fwd_vpp = self._get_virtual_pp_rank(fwd_id, True)
-            self.set_virtual_pipeline_rank(fwd_vpp)
-            if self.is_pipeline_last_stage():
-                output_tensor = None
-            bwd_vpp = self._get_virtual_pp_rank(micro_step, False)
-            self.set_virtual_pipeline_rank(bwd_vpp)
-            if self.is_pipeline_first_stage():
-                input_tensor_grad = None
-            recv_prev = True
-            next_fwd_vpp = self._get_virtual_pp_rank(fwd_id + 1, True)
-            if self.is_pipeline_first_stage(ignore_virtual=True) and next_fwd_vpp == 0:
-                recv_prev = False
-            if micro_step == steady_steps - 1:
-                recv_prev = False
-            recv_next = True
-            next_bwd_vpp = self._get_virtual_pp_rank(micro_step + 1, False)
-            if self.is_pipeline_last_stage(ignore_virtual=True) and next_bwd_vpp == self.num_model_chunks - 1:
-                recv_next = False
-            input_tensor, out_grad = helper.send_forward_backward_recv_forward_backward(
-                output_tensor, input_tensor_grad, recv_prev=recv_prev, recv_next=recv_next)
-            if recv_prev:
-                self.input_tensors[next_fwd_vpp].append(input_tensor)
-            if recv_next:
-                self.output_tensor_grads[next_bwd_vpp].append(out_grad)
+            return self._describe(slots)
+        self._run_slots(slots, self._wrap_data_v(data), forward_only, split_turn=self.schedule_mode == "fthenb")
         if not forward_only:
-            for micro_step in range(steady_steps, num_steps):
-                input_tensor_grad = self._backward_step_helper(micro_step)
-                next_bwd_vpp = self._get_virtual_pp_rank(micro_step + 1, False)
-                recv_next = True
-                if self.is_pipeline_last_stage(ignore_virtual=True) and next_bwd_vpp == self.num_model_chunks - 1:
-                    recv_next = False
-                if micro_step == num_steps - 1:
-                    recv_next = False
-                bwd_vpp = self._get_virtual_pp_rank(micro_step, False)
-                self.set_virtual_pipeline_rank(bwd_vpp)
-                if self.is_pipeline_first_stage():
-                    input_tensor_grad = None
-                g = helper.send_backward_recv_backward(input_tensor_grad, recv_next=recv_next)
-                if recv_next:
-                    self.output_tensor_grads[next_bwd_vpp].append(g)
             self._layers.allreduce_shared_weight_gradients()
         if compute_loss:
             with torch.no_grad():
@@ -541,7 +539,7 @@ class PipelineParallelWithInterleave(PipelineParallel):
         else:
             train_loss = self.output_tensors
         if self._clear_every_step_cache:
-            helper.clear_meta_cache()
+            self._p2p_helper.clear_meta_cache()
         return train_loss
 
     def train_batch(self, data, optimizer, lr_scheduler=None, scaler=None, loss_fn_idx=0, return_micro_batch_loss=False):
@@ -562,59 +560,7 @@ class PipelineParallelWithInterleave(PipelineParallel):
 
 
 class PipelineParallelWithInterleaveFthenB(PipelineParallelWithInterleave):
-    """All forwards of every chunk, then all backwards (reference :1831-2060), for pp <= acc < 2 pp."""
+    """All forwards of every chunk, then all backwards, for pp <= accumulate_steps < 2 pp: the same executor on the
+    ``"fthenb"`` table."""
 
-    def forward_backward_pipeline(self, data, scaler=None, forward_only=False, compute_loss=True, static_scheduler=False,
-                                  return_micro_batch_loss=False):
-        self._forward_only = forward_only
-        self._compute_loss = compute_loss
-        self.scaler = scaler
-        self.total_loss = None
-        self.micro_batch_id = 0
-        num_steps = self.accumulate_steps * self.num_model_chunks
-        if static_scheduler:
-            return "".join(f"f{i};" for i in range(num_steps)) + "".join(f"b{i};" for i in range(num_steps))
-        micro_dataset = self._wrap_data_v(data)
-        self.input_tensors = [[] for _ in range(self.num_model_chunks)]
-        self.output_tensors = [[] for _ in range(self.num_model_chunks)]
-        self.output_tensor_grads = [[] for _ in range(self.num_model_chunks)]
-        helper = self._p2p_helper
-        self.set_virtual_pipeline_rank(0)
-        self.input_tensors[0].append(helper.recv_forward(self.is_pipeline_first_stage()))
-        for micro_step in range(num_steps):
-            output_tensor = self._forward_step_helper(micro_dataset, micro_step)
-            next_vpp = self._get_virtual_pp_rank(micro_step + 1, True)
-            recv_prev = True
-            if self.is_pipeline_first_stage(ignore_virtual=True) and next_vpp == 0:
-                recv_prev = False
-            if micro_step == num_steps - 1:
-                recv_prev = False
-            if self.is_pipeline_last_stage():
-                output_tensor = None
-            input_tensor = helper.send_forward_recv_forward(output_tensor, recv_prev=recv_prev)
-            if recv_prev:
-                self.input_tensors[next_vpp].append(input_tensor)
-        if not forward_only:
-            self.set_virtual_pipeline_rank(self.num_model_chunks - 1)
-            self.output_tensor_grads[self.num_model_chunks - 1].append(
-                helper.recv_backward(self.is_pipeline_last_stage()))
-            for micro_step in range(num_steps):
-                input_tensor_grad = self._backward_step_helper(micro_step)
-                next_bwd_vpp = self._get_virtual_pp_rank(micro_step + 1, False)
-                recv_next = True
-                if self.is_pipeline_last_stage(ignore_virtual=True) and next_bwd_vpp == self.num_model_chunks - 1:
-                    recv_next = False
-                if micro_step == num_steps - 1:
-                    recv_next = False
-                bwd_vpp = self._get_virtual_pp_rank(micro_step, False)
-                self.set_virtual_pipeline_rank(bwd_vpp)
-                if self.is_pipeline_first_stage():
-                    input_tensor_grad = None
-                g = helper.send_backward_recv_backward(input_tensor_grad, recv_next=recv_next)
-                if recv_next:
-                    self.output_tensor_grads[next_bwd_vpp].append(g)
-            self._layers.allreduce_shared_weight_gradients()
-        if compute_loss:
-            with torch.no_grad():
-                return self._broadcast_final_loss(return_micro_batch_loss)
-        return self.output_tensors
+    schedule_mode = "fthenb"

@@ -291,3 +291,26 @@ def test_incubate_namespace():
     assert inn.FusedEcMoe(16, 32, 4, "gelu")(torch.randn(2, 3, 16), torch.randn(2, 3, 4)).shape == (2, 3, 16)
     y = inn.functional.fused_bias_dropout_residual_layer_norm(torch.randn(2, 8), torch.randn(2, 8), dropout_rate=0.0)
     torch.testing.assert_close(y.mean(-1), torch.zeros(2), atol=1e-5, rtol=0)
+
+
+def test_interleaved_pipeline_schedule_table():
+    """The virtual-stage schedule is a table: every forward / backward micro-step appears exactly once per stage, a
+    backward never precedes its forward, the warm-up lead shrinks towards the last stage, and the stages' tables pair up
+    (what stage s sends after a slot is what stage s+1 receives for a slot of its own)."""
+    from paddle_b200.distributed.fleet.meta_parallel.pipeline_parallel import interleave_slots
+    for P, V, acc in ((2, 2, 2), (4, 2, 8), (4, 3, 8), (3, 2, 6)):
+        total = acc * V
+        leads = []
+        for s in range(P):
+            slots = interleave_slots(P, V, acc, s)
+            fs = [f for f, _ in slots if f is not None]
+            bs = [b for _, b in slots if b is not None]
+            assert fs == list(range(total)) and bs == list(range(total))
+            pos_f = {f: i for i, (f, _) in enumerate(slots) if f is not None}
+            pos_b = {b: i for i, (_, b) in enumerate(slots) if b is not None}
+            assert all(pos_b[k] >= pos_f[k] for k in range(total))
+            leads.append(next(i for i, (_, b) in enumerate(slots) if b is not None))
+        assert leads == sorted(leads, reverse=True) and leads[-1] == min((V - 1) * P, total)
+        ftb = interleave_slots(P, V, acc, 0, mode="fthenb")
+        assert [f for f, b in ftb[:total]] == list(range(total)) and all(b is None for _, b in ftb[:total])
+        assert interleave_slots(P, V, acc, 1, forward_only=True) == [(k, None) for k in range(total)]
