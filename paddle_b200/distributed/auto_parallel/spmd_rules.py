@@ -279,6 +279,16 @@ def fused_rope(q, k=None, v=None):
     return ins, [DistTensorSpec(s.shape, s.dims_mapping) for s in ins]
 
 
+def qkv_split_rope(qkv, num_q_heads=1, num_kv_heads=1):
+    """Packed projection [b, s, (hq + 2 hk) d] -> q [b, s, hq, d], k, v [b, s, hk, d]: the packed dim mixes q, k and v, so
+    it must be whole; batch and sequence shardings pass through (the rotary tables are indexed by position ids)."""
+    d = qkv.shape[-1] // (num_q_heads + 2 * num_kv_heads)
+    dm = list(qkv.dims_mapping[:-1]) + [-1]
+    lead = tuple(qkv.shape[:-1])
+    outs = [DistTensorSpec(lead + (h, d), dm[:-1] + [-1, -1]) for h in (num_q_heads, num_kv_heads, num_kv_heads)]
+    return [DistTensorSpec(qkv.shape, dm)], outs
+
+
 def swiglu(x, y=None):
     if y is None:
         dm = x.dims_mapping[:-1] + [-1]          # the packed gate|up dim must be whole to be split in halves
@@ -298,7 +308,8 @@ _RULES = {"matmul": matmul, "elementwise": elementwise, "add": elementwise, "sub
           "reduction": reduction, "embedding": embedding, "layer_norm": layer_norm, "rms_norm": rms_norm,
           "softmax": softmax, "cross_entropy_with_softmax": cross_entropy_with_softmax, "transpose": transpose,
           "reshape": reshape, "concat": concat, "split": split, "flash_attention": flash_attention,
-          "fused_rotary_position_embedding": fused_rope, "swiglu": swiglu, "default": replicated}
+          "fused_rotary_position_embedding": fused_rope, "swiglu": swiglu, "qkv_split_rope": qkv_split_rope,
+          "default": replicated}
 
 
 def get_spmd_rule(op_name):

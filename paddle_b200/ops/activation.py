@@ -95,6 +95,9 @@ class _SwigluPackedFn(torch.autograd.Function):
 
 
 def swiglu(x, y=None):
+    if hasattr(x, "placements") or hasattr(y, "placements"):
+        from ..distributed.auto_parallel import dtensor as D
+        return D.run_rule("swiglu", (lambda a: swiglu(a)) if y is None else (lambda a, b: swiglu(a, b)), [x] if y is None else [x, y])
     if y is None:
         if use_native(x) and x.shape[-1] % 2 == 0 and (x.shape[-1] // 2 * x.element_size()) % 16 == 0:
             return _SwigluPackedFn.apply(x)

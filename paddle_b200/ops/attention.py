@@ -145,6 +145,15 @@ def _sdpa(q, k, v, causal, scale, dropout, mask, training):
 
 def flash_attention(q, k, v, dropout=0.0, causal=False, softmax_scale=None, attn_mask=None, training=True,
                     return_lse=False, fixed_seed_offset=None):
+    if hasattr(q, "placements") or hasattr(k, "placements") or hasattr(v, "placements"):
+        # distributed tensors (auto_parallel): batch and heads may stay sharded, the rule gathers the rest
+        from ..distributed.auto_parallel import dtensor as D
+        if attn_mask is not None and hasattr(attn_mask, "placements"):
+            attn_mask = D.replicate_all((attn_mask,), {})[0][0]
+        out = D.run_rule("flash_attention",
+                         lambda a, b, c: flash_attention(a, b, c, dropout, causal, softmax_scale, attn_mask, training, True,
+                                                         fixed_seed_offset), [q, k, v])
+        return out if return_lse else out[0]
     scale = softmax_scale if softmax_scale is not None else 1.0 / math.sqrt(q.shape[-1])
     p_drop = float(dropout) if training else 0.0
     if _native_ok(q, k, v, p_drop, attn_mask):

@@ -37,6 +37,11 @@ class _SoftmaxCEFn(torch.autograd.Function):
 
 def softmax_cross_entropy(logits, labels, ignore_index=-100):
     """Per-row loss (fp32), shape = labels.shape; rows whose label == ignore_index give 0."""
+    if hasattr(logits, "placements") or hasattr(labels, "placements"):
+        from ..distributed.auto_parallel import dtensor as D
+        V = logits.shape[-1]
+        flat = D._TABLE[TF.cross_entropy](logits.reshape(-1, V), labels.reshape(-1), ignore_index=ignore_index, reduction="none")
+        return flat.reshape(*labels._global_shape) if hasattr(labels, "_global_shape") else flat.reshape(labels.shape)
     if use_native(logits):
         return _SoftmaxCEFn.apply(logits, labels, ignore_index)
     V = logits.shape[-1]

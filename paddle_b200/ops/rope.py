@@ -117,6 +117,11 @@ class _QKVRopeFn(torch.autograd.Function):
 def qkv_split_rope(qkv, num_q_heads, num_kv_heads, sin=None, cos=None, position_ids=None, use_neox_rotary_style=True,
                    rotary_emb_base=10000.0):
     """qkv: [b, s, (hq + 2 hk) * d] packed projection output -> (q [b,s,hq,d], k, v [b,s,hk,d]) with q/k rotated."""
+    if hasattr(qkv, "placements"):
+        from ..distributed.auto_parallel import dtensor as D
+        return D.run_rule("qkv_split_rope", lambda a: qkv_split_rope(a, num_q_heads, num_kv_heads, sin, cos, position_ids,
+                                                                     use_neox_rotary_style, rotary_emb_base),
+                          [qkv], {"num_q_heads": num_q_heads, "num_kv_heads": num_kv_heads})
     pairs = bool(use_neox_rotary_style)
     d = qkv.shape[-1] // (num_q_heads + 2 * num_kv_heads)
     if use_native(qkv):

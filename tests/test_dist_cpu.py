@@ -24,6 +24,11 @@ def test_auto_parallel_dist_tensors_train_like_single_process():
     run_dist("auto_parallel_train.py", 2)
 
 
+def test_auto_parallel_llama_matches_single_process():
+    """The repo's Llama with Megatron-style sharded parameters (shard_layer only): loss and all gradients match."""
+    run_dist("auto_parallel_llama.py", 2)
+
+
 def test_auto_parallel_2d_mesh():
     run_dist("auto_parallel_2d.py", 4)
 
