@@ -314,3 +314,53 @@ def test_interleaved_pipeline_schedule_table():
         ftb = interleave_slots(P, V, acc, 0, mode="fthenb")
         assert [f for f, b in ftb[:total]] == list(range(total)) and all(b is None for _, b in ftb[:total])
         assert interleave_slots(P, V, acc, 1, forward_only=True) == [(k, None) for k in range(total)]
+
+
+def test_jit_to_static_save_load_roundtrip(tmp_path):
+    """paddle.jit: to_static keeps layers / functions callable (and differentiable), save writes parameters + a program
+    traced through library ops, load gives a callable TranslatedLayer that follows the batch size."""
+    import paddle_b200 as paddle
+    from paddle_b200.static import InputSpec
+
+    class Net(paddle.nn.Layer):
+        def __init__(self):
+            super().__init__()
+            self.fc1 = paddle.nn.Linear(8, 16)
+            self.norm = paddle.nn.LayerNorm(16)
+            self.fc2 = paddle.nn.Linear(16, 4)
+
+        def forward(self, x):
+            h = paddle.nn.functional.gelu(self.fc1(x))
+            return self.fc2(self.norm(h)).reshape([x.shape[0], 2, 2])
+
+    paddle.seed(3)
+    net = Net()
+    x = torch.randn(5, 8)
+    ref = net(x).detach()
+    snet = paddle.jit.to_static(net, input_spec=[InputSpec([None, 8], "float32", "x")])
+    assert snet is net and isinstance(net.forward, paddle.jit.StaticFunction)
+    out = net(x)
+    torch.testing.assert_close(out.detach(), ref)
+    out.sum().backward()                                     # training through a StaticFunction is plain autograd
+    assert net.fc1.weight.grad is not None
+    assert "def forward" in net.forward.code
+    path = str(tmp_path / "m" / "net")
+    paddle.jit.save(net, path)
+    assert os.path.exists(path + ".pdiparams") and os.path.exists(path + ".pdmodel") and os.path.exists(path + ".pdmodel.json")
+    loaded = paddle.jit.load(path)
+    torch.testing.assert_close(loaded(x), ref, rtol=1e-5, atol=1e-5)
+    x3 = torch.randn(3, 8)                                   # another batch size than the traced one
+    torch.testing.assert_close(loaded(x3), net(x3).detach(), rtol=1e-5, atol=1e-5)
+    assert set(loaded.state_dict()) == set(net.state_dict())
+    net.forward.rollback()
+    assert not isinstance(net.forward, paddle.jit.StaticFunction)
+    # without shapes only the parameters are saved; calling the loaded object says so
+    paddle.jit.save(Net(), str(tmp_path / "p"))
+    only = paddle.jit.load(str(tmp_path / "p"))
+    with pytest.raises(RuntimeError):
+        only(x)
+
+    @paddle.jit.to_static
+    def f(t):
+        return t * 2
+    assert float(f(torch.tensor(2.0))) == 4.0
