@@ -544,12 +544,31 @@ class Strategy:
 
 
 class DistModel:
-    """``to_static`` result (reference: api.py DistModel).  There is no static graph here: the object drives the
-    same dygraph layer with train/eval/predict modes and an optional loss + optimizer."""
+    """``to_static`` result (reference: api.py DistModel :1900-2400).  There is no static graph here: the object drives
+    the same dygraph layer with train / eval / predict modes and applies the ``Strategy`` itself:
+      sharding        -> ``shard_optimizer`` with ShardingStage{1,2,3} over the mesh dim named "dp" (or the first one)
+      gradient_merge  -> the update runs every ``k_steps`` calls (``avg``: the accumulated gradient is the mean)
+      amp             -> forward and loss under ``paddle.amp.auto_cast`` (+ a dynamic loss scaler for float16)
+    """
 
     def __init__(self, layer, loader=None, loss=None, optimizer=None, strategy=None):
-        self._layer, self._loss, self._opt, self._strategy = layer, loss, optimizer, strategy
+        self._layer, self._loss, self._strategy = layer, loss, strategy or Strategy()
+        self._loader = loader
         self._mode = "train" if optimizer is not None and loss is not None else ("eval" if loss is not None else "predict")
+        st = self._strategy
+        self._k = max(int(st.gradient_merge.k_steps), 1) if st.gradient_merge.enable else 1
+        self._avg = bool(st.gradient_merge.avg)
+        self._calls = 0
+        self._scaler = None
+        if optimizer is not None and st.sharding.enable and not isinstance(optimizer, _ShardOptimizer):
+            mesh = next((p.process_mesh for p in layer.parameters() if is_dist(p)), get_mesh())
+            stage = {1: ShardingStage1, 2: ShardingStage2, 3: ShardingStage3}[int(st.sharding.stage)]
+            dim = "dp" if mesh is not None and "dp" in mesh.dim_names else (mesh.dim_names[0] if mesh is not None else None)
+            optimizer = shard_optimizer(optimizer, stage(dim, mesh))
+        self._opt = optimizer
+        if st.amp.enable and str(st.amp.dtype) == "float16" and optimizer is not None:
+            from paddle_b200.amp import GradScaler
+            self._scaler = shard_scaler(GradScaler(init_loss_scaling=float(st.amp.init_loss_scaling)))
 
     def train(self):
         self._mode = "train"
@@ -563,28 +582,57 @@ class DistModel:
         self._mode = "predict"
         self._layer.eval()
 
+    def _forward(self, inputs, label=None):
+        st = self._strategy
+        if st.amp.enable:
+            from paddle_b200.amp import auto_cast
+            with auto_cast(True, level=str(st.amp.level).upper(), dtype=str(st.amp.dtype)):
+                out = self._layer(*inputs)
+                return out if label is None else self._loss(out, label)
+        out = self._layer(*inputs)
+        return out if label is None else self._loss(out, label)
+
     def __call__(self, *args):
         if self._mode == "predict":
             with torch.no_grad():
-                return self._layer(*args)
+                return self._forward(args)
         *inputs, label = args
         if self._mode == "eval":
             with torch.no_grad():
-                return self._loss(self._layer(*inputs), label)
-        loss = self._loss(self._layer(*inputs), label)
-        loss.backward()
-        self._opt.step()
-        self._opt.clear_grad()
+                return self._forward(inputs, label)
+        loss = self._forward(inputs, label)
+        scaled = loss / self._k if (self._k > 1 and self._avg) else loss
+        if self._scaler is not None:
+            self._scaler.scale(scaled).backward()
+        else:
+            scaled.backward()
+        self._calls += 1
+        if self._calls % self._k == 0:
+            if self._scaler is not None:
+                self._scaler.step(self._opt)
+                self._scaler.update()
+            else:
+                self._opt.step()
+            self._opt.clear_grad()
         return loss.detach()
 
     def state_dict(self, mode="all"):
-        sd = dict(self._layer.state_dict())
+        sd = dict(self._layer.state_dict()) if mode in ("all", "param") else {}
         if mode in ("all", "opt") and self._opt is not None:
             sd.update(self._opt.state_dict())
         return sd
 
     def set_state_dict(self, sd):
-        self._layer.set_state_dict({k: v for k, v in sd.items() if k in self._layer.state_dict()})
+        own = self._layer.state_dict()
+        self._layer.set_state_dict({k: v for k, v in sd.items() if k in own})
+        if self._opt is not None:
+            rest = {k: v for k, v in sd.items() if k not in own}
+            if rest:
+                self._opt.set_state_dict(rest)
+
+    def dist_main_program(self, mode=None):
+        """There is no program object: the dygraph layer is the program."""
+        return self._layer
 
 
 def to_static(layer, loader=None, loss=None, optimizer=None, strategy=None):

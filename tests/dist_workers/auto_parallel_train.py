@@ -151,4 +151,25 @@ for (gx, gy), (bx, by) in zip(data, loader):
 close(ap.unshard_dtensor(net.fc1.weight), ref_net.fc1.weight.detach(), tol=2e-4, what="fc1.weight after 2 steps")
 close(ap.unshard_dtensor(net.fc2.weight), ref_net.fc2.weight.detach(), tol=2e-4, what="fc2.weight after 2 steps")
 close(ap.unshard_dtensor(net.norm.weight), ref_net.norm.weight.detach(), tol=2e-4, what="norm.weight after 2 steps")
+# ---- to_static / DistModel with a Strategy: gradient merge over 2 calls + sharding stage 2 of the update
+ref_net, net = build(), ap.shard_layer(build(), mesh, shard_fn)
+ref_opt = paddle.optimizer.AdamW(1e-2, parameters=ref_net.parameters())
+strategy = ap.Strategy()
+strategy.gradient_merge.enable, strategy.gradient_merge.k_steps = True, 2
+strategy.sharding.enable, strategy.sharding.stage = True, 2
+mse = lambda out, lab: ((out - lab) ** 2).mean()
+dm = ap.to_static(net, None, mse, paddle.optimizer.AdamW(1e-2, parameters=net.parameters()), strategy)
+dm.train()
+data = [(torch.randn(8, 16), torch.randn(8, 4)) for _ in range(4)]
+for i, ((gx, gy), (bx, by)) in enumerate(zip(data, ap.shard_dataloader(data, mesh, shard_dims="x"))):
+    (mse(ref_net(gx), gy) / 2).backward()
+    if i % 2 == 1:
+        ref_opt.step()
+        ref_opt.clear_grad()
+    dm(bx, by)
+close(ap.unshard_dtensor(net.fc1.weight), ref_net.fc1.weight.detach(), tol=2e-4, what="DistModel fc1.weight")
+close(ap.unshard_dtensor(net.fc2.bias), ref_net.fc2.bias.detach(), tol=2e-4, what="DistModel fc2.bias")
+dm.eval()
+close(torch.tensor(float(dm(ap.shard_tensor(data[0][0], mesh, [S(0)]), ap.shard_tensor(data[0][1], mesh, [S(0)])))),
+      mse(ref_net(data[0][0]), data[0][1]).detach(), tol=1e-4, what="DistModel eval loss")
 print("auto_parallel_train ok", r)
