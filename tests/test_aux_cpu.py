@@ -364,3 +364,66 @@ def test_jit_to_static_save_load_roundtrip(tmp_path):
     def f(t):
         return t * 2
     assert float(f(torch.tensor(2.0))) == 4.0
+
+
+def test_incubate_fused_transformer_functionals_match_plain_composition():
+    """fused_multi_head_attention / fused_feedforward / masked_multihead_attention against step-by-step torch."""
+    import paddle_b200 as paddle
+    IF = paddle.incubate.nn.functional
+    torch.manual_seed(0)
+    b, s, nh, hd = 2, 5, 2, 4
+    e = nh * hd
+    x = torch.randn(b, s, e)
+    qkv_w, qkv_b = torch.randn(3, nh, hd, e) * 0.3, torch.randn(3, nh, hd) * 0.1
+    lin_w, lin_b = torch.randn(e, e) * 0.3, torch.randn(e) * 0.1
+    ln_s, ln_b = torch.rand(e) + 0.5, torch.randn(e) * 0.1
+    mask = torch.zeros(b, 1, s, s).masked_fill(torch.ones(s, s).triu(1).bool(), -1e4)
+
+    def ref_attn(pre):
+        h = torch.nn.functional.layer_norm(x, (e,), ln_s, ln_b) if pre else x
+        qkv = (h @ qkv_w.reshape(3 * e, e).t() + qkv_b.reshape(-1)).reshape(b, s, 3, nh, hd).permute(2, 0, 3, 1, 4)
+        sc = (qkv[0] * hd ** -0.5) @ qkv[1].transpose(-1, -2) + mask
+        o = (torch.softmax(sc, -1) @ qkv[2]).transpose(1, 2).reshape(b, s, e) @ lin_w + lin_b + x
+        return o if pre else torch.nn.functional.layer_norm(o, (e,), ln_s, ln_b)
+
+    for pre in (False, True):
+        out = IF.fused_multi_head_attention(x, qkv_w, lin_w, pre_layer_norm=pre, pre_ln_scale=ln_s, pre_ln_bias=ln_b,
+                                            ln_scale=ln_s, ln_bias=ln_b, qkv_bias=qkv_b, linear_bias=lin_b, attn_mask=mask,
+                                            dropout_rate=0.0, attn_dropout_rate=0.0)
+        torch.testing.assert_close(out, ref_attn(pre), rtol=1e-4, atol=1e-4)
+    # no mask -> the flash-attention op; and the [embed, 3 embed] weight layout
+    w2 = qkv_w.reshape(3 * e, e).t().contiguous()
+    a = IF.fused_multi_head_attention(x, qkv_w, lin_w, qkv_bias=qkv_b, dropout_rate=0.0, attn_dropout_rate=0.0, ln_scale=ln_s, ln_bias=ln_b)
+    c = IF.fused_multi_head_attention(x, w2, lin_w, qkv_bias=qkv_b.reshape(-1), dropout_rate=0.0, attn_dropout_rate=0.0,
+                                      ln_scale=ln_s, ln_bias=ln_b, num_heads=nh, transpose_qkv_wb=True)
+    torch.testing.assert_close(a, c, rtol=1e-4, atol=1e-4)
+    # KV cache: the second half of a sequence against a cache of the first half == the full causal-free attention rows
+    cache = torch.zeros(2, b, nh, 0, hd)
+    o1, cache = IF.fused_multi_head_attention(x[:, :3], qkv_w, lin_w, cache_kv=cache, dropout_rate=0.0, attn_dropout_rate=0.0,
+                                              ln_scale=ln_s, ln_bias=ln_b)
+    assert cache.shape == (2, b, nh, 3, hd)
+    o2, cache = IF.fused_multi_head_attention(x[:, 3:], qkv_w, lin_w, cache_kv=cache, dropout_rate=0.0, attn_dropout_rate=0.0,
+                                              ln_scale=ln_s, ln_bias=ln_b)
+    assert cache.shape == (2, b, nh, 5, hd)
+    full = IF.fused_multi_head_attention(x, qkv_w, lin_w, dropout_rate=0.0, attn_dropout_rate=0.0, ln_scale=ln_s, ln_bias=ln_b)
+    torch.testing.assert_close(o2, full[:, 3:], rtol=1e-4, atol=1e-4)
+
+    w1, b1, w2_, b2 = torch.randn(e, 16) * 0.3, torch.randn(16) * 0.1, torch.randn(16, e) * 0.3, torch.randn(e) * 0.1
+    for pre in (False, True):
+        out = IF.fused_feedforward(x, w1, w2_, b1, b2, ln_s, ln_b, ln_s, ln_b, 0.0, 0.0, activation="gelu", pre_layer_norm=pre)
+        h = torch.nn.functional.layer_norm(x, (e,), ln_s, ln_b) if pre else x
+        ref = torch.nn.functional.gelu(h @ w1 + b1) @ w2_ + b2 + x
+        ref = ref if pre else torch.nn.functional.layer_norm(ref, (e,), ln_s, ln_b)
+        torch.testing.assert_close(out, ref, rtol=1e-4, atol=1e-4)
+
+    # decode steps with a cache == causal attention over the whole sequence
+    T = 6
+    qkv_seq = torch.randn(b, T, 3, nh, hd)
+    cache = torch.zeros(2, b, nh, 8, hd)
+    outs = []
+    for t in range(T):
+        o, cache = IF.masked_multihead_attention(qkv_seq[:, t].reshape(b, -1), cache, sequence_lengths=torch.full((b, 1), t))
+        outs.append(o)
+    q, k, v = (qkv_seq[:, :, i].transpose(1, 2) for i in range(3))
+    ref = torch.nn.functional.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(b, T, nh * hd)
+    torch.testing.assert_close(torch.stack(outs, 1), ref, rtol=1e-4, atol=1e-4)
