@@ -5,7 +5,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def run_dist(script, nproc=2, timeout=240, extra_env=None, args=()):
+def run_dist(script, nproc=2, timeout=480, extra_env=None, args=()):
     """Driver half of the worker-script pattern: launch ``script`` on ``nproc`` CPU/gloo ranks through
     paddle.distributed.launch; assertions live in the worker; only the exit code is checked here."""
     env = dict(os.environ)
