@@ -45,5 +45,16 @@ def prune_by_memory(tuner_cfg, cur, history):
     return False
 
 
+@register_prune
+def prune_by_memory_model(tuner_cfg, cur, history):
+    """The analytic estimate (cost_model.estimate_memory_gb) says the candidate cannot fit in HBM.  Needs the model
+    shape in ``model_cfg``; off unless ``tuner_cfg["use_memory_model"]`` (default on when the shape is known)."""
+    m = tuner_cfg.get("model_cfg", {})
+    if not all(k in m for k in ("hidden_size", "num_layers", "vocab_size")) or tuner_cfg.get("use_memory_model") is False:
+        return False
+    from .cost_model import HBM_GB, estimate_memory_gb
+    return estimate_memory_gb(cur, m) > float(tuner_cfg.get("max_mem_usage_gb", HBM_GB * 0.92))
+
+
 def should_prune(tuner_cfg, cur, history):
     return any(fn(tuner_cfg, cur, history) for fn in _PRUNES)

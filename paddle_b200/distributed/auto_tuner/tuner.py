@@ -13,7 +13,7 @@ import subprocess
 import sys
 
 from .recorder import HistoryRecorder
-from .search import GridSearch
+from .search import ALGOS, GridSearch  # noqa: F401
 from .utils import default_candidates
 
 
@@ -25,9 +25,10 @@ class AutoTuner:
         tuner_cfg["candidates"] = default_candidates(tuner_cfg)
         self.tuner_cfg = tuner_cfg
         algo = tuner_cfg.get("search_algo", "grid")
-        if algo != "grid":
-            raise NotImplementedError(f"search_algo {algo!r}: only grid search is implemented")
-        self.algo = GridSearch(tuner_cfg)
+        algo = algo.get("name", "grid") if isinstance(algo, dict) else algo
+        if algo not in ALGOS:
+            raise ValueError(f"search_algo {algo!r}: choose from {sorted(ALGOS)}")
+        self.algo = ALGOS[algo](tuner_cfg)
         self.recorder = HistoryRecorder(tuner_cfg.get("metric_cfg", {}).get("name", "tokens_per_second"),
                                         tuner_cfg.get("metric_cfg", {}).get("OptimizationDirection", "Maximize"))
         self.history_cfgs = self.recorder.history

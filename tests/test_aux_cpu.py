@@ -69,7 +69,7 @@ def test_auto_checkpoint_resumes(tmp_path, monkeypatch):
 def test_auto_tuner_grid_search_prunes_and_picks_best():
     from paddle_b200.distributed.auto_tuner import AutoTuner
     cfg = {"num_gpus": 8, "dp_degree": "auto", "mp_degree": "auto", "pp_degree": "auto", "sharding_degree": [1],
-           "sharding_stage": [1], "micro_batch_size": [1, 2], "use_recompute": [False],
+           "sharding_stage": [1], "micro_batch_size": [1, 2], "use_recompute": [False], "use_memory_model": False,
            "model_cfg": {"num_attention_heads": 32, "num_layers": 32, "hidden_size": 4096, "vocab_size": 32000,
                          "global_batch_size": 16}}
     tuner = AutoTuner(cfg)
@@ -427,3 +427,49 @@ def test_incubate_fused_transformer_functionals_match_plain_composition():
     q, k, v = (qkv_seq[:, :, i].transpose(1, 2) for i in range(3))
     ref = torch.nn.functional.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(b, T, nh * hd)
     torch.testing.assert_close(torch.stack(outs, 1), ref, rtol=1e-4, atol=1e-4)
+
+
+def test_auto_tuner_cost_model_and_search_algorithms():
+    from paddle_b200.distributed.auto_tuner import AutoTuner
+    from paddle_b200.distributed.auto_tuner.cost_model import estimate_memory_gb, estimate_step_ms, param_count
+    llama7b = dict(hidden_size=4096, num_layers=32, vocab_size=32000, intermediate_size=11008, num_attention_heads=32,
+                   seq_length=4096, global_batch_size=16)
+    assert abs(param_count(llama7b) / 6.74e9 - 1) < 0.02
+    base = dict(dp_degree=1, mp_degree=1, pp_degree=1, sharding_degree=8, sharding_stage=3, micro_batch_size=2, use_recompute=False)
+    whole = dict(base, sharding_degree=1, dp_degree=8)
+    # 7B with full AdamW state does not fit one 180 GB GPU unsharded with activations of 2 x 4096 tokens... it does (108 GB
+    # of state); stage 3 over 8 GPUs is far below it; 70B unsharded is far above
+    assert estimate_memory_gb(base, llama7b) < estimate_memory_gb(whole, llama7b) < 180
+    llama70b = dict(llama7b, hidden_size=8192, num_layers=80, intermediate_size=28672, num_attention_heads=64, num_key_value_heads=8)
+    assert estimate_memory_gb(whole, llama70b) > 180
+    assert estimate_step_ms(dict(base, use_recompute=True), llama7b) > estimate_step_ms(base, llama7b)
+    cfg = dict(num_gpus=8, model_cfg=llama70b, search_algo="cost_model", micro_batch_size=[1, 2], sharding_stage=[3],
+               use_recompute=[False, True], task_limit=1000)
+    tuner = AutoTuner(cfg)
+    seen = []
+    while True:
+        c = tuner.search_once()
+        if c is None:
+            break
+        assert estimate_memory_gb(c, llama70b) <= 180 * 0.92          # the memory model pruned what cannot fit
+        seen.append(estimate_step_ms(c, llama70b))
+        tuner.add_cfg(dict(c, tokens_per_second=1.0 / seen[-1]))
+    assert len(seen) > 3 and seen == sorted(seen)                      # cheapest estimate first
+    # customize: the user's list, still pruned by divisibility
+    t2 = AutoTuner(dict(num_gpus=8, model_cfg=dict(llama7b, num_layers=30), search_algo="customize",
+                        configs=[dict(base, pp_degree=4, sharding_degree=2), base]))
+    assert t2.search_once() == base and t2.search_once() is None       # 30 layers do not split over pp=4
+    # gbs: doubles until a trial fails
+    t3 = AutoTuner(dict(num_gpus=8, model_cfg=llama7b, search_algo="gbs", gbs_start=8, dp_degree=[1], mp_degree=[1], pp_degree=[1],
+                        sharding_degree=[8], sharding_stage=[3], micro_batch_size=[1], use_recompute=[False], use_memory_model=False))
+    sizes = []
+    while True:
+        c = t3.search_once()
+        if c is None:
+            break
+        sizes.append(c["global_batch_size"])
+        t3.add_cfg(dict(c, **({"error": "oom"} if c["global_batch_size"] >= 32 else {"tokens_per_second": 1.0})))
+    assert sizes == [8, 16, 32]
+    t4 = AutoTuner(dict(num_gpus=8, model_cfg=llama7b, search_algo="dp_estimation", dp_estimation_degree=2, task_limit=5))
+    c = t4.search_once()
+    assert c["dp_degree"] == 1 and c["mp_degree"] * c["pp_degree"] * c["sharding_degree"] == 4
