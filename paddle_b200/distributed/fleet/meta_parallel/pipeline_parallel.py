@@ -78,6 +78,17 @@ class FakeMicroDataset:
             f"micro_batch_size = {self._micro_batch_size}, accumulate_steps = {self._acc_steps}.")
 
 
+def one_f_one_b_slots(num_stages, acc_steps, stage):
+    """1F1B for one chunk per stage, as a table of ``(forward micro-batch or None, backward micro-batch or None)``:
+    stage s runs ``P - s - 1`` forwards ahead (so that the last stage can start its first backward right after its first
+    forward), then pairs one forward with one backward per slot, then drains the backwards it is ahead by."""
+    lead = min(num_stages - stage - 1, acc_steps)
+    slots = [(k, None) for k in range(lead)]
+    slots += [(lead + i, i) for i in range(acc_steps - lead)]
+    slots += [(None, i) for i in range(acc_steps - lead, acc_steps)]
+    return slots
+
+
 class PipelineParallel(MetaParallelBase):
     def __init__(self, layers, hcg, strategy):
         if not isinstance(layers, PipelineLayer):
@@ -182,69 +193,65 @@ class PipelineParallel(MetaParallelBase):
         return self.forward_backward_pipeline(data=None, scaler=None, static_scheduler=True)
 
     # ------------------------------------------------------------------ 1F1B
+    def _run_slots_1f1b(self, slots, micro_dataset, keep_outputs=False):
+        """Execute a plain (one chunk per stage) slot table.  Communication follows from the table alone:
+          * a forward needs its input: received right before it, unless the previous backward already fetched it;
+          * a forward paired with a backward in its slot hands its output over and takes the gradient for that backward
+            in one call; a lone forward just sends;
+          * a backward followed by a slot with a forward sends its input gradient and fetches that forward's input in one
+            call; otherwise it just sends, and a lone backward first receives its gradient.
+        Inputs / outputs wait in FIFO order for their backward."""
+        helper = self._p2p_helper
+        first, last = self.is_pipeline_first_stage(), self.is_pipeline_last_stage()
+        waiting_in, waiting_out, outputs = [], [], []
+        have_input, next_input = False, None
+        for idx, (f, b) in enumerate(slots):
+            nxt = slots[idx + 1] if idx + 1 < len(slots) else None
+            grad_in = None
+            if f is not None:
+                input_tensor = next_input if have_input else helper.recv_forward(first)
+                have_input, next_input = False, None
+                self._record_stamp("F", f, '"B"', "rail_response")
+                output_tensor = self._forward_step(input_tensor, micro_dataset)
+                self._record_stamp("F", f, '"E"', "rail_response")
+                if b is not None:
+                    grad_in = helper.send_forward_recv_backward(output_tensor, last)
+                else:
+                    helper.send_forward(output_tensor, last)
+                if keep_outputs:
+                    outputs.append(output_tensor)
+                    continue
+                waiting_in.append(input_tensor)
+                waiting_out.append(output_tensor)
+                if not last:
+                    self._release_output(output_tensor)
+            if b is not None:
+                input_tensor, output_tensor = waiting_in.pop(0), waiting_out.pop(0)
+                if f is None:
+                    grad_in = helper.recv_backward(last)
+                self._record_stamp("B", b, '"B"', "rail_animation")
+                input_grad = self._backward_step(input_tensor, output_tensor, grad_in)
+                self._record_stamp("B", b, '"E"', "rail_animation")
+                if nxt is not None and nxt[0] is not None:
+                    next_input, have_input = helper.send_backward_recv_forward(input_grad, first), True
+                else:
+                    helper.send_backward(input_grad, first)
+        return outputs
+
     def forward_backward_pipeline(self, data, scaler=None, static_scheduler=False, return_micro_batch_loss=False):
         self.scaler = scaler
         self.total_loss = None
         self.micro_batch_id = 0
-        startup_steps = min(self.num_stages - self.stage_id - 1, self.accumulate_steps)
-        steady_steps = self.accumulate_steps - startup_steps
+        slots = one_f_one_b_slots(self.num_stages, self.accumulate_steps, self.stage_id)
         if static_scheduler:
-            schedule = ""
-            for i in range(startup_steps):
-                schedule += f"f{i};"
-            for i in range(steady_steps):
-                schedule += f"f{startup_steps + i};b{i};"
-            for i in range(startup_steps):
-                schedule += f"b{steady_steps + i};"
-            return schedule
-        micro_dataset = self._wrap_data(data)
-        input_buffers, output_buffers = [], []
-        helper = self._p2p_helper
-        first, last = self.is_pipeline_first_stage(), self.is_pipeline_last_stage()
-        for step_id in range(startup_steps):
-            input_tensor = helper.recv_forward(first)
-            self._record_stamp("F", step_id, '"B"', "rail_response")
-            output_tensor = self._forward_step(input_tensor, micro_dataset)
-            self._record_stamp("F", step_id, '"E"', "rail_response")
-            helper.send_forward(output_tensor, last)
-            input_buffers.append(input_tensor)
-            output_buffers.append(output_tensor)
-            if not last:
-                self._release_output(output_tensor)
-        if steady_steps > 0:
-            input_tensor = helper.recv_forward(first)
-        for i in range(steady_steps):
-            last_iter = i == steady_steps - 1
-            self._record_stamp("F", startup_steps + i, '"B"', "rail_response")
-            output_tensor = self._forward_step(input_tensor, micro_dataset)
-            self._record_stamp("F", startup_steps + i, '"E"', "rail_response")
-            output_tensor_grad = helper.send_forward_recv_backward(output_tensor, last)
-            input_buffers.append(input_tensor)
-            output_buffers.append(output_tensor)
-            if not last:
-                self._release_output(output_tensor)
-            input_tensor, output_tensor = input_buffers.pop(0), output_buffers.pop(0)
-            self._record_stamp("B", i, '"B"', "rail_animation")
-            input_tensor_grad = self._backward_step(input_tensor, output_tensor, output_tensor_grad)
-            self._record_stamp("B", i, '"E"', "rail_animation")
-            if last_iter:
-                input_tensor = None
-                helper.send_backward(input_tensor_grad, first)
-            else:
-                input_tensor = helper.send_backward_recv_forward(input_tensor_grad, first)
-        for i in range(startup_steps):
-            input_tensor, output_tensor = input_buffers.pop(0), output_buffers.pop(0)
-            output_tensor_grad = helper.recv_backward(last)
-            self._record_stamp("B", steady_steps + i, '"B"', "rail_animation")
-            input_tensor_grad = self._backward_step(input_tensor, output_tensor, output_tensor_grad)
-            self._record_stamp("B", steady_steps + i, '"E"', "rail_animation")
-            helper.send_backward(input_tensor_grad, first)
+            return "".join((f"f{f};" if f is not None else "") + (f"b{b};" if b is not None else "") for f, b in slots)
+        self._run_slots_1f1b(slots, self._wrap_data(data))
         self._flush_records()
         self._layers.allreduce_shared_weight_gradients()
         with torch.no_grad():
             train_loss = self._broadcast_final_loss(return_micro_batch_loss)
         if self._clear_every_step_cache:
-            helper.clear_meta_cache()
+            self._p2p_helper.clear_meta_cache()
         return train_loss
 
     def train_batch(self, data, optimizer, lr_scheduler=None, scaler=None, loss_fn_idx=0, return_micro_batch_loss=False):
@@ -255,21 +262,15 @@ class PipelineParallel(MetaParallelBase):
         return train_loss
 
     def eval_batch(self, data, compute_loss=False, loss_fn_idx=0):
+        """Forward-only slots; the outputs (or the broadcast loss) are returned."""
         self.loss_fn_idx = loss_fn_idx
         self._layers.eval()
         self._compute_loss = compute_loss
         self.total_loss = None
         self.micro_batch_id = 0
-        micro_dataset = self._wrap_data(data)
-        helper = self._p2p_helper
-        first, last = self.is_pipeline_first_stage(), self.is_pipeline_last_stage()
-        outputs = []
+        slots = [(k_, None) for k_ in range(self.accumulate_steps)]
         with torch.no_grad():
-            for _ in range(self.accumulate_steps):
-                input_tensor = helper.recv_forward(first)
-                output_tensor = self._forward_step(input_tensor, micro_dataset)
-                helper.send_forward(output_tensor, last)
-                outputs.append(output_tensor)
+            outputs = self._run_slots_1f1b(slots, self._wrap_data(data), keep_outputs=True)
             res = self._broadcast_final_loss() if self._compute_loss else outputs
         self._compute_loss = True
         return res

@@ -311,6 +311,11 @@ def test_interleaved_pipeline_schedule_table():
             assert all(pos_b[k] >= pos_f[k] for k in range(total))
             leads.append(next(i for i, (_, b) in enumerate(slots) if b is not None))
         assert leads == sorted(leads, reverse=True) and leads[-1] == min((V - 1) * P, total)
+        from paddle_b200.distributed.fleet.meta_parallel.pipeline_parallel import one_f_one_b_slots
+        for st in range(P):
+            plain = one_f_one_b_slots(P, acc, st)
+            assert [f for f, _ in plain if f is not None] == list(range(acc)) == [b for _, b in plain if b is not None]
+            assert next(i for i, (_, b) in enumerate(plain) if b is not None) == min(P - st - 1, acc)
         ftb = interleave_slots(P, V, acc, 0, mode="fthenb")
         assert [f for f, b in ftb[:total]] == list(range(total)) and all(b is None for _, b in ftb[:total])
         assert interleave_slots(P, V, acc, 1, forward_only=True) == [(k, None) for k in range(total)]
