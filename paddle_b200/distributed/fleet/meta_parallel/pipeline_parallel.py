@@ -24,58 +24,39 @@ from .pp_utils import p2p_communication as p2p
 
 
 class FakeMicroDataset:
+    """Iterator over the micro-batches of one global batch ``(inputs, labels)`` (the reference's name for it:
+    pipeline_parallel.py FakeMicroDataset).  The first stage reads inputs, the last stage labels, the others nothing.
+    A field is either one tensor of ``acc_steps * micro_batch_size`` rows (cut into row blocks), a list of ``acc_steps``
+    ready-made micro-batches, ``None``, or a tuple of such fields."""
+
     def __init__(self, data, is_first_stage, is_last_stage, acc_steps, micro_batch_size):
-        self._data = data
-        self._index = 0
-        self._acc_steps = acc_steps
-        self._is_first_stage = is_first_stage
-        self._is_last_stage = is_last_stage
-        self._micro_batch_size = micro_batch_size
+        self._fields = data
+        self._want = (bool(is_first_stage), bool(is_last_stage))
+        self._n, self._rows = acc_steps, micro_batch_size
+        self._k = 0
 
     def __iter__(self):
         return self
 
-    def __next__(self):
-        if self._index >= self._acc_steps:
-            raise StopIteration
-        assert self._is_first_stage or self._is_last_stage
-        micro = self._load_micro_batch(self._index)
-        self._index += 1
-        return micro
-
-    def _load_micro_batch(self, step):
-        inputs = self._data
-        data = self._slice(inputs[0], step) if self._is_first_stage else None
-        label = self._slice(inputs[1], step) if self._is_last_stage else None
-        return data, label
-
-    def _slice(self, inputs, step):
-        if inputs is None:
+    def _cut(self, field, k):
+        if field is None:
             return None
-        begin = step * self._micro_batch_size
-        end = begin + self._micro_batch_size
-        if isinstance(inputs, tuple):
-            out = []
-            for d in inputs:
-                if isinstance(d, list):
-                    assert len(d) == self._acc_steps, f"length of data should be {self._acc_steps}, but it is {len(d)}"
-                    out.append(d[step].detach())
-                elif d is not None:
-                    self._check(d)
-                    out.append(d[begin:end].detach())
-                else:
-                    out.append(None)
-            return tuple(out)
-        if isinstance(inputs, list):
-            assert len(inputs) == self._acc_steps
-            return inputs[step].detach()
-        self._check(inputs)
-        return inputs[begin:end].detach()
+        if isinstance(field, tuple):
+            return tuple(self._cut(f, k) for f in field)
+        if isinstance(field, list):
+            assert len(field) == self._n, f"a list field holds one entry per micro-batch: {len(field)} != {self._n}"
+            return field[k].detach()
+        assert field.shape[0] == self._n * self._rows, (
+            f"batch_size needs to be divisible by micro_batch_size. Currently, batch_size = {field.shape[0]}, "
+            f"micro_batch_size = {self._rows}, accumulate_steps = {self._n}.")
+        return field[k * self._rows:(k + 1) * self._rows].detach()
 
-    def _check(self, data):
-        assert data.shape[0] == self._micro_batch_size * self._acc_steps, (
-            f"batch_size needs to be divisible by micro_batch_size. Currently, batch_size = {data.shape[0]}, "
-            f"micro_batch_size = {self._micro_batch_size}, accumulate_steps = {self._acc_steps}.")
+    def __next__(self):
+        if self._k >= self._n:
+            raise StopIteration
+        assert any(self._want), "only the first and the last pipeline stage read data"
+        k, self._k = self._k, self._k + 1
+        return tuple(self._cut(self._fields[i], k) if self._want[i] else None for i in (0, 1))
 
 
 def one_f_one_b_slots(num_stages, acc_steps, stage):
