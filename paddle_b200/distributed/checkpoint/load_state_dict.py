@@ -57,6 +57,10 @@ def load_state_dict(state_dict, path, process_group=None, coordinator_rank=0):
             if not isinstance(target, torch.Tensor):
                 continue
             gshape, goff = shard_info(target)
+            if hasattr(target, "placements"):
+                # an auto_parallel DistTensor: fill its local shard (ops on the tensor itself would be global ops)
+                from paddle_b200.distributed.auto_parallel.dtensor import local_of
+                target = local_of(target)
             filled = False
             # coverage of the target shard: every element must come from some stored shard (the newest save of a key
             # wins, older ones only fill what it does not cover)

@@ -74,6 +74,9 @@ def save_state_dict(state_dict, path, process_group=None, coordinator_rank=0):
         replicated = tuple(gshape) == tuple(val.shape)
         local_meta[key] = (LocalTensorMetadata(goff, tuple(val.shape), str(val.dtype).replace("torch.", "")), replicated)
         local_storage[LocalTensorIndex(key, goff)] = file_name
+        if hasattr(val, "placements"):
+            from paddle_b200.distributed.auto_parallel.dtensor import local_of
+            val = local_of(val).detach()
         local_tensors[key] = val
     gathered = []
     if multi:

@@ -172,4 +172,29 @@ close(ap.unshard_dtensor(net.fc2.bias), ref_net.fc2.bias.detach(), tol=2e-4, wha
 dm.eval()
 close(torch.tensor(float(dm(ap.shard_tensor(data[0][0], mesh, [S(0)]), ap.shard_tensor(data[0][1], mesh, [S(0)])))),
       mse(ref_net(data[0][0]), data[0][1]).detach(), tol=1e-4, what="DistModel eval loss")
+# ---- distributed checkpoint of DistTensors: saved under one sharding, loaded under another (reshard on load)
+import os
+import tempfile
+box = [tempfile.mkdtemp() if r == 0 else None]
+dist.broadcast_object_list(box, 0)
+dist.save_state_dict(dict(net.state_dict()), box[0])
+
+
+def other_shard_fn(name, layer, m):
+    if name in ("fc1", "fc2"):
+        layer.weight = ap.shard_tensor(layer.weight, m, [S(0)])      # row-sharded now (fc1 was column-sharded, fc2 whole)
+        layer.bias = ap.shard_tensor(layer.bias, m, [R_()])
+    elif name == "norm":
+        layer.weight = ap.shard_tensor(layer.weight, m, [S(0)])
+        layer.bias = ap.shard_tensor(layer.bias, m, [R_()])
+
+
+paddle.seed(99)
+fresh = ap.shard_layer(Net(), mesh, other_shard_fn)
+sd = dict(fresh.state_dict())
+dist.load_state_dict(sd, box[0])
+fresh.set_state_dict(sd)
+for name in ("fc1.weight", "fc1.bias", "fc2.weight", "norm.weight"):
+    close(ap.unshard_dtensor(dict(fresh.named_parameters())[name]), ap.unshard_dtensor(dict(net.named_parameters())[name]),
+          tol=0, what=f"checkpoint reshard {name}")
 print("auto_parallel_train ok", r)
