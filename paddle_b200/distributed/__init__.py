@@ -8,7 +8,7 @@ from .communication import (P2POp, all_gather, all_gather_object, all_reduce, al
 from .parallel import DataParallel, ParallelEnv, get_rank, get_world_size, init_parallel_env  # noqa: F401
 from .spawn import spawn  # noqa: F401
 from . import fleet  # noqa: F401
-from . import checkpoint, launch, sharding, utils  # noqa: F401
+from . import checkpoint, launch, rpc, sharding, utils  # noqa: F401
 from .checkpoint import load_state_dict, save_state_dict  # noqa: F401
 from .fleet.layers.mpu.mp_ops import split  # noqa: F401
 from .auto_parallel import (DistAttr, DistModel, Partial, Placement, ProcessMesh, Replicate, Shard, Strategy,  # noqa: F401

@@ -478,3 +478,22 @@ def test_auto_tuner_cost_model_and_search_algorithms():
     t4 = AutoTuner(dict(num_gpus=8, model_cfg=llama7b, search_algo="dp_estimation", dp_estimation_degree=2, task_limit=5))
     c = t4.search_once()
     assert c["dp_degree"] == 1 and c["mp_degree"] * c["pp_degree"] * c["sharding_degree"] == 4
+
+
+def test_rpc_between_two_processes():
+    import socket
+    import subprocess
+    import sys
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    procs = []
+    for r in range(2):
+        env = dict(os.environ, PADDLE_TRAINER_ID=str(r), RPC_MASTER=f"127.0.0.1:{port}", PYTHONPATH=root, CUDA_VISIBLE_DEVICES="")
+        procs.append(subprocess.Popen([sys.executable, os.path.join(root, "tests", "dist_workers", "rpc_worker.py")], env=env,
+                                      stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
+    outs = [p.communicate(timeout=120)[0] for p in procs]
+    assert all(p.returncode == 0 for p in procs), outs
+    assert "rpc ok 0" in outs[0] and "rpc ok 1" in outs[1]
