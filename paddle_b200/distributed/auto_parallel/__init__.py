@@ -125,6 +125,34 @@ class ProcessMesh:
             return ProcessMesh(moved[index], names[1:])
         return ProcessMesh(moved, names)
 
+    def __getitem__(self, index):
+        """Sub-mesh by numpy-style indexing of the rank array (reference: process_mesh.py __getitem__)."""
+        sub = self._mesh[index]
+        if np.ndim(sub) == 0:
+            return ProcessMesh([int(sub)], [self._dim_names[-1]])
+        idx = index if isinstance(index, tuple) else (index,)
+        kept = [n for i, n in enumerate(self._dim_names) if i >= len(idx) or not isinstance(idx[i], (int, np.integer))]
+        return ProcessMesh(sub, kept)
+
+    def __contains__(self, rank):
+        return int(rank) in self._process_ids
+
+    def get_rank_by_dim_and_process_id(self, dim, process_id):
+        """Coordinate of ``process_id`` along mesh dim ``dim`` (name or index); -1 if the rank is not in the mesh."""
+        c = self.coord_of(process_id)
+        if c is None:
+            return -1
+        return c[self._dim_names.index(dim) if isinstance(dim, str) else int(dim)]
+
+    def get_submesh_with_dim(self, dim_name):
+        """The 1-D mesh along ``dim_name`` that contains the calling rank."""
+        axis = self._dim_names.index(dim_name)
+        c = self.coord_of(C.get_rank())
+        if c is None:
+            return None
+        idx = tuple(slice(None) if i == axis else c[i] for i in range(self.ndim))
+        return ProcessMesh(self._mesh[idx], [dim_name])
+
     def axis_group(self, axis):
         """Communicator along mesh axis ``axis`` containing the calling rank (created collectively, cached)."""
         if axis in self._groups:
@@ -541,6 +569,9 @@ class Strategy:
         self.pipeline = _S(enable=False, schedule_mode="1F1B", micro_batch_size=1, accumulate_steps=1, **cfg.get("pipeline", {}))
         self.amp = _S(enable=False, dtype="float16", level="O1", init_loss_scaling=32768.0, **cfg.get("amp", {}))
         self.recompute = _S(enable=False, **cfg.get("recompute", {}))
+
+
+from .random import parallel_manual_seed  # noqa: E402,F401
 
 
 class DistModel:

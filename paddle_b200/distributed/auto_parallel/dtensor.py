@@ -469,7 +469,7 @@ def _h_unary(op):
 
 
 for _f in (torch.relu, TF.relu, TF.gelu, TF.silu, torch.tanh, torch.sigmoid, torch.exp, torch.log, torch.sqrt, torch.rsqrt, torch.neg,
-           torch.abs, torch.square, torch.clone, TF.dropout, torch.nan_to_num, torch.clamp, torch.erf, torch.sin, torch.cos,
+           torch.abs, torch.square, torch.clone, torch.nan_to_num, torch.clamp, torch.erf, torch.sin, torch.cos,
            torch.Tensor.relu, torch.Tensor.tanh, torch.Tensor.sigmoid, torch.Tensor.exp, torch.Tensor.log, torch.Tensor.sqrt,
            torch.Tensor.rsqrt, torch.Tensor.neg, torch.Tensor.__neg__, torch.Tensor.abs, torch.Tensor.square, torch.Tensor.clone,
            torch.Tensor.contiguous, torch.Tensor.to, torch.Tensor.float, torch.Tensor.half, torch.Tensor.bfloat16,
@@ -477,6 +477,19 @@ for _f in (torch.relu, TF.relu, TF.gelu, TF.silu, torch.tanh, torch.sigmoid, tor
            torch.Tensor.detach, torch.detach, torch.Tensor.type_as, torch.zeros_like, torch.ones_like, torch.empty_like,
            torch.Tensor.masked_fill):
     _TABLE[_f] = _h_unary(_f)
+
+
+@_register(TF.dropout, torch.dropout)
+def _h_dropout(x, p=0.5, training=True, inplace=False, **kw):
+    """Element-wise, with the generator chosen by the placement (auto_parallel/random.py): different numbers along
+    sharding axes, the same numbers along replicating axes, once ``parallel_manual_seed`` switched the control on."""
+    from . import random as PR
+    train = kw.pop("train", training)
+
+    def fn(a):
+        with PR.rng_for(x.process_mesh, x.placements, a.device):
+            return TF.dropout(a, p, train)
+    return run_rule("elementwise", fn, [x])
 
 
 @_register(torch.where)

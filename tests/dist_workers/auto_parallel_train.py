@@ -172,6 +172,19 @@ close(ap.unshard_dtensor(net.fc2.bias), ref_net.fc2.bias.detach(), tol=2e-4, wha
 dm.eval()
 close(torch.tensor(float(dm(ap.shard_tensor(data[0][0], mesh, [S(0)]), ap.shard_tensor(data[0][1], mesh, [S(0)])))),
       mse(ref_net(data[0][0]), data[0][1]).detach(), tol=1e-4, what="DistModel eval loss")
+# ---- randomness: dropout draws different numbers along a sharding axis, the same numbers along a replicating one
+ap.parallel_manual_seed(123)
+ones = torch.ones(8, 64)
+d_sh = F.dropout(ap.shard_tensor(ones, mesh, [S(0)]), 0.5)
+d_re = F.dropout(ap.shard_tensor(ones, mesh, [R_()]), 0.5)
+both = [None, None]
+dist.all_gather_object(both, (loc(d_sh), loc(d_re)))
+assert not torch.equal(both[0][0], both[1][0]), "shards of one tensor must not share a dropout mask"
+assert torch.equal(both[0][1], both[1][1]), "replicas must share the dropout mask"
+assert not torch.equal(loc(F.dropout(ap.shard_tensor(ones, mesh, [R_()]), 0.5)), loc(d_re)), "successive calls must differ"
+sub = ap.ProcessMesh([[0, 1]], dim_names=["a", "b"])
+assert sub[0].process_ids == [0, 1] and sub[0].dim_names == ["b"] and (1 in sub) and sub.get_rank_by_dim_and_process_id("b", 1) == 1
+
 # ---- distributed checkpoint of DistTensors: saved under one sharding, loaded under another (reshard on load)
 import os
 import tempfile
