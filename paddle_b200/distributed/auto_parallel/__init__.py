@@ -199,6 +199,15 @@ def shard_tensor(data, mesh, placements, dtype=None, place=None, stop_gradient=N
     from . import dtensor as D
     t = data if isinstance(data, torch.Tensor) else to_tensor(data, dtype=dtype, place=place)
     gshape = tuple(t.shape)
+    if mesh.coord_of(C.get_rank()) is None and C.get_world_size() > 1:
+        # not a member of the mesh: keep a zero-element placeholder (dtype, global shape, placements)
+        empty = torch.empty(0, dtype=t.dtype, device=t.device)
+        if isinstance(data, torch.nn.Parameter):
+            out = D.make_parameter(empty, mesh, placements, gshape, like=data)
+        else:
+            out = D.make_leaf(empty, mesh, placements, gshape, requires_grad=False)
+        out._placeholder = True
+        return out
     coord = mesh.coord_of(C.get_rank()) or tuple([0] * mesh.ndim)
     local = D.local_of(t).detach()
     for ax, pl in enumerate(placements):
@@ -275,21 +284,10 @@ def _gather_axis(t, group, dim):
 
 def _cross_mesh(dist_tensor, mesh):
     """Same placements on another mesh of the same shape: rank i of the source mesh sends its shard to rank i of the
-    destination mesh (reference: same_status_reshard_function.cc)."""
-    src_mesh = dist_tensor.process_mesh
-    assert list(src_mesh.shape) == list(mesh.shape), "cross-mesh reshard needs meshes of the same shape"
-    me = C.get_rank()
-    t = dist_tensor.detach()
-    out = t
-    for s_rank, d_rank in zip(src_mesh.process_ids, mesh.process_ids):
-        if s_rank == d_rank:
-            continue
-        if me == s_rank:
-            comm.send(t.contiguous(), d_rank)
-        elif me == d_rank:
-            out = torch.empty_like(t)
-            comm.recv(out, s_rank)
-    return _attach(out, mesh, dist_tensor.placements, dist_tensor._global_shape)
+    destination mesh (reference: same_status_reshard_function.cc).  Differentiable; ranks outside a mesh hold
+    placeholders (dtensor.py)."""
+    from . import dtensor as D
+    return D.cross_mesh(dist_tensor, mesh)
 
 
 def reshard(dist_tensor, mesh, placements):
@@ -301,6 +299,10 @@ def reshard(dist_tensor, mesh, placements):
     if dist_tensor.process_mesh != mesh and C.get_world_size() > 1:
         dist_tensor = _cross_mesh(dist_tensor, mesh)
     gshape = dist_tensor._global_shape
+    if not D.in_mesh(mesh):
+        out = D.wrap(D.local_of(dist_tensor).view_as(D.local_of(dist_tensor)), mesh, placements, gshape)
+        out._placeholder = True
+        return out
     loc = D.reshard_local(D.local_of(dist_tensor), mesh, list(dist_tensor.placements), list(placements))
     if loc is D.local_of(dist_tensor) or loc.data_ptr() == dist_tensor.data_ptr():
         loc = loc.view_as(loc) if loc.requires_grad else loc.detach()        # a fresh label, not a relabelled input

@@ -70,7 +70,7 @@ def _attach(t, mesh, placements, global_shape):
     coord = mesh.coord_of(C.get_rank()) or tuple([0] * mesh.ndim)
     off = [0] * len(global_shape)
     for ax, pl in enumerate(placements):
-        if isinstance(pl, Shard) and pl.dim < len(global_shape):
+        if isinstance(pl, Shard) and pl.dim < len(global_shape) and pl.dim < t.dim():
             off[pl.dim] += coord[ax] * t.shape[pl.dim]
     t._dist_meta = (tuple(global_shape), tuple(off))
     t._global_shape = tuple(global_shape)
@@ -277,6 +277,22 @@ def run_rule(rule, local_fn, tensors, attrs=None, out_reduce=None):
     fn = rule if callable(rule) else R.get_spmd_rule(rule)
     new_specs, out_specs = fn(*specs, **(attrs or {}))
     nd = mesh.ndim
+    if not in_mesh(mesh):
+        # this rank holds placeholders only: nothing to compute, the outputs are placeholders tied into the graph
+        ref = next(t for t in present if isinstance(t, torch.Tensor))
+        locs = [local_of(t) for t in present]
+        need_graph = torch.is_grad_enabled() and any(l.requires_grad for l in locs)
+        raw = _Skip.apply(len(out_specs), ref.dtype, ref.device, *locs) if need_graph else tuple(
+            torch.empty(0, dtype=ref.dtype, device=ref.device) for _ in out_specs)
+        outs = []
+        for o, sp in zip(raw, out_specs):
+            pl = sp.placements(nd)
+            if out_reduce is not None:
+                pl = [Partial(out_reduce) if isinstance(p, Partial) else p for p in pl]
+            w = wrap(o, mesh, pl, tuple(sp.shape))
+            w._placeholder = True
+            outs.append(w)
+        return outs[0] if len(outs) == 1 else tuple(outs)
     out_axes_busy = set()
     for sp in out_specs:
         out_axes_busy |= {ax for ax in sp.dims_mapping if ax >= 0} | set(sp.partial_dims)
@@ -854,12 +870,21 @@ def _h_backward(self, gradient=None, retain_graph=None, create_graph=False, inpu
     """``loss.backward()`` on a loss that is still a partial sum (e.g. the mean over a batch-sharded dim): the pending
     reduction is part of the function being differentiated, so it is applied first."""
     with torch._C.DisableTorchFunctionSubclass():
+        if is_placeholder(self):
+            # not a member of the loss's mesh: nothing to seed, but the walk back through this rank's graph must happen
+            # (it reaches the cross-mesh transfers that bring this rank's share of the gradient)
+            loc = local_of(self)
+            if loc.requires_grad:
+                torch.Tensor.backward(loc, torch.zeros_like(loc), retain_graph, create_graph, inputs=inputs)
+            return
         torch.Tensor.backward(_resolved(self), local_of(gradient) if gradient is not None else None, retain_graph, create_graph,
                               inputs=inputs)
 
 
 def _value_reader(method):
     def h(self, *a, **kw):
+        if is_placeholder(self):
+            return float("nan")                     # the value lives on the ranks of the tensor's mesh
         with torch._C.DisableTorchFunctionSubclass():
             return method(_resolved(self).detach(), *a, **kw)
     return h
@@ -867,3 +892,103 @@ def _value_reader(method):
 
 for _m in ("item", "tolist", "numpy", "__float__", "__int__", "__bool__"):
     _TABLE[getattr(torch.Tensor, _m)] = _value_reader(getattr(torch.Tensor, _m))
+
+
+# ---------------------------------------------------------------------------------------- tensors on other ranks' meshes
+# A rank that is not a member of a tensor's mesh holds a PLACEHOLDER for it: a zero-element local tensor with the right
+# dtype, the global shape and the placements.  Ops on placeholders compute nothing, but keep the autograd graph
+# connected, so that ``loss.backward()`` on every rank walks back to the cross-mesh transfers, whose backward moves the
+# gradient to the ranks that own the producer - pipeline stages as meshes, with no schedule object (the reference runs
+# dygraph semi-auto pipelines the same way: reshard between the stage meshes, api.py reshard + same_status reshard).
+def in_mesh(mesh):
+    return mesh.coord_of(C.get_rank()) is not None
+
+
+def is_placeholder(t):
+    return getattr(t, "_placeholder", False)
+
+
+def make_placeholder(mesh, placements, global_shape, dtype, device, like=None):
+    loc = torch.empty(0, dtype=dtype, device=device)
+    out = wrap(loc if like is None else like, mesh, placements, global_shape)
+    out._placeholder = True
+    return out
+
+
+class _Skip(torch.autograd.Function):
+    """n zero-element outputs that depend (for autograd's bookkeeping only) on the inputs."""
+
+    @staticmethod
+    def forward(ctx, n_out, dtype, device, *inputs):
+        ctx.shapes = [(tuple(i.shape), i.dtype, i.device) if isinstance(i, torch.Tensor) else None for i in inputs]
+        outs = tuple(torch.empty(0, dtype=dtype, device=device) for _ in range(n_out))
+        return outs
+
+    @staticmethod
+    def backward(ctx, *grads):
+        return (None, None, None) + tuple(None if s is None else torch.zeros(s[0], dtype=s[1], device=s[2]) for s in ctx.shapes)
+
+
+def _local_shape_of(global_shape, mesh, placements):
+    _, _, Shard = _P()
+    shp = list(global_shape)
+    for ax, p in enumerate(placements):
+        if isinstance(p, Shard):
+            shp[p.dim] //= mesh.shape[ax]
+    return tuple(shp)
+
+
+class _CrossMesh(torch.autograd.Function):
+    """Same placements, other ranks: rank i of the source mesh hands its shard to rank i of the destination mesh."""
+
+    @staticmethod
+    def forward(ctx, t, src_mesh, dst_mesh, local_shape, dtype):
+        me = C.get_rank()
+        ctx.cfg = (src_mesh, dst_mesh, tuple(local_shape), dtype, t.device)
+        out = None
+        for s_rank, d_rank in zip(src_mesh.process_ids, dst_mesh.process_ids):
+            if s_rank == d_rank:
+                if me == s_rank:
+                    out = t.view_as(t)
+                continue
+            if me == s_rank:
+                comm.send(t.detach().contiguous(), d_rank)
+            elif me == d_rank:
+                out = torch.empty(local_shape, dtype=dtype, device=t.device)
+                comm.recv(out, s_rank)
+        return out if out is not None else torch.empty(0, dtype=dtype, device=t.device)
+
+    @staticmethod
+    def backward(ctx, g):
+        src_mesh, dst_mesh, local_shape, dtype, device = ctx.cfg
+        me = C.get_rank()
+        out = None
+        for s_rank, d_rank in zip(src_mesh.process_ids, dst_mesh.process_ids):
+            if s_rank == d_rank:
+                if me == s_rank:
+                    out = g
+                continue
+            if me == d_rank:
+                comm.send(g.detach().contiguous(), s_rank)
+            elif me == s_rank:
+                out = torch.empty(local_shape, dtype=dtype, device=device)
+                comm.recv(out, d_rank)
+        if out is None:
+            out = torch.empty(0, dtype=dtype, device=device)
+        return out, None, None, None, None
+
+
+def cross_mesh(t, dst_mesh):
+    """DistTensor on its mesh -> the same placements on ``dst_mesh`` (a mesh of the same shape)."""
+    src_mesh = t.process_mesh
+    assert list(src_mesh.shape) == list(dst_mesh.shape), "cross-mesh reshard needs meshes of the same shape"
+    lshape = _local_shape_of(t._global_shape, src_mesh, t.placements)
+    loc = local_of(t)
+    if torch.is_grad_enabled() and loc.requires_grad:
+        out = _CrossMesh.apply(loc, src_mesh, dst_mesh, lshape, loc.dtype)
+    else:
+        out = _CrossMesh.forward(type("ctx", (), {})(), loc.detach(), src_mesh, dst_mesh, lshape, loc.dtype)
+    res = wrap(out, dst_mesh, t.placements, t._global_shape)
+    if not in_mesh(dst_mesh):
+        res._placeholder = True
+    return res

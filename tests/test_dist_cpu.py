@@ -29,6 +29,11 @@ def test_auto_parallel_llama_matches_single_process():
     run_dist("auto_parallel_llama.py", 2)
 
 
+def test_auto_parallel_pipeline_stages_as_meshes():
+    """Layers on different meshes, reshard across meshes at the stage boundary, placeholders on the other ranks."""
+    run_dist("auto_parallel_pp.py", 2)
+
+
 def test_auto_parallel_2d_mesh():
     run_dist("auto_parallel_2d.py", 4)
 
