@@ -497,3 +497,36 @@ def test_rpc_between_two_processes():
     outs = [p.communicate(timeout=120)[0] for p in procs]
     assert all(p.returncode == 0 for p in procs), outs
     assert "rpc ok 0" in outs[0] and "rpc ok 1" in outs[1]
+
+
+def test_asp_n_m_sparsity_masks_and_training():
+    import paddle_b200 as paddle
+    from paddle_b200.incubate import asp
+    torch.manual_seed(0)
+    w = torch.randn(16, 24)
+    m1 = asp.get_mask_1d(w, 2, 4)
+    assert asp.check_mask_1d(w * m1, 2, 4) and abs(asp.calculate_density(m1) - 0.5) < 1e-6
+    g = w.abs().reshape(16, 6, 4)
+    kept = (g * m1.reshape(16, 6, 4)).sum(-1)
+    torch.testing.assert_close(kept, g.topk(2, -1).values.sum(-1))            # the two largest of every group of four
+    for fn in (asp.get_mask_2d_greedy, asp.get_mask_2d_best):
+        m2 = fn(w, 2, 4)
+        assert asp.check_mask_2d(w * m2, 2, 4) and asp.check_mask_2d((w * m2).t(), 2, 4)
+    best, greedy = asp.get_mask_2d_best(w, 2, 4), asp.get_mask_2d_greedy(w, 2, 4)
+    assert (w.abs() * best).sum() >= (w.abs() * greedy).sum() - 1e-6
+    assert abs(asp.calculate_density(best) - 0.5) < 1e-6
+
+    net = paddle.nn.Sequential(paddle.nn.Linear(16, 32), paddle.nn.ReLU(), paddle.nn.Linear(32, 6))   # 6 outputs: still fine
+    asp.set_excluded_layers(["2"])
+    masks = asp.prune_model(net, n=2, m=4, mask_algo="mask_1d")
+    assert len(masks) == 1 and asp.check_sparsity(net[0].weight.detach(), asp.CheckMethod.CHECK_1D, 2, 4)
+    assert asp.calculate_density(net[2].weight.detach()) > 0.9               # excluded layer untouched
+    asp.reset_excluded_layers()
+    opt = asp.decorate(paddle.optimizer.SGD(0.1, parameters=net.parameters()))
+    for _ in range(3):
+        loss = net(torch.randn(8, 16)).square().mean()
+        loss.backward()
+        opt.step()
+        opt.clear_grad()
+    assert asp.check_sparsity(net[0].weight.detach(), asp.CheckMethod.CHECK_1D, 2, 4), "the update revived pruned weights"
+    assert abs(asp.calculate_density(net[0].weight.detach()) - 0.5) < 0.02
