@@ -1,7 +1,7 @@
 """paddle.incubate (reference: python/paddle/incubate/__init__.py)."""
 import torch as _torch
 
-from . import asp, distributed, nn, optimizer  # noqa: F401
+from . import asp, autograd, distributed, nn, optimizer  # noqa: F401
 from .optimizer import LookAhead, ModelAverage  # noqa: F401
 from ..geometric import segment_max, segment_mean, segment_min, segment_sum  # noqa: F401
 from ..geometric import send_u_recv as _send_u_recv

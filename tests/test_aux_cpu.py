@@ -530,3 +530,36 @@ def test_asp_n_m_sparsity_masks_and_training():
         opt.clear_grad()
     assert asp.check_sparsity(net[0].weight.detach(), asp.CheckMethod.CHECK_1D, 2, 4), "the update revived pruned weights"
     assert abs(asp.calculate_density(net[0].weight.detach()) - 0.5) < 0.02
+
+
+def test_autograd_jacobian_hessian_and_functional_jvp_vjp():
+    import paddle_b200 as paddle
+    torch.manual_seed(0)
+    A = torch.randn(3, 4)
+    x = torch.randn(4, requires_grad=True)
+    y = torch.tanh(A @ x)
+    J = paddle.autograd.jacobian(y, x)
+    ref = torch.autograd.functional.jacobian(lambda t: torch.tanh(A @ t), x.detach())
+    assert J.shape == (3, 4)
+    torch.testing.assert_close(J[:], ref)
+    torch.testing.assert_close(J[1], ref[1])
+    xb = torch.randn(5, 4, requires_grad=True)
+    yb = torch.tanh(xb @ A.t())
+    Jb = paddle.autograd.jacobian(yb, xb, batch_axis=0)
+    assert Jb.shape == (5, 3, 4)
+    torch.testing.assert_close(Jb[2], torch.autograd.functional.jacobian(lambda t: torch.tanh(A @ t), xb[2].detach()))
+    s = (x ** 3).sum()
+    H = paddle.autograd.hessian(s, x)
+    torch.testing.assert_close(H[:], torch.diag(6 * x.detach()))
+    IA = paddle.incubate.autograd
+    f = lambda t: torch.tanh(A @ t)          # noqa: E731
+    v = torch.randn(4)
+    ys, jv = IA.jvp(f, x.detach(), v)
+    torch.testing.assert_close(jv, ref @ v)
+    u = torch.randn(3)
+    ys, vj = IA.vjp(f, x.detach(), u)
+    torch.testing.assert_close(vj, u @ ref)
+    torch.testing.assert_close(IA.Jacobian(f, x.detach())[:], ref)
+    torch.testing.assert_close(IA.Hessian(lambda t: (t ** 3).sum(), x.detach())[:], torch.diag(6 * x.detach()))
+    Jbf = IA.Jacobian(lambda t: torch.tanh(t @ A.t()), xb.detach(), is_batched=True)
+    torch.testing.assert_close(Jbf[:], Jb[:].detach())
