@@ -42,6 +42,8 @@ from .tensor.compat import install_inplace_variants as _iiv  # noqa: E402
 from .tensor._inplace_names import INPLACE as _INPLACE  # noqa: E402
 
 _iiv(globals(), _INPLACE)
+from .framework import tensor_methods as _tensor_methods  # noqa: E402
+_tensor_methods.install(globals())       # x.max(axis=...), x.split(n, axis=...), ...: Paddle keywords -> Paddle semantics
 Tensor = _torch.Tensor
 version = type("version", (), {"full_version": __version__, "cuda": staticmethod(lambda: _torch.version.cuda),
                                 "show": staticmethod(lambda: print(__version__))})

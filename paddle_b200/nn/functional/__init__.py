@@ -28,8 +28,12 @@ def linear(x, weight, bias=None, name=None):
 def embedding(x, weight, padding_idx=None, sparse=False, name=None, max_norm=None, norm_type=2.0, scale_grad_by_freq=False):
     if padding_idx is not None and padding_idx < 0:
         padding_idx = weight.shape[0] + padding_idx
-    return TF.embedding(x.long() if x.dtype not in (torch.int32, torch.int64) else x, weight, padding_idx=padding_idx,
-                        sparse=bool(sparse))
+    ids = x.long() if x.dtype not in (torch.int32, torch.int64) else x
+    out = TF.embedding(ids, weight, padding_idx=padding_idx, sparse=bool(sparse))
+    if padding_idx is not None:
+        # the reference returns zeros for padding ids whatever the table row holds (and sends it no gradient)
+        out = out * (ids != padding_idx).unsqueeze(-1).to(out.dtype)
+    return out
 
 
 def one_hot(x, num_classes, name=None):

@@ -165,21 +165,38 @@ class CosineAnnealingDecay(LRScheduler):
 
 
 class OneCycleLR(LRScheduler):
+    """One-cycle policy.  Phases are (first step, last step, start lr, end lr): two phases - up to the peak at step
+    ``phase_pct * total - 1``, then down to ``end_learning_rate`` at the last step - or, ``three_phase``, up, back down to the
+    initial rate in as many steps, then down to the end rate (boundaries as in the reference, lr.py OneCycleLR)."""
+
     def __init__(self, max_learning_rate, total_steps, divide_factor=25.0, end_learning_rate=0.0001, phase_pct=0.3,
                  anneal_strategy="cos", three_phase=False, last_epoch=-1, verbose=False):
-        self.max_lr, self.total, self.init_lr, self.end_lr = max_learning_rate, total_steps, max_learning_rate / divide_factor, end_learning_rate
-        self.up = int(phase_pct * total_steps)
-        self.cos = anneal_strategy == "cos"
-        super().__init__(self.init_lr, last_epoch, verbose)
-
-    def _interp(self, a, b, pct):
-        return b + (a - b) / 2.0 * (math.cos(math.pi * pct) + 1) if self.cos else (b - a) * pct + a
+        if total_steps <= 0 or not 0 <= phase_pct <= 1:
+            raise ValueError("OneCycleLR: total_steps must be positive and phase_pct in [0, 1]")
+        if anneal_strategy not in ("cos", "linear"):
+            raise ValueError(f"'anneal_strategy' must by one of 'cos' or 'linear', but received {anneal_strategy}")
+        init, peak, low, last = max_learning_rate / float(divide_factor), float(max_learning_rate), float(end_learning_rate), total_steps - 1
+        top = phase_pct * total_steps - 1
+        if three_phase:
+            if phase_pct >= 0.5:
+                raise ValueError("When three_phase is True, 'phase_pct' must be less than 0.5")
+            back = 2 * phase_pct * total_steps - 2
+            self._phases = [(0, top, init, peak), (top, back, peak, init), (back, last, init, low)]
+        else:
+            self._phases = [(0, top, init, peak), (top, last, peak, low)]
+        self.total_steps, self._cos = total_steps, anneal_strategy == "cos"
+        super().__init__(init, last_epoch, verbose)
 
     def get_lr(self):
         e = self.last_epoch
-        if e <= self.up:
-            return self._interp(self.init_lr, self.max_lr, e / max(self.up, 1))
-        return self._interp(self.max_lr, self.end_lr, (e - self.up) / max(self.total - self.up, 1))
+        if e > self.total_steps:
+            raise ValueError(f"Tried to step {e} times. However the number of total steps is {self.total_steps}")
+        for k, (a, b, lr_a, lr_b) in enumerate(self._phases):
+            if e <= b or k == len(self._phases) - 1:
+                pct = (e - a) / (b - a) if b != a else 1.0
+                if self._cos:
+                    return lr_b + (lr_a - lr_b) / 2.0 * (math.cos(math.pi * pct) + 1)
+                return (lr_b - lr_a) * pct + lr_a
 
 
 class ReduceOnPlateau(LRScheduler):

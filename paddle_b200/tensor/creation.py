@@ -28,11 +28,13 @@ def to_tensor(data, dtype=None, place=None, stop_gradient=True):
         if t is data or t.data_ptr() == data.data_ptr():
             t = t.clone()
     else:
+        if isinstance(data, np.generic):
+            data = np.asarray(data)         # numpy scalars keep their dtype (python scalars take the default one)
         if isinstance(data, np.ndarray):
             if data.dtype == np.uint16:  # bf16 carried as uint16
                 t = torch.from_numpy(data.copy()).view(torch.bfloat16)
             else:
-                t = torch.from_numpy(np.ascontiguousarray(data))
+                t = torch.from_numpy(np.array(data, order="C"))      # a copy: the tensor never aliases the caller's array
         else:
             arr = np.asarray(data)
             if arr.dtype == np.float64 and td is None:

@@ -19,7 +19,10 @@ def _ints(v):
 
 
 def reshape(x, shape, name=None):
-    return x.reshape(_shape(shape))
+    shp = list(_shape(shape))
+    if 0 in shp:                            # 0 keeps the input's dim at that position (reference: manipulation.py reshape)
+        shp = [x.shape[i] if d == 0 else d for i, d in enumerate(shp)]
+    return x.reshape(shp)
 
 
 def reshape_(x, shape, name=None):
