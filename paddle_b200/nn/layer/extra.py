@@ -34,12 +34,26 @@ class _RNNBase(Layer):
                   dropout=dropout, bidirectional=bidir, bias=bias_ih_attr is not False)
         if self._mode == "RNN":
             kw["nonlinearity"] = activation
-        self._rnn = getattr(torch.nn, self._mode)(**kw)
+        rnn = getattr(torch.nn, self._mode)(**kw)
+        # The parameters belong to THIS layer under the reference's names (weight_ih_l0, weight_hh_l0_reverse, ...:
+        # python/paddle/nn/layer/rnn.py RNNBase), which are also what a .pdparams file uses; the torch module that
+        # computes with them is held outside the sublayer registry so that no "_rnn." prefix appears in state dicts.
+        object.__setattr__(self, "_rnn", rnn)
+        for pname, prm in list(rnn._parameters.items()):
+            own = self.create_parameter(list(prm.shape), dtype=prm.dtype)
+            with torch.no_grad():
+                own.copy_(prm)
+            self.add_parameter(pname, own)
+            rnn._parameters[pname] = own
+        rnn._flat_weights = [rnn._parameters.get(n) for n in rnn._flat_weights_names]
         self.input_size, self.hidden_size, self.num_layers = input_size, hidden_size, num_layers
         self.num_directions = 2 if bidir else 1
         self.time_major = time_major
 
     def forward(self, inputs, initial_states=None, sequence_length=None):
+        if inputs.is_cuda and self.__dict__.get("_flat_for") != inputs.device:
+            self._rnn.flatten_parameters()          # one contiguous weight block for cuDNN, once per device
+            self.__dict__["_flat_for"] = inputs.device
         if sequence_length is not None:
             lens = torch.as_tensor(sequence_length).cpu()
             packed = torch.nn.utils.rnn.pack_padded_sequence(inputs, lens, batch_first=not self.time_major, enforce_sorted=False)
@@ -48,6 +62,10 @@ class _RNNBase(Layer):
                                                             total_length=inputs.shape[0 if self.time_major else 1])
             return out, st
         return self._rnn(inputs, initial_states)
+
+    def train(self, mode=True):
+        self._rnn.train(mode)               # dropout between the layers follows this layer's mode
+        return super().train(mode)
 
 
 class LSTM(_RNNBase):

@@ -131,3 +131,33 @@ def test_conv_pool_pad_interpolate():
     seq = rng.randn(2, 3, 8).astype(np.float32)
     eq(F.conv1d(T(seq), T(rng.randn(4, 3, 3).astype(np.float32) * 0 + 1), padding=1), TF.conv1d(torch.tensor(seq), torch.ones(4, 3, 3), padding=1), 1e-4)
     eq(F.max_pool1d(T(seq), 2), TF.max_pool1d(torch.tensor(seq), 2)); eq(F.adaptive_max_pool1d(T(seq), 4), TF.adaptive_max_pool1d(torch.tensor(seq), 4))
+
+
+def test_layer_parameter_names_and_layouts_match_the_reference():
+    """state_dict keys and weight layouts are the .pdparams contract (reference: python/paddle/nn/layer/{common,conv,norm,
+    rnn,transformer}.py)."""
+    nn = paddle.nn
+
+    def keys(layer):
+        return {k: tuple(v.shape) for k, v in layer.state_dict().items()}
+
+    assert keys(nn.Linear(3, 5)) == {"weight": (3, 5), "bias": (5,)}                      # [in, out]
+    assert keys(nn.Conv2D(4, 8, 3, groups=2)) == {"weight": (8, 2, 3, 3), "bias": (8,)}
+    assert keys(nn.Conv2DTranspose(4, 8, 3)) == {"weight": (4, 8, 3, 3), "bias": (8,)}    # [in, out / groups, kh, kw]
+    assert keys(nn.BatchNorm2D(4)) == {"weight": (4,), "bias": (4,), "_mean": (4,), "_variance": (4,)}
+    assert keys(nn.LayerNorm(6)) == {"weight": (6,), "bias": (6,)} and keys(nn.Embedding(5, 3)) == {"weight": (5, 3)}
+    lstm = keys(nn.LSTM(4, 8, num_layers=2, direction="bidirect"))
+    assert lstm["weight_ih_l0"] == (32, 4) and lstm["weight_hh_l0_reverse"] == (32, 8) and lstm["weight_ih_l1"] == (32, 16)
+    assert set(keys(nn.GRU(4, 8))) == {"weight_ih_l0", "weight_hh_l0", "bias_ih_l0", "bias_hh_l0"} and keys(nn.GRU(4, 8))["weight_ih_l0"] == (24, 4)
+    assert set(keys(nn.MultiHeadAttention(8, 2))) == {f"{p}_proj.{w}" for p in ("q", "k", "v", "out") for w in ("weight", "bias")}
+    enc = set(keys(nn.TransformerEncoderLayer(8, 2, 16)))
+    assert {"self_attn.q_proj.weight", "linear1.weight", "linear2.bias", "norm1.weight", "norm2.bias"} <= enc
+    xs = torch.randn(2, 5, 4)
+    out, (h, c) = nn.LSTM(4, 8, direction="bidirect")(xs)
+    assert tuple(out.shape) == (2, 5, 16) and tuple(h.shape) == (2, 2, 8) == tuple(c.shape)
+    out, h = nn.GRU(4, 8, time_major=True)(xs)
+    assert tuple(out.shape) == (2, 5, 8) and tuple(h.shape) == (1, 5, 8)
+    out, _ = nn.LSTM(4, 8)(xs, sequence_length=torch.tensor([5, 3]))
+    assert float(out[1, 3:].abs().sum()) == 0.0                                            # padded steps produce zeros
+    m = nn.Sequential(nn.Linear(3, 4), nn.LSTM(4, 8))
+    assert "1.weight_ih_l0" in m.state_dict() and len(list(m.parameters())) == 6
