@@ -22,9 +22,56 @@ class Softmax2D(Layer):
         return torch.softmax(x, dim=-3)
 
 
+def _adopt(layer, inner, attr):
+    """Keep a torch module that does the computing OUT of the sublayer registry and make its parameters / buffers this
+    layer's own, under their own names - so that state dicts carry the reference's keys ("weight", "weight_ih", ...)
+    instead of a wrapper prefix.  Both objects share the very same tensors."""
+    object.__setattr__(layer, attr, inner)
+    for pname, prm in list(inner._parameters.items()):
+        if prm is None:
+            continue
+        own = layer.create_parameter(list(prm.shape), dtype=prm.dtype)
+        with torch.no_grad():
+            own.copy_(prm)
+        layer.add_parameter(pname, own)
+        inner._parameters[pname] = own
+    for bname, buf in list(inner._buffers.items()):
+        if buf is not None:
+            layer.register_buffer(bname, buf, persistable=bname not in inner._non_persistent_buffers_set)
+    return inner
+
+
+class _TrainFollows:
+    """Mixin: the adopted torch module follows this layer's train / eval mode."""
+    _inner_attr = "_m"
+
+    def train(self, mode=True):
+        getattr(self, self._inner_attr).train(mode)
+        return super().train(mode)
+
+    def eval(self):
+        getattr(self, self._inner_attr).eval()
+        return super().eval()
+
+    def _apply(self, fn, *args, **kwargs):
+        out = super()._apply(fn, *args, **kwargs)
+        inner = getattr(self, self._inner_attr)
+        for n in list(inner._parameters):               # a cast / move may have replaced tensors: share them again
+            if n in self._parameters:
+                inner._parameters[n] = self._parameters[n]
+        for n in list(inner._buffers):
+            if n in self._buffers:
+                inner._buffers[n] = self._buffers[n]
+        if hasattr(inner, "_flat_weights_names"):
+            inner._flat_weights = [inner._parameters.get(n) for n in inner._flat_weights_names]
+        self.__dict__.pop("_flat_for", None)
+        return out
+
+
 # ---------------------------------------------------------------------------------------------- recurrent layers
-class _RNNBase(Layer):
+class _RNNBase(_TrainFollows, Layer):
     _mode = "LSTM"
+    _inner_attr = "_rnn"
 
     def __init__(self, input_size, hidden_size, num_layers=1, direction="forward", time_major=False, dropout=0.0,
                  weight_ih_attr=None, weight_hh_attr=None, bias_ih_attr=None, bias_hh_attr=None, name=None, activation="tanh"):
@@ -63,9 +110,6 @@ class _RNNBase(Layer):
             return out, st
         return self._rnn(inputs, initial_states)
 
-    def train(self, mode=True):
-        self._rnn.train(mode)               # dropout between the layers follows this layer's mode
-        return super().train(mode)
 
 
 class LSTM(_RNNBase):
@@ -80,13 +124,14 @@ class SimpleRNN(_RNNBase):
     _mode = "RNN"
 
 
-class _CellBase(Layer):
+class _CellBase(_TrainFollows, Layer):
     _cls = torch.nn.LSTMCell
+    _inner_attr = "_cell"
 
     def __init__(self, input_size, hidden_size, weight_ih_attr=None, weight_hh_attr=None, bias_ih_attr=None,
                  bias_hh_attr=None, name=None, **kw):
         super().__init__()
-        self._cell = self._cls(input_size, hidden_size, bias=bias_ih_attr is not False, **kw)
+        _adopt(self, self._cls(input_size, hidden_size, bias=bias_ih_attr is not False, **kw), "_cell")
         self.input_size, self.hidden_size = input_size, hidden_size
 
     @property
@@ -220,11 +265,11 @@ class Transformer(Layer):
 # ---------------------------------------------------------------------------------------------- thin torch-backed layers
 def _wrap(name, factory, doc=""):
     """Layer whose forward is a torch module built from Paddle-style constructor arguments by ``factory``."""
-    class _W(Layer):
+    class _W(_TrainFollows, Layer):
         def __init__(self, *args, **kwargs):
             super().__init__()
             kwargs.pop("name", None)
-            self._m = factory(*args, **kwargs)
+            _adopt(self, factory(*args, **kwargs), "_m")
 
         def forward(self, *x):
             return self._m(*x)

@@ -159,5 +159,18 @@ def test_layer_parameter_names_and_layouts_match_the_reference():
     assert tuple(out.shape) == (2, 5, 8) and tuple(h.shape) == (1, 5, 8)
     out, _ = nn.LSTM(4, 8)(xs, sequence_length=torch.tensor([5, 3]))
     assert float(out[1, 3:].abs().sum()) == 0.0                                            # padded steps produce zeros
+    assert set(keys(nn.LSTMCell(4, 8))) == {"weight_ih", "weight_hh", "bias_ih", "bias_hh"} == set(keys(nn.GRUCell(4, 8)))
+    assert set(keys(nn.Conv1DTranspose(4, 8, 3))) == {"weight", "bias"} == set(keys(nn.Bilinear(4, 8, 3)))
+    import inspect
+    for name in dir(nn):                                   # no layer leaks a wrapper prefix into its state dict
+        cls = getattr(nn, name)
+        if inspect.isclass(cls) and issubclass(cls, torch.nn.Module):
+            for args in ((), (4,), (4, 8), (4, 8, 3), (8, 2), (8, 2, 16)):
+                try:
+                    layer = cls(*args)
+                except Exception:  # noqa: BLE001  (constructor needs other arguments)
+                    continue
+                assert not any(k.startswith("_m.") or k.startswith("_cell.") or k.startswith("_rnn.") or "._m." in k for k in layer.state_dict()), name
+                break
     m = nn.Sequential(nn.Linear(3, 4), nn.LSTM(4, 8))
     assert "1.weight_ih_l0" in m.state_dict() and len(list(m.parameters())) == 6
