@@ -38,8 +38,9 @@ class Embedding(Layer):
         self._num_embeddings, self._embedding_dim = num_embeddings, embedding_dim
         self._padding_idx = None if padding_idx is None else (padding_idx if padding_idx >= 0 else num_embeddings + padding_idx)
         self._sparse = bool(sparse)
-        self.weight = self.create_parameter([num_embeddings, embedding_dim], attr=weight_attr, dtype=self._dtype,
-                                            default_initializer=I.Normal(0.0, 1.0) if weight_attr is None else None)
+        # no layer-specific default: create_parameter's own (Xavier uniform over [num_embeddings, embedding_dim]), as in
+        # the reference (python/paddle/nn/layer/common.py Embedding -> LayerHelperBase.create_parameter)
+        self.weight = self.create_parameter([num_embeddings, embedding_dim], attr=weight_attr, dtype=self._dtype)
         self.weight._is_sparse_grad = self._sparse      # DataParallel's reducer routes it through the sparse path
         if self._padding_idx is not None:
             with torch.no_grad():

@@ -174,3 +174,24 @@ def test_layer_parameter_names_and_layouts_match_the_reference():
                 break
     m = nn.Sequential(nn.Linear(3, 4), nn.LSTM(4, 8))
     assert "1.weight_ih_l0" in m.state_dict() and len(list(m.parameters())) == 6
+
+
+def test_default_initializers_follow_the_reference():
+    """Linear / Embedding: Xavier uniform over [fan_in, fan_out] = weight shape; Conv: N(0, sqrt(2 / (in * kh * kw)));
+    biases zero (reference: LayerHelperBase.create_parameter, nn/layer/conv.py _get_default_param_initializer)."""
+    import math
+    nn, I = paddle.nn, paddle.nn.initializer
+    paddle.seed(0)
+    w = nn.Linear(400, 600).weight.detach()
+    assert abs(float(w.abs().max()) - math.sqrt(6 / 1000)) < 1e-3 and float(nn.Linear(4, 4).bias.detach().abs().sum()) == 0
+    assert abs(float(nn.Embedding(1000, 64).weight.detach().abs().max()) - math.sqrt(6 / 1064)) < 1e-3
+    assert abs(float(nn.Conv2D(16, 32, 3).weight.detach().std()) - math.sqrt(2 / (16 * 9))) < 5e-3
+    mk = lambda shape, init: paddle.create_parameter(shape, "float32", default_initializer=init).detach()   # noqa: E731
+    assert abs(float(mk([300, 500], I.KaimingNormal()).std()) - math.sqrt(2 / 300)) < 2e-3
+    assert abs(float(mk([300, 500], I.KaimingUniform()).abs().max()) - math.sqrt(6 / 300)) < 1e-3
+    assert abs(float(mk([64, 32, 3, 3], I.XavierNormal()).std()) - math.sqrt(2 / (32 * 9 + 64 * 9))) < 2e-3
+    assert float(mk([300, 500], I.TruncatedNormal(0.0, 1.0)).abs().max()) <= 2.0 + 1e-6
+    t = mk([6, 6], I.Orthogonal())
+    assert float((t @ t.t() - torch.eye(6)).abs().max()) < 1e-5
+    assert float((mk([4, 4], I.Assign(torch.eye(4))) - torch.eye(4)).abs().sum()) == 0
+    assert float(mk([3], I.Constant(2.5)).sum()) == 7.5 and abs(float(mk([2000], I.Uniform(-0.5, 0.5)).abs().max()) - 0.5) < 5e-3
