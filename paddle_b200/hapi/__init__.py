@@ -148,7 +148,13 @@ class Model:
                 break
         res = {"loss": [float(np.mean(losses))] if losses else []}
         for m in self._metrics:
-            res[m.name()] = m.accumulate()
+            names, vals = m.name(), m.accumulate()
+            names = names if isinstance(names, (list, tuple)) else [names]
+            vals = vals if isinstance(vals, (list, tuple)) else [vals]
+            if len(names) == 1:
+                res[names[0]] = vals[0] if len(vals) == 1 else list(vals)
+            else:
+                res.update(dict(zip(names, vals)))
         return res
 
     def predict(self, test_data, batch_size=1, num_workers=0, stack_outputs=False, verbose=1, callbacks=None):

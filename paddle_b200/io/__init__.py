@@ -193,6 +193,22 @@ def default_collate_fn(batch):
     raise TypeError(f"batch data can only contains: tensor, numpy.ndarray, dict, list, number, but got {type(s)}")
 
 
+def default_convert_fn(sample):
+    """``batch_size=None``: no batching, the fields of one sample become tensors as they are (reference:
+    python/paddle/io/dataloader/collate.py default_convert_fn)."""
+    if isinstance(sample, torch.Tensor):
+        return sample
+    if isinstance(sample, np.ndarray):
+        return torch.from_numpy(np.array(sample))
+    if isinstance(sample, (str, bytes)):
+        return sample
+    if isinstance(sample, dict):
+        return {k: default_convert_fn(v) for k, v in sample.items()}
+    if isinstance(sample, (list, tuple)):
+        return [default_convert_fn(v) for v in sample]
+    return sample
+
+
 class DataLoader:
     def __init__(self, dataset, feed_list=None, places=None, return_list=True, batch_sampler=None, batch_size=1,
                  shuffle=False, drop_last=False, collate_fn=None, num_workers=0, use_buffer_reader=True,
@@ -209,6 +225,7 @@ class DataLoader:
         else:
             if batch_sampler is None:
                 if batch_size is None:
+                    kw["collate_fn"] = collate_fn or default_convert_fn
                     self._loader = tud.DataLoader(dataset, batch_size=None, shuffle=shuffle, **kw)
                     return
                 batch_sampler = BatchSampler(dataset, shuffle=shuffle, batch_size=batch_size, drop_last=drop_last)

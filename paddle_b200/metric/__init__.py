@@ -26,8 +26,13 @@ class Accuracy(Metric):
     def __init__(self, topk=(1,), name=None, *args, **kwargs):
         self.topk = tuple(topk)
         self.maxk = max(self.topk)
-        self._name = name or "acc"
+        base = name or "acc"
+        # one name per k, as the reference reports them (metrics.py Accuracy._init_name)
+        self._name = [f"{base}_top{k}" for k in self.topk] if self.maxk != 1 else [base]
         self.reset()
+
+    def name(self):
+        return self._name
 
     def compute(self, pred, label, *args):
         idx = torch.argsort(pred, dim=-1, descending=True)[..., : self.maxk]
