@@ -208,133 +208,11 @@ def rms_norm(x, weight, epsilon=1e-6):
     return ops.rms_norm(x, weight, epsilon)
 
 
-def batch_norm(x, running_mean, running_var, weight=None, bias=None, training=False, momentum=0.9, epsilon=1e-05,
-               data_format="NCHW", use_global_stats=None, name=None):
-    use_batch = training and not use_global_stats
-    if data_format in ("NHWC", "NLC", "NDHWC"):
-        perm = [0, x.dim() - 1] + list(range(1, x.dim() - 1))
-        inv = [0] + list(range(2, x.dim())) + [1]
-        return TF.batch_norm(x.permute(perm), running_mean, running_var, weight, bias, use_batch, 1.0 - momentum,
-                             epsilon).permute(inv)
-    return TF.batch_norm(x, running_mean, running_var, weight, bias, use_batch, 1.0 - momentum, epsilon)
-
-
-def instance_norm(x, running_mean=None, running_var=None, weight=None, bias=None, use_input_stats=True, momentum=0.9,
-                  eps=1e-05, data_format="NCHW", name=None):
-    return TF.instance_norm(x, running_mean, running_var, weight, bias, use_input_stats, 1.0 - momentum, eps)
-
-
-def group_norm(x, num_groups, epsilon=1e-05, weight=None, bias=None, data_format="NCHW", name=None):
-    return TF.group_norm(x, num_groups, weight, bias, epsilon)
-
-
 def normalize(x, p=2, axis=1, epsilon=1e-12, name=None):
     return TF.normalize(x, p=p, dim=axis, eps=epsilon)
 
 
-def local_response_norm(x, size, alpha=1e-4, beta=0.75, k=1.0, data_format="NCHW", name=None):
-    return TF.local_response_norm(x, size, alpha, beta, k)
-
-
 # ------------------------------------------------------------------ conv / pool
-def _pad_arg(padding, nd):
-    if isinstance(padding, str):
-        return padding.lower()
-    if isinstance(padding, int):
-        return padding
-    padding = list(padding)
-    if len(padding) == nd:
-        return tuple(int(p) for p in padding)
-    if len(padding) == 2 * nd:
-        if all(padding[2 * i] == padding[2 * i + 1] for i in range(nd)):
-            return tuple(int(padding[2 * i]) for i in range(nd))
-        raise NotImplementedError("asymmetric conv padding: pad explicitly with F.pad")
-    return tuple(int(p) for p in padding)
-
-
-def conv1d(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, data_format="NCL", name=None):
-    return TF.conv1d(x, weight, bias, stride, _pad_arg(padding, 1), dilation, groups)
-
-
-def conv2d(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, data_format="NCHW", name=None):
-    if data_format == "NHWC":
-        return TF.conv2d(x.permute(0, 3, 1, 2), weight, bias, stride, _pad_arg(padding, 2), dilation, groups).permute(0, 2, 3, 1)
-    return TF.conv2d(x, weight, bias, stride, _pad_arg(padding, 2), dilation, groups)
-
-
-def conv3d(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, data_format="NCDHW", name=None):
-    return TF.conv3d(x, weight, bias, stride, _pad_arg(padding, 3), dilation, groups)
-
-
-def conv2d_transpose(x, weight, bias=None, stride=1, padding=0, output_padding=0, dilation=1, groups=1,
-                     output_size=None, data_format="NCHW", name=None):
-    return TF.conv_transpose2d(x, weight, bias, stride, _pad_arg(padding, 2), output_padding, groups, dilation)
-
-
-def conv1d_transpose(x, weight, bias=None, stride=1, padding=0, output_padding=0, groups=1, dilation=1,
-                     output_size=None, data_format="NCL", name=None):
-    return TF.conv_transpose1d(x, weight, bias, stride, _pad_arg(padding, 1), output_padding, groups, dilation)
-
-
-def max_pool2d(x, kernel_size, stride=None, padding=0, return_mask=False, ceil_mode=False, data_format="NCHW", name=None):
-    return TF.max_pool2d(x, kernel_size, stride, _pad_arg(padding, 2), ceil_mode=ceil_mode, return_indices=return_mask)
-
-
-def avg_pool2d(x, kernel_size, stride=None, padding=0, ceil_mode=False, exclusive=True, divisor_override=None,
-               data_format="NCHW", name=None):
-    return TF.avg_pool2d(x, kernel_size, stride, _pad_arg(padding, 2), ceil_mode, not exclusive, divisor_override)
-
-
-def max_pool1d(x, kernel_size, stride=None, padding=0, return_mask=False, ceil_mode=False, name=None):
-    return TF.max_pool1d(x, kernel_size, stride, _pad_arg(padding, 1), ceil_mode=ceil_mode, return_indices=return_mask)
-
-
-def avg_pool1d(x, kernel_size, stride=None, padding=0, exclusive=True, ceil_mode=False, name=None):
-    return TF.avg_pool1d(x, kernel_size, stride, _pad_arg(padding, 1), ceil_mode, not exclusive)
-
-
-def adaptive_avg_pool2d(x, output_size, data_format="NCHW", name=None):
-    return TF.adaptive_avg_pool2d(x, output_size)
-
-
-def adaptive_max_pool2d(x, output_size, return_mask=False, name=None):
-    return TF.adaptive_max_pool2d(x, output_size, return_mask)
-
-
-def adaptive_avg_pool1d(x, output_size, name=None):
-    return TF.adaptive_avg_pool1d(x, output_size)
-
-
-def interpolate(x, size=None, scale_factor=None, mode="nearest", align_corners=False, align_mode=0,
-                data_format="NCHW", name=None):
-    kw = {}
-    if mode in ("linear", "bilinear", "bicubic", "trilinear"):
-        kw["align_corners"] = align_corners
-    return TF.interpolate(x, size=size, scale_factor=scale_factor, mode=mode, **kw)
-
-
-upsample = interpolate
-
-
-def pad(x, pad, mode="constant", value=0.0, data_format="NCHW", name=None):
-    pad = [int(p) for p in (pad.tolist() if isinstance(pad, torch.Tensor) else pad)]
-    if len(pad) == 2 * x.dim():
-        # paddle: per-dim (before, after) from the first dim; torch wants last dim first
-        tp = []
-        for i in range(x.dim() - 1, -1, -1):
-            tp += [pad[2 * i], pad[2 * i + 1]]
-        pad = tp
-    return TF.pad(x, pad, mode=mode, value=value) if mode == "constant" else TF.pad(x, pad, mode=mode)
-
-
-def unfold(x, kernel_sizes, strides=1, paddings=0, dilations=1, name=None):
-    return TF.unfold(x, kernel_sizes, dilations, paddings, strides)
-
-
-def pixel_shuffle(x, upscale_factor, data_format="NCHW", name=None):
-    return TF.pixel_shuffle(x, upscale_factor)
-
-
 def grid_sample(x, grid, mode="bilinear", padding_mode="zeros", align_corners=True, name=None):
     return TF.grid_sample(x, grid, mode, padding_mode, align_corners)
 
@@ -466,6 +344,7 @@ def sequence_mask(x, maxlen=None, dtype="int64", name=None):
 
 
 from .extra import *  # noqa: E402,F401,F403
+from .conv_pool import *  # noqa: E402,F401,F403
 from .extra import _inplace as _mk_inplace  # noqa: E402
 
 elu_, hardtanh_, leaky_relu_, softmax_, tanh_, thresholded_relu_ = (_mk_inplace(f) for f in (elu, hardtanh, leaky_relu, softmax, tanh, thresholded_relu))

@@ -6,11 +6,6 @@ import torch
 import torch.nn.functional as TF
 
 
-def conv3d_transpose(x, weight, bias=None, stride=1, padding=0, output_padding=0, groups=1, dilation=1, output_size=None,
-                     data_format="NCDHW", name=None):
-    return TF.conv_transpose3d(x, weight, bias, stride, padding, output_padding, groups, dilation)
-
-
 def pairwise_distance(x, y, p=2.0, epsilon=1e-6, keepdim=False, name=None):
     return TF.pairwise_distance(x, y, p, epsilon, keepdim)
 
@@ -22,52 +17,6 @@ def _inplace(fn):
         return x
     f.__name__ = fn.__name__ + "_"
     return f
-
-
-def zeropad2d(x, padding, data_format="NCHW", name=None):
-    l, r, t, b = padding
-    return TF.pad(x, (l, r, t, b))
-
-
-def avg_pool3d(x, kernel_size, stride=None, padding=0, ceil_mode=False, exclusive=True, divisor_override=None,
-               data_format="NCDHW", name=None):
-    return TF.avg_pool3d(x, kernel_size, stride, padding, ceil_mode, not exclusive, divisor_override)
-
-
-def max_pool3d(x, kernel_size, stride=None, padding=0, return_mask=False, ceil_mode=False, data_format="NCDHW", name=None):
-    return TF.max_pool3d(x, kernel_size, stride, padding, ceil_mode=ceil_mode, return_indices=return_mask)
-
-
-def lp_pool1d(x, norm_type, kernel_size, stride=None, padding=0, ceil_mode=False, data_format="NCL", name=None):
-    return TF.lp_pool1d(x, float(norm_type), kernel_size, stride, ceil_mode)
-
-
-def lp_pool2d(x, norm_type, kernel_size, stride=None, padding=0, ceil_mode=False, data_format="NCHW", name=None):
-    return TF.lp_pool2d(x, float(norm_type), kernel_size, stride, ceil_mode)
-
-
-def max_unpool1d(x, indices, kernel_size, stride=None, padding=0, data_format="NCL", output_size=None, name=None):
-    return TF.max_unpool1d(x, indices.long(), kernel_size, stride, padding, output_size)
-
-
-def max_unpool2d(x, indices, kernel_size, stride=None, padding=0, data_format="NCHW", output_size=None, name=None):
-    return TF.max_unpool2d(x, indices.long(), kernel_size, stride, padding, output_size)
-
-
-def max_unpool3d(x, indices, kernel_size, stride=None, padding=0, data_format="NCDHW", output_size=None, name=None):
-    return TF.max_unpool3d(x, indices.long(), kernel_size, stride, padding, output_size)
-
-
-def adaptive_avg_pool3d(x, output_size, data_format="NCDHW", name=None):
-    return TF.adaptive_avg_pool3d(x, output_size)
-
-
-def adaptive_max_pool1d(x, output_size, return_mask=False, name=None):
-    return TF.adaptive_max_pool1d(x, output_size, return_indices=return_mask)
-
-
-def adaptive_max_pool3d(x, output_size, return_mask=False, name=None):
-    return TF.adaptive_max_pool3d(x, output_size, return_indices=return_mask)
 
 
 def fractional_max_pool2d(x, output_size, kernel_size=None, random_u=None, return_mask=False, name=None):
@@ -179,18 +128,6 @@ def class_center_sample(label, num_classes, num_samples, group=None):
 
 def affine_grid(theta, out_shape, align_corners=True, name=None):
     return TF.affine_grid(theta, list(out_shape), align_corners=align_corners)
-
-
-def pixel_unshuffle(x, downscale_factor, data_format="NCHW", name=None):
-    return TF.pixel_unshuffle(x, downscale_factor)
-
-
-def channel_shuffle(x, groups, data_format="NCHW", name=None):
-    return TF.channel_shuffle(x, groups)
-
-
-def fold(x, output_sizes, kernel_sizes, strides=1, paddings=0, dilations=1, name=None):
-    return TF.fold(x, output_sizes, kernel_sizes, dilations, paddings, strides)
 
 
 def gather_tree(ids, parents):

@@ -77,27 +77,6 @@ class Flatten(Layer):
         return torch.flatten(x, self.start_axis, self.stop_axis)
 
 
-class Pad2D(Layer):
-    def __init__(self, padding, mode="constant", value=0.0, data_format="NCHW", name=None):
-        super().__init__()
-        self.padding = [padding] * 4 if isinstance(padding, int) else list(padding)
-        self.mode, self.value = mode, value
-
-    def forward(self, x):
-        return torch.nn.functional.pad(x, self.padding, mode=self.mode, value=self.value) if self.mode == "constant" \
-            else torch.nn.functional.pad(x, self.padding, mode=self.mode)
-
-
-class Upsample(Layer):
-    def __init__(self, size=None, scale_factor=None, mode="nearest", align_corners=False, align_mode=0,
-                 data_format="NCHW", name=None):
-        super().__init__()
-        self.size, self.scale_factor, self.mode, self.align_corners = size, scale_factor, mode, align_corners
-
-    def forward(self, x):
-        return F.interpolate(x, self.size, self.scale_factor, self.mode, self.align_corners)
-
-
 # ------------------------------------------------------------------ norms
 class LayerNorm(Layer):
     def __init__(self, normalized_shape, epsilon=1e-05, weight_attr=None, bias_attr=None, name=None):
@@ -234,7 +213,7 @@ class _SyncBNFn(torch.autograd.Function):
         rstd = torch.rsqrt(var + eps)
         with torch.no_grad():
             rmean.mul_(momentum).add_(mean, alpha=1 - momentum)
-            rvar.mul_(momentum).add_(var * n / (n - 1).clamp(min=1), alpha=1 - momentum)
+            rvar.mul_(momentum).add_(var, alpha=1 - momentum)     # biased, as sync_batch_norm_utils.h:95-106
         shp = [1, C] + [1] * (x.dim() - 2)
         xhat = (xf - mean.reshape(shp)) * rstd.reshape(shp)
         y = xhat * w.float().reshape(shp) + b.float().reshape(shp)
@@ -259,152 +238,7 @@ class _SyncBNFn(torch.autograd.Function):
         return dx.to(dy.dtype), dw.to(w.dtype), db.to(w.dtype), None, None, None, None
 
 
-class GroupNorm(Layer):
-    def __init__(self, num_groups, num_channels, epsilon=1e-05, weight_attr=None, bias_attr=None, data_format="NCHW", name=None):
-        super().__init__()
-        self._num_groups, self._epsilon = num_groups, epsilon
-        self.weight = None if weight_attr is False else self.create_parameter([num_channels], attr=weight_attr, default_initializer=I.Constant(1.0))
-        self.bias = None if bias_attr is False else self.create_parameter([num_channels], attr=bias_attr, is_bias=True)
-
-    def forward(self, x):
-        return F.group_norm(x, self._num_groups, self._epsilon, self.weight, self.bias)
-
-
-class InstanceNorm2D(Layer):
-    def __init__(self, num_features, epsilon=1e-05, momentum=0.9, weight_attr=None, bias_attr=None, data_format="NCHW", name=None):
-        super().__init__()
-        self._epsilon = epsilon
-        self.scale = None if weight_attr is False else self.create_parameter([num_features], attr=weight_attr, default_initializer=I.Constant(1.0))
-        self.bias = None if bias_attr is False else self.create_parameter([num_features], attr=bias_attr, is_bias=True)
-
-    def forward(self, x):
-        return F.instance_norm(x, weight=self.scale, bias=self.bias, eps=self._epsilon)
-
-
 # ------------------------------------------------------------------ conv / pool
-class _ConvNd(Layer):
-    def __init__(self, nd, in_channels, out_channels, kernel_size, stride=1, padding=0, dilation=1, groups=1,
-                 padding_mode="zeros", weight_attr=None, bias_attr=None, data_format=None, transposed=False,
-                 output_padding=0):
-        super().__init__()
-        tup = lambda v: tuple(v) if isinstance(v, (list, tuple)) else (v,) * nd  # noqa: E731
-        self._nd, self._in, self._out = nd, in_channels, out_channels
-        self._kernel_size, self._stride, self._dilation = tup(kernel_size), tup(stride), tup(dilation)
-        self._padding, self._groups, self._data_format = padding, groups, data_format
-        self._transposed, self._output_padding = transposed, output_padding
-        wshape = ([in_channels, out_channels // groups] if transposed else [out_channels, in_channels // groups]) + list(self._kernel_size)
-        fan_in = (in_channels // groups) * int(math.prod(self._kernel_size))
-        self.weight = self.create_parameter(wshape, attr=weight_attr,
-                                            default_initializer=I.Normal(0.0, math.sqrt(2.0 / fan_in)))
-        self.bias = self.create_parameter([out_channels], attr=bias_attr, is_bias=True)
-
-
-class Conv1D(_ConvNd):
-    def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=0, dilation=1, groups=1,
-                 padding_mode="zeros", weight_attr=None, bias_attr=None, data_format="NCL"):
-        super().__init__(1, in_channels, out_channels, kernel_size, stride, padding, dilation, groups, padding_mode,
-                         weight_attr, bias_attr, data_format)
-
-    def forward(self, x):
-        return F.conv1d(x, self.weight, self.bias, self._stride, self._padding, self._dilation, self._groups)
-
-
-class Conv2D(_ConvNd):
-    def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=0, dilation=1, groups=1,
-                 padding_mode="zeros", weight_attr=None, bias_attr=None, data_format="NCHW"):
-        super().__init__(2, in_channels, out_channels, kernel_size, stride, padding, dilation, groups, padding_mode,
-                         weight_attr, bias_attr, data_format)
-
-    def forward(self, x):
-        return F.conv2d(x, self.weight, self.bias, self._stride, self._padding, self._dilation, self._groups,
-                        self._data_format)
-
-
-class Conv3D(_ConvNd):
-    def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=0, dilation=1, groups=1,
-                 padding_mode="zeros", weight_attr=None, bias_attr=None, data_format="NCDHW"):
-        super().__init__(3, in_channels, out_channels, kernel_size, stride, padding, dilation, groups, padding_mode,
-                         weight_attr, bias_attr, data_format)
-
-    def forward(self, x):
-        return F.conv3d(x, self.weight, self.bias, self._stride, self._padding, self._dilation, self._groups)
-
-
-class Conv2DTranspose(_ConvNd):
-    def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=0, output_padding=0, groups=1,
-                 dilation=1, weight_attr=None, bias_attr=None, data_format="NCHW"):
-        super().__init__(2, in_channels, out_channels, kernel_size, stride, padding, dilation, groups, "zeros",
-                         weight_attr, bias_attr, data_format, transposed=True, output_padding=output_padding)
-
-    def forward(self, x, output_size=None):
-        return F.conv2d_transpose(x, self.weight, self.bias, self._stride, self._padding, self._output_padding,
-                                  self._dilation, self._groups)
-
-
-class MaxPool2D(Layer):
-    def __init__(self, kernel_size, stride=None, padding=0, return_mask=False, ceil_mode=False, data_format="NCHW", name=None):
-        super().__init__()
-        self.k, self.s, self.p, self.rm, self.cm = kernel_size, stride, padding, return_mask, ceil_mode
-
-    def forward(self, x):
-        return F.max_pool2d(x, self.k, self.s, self.p, self.rm, self.cm)
-
-
-class AvgPool2D(Layer):
-    def __init__(self, kernel_size, stride=None, padding=0, ceil_mode=False, exclusive=True, divisor_override=None,
-                 data_format="NCHW", name=None):
-        super().__init__()
-        self.k, self.s, self.p, self.cm, self.ex, self.do = kernel_size, stride, padding, ceil_mode, exclusive, divisor_override
-
-    def forward(self, x):
-        return F.avg_pool2d(x, self.k, self.s, self.p, self.cm, self.ex, self.do)
-
-
-class MaxPool1D(Layer):
-    def __init__(self, kernel_size, stride=None, padding=0, return_mask=False, ceil_mode=False, name=None):
-        super().__init__()
-        self.k, self.s, self.p, self.rm, self.cm = kernel_size, stride, padding, return_mask, ceil_mode
-
-    def forward(self, x):
-        return F.max_pool1d(x, self.k, self.s, self.p, self.rm, self.cm)
-
-
-class AvgPool1D(Layer):
-    def __init__(self, kernel_size, stride=None, padding=0, exclusive=True, ceil_mode=False, name=None):
-        super().__init__()
-        self.k, self.s, self.p, self.ex, self.cm = kernel_size, stride, padding, exclusive, ceil_mode
-
-    def forward(self, x):
-        return F.avg_pool1d(x, self.k, self.s, self.p, self.ex, self.cm)
-
-
-class AdaptiveAvgPool2D(Layer):
-    def __init__(self, output_size, data_format="NCHW", name=None):
-        super().__init__()
-        self.output_size = output_size
-
-    def forward(self, x):
-        return F.adaptive_avg_pool2d(x, self.output_size)
-
-
-class AdaptiveMaxPool2D(Layer):
-    def __init__(self, output_size, return_mask=False, name=None):
-        super().__init__()
-        self.output_size, self.return_mask = output_size, return_mask
-
-    def forward(self, x):
-        return F.adaptive_max_pool2d(x, self.output_size, self.return_mask)
-
-
-class AdaptiveAvgPool1D(Layer):
-    def __init__(self, output_size, name=None):
-        super().__init__()
-        self.output_size = output_size
-
-    def forward(self, x):
-        return F.adaptive_avg_pool1d(x, self.output_size)
-
-
 # ------------------------------------------------------------------ activations
 def _act_layer(name, fn, **defaults):
     class _A(Layer):

@@ -282,35 +282,7 @@ def _bias(bias_attr):
     return bias_attr is not False
 
 
-Conv1DTranspose = _wrap("Conv1DTranspose", lambda i, o, k, stride=1, padding=0, output_padding=0, groups=1, dilation=1,
-                        weight_attr=None, bias_attr=None, data_format="NCL": torch.nn.ConvTranspose1d(
-                            i, o, k, stride, padding, output_padding, groups, _bias(bias_attr), dilation))
-Conv3DTranspose = _wrap("Conv3DTranspose", lambda i, o, k, stride=1, padding=0, output_padding=0, dilation=1, groups=1,
-                        weight_attr=None, bias_attr=None, data_format="NCDHW": torch.nn.ConvTranspose3d(
-                            i, o, k, stride, padding, output_padding, groups, _bias(bias_attr), dilation))
-MaxPool3D = _wrap("MaxPool3D", lambda kernel_size, stride=None, padding=0, ceil_mode=False, return_mask=False,
-                  data_format="NCDHW": torch.nn.MaxPool3d(kernel_size, stride, padding, ceil_mode=ceil_mode,
-                                                          return_indices=return_mask))
-AvgPool3D = _wrap("AvgPool3D", lambda kernel_size, stride=None, padding=0, ceil_mode=False, exclusive=True,
-                  divisor_override=None, data_format="NCDHW": torch.nn.AvgPool3d(
-                      kernel_size, stride, padding, ceil_mode, count_include_pad=not exclusive, divisor_override=divisor_override))
-AdaptiveAvgPool3D = _wrap("AdaptiveAvgPool3D", lambda output_size, data_format="NCDHW": torch.nn.AdaptiveAvgPool3d(output_size))
-AdaptiveMaxPool1D = _wrap("AdaptiveMaxPool1D", lambda output_size, return_mask=False: torch.nn.AdaptiveMaxPool1d(
-    output_size, return_indices=return_mask))
-PixelShuffle = _wrap("PixelShuffle", lambda upscale_factor, data_format="NCHW": torch.nn.PixelShuffle(upscale_factor))
-PixelUnshuffle = _wrap("PixelUnshuffle", lambda downscale_factor, data_format="NCHW": torch.nn.PixelUnshuffle(downscale_factor))
-ChannelShuffle = _wrap("ChannelShuffle", lambda groups, data_format="NCHW": torch.nn.ChannelShuffle(groups))
-Unfold = _wrap("Unfold", lambda kernel_sizes, dilations=1, paddings=0, strides=1: torch.nn.Unfold(
-    kernel_sizes, dilations, paddings, strides))
-Fold = _wrap("Fold", lambda output_sizes, kernel_sizes, dilations=1, paddings=0, strides=1: torch.nn.Fold(
-    output_sizes, kernel_sizes, dilations, paddings, strides))
 Unflatten = _wrap("Unflatten", lambda axis, shape: torch.nn.Unflatten(axis, tuple(shape)))
-LocalResponseNorm = _wrap("LocalResponseNorm", lambda size, alpha=1e-4, beta=0.75, k=1.0, data_format="NCHW":
-                          torch.nn.LocalResponseNorm(size, alpha, beta, k))
-InstanceNorm1D = _wrap("InstanceNorm1D", lambda num_features, epsilon=1e-5, momentum=0.9, weight_attr=None, bias_attr=None,
-                       data_format="NCL": torch.nn.InstanceNorm1d(num_features, epsilon, affine=weight_attr is not False))
-InstanceNorm3D = _wrap("InstanceNorm3D", lambda num_features, epsilon=1e-5, momentum=0.9, weight_attr=None, bias_attr=None,
-                       data_format="NCDHW": torch.nn.InstanceNorm3d(num_features, epsilon, affine=weight_attr is not False))
 AlphaDropout = _wrap("AlphaDropout", lambda p=0.5: torch.nn.AlphaDropout(p))
 Dropout3D = _wrap("Dropout3D", lambda p=0.5, data_format="NCDHW": torch.nn.Dropout3d(p))
 Bilinear = _wrap("Bilinear", lambda in1_features, in2_features, out_features, weight_attr=None, bias_attr=None:
@@ -333,48 +305,6 @@ class CTCLoss(Layer):
 
     def forward(self, log_probs, labels, input_lengths, label_lengths, norm_by_times=False):
         return F.ctc_loss(log_probs, labels, input_lengths, label_lengths, self.blank, self.reduction)
-
-
-class _PadNd(Layer):
-    _nd = 1
-
-    def __init__(self, padding, mode="constant", value=0.0, data_format=None, name=None):
-        super().__init__()
-        self.padding = [padding] * (2 * self._nd) if isinstance(padding, int) else list(padding)
-        self.mode, self.value = mode, value
-
-    def forward(self, x):
-        mode = {"constant": "constant", "reflect": "reflect", "replicate": "replicate", "circular": "circular"}[self.mode]
-        return TF.pad(x, self.padding, mode=mode, value=self.value) if mode == "constant" else TF.pad(x, self.padding, mode=mode)
-
-
-class Pad1D(_PadNd):
-    _nd = 1
-
-
-class Pad3D(_PadNd):
-    _nd = 3
-
-
-class ZeroPad2D(_PadNd):
-    _nd = 2
-
-    def __init__(self, padding, data_format="NCHW", name=None):
-        super().__init__(padding, "constant", 0.0)
-
-
-class UpsamplingNearest2D(Layer):
-    def __init__(self, size=None, scale_factor=None, data_format="NCHW", name=None):
-        super().__init__()
-        self.size, self.scale_factor = size, scale_factor
-
-    def forward(self, x):
-        return TF.interpolate(x, size=self.size, scale_factor=self.scale_factor, mode="nearest")
-
-
-class UpsamplingBilinear2D(UpsamplingNearest2D):
-    def forward(self, x):
-        return TF.interpolate(x, size=self.size, scale_factor=self.scale_factor, mode="bilinear", align_corners=True)
 
 
 class SpectralNorm(Layer):
@@ -435,8 +365,6 @@ class HSigmoidLoss(Layer):
 
 # ---------------------------------------------------------------------------------------------- remaining layers
 RNNCellBase = _CellBase
-AdaptiveMaxPool3D = _wrap("AdaptiveMaxPool3D", lambda output_size, return_mask=False: torch.nn.AdaptiveMaxPool3d(
-    output_size, return_indices=return_mask))
 PoissonNLLLoss = _wrap("PoissonNLLLoss", lambda log_input=True, full=False, epsilon=1e-8, reduction="mean":
                        torch.nn.PoissonNLLLoss(log_input, full, eps=epsilon, reduction=reduction))
 GaussianNLLLoss = _wrap("GaussianNLLLoss", lambda full=False, epsilon=1e-6, reduction="mean":
@@ -446,38 +374,14 @@ MultiMarginLoss = _wrap("MultiMarginLoss", lambda p=1, margin=1.0, weight=None, 
 TripletMarginWithDistanceLoss = _wrap("TripletMarginWithDistanceLoss", lambda distance_function=None, margin=1.0, swap=False,
                                       reduction="mean": torch.nn.TripletMarginWithDistanceLoss(
                                           distance_function=distance_function, margin=margin, swap=swap, reduction=reduction))
-MaxUnPool1D = _wrap("MaxUnPool1D", lambda kernel_size, stride=None, padding=0, data_format="NCL", output_size=None:
-                    torch.nn.MaxUnpool1d(kernel_size, stride, padding))
-MaxUnPool2D = _wrap("MaxUnPool2D", lambda kernel_size, stride=None, padding=0, data_format="NCHW", output_size=None:
-                    torch.nn.MaxUnpool2d(kernel_size, stride, padding))
-MaxUnPool3D = _wrap("MaxUnPool3D", lambda kernel_size, stride=None, padding=0, data_format="NCDHW", output_size=None:
-                    torch.nn.MaxUnpool3d(kernel_size, stride, padding))
 RReLU = _wrap("RReLU", lambda lower=1.0 / 8.0, upper=1.0 / 3.0: torch.nn.RReLU(lower, upper))
 FractionalMaxPool2D = _wrap("FractionalMaxPool2D", lambda output_size, kernel_size=None, random_u=None, return_mask=False:
                             torch.nn.FractionalMaxPool2d(kernel_size or 2, output_size=output_size, return_indices=return_mask))
 FractionalMaxPool3D = _wrap("FractionalMaxPool3D", lambda output_size, kernel_size=None, random_u=None, return_mask=False:
                             torch.nn.FractionalMaxPool3d(kernel_size or 2, output_size=output_size, return_indices=return_mask))
-LPPool1D = _wrap("LPPool1D", lambda norm_type, kernel_size, stride=None, padding=0, ceil_mode=False, data_format="NCL":
-                 torch.nn.LPPool1d(float(norm_type), kernel_size, stride, ceil_mode))
-LPPool2D = _wrap("LPPool2D", lambda norm_type, kernel_size, stride=None, padding=0, ceil_mode=False, data_format="NCHW":
-                 torch.nn.LPPool2d(float(norm_type), kernel_size, stride, ceil_mode))
 AdaptiveLogSoftmaxWithLoss = _wrap("AdaptiveLogSoftmaxWithLoss", lambda in_features, n_classes, cutoffs, div_value=4.0,
                                    head_bias=False: torch.nn.AdaptiveLogSoftmaxWithLoss(in_features, n_classes, cutoffs,
                                                                                         div_value, head_bias))
-
-
-class ZeroPad1D(_PadNd):
-    _nd = 1
-
-    def __init__(self, padding, data_format="NCL", name=None):
-        super().__init__(padding, "constant", 0.0)
-
-
-class ZeroPad3D(_PadNd):
-    _nd = 3
-
-    def __init__(self, padding, data_format="NCDHW", name=None):
-        super().__init__(padding, "constant", 0.0)
 
 
 class RNNTLoss(Layer):
