@@ -391,74 +391,3 @@ class CosineSimilarity(Layer):
 
 
 # ------------------------------------------------------------------ attention / transformer
-class MultiHeadAttention(Layer):
-    """Reference: python/paddle/nn/layer/transformer.py MultiHeadAttention ([b, s, e] inputs)."""
-
-    def __init__(self, embed_dim, num_heads, dropout=0.0, kdim=None, vdim=None, need_weights=False, weight_attr=None,
-                 bias_attr=None):
-        super().__init__()
-        self.embed_dim, self.num_heads, self.dropout = embed_dim, num_heads, dropout
-        self.head_dim = embed_dim // num_heads
-        self.need_weights = need_weights
-        self.q_proj = Linear(embed_dim, embed_dim, weight_attr, bias_attr)
-        self.k_proj = Linear(kdim or embed_dim, embed_dim, weight_attr, bias_attr)
-        self.v_proj = Linear(vdim or embed_dim, embed_dim, weight_attr, bias_attr)
-        self.out_proj = Linear(embed_dim, embed_dim, weight_attr, bias_attr)
-
-    def forward(self, query, key=None, value=None, attn_mask=None, cache=None):
-        key = query if key is None else key
-        value = key if value is None else value
-        b, sq, _ = query.shape
-        q = self.q_proj(query).reshape(b, sq, self.num_heads, self.head_dim)
-        k = self.k_proj(key).reshape(b, key.shape[1], self.num_heads, self.head_dim)
-        v = self.v_proj(value).reshape(b, value.shape[1], self.num_heads, self.head_dim)
-        mask = attn_mask
-        if mask is not None and mask.dtype != torch.bool:
-            mask = mask.to(q.dtype)
-        out = F.scaled_dot_product_attention(q, k, v, mask, self.dropout, False, self.training)
-        out = self.out_proj(out.reshape(b, sq, self.embed_dim))
-        return out if not self.need_weights else (out, None)
-
-
-class TransformerEncoderLayer(Layer):
-    def __init__(self, d_model, nhead, dim_feedforward, dropout=0.1, activation="relu", attn_dropout=None,
-                 act_dropout=None, normalize_before=False, weight_attr=None, bias_attr=None, layer_norm_eps=1e-5):
-        super().__init__()
-        self.normalize_before = normalize_before
-        self.self_attn = MultiHeadAttention(d_model, nhead, attn_dropout if attn_dropout is not None else dropout)
-        self.linear1 = Linear(d_model, dim_feedforward)
-        self.linear2 = Linear(dim_feedforward, d_model)
-        self.norm1 = LayerNorm(d_model, layer_norm_eps)
-        self.norm2 = LayerNorm(d_model, layer_norm_eps)
-        self.dropout = Dropout(act_dropout if act_dropout is not None else dropout)
-        self.dropout1 = Dropout(dropout)
-        self.dropout2 = Dropout(dropout)
-        self.activation = getattr(F, activation)
-
-    def forward(self, src, src_mask=None, cache=None):
-        residual = src
-        if self.normalize_before:
-            src = self.norm1(src)
-        src = residual + self.dropout1(self.self_attn(src, src, src, src_mask))
-        if not self.normalize_before:
-            src = self.norm1(src)
-        residual = src
-        if self.normalize_before:
-            src = self.norm2(src)
-        src = residual + self.dropout2(self.linear2(self.dropout(self.activation(self.linear1(src)))))
-        if not self.normalize_before:
-            src = self.norm2(src)
-        return src
-
-
-class TransformerEncoder(Layer):
-    def __init__(self, encoder_layer, num_layers, norm=None):
-        super().__init__()
-        import copy
-        self.layers = LayerList([encoder_layer if i == 0 else copy.deepcopy(encoder_layer) for i in range(num_layers)])
-        self.norm = norm
-
-    def forward(self, src, src_mask=None, cache=None):
-        for l in self.layers:
-            src = l(src, src_mask)
-        return self.norm(src) if self.norm is not None else src

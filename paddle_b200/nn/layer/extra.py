@@ -7,7 +7,7 @@ import torch
 import torch.nn.functional as TF
 
 from .. import functional as F
-from .common import Dropout, LayerNorm, Linear, MultiHeadAttention, _act_layer
+from .common import Dropout, LayerNorm, Linear, _act_layer
 from .layers import Layer, LayerList
 
 # ---------------------------------------------------------------------------------------------- activations
@@ -201,67 +201,6 @@ class BiRNN(Layer):
 
 
 # ---------------------------------------------------------------------------------------------- transformer decoder
-class TransformerDecoderLayer(Layer):
-    def __init__(self, d_model, nhead, dim_feedforward, dropout=0.1, activation="relu", attn_dropout=None,
-                 act_dropout=None, normalize_before=False, weight_attr=None, bias_attr=None, layer_norm_eps=1e-5):
-        super().__init__()
-        self.normalize_before = normalize_before
-        ad = attn_dropout if attn_dropout is not None else dropout
-        self.self_attn = MultiHeadAttention(d_model, nhead, ad)
-        self.cross_attn = MultiHeadAttention(d_model, nhead, ad)
-        self.linear1, self.linear2 = Linear(d_model, dim_feedforward), Linear(dim_feedforward, d_model)
-        self.norm1, self.norm2, self.norm3 = (LayerNorm(d_model, layer_norm_eps) for _ in range(3))
-        self.dropout = Dropout(act_dropout if act_dropout is not None else dropout)
-        self.dropout1, self.dropout2, self.dropout3 = Dropout(dropout), Dropout(dropout), Dropout(dropout)
-        self.activation = getattr(F, activation)
-
-    def _block(self, x, norm, fn, drop):
-        y = norm(x) if self.normalize_before else x
-        x = x + drop(fn(y))
-        return x if self.normalize_before else norm(x)
-
-    def forward(self, tgt, memory, tgt_mask=None, memory_mask=None, cache=None):
-        tgt = self._block(tgt, self.norm1, lambda t: self.self_attn(t, t, t, tgt_mask), self.dropout1)
-        tgt = self._block(tgt, self.norm2, lambda t: self.cross_attn(t, memory, memory, memory_mask), self.dropout2)
-        return self._block(tgt, self.norm3, lambda t: self.linear2(self.dropout(self.activation(self.linear1(t)))), self.dropout3)
-
-
-class TransformerDecoder(Layer):
-    def __init__(self, decoder_layer, num_layers, norm=None):
-        super().__init__()
-        import copy
-        self.layers = LayerList([decoder_layer if i == 0 else copy.deepcopy(decoder_layer) for i in range(num_layers)])
-        self.norm = norm
-
-    def forward(self, tgt, memory, tgt_mask=None, memory_mask=None, cache=None):
-        for l in self.layers:
-            tgt = l(tgt, memory, tgt_mask, memory_mask)
-        return self.norm(tgt) if self.norm is not None else tgt
-
-
-class Transformer(Layer):
-    def __init__(self, d_model=512, nhead=8, num_encoder_layers=6, num_decoder_layers=6, dim_feedforward=2048, dropout=0.1,
-                 activation="relu", attn_dropout=None, act_dropout=None, normalize_before=False, weight_attr=None,
-                 bias_attr=None, custom_encoder=None, custom_decoder=None):
-        super().__init__()
-        from .common import TransformerEncoder, TransformerEncoderLayer
-        self.encoder = custom_encoder or TransformerEncoder(
-            TransformerEncoderLayer(d_model, nhead, dim_feedforward, dropout, activation, attn_dropout, act_dropout,
-                                    normalize_before), num_encoder_layers, LayerNorm(d_model) if normalize_before else None)
-        self.decoder = custom_decoder or TransformerDecoder(
-            TransformerDecoderLayer(d_model, nhead, dim_feedforward, dropout, activation, attn_dropout, act_dropout,
-                                    normalize_before), num_decoder_layers, LayerNorm(d_model) if normalize_before else None)
-        self.d_model, self.nhead = d_model, nhead
-
-    def forward(self, src, tgt, src_mask=None, tgt_mask=None, memory_mask=None):
-        memory = self.encoder(src, src_mask)
-        return self.decoder(tgt, memory, tgt_mask, memory_mask)
-
-    @staticmethod
-    def generate_square_subsequent_mask(length):
-        return torch.full((length, length), float("-inf")).triu(1)
-
-
 # ---------------------------------------------------------------------------------------------- thin torch-backed layers
 def _wrap(name, factory, doc=""):
     """Layer whose forward is a torch module built from Paddle-style constructor arguments by ``factory``."""
