@@ -342,6 +342,7 @@ class Transformer(Layer):
         memory = self.encoder(src, src_mask=src_mask)
         return self.decoder(tgt, memory, tgt_mask=tgt_mask, memory_mask=memory_mask)
 
-    def generate_square_subsequent_mask(self, length):
+    @staticmethod
+    def generate_square_subsequent_mask(length):
         """[length, length] float mask: 0 on and below the diagonal, -inf above (a position sees itself and the past)."""
         return torch.triu(torch.full((int(length), int(length)), float("-inf"), dtype=torch.get_default_dtype()), 1)
