@@ -1,5 +1,5 @@
 """Count the Blackwell-specific SASS mnemonics per kernel of libpdb200_kernels.so (evidence that the tcgen05 / TMA /
-NVLS paths are real): UTCHMMA(.2CTA) = tcgen05.mma, UTMALDG = TMA load, LDTM/STTM = tcgen05.ld/st, UTCBAR = commit,
+NVLS paths are real): UTCHMMA(.2CTA) = tcgen05.mma, UTMALDG / UTMASTG = TMA load / store, LDTM/STTM = tcgen05.ld/st, UTCBAR = commit,
 SYNCS = mbarrier, LDGMC = multimem.ld_reduce (NVLS in-switch reduction), *.STRONG.SYS = system-scope peer loads /
 stores and flags, FFMA2 = packed fp32.  Kernels without any of these are omitted.
 usage: python tools/sass_evidence.py > profiles/sass_evidence.md"""
@@ -8,8 +8,8 @@ from collections import OrderedDict
 
 so = sys.argv[1] if len(sys.argv) > 1 else "paddle_b200/lib/libpdb200_kernels.so"
 out = subprocess.run(["cuobjdump", "-sass", so], capture_output=True, text=True).stdout
-KEYS = ["UTCHMMA.2CTA", "UTCHMMA", "UTMALDG", "LDTM", "STTM", "UTCBAR", "SYNCS", "LDGMC", "STG.E.128.STRONG.SYS", "LDG.E.STRONG.SYS", "FFMA2", "MUFU.EX2"]
-PROOF = KEYS[:10]
+KEYS = ["UTCHMMA.2CTA", "UTCHMMA", "UTMALDG", "UTMASTG", "LDTM", "STTM", "UTCBAR", "SYNCS", "LDGMC", "STG.E.128.STRONG.SYS", "LDG.E.STRONG.SYS", "FFMA2", "MUFU.EX2"]
+PROOF = KEYS[:11]
 per = OrderedDict()
 cur = None
 for line in out.splitlines():
