@@ -133,3 +133,27 @@ def wide_resnet50_2(pretrained=False, **kw):
 
 def resnext50_32x4d(pretrained=False, **kw):
     return _resnet(BottleneckBlock, 50, pretrained, groups=32, width=4, **kw)
+
+
+def resnext50_64x4d(pretrained=False, **kw):
+    return _resnet(BottleneckBlock, 50, pretrained, groups=64, width=4, **kw)
+
+
+def resnext101_32x4d(pretrained=False, **kw):
+    return _resnet(BottleneckBlock, 101, pretrained, groups=32, width=4, **kw)
+
+
+def resnext101_64x4d(pretrained=False, **kw):
+    return _resnet(BottleneckBlock, 101, pretrained, groups=64, width=4, **kw)
+
+
+def resnext152_32x4d(pretrained=False, **kw):
+    return _resnet(BottleneckBlock, 152, pretrained, groups=32, width=4, **kw)
+
+
+def resnext152_64x4d(pretrained=False, **kw):
+    return _resnet(BottleneckBlock, 152, pretrained, groups=64, width=4, **kw)
+
+
+def wide_resnet101_2(pretrained=False, **kw):
+    return _resnet(BottleneckBlock, 101, pretrained, width=128, **kw)
