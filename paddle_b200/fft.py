@@ -44,3 +44,24 @@ def fftshift(x, axes=None, name=None):
 
 def ifftshift(x, axes=None, name=None):
     return torch.fft.ifftshift(x, dim=axes)
+
+
+# Hermitian-input transforms in 2 / n dimensions.  hfftn(x) = irfftn(conj(x)) with the normalisation roles swapped
+# ("backward" <-> "forward"), ihfftn(x) = conj(rfftn(x)) likewise: a Hermitian-symmetric signal has a real spectrum.
+_SWAP = {"backward": "forward", "forward": "backward", "ortho": "ortho"}
+
+
+def hfftn(x, s=None, axes=None, norm="backward", name=None):
+    return torch.fft.irfftn(torch.conj(x), s=s, dim=axes, norm=_SWAP[norm])
+
+
+def ihfftn(x, s=None, axes=None, norm="backward", name=None):
+    return torch.conj(torch.fft.rfftn(x, s=s, dim=axes, norm=_SWAP[norm]))
+
+
+def hfft2(x, s=None, axes=(-2, -1), norm="backward", name=None):
+    return hfftn(x, s, axes, norm)
+
+
+def ihfft2(x, s=None, axes=(-2, -1), norm="backward", name=None):
+    return ihfftn(x, s, axes, norm)

@@ -105,8 +105,15 @@ class Model:
             cbs.append(ProgBarLogger(log_freq, verbose))
         if save_dir:
             cbs.append(ModelCheckpoint(save_freq, save_dir))
+        try:
+            steps = len(loader)
+        except TypeError:
+            steps = None
+        metric_names = ["loss"] + [n for m in self._metrics for n in (m.name() if isinstance(m.name(), (list, tuple)) else [m.name()])]
+        self._fit_has_eval = eval_loader is not None
         for cb in cbs:
             cb.set_model(self)
+            cb.set_params({"batch_size": batch_size, "epochs": epochs, "steps": steps, "verbose": verbose, "metrics": metric_names})
             cb.on_train_begin()
         it = 0
         for epoch in range(epochs):
@@ -116,6 +123,8 @@ class Model:
                 cb.on_epoch_begin(epoch)
             logs = {}
             for step, batch in enumerate(loader):
+                for cb in cbs:
+                    cb.on_train_batch_begin(step, logs)
                 ins, labs = self._split(batch)
                 out = self.train_batch(ins, labs, update=(step + 1) % accumulate_grad_batches == 0)
                 logs = {"loss": out[0] if isinstance(out, tuple) else out, "step": step}
@@ -127,14 +136,20 @@ class Model:
             for cb in cbs:
                 cb.on_epoch_end(epoch, logs)
             if eval_loader is not None and (epoch + 1) % eval_freq == 0:
-                logs.update(self.evaluate(eval_loader, verbose=0))
+                logs.update(self.evaluate(eval_loader, verbose=0, callbacks=cbs, _from_fit=True))
             if self.stop_training or (num_iters is not None and it >= num_iters):
                 break
         for cb in cbs:
             cb.on_train_end()
 
-    def evaluate(self, eval_data, batch_size=1, log_freq=10, verbose=2, num_workers=0, callbacks=None, num_iters=None):
+    def evaluate(self, eval_data, batch_size=1, log_freq=10, verbose=2, num_workers=0, callbacks=None, num_iters=None,
+                 _from_fit=False):
         loader = self._loader(eval_data, batch_size, False, num_workers)
+        cbs = list(callbacks or [])
+        for cb in cbs:
+            if not _from_fit:
+                cb.set_model(self)
+            cb.on_eval_begin({})
         for m in self._metrics:
             m.reset()
         losses = []
@@ -155,6 +170,8 @@ class Model:
                 res[names[0]] = vals[0] if len(vals) == 1 else list(vals)
             else:
                 res.update(dict(zip(names, vals)))
+        for cb in cbs:
+            cb.on_eval_end(res)
         return res
 
     def predict(self, test_data, batch_size=1, num_workers=0, stack_outputs=False, verbose=1, callbacks=None):

@@ -102,3 +102,6 @@ class ModelAverage:
             for p in self._params:
                 p.copy_(self._backup[id(p)])
             self._backup = None
+
+
+from ..optimizer import LBFGS  # noqa: E402,F401  (the reference keeps the old import path alive)

@@ -137,6 +137,21 @@ def ignore_module(modules):
     return None
 
 
+_verbosity = {"level": 0, "code_level": 0, "also_to_stdout": False}
+
+
+def set_verbosity(level=0, also_to_stdout=False):
+    """Logging level of the translator.  Nothing is transformed here (a StaticFunction replays a CUDA graph), so the
+    level only gates the messages ``StaticFunction`` prints about capture / fallback."""
+    _verbosity["level"], _verbosity["also_to_stdout"] = int(level), bool(also_to_stdout)
+
+
+def set_code_level(level=100, also_to_stdout=False):
+    """The reference prints the transformed code of AST pass ``level``; the source is untransformed here, so any level
+    > 0 makes ``StaticFunction.code`` the thing to look at.  Kept for scripts that call it."""
+    _verbosity["code_level"], _verbosity["also_to_stdout"] = int(level), bool(also_to_stdout)
+
+
 def enable_to_static(enable_to_static_bool):
     """Global switch: off -> StaticFunctions run eagerly (no graph capture)."""
     _enabled[0] = bool(enable_to_static_bool)
