@@ -36,8 +36,8 @@ from . import distributed  # noqa: E402,F401
 from .distributed.parallel import DataParallel  # noqa: E402,F401
 from .hapi import Model, summary  # noqa: E402,F401
 from . import models, ops, parallel  # noqa: E402,F401
-from . import (audio, callbacks, distribution, fft, geometric, hub, jit, linalg, quantization, signal, sparse, static, sysconfig,  # noqa: E402,F401
-               text)
+from . import (audio, callbacks, cost_model, distribution, fft, geometric, hub, inference, jit, linalg, onnx, quantization, signal,  # noqa: E402,F401
+               sparse, static, sysconfig, text)
 from .batch import batch  # noqa: E402,F401
 
 from .tensor.compat import install_inplace_variants as _iiv  # noqa: E402

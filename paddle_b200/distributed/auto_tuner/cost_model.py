@@ -79,3 +79,23 @@ def get_not_oom_cfgs(cfgs, tuner_cfg):
     m = tuner_cfg.get("model_cfg", {})
     limit = float(tuner_cfg.get("max_mem_usage_gb", HBM_GB * 0.92))
     return [c for c in cfgs if estimate_memory_gb(c, m) <= limit]
+
+
+def hardware_peaks():
+    """Measured peaks of the box (``MEASURED_PEAKS.json`` at the repo root, written by the driver) with the constants
+    above as fall-back: {"hbm_gbs", "tflops_bf16", "tflops_bf16_burst", "nvlink_gbs", "hbm_gb"}."""
+    import json
+    import os
+    peaks = {"hbm_gbs": 6550.0, "tflops_bf16": SUSTAINED_TFLOPS, "tflops_bf16_burst": 1614.0, "nvlink_gbs": NVLINK_GBS, "hbm_gb": HBM_GB}
+    root = os.path.dirname(os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+    path = os.path.join(root, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            with open(path) as f:
+                m = json.load(f)
+            peaks["hbm_gbs"] = float(m.get("hbm_gbs", peaks["hbm_gbs"]))
+            peaks["tflops_bf16"] = float(m.get("bf16_tflops_sustained", peaks["tflops_bf16"]))
+            peaks["tflops_bf16_burst"] = float(m.get("bf16_tflops", peaks["tflops_bf16_burst"]))
+        except (OSError, ValueError):
+            pass
+    return peaks

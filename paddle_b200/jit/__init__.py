@@ -192,6 +192,7 @@ def save(layer, path, input_spec=None, **configs):
     meta_specs = [dict(shape=[None if d is None else int(d) for d in getattr(s, "shape", ())], dtype=str(getattr(s, "dtype", "")),
                        name=getattr(s, "name", None)) for s in (specs or [])]
     has_program = False
+    num_outputs = None
     if specs:
         params = [p for p in layer.parameters()]
         device = params[0].device if params else torch.device("cpu")
@@ -208,13 +209,16 @@ def save(layer, path, input_spec=None, **configs):
                 traced = torch.jit.trace(layer, tuple(examples), check_trace=False, strict=False)
             torch.jit.save(traced, path + ".pdmodel")
             has_program = True
+            with torch.no_grad():
+                sample_out = traced(*examples)
+            num_outputs = len(sample_out) if isinstance(sample_out, (list, tuple)) else 1
         finally:
             if saved_forward is not None:
                 layer.forward = saved_forward
             set_flags(old)
             layer.train(was_training)
     with open(path + ".pdmodel.json", "w") as f:
-        json.dump({"class": type(layer).__name__, "input_spec": meta_specs, "program": has_program}, f)
+        json.dump({"class": type(layer).__name__, "input_spec": meta_specs, "program": has_program, "num_outputs": num_outputs}, f)
 
 
 class TranslatedLayer(torch.nn.Module):
@@ -259,5 +263,6 @@ def load(path, **configs):
     if meta.get("program") and os.path.exists(path + ".pdmodel"):
         module = torch.jit.load(path + ".pdmodel", map_location=configs.get("map_location"))
     layer = TranslatedLayer(_load(path + ".pdiparams"), meta.get("input_spec"), module)
+    layer.num_outputs = meta.get("num_outputs")
     layer.eval()
     return layer

@@ -112,3 +112,127 @@ def test_callbacks_follow_evaluation(tmp_path):
             paddle.callbacks.WandbCallback(project="x")
     else:
         assert paddle.callbacks.WandbCallback(project="x", mode="disabled").wandb_args["project"] == "x"
+
+
+def test_geometric_reindex_and_sampling():
+    import paddle.geometric as G
+    x = torch.tensor([0, 1, 2])
+    nb, cnt = torch.tensor([8, 9, 0, 4, 7, 6, 7]), torch.tensor([2, 3, 2], dtype=torch.int32)
+    src, dst, nodes = G.reindex_graph(x, nb, cnt)
+    assert src.tolist() == [3, 4, 0, 5, 6, 7, 6] and dst.tolist() == [0, 0, 1, 1, 1, 2, 2] and nodes.tolist() == [0, 1, 2, 8, 9, 4, 7, 6]
+    assert nodes[src].tolist() == nb.tolist()                               # the numbering is invertible
+    nb2, cnt2 = torch.tensor([0, 2, 3, 5, 1]), torch.tensor([1, 3, 1], dtype=torch.int32)
+    src, dst, nodes = G.reindex_heter_graph(x, [nb, nb2], [cnt, cnt2])
+    assert src.tolist() == [3, 4, 0, 5, 6, 7, 6, 0, 2, 8, 9, 1] and dst.tolist() == [0, 0, 1, 1, 1, 2, 2, 0, 1, 1, 1, 2]
+    assert nodes.tolist() == [0, 1, 2, 8, 9, 4, 7, 6, 3, 5]
+    with pytest.raises(ValueError):
+        G.reindex_graph(torch.tensor([0, 0]), nb[:2], torch.tensor([1, 1]))
+    with pytest.raises(ValueError):
+        G.reindex_graph(x, nb, torch.tensor([2, 3, 3]))
+    # CSC graph: neighbours of v are row[colptr[v]:colptr[v + 1]]
+    row = torch.tensor([3, 7, 0, 9, 1, 4, 2, 9, 3, 9, 1, 9, 7])
+    colptr = torch.tensor([0, 2, 4, 5, 6, 7, 9, 11, 11, 13, 13])
+    full, counts = G.sample_neighbors(row, colptr, torch.tensor([0, 8, 1, 2, 7]))
+    assert full.tolist() == [3, 7, 9, 7, 0, 9, 1] and counts.tolist() == [2, 2, 2, 1, 0]
+    paddle.seed(3)
+    n1, c1, e1 = G.sample_neighbors(row, colptr, torch.tensor([0, 8, 1, 2]), sample_size=1, eids=torch.arange(13) + 100, return_eids=True)
+    assert c1.tolist() == [1, 1, 1, 1] and (e1 - 100).tolist() == [int(i) for i in (e1 - 100)]
+    for node, got, eid in zip([0, 8, 1, 2], n1.tolist(), (e1 - 100).tolist()):
+        lo, hi = int(colptr[node]), int(colptr[node + 1])
+        assert lo <= eid < hi and int(row[eid]) == got
+    paddle.seed(3)
+    n2, _, _ = G.sample_neighbors(row, colptr, torch.tensor([0, 8, 1, 2]), sample_size=1, eids=torch.arange(13) + 100, return_eids=True)
+    assert n1.tolist() == n2.tolist()                                       # reproducible under paddle.seed
+    draws = torch.cat([G.sample_neighbors(row, colptr, torch.tensor([5]), 1)[0] for _ in range(200)])
+    assert set(draws.tolist()) == {9, 3} and 60 < int((draws == 9).sum()) < 140
+    with pytest.raises(ValueError):
+        G.sample_neighbors(row, colptr, torch.tensor([0]), return_eids=True)
+    w = torch.ones(13)
+    w[0] = 1e-9                                                             # edge 0 (neighbour 3 of node 0) is almost never taken
+    picks = [int(G.weighted_sample_neighbors(row, colptr, w, torch.tensor([0]), 1)[0]) for _ in range(50)]
+    assert picks == [7] * 50
+    allw, cw = G.weighted_sample_neighbors(row, colptr, w, torch.tensor([0, 5]), sample_size=5)
+    assert allw.tolist() == [3, 7, 9, 3] and cw.tolist() == [2, 2]
+
+
+class _Two(paddle.nn.Layer):
+    def __init__(self):
+        super().__init__()
+        self.fc = paddle.nn.Linear(4, 3)
+
+    def forward(self, x):
+        h = self.fc(x)
+        return h, torch.relu(h).sum(-1)
+
+
+def test_inference_predictor_onnx_and_cost_model(tmp_path):
+    import paddle.inference as inf
+    from paddle.static import InputSpec
+    net = _Two()
+    net.eval()
+    prefix = str(tmp_path / "deploy" / "model")
+    paddle.jit.save(net, prefix, input_spec=[InputSpec([None, 4], "float32", "feat")])
+    config = inf.Config(prefix + ".pdmodel", prefix + ".pdiparams")
+    assert config.prog_file() == prefix + ".pdmodel" and config.params_file() == prefix + ".pdiparams" and not config.use_gpu()
+    config.disable_gpu()
+    config.set_cpu_math_library_num_threads(2)
+    config.switch_ir_optim(True)
+    config.enable_memory_optim()
+    assert "use_gpu" in config.summary() and config.cpu_math_library_num_threads() == 2
+    pred = inf.create_predictor(config)
+    assert pred.get_input_names() == ["feat"] and len(pred.get_output_names()) == 2
+    x = np.random.RandomState(0).randn(5, 4).astype("float32")
+    handle = pred.get_input_handle("feat")
+    handle.reshape([5, 4])
+    handle.copy_from_cpu(x)
+    assert pred.run() is True
+    outs = [pred.get_output_handle(n).copy_to_cpu() for n in pred.get_output_names()]
+    with torch.no_grad():
+        ref = net(torch.from_numpy(x))
+    np.testing.assert_allclose(outs[0], ref[0].numpy(), rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(outs[1], ref[1].numpy(), rtol=1e-5, atol=1e-6)
+    out_handle = pred.get_output_handle(pred.get_output_names()[0])
+    assert out_handle.shape() == [5, 3] and out_handle.type() == inf.DataType.FLOAT32
+    listed = pred.run([torch.from_numpy(x[:2])])                            # dynamic batch, list style
+    torch.testing.assert_close(listed[0], ref[0][:2], rtol=1e-5, atol=1e-6)
+    assert inf.Config(str(tmp_path / "deploy")).prog_file() == prefix + ".pdmodel"        # model dir form
+    assert inf.PredictorPool(config, 2).retrieve(1).get_input_names() == ["feat"]
+    clone = pred.clone()
+    torch.testing.assert_close(clone.run([torch.from_numpy(x)])[1], ref[1], rtol=1e-5, atol=1e-6)
+    with pytest.raises(TypeError):
+        handle.copy_from_cpu([1, 2, 3])
+    with pytest.raises(NotImplementedError):
+        config.enable_tensorrt_engine()
+    with pytest.raises(RuntimeError):
+        gpu = inf.Config(prefix)
+        gpu.enable_use_gpu(100, 0)
+        if torch.cuda.is_available():
+            raise RuntimeError("a GPU is present: nothing to refuse")
+        inf.create_predictor(gpu)
+    # mixed precision conversion keeps the black-listed parameters in float32
+    mixed = str(tmp_path / "mixed" / "model")
+    inf.convert_to_mixed_precision(prefix + ".pdmodel", prefix + ".pdiparams", mixed + ".pdmodel", mixed + ".pdiparams",
+                                   inf.PrecisionType.Bfloat16, black_list={"bias"})
+    state = paddle.load(mixed + ".pdiparams")
+    assert state["fc.weight"].dtype == torch.bfloat16 and state["fc.bias"].dtype == torch.float32
+    assert os.path.exists(mixed + ".pdmodel") and os.path.exists(mixed + ".pdmodel.json")
+    assert inf.get_num_bytes_of_data_type(inf.DataType.FLOAT16) == 2 and "paddle_b200" in inf.get_version()
+    assert inf.get_trt_compile_version() == (0, 0, 0)
+    # onnx export needs the onnx package
+    import importlib.util
+    if importlib.util.find_spec("onnx") is None:
+        with pytest.raises(ImportError):
+            paddle.onnx.export(net, str(tmp_path / "m"), input_spec=[InputSpec([None, 4], "float32", "feat")])
+    else:
+        assert os.path.exists(paddle.onnx.export(net, str(tmp_path / "m"), input_spec=[InputSpec([None, 4], "float32", "feat")]))
+    cm = paddle.cost_model.CostModel()
+    peaks = cm.static_cost_data()
+    assert peaks["hbm_gbs"] > 1000 and peaks["tflops_bf16"] > 100
+    mm = cm.get_static_op_time("matmul", dtype="bfloat16", shape=(4096, 4096, 4096))
+    assert mm["op_time"] == pytest.approx(2 * 4096 ** 3 / (peaks["tflops_bf16"] * 1e12) * 1e3, rel=1e-6)
+    assert cm.get_static_op_time("matmul", forward=False, dtype="bfloat16", shape=(4096, 4096, 4096))["op_time"] == pytest.approx(2 * mm["op_time"])
+    ew = cm.get_static_op_time("relu", dtype="float32", shape=(1 << 24,))
+    assert ew["op_time"] == pytest.approx(2 * (1 << 24) * 4 / (peaks["hbm_gbs"] * 1e9) * 1e3, rel=1e-6)
+    assert cm.profile_measure(lambda: torch.ones(64).sum(), warmup=1, iters=3, device="cpu") > 0
+    with pytest.raises(ValueError):
+        cm.get_static_op_time(None)
