@@ -104,4 +104,5 @@ class ModelAverage:
             self._backup = None
 
 
-from ..optimizer import LBFGS  # noqa: E402,F401  (the reference keeps the old import path alive)
+from ...optimizer import LBFGS  # noqa: E402,F401  (the reference keeps the old import path alive)
+from . import functional  # noqa: E402,F401

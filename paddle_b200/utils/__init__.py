@@ -1,5 +1,5 @@
 """paddle.utils (reference: python/paddle/utils/)."""
-from . import unique_name  # noqa: F401
+from . import cpp_extension, unique_name  # noqa: F401
 
 
 def try_import(name):

@@ -236,3 +236,84 @@ def test_inference_predictor_onnx_and_cost_model(tmp_path):
     assert cm.profile_measure(lambda: torch.ones(64).sum(), warmup=1, iters=3, device="cpu") > 0
     with pytest.raises(ValueError):
         cm.get_static_op_time(None)
+
+
+def test_quasi_newton_minimisers():
+    from paddle.incubate.optimizer.functional import minimize_bfgs, minimize_lbfgs
+
+    def rosenbrock(x):
+        return (100 * (x[1:] - x[:-1] ** 2) ** 2 + (1 - x[:-1]) ** 2).sum()
+    for fn in (minimize_bfgs, minimize_lbfgs):
+        out = fn(rosenbrock, torch.tensor([-1.2, 1.0, 0.5]), max_iters=200, dtype="float64")
+        converged, calls, pos, val, grad = out[:5]
+        assert bool(converged) and int(calls) < 200 and pos.dtype == torch.float64
+        torch.testing.assert_close(pos, torch.ones(3, dtype=torch.float64), rtol=1e-4, atol=1e-4)
+        assert float(val) < 1e-8 and float(grad.abs().max()) < 1e-3
+    # on a quadratic BFGS recovers the inverse Hessian
+    A = torch.tensor([[3.0, 1.0], [1.0, 2.0]], dtype=torch.float64)
+    b = torch.tensor([1.0, -1.0], dtype=torch.float64)
+    out = minimize_bfgs(lambda x: 0.5 * x @ A @ x - b @ x, torch.zeros(2), dtype="float64")
+    torch.testing.assert_close(out[2], torch.linalg.solve(A, b), rtol=1e-6, atol=1e-8)
+    torch.testing.assert_close(out[5], torch.linalg.inv(A), rtol=1e-5, atol=1e-6)
+    short = minimize_lbfgs(rosenbrock, torch.tensor([-1.2, 1.0]), history_size=3, max_iters=2)
+    assert not bool(short[0]) and short[2].dtype == torch.float32
+    warm = minimize_bfgs(lambda x: (x ** 2).sum(), torch.ones(2), initial_inverse_hessian_estimate=torch.eye(2) * 0.5)
+    assert bool(warm[0]) and float(warm[3]) < 1e-10
+    with pytest.raises(ValueError):
+        minimize_bfgs(rosenbrock, torch.zeros(2), initial_inverse_hessian_estimate=torch.tensor([[1.0, 2.0], [0.0, 1.0]]))
+    with pytest.raises(NotImplementedError):
+        minimize_lbfgs(rosenbrock, torch.zeros(2), line_search_fn="armijo")
+    with pytest.raises(ValueError):
+        minimize_bfgs(rosenbrock, torch.zeros(2), dtype="float16")
+
+
+def test_cpp_extension_and_hdfs_client(tmp_path, monkeypatch):
+    from paddle.utils import cpp_extension as C
+    monkeypatch.setenv("PADDLE_EXTENSION_DIR", str(tmp_path / "ext"))
+    assert C.get_build_directory() == str(tmp_path / "ext") and os.path.isdir(tmp_path / "ext")
+    cuda = C.CUDAExtension(["op.cu", "op.cc"], extra_compile_args={"cxx": ["-O2"]})
+    assert "arch=compute_100a,code=sm_100a" in cuda.extra_compile_args["nvcc"] and cuda.extra_compile_args["cxx"] == ["-O2"]
+    assert paddle.sysconfig.get_include() in cuda.include_dirs
+    named = C.CUDAExtension(["op.cu"], extra_compile_args={"nvcc": ["-arch=sm_90"]})
+    assert named.extra_compile_args["nvcc"] == ["-arch=sm_90"]                    # a caller-chosen arch is left alone
+    cpp = C.CppExtension(["op.cc"], name="mine")
+    assert cpp.name == "mine" and cpp.sources == ["op.cc"]
+    with pytest.raises(ValueError):
+        C.setup(ext_modules=cpp)
+    src = tmp_path / "add_one.cc"
+    src.write_text('#include <torch/extension.h>\ntorch::Tensor add_one(torch::Tensor x) { return x + 1; }\n'
+                   'PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) { m.def("add_one", &add_one); }\n')
+    mod = C.load("pd_test_add_one", [str(src)])
+    assert mod.add_one(torch.zeros(3)).tolist() == [1.0, 1.0, 1.0]
+    assert os.path.isdir(tmp_path / "ext" / "pd_test_add_one")
+    # HDFS client: command construction against a stand-in `hadoop` that records its arguments
+    from paddle.distributed.fleet.utils import DistributedInfer, HDFSClient
+    from paddle.distributed.fleet.utils.fs import ExecuteError, FSFileNotExistsError
+    home = tmp_path / "hadoop"
+    os.makedirs(home / "bin")
+    log = tmp_path / "calls.log"
+    (home / "bin" / "hadoop").write_text(f'#!/bin/sh\necho "$@" >> {log}\ncase "$*" in\n  *"-test -e /missing"*) exit 1;;\n'
+                                         '  *"-test -d /data/file"*) exit 1;;\n'
+                                         '  *"-ls /data"*) echo "Found 2 items"; echo "drwxr-xr-x   - u g          0 2024-01-01 00:00 /data/sub";'
+                                         ' echo "-rw-r--r--   3 u g         12 2024-01-01 00:00 /data/file";;\nesac\nexit 0\n')
+    os.chmod(home / "bin" / "hadoop", 0o755)
+    client = HDFSClient(str(home), {"fs.default.name": "hdfs://nn:9000", "hadoop.job.ugi": "u,p"}, time_out=2000, sleep_inter=100)
+    assert client.is_exist("/data") and not client.is_exist("/missing") and client.is_file("/data/file") and client.is_dir("/data")
+    assert client.ls_dir("/data") == (["sub"], ["file"]) and client.list_dirs("/data") == ["sub"] and client.ls_dir("/missing") == ([], [])
+    client.mkdirs("/missing")
+    client.delete("/data")
+    local = tmp_path / "local.txt"
+    local.write_text("x")
+    client.upload(str(local), "/missing")
+    with pytest.raises(FSFileNotExistsError):
+        client.upload(str(tmp_path / "nope"), "/missing")
+    with pytest.raises(FSFileNotExistsError):
+        client.download("/missing", str(tmp_path / "dl"))
+    calls = log.read_text()
+    assert "-D fs.default.name=hdfs://nn:9000 -D hadoop.job.ugi=u,p" in calls
+    for piece in ("-mkdir -p /missing", "-rm -r -f /data", f"-put {local} /missing"):
+        assert piece in calls, piece
+    with pytest.raises(ExecuteError):
+        HDFSClient(str(tmp_path / "no_hadoop")).is_exist("/x")
+    with pytest.raises(NotImplementedError):
+        DistributedInfer()
