@@ -58,6 +58,17 @@ def install(namespace):
     # methods torch does not have at all: attach the paddle function as is
     for name in ("take_along_axis", "put_along_axis", "gather_nd", "scatter_nd_add", "index_sample", "strided_slice", "slice",
                  "crop", "unstack", "rank", "add_n", "stanh", "increment", "is_empty", "equal_all", "floor_mod", "mod",
-                 "multiplex", "broadcast_to", "expand_as", "reverse", "astype", "tolist", "top_p_sampling", "lerp", "masked_fill"):
+                 "multiplex", "broadcast_to", "expand_as", "reverse", "astype", "tolist", "top_p_sampling", "lerp", "masked_fill",
+                 # the rest of the reference's tensor_method_func list
+                 "create_parameter", "create_tensor", "histogramdd", "reduce_as", "multigammaln", "block_diag", "isin",
+                 "broadcast_shape", "gammaincc", "gammainc", "greater_than", "less_than", "is_tensor", "reshape_", "scatter_nd",
+                 "shard_index", "tensordot", "is_integer", "gammaln", "broadcast_tensors", "cdist", "as_complex", "as_real",
+                 "put_along_axis_", "bucketize", "trapezoid", "cumulative_trapezoid", "polar", "vander", "i0e", "i1", "i1e",
+                 "atleast_1d", "atleast_2d", "atleast_3d", "combinations"):
         if not hasattr(torch.Tensor, name) and callable(namespace.get(name)):
             setattr(torch.Tensor, name, namespace[name])
+    linalg = namespace.get("linalg")
+    for name in ("cond", "householder_product", "pca_lowrank", "svd_lowrank", "eigvals", "eigvalsh", "multi_dot", "lu_unpack", "pinv"):
+        fn = getattr(linalg, name, None) if linalg is not None else None
+        if fn is not None and not hasattr(torch.Tensor, name):
+            setattr(torch.Tensor, name, fn)

@@ -145,3 +145,13 @@ def complex(real, imag, name=None):
 
 def tolist(x):
     return x.tolist()
+
+
+def create_tensor(dtype, name=None, persistable=False):
+    """An empty (0-element) tensor of ``dtype`` to be filled later (reference: tensor/creation.py create_tensor)."""
+    from ..framework import dtype as _dtm
+    t = torch.empty(0, dtype=_dtm.to_torch_dtype(dtype))
+    if name:
+        t.name = name
+    t.persistable = persistable
+    return t

@@ -325,3 +325,11 @@ def multinomial(x, num_samples=1, replacement=False, name=None):
 
 def poisson(x, name=None):
     return torch.poisson(x)
+
+
+def put_along_axis_(arr, indices, values, axis, reduce="assign", include_self=True, broadcast=True):
+    """In-place ``put_along_axis``."""
+    out = put_along_axis(arr, indices, values, axis, reduce, include_self, broadcast)
+    with torch.no_grad():
+        arr.copy_(out)
+    return arr

@@ -501,3 +501,28 @@ def increment(x, value=1.0, name=None):
     with torch.no_grad():
         x.add_(value)
     return x
+
+
+def top_p_sampling(x, ps, threshold=None, seed=None, name=None):
+    """Nucleus sampling (reference: python/paddle/tensor/search.py top_p_sampling, kernel
+    paddle/phi/kernels/gpu/top_p_sampling_kernel.cu).  ``x`` [batch, vocab] probabilities, ``ps`` [batch]: per row, keep
+    the most probable tokens until their cumulative probability reaches ``ps`` (the token that crosses it included, the
+    top token always), drop tokens below ``threshold`` [batch] if given, renormalise and draw one.
+    Returns (probability of the drawn token [batch, 1], its id [batch, 1] int64)."""
+    if x.dim() != 2:
+        raise ValueError("top_p_sampling expects x of shape [batch, vocab]")
+    probs = x.float()
+    sorted_p, order = probs.sort(-1, descending=True)
+    cum = sorted_p.cumsum(-1)
+    p = ps.reshape(-1, 1).float().to(probs.device)
+    keep = (cum - sorted_p) < p                       # mass BEFORE the token is still below p
+    keep[:, 0] = True
+    if threshold is not None:
+        keep = keep & ((sorted_p >= threshold.reshape(-1, 1).float().to(probs.device)) | (torch.arange(probs.shape[1], device=probs.device) == 0))
+    kept = torch.where(keep, sorted_p, torch.zeros_like(sorted_p))
+    gen = None
+    if seed is not None and int(seed) >= 0:
+        gen = torch.Generator(device=probs.device).manual_seed(int(seed))
+    pick = torch.multinomial(kept / kept.sum(-1, keepdim=True), 1, generator=gen)
+    ids = order.gather(1, pick)
+    return x.gather(1, ids), ids

@@ -159,3 +159,33 @@ def test_tensor_methods_follow_the_functions():
     assert g.detach().stop_gradient and not g.stop_gradient and t.place is not None and t.is_contiguous()
     eq(t.add_(T(x)), 2 * x)                                                 # in place
     eq(t.scale_(0.5), x)
+
+
+def test_every_reference_tensor_method_exists_and_top_p_sampling():
+    import os
+    import re
+    path = "/root/reference/python/paddle/tensor/__init__.py"
+    if os.path.exists(path):
+        names = re.findall(r"['\"]([^'\"]+)['\"]", re.search(r"tensor_method_func = \[(.*?)\]", open(path).read(), re.S).group(1))
+        assert [n for n in names if not hasattr(torch.Tensor, n)] == []
+    x = torch.rand(3, 3) + torch.eye(3)
+    torch.testing.assert_close(x.pinv(), torch.linalg.pinv(x))
+    assert x.atleast_3d().shape == (3, 3, 1) and x.tensordot(x, axes=1).shape == (3, 3) and bool(x.is_tensor())
+    assert paddle.create_tensor("int64").dtype == torch.int64 and paddle.create_tensor("float32").numel() == 0
+    y = torch.zeros(2, 3)
+    assert y.put_along_axis_(torch.tensor([[0], [2]]), torch.tensor([[5.0], [7.0]]), 1) is y and y.tolist() == [[5.0, 0, 0], [0, 0, 7.0]]
+    # nucleus sampling: only the tokens needed to reach p can be drawn
+    probs = torch.tensor([[0.05, 0.6, 0.3, 0.05], [0.4, 0.3, 0.2, 0.1]])
+    seen = [set(), set()]
+    for s in range(200):
+        v, i = paddle.top_p_sampling(probs, torch.tensor([0.5, 0.65]), seed=s)
+        assert v.shape == (2, 1) and i.dtype == torch.int64
+        torch.testing.assert_close(v, probs.gather(1, i))
+        seen[0].add(int(i[0]))
+        seen[1].add(int(i[1]))
+    assert seen[0] == {1} and seen[1] == {0, 1}            # row 0: the top token alone covers 0.5; row 1: 0.4 + 0.3 crosses 0.65
+    a = paddle.top_p_sampling(probs, torch.tensor([0.99, 0.99]), seed=7)[1]
+    b = paddle.top_p_sampling(probs, torch.tensor([0.99, 0.99]), seed=7)[1]
+    assert a.tolist() == b.tolist()
+    only_top = {int(paddle.top_p_sampling(probs, torch.tensor([0.99, 0.99]), threshold=torch.tensor([0.5, 0.35]), seed=s)[1][1]) for s in range(50)}
+    assert only_top == {0}
