@@ -113,6 +113,33 @@ class GradScaler:
         self._tables = {}
 
     # -- device state is created lazily on the device of the first loss
+    # --- the reference's accessors for the dynamic-scaling knobs
+    def get_incr_ratio(self):
+        return self._incr_ratio
+
+    def set_incr_ratio(self, new_incr_ratio):
+        assert new_incr_ratio > 1.0, "The new_incr_ratio must be > 1.0."
+        self._incr_ratio = float(new_incr_ratio)
+
+    def get_decr_ratio(self):
+        return self._decr_ratio
+
+    def set_decr_ratio(self, new_decr_ratio):
+        assert new_decr_ratio < 1.0, "The new_decr_ratio must be < 1.0."
+        self._decr_ratio = float(new_decr_ratio)
+
+    def get_incr_every_n_steps(self):
+        return self._incr_every_n_steps
+
+    def set_incr_every_n_steps(self, new_incr_every_n_steps):
+        self._incr_every_n_steps = int(new_incr_every_n_steps)
+
+    def get_decr_every_n_nan_or_inf(self):
+        return self._decr_every_n_nan_or_inf
+
+    def set_decr_every_n_nan_or_inf(self, new_decr_every_n_nan_or_inf):
+        self._decr_every_n_nan_or_inf = int(new_decr_every_n_nan_or_inf)
+
     def _init_state(self, device):
         if self._scale is None:
             self._scale = torch.full((1,), self._init_loss_scaling, dtype=torch.float32, device=device)

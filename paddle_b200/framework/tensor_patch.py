@@ -227,6 +227,40 @@ if not hasattr(Tensor, "ndimension"):
     Tensor.ndimension = _ndimension
 
 
+def _apply(self, func):
+    """``func(tensor)`` -> a new tensor; refused on tensors that take part in autograd (tensor_patch_methods.py apply)."""
+    if self.requires_grad:
+        raise RuntimeError("Cannot apply function on a tensor that required gradient.")
+    return func(self)
+
+
+def _apply_(self, func):
+    """In-place ``apply``: the tensor takes the function's result."""
+    if self.requires_grad:
+        raise RuntimeError("Cannot apply function on a tensor that required gradient.")
+    with torch.no_grad():
+        self.copy_(func(self))
+    return self
+
+
+if not hasattr(Tensor, "apply"):
+    Tensor.apply = _apply
+if getattr(Tensor.apply_, "__name__", "") != "_apply_":
+    _torch_apply_ = Tensor.apply_
+
+    def _apply_dispatch(self, func):            # torch's apply_ maps a Python scalar function element by element (CPU only)
+        try:
+            return _apply_(self, func)
+        except (TypeError, RuntimeError):
+            if self.requires_grad:
+                raise
+            return _torch_apply_(self, func)
+    _apply_dispatch.__name__ = "_apply_"
+    Tensor.apply_ = _apply_dispatch
+if not hasattr(Tensor, "inplace_version"):
+    Tensor.inplace_version = property(lambda self: self._version)
+
+
 # ---------------------------------------------------------------- parameters
 class Parameter(torch.nn.Parameter):
     """EagerParamBase equivalent (reference: python/paddle/base/framework.py EagerParamBase).

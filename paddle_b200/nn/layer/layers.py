@@ -155,6 +155,9 @@ class Layer(torch.nn.Module):
             dest[structured_name_prefix + n] = p
         for n, b in self._named_persistent_buffers(include_sublayers):
             dest[structured_name_prefix + n] = b
+        if use_hook:
+            for hook in self.__dict__.get("_pd_state_dict_hooks", {}).values():
+                hook(dest)
         return dest
 
     def _named_persistent_buffers(self, include_sublayers=True):
@@ -169,6 +172,23 @@ class Layer(torch.nn.Module):
 
     def to_static_state_dict(self, *a, **k):
         return self.state_dict(*a, **k)
+
+    def register_state_dict_hook(self, hook):
+        """``hook(state_dict)`` runs on (and may edit) every dict ``state_dict()`` returns; the returned helper's
+        ``remove()`` unregisters it."""
+        hooks = self.__dict__.setdefault("_pd_state_dict_hooks", OrderedDict())
+        key = len(hooks)
+        while key in hooks:
+            key += 1
+        hooks[key] = hook
+
+        class _Remove:
+            def remove(self_inner):
+                hooks.pop(key, None)
+        return _Remove()
+
+    def backward(self, *inputs):
+        raise ValueError("Layer shouldn't implement backward")
 
     def set_state_dict(self, state_dict, use_structured_name=True):
         own = self.state_dict()

@@ -26,6 +26,10 @@ class LRScheduler:
     def get_lr(self):
         return self.base_lr
 
+    def state_keys(self):
+        """Names of the attributes ``state_dict`` saves; subclasses with more state override this."""
+        self.keys = ["last_epoch", "last_lr"]
+
     def state_dict(self):
         return {"last_epoch": self.last_epoch, "last_lr": self.last_lr}
 

@@ -182,8 +182,50 @@ class Optimizer:
         raise NotImplementedError
 
     def minimize(self, loss, startup_program=None, parameters=None, no_grad_set=None):
+        """Apply the gradients that ``loss.backward()`` left on the parameters (dygraph contract of the reference:
+        minimize does not run the backward pass itself).  Returns (None, [(param, grad)])."""
+        params_grads = self._collect_params_grads()
         self.step()
-        return None, None
+        return None, params_grads
+
+    def backward(self, loss, startup_program=None, parameters=None, no_grad_set=None, callbacks=None):
+        """[(param, grad)] of the parameters that already hold a gradient (reference: optimizer.py backward, dygraph
+        branch); ``parameters`` restricts the list."""
+        pairs = self._collect_params_grads()
+        if parameters is not None:
+            wanted = {id(p) for p in parameters}
+            pairs = [(p, g) for p, g in pairs if id(p) in wanted]
+        return pairs
+
+    def append_regularization_ops(self, parameters_and_grads, regularization=None):
+        """grad + regulariser(param) for every pair: the parameter's own ``regularizer`` attribute wins over
+        ``regularization`` (or the optimizer's ``weight_decay``)."""
+        from ..regularizer import L1Decay, L2Decay
+        default = regularization if regularization is not None else self.regularization
+        out = []
+        for p, g in parameters_and_grads:
+            reg = getattr(p, "regularizer", None) or default
+            if g is None or reg is None:
+                out.append((p, g))
+                continue
+            if isinstance(reg, (int, float)):
+                reg = L2Decay(float(reg))
+            coeff = float(getattr(reg, "_coeff", getattr(reg, "coeff", 0.0)))
+            if isinstance(reg, L1Decay):
+                out.append((p, g + coeff * torch.sign(p.detach()).to(g.dtype)))
+            elif isinstance(reg, L2Decay):
+                out.append((p, g + coeff * p.detach().to(g.dtype)))
+            else:
+                out.append((p, g))
+        return out
+
+    @torch.no_grad()
+    def apply_gradients(self, params_grads):
+        """Clip and apply explicit [(param, grad)] pairs."""
+        return self._apply_optimize(None, None, [(p, g) for p, g in params_grads if g is not None])
+
+    def get_opti_var_name_list(self):
+        return [f"{p}_{acc}" for acc, table in self._accumulators.items() for p in table]
 
     def clear_grad(self, set_to_zero=True):
         for p, _ in self._all_params():

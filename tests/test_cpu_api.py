@@ -349,3 +349,57 @@ def test_elastic_manager_state_machine(tmp_path):
     store.put("/paddle/t/nodes/10.0.0.2", "10.0.0.2", ttl=10)
     assert m.watch() == ElasticStatus.RESTART
     m.exit()
+
+
+def test_class_method_surface_of_layer_optimizer_scaler():
+    """Methods the reference's Layer / Optimizer / LRScheduler / GradScaler / Tensor expose beyond the common ones."""
+    net = paddle.nn.Linear(3, 2)
+    seen = []
+    handle = net.register_state_dict_hook(lambda sd: seen.append(sorted(sd)) or sd.__setitem__("extra", torch.zeros(1)))
+    sd = net.state_dict()
+    assert seen == [["bias", "weight"]] and "extra" in sd
+    handle.remove()
+    assert "extra" not in net.state_dict() and "extra" not in net.state_dict(use_hook=False)
+    with pytest.raises(ValueError):
+        net.backward()
+    opt = paddle.optimizer.Momentum(0.1, parameters=net.parameters(), weight_decay=0.5)
+    x = torch.randn(4, 3)
+    net(x).sum().backward()
+    pairs = opt.backward(None)
+    assert [p is q for (p, _), q in zip(pairs, net.parameters())] == [True, True]
+    assert len(opt.backward(None, parameters=[net.bias])) == 1
+    reg = opt.append_regularization_ops(pairs)
+    torch.testing.assert_close(reg[0][1], pairs[0][1] + 0.5 * net.weight.detach())
+    l1 = opt.append_regularization_ops(pairs, paddle.regularizer.L1Decay(0.1))
+    torch.testing.assert_close(l1[1][1], pairs[1][1] + 0.1 * torch.sign(net.bias.detach()))
+    net.weight.regularizer = paddle.regularizer.L2Decay(2.0)             # the parameter's own regulariser wins
+    torch.testing.assert_close(opt.append_regularization_ops(pairs)[0][1], pairs[0][1] + 2.0 * net.weight.detach())
+    net.weight.regularizer = None
+    before = net.weight.detach().clone()
+    _, returned = opt.minimize(None)
+    assert len(returned) == 2 and not torch.equal(before, net.weight.detach())
+    assert any("velocity" in n for n in opt.get_opti_var_name_list())
+    plain = paddle.optimizer.SGD(0.5, parameters=net.parameters())
+    w0 = net.weight.detach().clone()
+    plain.apply_gradients([(net.weight, torch.ones_like(net.weight)), (net.bias, None)])
+    torch.testing.assert_close(net.weight.detach(), w0 - 0.5)
+    sched = paddle.optimizer.lr.StepDecay(0.1, 2)
+    sched.state_keys()
+    assert sched.keys == ["last_epoch", "last_lr"]
+    scaler = paddle.amp.GradScaler(init_loss_scaling=8.0)
+    scaler.set_incr_ratio(3.0)
+    scaler.set_decr_ratio(0.25)
+    scaler.set_incr_every_n_steps(7)
+    scaler.set_decr_every_n_nan_or_inf(2)
+    assert (scaler.get_incr_ratio(), scaler.get_decr_ratio(), scaler.get_incr_every_n_steps(), scaler.get_decr_every_n_nan_or_inf()) == (3.0, 0.25, 7, 2)
+    assert scaler.state_dict()["incr_ratio"] == 3.0
+    with pytest.raises(AssertionError):
+        scaler.set_incr_ratio(0.5)
+    t = torch.tensor([1.0, -2.0])
+    assert t.apply(lambda v: v * 2).tolist() == [2.0, -4.0] and t.tolist() == [1.0, -2.0]
+    assert t.apply_(lambda v: v.abs()) is t and t.tolist() == [1.0, 2.0]
+    v0 = t.inplace_version
+    t.add_(1)
+    assert t.inplace_version == v0 + 1
+    with pytest.raises(RuntimeError):
+        torch.ones(2, requires_grad=True).apply(lambda v: v)
