@@ -91,6 +91,12 @@ class ProcessMesh:
         self._groups = {}
 
     @property
+    def unique_id(self):
+        """A number identifying the mesh (shape + process ids + dim names), equal for equal meshes."""
+        import zlib
+        return zlib.crc32(repr((self._shape, self._process_ids, self._dim_names)).encode())
+
+    @property
     def shape(self):
         return self._shape
 
@@ -666,6 +672,16 @@ class DistModel:
     def dist_main_program(self, mode=None):
         """There is no program object: the dygraph layer is the program."""
         return self._layer
+
+    def dist_startup_program(self, mode=None):
+        """Parameters are initialised when the layer is built; there is nothing to run at start-up."""
+        return None
+
+    def serial_main_program(self, mode=None):
+        return self._layer
+
+    def serial_startup_program(self, mode=None):
+        return None
 
 
 def to_static(layer, loader=None, loss=None, optimizer=None, strategy=None):

@@ -74,6 +74,8 @@ class DistributedStrategy:
             "hierarchical_allreduce_inter_nranks": 1, "sync_batch_norm": False, "cudnn_exhaustive_search": False,
             "conv_workspace_size_limit": 512, "cudnn_batchnorm_spatial_persistent": False, "calc_comm_same_stream": False,
             "split_data": True,
+            # parameter-server / static-graph switches: stored and serialised, read by nothing in this framework
+            "adam_d2sum": False, "is_with_coordinator": False, "build_strategy": None,
         }
         self._cfgs = {
             "hybrid_configs": _Cfg(copy.deepcopy(_HYBRID)), "amp_configs": _Cfg(copy.deepcopy(_AMP)),
@@ -83,6 +85,12 @@ class DistributedStrategy:
             "gradient_merge_configs": _Cfg(copy.deepcopy(_GRADIENT_MERGE)), "lars_configs": _Cfg(copy.deepcopy(_LARS)),
             "lamb_configs": _Cfg(copy.deepcopy(_LAMB)), "localsgd_configs": _Cfg(copy.deepcopy(_LOCALSGD)),
             "dgc_configs": _Cfg(copy.deepcopy(_DGC)), "a_sync_configs": _Cfg(copy.deepcopy(_A_SYNC)),
+            "adaptive_localsgd_configs": _Cfg({"init_k_steps": 1, "begin_step": 1}), "qat_configs": _Cfg({
+                "channel_wise_abs_max": True, "weight_bits": 8, "activation_bits": 8, "not_quant_pattern": [], "algo": None}),
+            "gradient_scale_configs": _Cfg({"scale_strategy": "avg", "scale_gradient": False}),
+            "trainer_desc_configs": _Cfg({"dump_fields_path": "", "dump_fields": [], "dump_param": [], "stat_var_names": []}),
+            "fs_client_param": _Cfg({"uri": "", "user": "", "passwd": "", "hadoop_bin": ""}),
+            "sparse_table_configs": _Cfg({}), "fleet_desc_configs": _Cfg({}),
         }
         self._cfgs["hybrid_configs"]["mp_configs"] = _Cfg(self._cfgs["hybrid_configs"]["mp_configs"])
         self._cfgs["hybrid_configs"]["pp_configs"] = _Cfg(self._cfgs["hybrid_configs"]["pp_configs"])
@@ -113,7 +121,7 @@ class DistributedStrategy:
             want = type(self._d[name])
             if want is bool and not isinstance(value, bool):
                 raise ValueError(f"{name} should have value of bool type")
-            self._d[name] = want(value) if want is not bool else value
+            self._d[name] = value if want in (bool, type(None)) else want(value)
             return
         if name in self._cfgs:
             self._set_configs(name, value)
@@ -121,9 +129,12 @@ class DistributedStrategy:
         raise AttributeError(f"DistributedStrategy has no attribute {name}")
 
     def _set_configs(self, name, configs):
-        defaults = self._DEFAULTS[name]
-        check_configs_key(defaults, configs, name)
         tgt = self._cfgs[name]
+        defaults = self._DEFAULTS.get(name)
+        if defaults is None:                       # PS / static-graph config blocks: free-form, stored as given
+            tgt.update(configs)
+            return
+        check_configs_key(defaults, configs, name)
         for k, v in configs.items():
             if name == "hybrid_configs" and k in ("mp_configs", "pp_configs", "sharding_configs"):
                 sub_defaults = {"mp_configs": _MP_CONFIGS, "pp_configs": _PP_CONFIGS, "sharding_configs": _SHARDING_CONFIGS_DY}[k]

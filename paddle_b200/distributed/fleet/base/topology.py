@@ -283,6 +283,10 @@ class HybridCommunicateGroup:
         assert self._sep_degree > 1, "sep not exist"
         return self._sep_comm_group
 
+    def get_sep_parallel_group_src_rank(self):
+        assert self._sep_degree > 1, "sep not exist"
+        return self._sep_comm_group.ranks[0]
+
     def get_dp_sep_parallel_group(self):
         assert self._sep_degree > 1, "sep not exist"
         return self._dp_sep_comm_group

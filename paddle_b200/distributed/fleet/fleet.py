@@ -125,17 +125,20 @@ class Fleet:
     # ------------------------------------------------------------- wrapping
     def distributed_model(self, model):
         from .model import distributed_model
-        return distributed_model(model)
+        self._model = distributed_model(model)
+        return self._model
 
     def distributed_optimizer(self, optimizer, strategy=None):
         from .optimizer import distributed_optimizer
         if strategy is not None:
             self._user_defined_strategy = strategy
-        return distributed_optimizer(optimizer, strategy)
+        self._optimizer = distributed_optimizer(optimizer, strategy)
+        return self._optimizer
 
     def distributed_scaler(self, scaler):
         from .scaler import distributed_scaler
-        return distributed_scaler(scaler)
+        self._scaler = distributed_scaler(scaler)
+        return self._scaler
 
     # ------------------------------------------------------------- self benchmark
     def collective_perf(self, comm_type, round=50, size_and_time=None):
@@ -187,12 +190,105 @@ class Fleet:
             logger.info(f"[{comm_type}] {nbytes / (1 << 20):.0f} MB: {sec * 1e3:.3f} ms")
         return results
 
-    # PS-mode / static-graph entry points kept for API shape
+    # the per-collective entry points ``collective_perf`` dispatches to in the reference (fleet.py:363-560)
+    def allreduce_perf(self, iteration, x=None, y=None, pred_time=None, size=None):
+        return self._one_perf("allreduce", iteration, x, pred_time, size)
+
+    def reduce_perf(self, iteration, x=None, pred_time=None, size=None):
+        return self._one_perf("reduce", iteration, x, pred_time, size)
+
+    def broadcast_perf(self, iteration, x=None, pred_time=None, size=None):
+        return self._one_perf("broadcast", iteration, x, pred_time, size)
+
+    def allgather_perf(self, iteration, x=None, y=None, pred_time=None, size=None):
+        return self._one_perf("allgather", iteration, x, pred_time, size)
+
+    def reduce_scatter_perf(self, iteration, x=None, y=None, pred_time=None, size=None):
+        return self._one_perf("reduce_scatter", iteration, x, pred_time, size)
+
+    def _one_perf(self, comm_type, iteration, x, pred_time, size):
+        nbytes = int(size) if size is not None else (x.numel() * x.element_size() if x is not None else 1 << 20)
+        return self.collective_perf(comm_type, round=int(iteration), size_and_time={nbytes: pred_time if pred_time else 0})[nbytes]
+
+    def all_reduce(self, input, mode="sum"):
+        """All-reduce a tensor / ndarray / number over the workers and return the result (reference: fleet.py all_reduce,
+        used for metrics)."""
+        import numpy as np
+        t = input.clone() if isinstance(input, torch.Tensor) else torch.as_tensor(np.asarray(input))
+        if C.is_initialized() and C.get_world_size() > 1:
+            op = {"sum": comm.ReduceOp.SUM, "max": comm.ReduceOp.MAX, "min": comm.ReduceOp.MIN}[mode]
+            dev = "cuda" if C._state.backend == "nccl" else "cpu"
+            moved = t.to(dev)
+            comm.all_reduce(moved, op)
+            t = moved.to(t.device)
+        return t if isinstance(input, torch.Tensor) else t.numpy()
+
+    def get_loss_scaling(self):
+        """Current loss scale of the scaler handed to ``distributed_scaler`` (or the strategy's initial value)."""
+        scaler = getattr(self, "_scaler", None)
+        if scaler is not None:
+            return scaler.get_loss_scaling()
+        cfg = getattr(self._strategy, "amp_configs", {}) if getattr(self, "_strategy", None) is not None else {}
+        return torch.tensor([float(cfg.get("init_loss_scaling", 32768.0))])
+
+    def amp_init(self, place=None, scope=None, test_program=None, use_fp16_test=False):
+        """Static-graph AMP casts parameters here; in dygraph ``paddle.amp.decorate`` already did, so nothing is left."""
+        return None
+
+    def qat_init(self, place=None, scope=None, test_program=None):
+        return None
+
+    def save(self, dirname, feed=(), fetch=(), **configs):
+        """Collective-mode checkpoint of the wrapped model (and optimizer) from the first worker:
+        ``dirname/model.pdparams`` (+ ``model.pdopt``)."""
+        import os
+        from ...framework.io import save as _save
+        model = getattr(self, "_model", None)
+        if model is None:
+            raise RuntimeError("fleet.save needs a model wrapped by fleet.distributed_model first")
+        if self.is_first_worker():
+            os.makedirs(dirname, exist_ok=True)
+            _save(model.state_dict(), os.path.join(dirname, "model.pdparams"))
+            opt = getattr(self, "_optimizer", None)
+            if opt is not None:
+                _save(opt.state_dict(), os.path.join(dirname, "model.pdopt"))
+        self.barrier_worker()
+
+    def load_model(self, path, mode=0):
+        import os
+        from ...framework.io import load as _load
+        model = getattr(self, "_model", None)
+        if model is None:
+            raise RuntimeError("fleet.load_model needs a model wrapped by fleet.distributed_model first")
+        model.set_state_dict(_load(os.path.join(path, "model.pdparams")))
+
+    # static-graph entry point
     def minimize(self, *a, **k):
         raise NotImplementedError("static-graph fleet.minimize is out of scope (SURVEY P37)")
 
     def save_persistables(self, *a, **k):
         raise NotImplementedError("parameter-server persistence is out of scope")
+
+    # parameter-server / federated-learning mode: not part of this framework (SURVEY P38 / N15)
+    def is_coordinator(self):
+        return False
+
+    def server_num(self):
+        return 0
+
+    def server_index(self):
+        return -1
+
+    def server_endpoints(self, to_string=False):
+        return "" if to_string else []
+
+    def _ps_only(self, *a, **k):
+        raise NotImplementedError("this entry point belongs to the parameter-server mode, which this framework does not "
+                                  "implement (collective training only)")
+
+    init_coordinator = make_fl_strategy = get_fl_client = init_server = load_one_table = load_inference_model = _ps_only
+    run_server = save_inference_model = save_cache_model = check_save_pre_patch_done = save_cache_table = _ps_only
+    save_one_table = save_dense_params = set_date = shrink = _ps_only
 
 
 fleet = Fleet()

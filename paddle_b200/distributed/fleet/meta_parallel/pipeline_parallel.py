@@ -117,6 +117,8 @@ class PipelineParallel(MetaParallelBase):
         self._comm_buffers = []
         self.loss_fn_idx = 0
         self.micro_batch_id = 0
+        if self._dp_comm_overlap and self.dp_group is not None and self.dp_group.nranks > 1:
+            self.register_allreduce_overlap_hook(self._layers, self.dp_group, self.accumulate_steps, True)
 
     def _prepare_for_model(self):
         hcg = self._hcg
@@ -128,6 +130,71 @@ class PipelineParallel(MetaParallelBase):
             broadcast_sharding_parameters(self._layers, hcg)
         if hcg.get_data_parallel_world_size() > 1:
             broadcast_dp_parameters(self._layers, hcg)
+
+    # ------------------------------------------------- gradient communication overlapped with the backward pass
+    def fused_gradient(self, model, comm_group, acc_steps, dp, group_size=128 * 1024 * 1024, dst_of=None):
+        """FusedCommBuffers (<= ``group_size`` bytes each) over the trainable parameters of every model chunk.  ``dp``:
+        all-reduce over the data-parallel group; otherwise reduce to the sharding rank that owns the parameters
+        (``dst_of``: parameter -> owner rank, from the sharding optimizer)."""
+        from ..utils.tensor_fusion_helper import HOOK_ACTION, FusedCommBuffer, assign_group_by_size
+        chunks = model.get_model_chunks() if getattr(model, "get_num_virtual_stages", lambda: 1)() > 1 else [model]
+        buffers = []
+        for chunk in chunks:
+            params = [p for p in chunk.parameters() if p.requires_grad]
+            if not params:
+                continue
+            if dp:
+                partitions = {-1: params}
+            else:
+                partitions = {}
+                for prm in params:
+                    partitions.setdefault(dst_of(prm), []).append(prm)
+            for dst, part in sorted(partitions.items()):
+                for ps in assign_group_by_size(part, group_size).values():
+                    buffers.append(FusedCommBuffer(len(self._comm_buffers) + len(buffers), ps, comm_group, acc_steps,
+                                                   HOOK_ACTION.ALL_REDUCE if dp else HOOK_ACTION.REDUCE,
+                                                   dst=-1 if dp else comm_group.ranks[dst]))
+        return buffers
+
+    def bw_hook_func(self, buffer, param):
+        """Backward hook of one parameter: check its gradient into its buffer; the buffer launches its collective
+        (asynchronously, on the communication stream) when every parameter has checked in ``acc_steps`` times - i.e.
+        during the last micro-batch's backward, overlapping the layers still to be differentiated."""
+        def hook(*_):
+            buffer.add_grad(param)
+        return hook
+
+    def register_allreduce_overlap_hook(self, model, comm_group, acc_steps, dp, group_size=128 * 1024 * 1024, dst_of=None):
+        """reference: pipeline_parallel.py register_allreduce_overlap_hook (``pp_configs.dp_comm_overlap`` /
+        ``sharding_comm_overlap``)."""
+        buffers = self.fused_gradient(model, comm_group, acc_steps, dp, group_size, dst_of)
+        for buffer in buffers:
+            for param in buffer.params:
+                param.register_post_accumulate_grad_hook(self.bw_hook_func(buffer, param))
+        self._comm_buffers += buffers
+        return buffers
+
+    def register_sharding_comm_overlap_hook(self, optimizer):
+        """Called with the (sharding) optimizer at the first ``train_batch``: gradients are reduced to their owner rank
+        while the backward pass is still running."""
+        if not self._sharding_comm_overlap or self._comm_buffers:
+            return
+        inner = optimizer
+        while hasattr(inner, "_inner_opt") and not hasattr(inner, "_param2rank"):
+            inner = inner._inner_opt
+        table = getattr(inner, "_param2rank", None)
+        if table is None:
+            raise RuntimeError("sharding_comm_overlap needs the stage-1 sharding optimizer (its parameter -> rank table)")
+        group = self._hcg.get_sharding_parallel_group()
+        self.register_allreduce_overlap_hook(self._layers, group, self.accumulate_steps, False, dst_of=lambda q: table[q.name])
+
+    def _finish_overlapped_comm(self):
+        for buffer in self._comm_buffers:
+            buffer.scale_grads()
+
+    def timer_printer(self):
+        if self._enable_timer and timer.is_timer_initialized():
+            timer.get_timers().log(timer.get_timers().timers.keys())
 
     # ------------------------------------------------------------------ helpers
     def is_pipeline_first_stage(self, ignore_virtual=False):
@@ -168,6 +235,7 @@ class PipelineParallel(MetaParallelBase):
         self.optimizer = optimizer
         self.lr_scheduler = lr_scheduler
         self._layers.train()
+        self.register_sharding_comm_overlap_hook(optimizer)
         return data
 
     def get_static_scheduler(self):
@@ -228,6 +296,7 @@ class PipelineParallel(MetaParallelBase):
             return "".join((f"f{f};" if f is not None else "") + (f"b{b};" if b is not None else "") for f, b in slots)
         self._run_slots_1f1b(slots, self._wrap_data(data))
         self._flush_records()
+        self._finish_overlapped_comm()
         self._layers.allreduce_shared_weight_gradients()
         with torch.no_grad():
             train_loss = self._broadcast_final_loss(return_micro_batch_loss)
@@ -514,6 +583,7 @@ class PipelineParallelWithInterleave(PipelineParallel):
             return self._describe(slots)
         self._run_slots(slots, self._wrap_data_v(data), forward_only, split_turn=self.schedule_mode == "fthenb")
         if not forward_only:
+            self._finish_overlapped_comm()
             self._layers.allreduce_shared_weight_gradients()
         if compute_loss:
             with torch.no_grad():

@@ -66,3 +66,8 @@ def test_moe_expert_parallel_matches_dense():
 
 def test_dist_checkpoint_reshard(tmp_path):
     run_dist("dist_ckpt.py", 2, args=(str(tmp_path),))
+
+
+@pytest.mark.parametrize("mode", ["dp", "dp_overlap", "sharding", "sharding_overlap"])
+def test_pipeline_gradient_comm_overlap_matches_single_process(mode):
+    run_dist("pipeline_overlap.py", 4, args=(mode,))
