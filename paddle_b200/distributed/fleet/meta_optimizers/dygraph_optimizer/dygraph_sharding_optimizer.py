@@ -51,8 +51,35 @@ class DygraphShardingOptimizer:
         local = self._rank2params[self._sharding_rank]
         self._set_inner_opt_attr("_parameter_list", local)
         self._set_inner_opt_attr("_param_groups", [{"params": local}])
-        self.comm_overlap = False
-        self.tensor_fusion = False
+        from paddle_b200.distributed import fleet
+        st = fleet.fleet._user_defined_strategy
+        sc = st.hybrid_configs["sharding_configs"] if st is not None else {}
+        ppc = st.hybrid_configs["pp_configs"] if st is not None else {}
+        self.tensor_fusion = bool(sc.get("tensor_fusion", False))
+        self.comm_overlap = bool(sc.get("comm_overlap", False))
+        self.accumulate_steps = int(sc.get("accumulate_steps", 1))
+        self._use_reduce_avg = bool(sc.get("use_reduce_avg", True))
+        self._comm_buffers = []
+        # the pipeline engine owns the overlap when pp_configs.sharding_comm_overlap is set (it knows the micro-batch count)
+        if (self.tensor_fusion or self.comm_overlap) and not ppc.get("sharding_comm_overlap", False):
+            self._build_fused_buffers(int(sc.get("comm_buffer_size_MB", 256)) << 20)
+
+    def _build_fused_buffers(self, group_bytes):
+        """``tensor_fusion``: the gradients of every owner rank's parameters live in fused buffers, so a step needs one
+        reduce per buffer instead of one per parameter.  ``comm_overlap``: a buffer is reduced from the backward hook of
+        the last of its parameters (after ``accumulate_steps`` backward passes), overlapping the rest of the backward
+        (reference: dygraph_sharding_optimizer.py:120-230, tensor_fusion_helper.fused_parameters)."""
+        for r, ps in sorted(self._rank2params.items()):
+            ps = [q for q in ps if q.requires_grad]
+            if not ps:
+                continue
+            for group in tfh.assign_group_by_size(ps, group_bytes).values():
+                buf = tfh.FusedCommBuffer(len(self._comm_buffers), group, self._group, self.accumulate_steps,
+                                          tfh.HOOK_ACTION.REDUCE, dst=self._group.ranks[r], use_reduce_avg=self._use_reduce_avg)
+                self._comm_buffers.append(buf)
+                if self.comm_overlap:
+                    for q in group:
+                        q.register_post_accumulate_grad_hook(lambda *_, b=buf, prm=q: b.add_grad(prm))
 
     def _set_inner_opt_attr(self, name, value):
         opt = self._inner_opt
@@ -84,6 +111,25 @@ class DygraphShardingOptimizer:
 
     @torch.no_grad()
     def reduce_gradients(self, parameter_list, hcg):
+        if self._comm_buffers:
+            for buf in self._comm_buffers:
+                if not self.comm_overlap:                      # fused, not overlapped: check everything in, then one reduce
+                    buf._params_step_dict = {}
+                    buf._params_checked_in = len(buf.params)
+                    for q in buf.params:
+                        g = _grad_of(q)
+                        view = buf.grad_view(q)
+                        if g is None:
+                            view.zero_()
+                        elif g.data_ptr() != view.data_ptr():
+                            view.copy_(g)
+                        if buf.use_main_grad:
+                            q.main_grad = view
+                        else:
+                            q.grad = view
+                    buf.comm_grads()
+                buf.scale_grads()
+            return
         tasks = []
         for p in parameter_list:
             g = _grad_of(p)

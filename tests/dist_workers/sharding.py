@@ -62,16 +62,21 @@ if mode in ("v1amp", "v2amp"):
         opt.clear_grad()
     assert float(scaler._scale) == 512.0, float(scaler._scale)      # one decrease, on every rank
     ref = reference(STEPS, n, clip=True)
-elif mode in ("v1", "v2"):
+elif mode in ("v1", "v2", "v1fuse", "v1overlap"):
     st = fleet.DistributedStrategy()
     st.hybrid_configs = {"dp_degree": 1, "mp_degree": 1, "pp_degree": 1, "sharding_degree": 2,
-                         "sharding_configs": {"split_param": mode == "v2"}}
+                         "sharding_configs": {"split_param": mode == "v2", "tensor_fusion": mode == "v1fuse",
+                                              "comm_overlap": mode == "v1overlap", "comm_buffer_size_MB": 1}}
     fleet.init(is_collective=True, strategy=st)
     r, n = dist.get_rank(), dist.get_world_size()
     m = build()
     opt = paddle.optimizer.AdamW(1e-2, parameters=m.parameters(), weight_decay=0.01, grad_clip=nn.ClipGradByGlobalNorm(0.5))
     model = fleet.distributed_model(m)
     opt = fleet.distributed_optimizer(opt)
+    if mode in ("v1fuse", "v1overlap"):
+        inner = opt._inner_opt
+        assert inner._comm_buffers and inner.tensor_fusion == (mode == "v1fuse") and inner.comm_overlap == (mode == "v1overlap")
+        assert sum(len(b.params) for b in inner._comm_buffers) == len([p for p in m.parameters() if p.requires_grad])
     for s in range(STEPS):
         x, y = data(s, r)
         ((model(x) - y) ** 2).mean().backward()

@@ -42,7 +42,7 @@ def test_tp_layers_shard_vs_whole():
     run_dist("tp_layers.py", 2)
 
 
-@pytest.mark.parametrize("mode", ["v1", "v2", "v1amp", "v2amp", "stage2", "stage3", "stage2_offload", "stage3_offload"])
+@pytest.mark.parametrize("mode", ["v1", "v1fuse", "v1overlap", "v2", "v1amp", "v2amp", "stage2", "stage3", "stage2_offload", "stage3_offload"])
 def test_sharding_matches_data_parallel(mode):
     run_dist("sharding.py", 2, args=(mode,))
 
