@@ -15,7 +15,7 @@ from ..framework import dtype as _dt
 from ..framework.place import current_place
 from . import debugging  # noqa: F401
 
-_state = {"enable": False, "level": "O0", "dtype": "float32"}
+_state = {"enable": False, "level": "O0", "dtype": "float32", "white": set(), "black": set()}
 
 
 def is_float16_supported(device=None):
@@ -26,20 +26,86 @@ def is_bfloat16_supported(device=None):
     return True
 
 
+# Paddle op names (what the white / black lists hold) -> names of the torch-level functions that implement them here
+_OP_ALIASES = {
+    "matmul": {"matmul", "mm", "bmm", "linear", "addmm", "baddbmm", "einsum"}, "matmul_v2": {"matmul", "mm", "bmm", "linear"},
+    "mul": {"matmul", "mm"}, "conv2d": {"conv2d"}, "conv3d": {"conv3d"}, "conv1d": {"conv1d"},
+    "conv2d_transpose": {"conv_transpose2d"}, "depthwise_conv2d": {"conv2d"},
+    "elementwise_add": {"add", "__add__", "__radd__"}, "elementwise_sub": {"sub", "__sub__", "__rsub__"},
+    "elementwise_mul": {"mul", "multiply", "__mul__", "__rmul__"}, "elementwise_div": {"div", "true_divide", "__truediv__"},
+    "softmax": {"softmax"}, "log_softmax": {"log_softmax"}, "softmax_with_cross_entropy": {"cross_entropy"},
+    "cross_entropy": {"cross_entropy", "nll_loss"}, "layer_norm": {"layer_norm"}, "batch_norm": {"batch_norm"},
+    "group_norm": {"group_norm"}, "reduce_sum": {"sum"}, "reduce_mean": {"mean"}, "mean": {"mean"}, "sum": {"sum"},
+    "exp": {"exp"}, "log": {"log"}, "pow": {"pow", "__pow__"}, "square": {"square"}, "sqrt": {"sqrt"}, "rsqrt": {"rsqrt"},
+    "tanh": {"tanh"}, "sigmoid": {"sigmoid"}, "relu": {"relu"}, "gelu": {"gelu"}, "silu": {"silu"}, "dropout": {"dropout"},
+    "cumsum": {"cumsum"}, "scale": {"mul"}, "lookup_table_v2": {"embedding"}, "embedding": {"embedding"},
+    "flash_attn": {"scaled_dot_product_attention"}, "scaled_dot_product_attention": {"scaled_dot_product_attention"},
+}
+
+
+def _torch_names(op_names):
+    out = set()
+    for n in op_names or ():
+        out |= _OP_ALIASES.get(n, {n})
+    return out
+
+
+class _AmpListMode(torch.overrides.TorchFunctionMode):
+    """User lists on top of torch.autocast: a black-listed op runs in float32 with autocast off, a white-listed op has
+    its floating-point tensor arguments cast to the AMP dtype."""
+
+    def __init__(self, white, black, dtype, device_type):
+        super().__init__()
+        self.white, self.black, self.dtype, self.device_type = white, black, dtype, device_type
+
+    @staticmethod
+    def _cast(obj, dtype):
+        if isinstance(obj, torch.Tensor):
+            return obj.to(dtype) if obj.is_floating_point() and obj.dtype != dtype else obj
+        if isinstance(obj, (list, tuple)):
+            return type(obj)(_AmpListMode._cast(o, dtype) for o in obj)
+        if isinstance(obj, dict):
+            return {k: _AmpListMode._cast(v, dtype) for k, v in obj.items()}
+        return obj
+
+    def __torch_function__(self, func, types, args=(), kwargs=None):
+        kwargs = kwargs or {}
+        name = getattr(func, "__name__", "")
+        if name in self.black:
+            with torch.autocast(device_type=self.device_type, enabled=False):
+                return func(*self._cast(args, torch.float32), **self._cast(kwargs, torch.float32))
+        if name in self.white:
+            return func(*self._cast(args, self.dtype), **self._cast(kwargs, self.dtype))
+        return func(*args, **kwargs)
+
+
 @contextlib.contextmanager
 def auto_cast(enable=True, custom_white_list=None, custom_black_list=None, level="O1", dtype="float16", use_promote=True):
+    """reference: python/paddle/amp/auto_cast.py amp_guard.  ``custom_white_list`` / ``custom_black_list`` hold Paddle op
+    names (``matmul``, ``softmax``, ``elementwise_add`` ...); an op may not be in both."""
     if level not in ("O0", "OD", "O1", "O2"):
         raise ValueError("level should be O0, OD, O1 or O2.")
+    if dtype not in ("float16", "bfloat16") and _dt.to_torch_dtype(dtype) not in (torch.float16, torch.bfloat16):
+        raise ValueError("dtype should be 'float16' or 'bfloat16'.")
+    white_ops, black_ops = set(custom_white_list or ()), set(custom_black_list or ())
+    both = white_ops & black_ops
+    if both:
+        raise ValueError(f"Custom white list overlap custom black list: {sorted(both)}")
     td = _dt.to_torch_dtype(dtype)
     active = bool(enable) and level != "O0"
     dev = "cuda" if current_place().is_gpu_place() else "cpu"
     if dev == "cpu" and td == torch.float16:
         td = torch.bfloat16
     prev = dict(_state)
-    _state.update(enable=active, level=level if active else "O0", dtype=_dt.convert_dtype(td))
+    _state.update(enable=active, level=level if active else "O0", dtype=_dt.convert_dtype(td),
+                  white=white_ops if active else set(), black=black_ops if active else set())
     try:
         with torch.autocast(device_type=dev, dtype=td, enabled=active):
-            yield
+            if active and (white_ops or black_ops):
+                with _AmpListMode(_torch_names(white_ops), _torch_names(black_ops), td, dev):
+                    yield
+            else:
+                yield
     finally:
         _state.clear()
         _state.update(prev)

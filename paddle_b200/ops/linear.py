@@ -67,13 +67,20 @@ class _LinearFn(torch.autograd.Function):
         return dx, dw, db
 
 
+def _amp_black_listed():
+    """``matmul`` / ``linear`` put on auto_cast's custom black list: the product stays in the operands' precision."""
+    from ..amp import _state
+    black = _state.get("black")
+    return bool(black) and bool(black & {"matmul", "matmul_v2", "linear", "mul"})
+
+
 def linear(x, weight, bias=None):
     if hasattr(x, "placements") or hasattr(weight, "placements"):
         # distributed tensors (auto_parallel): the matmul SPMD rule decides resharding, the local product comes back here
         from ..distributed.auto_parallel import dtensor as D
         return D.dist_linear(x, weight, bias)
-    if x.is_cuda and torch.is_autocast_enabled("cuda"):
-        dt = torch.get_autocast_dtype("cuda")
+    if torch.is_autocast_enabled(x.device.type) and not _amp_black_listed():
+        dt = torch.get_autocast_dtype(x.device.type)
         x = x.to(dt)
         weight_c = weight.to(dt)
         bias = bias.to(dt) if bias is not None else None

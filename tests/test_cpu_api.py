@@ -403,3 +403,32 @@ def test_class_method_surface_of_layer_optimizer_scaler():
     assert t.inplace_version == v0 + 1
     with pytest.raises(RuntimeError):
         torch.ones(2, requires_grad=True).apply(lambda v: v)
+
+
+def test_auto_cast_custom_lists():
+    x = torch.randn(4, 8)
+    lin = paddle.nn.Linear(8, 8)
+    with paddle.amp.auto_cast(dtype="bfloat16"):
+        y = lin(x)
+        assert y.dtype == torch.bfloat16
+        assert paddle.amp.amp_state()["enable"]
+    with paddle.amp.auto_cast(dtype="bfloat16", custom_black_list=["matmul"], custom_white_list=["exp", "softmax"]):
+        y = lin(x)
+        assert y.dtype == torch.float32 and torch.matmul(x, x.t()).dtype == torch.float32          # black: stays float32
+        assert torch.exp(y).dtype == torch.bfloat16 and torch.softmax(y, -1).dtype == torch.bfloat16  # white: low precision
+        assert (x + x).dtype == torch.float32                                                       # unlisted: untouched
+    with paddle.amp.auto_cast(dtype="bfloat16", custom_black_list=["elementwise_add"]):
+        b = lin(x)
+        assert (b + b).dtype == torch.float32
+    with paddle.amp.auto_cast(enable=False, custom_black_list=["matmul"]):
+        assert lin(x).dtype == torch.float32 and not paddle.amp.amp_state()["enable"]
+    assert lin(x).dtype == torch.float32 and paddle.amp.amp_state()["black"] == set()
+    with pytest.raises(ValueError):
+        with paddle.amp.auto_cast(custom_white_list=["exp"], custom_black_list=["exp"]):
+            pass
+    with pytest.raises(ValueError):
+        with paddle.amp.auto_cast(level="O3"):
+            pass
+    with pytest.raises(ValueError):
+        with paddle.amp.auto_cast(dtype="float32"):
+            pass
