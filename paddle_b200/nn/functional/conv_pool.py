@@ -585,15 +585,17 @@ def batch_norm(x, running_mean, running_var, weight=None, bias=None, training=Fa
     if not use_batch:
         y = TF.batch_norm(x, running_mean, running_var, weight, bias, False, 0.0, epsilon)
         return _to_cl(y) if cl else y
-    y = TF.batch_norm(x, None, None, weight, bias, True, 0.0, epsilon)
-    if running_mean is not None and running_var is not None:
+    if running_mean is None or running_var is None:
+        y = TF.batch_norm(x, None, None, weight, bias, True, 0.0, epsilon)
+        return _to_cl(y) if cl else y
+    # one pass: the library kernel updates the running statistics with the UNBIASED variance; the biased update the
+    # reference makes follows from it on the C-sized vectors: (new - m old) is (1 - m) var_unbiased, times (n - 1) / n
+    n = x.numel() // x.shape[1]
+    old_var = running_var.detach().clone()
+    y = TF.batch_norm(x, running_mean, running_var, weight, bias, True, 1.0 - momentum, epsilon)
+    if n > 1:
         with torch.no_grad():
-            dims = [0] + list(range(2, x.dim()))
-            xf = x.detach().float()
-            mean = xf.mean(dims)
-            var = xf.var(dims, unbiased=False)
-            running_mean.mul_(momentum).add_(mean.to(running_mean.dtype), alpha=1.0 - momentum)
-            running_var.mul_(momentum).add_(var.to(running_var.dtype), alpha=1.0 - momentum)
+            running_var.copy_(old_var * momentum + (running_var - old_var * momentum) * ((n - 1) / n))
     return _to_cl(y) if cl else y
 
 
