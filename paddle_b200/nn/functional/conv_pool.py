@@ -591,11 +591,16 @@ def batch_norm(x, running_mean, running_var, weight=None, bias=None, training=Fa
     # one pass: the library kernel updates the running statistics with the UNBIASED variance; the biased update the
     # reference makes follows from it on the C-sized vectors: (new - m old) is (1 - m) var_unbiased, times (n - 1) / n
     n = x.numel() // x.shape[1]
-    old_var = running_var.detach().clone()
-    y = TF.batch_norm(x, running_mean, running_var, weight, bias, True, 1.0 - momentum, epsilon)
-    if n > 1:
-        with torch.no_grad():
-            running_var.copy_(old_var * momentum + (running_var - old_var * momentum) * ((n - 1) / n))
+    # the kernel may keep the variance buffer it was given for its backward pass, so it gets a scratch copy and the
+    # real buffer is written once, afterwards
+    new_var = running_var.detach().clone()
+    y = TF.batch_norm(x, running_mean, new_var, weight, bias, True, 1.0 - momentum, epsilon)
+    with torch.no_grad():
+        if n > 1:
+            keep = running_var * momentum
+            running_var.copy_(keep + (new_var - keep) * ((n - 1) / n))
+        else:
+            running_var.copy_(new_var)
     return _to_cl(y) if cl else y
 
 

@@ -1,6 +1,7 @@
 """Paddle semantics of paddle.nn.functional where they differ from torch.nn.functional (reference:
 python/paddle/nn/functional/*.py), against numpy / explicit torch restatements."""
 import numpy as np
+import pytest
 import torch
 import torch.nn.functional as TF
 
@@ -195,3 +196,42 @@ def test_default_initializers_follow_the_reference():
     assert float((t @ t.t() - torch.eye(6)).abs().max()) < 1e-5
     assert float((mk([4, 4], I.Assign(torch.eye(4))) - torch.eye(4)).abs().sum()) == 0
     assert float(mk([3], I.Constant(2.5)).sum()) == 7.5 and abs(float(mk([2000], I.Uniform(-0.5, 0.5)).abs().max()) - 0.5) < 5e-3
+
+
+def test_weight_norm_parameter_layout_and_copy():
+    """Reference: python/paddle/nn/utils/weight_norm_hook.py — ``weight_g`` is 1-D (``shape[dim]`` entries, one for
+    ``dim=None``), ``weight_v`` keeps the weight's shape, the weight is rebuilt before every forward."""
+    import copy
+    import paddle.nn as nn
+    from paddle.nn.utils import weight_norm, remove_weight_norm
+    lin = nn.Linear(4, 3)
+    w0 = lin.weight.detach().clone()
+    weight_norm(lin, dim=1)
+    assert sorted(n for n, _ in lin.named_parameters()) == ["bias", "weight_g", "weight_v"]
+    assert tuple(lin.weight_g.shape) == (3,) and tuple(lin.weight_v.shape) == (4, 3)
+    torch.testing.assert_close(lin.weight_g.detach(), w0.norm(dim=0))
+    x = torch.randn(5, 4)
+    y = lin(x)
+    torch.testing.assert_close(y, x @ w0 + lin.bias)
+    y.sum().backward()
+    assert lin.weight_g.grad is not None and lin.weight_v.grad is not None
+    with torch.no_grad():
+        lin.weight_g.mul_(2.0)
+    torch.testing.assert_close(lin(x), x @ (2 * w0) + lin.bias)
+    assert sorted(lin.state_dict()) == ["bias", "weight_g", "weight_v"]
+    remove_weight_norm(lin)
+    assert sorted(n for n, _ in lin.named_parameters()) == ["bias", "weight"]
+    torch.testing.assert_close(lin.weight.detach(), 2 * w0)
+    conv = nn.Conv2D(3, 6, 3)
+    weight_norm(conv)                                   # dim=0
+    assert tuple(conv.weight_g.shape) == (6,)
+    whole = nn.Conv2D(3, 6, 3)
+    k0 = whole.weight.detach().clone()
+    weight_norm(whole, dim=None)
+    assert tuple(whole.weight_g.shape) == (1,)
+    torch.testing.assert_close(whole.weight_g.detach(), k0.norm().reshape(1))
+    img = torch.randn(1, 3, 5, 5)
+    twin = copy.deepcopy(conv)
+    torch.testing.assert_close(twin(img), conv(img))
+    with pytest.raises(ValueError):
+        remove_weight_norm(nn.Linear(2, 2))
