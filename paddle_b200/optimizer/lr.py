@@ -31,11 +31,26 @@ class LRScheduler:
         self.keys = ["last_epoch", "last_lr"]
 
     def state_dict(self):
-        return {"last_epoch": self.last_epoch, "last_lr": self.last_lr}
+        """Reference: python/paddle/optimizer/lr.py:178-199 -- the attributes ``state_keys`` names, tensors as floats."""
+        self.state_keys()
+        out = {}
+        for key in self.keys:
+            if key not in self.__dict__:
+                continue
+            value = self.__dict__[key]
+            if hasattr(value, "numel") and hasattr(value, "item"):
+                assert value.numel() == 1, "numel of Tensor in state_dict must be 1"
+                value = float(value.item())
+            out[key] = value
+        return out
 
     def set_state_dict(self, sd):
-        self.last_epoch = sd.get("last_epoch", self.last_epoch)
-        self.last_lr = sd.get("last_lr", self.last_lr)
+        self.state_keys()
+        for key in self.keys:
+            if key in sd:
+                self.__dict__[key] = sd[key]
+            else:
+                raise RuntimeError(f"Please check whether state_dict is correct for optimizer. Can't find [ {key} ] in state_dict")
 
     set_dict = set_state_dict
 
@@ -208,31 +223,46 @@ class ReduceOnPlateau(LRScheduler):
                  cooldown=0, min_lr=0, epsilon=1e-8, verbose=False):
         self.mode, self.factor, self.patience, self.threshold = mode, factor, patience, threshold
         self.threshold_mode, self.cooldown, self.min_lr, self.epsilon = threshold_mode, cooldown, min_lr, epsilon
-        self.best, self.num_bad, self.cooldown_counter = None, 0, 0
+        self.best, self.num_bad_epochs, self.cooldown_counter = None, 0, 0
         self.base_lr = self.last_lr = float(learning_rate)
         self.last_epoch = 0
         self.verbose = verbose
 
+    def state_keys(self):
+        self.keys = ["cooldown_counter", "best", "num_bad_epochs", "last_epoch", "last_lr"]
+
+    def _is_better(self, current, best):
+        # reference: python/paddle/optimizer/lr.py:1556-1567 -- the relative margin is best * threshold, sign and all
+        margin = best * self.threshold if self.threshold_mode == "rel" else self.threshold
+        return current < best - margin if self.mode == "min" else current > best + margin
+
     def step(self, metrics=None, epoch=None):
+        """Reference: python/paddle/optimizer/lr.py:1501-1554.  While cooling down the metric is not looked at at all
+        (neither ``best`` nor the bad-epoch count moves); otherwise a non-improving epoch counts as bad and the rate
+        drops once more than ``patience`` of them have piled up."""
         self.last_epoch = self.last_epoch + 1 if epoch is None else epoch
         if metrics is None:
             return
+        if hasattr(metrics, "size") and not isinstance(metrics, (int, float)):
+            size = metrics.numel() if hasattr(metrics, "numel") else metrics.size
+            assert size == 1, f"the size of metrics must be 1, but the current metrics.size is {size}"
+        elif not isinstance(metrics, (int, float)):
+            raise TypeError(f"metrics must be a number, a numpy.ndarray or a Tensor, but received {type(metrics)}")
         m = float(metrics.item() if hasattr(metrics, "item") else metrics)
-        better = self.best is None or (m < self.best - (abs(self.best) * self.threshold if self.threshold_mode == "rel" else self.threshold)
-                                       if self.mode == "min" else
-                                       m > self.best + (abs(self.best) * self.threshold if self.threshold_mode == "rel" else self.threshold))
-        if better:
-            self.best, self.num_bad = m, 0
-        else:
-            self.num_bad += 1
         if self.cooldown_counter > 0:
             self.cooldown_counter -= 1
-            self.num_bad = 0
-        if self.num_bad > self.patience:
+            return
+        if self.best is None or self._is_better(m, self.best):
+            self.best, self.num_bad_epochs = m, 0
+        else:
+            self.num_bad_epochs += 1
+        if self.num_bad_epochs > self.patience:
+            self.cooldown_counter, self.num_bad_epochs = self.cooldown, 0
             new_lr = max(self.last_lr * self.factor, self.min_lr)
             if self.last_lr - new_lr > self.epsilon:
                 self.last_lr = new_lr
-            self.cooldown_counter, self.num_bad = self.cooldown, 0
+                if self.verbose:
+                    print(f"Epoch {self.last_epoch}: {type(self).__name__} set learning rate to {self.last_lr}.")
 
 
 class MultiplicativeDecay(LRScheduler):
