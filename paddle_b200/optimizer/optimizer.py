@@ -31,6 +31,14 @@ def _grad_of(p):
 
 class Optimizer:
     _acc_names: tuple = ()
+    # who adds the regulariser (the ``weight_decay`` argument, or a parameter's own ``regularizer``) to the gradient:
+    #   "grad"      the base class does, after clipping (reference: optimizer.py _apply_optimize -> append_regularization_ops)
+    #   "kernel"    the update rule adds ``coeff * p`` itself (L2 only; the reference fuses it the same way in momentum)
+    #   "decoupled" ``weight_decay`` is not a regulariser (AdamW, Lamb); only a parameter's own regulariser reaches the gradient
+    _decay_mode = "grad"
+    # True when the update masks itself on the GradScaler's device flag; otherwise the base class reads the flag and
+    # skips the whole step, as the reference's scaler does (python/paddle/amp/grad_scaler.py: step -> _found_inf)
+    _masks_found_inf = False
 
     def __init__(self, learning_rate, parameters=None, weight_decay=None, grad_clip=None, name=None,
                  multi_precision=False):
@@ -164,13 +172,51 @@ class Optimizer:
                 params_grads = self._grad_clip(params_grads)
         if not params_grads:
             return
+        if self._found_inf is not None and not self._masks_found_inf and bool((self._found_inf > 0).any()):
+            return
         try:
+            params_grads = self._regularize(params_grads)
             self._create_accumulators([p for p, _ in params_grads])
             self._update(params_grads)
         finally:
             if folded:
                 self._grad_scale_dev = prev
         self._step_count += 1
+
+    def _regularize(self, params_grads):
+        """Gradients with the regulariser added, according to ``_decay_mode``.  A device-side gradient scale that the
+        update applies later (folded clip coefficient, deferred unscale) is divided out of the added term, so the
+        update sees ``scale * g + reg(p)`` as if the gradient had been scaled first."""
+        from ..regularizer import L1Decay
+        mode = self._decay_mode
+        own_any = any(getattr(p, "regularizer", None) is not None for p, _ in params_grads)
+        if mode == "grad":
+            if not own_any and self.regularization is None and not any("weight_decay" in g for g in self._param_groups):
+                return params_grads
+        elif not own_any and not (mode == "kernel" and any(
+                isinstance(g.get("weight_decay", self.regularization), L1Decay) for g in self._param_groups)):
+            return params_grads
+        scale = self._grad_scale_dev
+        out = []
+        for p, g in params_grads:
+            grp = self._group_of(p)
+            default = grp.get("weight_decay", self.regularization)
+            own = getattr(p, "regularizer", None)
+            if mode == "decoupled":
+                default = None
+            if own is None and (default is None or (mode == "kernel" and not isinstance(default, L1Decay))):
+                out.append((p, g))
+                continue
+            zero = torch.zeros_like(g)
+            (_, term), = self.append_regularization_ops([(p, zero)], default if default is not None else 0.0)
+            if mode == "kernel":
+                c = self._coeff(grp)           # the update will add c * p on its own: take it back out here
+                if c:
+                    term = term - c * p.detach().to(g.dtype)
+            if scale is not None:
+                term = term / scale.to(term.dtype)
+            out.append((p, g + term))
+        return out
 
     def _can_fold_clip(self, params_grads):
         from ..nn.clip import ClipGradByGlobalNorm
@@ -309,6 +355,8 @@ def _np_to_t(v):
 
 # ======================================================================================= SGD / Momentum
 class SGD(Optimizer):
+    _decay_mode = "kernel"
+    _masks_found_inf = True
     def __init__(self, learning_rate=0.001, parameters=None, weight_decay=None, grad_clip=None, multi_precision=False,
                  name=None):
         super().__init__(learning_rate, parameters, weight_decay, grad_clip, name, multi_precision)
@@ -396,6 +444,7 @@ class Momentum(SGD):
 # ======================================================================================= Adam / AdamW
 class Adam(Optimizer):
     _decoupled = False
+    _masks_found_inf = True
     _fold_clip_ok = True      # the native kernel multiplies grads by a device scalar
 
     def __init__(self, learning_rate=0.001, beta1=0.9, beta2=0.999, epsilon=1e-08, parameters=None, weight_decay=None,
@@ -405,6 +454,9 @@ class Adam(Optimizer):
         self._beta_pows = {}   # device -> fp32[2] (beta1^t, beta2^t)
 
     def _coeff(self, group):
+        """Decoupled decay coefficient; plain Adam has none (its regulariser is added to the gradients by the base)."""
+        if not self._decoupled:
+            return 0.0
         wd = group.get("weight_decay", self.regularization)
         if wd is None:
             return 0.0
@@ -521,6 +573,7 @@ class Adam(Optimizer):
 class AdamW(Adam):
     """Decoupled weight decay: ``p *= 1 - lr * coeff`` before the Adam update (adamw_kernel.cu:35-130)."""
     _decoupled = True
+    _decay_mode = "decoupled"
 
     def __init__(self, learning_rate=0.001, beta1=0.9, beta2=0.999, epsilon=1e-08, parameters=None, weight_decay=0.01,
                  lr_ratio=None, apply_decay_param_fun=None, grad_clip=None, lazy_mode=False, multi_precision=False,
@@ -587,6 +640,12 @@ class RMSProp(Optimizer):
 
 class Lamb(Adam):
     _fold_clip_ok = False
+    _decay_mode = "decoupled"  # lamb_weight_decay enters the trust-ratio update, not the gradient
+    _masks_found_inf = False
+
+    def _coeff(self, group):
+        wd = group.get("weight_decay", self.regularization)
+        return 0.0 if wd is None else float(getattr(wd, "_coeff", getattr(wd, "coeff", wd)))
 
     def __init__(self, learning_rate=0.001, lamb_weight_decay=0.01, beta1=0.9, beta2=0.999, epsilon=1e-06,
                  parameters=None, grad_clip=None, exclude_from_weight_decay_fn=None, multi_precision=False,
@@ -727,28 +786,40 @@ class RAdam(Optimizer):
 
 
 class ASGD(Optimizer):
-    """Averaged-gradient SGD over the last ``batch_num`` gradients (reference: python/paddle/optimizer/asgd.py)."""
+    """Stochastic average gradient over the last ``batch_num`` gradients (reference: python/paddle/optimizer/asgd.py:
+    30-45 for the rule, 146-168 for the state).  Per parameter: ``d`` the running sum of the kept gradients, ``y`` the
+    ``[batch_num, *shape]`` ring of them, ``m`` the step count; all three are accumulators, so they are saved."""
 
     def __init__(self, learning_rate=0.001, batch_num=1, parameters=None, weight_decay=None, grad_clip=None,
                  multi_precision=False, name=None):
+        if batch_num is None or batch_num <= 0:
+            raise ValueError("batch_num should be greater than 0")
         super().__init__(learning_rate, parameters, weight_decay, grad_clip, name)
         self._n = int(batch_num)
-        self._step_i = 0
-        self._hist = {}
+        self._multi_precision = multi_precision
+
+    def _create_accumulators(self, params):
+        for p in params:
+            if self._use_master(p):
+                self._create_master_weight(p)
+            self._add_accumulator("d", p)
+            self._add_accumulator("y", p, shape=[self._n] + list(p.shape))
+            self._add_accumulator("m", p, dtype=torch.int64, shape=[1])
 
     def _update(self, params_grads):
         lr = self.get_lr()
-        slot = self._step_i % self._n
-        self._step_i += 1
-        m = min(self._step_i, self._n)
         for p, g in params_grads:
-            h = self._hist.setdefault(id(p), dict(sum=torch.zeros_like(p, dtype=torch.float32), ys=[None] * self._n))
+            d, ys, m = self._get_accumulator("d", p), self._get_accumulator("y", p), self._get_accumulator("m", p)
+            step = int(m.item())
+            slot = step % self._n
             gf = g.float()
-            if h["ys"][slot] is not None:
-                h["sum"].sub_(h["ys"][slot])
-            h["ys"][slot] = gf.clone()
-            h["sum"].add_(gf)
-            p.sub_((lr * h["sum"] / m).to(p.dtype))
+            d.add_(gf - ys[slot])
+            ys[slot].copy_(gf)
+            m.add_(1)
+            target = self._master_weights[p.name] if self._use_master(p) else p
+            target.sub_((lr * d / min(step + 1, self._n)).to(target.dtype))
+            if target is not p:
+                p.copy_(target.to(p.dtype))
 
 
 class Rprop(Optimizer):
